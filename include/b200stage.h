@@ -1,0 +1,134 @@
+/* b200stage -- C ABI of the B200-native W8A8 decoder-block hot path.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no torch types, no C++ exceptions.
+ * Every pointer is a DEVICE pointer unless said otherwise; `stream` is a cudaStream_t passed
+ * as void* (NULL = legacy default stream).  All calls are asynchronous with respect to `stream`,
+ * re-entrant, and allocate nothing: every buffer, including workspaces, belongs to the caller.
+ * Return value: 0 (B2_OK) or a negative B2_ERR_* code; b2_strerror() names it.  An unsupported
+ * shape is an error, never a silent fallback.
+ *
+ * The reference (parthabp55/LLM-for-Distributed-Egde-Devices) has no FFI or native code; its
+ * decoder-block forward runs inside third-party modules reached from the call sites cited per
+ * entry point below (paths relative to the reference root).  "Replaces" therefore names the
+ * reference call site plus the third-party routine (transformers 5.5.0 paths under
+ * site-packages/transformers/) whose work the entry point takes over.
+ */
+#ifndef B200STAGE_H
+#define B200STAGE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2_OK 0
+#define B2_ERR_BAD_SHAPE (-1)
+#define B2_ERR_BAD_ALIGN (-2)   /* pointers must be 16-byte aligned */
+#define B2_ERR_NULL_PTR (-3)
+#define B2_ERR_ARCH (-4)        /* not an sm_100 device / attribute set failed */
+#define B2_ERR_LAUNCH (-5)
+#define B2_ERR_UNSUPPORTED (-6)
+#define B2_ERR_DRIVER (-7)      /* cuTensorMapEncodeTiled unavailable or failed */
+#define B2_ERR_TOO_LARGE (-8)
+
+/* Library version (major*10000 + minor*100 + patch). */
+int b2_version(void);
+/* Static string for an error code. */
+const char* b2_strerror(int code);
+
+/* Fused (RMSNorm | LayerNorm) -> smoothing multiply -> per-token absmax int8 quantise.
+ * x [T,d] fp16; gamma [d] fp16; beta [d] fp16 or NULL (NULL selects RMSNorm); smooth [d] fp32 or
+ * NULL (the SmoothQuant 1/s multiplier); q [T,d] int8; row_scale [T] fp32 (amax/127).
+ * Replaces: `input_layernorm` / `post_attention_layernorm` (models/llama/modeling_llama.py:62-67,
+ * :303-334) plus the activation-quantising half of the int8 linear requested at
+ * Code/Quantised Models/models_quant_updated.py:30-38 (bitsandbytes Linear8bitLt) and
+ * Code/C-DAC Server/try.py:205 (quantize_dynamic). */
+int b2_norm_quant(const void* x, const void* gamma, const void* beta, const float* smooth, int8_t* q,
+                  float* row_scale, int T, int d, float eps, void* stream);
+
+/* Norm only, fp16 result y [T,d] (the final norm before lm_head).
+ * Replaces: `model.norm` (modeling_llama.py:62-67) reached from models_quant_updated.py:66-67, :84-93. */
+int b2_norm(const void* x, const void* gamma, const void* beta, void* y, int T, int d, float eps, void* stream);
+
+/* fp16 activation [T,K] -> smoothing multiply -> per-token int8 (input of o_proj).
+ * Replaces: the activation quantisation inside Linear8bitLt for `o_proj` (models_quant_updated.py:30-38). */
+int b2_smooth_quant(const void* x, const float* smooth, int8_t* q, float* row_scale, int T, int K, void* stream);
+
+/* act(gate)*up -> smoothing -> per-token int8 (input of down_proj).  gate_up [T,2F] fp16, gate in
+ * columns [0,F), up in [F,2F).  act: 0 silu*up, 1 gelu_new*up, 2 gelu_new (ungated, input [T,F]),
+ * 3 silu (ungated).
+ * Replaces: `act_fn(gate_proj(x)) * up_proj(x)` (modeling_llama.py:182-184) plus the activation
+ * quantisation of `down_proj`. */
+int b2_act_mul_quant(const void* gate_up, const float* smooth, int8_t* q, float* row_scale, int T, int F, int act,
+                     void* stream);
+
+/* W8A8 linear with fused dequantise + bias + residual epilogue.
+ * A [M,K] int8 row-major; W [N,K] int8 row-major; a_scale [M], w_scale [N] fp32; bias [N] fp16 or
+ * NULL; residual [M,N] fp16 or NULL; out [M,N] fp16; acc_dump [M,N] int32 or NULL (test hook: the
+ * raw accumulators).  K % 16 == 0, N % 8 == 0.
+ * out = fp16(((float)acc * a_scale[m]) * w_scale[n] + bias[n] + residual[m,n]).
+ * Replaces: every nn.Linear of the decoder layer as swapped for bitsandbytes Linear8bitLt by
+ * `BitsAndBytesConfig(load_in_8bit=True)` (models_quant_updated.py:30-38; combiner_quant_updated.py:37)
+ * or torch.ao dynamic qint8 Linear (try.py:205). */
+int b2_gemm_w8a8(const int8_t* A, const int8_t* W, const float* a_scale, const float* w_scale, const void* bias,
+                 const void* residual, void* out, int32_t* acc_dump, int M, int N, int K, void* stream);
+/* Same, with the schedule forced: 1 = tcgen05 tensor-core path, 2 = dp4a streaming path (M <= 8).
+ * Test hook so both schedules are checked on the same inputs. */
+int b2_gemm_w8a8_sched(const int8_t* A, const int8_t* W, const float* a_scale, const float* w_scale,
+                       const void* bias, const void* residual, void* out, int32_t* acc_dump, int M, int N, int K,
+                       int schedule, void* stream);
+
+/* Rotary embedding of q and k (in fp32 from a caller-supplied cos/sin table [max_pos, hd/2] fp32)
+ * and append of rotated k and v to the KV cache.  qkv [T, ld] fp16: q heads at columns
+ * [0,H*hd), k at [H*hd,(H+KV)*hd), v after; q is rotated in place.  positions [T] int32;
+ * seq_ids [T] int32 cache row per token, or NULL for row `seq0`.  Caches: [rows][KV][Smax][hd] fp16.
+ * use_rope = 0 skips the rotation (GPT-2).
+ * Replaces: apply_rotary_pos_emb + DynamicCache.update (modeling_llama.py:128-153, :251-289). */
+int b2_rope_kv_append(void* qkv, long long ld, const float* cos_table, const float* sin_table, const int* positions,
+                      const int* seq_ids, int seq0, void* kcache, void* vcache, int T, int H, int KV, int hd,
+                      int Smax, int use_rope, void* stream);
+
+/* Decode attention (one query token per sequence) over the KV cache.
+ * q: token b's heads at q + b*q_ld (fp16, H*hd contiguous); seqlens [B] int32 = keys valid per
+ * sequence INCLUDING the token just appended; rows [B] int32 cache row per sequence or NULL (= b);
+ * out: token b at out + b*o_ld.  window = 0 for full attention, else sliding window size.
+ * max_seqlen: host-side upper bound of seqlens (chooses the kv split count without a device read).
+ * workspace: scratch for the split-KV partials, at least b2_decode_attn_workspace_bytes(...) bytes;
+ * may be NULL/short, in which case fewer splits are used.
+ * Replaces: eager_attention_forward at q_len = 1 (modeling_llama.py:199-222) inside the decode
+ * loop of `model.generate` (models_quant_updated.py:84-93). */
+int b2_decode_attn(const void* q, long long q_ld, const void* kcache, const void* vcache, const int* seqlens,
+                   const int* rows, void* out, long long o_ld, void* workspace, size_t workspace_bytes, int B, int H,
+                   int KV, int hd, int Smax, int max_seqlen, float scale, int window, void* stream);
+/* Bytes of workspace b2_decode_attn wants for these sizes (0 if it will not split). */
+size_t b2_decode_attn_workspace_bytes(int B, int H, int KV, int hd, int max_seqlen, int window);
+
+/* Causal (optionally sliding-window) attention for one contiguous chunk of T query tokens of one
+ * sequence at positions [pos0, pos0+T), keys 0..pos0+T-1 read from cache row `row` (the chunk's
+ * own k/v must already be appended).
+ * Replaces: eager_attention_forward at q_len > 1 (modeling_llama.py:199-222): the prefill forward
+ * of `generate` and the `model(**inputs).logits` pass of confidence_score
+ * (models_quant_updated.py:63-70). */
+int b2_prefill_attn(const void* q, long long q_ld, const void* kcache, const void* vcache, void* out, long long o_ld,
+                    int T, int pos0, int row, int H, int KV, int hd, int Smax, float scale, int window, void* stream);
+
+/* Token (+ learned position) embedding gather.  ids [T] int64; positions [T] int32 (only read
+ * when pos_table != NULL); tables fp16 [vocab,d] / [max_pos,d]; out [T,d] fp16.
+ * Replaces: `embed_tokens` (and GPT-2 `wpe`) at the head of `model(**inputs)` (models_quant_updated.py:66). */
+int b2_embed(const long long* ids, const int* positions, const void* table, const void* pos_table, void* out, int T,
+             int d, int vocab, void* stream);
+
+/* Unquantised lm_head: logits [M,V] fp32 = x [M,d] fp16 . W [V,d]^T fp16 (fp32 accumulate).
+ * Replaces: `lm_head` (left unquantised by load_in_8bit; models_quant_updated.py:66-67 `.logits`). */
+int b2_lm_head(const void* x, const void* W, float* logits, int M, int V, int d, void* stream);
+
+/* Row-wise argmax of fp32 logits [T,V] -> int64 [T]; ties to the lowest index.
+ * Replaces: the greedy (do_sample=False) token selection of `generate`. */
+int b2_argmax(const float* logits, long long* out, int T, int V, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200STAGE_H */

@@ -1,0 +1,100 @@
+"""Model shapes for the decoder families the stage path serves.
+
+The dims are the public HF configs of the models BASELINE.json:configs names;
+the reference itself only ever loads whole checkpoints by path
+(Code/Quantised Models/models_quant_updated.py:34-38) and ships no config of its own.
+"""
+from __future__ import annotations
+
+import json
+import os
+from dataclasses import dataclass, asdict
+
+
+@dataclass(frozen=True)
+class ModelConfig:
+    name: str
+    n_layers: int
+    d_model: int
+    n_heads: int
+    n_kv_heads: int
+    head_dim: int
+    ffn: int
+    vocab: int
+    eps: float = 1e-5
+    rope_theta: float = 10000.0
+    window: int = 0            # sliding-window size, 0 = full attention
+    max_pos: int = 4096
+    act: str = "silu"          # "silu" | "gelu_new"
+    gated: bool = True         # gate/up MLP (Llama) vs single up projection (GPT-2)
+    norm: str = "rms"          # "rms" | "layernorm"
+    rope: bool = True          # False -> learned absolute positions (GPT-2)
+    bias: bool = False         # linear layers carry a bias (GPT-2)
+    tie_embeddings: bool = True
+
+    @property
+    def qkv_out(self) -> int:
+        return (self.n_heads + 2 * self.n_kv_heads) * self.head_dim
+
+    @property
+    def up_out(self) -> int:
+        return (2 if self.gated else 1) * self.ffn
+
+    def linear_params_per_layer(self) -> int:
+        d = self.d_model
+        return self.qkv_out * d + d * self.n_heads * self.head_dim + self.up_out * d + d * self.ffn
+
+    def kernel_cfg(self) -> dict:
+        """The plain-dict view the oracle consumes."""
+        return dict(n_heads=self.n_heads, n_kv_heads=self.n_kv_heads, head_dim=self.head_dim, eps=self.eps,
+                    rope_theta=self.rope_theta, window=self.window, act=self.act, gated=self.gated, rope=self.rope)
+
+    def to_dict(self) -> dict:
+        return asdict(self)
+
+
+PRESETS = {
+    "gpt2": ModelConfig("gpt2", 12, 768, 12, 12, 64, 3072, 50257, eps=1e-5, max_pos=1024, act="gelu_new",
+                        gated=False, norm="layernorm", rope=False, bias=True),
+    "tinyllama-1.1b": ModelConfig("tinyllama-1.1b", 22, 2048, 32, 4, 64, 5632, 32000, max_pos=2048),
+    "llama-2-7b": ModelConfig("llama-2-7b", 32, 4096, 32, 32, 128, 11008, 32000, max_pos=4096),
+    "llama-2-13b": ModelConfig("llama-2-13b", 40, 5120, 40, 40, 128, 13824, 32000, max_pos=4096),
+    "mistral-7b": ModelConfig("mistral-7b", 32, 4096, 32, 8, 128, 14336, 32000, window=4096, max_pos=32768),
+    # small shapes for tests (same structure, seconds on the CPU oracle)
+    "tiny-llama-test": ModelConfig("tiny-llama-test", 4, 256, 4, 4, 64, 512, 512, max_pos=512),
+    "tiny-gqa-test": ModelConfig("tiny-gqa-test", 4, 512, 8, 2, 64, 1024, 1024, window=0, max_pos=512),
+    "tiny-window-test": ModelConfig("tiny-window-test", 2, 256, 4, 2, 64, 512, 512, window=48, max_pos=512),
+    "tiny-hd128-test": ModelConfig("tiny-hd128-test", 2, 512, 4, 4, 128, 1024, 512, max_pos=512),
+}
+
+
+def get_config(spec) -> ModelConfig:
+    """Preset name, ModelConfig, dict, or a HF model dir / config.json (the reference's
+    `from_pretrained(model_path)` convention, models_quant_updated.py:25-38)."""
+    if isinstance(spec, ModelConfig):
+        return spec
+    if isinstance(spec, dict):
+        return from_hf_dict(spec) if "hidden_size" in spec or "n_embd" in spec else ModelConfig(**spec)
+    if spec in PRESETS:
+        return PRESETS[spec]
+    path = spec
+    if os.path.isdir(path):
+        path = os.path.join(path, "config.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return from_hf_dict(json.load(f))
+    raise ValueError(f"unknown model spec {spec!r}")
+
+
+def from_hf_dict(c: dict) -> ModelConfig:
+    if c.get("model_type") == "gpt2" or "n_embd" in c:
+        d, h = c["n_embd"], c["n_head"]
+        return ModelConfig(c.get("_name_or_path", "gpt2"), c["n_layer"], d, h, h, d // h, c.get("n_inner") or 4 * d,
+                           c["vocab_size"], eps=c.get("layer_norm_epsilon", 1e-5), max_pos=c.get("n_positions", 1024),
+                           act="gelu_new", gated=False, norm="layernorm", rope=False, bias=True)
+    d, h = c["hidden_size"], c["num_attention_heads"]
+    return ModelConfig(c.get("_name_or_path", c.get("model_type", "llama")), c["num_hidden_layers"], d, h,
+                       c.get("num_key_value_heads", h), c.get("head_dim") or d // h, c["intermediate_size"],
+                       c["vocab_size"], eps=c.get("rms_norm_eps", 1e-5), rope_theta=c.get("rope_theta", 10000.0),
+                       window=c.get("sliding_window") or 0, max_pos=c.get("max_position_embeddings", 4096),
+                       tie_embeddings=c.get("tie_word_embeddings", False))

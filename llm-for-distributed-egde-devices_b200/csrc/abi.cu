@@ -1,0 +1,105 @@
+// extern "C" surface of libb200stage.so -- see include/b200stage.h for the contract.
+#include "common.cuh"
+#include "../../include/b200stage.h"
+
+namespace b2 {
+int norm_quant(const void*, const void*, const void*, const float*, int8_t*, float*, int, int, float, cudaStream_t);
+int norm_f16(const void*, const void*, const void*, void*, int, int, float, cudaStream_t);
+int smooth_quant(const void*, const float*, int8_t*, float*, int, int, cudaStream_t);
+int act_mul_quant(const void*, const float*, int8_t*, float*, int, int, int, cudaStream_t);
+int gemm_w8a8(const int8_t*, const int8_t*, const float*, const float*, const void*, const void*, void*, int32_t*, int,
+              int, int, int, cudaStream_t);
+int lm_head(const void*, const void*, float*, int, int, int, cudaStream_t);
+int rope_kv_append(void*, long long, const float*, const float*, const int*, const int*, int, void*, void*, int, int,
+                   int, int, int, int, cudaStream_t);
+int decode_attn(const void*, long long, const void*, const void*, const int*, const int*, void*, long long, void*,
+                size_t, int, int, int, int, int, int, float, int, cudaStream_t);
+int decode_attn_splits(int, int, int, int);
+size_t decode_attn_workspace_bytes(int, int, int, int);
+int prefill_attn(const void*, long long, const void*, const void*, void*, long long, int, int, int, int, int, int, int,
+                 float, int, cudaStream_t);
+int embed(const long long*, const int*, const void*, const void*, void*, int, int, int, cudaStream_t);
+int argmax_rows(const float*, long long*, int, int, cudaStream_t);
+}  // namespace b2
+
+#define ST(s) reinterpret_cast<cudaStream_t>(s)
+
+extern "C" {
+
+int b2_version(void) { return 100; }
+
+const char* b2_strerror(int code) {
+  switch (code) {
+    case B2_OK: return "ok";
+    case B2_ERR_BAD_SHAPE: return "bad shape";
+    case B2_ERR_BAD_ALIGN: return "pointer not 16-byte aligned";
+    case B2_ERR_NULL_PTR: return "null pointer";
+    case B2_ERR_ARCH: return "device/attribute not supported (sm_100a required)";
+    case B2_ERR_LAUNCH: return "kernel launch failed";
+    case B2_ERR_UNSUPPORTED: return "unsupported configuration";
+    case B2_ERR_DRIVER: return "cuTensorMapEncodeTiled unavailable or failed";
+    case B2_ERR_TOO_LARGE: return "size exceeds the supported maximum";
+    default: return "unknown error";
+  }
+}
+
+int b2_norm_quant(const void* x, const void* gamma, const void* beta, const float* smooth, int8_t* q, float* row_scale,
+                  int T, int d, float eps, void* stream) {
+  return b2::norm_quant(x, gamma, beta, smooth, q, row_scale, T, d, eps, ST(stream));
+}
+int b2_norm(const void* x, const void* gamma, const void* beta, void* y, int T, int d, float eps, void* stream) {
+  return b2::norm_f16(x, gamma, beta, y, T, d, eps, ST(stream));
+}
+int b2_smooth_quant(const void* x, const float* smooth, int8_t* q, float* row_scale, int T, int K, void* stream) {
+  return b2::smooth_quant(x, smooth, q, row_scale, T, K, ST(stream));
+}
+int b2_act_mul_quant(const void* gate_up, const float* smooth, int8_t* q, float* row_scale, int T, int F, int act,
+                     void* stream) {
+  return b2::act_mul_quant(gate_up, smooth, q, row_scale, T, F, act, ST(stream));
+}
+int b2_gemm_w8a8(const int8_t* A, const int8_t* W, const float* a_scale, const float* w_scale, const void* bias,
+                 const void* residual, void* out, int32_t* acc_dump, int M, int N, int K, void* stream) {
+  return b2::gemm_w8a8(A, W, a_scale, w_scale, bias, residual, out, acc_dump, M, N, K, 0, ST(stream));
+}
+int b2_gemm_w8a8_sched(const int8_t* A, const int8_t* W, const float* a_scale, const float* w_scale, const void* bias,
+                       const void* residual, void* out, int32_t* acc_dump, int M, int N, int K, int schedule,
+                       void* stream) {
+  return b2::gemm_w8a8(A, W, a_scale, w_scale, bias, residual, out, acc_dump, M, N, K, schedule, ST(stream));
+}
+int b2_rope_kv_append(void* qkv, long long ld, const float* cos_table, const float* sin_table, const int* positions,
+                      const int* seq_ids, int seq0, void* kcache, void* vcache, int T, int H, int KV, int hd, int Smax,
+                      int use_rope, void* stream) {
+  return b2::rope_kv_append(qkv, ld, cos_table, sin_table, positions, seq_ids, seq0, kcache, vcache, T, H, KV, hd, Smax,
+                            use_rope, ST(stream));
+}
+int b2_decode_attn(const void* q, long long q_ld, const void* kcache, const void* vcache, const int* seqlens,
+                   const int* rows, void* out, long long o_ld, void* workspace, size_t workspace_bytes, int B, int H,
+                   int KV, int hd, int Smax, int max_seqlen, float scale, int window, void* stream) {
+  return b2::decode_attn(q, q_ld, kcache, vcache, seqlens, rows, out, o_ld, workspace, workspace_bytes, B, H, KV, hd,
+                         Smax, max_seqlen, scale, window, ST(stream));
+}
+size_t b2_decode_attn_workspace_bytes(int B, int H, int KV, int hd, int max_seqlen, int window) {
+  int dev = 0, sms = 148;
+  if (cudaGetDevice(&dev) == cudaSuccess) {
+    int v = 0;
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0) sms = v;
+  }
+  const int eff = (window > 0 && max_seqlen > window) ? window : max_seqlen;
+  return b2::decode_attn_workspace_bytes(B, H, hd, b2::decode_attn_splits(B, KV, eff, sms));
+}
+int b2_prefill_attn(const void* q, long long q_ld, const void* kcache, const void* vcache, void* out, long long o_ld,
+                    int T, int pos0, int row, int H, int KV, int hd, int Smax, float scale, int window, void* stream) {
+  return b2::prefill_attn(q, q_ld, kcache, vcache, out, o_ld, T, pos0, row, H, KV, hd, Smax, scale, window, ST(stream));
+}
+int b2_embed(const long long* ids, const int* positions, const void* table, const void* pos_table, void* out, int T,
+             int d, int vocab, void* stream) {
+  return b2::embed(ids, positions, table, pos_table, out, T, d, vocab, ST(stream));
+}
+int b2_lm_head(const void* x, const void* W, float* logits, int M, int V, int d, void* stream) {
+  return b2::lm_head(x, W, logits, M, V, d, ST(stream));
+}
+int b2_argmax(const float* logits, long long* out, int T, int V, void* stream) {
+  return b2::argmax_rows(logits, out, T, V, ST(stream));
+}
+
+}  // extern "C"

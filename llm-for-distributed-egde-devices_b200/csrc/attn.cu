@@ -1,0 +1,576 @@
+// Rotary embedding + KV-cache append, decode attention (split-KV, HBM-bound) and causal prefill
+// attention over the stage-local KV cache.
+//
+// Replaces `eager_attention_forward` + `apply_rotary_pos_emb` + `DynamicCache.update` that the
+// reference executes inside HF `generate` (call site Code/Quantised Models/models_quant_updated.py:84-93;
+// transformers modeling_llama.py:199-222, :128-153, :251-289).  Oracle: oracle/w8a8.py apply_rope
+// (bit-exact) and attention (tolerance: softmax sum order / exp2 differ).
+//
+// KV cache layout (per layer): K and V each [rows][KV][Smax][hd] fp16 -- for one (row, kv head) the
+// keys are contiguous, so a CTA streams its key range with fully coalesced 16-byte cp.async.
+//
+// Decode attention: grid = (kv head, sequence, kv split).  The G = H/KV query heads that share a kv
+// head are packed into the 16-row A operand of mma.sync.m16n8k16 so K/V are read once per group.
+// Each CTA streams its key range through a double-buffered cp.async ring (128 keys a stage), the 4
+// warps take 32 keys each, keep private online-softmax state and are merged through shared memory.
+// With splits > 1 the unnormalised partials go to a caller-provided workspace and a second small
+// kernel merges them.
+#include "common.cuh"
+
+namespace b2 {
+
+// ---------------------------------------------------------------------------------------------
+// small PTX helpers
+// ---------------------------------------------------------------------------------------------
+B2_DEVINL void cp_async16(uint32_t dst, const void* src, bool valid) {
+  const int sz = valid ? 16 : 0;   // src-size 0 -> zero fill
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(sz) : "memory");
+}
+B2_DEVINL void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+B2_DEVINL void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+B2_DEVINL void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+B2_DEVINL void ldsm_x4_t(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+// D(16x8,f32) += A(16x16,f16,row) * B(16x8,f16,col)
+B2_DEVINL void mma16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+// =============================================================================================
+// RoPE + KV append
+// =============================================================================================
+// qkv: [T][ld] fp16 with q heads at [0,H*hd), k at [H*hd,(H+KV)*hd), v after.  q is rotated in
+// place, rotated k and v are written to the cache at (row = seq_ids[t] or seq0, positions[t]).
+__global__ void __launch_bounds__(256)
+rope_kv_append_kernel(__half* __restrict__ qkv, long long ld, const float* __restrict__ cosT,
+                      const float* __restrict__ sinT, const int* __restrict__ positions,
+                      const int* __restrict__ seq_ids, int seq0, __half* __restrict__ kcache,
+                      __half* __restrict__ vcache, int H, int KV, int hd, int Smax, int use_rope) {
+  const int t = blockIdx.x;
+  const int pos = positions[t];
+  const int row = seq_ids ? seq_ids[t] : seq0;
+  const int half = hd >> 1;
+  const int cph = half >> 3;                  // 8-element chunks per half head
+  const int items = (H + 2 * KV) * cph;
+  __half* base = qkv + (long long)t * ld;
+  for (int it = threadIdx.x; it < items; it += blockDim.x) {
+    const int head = it / cph, j = it - head * cph;
+    __half* hp = base + head * hd;
+    uint4 u1 = ld_v4(hp + j * 8);
+    uint4 u2 = ld_v4(hp + half + j * 8);
+    if (head < H + KV && use_rope) {
+      const float4 cA = *reinterpret_cast<const float4*>(cosT + (long long)pos * half + j * 8);
+      const float4 cB = *reinterpret_cast<const float4*>(cosT + (long long)pos * half + j * 8 + 4);
+      const float4 sA = *reinterpret_cast<const float4*>(sinT + (long long)pos * half + j * 8);
+      const float4 sB = *reinterpret_cast<const float4*>(sinT + (long long)pos * half + j * 8 + 4);
+      const float c[8] = {cA.x, cA.y, cA.z, cA.w, cB.x, cB.y, cB.z, cB.w};
+      const float s[8] = {sA.x, sA.y, sA.z, sA.w, sB.x, sB.y, sB.z, sB.w};
+      const uint32_t* p1 = &u1.x;
+      const uint32_t* p2 = &u2.x;
+      uint32_t o1[4], o2[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 a = h2_to_f2(p1[e]), b = h2_to_f2(p2[e]);
+        const float x0 = sub_rn(mul_rn(a.x, c[2 * e]), mul_rn(b.x, s[2 * e]));
+        const float x1 = sub_rn(mul_rn(a.y, c[2 * e + 1]), mul_rn(b.y, s[2 * e + 1]));
+        const float y0 = add_rn(mul_rn(b.x, c[2 * e]), mul_rn(a.x, s[2 * e]));
+        const float y1 = add_rn(mul_rn(b.y, c[2 * e + 1]), mul_rn(a.y, s[2 * e + 1]));
+        o1[e] = f2_to_h2(x0, x1);
+        o2[e] = f2_to_h2(y0, y1);
+      }
+      u1 = make_uint4(o1[0], o1[1], o1[2], o1[3]);
+      u2 = make_uint4(o2[0], o2[1], o2[2], o2[3]);
+    }
+    if (head < H) {
+      st_v4(hp + j * 8, u1);
+      st_v4(hp + half + j * 8, u2);
+    } else {
+      const bool isk = head < H + KV;
+      const int kvh = isk ? head - H : head - H - KV;
+      __half* dst = (isk ? kcache : vcache) + (((long long)row * KV + kvh) * Smax + pos) * hd;
+      st_v4(dst + j * 8, u1);
+      st_v4(dst + half + j * 8, u2);
+    }
+  }
+}
+
+int rope_kv_append(void* qkv, long long ld, const float* cosT, const float* sinT, const int* positions,
+                   const int* seq_ids, int seq0, void* kcache, void* vcache, int T, int H, int KV, int hd, int Smax,
+                   int use_rope, cudaStream_t st) {
+  if (T == 0) return OK;
+  if (!qkv || !positions || !kcache || !vcache || (use_rope && (!cosT || !sinT))) return ERR_NULL_PTR;
+  if (T < 0 || hd % 16 || H <= 0 || KV <= 0 || (ld & 7)) return ERR_BAD_SHAPE;
+  rope_kv_append_kernel<<<T, 256, 0, st>>>((__half*)qkv, ld, cosT, sinT, positions, seq_ids, seq0, (__half*)kcache,
+                                           (__half*)vcache, H, KV, hd, Smax, use_rope);
+  return launch_status();
+}
+
+// =============================================================================================
+// decode attention
+// =============================================================================================
+constexpr int DEC_TK = 128;       // keys per stage (32 per warp)
+constexpr int DEC_THREADS = 128;
+
+struct DecParams {
+  const __half* q; long long q_ld;     // q[b] at q + b*q_ld, heads contiguous
+  const __half* k; const __half* v;    // caches
+  const int* seqlens;                  // [B] keys valid per sequence (incl. the new token)
+  const int* rows;                     // [B] cache row per sequence (nullable -> b)
+  __half* out; long long o_ld;
+  float* part_o;                       // [B][H][splits][hd]
+  float* part_ml;                      // [B][H][splits][2]
+  int H, KV, Smax, splits, window;
+  float scale_log2;
+};
+
+template <int HD>
+__global__ void __launch_bounds__(DEC_THREADS, 1) decode_attn_kernel(const DecParams p) {
+  constexpr int LDS = HD + 8;                       // padded row (halves): ldmatrix conflict-free
+  constexpr int TILE_HALVES = DEC_TK * LDS;
+  extern __shared__ __align__(16) uint8_t smem_dec[];
+  __half* sK = reinterpret_cast<__half*>(smem_dec);   // [2][TK][LDS]
+  __half* sV = sK + 2 * TILE_HALVES;                  // [2][TK][LDS]
+  const int kvh = blockIdx.x, b = blockIdx.y, split = blockIdx.z;
+  const int G = p.H / p.KV;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = lane >> 2, t4 = lane & 3;
+  const int seqlen = p.seqlens[b];
+  const int row = p.rows ? p.rows[b] : b;
+  const int first = (p.window > 0 && seqlen > p.window) ? seqlen - p.window : 0;
+  const int n = seqlen - first;
+  const int chunk = (((n + p.splits - 1) / p.splits) + 31) & ~31;
+  const int kbeg = first + split * chunk;
+  const int kend = min(seqlen, kbeg + chunk);
+  const int ntiles = kend > kbeg ? (kend - kbeg + DEC_TK - 1) / DEC_TK : 0;
+  const __half* kg = p.k + ((long long)row * p.KV + kvh) * p.Smax * HD;
+  const __half* vg = p.v + ((long long)row * p.KV + kvh) * p.Smax * HD;
+
+  auto load_tile = [&](int tile, int stage) {
+    const int k0 = kbeg + tile * DEC_TK;
+    constexpr int CPR = HD / 8;                       // 16-byte chunks per row
+    for (int i = threadIdx.x; i < DEC_TK * CPR; i += DEC_THREADS) {
+      const int r = i / CPR, c = i - r * CPR;
+      const bool ok = (k0 + r) < kend;
+      const long long goff = (long long)(ok ? k0 + r : kbeg) * HD + c * 8;
+      const int soff = stage * TILE_HALVES + r * LDS + c * 8;
+      cp_async16(smem_u32(sK + soff), kg + goff, ok);
+      cp_async16(smem_u32(sV + soff), vg + goff, ok);
+    }
+  };
+
+  // Q fragments: rows 0..G-1 = the query heads of this kv group, rows >= G zero
+  uint32_t qf[HD / 16][4];
+  {
+    const __half* qb = p.q + (long long)b * p.q_ld + (long long)kvh * G * HD;
+#pragma unroll
+    for (int kk = 0; kk < HD / 16; ++kk) {
+      qf[kk][0] = (g < G) ? *reinterpret_cast<const uint32_t*>(qb + g * HD + kk * 16 + 2 * t4) : 0u;
+      qf[kk][2] = (g < G) ? *reinterpret_cast<const uint32_t*>(qb + g * HD + kk * 16 + 8 + 2 * t4) : 0u;
+      qf[kk][1] = 0u;   // rows g+8 >= 8 >= G
+      qf[kk][3] = 0u;
+    }
+  }
+  float o[HD / 8][4];
+#pragma unroll
+  for (int i = 0; i < HD / 8; ++i) { o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f; }
+  float m_run = -INFINITY, l_run = 0.f;     // row g (rows g+8 are padding)
+
+  if (ntiles > 0) { load_tile(0, 0); }
+  cp_async_commit();
+  for (int tile = 0; tile < ntiles; ++tile) {
+    const int stage = tile & 1;
+    if (tile + 1 < ntiles) load_tile(tile + 1, stage ^ 1);
+    cp_async_commit();
+    cp_async_wait<1>();
+    __syncthreads();
+    const __half* tK = sK + stage * TILE_HALVES + warp * 32 * LDS;
+    const __half* tV = sV + stage * TILE_HALVES + warp * 32 * LDS;
+    // ---- S = Q K^T for this warp's 32 keys ----
+    float s[4][4];
+#pragma unroll
+    for (int nb = 0; nb < 4; ++nb) { s[nb][0] = s[nb][1] = s[nb][2] = s[nb][3] = 0.f; }
+#pragma unroll
+    for (int kp = 0; kp < HD / 32; ++kp) {
+#pragma unroll
+      for (int nb = 0; nb < 4; ++nb) {
+        uint32_t bf[4];
+        const int r = nb * 8 + (lane & 7);
+        const int c = kp * 32 + (lane >> 3) * 8;
+        ldsm_x4(bf, smem_u32(tK + r * LDS + c));
+        mma16816(s[nb], qf[2 * kp], bf[0], bf[1]);
+        mma16816(s[nb], qf[2 * kp + 1], bf[2], bf[3]);
+      }
+    }
+    // ---- mask + online softmax (row g only) ----
+    const int key0 = kbeg + tile * DEC_TK + warp * 32;
+    float mx = -INFINITY;
+#pragma unroll
+    for (int nb = 0; nb < 4; ++nb) {
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int key = key0 + nb * 8 + 2 * t4 + e;
+        float v = s[nb][e] * p.scale_log2;
+        v = (key < kend) ? v : -INFINITY;
+        s[nb][e] = v;
+        mx = fmaxf(mx, v);
+      }
+    }
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+    const float m_new = fmaxf(m_run, mx);
+    const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
+    const float corr = exp2f(m_run - m_use);          // m_run = -inf -> 0
+    float ls = 0.f;
+    uint32_t pf[2][4];
+#pragma unroll
+    for (int nb = 0; nb < 4; ++nb) {
+      const float p0 = exp2f(s[nb][0] - m_use);
+      const float p1 = exp2f(s[nb][1] - m_use);
+      ls += p0 + p1;
+      // C layout of S -> A layout of P: k-block kk2 = nb/2, regs {0,1} = cols 0-7, {2,3} = cols 8-15
+      pf[nb >> 1][(nb & 1) * 2] = f2_to_h2(p0, p1);
+      pf[nb >> 1][(nb & 1) * 2 + 1] = 0u;             // rows g+8: padding
+    }
+    ls += __shfl_xor_sync(0xffffffffu, ls, 1);
+    ls += __shfl_xor_sync(0xffffffffu, ls, 2);
+    l_run = l_run * corr + ls;
+    m_run = m_new;
+#pragma unroll
+    for (int i = 0; i < HD / 8; ++i) { o[i][0] *= corr; o[i][1] *= corr; }
+    // ---- O += P V ----
+#pragma unroll
+    for (int kk2 = 0; kk2 < 2; ++kk2) {
+#pragma unroll
+      for (int np = 0; np < HD / 16; ++np) {
+        uint32_t bf[4];
+        const int mat = lane >> 3;
+        const int r = kk2 * 16 + (mat & 1) * 8 + (lane & 7);
+        const int c = np * 16 + (mat >> 1) * 8;
+        ldsm_x4_t(bf, smem_u32(tV + r * LDS + c));
+        mma16816(o[2 * np], pf[kk2], bf[0], bf[1]);
+        mma16816(o[2 * np + 1], pf[kk2], bf[2], bf[3]);
+      }
+    }
+    __syncthreads();   // all warps done with this stage before it is refilled
+  }
+  cp_async_wait<0>();
+  __syncthreads();
+  // ---- merge the 4 warps through shared memory (reuse the K buffers) ----
+  float* sO = reinterpret_cast<float*>(smem_dec);          // [4][8][HD]
+  float* sM = sO + 4 * 8 * HD;                             // [4][8]
+  float* sL = sM + 32;                                     // [4][8]
+#pragma unroll
+  for (int i = 0; i < HD / 8; ++i) {
+    sO[(warp * 8 + g) * HD + i * 8 + 2 * t4] = o[i][0];
+    sO[(warp * 8 + g) * HD + i * 8 + 2 * t4 + 1] = o[i][1];
+  }
+  if (t4 == 0) { sM[warp * 8 + g] = m_run; sL[warp * 8 + g] = l_run; }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < G * HD; idx += DEC_THREADS) {
+    const int gh = idx / HD, d = idx - gh * HD;
+    float m = -INFINITY;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) m = fmaxf(m, sM[w * 8 + gh]);
+    float l = 0.f, acc = 0.f;
+    if (m != -INFINITY) {
+#pragma unroll
+      for (int w = 0; w < 4; ++w) {
+        const float f = exp2f(sM[w * 8 + gh] - m);
+        l += sL[w * 8 + gh] * f;
+        acc += sO[(w * 8 + gh) * HD + d] * f;
+      }
+    }
+    const int h = kvh * G + gh;
+    if (p.splits == 1) {
+      p.out[(long long)b * p.o_ld + h * HD + d] = __float2half_rn(l > 0.f ? acc / l : 0.f);
+    } else {
+      const long long po = (((long long)b * p.H + h) * p.splits + split);
+      p.part_o[po * HD + d] = acc;
+      if (d == 0) { p.part_ml[po * 2] = m; p.part_ml[po * 2 + 1] = l; }
+    }
+  }
+}
+
+template <int HD>
+__global__ void __launch_bounds__(HD) decode_merge_kernel(const DecParams p) {
+  const int h = blockIdx.x, b = blockIdx.y, d = threadIdx.x;
+  const long long base = ((long long)b * p.H + h) * p.splits;
+  float m = -INFINITY;
+  for (int s = 0; s < p.splits; ++s) m = fmaxf(m, p.part_ml[(base + s) * 2]);
+  float l = 0.f, acc = 0.f;
+  if (m != -INFINITY) {
+    for (int s = 0; s < p.splits; ++s) {
+      const float f = exp2f(p.part_ml[(base + s) * 2] - m);
+      l += p.part_ml[(base + s) * 2 + 1] * f;
+      acc += p.part_o[(base + s) * HD + d] * f;
+    }
+  }
+  p.out[(long long)b * p.o_ld + h * HD + d] = __float2half_rn(l > 0.f ? acc / l : 0.f);
+}
+
+// How many kv splits the decode kernel will use for these sizes; the caller sizes the workspace
+// with decode_attn_workspace_bytes() (0 when splits == 1).
+int decode_attn_splits(int B, int KV, int max_seqlen, int sms) {
+  if (B <= 0 || KV <= 0) return 1;
+  const int ctas = B * KV;
+  int want = (2 * sms + ctas - 1) / ctas;
+  const int max_by_len = (max_seqlen + 2 * DEC_TK - 1) / (2 * DEC_TK);   // >= 256 keys per split
+  int s = want < max_by_len ? want : max_by_len;
+  if (s < 1) s = 1;
+  if (s > 64) s = 64;
+  return s;
+}
+size_t decode_attn_workspace_bytes(int B, int H, int hd, int splits) {
+  if (splits <= 1) return 0;
+  return (size_t)B * H * splits * (hd + 2) * sizeof(float);
+}
+
+static int sm_count_attn() {
+  static int n = []() {
+    int dev = 0, v = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
+    return v > 0 ? v : 148;
+  }();
+  return n;
+}
+
+template <int HD>
+static int launch_decode(const DecParams& p, int B, cudaStream_t st) {
+  constexpr int SMEM = 2 * 2 * DEC_TK * (HD + 8) * 2;
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(decode_attn_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM) != cudaSuccess)
+      return ERR_ARCH;
+    attr_set = true;
+  }
+  decode_attn_kernel<HD><<<dim3(p.KV, B, p.splits), DEC_THREADS, SMEM, st>>>(p);
+  if (p.splits > 1) decode_merge_kernel<HD><<<dim3(p.H, B), HD, 0, st>>>(p);
+  return launch_status();
+}
+
+// max_seqlen: upper bound of seqlens[] known to the host (sizes the split count; no device read)
+int decode_attn(const void* q, long long q_ld, const void* kcache, const void* vcache, const int* seqlens,
+                const int* rows, void* out, long long o_ld, void* workspace, size_t workspace_bytes, int B, int H,
+                int KV, int hd, int Smax, int max_seqlen, float scale, int window, cudaStream_t st) {
+  if (B == 0) return OK;
+  if (!q || !kcache || !vcache || !seqlens || !out) return ERR_NULL_PTR;
+  if (B < 0 || H <= 0 || KV <= 0 || H % KV || H / KV > 8 || (q_ld & 1) || max_seqlen <= 0) return ERR_BAD_SHAPE;
+  if (hd != 64 && hd != 128) return ERR_UNSUPPORTED;
+  const int eff = (window > 0 && max_seqlen > window) ? window : max_seqlen;
+  int splits = decode_attn_splits(B, KV, eff, sm_count_attn());
+  const size_t need = decode_attn_workspace_bytes(B, H, hd, splits);
+  if (need > 0 && (!workspace || workspace_bytes < need)) {
+    // shrink to what the workspace allows rather than failing; 1 split needs none
+    while (splits > 1 && (!workspace || decode_attn_workspace_bytes(B, H, hd, splits) > workspace_bytes)) --splits;
+  }
+  DecParams p;
+  p.q = (const __half*)q; p.q_ld = q_ld; p.k = (const __half*)kcache; p.v = (const __half*)vcache;
+  p.seqlens = seqlens; p.rows = rows; p.out = (__half*)out; p.o_ld = o_ld;
+  p.part_o = (float*)workspace;
+  p.part_ml = p.part_o ? p.part_o + (size_t)B * H * splits * hd : nullptr;
+  p.H = H; p.KV = KV; p.Smax = Smax; p.splits = splits; p.window = window;
+  p.scale_log2 = scale * 1.4426950408889634f;
+  return hd == 128 ? launch_decode<128>(p, B, st) : launch_decode<64>(p, B, st);
+}
+
+// =============================================================================================
+// prefill attention (one contiguous chunk of one sequence; causal, optional sliding window)
+// =============================================================================================
+constexpr int PF_BM = 64;     // query rows per CTA (16 per warp)
+constexpr int PF_TK = 64;     // keys per stage
+constexpr int PF_THREADS = 128;
+
+struct PfParams {
+  const __half* q; long long q_ld;     // q[t] at q + t*q_ld
+  const __half* k; const __half* v;
+  __half* out; long long o_ld;
+  int T, pos0, row, H, KV, Smax, window;
+  float scale_log2;
+};
+
+template <int HD>
+__global__ void __launch_bounds__(PF_THREADS) prefill_attn_kernel(const PfParams p) {
+  constexpr int LDS = HD + 8;
+  constexpr int TILE_HALVES = PF_TK * LDS;
+  extern __shared__ __align__(16) uint8_t smem_pf[];
+  __half* sK = reinterpret_cast<__half*>(smem_pf);
+  __half* sV = sK + 2 * TILE_HALVES;
+  const int qt = gridDim.x - 1 - blockIdx.x;          // heavy (late) query tiles first
+  const int h = blockIdx.y;
+  const int kvh = h / (p.H / p.KV);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = lane >> 2, t4 = lane & 3;
+  const int q0 = qt * PF_BM;
+  const int r0 = q0 + warp * 16 + g, r1 = r0 + 8;     // this thread's two query rows (chunk-relative)
+  const int pos_r0 = p.pos0 + r0, pos_r1 = p.pos0 + r1;
+  const int last_q = min(q0 + PF_BM, p.T) - 1;
+  const int kend = p.pos0 + last_q + 1;               // exclusive
+  int kfirst = 0;
+  if (p.window > 0) { kfirst = p.pos0 + q0 - p.window + 1; kfirst = kfirst > 0 ? (kfirst / PF_TK) * PF_TK : 0; }
+  const int ntiles = (kend - kfirst + PF_TK - 1) / PF_TK;
+  const __half* kg = p.k + ((long long)p.row * p.KV + kvh) * p.Smax * HD;
+  const __half* vg = p.v + ((long long)p.row * p.KV + kvh) * p.Smax * HD;
+
+  auto load_tile = [&](int tile, int stage) {
+    const int k0 = kfirst + tile * PF_TK;
+    constexpr int CPR = HD / 8;
+    for (int i = threadIdx.x; i < PF_TK * CPR; i += PF_THREADS) {
+      const int r = i / CPR, c = i - r * CPR;
+      const bool ok = (k0 + r) < kend;
+      const long long goff = (long long)(ok ? k0 + r : kfirst) * HD + c * 8;
+      const int soff = stage * TILE_HALVES + r * LDS + c * 8;
+      cp_async16(smem_u32(sK + soff), kg + goff, ok);
+      cp_async16(smem_u32(sV + soff), vg + goff, ok);
+    }
+  };
+
+  uint32_t qf[HD / 16][4];
+  {
+    const __half* qa = p.q + (long long)r0 * p.q_ld + h * HD;
+    const __half* qb = p.q + (long long)r1 * p.q_ld + h * HD;
+    const bool ok0 = r0 < p.T, ok1 = r1 < p.T;
+#pragma unroll
+    for (int kk = 0; kk < HD / 16; ++kk) {
+      qf[kk][0] = ok0 ? *reinterpret_cast<const uint32_t*>(qa + kk * 16 + 2 * t4) : 0u;
+      qf[kk][1] = ok1 ? *reinterpret_cast<const uint32_t*>(qb + kk * 16 + 2 * t4) : 0u;
+      qf[kk][2] = ok0 ? *reinterpret_cast<const uint32_t*>(qa + kk * 16 + 8 + 2 * t4) : 0u;
+      qf[kk][3] = ok1 ? *reinterpret_cast<const uint32_t*>(qb + kk * 16 + 8 + 2 * t4) : 0u;
+    }
+  }
+  float o[HD / 8][4];
+#pragma unroll
+  for (int i = 0; i < HD / 8; ++i) { o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f; }
+  float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+
+  load_tile(0, 0);
+  cp_async_commit();
+  for (int tile = 0; tile < ntiles; ++tile) {
+    const int stage = tile & 1;
+    if (tile + 1 < ntiles) load_tile(tile + 1, stage ^ 1);
+    cp_async_commit();
+    cp_async_wait<1>();
+    __syncthreads();
+    const __half* tK = sK + stage * TILE_HALVES;
+    const __half* tV = sV + stage * TILE_HALVES;
+    const int key0 = kfirst + tile * PF_TK;
+    float s[PF_TK / 8][4];
+#pragma unroll
+    for (int nb = 0; nb < PF_TK / 8; ++nb) { s[nb][0] = s[nb][1] = s[nb][2] = s[nb][3] = 0.f; }
+#pragma unroll
+    for (int kp = 0; kp < HD / 32; ++kp) {
+#pragma unroll
+      for (int nb = 0; nb < PF_TK / 8; ++nb) {
+        uint32_t bf[4];
+        const int r = nb * 8 + (lane & 7);
+        const int c = kp * 32 + (lane >> 3) * 8;
+        ldsm_x4(bf, smem_u32(tK + r * LDS + c));
+        mma16816(s[nb], qf[2 * kp], bf[0], bf[1]);
+        mma16816(s[nb], qf[2 * kp + 1], bf[2], bf[3]);
+      }
+    }
+    float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+    for (int nb = 0; nb < PF_TK / 8; ++nb) {
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int key = key0 + nb * 8 + 2 * t4 + e;
+        const bool v0 = key <= pos_r0 && (p.window == 0 || key > pos_r0 - p.window);
+        const bool v1 = key <= pos_r1 && (p.window == 0 || key > pos_r1 - p.window);
+        const float a = v0 ? s[nb][e] * p.scale_log2 : -INFINITY;
+        const float c = v1 ? s[nb][2 + e] * p.scale_log2 : -INFINITY;
+        s[nb][e] = a; s[nb][2 + e] = c;
+        mx0 = fmaxf(mx0, a); mx1 = fmaxf(mx1, c);
+      }
+    }
+    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+    const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);
+    const float mu0 = (mn0 == -INFINITY) ? 0.f : mn0, mu1 = (mn1 == -INFINITY) ? 0.f : mn1;
+    const float c0 = exp2f(m0 - mu0), c1 = exp2f(m1 - mu1);
+    float ls0 = 0.f, ls1 = 0.f;
+    uint32_t pf[PF_TK / 16][4];
+#pragma unroll
+    for (int nb = 0; nb < PF_TK / 8; ++nb) {
+      const float p00 = exp2f(s[nb][0] - mu0), p01 = exp2f(s[nb][1] - mu0);
+      const float p10 = exp2f(s[nb][2] - mu1), p11 = exp2f(s[nb][3] - mu1);
+      ls0 += p00 + p01; ls1 += p10 + p11;
+      pf[nb >> 1][(nb & 1) * 2] = f2_to_h2(p00, p01);
+      pf[nb >> 1][(nb & 1) * 2 + 1] = f2_to_h2(p10, p11);
+    }
+    ls0 += __shfl_xor_sync(0xffffffffu, ls0, 1); ls0 += __shfl_xor_sync(0xffffffffu, ls0, 2);
+    ls1 += __shfl_xor_sync(0xffffffffu, ls1, 1); ls1 += __shfl_xor_sync(0xffffffffu, ls1, 2);
+    l0 = l0 * c0 + ls0; l1 = l1 * c1 + ls1;
+    m0 = mn0; m1 = mn1;
+#pragma unroll
+    for (int i = 0; i < HD / 8; ++i) { o[i][0] *= c0; o[i][1] *= c0; o[i][2] *= c1; o[i][3] *= c1; }
+#pragma unroll
+    for (int kk2 = 0; kk2 < PF_TK / 16; ++kk2) {
+#pragma unroll
+      for (int np = 0; np < HD / 16; ++np) {
+        uint32_t bf[4];
+        const int mat = lane >> 3;
+        const int r = kk2 * 16 + (mat & 1) * 8 + (lane & 7);
+        const int c = np * 16 + (mat >> 1) * 8;
+        ldsm_x4_t(bf, smem_u32(tV + r * LDS + c));
+        mma16816(o[2 * np], pf[kk2], bf[0], bf[1]);
+        mma16816(o[2 * np + 1], pf[kk2], bf[2], bf[3]);
+      }
+    }
+    __syncthreads();
+  }
+  cp_async_wait<0>();
+  const float i0 = l0 > 0.f ? 1.f / l0 : 0.f, i1 = l1 > 0.f ? 1.f / l1 : 0.f;
+  if (r0 < p.T) {
+    __half* op = p.out + (long long)r0 * p.o_ld + h * HD;
+#pragma unroll
+    for (int i = 0; i < HD / 8; ++i)
+      *reinterpret_cast<uint32_t*>(op + i * 8 + 2 * t4) = f2_to_h2(o[i][0] * i0, o[i][1] * i0);
+  }
+  if (r1 < p.T) {
+    __half* op = p.out + (long long)r1 * p.o_ld + h * HD;
+#pragma unroll
+    for (int i = 0; i < HD / 8; ++i)
+      *reinterpret_cast<uint32_t*>(op + i * 8 + 2 * t4) = f2_to_h2(o[i][2] * i1, o[i][3] * i1);
+  }
+}
+
+template <int HD>
+static int launch_prefill(const PfParams& p, cudaStream_t st) {
+  constexpr int SMEM = 2 * 2 * PF_TK * (HD + 8) * 2;
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(prefill_attn_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM) != cudaSuccess)
+      return ERR_ARCH;
+    attr_set = true;
+  }
+  prefill_attn_kernel<HD><<<dim3((p.T + PF_BM - 1) / PF_BM, p.H), PF_THREADS, SMEM, st>>>(p);
+  return launch_status();
+}
+
+int prefill_attn(const void* q, long long q_ld, const void* kcache, const void* vcache, void* out, long long o_ld,
+                 int T, int pos0, int row, int H, int KV, int hd, int Smax, float scale, int window, cudaStream_t st) {
+  if (T == 0) return OK;
+  if (!q || !kcache || !vcache || !out) return ERR_NULL_PTR;
+  if (T < 0 || pos0 < 0 || pos0 + T > Smax || H <= 0 || KV <= 0 || H % KV || (q_ld & 1) || (o_ld & 1)) return ERR_BAD_SHAPE;
+  if (hd != 64 && hd != 128) return ERR_UNSUPPORTED;
+  PfParams p;
+  p.q = (const __half*)q; p.q_ld = q_ld; p.k = (const __half*)kcache; p.v = (const __half*)vcache;
+  p.out = (__half*)out; p.o_ld = o_ld; p.T = T; p.pos0 = pos0; p.row = row; p.H = H; p.KV = KV; p.Smax = Smax;
+  p.window = window; p.scale_log2 = scale * 1.4426950408889634f;
+  return hd == 128 ? launch_prefill<128>(p, st) : launch_prefill<64>(p, st);
+}
+
+}  // namespace b2

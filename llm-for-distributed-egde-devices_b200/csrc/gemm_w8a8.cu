@@ -1,0 +1,528 @@
+// W8A8 linear:  out[M,N] = fp16( (int32(A[M,K] . W[N,K]^T) * a_scale[m]) * w_scale[n] + bias[n] + residual[m,n] )
+//
+// Replaces the int8 linear that the reference reaches through bitsandbytes `Linear8bitLt`
+// (Code/Quantised Models/models_quant_updated.py:30-38) / `quantize_dynamic`
+// (Code/C-DAC Server/try.py:205): quantise - int8 GEMM - dequantise as three unfused passes.  Here
+// the dequantise, bias and residual add are the GEMM epilogue.
+//
+// Two schedules, chosen by M (number of tokens):
+//   * M > GEMV_MAX_M : tcgen05.mma kind::i8 (UMMA 128 x BN x 32), operands staged by TMA into
+//     128B-swizzled shared-memory tiles through a STAGES-deep mbarrier ring, int32 accumulators in
+//     TMEM (two buffers, so the epilogue of tile i overlaps the MMAs of tile i+1), persistent CTAs
+//     (one per SM) walking a static tile schedule.  Warp roles: 0 = TMA producer, 1 = MMA issuer,
+//     2 = TMEM allocator, 4..7 = epilogue (TMEM lane quadrant = warp % 4).  Tensor-pipe bound.
+//   * M <= GEMV_MAX_M (decode): the weight matrix is streamed once from HBM with 128-bit loads and
+//     reduced with dp4a on the CUDA cores -- HBM-bound, the tensor pipe would add nothing.
+// Both produce the exact int32 accumulator, so results are bit-identical between schedules and
+// against oracle/w8a8.py:gemm_w8a8.
+#include <cuda.h>
+#include "common.cuh"
+
+namespace b2 {
+
+// =============================================================================================
+// tcgen05 path
+// =============================================================================================
+constexpr int BM = 128;         // UMMA M
+constexpr int BK = 128;         // int8 elements per k-block = one 128-byte swizzle atom
+constexpr int UMMA_K = 32;      // int8
+constexpr int GEMM_THREADS = 256;
+
+template <int BN, int STAGES>
+struct GemmSmem {
+  static constexpr int A_BYTES = BM * BK;
+  static constexpr int B_BYTES = BN * BK;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int BAR_OFF = STAGES * STAGE_BYTES;
+  static constexpr int TOTAL = BAR_OFF + 256 + 1024;   // barriers + alignment slack
+};
+
+struct GemmParams {
+  const float* a_scale;
+  const float* w_scale;
+  const __half* bias;
+  const __half* residual;
+  __half* out;
+  float* out_f32;  // KIND_F16 only: fp32 result (lm_head logits)
+  int32_t* acc_dump;
+  int M, N, K;
+  int ldo;         // row stride (elements) of out / residual / acc_dump
+};
+
+constexpr int KIND_I8 = 0, KIND_F16 = 1;
+
+template <int BN, int STAGES, int KIND>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                  const GemmParams p) {
+  using S = GemmSmem<BN, STAGES>;
+  constexpr int TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + S::BAR_OFF);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tfull_bar = empty_bar + STAGES;     // [2] accumulator ready
+  uint64_t* tempty_bar = tfull_bar + 2;         // [2] accumulator drained
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int m_tiles = (p.M + BM - 1) / BM;
+  const int n_tiles = (p.N + BN - 1) / BN;
+  const int num_tiles = m_tiles * n_tiles;
+  constexpr int BKE = (KIND == KIND_I8) ? BK : BK / 2;   // elements per 128-byte k-block
+  const int kblocks = (p.K + BKE - 1) / BKE;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 4); }
+    mbar_fence_init();
+  }
+  if (warp == 2) tmem_alloc<TMEM_COLS>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        const int mt = t % m_tiles, nt = t / m_tiles;
+        for (int kb = 0; kb < kblocks; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * S::STAGE_BYTES;
+          uint8_t* sb = sa + S::A_BYTES;
+          mbar_expect_tx(&full_bar[stage], S::STAGE_BYTES);
+          tma_load_2d(sa, &tmA, &full_bar[stage], kb * BKE, mt * BM);
+          tma_load_2d(sb, &tmB, &full_bar[stage], kb * BKE, nt * BN);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = (KIND == KIND_I8) ? umma_idesc(IDESC_FMT_S32, IDESC_S8, IDESC_S8, BM, BN)
+                                                   : umma_idesc(IDESC_FMT_F32, IDESC_F16, IDESC_F16, BM, BN);
+      int stage = 0; uint32_t phase = 0;
+      int it = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+        const int buf = it & 1;
+        const uint32_t bphase = (it >> 1) & 1;
+        mbar_wait(&tempty_bar[buf], bphase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + buf * BN;
+        for (int kb = 0; kb < kblocks; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * S::STAGE_BYTES);
+          const uint64_t adesc = umma_desc_sw128(sa);
+          const uint64_t bdesc = umma_desc_sw128(sa + S::A_BYTES);
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            // advancing K inside the swizzle atom: +32 bytes -> +2 in the (addr >> 4) field
+            if (KIND == KIND_I8) umma_i8(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+            else umma_f16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+          }
+          umma_commit(&empty_bar[stage]);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&tfull_bar[buf]);
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue =====================
+    const int quad = warp & 3;
+    int it = 0;
+    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+      const int mt = t % m_tiles, nt = t / m_tiles;
+      const int buf = it & 1;
+      const uint32_t bphase = (it >> 1) & 1;
+      mbar_wait(&tfull_bar[buf], bphase);
+      tc_fence_after();
+      const int row = mt * BM + quad * 32 + lane;
+      const bool row_ok = row < p.M;
+      const float as = (KIND == KIND_I8 && row_ok) ? p.a_scale[row] : 0.0f;
+      const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + buf * BN;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(taddr + c * 32, r);
+        tmem_ld_wait();
+        const int col0 = nt * BN + c * 32;
+        if (KIND == KIND_F16) {
+          if (row_ok && col0 < p.N) {
+            float* op = p.out_f32 + (long long)row * p.ldo + col0;
+            if (col0 + 32 <= p.N) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 4)
+                *reinterpret_cast<uint4*>(op + j) = make_uint4(r[j], r[j + 1], r[j + 2], r[j + 3]);
+            } else {
+              for (int j = 0; j < 32 && col0 + j < p.N; ++j) op[j] = __uint_as_float(r[j]);
+            }
+          }
+        } else if (row_ok && col0 < p.N) {
+          const long long off = (long long)row * p.ldo + col0;
+          if (col0 + 32 <= p.N) {
+            if (p.acc_dump) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 4)
+                *reinterpret_cast<uint4*>(p.acc_dump + off + j) = make_uint4(r[j], r[j + 1], r[j + 2], r[j + 3]);
+            }
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              const float4 w0 = *reinterpret_cast<const float4*>(p.w_scale + col0 + j);
+              const float4 w1 = *reinterpret_cast<const float4*>(p.w_scale + col0 + j + 4);
+              const float ws[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+              float v[8];
+#pragma unroll
+              for (int e = 0; e < 8; ++e) v[e] = mul_rn(mul_rn((float)(int)r[j + e], as), ws[e]);
+              if (p.bias) {
+                const uint4 b = ld_v4(p.bias + col0 + j);
+                const float2 b0 = h2_to_f2(b.x), b1 = h2_to_f2(b.y), b2_ = h2_to_f2(b.z), b3 = h2_to_f2(b.w);
+                v[0] = add_rn(v[0], b0.x); v[1] = add_rn(v[1], b0.y); v[2] = add_rn(v[2], b1.x); v[3] = add_rn(v[3], b1.y);
+                v[4] = add_rn(v[4], b2_.x); v[5] = add_rn(v[5], b2_.y); v[6] = add_rn(v[6], b3.x); v[7] = add_rn(v[7], b3.y);
+              }
+              if (p.residual) {
+                const uint4 b = ld_v4(p.residual + off + j);
+                const float2 b0 = h2_to_f2(b.x), b1 = h2_to_f2(b.y), b2_ = h2_to_f2(b.z), b3 = h2_to_f2(b.w);
+                v[0] = add_rn(v[0], b0.x); v[1] = add_rn(v[1], b0.y); v[2] = add_rn(v[2], b1.x); v[3] = add_rn(v[3], b1.y);
+                v[4] = add_rn(v[4], b2_.x); v[5] = add_rn(v[5], b2_.y); v[6] = add_rn(v[6], b3.x); v[7] = add_rn(v[7], b3.y);
+              }
+              uint4 o;
+              o.x = f2_to_h2(v[0], v[1]); o.y = f2_to_h2(v[2], v[3]);
+              o.z = f2_to_h2(v[4], v[5]); o.w = f2_to_h2(v[6], v[7]);
+              st_v4(p.out + off + j, o);
+            }
+          } else {   // ragged N tail: scalar
+            for (int j = 0; j < 32 && col0 + j < p.N; ++j) {
+              float v = mul_rn(mul_rn((float)(int)r[j], as), p.w_scale[col0 + j]);
+              if (p.bias) v = add_rn(v, __half2float(p.bias[col0 + j]));
+              if (p.residual) v = add_rn(v, __half2float(p.residual[off + j]));
+              p.out[off + j] = __float2half_rn(v);
+              if (p.acc_dump) p.acc_dump[off + j] = (int)r[j];
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty_bar[buf]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc<TMEM_COLS>(tmem_base);
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side: tensor maps
+// ---------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = []() -> EncodeTiledFn {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qr) != cudaSuccess) return nullptr;
+    if (qr != cudaDriverEntryPointSuccess) return nullptr;
+    return reinterpret_cast<EncodeTiledFn>(p);
+  }();
+  return fn;
+}
+
+// rows x K (int8 or fp16), row-major (K contiguous); box = box_rows x 128 bytes, 128B swizzle,
+// out-of-bounds elements read as zero
+static int make_tmap(CUtensorMap* tm, const void* base, int rows, int K, int box_rows, int kind) {
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc) return ERR_DRIVER;
+  const int esz = kind == KIND_I8 ? 1 : 2;
+  cuuint64_t gdim[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)K * esz};
+  cuuint32_t box[2] = {(cuuint32_t)(BK / esz), (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(tm, kind == KIND_I8 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
+                   const_cast<void*>(base), gdim, gstride, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? OK : ERR_DRIVER;
+}
+
+static int sm_count() {
+  static int n = []() {
+    int dev = 0, v = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
+    return v > 0 ? v : 148;
+  }();
+  return n;
+}
+
+template <int BN, int STAGES, int KIND>
+static int launch_tc(const void* A, const void* W, const GemmParams& p, cudaStream_t st) {
+  using S = GemmSmem<BN, STAGES>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES, KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL) !=
+        cudaSuccess)
+      return ERR_ARCH;
+    attr_set = true;
+  }
+  CUtensorMap tmA, tmB;
+  int rc = make_tmap(&tmA, A, p.M, p.K, BM, KIND);
+  if (rc) return rc;
+  rc = make_tmap(&tmB, W, p.N, p.K, BN, KIND);
+  if (rc) return rc;
+  const int tiles = ((p.M + BM - 1) / BM) * ((p.N + BN - 1) / BN);
+  const int grid = tiles < sm_count() ? tiles : sm_count();
+  gemm_tc_kernel<BN, STAGES, KIND><<<grid, GEMM_THREADS, S::TOTAL, st>>>(tmA, tmB, p);
+  return launch_status();
+}
+
+// =============================================================================================
+// skinny-M streaming path (decode): dp4a over 128-bit weight loads
+// =============================================================================================
+constexpr int GEMV_MAX_M = 8;
+constexpr int GEMV_WARPS = 4;
+constexpr int GEMV_ROWS = 2;      // weight rows per warp
+
+template <int MT>
+__global__ void __launch_bounds__(GEMV_WARPS * 32)
+gemv_i8_kernel(const int8_t* __restrict__ A, const int8_t* __restrict__ W, const GemmParams p) {
+  extern __shared__ uint8_t xs[];   // [MT][K] int8 activations
+  const int K = p.K;
+  const int kvec = K >> 4;          // 16-byte vectors per row
+  for (int i = threadIdx.x; i < MT * kvec; i += blockDim.x) {
+    const int m = i / kvec, c = i - m * kvec;
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (m < p.M) v = ld_v4(A + (long long)m * K + c * 16);
+    reinterpret_cast<uint4*>(xs)[i] = v;
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n0 = (blockIdx.x * GEMV_WARPS + warp) * GEMV_ROWS;
+  if (n0 >= p.N) return;
+  int acc[GEMV_ROWS][MT];
+#pragma unroll
+  for (int r = 0; r < GEMV_ROWS; ++r)
+#pragma unroll
+    for (int m = 0; m < MT; ++m) acc[r][m] = 0;
+  const int8_t* wrow[GEMV_ROWS];
+#pragma unroll
+  for (int r = 0; r < GEMV_ROWS; ++r) wrow[r] = W + (long long)min(n0 + r, p.N - 1) * K;
+
+  constexpr int UNR = 4;
+  int c = lane;
+  for (; c + (UNR - 1) * 32 < kvec; c += UNR * 32) {
+    uint4 w[UNR][GEMV_ROWS];
+#pragma unroll
+    for (int u = 0; u < UNR; ++u)
+#pragma unroll
+      for (int r = 0; r < GEMV_ROWS; ++r) w[u][r] = ld_nc_v4(wrow[r] + (c + u * 32) * 16);
+#pragma unroll
+    for (int u = 0; u < UNR; ++u) {
+#pragma unroll
+      for (int m = 0; m < MT; ++m) {
+        const uint4 x = reinterpret_cast<const uint4*>(xs)[m * kvec + c + u * 32];
+#pragma unroll
+        for (int r = 0; r < GEMV_ROWS; ++r) {
+          int a = acc[r][m];
+          a = __dp4a((int)w[u][r].x, (int)x.x, a);
+          a = __dp4a((int)w[u][r].y, (int)x.y, a);
+          a = __dp4a((int)w[u][r].z, (int)x.z, a);
+          a = __dp4a((int)w[u][r].w, (int)x.w, a);
+          acc[r][m] = a;
+        }
+      }
+    }
+  }
+  for (; c < kvec; c += 32) {
+    uint4 w[GEMV_ROWS];
+#pragma unroll
+    for (int r = 0; r < GEMV_ROWS; ++r) w[r] = ld_nc_v4(wrow[r] + c * 16);
+#pragma unroll
+    for (int m = 0; m < MT; ++m) {
+      const uint4 x = reinterpret_cast<const uint4*>(xs)[m * kvec + c];
+#pragma unroll
+      for (int r = 0; r < GEMV_ROWS; ++r) {
+        int a = acc[r][m];
+        a = __dp4a((int)w[r].x, (int)x.x, a);
+        a = __dp4a((int)w[r].y, (int)x.y, a);
+        a = __dp4a((int)w[r].z, (int)x.z, a);
+        a = __dp4a((int)w[r].w, (int)x.w, a);
+        acc[r][m] = a;
+      }
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < GEMV_ROWS; ++r)
+#pragma unroll
+    for (int m = 0; m < MT; ++m) acc[r][m] = warp_sum_i(acc[r][m]);
+  // lane l < MT*GEMV_ROWS finishes element (m = l % MT, r = l / MT)
+#pragma unroll
+  for (int r = 0; r < GEMV_ROWS; ++r)
+#pragma unroll
+    for (int m = 0; m < MT; ++m) {
+      if (lane == r * MT + m) {
+        const int n = n0 + r;
+        if (n < p.N && m < p.M) {
+          const long long off = (long long)m * p.ldo + n;
+          float v = mul_rn(mul_rn((float)acc[r][m], p.a_scale[m]), p.w_scale[n]);
+          if (p.bias) v = add_rn(v, __half2float(p.bias[n]));
+          if (p.residual) v = add_rn(v, __half2float(p.residual[off]));
+          p.out[off] = __float2half_rn(v);
+          if (p.acc_dump) p.acc_dump[off] = acc[r][m];
+        }
+      }
+    }
+}
+
+template <int MT>
+static int launch_gemv(const int8_t* A, const int8_t* W, const GemmParams& p, cudaStream_t st) {
+  const size_t smem = (size_t)MT * p.K;
+  static size_t attr = 48 * 1024;
+  if (smem > attr) {
+    if (smem > 200 * 1024) return ERR_TOO_LARGE;
+    if (cudaFuncSetAttribute(gemv_i8_kernel<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(200 * 1024)) != cudaSuccess)
+      return ERR_ARCH;
+    attr = 200 * 1024;
+  }
+  const int rows_per_cta = GEMV_WARPS * GEMV_ROWS;
+  const int grid = (p.N + rows_per_cta - 1) / rows_per_cta;
+  gemv_i8_kernel<MT><<<grid, GEMV_WARPS * 32, smem, st>>>(A, W, p);
+  return launch_status();
+}
+
+// =============================================================================================
+// entry
+// =============================================================================================
+int gemm_w8a8(const int8_t* A, const int8_t* W, const float* a_scale, const float* w_scale, const void* bias,
+              const void* residual, void* out, int32_t* acc_dump, int M, int N, int K, int schedule, cudaStream_t st) {
+  if (!A || !W || !a_scale || !w_scale || !out) return ERR_NULL_PTR;
+  if (M == 0 || N == 0) return OK;
+  if (M < 0 || N < 0 || K <= 0 || (K & 15) || (N & 7)) return ERR_BAD_SHAPE;
+  auto mis = [](const void* q) { return q && (reinterpret_cast<uintptr_t>(q) & 15); };
+  if (mis(A) || mis(W) || mis(w_scale) || mis(bias) || mis(residual) || mis(out) || mis(acc_dump)) return ERR_BAD_ALIGN;
+  GemmParams p{a_scale, w_scale, (const __half*)bias, (const __half*)residual, (__half*)out, nullptr, acc_dump, M, N, K, N};
+  // schedule: 0 = auto, 1 = force tensor-core path, 2 = force streaming path (M <= 8 only)
+  const bool gemv = (schedule == 2) || (schedule == 0 && M <= GEMV_MAX_M);
+  if (gemv) {
+    if (M > GEMV_MAX_M) return ERR_UNSUPPORTED;
+    if (M == 1) return launch_gemv<1>(A, W, p, st);
+    if (M == 2) return launch_gemv<2>(A, W, p, st);
+    if (M <= 4) return launch_gemv<4>(A, W, p, st);
+    return launch_gemv<8>(A, W, p, st);
+  }
+  const int m_tiles = (M + BM - 1) / BM;
+  const int sms = sm_count();
+  if (N >= 256 && m_tiles * ((N + 255) / 256) >= sms) return launch_tc<256, 4, KIND_I8>(A, W, p, st);
+  if (N >= 128 && m_tiles * ((N + 127) / 128) >= sms) return launch_tc<128, 6, KIND_I8>(A, W, p, st);
+  if (N >= 64) return launch_tc<64, 8, KIND_I8>(A, W, p, st);
+  return launch_tc<32, 8, KIND_I8>(A, W, p, st);
+}
+
+// =============================================================================================
+// fp16 lm_head:  logits[M,V] (fp32) = x[M,d] (fp16) . W[V,d]^T (fp16), fp32 accumulation
+// =============================================================================================
+template <int MT>
+__global__ void __launch_bounds__(GEMV_WARPS * 32)
+gemv_f16_kernel(const __half* __restrict__ X, const __half* __restrict__ W, float* __restrict__ out, int M, int N, int K) {
+  extern __shared__ uint8_t xs[];   // [MT][K] fp16
+  const int kvec = K >> 3;          // 8 halves per 16 bytes
+  for (int i = threadIdx.x; i < MT * kvec; i += blockDim.x) {
+    const int m = i / kvec, c = i - m * kvec;
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (m < M) v = ld_v4(X + (long long)m * K + c * 8);
+    reinterpret_cast<uint4*>(xs)[i] = v;
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n0 = (blockIdx.x * GEMV_WARPS + warp) * GEMV_ROWS;
+  if (n0 >= N) return;
+  float acc[GEMV_ROWS][MT];
+#pragma unroll
+  for (int r = 0; r < GEMV_ROWS; ++r)
+#pragma unroll
+    for (int m = 0; m < MT; ++m) acc[r][m] = 0.f;
+  const __half* wrow[GEMV_ROWS];
+#pragma unroll
+  for (int r = 0; r < GEMV_ROWS; ++r) wrow[r] = W + (long long)min(n0 + r, N - 1) * K;
+  constexpr int UNR = 4;
+  for (int c = lane; c < kvec; c += UNR * 32) {
+    uint4 w[UNR][GEMV_ROWS];
+#pragma unroll
+    for (int u = 0; u < UNR; ++u)
+#pragma unroll
+      for (int r = 0; r < GEMV_ROWS; ++r)
+        w[u][r] = (c + u * 32 < kvec) ? ld_nc_v4(wrow[r] + (c + u * 32) * 8) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+    for (int u = 0; u < UNR; ++u) {
+      if (c + u * 32 < kvec) {
+#pragma unroll
+        for (int m = 0; m < MT; ++m) {
+          const uint4 x = reinterpret_cast<const uint4*>(xs)[m * kvec + c + u * 32];
+          const float2 x0 = h2_to_f2(x.x), x1 = h2_to_f2(x.y), x2 = h2_to_f2(x.z), x3 = h2_to_f2(x.w);
+#pragma unroll
+          for (int r = 0; r < GEMV_ROWS; ++r) {
+            const float2 w0 = h2_to_f2(w[u][r].x), w1 = h2_to_f2(w[u][r].y), w2 = h2_to_f2(w[u][r].z), w3 = h2_to_f2(w[u][r].w);
+            float a = acc[r][m];
+            a = fmaf(w0.x, x0.x, a); a = fmaf(w0.y, x0.y, a); a = fmaf(w1.x, x1.x, a); a = fmaf(w1.y, x1.y, a);
+            a = fmaf(w2.x, x2.x, a); a = fmaf(w2.y, x2.y, a); a = fmaf(w3.x, x3.x, a); a = fmaf(w3.y, x3.y, a);
+            acc[r][m] = a;
+          }
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < GEMV_ROWS; ++r)
+#pragma unroll
+    for (int m = 0; m < MT; ++m) {
+      const float v = warp_sum(acc[r][m]);
+      if (lane == r * MT + m && n0 + r < N && m < M) out[(long long)m * N + n0 + r] = v;
+    }
+}
+
+template <int MT>
+static int launch_gemv_f16(const __half* X, const __half* W, float* out, int M, int N, int K, cudaStream_t st) {
+  const size_t smem = (size_t)MT * K * 2;
+  static size_t attr = 48 * 1024;
+  if (smem > attr) {
+    if (smem > 200 * 1024) return ERR_TOO_LARGE;
+    if (cudaFuncSetAttribute(gemv_f16_kernel<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(200 * 1024)) != cudaSuccess)
+      return ERR_ARCH;
+    attr = 200 * 1024;
+  }
+  const int rows_per_cta = GEMV_WARPS * GEMV_ROWS;
+  gemv_f16_kernel<MT><<<(N + rows_per_cta - 1) / rows_per_cta, GEMV_WARPS * 32, smem, st>>>(X, W, out, M, N, K);
+  return launch_status();
+}
+
+int lm_head(const void* x, const void* W, float* logits, int M, int V, int d, cudaStream_t st) {
+  if (!x || !W || !logits) return ERR_NULL_PTR;
+  if (M == 0 || V == 0) return OK;
+  if (M < 0 || V < 0 || d <= 0 || (d & 7) || (V & 3)) return ERR_BAD_SHAPE;
+  auto mis = [](const void* q) { return q && (reinterpret_cast<uintptr_t>(q) & 15); };
+  if (mis(x) || mis(W) || mis(logits)) return ERR_BAD_ALIGN;
+  if (M <= GEMV_MAX_M) {
+    if (M == 1) return launch_gemv_f16<1>((const __half*)x, (const __half*)W, logits, M, V, d, st);
+    if (M == 2) return launch_gemv_f16<2>((const __half*)x, (const __half*)W, logits, M, V, d, st);
+    if (M <= 4) return launch_gemv_f16<4>((const __half*)x, (const __half*)W, logits, M, V, d, st);
+    return launch_gemv_f16<8>((const __half*)x, (const __half*)W, logits, M, V, d, st);
+  }
+  GemmParams p{nullptr, nullptr, nullptr, nullptr, nullptr, logits, nullptr, M, V, d, V};
+  const int m_tiles = (M + BM - 1) / BM;
+  if (V >= 256 && m_tiles * ((V + 255) / 256) >= sm_count()) return launch_tc<256, 4, KIND_F16>(x, W, p, st);
+  if (V >= 128) return launch_tc<128, 6, KIND_F16>(x, W, p, st);
+  return launch_tc<64, 8, KIND_F16>(x, W, p, st);
+}
+
+}  // namespace b2

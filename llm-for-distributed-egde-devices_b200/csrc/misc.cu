@@ -1,0 +1,87 @@
+// Embedding gather (+ learned positions for GPT-2) and greedy argmax over the logits.
+// Reference call sites: token embedding inside HF `model(**inputs)` / `generate`
+// (Code/Quantised Models/models_quant_updated.py:66-67, :84-93); greedy selection is the
+// `do_sample=False` subset of `generate` that the build's Pipeline exposes.
+#include "common.cuh"
+
+namespace b2 {
+
+__global__ void __launch_bounds__(256)
+embed_kernel(const long long* __restrict__ ids, const int* __restrict__ positions, const __half* __restrict__ table,
+             const __half* __restrict__ pos_table, __half* __restrict__ out, int d, int vocab) {
+  const int t = blockIdx.x;
+  long long id = ids[t];
+  id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
+  const __half* src = table + id * d;
+  const __half* ps = pos_table ? pos_table + (long long)positions[t] * d : nullptr;
+  __half* dst = out + (long long)t * d;
+  for (int c = threadIdx.x; c < (d >> 3); c += blockDim.x) {
+    uint4 u = ld_v4(src + c * 8);
+    if (ps) {   // fp32 add, one rounding (oracle: stage_forward)
+      const uint4 q = ld_v4(ps + c * 8);
+      const uint32_t* a = &u.x;
+      const uint32_t* b = &q.x;
+      uint32_t o[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 x = h2_to_f2(a[e]), y = h2_to_f2(b[e]);
+        o[e] = f2_to_h2(add_rn(x.x, y.x), add_rn(x.y, y.y));
+      }
+      u = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+    st_v4(dst + c * 8, u);
+  }
+}
+
+int embed(const long long* ids, const int* positions, const void* table, const void* pos_table, void* out, int T, int d,
+          int vocab, cudaStream_t st) {
+  if (T == 0) return OK;
+  if (!ids || !table || !out || (pos_table && !positions)) return ERR_NULL_PTR;
+  if (T < 0 || d <= 0 || (d & 7) || vocab <= 0) return ERR_BAD_SHAPE;
+  embed_kernel<<<T, 256, 0, st>>>(ids, positions, (const __half*)table, (const __half*)pos_table, (__half*)out, d, vocab);
+  return launch_status();
+}
+
+// one CTA per row; ties resolve to the lowest index (torch.argmax / HF greedy convention)
+__global__ void __launch_bounds__(1024)
+argmax_kernel(const float* __restrict__ logits, long long* __restrict__ out, int V) {
+  __shared__ float sv[32];
+  __shared__ int si[32];
+  const float* row = logits + (long long)blockIdx.x * V;
+  float best = -INFINITY;
+  int bi = 0x7fffffff;
+  for (int i = threadIdx.x; i < V; i += blockDim.x) {
+    const float v = row[i];
+    if (v > best || (v == best && i < bi)) { best = v; bi = i; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+  }
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  if (l == 0) { sv[w] = best; si[w] = bi; }
+  __syncthreads();
+  if (w == 0) {
+    best = l < (blockDim.x >> 5) ? sv[l] : -INFINITY;
+    bi = l < (blockDim.x >> 5) ? si[l] : 0x7fffffff;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+    }
+    if (l == 0) out[blockIdx.x] = bi == 0x7fffffff ? 0 : bi;
+  }
+}
+
+int argmax_rows(const float* logits, long long* out, int T, int V, cudaStream_t st) {
+  if (T == 0) return OK;
+  if (!logits || !out) return ERR_NULL_PTR;
+  if (T < 0 || V <= 0) return ERR_BAD_SHAPE;
+  argmax_kernel<<<T, 1024, 0, st>>>(logits, out, V);
+  return launch_status();
+}
+
+}  // namespace b2

@@ -1,0 +1,152 @@
+"""Torch-tensor front ends of the C-ABI entry points (one function per entry point).
+
+Each wrapper only validates dtypes/devices, allocates the output with torch (device memory is
+torch's job here) and forwards raw pointers.  All compute happens in libb200stage.so.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _abi
+from ._abi import check, ptr, stream_handle
+
+ACT_SILU_MUL, ACT_GELU_MUL, ACT_GELU, ACT_SILU = 0, 1, 2, 3
+
+
+def _cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise ValueError("b200stage ops need CUDA tensors (there is no CPU path)")
+        if t is not None and not t.is_contiguous():
+            raise ValueError("b200stage ops need contiguous tensors")
+
+
+def norm_quant(x, gamma, beta=None, smooth=None, eps=1e-5, out_q=None, out_scale=None):
+    """x [T,d] fp16 -> (q [T,d] int8, scale [T] fp32).  b2_norm_quant."""
+    _cuda(x, gamma, beta, smooth)
+    T, d = x.shape
+    q = out_q if out_q is not None else torch.empty((T, d), dtype=torch.int8, device=x.device)
+    s = out_scale if out_scale is not None else torch.empty((T,), dtype=torch.float32, device=x.device)
+    check(_abi.lib().b2_norm_quant(ptr(x), ptr(gamma), ptr(beta), ptr(smooth), ptr(q), ptr(s), T, d, float(eps),
+                                   stream_handle()), "b2_norm_quant")
+    return q, s
+
+
+def norm(x, gamma, beta=None, eps=1e-5, out=None):
+    """x [T,d] fp16 -> normalised fp16 [T,d].  b2_norm."""
+    _cuda(x, gamma, beta)
+    T, d = x.shape
+    y = out if out is not None else torch.empty_like(x)
+    check(_abi.lib().b2_norm(ptr(x), ptr(gamma), ptr(beta), ptr(y), T, d, float(eps), stream_handle()), "b2_norm")
+    return y
+
+
+def smooth_quant(x, smooth=None, out_q=None, out_scale=None):
+    """x [T,K] fp16 -> (q int8, scale fp32).  b2_smooth_quant."""
+    _cuda(x, smooth)
+    T, K = x.shape
+    q = out_q if out_q is not None else torch.empty((T, K), dtype=torch.int8, device=x.device)
+    s = out_scale if out_scale is not None else torch.empty((T,), dtype=torch.float32, device=x.device)
+    check(_abi.lib().b2_smooth_quant(ptr(x), ptr(smooth), ptr(q), ptr(s), T, K, stream_handle()), "b2_smooth_quant")
+    return q, s
+
+
+def act_mul_quant(gate_up, smooth=None, act=ACT_SILU_MUL, out_q=None, out_scale=None):
+    """gate_up [T,2F] (gated) or [T,F] (ungated) fp16 -> (q [T,F] int8, scale).  b2_act_mul_quant."""
+    _cuda(gate_up, smooth)
+    T = gate_up.shape[0]
+    F = gate_up.shape[1] // 2 if act in (ACT_SILU_MUL, ACT_GELU_MUL) else gate_up.shape[1]
+    q = out_q if out_q is not None else torch.empty((T, F), dtype=torch.int8, device=gate_up.device)
+    s = out_scale if out_scale is not None else torch.empty((T,), dtype=torch.float32, device=gate_up.device)
+    check(_abi.lib().b2_act_mul_quant(ptr(gate_up), ptr(smooth), ptr(q), ptr(s), T, F, int(act), stream_handle()),
+          "b2_act_mul_quant")
+    return q, s
+
+
+def gemm_w8a8(a_q, w_q, a_scale, w_scale, bias=None, residual=None, out=None, acc_dump=None, schedule=0):
+    """a_q [M,K] int8, w_q [N,K] int8 -> out [M,N] fp16.  b2_gemm_w8a8 (schedule 0) / _sched."""
+    _cuda(a_q, w_q, a_scale, w_scale, bias, residual, out, acc_dump)
+    M, K = a_q.shape
+    N = w_q.shape[0]
+    if w_q.shape[1] != K:
+        raise ValueError("K mismatch")
+    o = out if out is not None else torch.empty((M, N), dtype=torch.float16, device=a_q.device)
+    L = _abi.lib()
+    if schedule == 0:
+        rc = L.b2_gemm_w8a8(ptr(a_q), ptr(w_q), ptr(a_scale), ptr(w_scale), ptr(bias), ptr(residual), ptr(o),
+                            ptr(acc_dump), M, N, K, stream_handle())
+    else:
+        rc = L.b2_gemm_w8a8_sched(ptr(a_q), ptr(w_q), ptr(a_scale), ptr(w_scale), ptr(bias), ptr(residual), ptr(o),
+                                  ptr(acc_dump), M, N, K, int(schedule), stream_handle())
+    check(rc, "b2_gemm_w8a8")
+    return o
+
+
+def rope_kv_append(qkv, cos, sin, positions, kcache, vcache, H, KV, hd, seq_ids=None, seq0=0, use_rope=True):
+    """qkv [T,(H+2KV)*hd] fp16 (q rotated in place); caches [rows,KV,Smax,hd].  b2_rope_kv_append."""
+    _cuda(qkv, cos, sin, positions, kcache, vcache, seq_ids)
+    T = qkv.shape[0]
+    Smax = kcache.shape[2]
+    check(_abi.lib().b2_rope_kv_append(ptr(qkv), qkv.stride(0), ptr(cos), ptr(sin), ptr(positions), ptr(seq_ids),
+                                       int(seq0), ptr(kcache), ptr(vcache), T, H, KV, hd, Smax, int(bool(use_rope)),
+                                       stream_handle()), "b2_rope_kv_append")
+
+
+def decode_attn_workspace_bytes(B, H, KV, hd, max_seqlen, window=0):
+    return int(_abi.lib().b2_decode_attn_workspace_bytes(B, H, KV, hd, int(max_seqlen), int(window)))
+
+
+def decode_attn(qkv, kcache, vcache, seqlens, H, KV, hd, max_seqlen, scale, window=0, rows=None, out=None,
+                workspace=None):
+    """One query token per sequence; q read in place from the qkv buffer.  b2_decode_attn."""
+    _cuda(qkv, kcache, vcache, seqlens, rows, out, workspace)
+    B = qkv.shape[0]
+    Smax = kcache.shape[2]
+    o = out if out is not None else torch.empty((B, H * hd), dtype=torch.float16, device=qkv.device)
+    wsb = 0 if workspace is None else workspace.numel() * workspace.element_size()
+    check(_abi.lib().b2_decode_attn(ptr(qkv), qkv.stride(0), ptr(kcache), ptr(vcache), ptr(seqlens), ptr(rows), ptr(o),
+                                    o.stride(0), ptr(workspace), wsb, B, H, KV, hd, Smax, int(max_seqlen),
+                                    float(scale), int(window), stream_handle()), "b2_decode_attn")
+    return o
+
+
+def prefill_attn(qkv, kcache, vcache, pos0, row, H, KV, hd, scale, window=0, out=None):
+    """Causal attention for one chunk of one sequence.  b2_prefill_attn."""
+    _cuda(qkv, kcache, vcache, out)
+    T = qkv.shape[0]
+    Smax = kcache.shape[2]
+    o = out if out is not None else torch.empty((T, H * hd), dtype=torch.float16, device=qkv.device)
+    check(_abi.lib().b2_prefill_attn(ptr(qkv), qkv.stride(0), ptr(kcache), ptr(vcache), ptr(o), o.stride(0), T,
+                                     int(pos0), int(row), H, KV, hd, Smax, float(scale), int(window),
+                                     stream_handle()), "b2_prefill_attn")
+    return o
+
+
+def embed(ids, table, positions=None, pos_table=None, out=None):
+    """ids [T] int64 -> [T,d] fp16.  b2_embed."""
+    _cuda(ids, table, positions, pos_table)
+    T = ids.shape[0]
+    V, d = table.shape
+    o = out if out is not None else torch.empty((T, d), dtype=torch.float16, device=ids.device)
+    check(_abi.lib().b2_embed(ptr(ids), ptr(positions), ptr(table), ptr(pos_table), ptr(o), T, d, V, stream_handle()),
+          "b2_embed")
+    return o
+
+
+def lm_head(x, w, out=None):
+    """x [M,d] fp16, w [V,d] fp16 -> logits [M,V] fp32.  b2_lm_head."""
+    _cuda(x, w)
+    M, d = x.shape
+    V = w.shape[0]
+    o = out if out is not None else torch.empty((M, V), dtype=torch.float32, device=x.device)
+    check(_abi.lib().b2_lm_head(ptr(x), ptr(w), ptr(o), M, V, d, stream_handle()), "b2_lm_head")
+    return o
+
+
+def argmax(logits, out=None):
+    """logits [T,V] fp32 -> int64 [T].  b2_argmax."""
+    _cuda(logits)
+    T, V = logits.shape
+    o = out if out is not None else torch.empty((T,), dtype=torch.int64, device=logits.device)
+    check(_abi.lib().b2_argmax(ptr(logits), ptr(o), T, V, stream_handle()), "b2_argmax")
+    return o

@@ -1,0 +1,198 @@
+"""Layer-range shard construction: synthetic (seeded) or checkpoint weights -> W8A8 stage weights.
+
+Counterpart of the reference's loaders ``load_int8_model`` (Code/Quantised Models/models_quant_updated.py:25-40)
+and ``load_model_int8_cpu`` (Code/C-DAC Server/try.py:198-206), which load a *whole* model and let
+bitsandbytes / quantize_dynamic quantise every nn.Linear on load.  Here a stage loads only its
+contiguous layer range and quantises offline with the SmoothQuant recipe of SURVEY.md §8(c):
+
+  smoothing   s[k] = amax_act[k]^alpha / amax_w[k]^(1-alpha)           (alpha = 0.5)
+  weights     W'[n,k] = W[n,k]*s[k];  s_w[n] = max_k|W'[n,k]|/127;  Wq = clamp(rint(W'/s_w), +-127)
+  activations multiplied by 1/s[k] (vector `sm_*`) inside the fused norm/act quantise kernels.
+
+No checkpoints or network exist in this environment, so weights are random-init from the config
+under a seed (HF default N(0, 0.02); embeddings x8 and tied to lm_head to widen greedy margins,
+SURVEY.md §8d).  Per-layer generators make a stage able to build only its own layers.
+This is host-side set-up code (numpy/torch CPU or torch CUDA), not the hot path.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from .config import ModelConfig
+
+ALPHA = 0.5
+
+
+def _gen(seed: int, *tags: int) -> torch.Generator:
+    g = torch.Generator(device="cpu")
+    g.manual_seed((seed * 1000003 + sum((t + 1) * 7919 ** (i + 1) for i, t in enumerate(tags))) % (2 ** 63 - 1))
+    return g
+
+
+def init_layer_fp32(cfg: ModelConfig, layer: int, seed: int = 0) -> dict:
+    """fp32 weights of one decoder layer (HF naming collapsed: wqkv = [q;k;v], wgu = [gate;up])."""
+    g = _gen(seed, layer)
+    d, F = cfg.d_model, cfg.ffn
+    std = 0.02
+
+    def rn(*shape):
+        return torch.randn(*shape, generator=g, dtype=torch.float32) * std
+
+    w = dict(
+        ln1_g=1.0 + 0.1 * torch.randn(d, generator=g), ln2_g=1.0 + 0.1 * torch.randn(d, generator=g),
+        wqkv=rn(cfg.qkv_out, d), wo=rn(d, cfg.n_heads * cfg.head_dim), wgu=rn(cfg.up_out, d), wd=rn(d, F))
+    if cfg.norm == "layernorm":
+        w["ln1_b"] = 0.02 * torch.randn(d, generator=g)
+        w["ln2_b"] = 0.02 * torch.randn(d, generator=g)
+    if cfg.bias:
+        w["b_qkv"] = rn(cfg.qkv_out)
+        w["b_o"] = rn(d)
+        w["b_gu"] = rn(cfg.up_out)
+        w["b_d"] = rn(d)
+    return w
+
+
+def init_embed_fp32(cfg: ModelConfig, seed: int = 0) -> dict:
+    g = _gen(seed, 100003)
+    e = torch.randn(cfg.vocab, cfg.d_model, generator=g, dtype=torch.float32) * (0.02 * 8.0)
+    out = dict(embed=e, lnf_g=1.0 + 0.1 * torch.randn(cfg.d_model, generator=g))
+    if cfg.norm == "layernorm":
+        out["lnf_b"] = 0.02 * torch.randn(cfg.d_model, generator=g)
+    if not cfg.rope:
+        out["pos_embed"] = torch.randn(cfg.max_pos, cfg.d_model, generator=g, dtype=torch.float32) * 0.02
+    out["lm_head"] = e if cfg.tie_embeddings else torch.randn(cfg.vocab, cfg.d_model, generator=g) * 0.02
+    return out
+
+
+def _smooth_vec(W: torch.Tensor, act_amax: torch.Tensor | None, alpha: float) -> torch.Tensor:
+    """s[k] for weight W [N,K]; act_amax None -> 1 (weight-only statistics)."""
+    w_amax = W.abs().amax(dim=0).clamp_min(1e-5)
+    a = torch.ones_like(w_amax) if act_amax is None else act_amax.to(w_amax).clamp_min(1e-5)
+    s = a.pow(alpha) / w_amax.pow(1.0 - alpha)
+    return s.clamp(1e-4, 1e4).to(torch.float32)
+
+
+def quantize_weight(W: torch.Tensor, s: torch.Tensor | None):
+    """W [N,K] fp32 (any device) -> (Wq int8 [N,K], s_w fp32 [N]).  Same formula as
+    oracle/w8a8.py:quantize_weight (checked in tests/test_weights.py)."""
+    W = W.to(torch.float32)
+    if s is not None:
+        W = W * s[None, :]
+    amax = W.abs().amax(dim=1)
+    safe = torch.where(amax > 0, amax, torch.ones_like(amax))
+    step = safe / 127.0
+    scale = torch.where(amax > 0, amax / 127.0, torch.zeros_like(amax))
+    Wq = torch.clamp(torch.round(W / step[:, None]), -127, 127).to(torch.int8)
+    return Wq.contiguous(), scale.to(torch.float32).contiguous()
+
+
+def quantize_layer(cfg: ModelConfig, w: dict, act_stats: dict | None = None, alpha: float = ALPHA) -> dict:
+    """fp32 layer dict -> W8A8 layer dict (torch tensors on w's device).
+
+    act_stats (optional): per-input-channel activation absmax for 'qkv', 'o', 'gu', 'd' gathered by
+    a calibration pass; absent -> weight-only smoothing statistics.
+    """
+    st = act_stats or {}
+    out = {}
+    for name, wk, smk, sk in (("qkv", "wqkv", "sm_qkv", "s_qkv"), ("o", "wo", "sm_o", "s_o"),
+                              ("gu", "wgu", "sm_gu", "s_gu"), ("d", "wd", "sm_d", "s_d")):
+        s = _smooth_vec(w[wk], st.get(name), alpha)
+        out[wk], out[sk] = quantize_weight(w[wk], s)
+        out[smk] = (1.0 / s).to(torch.float32).contiguous()
+    for k in ("ln1_g", "ln2_g", "ln1_b", "ln2_b", "b_qkv", "b_o", "b_gu", "b_d"):
+        if k in w:
+            out[k] = w[k].to(torch.float16).contiguous()
+    return out
+
+
+def build_stage_weights(cfg: ModelConfig, layer_begin: int, layer_end: int, first: bool, last: bool,
+                        seed: int = 0, device="cpu", act_stats: list | None = None) -> dict:
+    """Seeded synthetic W8A8 shard for layers [layer_begin, layer_end) (CPU generation, exact
+    and reproducible; used by the parity tests so the oracle sees identical weights)."""
+    sw = dict(first=first, last=last, layers=[])
+    for li in range(layer_begin, layer_end):
+        lw = quantize_layer(cfg, init_layer_fp32(cfg, li, seed), None if act_stats is None else act_stats[li])
+        sw["layers"].append({k: v.to(device) for k, v in lw.items()})
+    if first or last:
+        e = init_embed_fp32(cfg, seed)
+        if first:
+            sw["embed"] = e["embed"].to(torch.float16).to(device)
+            if "pos_embed" in e:
+                sw["pos_embed"] = e["pos_embed"].to(torch.float16).to(device)
+        if last:
+            sw["lnf_g"] = e["lnf_g"].to(torch.float16).to(device)
+            if "lnf_b" in e:
+                sw["lnf_b"] = e["lnf_b"].to(torch.float16).to(device)
+            sw["lm_head"] = sw["embed"] if (first and cfg.tie_embeddings) else e["lm_head"].to(torch.float16).to(device)
+    return sw
+
+
+def build_stage_weights_fast(cfg: ModelConfig, layer_begin: int, layer_end: int, first: bool, last: bool,
+                             seed: int = 0, device="cuda") -> dict:
+    """Same structure generated directly on `device` with torch's device RNG (benchmarks: the
+    7B/13B shapes would take minutes through the CPU generator).  Statistically identical,
+    not bit-identical to build_stage_weights."""
+    dev = torch.device(device)
+    g = torch.Generator(device=dev)
+    sw = dict(first=first, last=last, layers=[])
+    d, F = cfg.d_model, cfg.ffn
+    for li in range(layer_begin, layer_end):
+        g.manual_seed(seed * 1000003 + li)
+
+        def rn(*shape, std=0.02):
+            return torch.randn(*shape, generator=g, dtype=torch.float32, device=dev) * std
+
+        w = dict(ln1_g=1.0 + rn(d, std=0.1), ln2_g=1.0 + rn(d, std=0.1))
+        lw = {}
+        for wk, shape in (("wqkv", (cfg.qkv_out, d)), ("wo", (d, cfg.n_heads * cfg.head_dim)),
+                          ("wgu", (cfg.up_out, d)), ("wd", (d, F))):
+            W = rn(*shape)
+            s = _smooth_vec(W, None, ALPHA)
+            sfx = wk[1:]
+            lw[wk], lw["s_" + sfx] = quantize_weight(W, s)
+            lw["sm_" + sfx] = (1.0 / s).contiguous()
+            del W
+        lw["ln1_g"] = w["ln1_g"].to(torch.float16)
+        lw["ln2_g"] = w["ln2_g"].to(torch.float16)
+        if cfg.norm == "layernorm":
+            lw["ln1_b"] = rn(d).to(torch.float16)
+            lw["ln2_b"] = rn(d).to(torch.float16)
+        if cfg.bias:
+            lw["b_qkv"] = rn(cfg.qkv_out).to(torch.float16)
+            lw["b_o"] = rn(d).to(torch.float16)
+            lw["b_gu"] = rn(cfg.up_out).to(torch.float16)
+            lw["b_d"] = rn(d).to(torch.float16)
+        sw["layers"].append(lw)
+    if first or last:
+        g.manual_seed(seed * 1000003 + 100003)
+        e = (torch.randn(cfg.vocab, cfg.d_model, generator=g, dtype=torch.float32, device=dev) * 0.16).to(torch.float16)
+        if first:
+            sw["embed"] = e
+            if not cfg.rope:
+                sw["pos_embed"] = (torch.randn(cfg.max_pos, d, generator=g, device=dev) * 0.02).to(torch.float16)
+        if last:
+            sw["lnf_g"] = (1.0 + 0.1 * torch.randn(d, generator=g, device=dev)).to(torch.float16)
+            if cfg.norm == "layernorm":
+                sw["lnf_b"] = (0.02 * torch.randn(d, generator=g, device=dev)).to(torch.float16)
+            sw["lm_head"] = e
+    return sw
+
+
+def to_numpy(sw: dict) -> dict:
+    """Stage weights as plain numpy arrays (the form oracle/w8a8.py consumes)."""
+    def cv(v):
+        return v.detach().cpu().numpy() if isinstance(v, torch.Tensor) else v
+    out = {k: cv(v) for k, v in sw.items() if k != "layers"}
+    out["layers"] = [{k: cv(v) for k, v in lw.items()} for lw in sw["layers"]]
+    return out
+
+
+def rope_table(head_dim: int, max_pos: int, theta: float = 10000.0):
+    """cos/sin fp32 [max_pos, head_dim/2]: angle formed in fp32 as HF does
+    (modeling_llama.py:100-126), cos/sin evaluated in fp64 and rounded once.  Host-side table; the
+    kernels only read it, so device and oracle use bit-identical values."""
+    i = np.arange(0, head_dim, 2, dtype=np.float64)
+    inv_freq = (1.0 / (theta ** (i / head_dim))).astype(np.float32).astype(np.float64)
+    ang = (np.arange(max_pos, dtype=np.float64)[:, None] * inv_freq[None, :]).astype(np.float32).astype(np.float64)
+    return torch.from_numpy(np.cos(ang).astype(np.float32)), torch.from_numpy(np.sin(ang).astype(np.float32))

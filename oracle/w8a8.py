@@ -1,0 +1,405 @@
+"""Tier-S oracle: CPU restatement (numpy) of the W8A8 decoder-block forward.
+
+TEST INFRASTRUCTURE ONLY.  Nothing under ``oracle/`` is on the product path: only
+``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s CPU-baseline leg may import it.
+
+PARITY UNPINNED.  The reference (parthabp55/LLM-for-Distributed-Egde-Devices) ships no
+tests, golden vectors or fixtures, and the arithmetic of its quantised path
+lives in unvendored, unpinned third-party code (``Code/others/requirements.txt:1-10``:
+transformers, bitsandbytes).  This file therefore restates
+
+  * the decoder-block *structure* the reference executes through HF ``generate``
+    (call sites ``Code/Quantised Models/models_quant_updated.py:84-93`` and ``:66-67``;
+    block = transformers 5.5.0 ``models/llama/modeling_llama.py:303-334`` (layer),
+    ``:251-289`` (attention), ``:199-222`` (eager attention), ``:182-184`` (MLP),
+    ``:62-67`` (RMSNorm), rotary ``:128-153``), and
+  * the *W8A8 numerics* that ``BASELINE.json:north_star`` specifies (SmoothQuant,
+    arXiv 2211.10438: per-output-channel symmetric int8 weights, per-token dynamic
+    symmetric int8 activations, exact int32 accumulation, fp32 dequantising epilogue).
+    bitsandbytes ``Linear8bitLt`` (``models_quant_updated.py:30-32``) with no activation
+    outlier >= 6.0 is this scheme with smoothing alpha = 0.
+
+Every floating-point step is written as individually rounded IEEE fp32 operations
+(no fused multiply-add, no library transcendental) so the CUDA kernels can reproduce the
+int8 activations, the int32 accumulators and the fp16 GEMM outputs bit for bit.  The one
+exception is the softmax in attention (sum order and exp differ) which is compared within
+a stated tolerance.
+
+Pinned formulas (shared with the kernels in ``llm-for-distributed-egde-devices_b200/csrc``):
+
+  quantise row y (fp32):  amax = max|y|;  scale = amax / 127;  inv = 127 / amax;
+                          q = clamp(rint(y * inv), -127, 127)   (rint = half-to-even);
+                          amax == 0  ->  q = 0, scale = 0.
+  RMSNorm:   ss = sum_k double(x_k)^2  (fp64; order-insensitive to ~2^-53);
+             var = float(ss / d);  r = 1 / sqrt(var + eps)  (IEEE fp32 div and sqrt);
+             y_k = ((x_k * r) * gamma_k) [* smooth_k]
+  epilogue:  v = (float(acc) * a_scale[m]) * w_scale[n] [+ bias[n]] [+ residual[m,n]]
+             out = fp16(v)   (one rounding)
+  exp_det:   Cody-Waite range reduction + degree-5 polynomial, all separately rounded.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+f32 = np.float32
+f16 = np.float16
+
+# ----------------------------------------------------------------------------------------
+# deterministic transcendental pieces
+# ----------------------------------------------------------------------------------------
+_LOG2E = f32(1.4426950408889634)
+_LN2_HI = f32(0.693359375)            # 355/512: n*_LN2_HI is exact for |n| < 2^15
+_LN2_LO = f32(-2.12194440e-4)
+_EXP_C = [f32(1.9875691500e-4), f32(1.3981999507e-3), f32(8.3334519073e-3),
+          f32(4.1665795894e-2), f32(1.6666665459e-1), f32(5.0000001201e-1)]
+_EXP_CLAMP = f32(80.0)
+
+
+def exp_det(t: np.ndarray) -> np.ndarray:
+    """exp(t) for fp32 t, as a fixed sequence of individually rounded fp32 operations.
+
+    Mirrors ``b2_exp_det`` in csrc/common.cuh operation for operation.
+    """
+    t = np.asarray(t, dtype=f32)
+    t = np.minimum(np.maximum(t, -_EXP_CLAMP), _EXP_CLAMP)
+    n = np.rint(t * _LOG2E).astype(f32)
+    r = (t - n * _LN2_HI).astype(f32)
+    r = (r - (n * _LN2_LO).astype(f32)).astype(f32)
+    p = np.full_like(r, _EXP_C[0])
+    for c in _EXP_C[1:]:
+        p = ((p * r).astype(f32) + c).astype(f32)
+    r2 = (r * r).astype(f32)
+    res = ((p * r2).astype(f32) + r).astype(f32)
+    res = (res + f32(1.0)).astype(f32)
+    return np.ldexp(res, n.astype(np.int32)).astype(f32)
+
+
+def silu_det(g: np.ndarray) -> np.ndarray:
+    """SiLU g*sigmoid(g) (modeling_llama.py:182-184 act_fn) with the deterministic exp."""
+    g = np.asarray(g, dtype=f32)
+    e = exp_det(-g)
+    den = (f32(1.0) + e).astype(f32)
+    return (g / den).astype(f32)
+
+
+def gelu_new_det(u: np.ndarray) -> np.ndarray:
+    """GPT-2 ``gelu_new`` 0.5*u*(1+tanh(sqrt(2/pi)*(u+0.044715*u^3))) with tanh via exp_det."""
+    u = np.asarray(u, dtype=f32)
+    u3 = ((u * u).astype(f32) * u).astype(f32)
+    inner = (u + (f32(0.044715) * u3).astype(f32)).astype(f32)
+    z = (f32(0.7978845608028654) * inner).astype(f32)
+    e = exp_det((f32(2.0) * z).astype(f32))
+    th = (f32(1.0) - (f32(2.0) / (e + f32(1.0)).astype(f32)).astype(f32)).astype(f32)
+    return ((f32(0.5) * u).astype(f32) * (f32(1.0) + th).astype(f32)).astype(f32)
+
+
+# ----------------------------------------------------------------------------------------
+# quantisation
+# ----------------------------------------------------------------------------------------
+def quant_rows(y: np.ndarray):
+    """Per-token (row) dynamic symmetric absmax int8 quantisation of fp32 y [T, K]."""
+    y = np.asarray(y, dtype=f32)
+    amax = np.max(np.abs(y), axis=-1).astype(f32)
+    safe = np.where(amax > 0, amax, f32(1.0)).astype(f32)
+    scale = np.where(amax > 0, (amax / f32(127.0)).astype(f32), f32(0.0)).astype(f32)
+    inv = np.where(amax > 0, (f32(127.0) / safe).astype(f32), f32(0.0)).astype(f32)
+    q = np.rint((y * inv[:, None]).astype(f32))
+    q = np.clip(q, -127, 127).astype(np.int8)
+    return q, scale
+
+
+def rmsnorm_rows(x16: np.ndarray, gamma16: np.ndarray, eps: float) -> np.ndarray:
+    """RMSNorm (modeling_llama.py:62-67) in the pinned fp64-sum / fp32-elementwise form."""
+    x = np.asarray(x16, dtype=f16)
+    xd = x.astype(np.float64)
+    ss = np.sum(xd * xd, axis=-1)
+    var = (ss / x.shape[-1]).astype(f32)
+    r = (f32(1.0) / np.sqrt((var + f32(eps)).astype(f32)).astype(f32)).astype(f32)
+    y = (x.astype(f32) * r[:, None]).astype(f32)
+    return (y * np.asarray(gamma16, dtype=f16).astype(f32)[None, :]).astype(f32)
+
+
+def layernorm_rows(x16, gamma16, beta16, eps: float) -> np.ndarray:
+    """LayerNorm (GPT-2 ``ln_1``/``ln_2``): fp64 moments, fp32 elementwise."""
+    x = np.asarray(x16, dtype=f16)
+    xd = x.astype(np.float64)
+    d = x.shape[-1]
+    mean_d = np.sum(xd, axis=-1) / d
+    var_d = np.sum(xd * xd, axis=-1) / d - mean_d * mean_d
+    mean = mean_d.astype(f32)
+    var = np.maximum(var_d, 0.0).astype(f32)
+    r = (f32(1.0) / np.sqrt((var + f32(eps)).astype(f32)).astype(f32)).astype(f32)
+    y = ((x.astype(f32) - mean[:, None]).astype(f32) * r[:, None]).astype(f32)
+    y = (y * np.asarray(gamma16, dtype=f16).astype(f32)[None, :]).astype(f32)
+    return (y + np.asarray(beta16, dtype=f16).astype(f32)[None, :]).astype(f32)
+
+
+def norm_quant(x16, gamma16, beta16, smooth, eps):
+    """Fused norm -> smoothing multiply -> per-token int8 quantise (kernel b2_norm_quant).
+
+    ``beta16 is None`` selects RMSNorm.  ``smooth`` (fp32 [d], nullable) is the SmoothQuant
+    multiplier 1/s applied to the activation (W carries s).
+    """
+    y = rmsnorm_rows(x16, gamma16, eps) if beta16 is None else layernorm_rows(x16, gamma16, beta16, eps)
+    if smooth is not None:
+        y = (y * np.asarray(smooth, dtype=f32)[None, :]).astype(f32)
+    return quant_rows(y)
+
+
+def smooth_quant(x16, smooth):
+    """fp16 activation -> optional smoothing multiply -> per-token int8 (kernel b2_smooth_quant)."""
+    y = np.asarray(x16, dtype=f16).astype(f32)
+    if smooth is not None:
+        y = (y * np.asarray(smooth, dtype=f32)[None, :]).astype(f32)
+    return quant_rows(y)
+
+
+def act_mul_quant(gate_up16, smooth, act="silu"):
+    """act(gate)*up -> smoothing -> per-token int8 (kernel b2_act_mul_quant).
+
+    gate_up16: fp16 [T, 2F], gate in columns [0,F), up in [F,2F)  (modeling_llama.py:182-184).
+    """
+    gu = np.asarray(gate_up16, dtype=f16).astype(f32)
+    F = gu.shape[1] // 2
+    g, u = gu[:, :F], gu[:, F:]
+    a = silu_det(g) if act == "silu" else gelu_new_det(g)
+    y = (a * u).astype(f32)
+    if smooth is not None:
+        y = (y * np.asarray(smooth, dtype=f32)[None, :]).astype(f32)
+    return quant_rows(y)
+
+
+def act_quant(h16, smooth, act="gelu_new"):
+    """act(h) -> smoothing -> per-token int8, for non-gated MLPs (GPT-2)."""
+    h = np.asarray(h16, dtype=f16).astype(f32)
+    y = gelu_new_det(h) if act == "gelu_new" else silu_det(h)
+    if smooth is not None:
+        y = (y * np.asarray(smooth, dtype=f32)[None, :]).astype(f32)
+    return quant_rows(y)
+
+
+def quantize_weight(W: np.ndarray, s: np.ndarray | None):
+    """Offline weight quantisation: W [N,K] fp32, smoothing s [K] multiplied into columns;
+    per-output-channel symmetric int8."""
+    W = np.asarray(W, dtype=f32)
+    if s is not None:
+        W = (W * np.asarray(s, dtype=f32)[None, :]).astype(f32)
+    amax = np.max(np.abs(W), axis=1).astype(f32)
+    safe = np.where(amax > 0, amax, f32(1.0)).astype(f32)
+    scale = np.where(amax > 0, (amax / f32(127.0)).astype(f32), f32(0.0)).astype(f32)
+    Wq = np.clip(np.rint((W / (safe / f32(127.0)).astype(f32)[:, None]).astype(f32)), -127, 127).astype(np.int8)
+    return Wq, scale
+
+
+# ----------------------------------------------------------------------------------------
+# W8A8 linear
+# ----------------------------------------------------------------------------------------
+def int8_acc(q: np.ndarray, wq: np.ndarray) -> np.ndarray:
+    """Exact int32 accumulators q [M,K] x wq [N,K]^T.  fp64 BLAS is exact here:
+    |acc| <= K*127^2 < 2^53 for any K this path sees (K <= 14336)."""
+    acc = q.astype(np.float64) @ wq.astype(np.float64).T
+    return acc.astype(np.int64).astype(np.int32)
+
+
+def int8_acc_slow(q: np.ndarray, wq: np.ndarray) -> np.ndarray:
+    """Pure integer restatement (int64 einsum) used to pin int8_acc on small shapes."""
+    return np.einsum("mk,nk->mn", q.astype(np.int64), wq.astype(np.int64)).astype(np.int32)
+
+
+def epilogue(acc, a_scale, w_scale, bias16=None, residual16=None) -> np.ndarray:
+    v = (acc.astype(f32) * np.asarray(a_scale, f32)[:, None]).astype(f32)
+    v = (v * np.asarray(w_scale, f32)[None, :]).astype(f32)
+    if bias16 is not None:
+        v = (v + np.asarray(bias16, f16).astype(f32)[None, :]).astype(f32)
+    if residual16 is not None:
+        v = (v + np.asarray(residual16, f16).astype(f32)).astype(f32)
+    return v.astype(f16)
+
+
+def gemm_w8a8(q, wq, a_scale, w_scale, bias16=None, residual16=None):
+    """W8A8 linear with fused dequantising epilogue (kernel b2_gemm_w8a8).
+    Returns (out fp16 [M,N], acc int32 [M,N])."""
+    acc = int8_acc(q, wq)
+    return epilogue(acc, a_scale, w_scale, bias16, residual16), acc
+
+
+# ----------------------------------------------------------------------------------------
+# rotary embedding, KV cache append, attention
+# ----------------------------------------------------------------------------------------
+def rope_table(head_dim: int, max_pos: int, theta: float = 10000.0):
+    """cos/sin tables fp32 [max_pos, head_dim/2] (modeling_llama.py:100-153: inv_freq =
+    theta^(-2i/hd), angle = pos*inv_freq).  Computed in fp64, rounded once; the GPU reads
+    this exact table, so no device-side sincos is involved."""
+    i = np.arange(0, head_dim, 2, dtype=np.float64)
+    inv_freq = (1.0 / (theta ** (i / head_dim))).astype(f32).astype(np.float64)
+    ang = np.arange(max_pos, dtype=np.float64)[:, None] * inv_freq[None, :]
+    ang = ang.astype(f32).astype(np.float64)   # HF forms the angle in fp32
+    return np.cos(ang).astype(f32), np.sin(ang).astype(f32)
+
+
+def apply_rope(x16: np.ndarray, positions: np.ndarray, cos: np.ndarray, sin: np.ndarray) -> np.ndarray:
+    """x16 [T, nheads, hd] fp16 -> rotated fp16.  rotate_half convention
+    (modeling_llama.py:128-153): out[:h] = x[:h]*c - x[h:]*s ; out[h:] = x[h:]*c + x[:h]*s."""
+    x = np.asarray(x16, f16).astype(f32)
+    h = x.shape[-1] // 2
+    c = cos[positions][:, None, :]
+    s = sin[positions][:, None, :]
+    x1, x2 = x[..., :h], x[..., h:]
+    o1 = ((x1 * c).astype(f32) - (x2 * s).astype(f32)).astype(f32)
+    o2 = ((x2 * c).astype(f32) + (x1 * s).astype(f32)).astype(f32)
+    return np.concatenate([o1, o2], axis=-1).astype(f16)
+
+
+def attention(q16, k16, v16, q_pos, scale, window=0):
+    """Causal (optionally sliding-window) attention, eager form (modeling_llama.py:199-222).
+
+    q16 [Tq, H, hd]; k16/v16 [S, KV, hd] (the cache contents for this sequence, positions
+    0..S-1); q_pos [Tq] absolute positions.  Key j is visible to query i iff
+    j <= q_pos[i] and (window == 0 or j > q_pos[i] - window).  fp32 math, fp16 result.
+    Compared against the kernels within tolerance, not bit-exactly.
+    """
+    q = np.asarray(q16, f16).astype(f32)
+    k = np.asarray(k16, f16).astype(f32)
+    v = np.asarray(v16, f16).astype(f32)
+    Tq, H, hd = q.shape
+    S, KV, _ = k.shape
+    g = H // KV
+    out = np.zeros((Tq, H, hd), dtype=f32)
+    j = np.arange(S)[None, :]
+    vis = j <= np.asarray(q_pos)[:, None]
+    if window and window > 0:
+        vis &= j > (np.asarray(q_pos)[:, None] - window)
+    for h in range(H):
+        kh = k[:, h // g, :]
+        vh = v[:, h // g, :]
+        s = (q[:, h, :] @ kh.T) * f32(scale)
+        s = np.where(vis, s, -np.inf)
+        m = np.max(s, axis=-1, keepdims=True)
+        p = np.exp(s - m)
+        p = p / np.sum(p, axis=-1, keepdims=True)
+        out[:, h, :] = p @ vh
+    return out.astype(f16)
+
+
+# ----------------------------------------------------------------------------------------
+# decoder block / stage (Llama, Mistral family)
+# ----------------------------------------------------------------------------------------
+class KVCacheOracle:
+    """Per-stage KV cache, fp16, [layer][B][KV][Smax][hd] like the device layout."""
+
+    def __init__(self, n_layers, batch, kv_heads, max_seq, head_dim):
+        self.k = np.zeros((n_layers, batch, kv_heads, max_seq, head_dim), dtype=f16)
+        self.v = np.zeros_like(self.k)
+        self.seqlens = np.zeros((batch,), dtype=np.int32)
+
+
+def block_forward(h16, lw, cfg, cache: KVCacheOracle, li, seq_ids, positions, cos, sin, trace=None):
+    """One W8A8 decoder layer over T tokens.
+
+    h16 [T,d] fp16; seq_ids [T] (which cache row each token belongs to); positions [T].
+    lw: dict of numpy arrays as produced by weights.quantize_layer (see package).
+    Follows modeling_llama.py:303-334 with every nn.Linear replaced by gemm_w8a8.
+    """
+    H, KV, hd = cfg["n_heads"], cfg["n_kv_heads"], cfg["head_dim"]
+    eps = cfg["eps"]
+    T = h16.shape[0]
+    # --- attention half -------------------------------------------------------------
+    q1, s1 = norm_quant(h16, lw["ln1_g"], lw.get("ln1_b"), lw.get("sm_qkv"), eps)
+    qkv, acc_qkv = gemm_w8a8(q1, lw["wqkv"], s1, lw["s_qkv"], lw.get("b_qkv"), None)
+    qh = qkv[:, : H * hd].reshape(T, H, hd)
+    kh = qkv[:, H * hd: (H + KV) * hd].reshape(T, KV, hd)
+    vh = qkv[:, (H + KV) * hd:].reshape(T, KV, hd)
+    if cfg.get("rope", True):
+        qh = apply_rope(qh, positions, cos, sin)
+        kh = apply_rope(kh, positions, cos, sin)
+    for t in range(T):
+        cache.k[li, seq_ids[t], :, positions[t], :] = kh[t]
+        cache.v[li, seq_ids[t], :, positions[t], :] = vh[t]
+    attn = np.zeros((T, H, hd), dtype=f16)
+    scale = 1.0 / np.sqrt(hd)
+    for b in np.unique(seq_ids):
+        idx = np.nonzero(seq_ids == b)[0]
+        S = int(positions[idx].max()) + 1
+        kb = np.transpose(cache.k[li, b, :, :S, :], (1, 0, 2))
+        vb = np.transpose(cache.v[li, b, :, :S, :], (1, 0, 2))
+        attn[idx] = attention(qh[idx], kb, vb, positions[idx], scale, cfg.get("window", 0))
+    q2, s2 = smooth_quant(attn.reshape(T, H * hd), lw.get("sm_o"))
+    h1, acc_o = gemm_w8a8(q2, lw["wo"], s2, lw["s_o"], lw.get("b_o"), h16)
+    # --- MLP half -------------------------------------------------------------------
+    q3, s3 = norm_quant(h1, lw["ln2_g"], lw.get("ln2_b"), lw.get("sm_gu"), eps)
+    gu, acc_gu = gemm_w8a8(q3, lw["wgu"], s3, lw["s_gu"], lw.get("b_gu"), None)
+    if cfg.get("gated", True):
+        q4, s4 = act_mul_quant(gu, lw.get("sm_d"), cfg.get("act", "silu"))
+    else:
+        q4, s4 = act_quant(gu, lw.get("sm_d"), cfg.get("act", "gelu_new"))
+    h2, acc_d = gemm_w8a8(q4, lw["wd"], s4, lw["s_d"], lw.get("b_d"), h1)
+    if trace is not None:
+        trace.append(dict(q1=q1, s1=s1, acc_qkv=acc_qkv, qkv=qkv, attn=attn, q2=q2, s2=s2, acc_o=acc_o,
+                          h1=h1, q3=q3, s3=s3, acc_gu=acc_gu, gu=gu, q4=q4, s4=s4, acc_d=acc_d, h2=h2))
+    return h2
+
+
+def final_norm(h16, g16, b16, eps):
+    y = rmsnorm_rows(h16, g16, eps) if b16 is None else layernorm_rows(h16, g16, b16, eps)
+    return y.astype(f16)
+
+
+def lm_head(hn16, w16):
+    """Unquantised fp16 lm_head with fp32 accumulation -> fp32 logits."""
+    return (np.asarray(hn16, f16).astype(f32) @ np.asarray(w16, f16).astype(f32).T).astype(f32)
+
+
+def stage_forward(x, sw, cfg, cache, seq_ids, positions, cos, sin, trace=None, logits_rows=None):
+    """Forward over a contiguous layer range (the build-defined Stage contract).
+
+    x: int64 ids [T] if sw['first'] else fp16 hidden [T,d].  Returns fp16 hidden [T,d], or fp32
+    logits for ``logits_rows`` (default: all rows) if sw['last'].
+    """
+    if sw["first"]:
+        h = np.asarray(sw["embed"], f16)[np.asarray(x)]
+        if "pos_embed" in sw:
+            h = (h.astype(f32) + np.asarray(sw["pos_embed"], f16)[positions].astype(f32)).astype(f16)
+    else:
+        h = np.asarray(x, f16)
+    for li, lw in enumerate(sw["layers"]):
+        h = block_forward(h, lw, cfg, cache, li, seq_ids, positions, cos, sin, trace)
+    if not sw["last"]:
+        return h
+    if logits_rows is not None:
+        h = h[logits_rows]
+    hn = final_norm(h, sw["lnf_g"], sw.get("lnf_b"), cfg["eps"])
+    return lm_head(hn, sw["lm_head"])
+
+
+def greedy_generate(stages, cfg, ids, max_new_tokens, max_seq, chunk=None):
+    """Greedy decode through a list of stage-weight dicts (prefill, then one token a step).
+    Returns (tokens [len(ids)+max_new_tokens], top-1 margins per generated token)."""
+    hd = cfg["head_dim"]
+    cos, sin = rope_table(hd, max_seq, cfg.get("rope_theta", 10000.0))
+    caches = [KVCacheOracle(len(s["layers"]), 1, cfg["n_kv_heads"], max_seq, hd) for s in stages]
+    toks = list(int(t) for t in ids)
+    margins = []
+
+    def run(x, pos):
+        seq = np.zeros(len(pos), dtype=np.int64)
+        for s, c in zip(stages, caches):
+            x = stage_forward(x, s, cfg, c, seq, pos, cos, sin,
+                              logits_rows=np.array([len(pos) - 1]) if s["last"] else None)
+        return x
+
+    T = len(toks)
+    chunk = chunk or T
+    logits = None
+    for c0 in range(0, T, chunk):
+        pos = np.arange(c0, min(T, c0 + chunk))
+        logits = run(np.array(toks[c0:c0 + chunk]), pos)
+    for _ in range(max_new_tokens):
+        row = logits[-1]
+        order = np.argsort(row)
+        margins.append(float(row[order[-1]] - row[order[-2]]))
+        nxt = int(order[-1])
+        toks.append(nxt)
+        if len(toks) >= max_seq:
+            break
+        logits = run(np.array([nxt]), np.array([len(toks) - 1]))
+    return np.array(toks, dtype=np.int64), margins
