@@ -1,0 +1,373 @@
+#!/usr/bin/env python
+"""bench.py -- tokens/sec (prefill + decode) of the W8A8 stage path on Llama-2-7B, 1..8 B200.
+
+One step = one pass of the hot path over one batch of synthetic input: per GPU-stage pipeline,
+N prompts (N = number of GPUs/stages; weak scaling: per-GPU layers x tokens is constant) of
+PROMPT tokens are prefilled (chunked) and NEW tokens are greedily decoded for each.
+value = (prompt + generated tokens) / second, the reference's single-model TPS definition
+(Code/Quantised Models/models_quant_updated.py:95-96 counts len(output[0]) = prompt + new).
+
+    python bench.py --gpus 1 --steps K --warmup W            # our arm
+    python bench.py --impl reference ...                     # the reference's CPU int8 path
+    torchrun --nproc-per-node N bench.py --gpus N ...        # one rank per GPU, NCCL send/recv
+
+Prints ONE JSON line on rank 0 (see DESIGN.md "Measurement" for every key).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "tokens/sec prefill+decode, Llama-2-7B W8A8"
+UNIT = "tokens/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--model", default="llama-2-7b")
+    ap.add_argument("--prompt", type=int, default=2048)
+    ap.add_argument("--new", type=int, default=128)
+    ap.add_argument("--chunk", type=int, default=512)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return dict(hbm=float(d["hbm_gbs"]), bf16=float(d["bf16_tflops"]), bf16_sus=float(d.get("bf16_tflops_sustained", d["bf16_tflops"])),
+                    which="measured")
+    return dict(hbm=6650.0, bf16=1590.0, bf16_sus=1400.0, which="fallback")
+
+
+# ----------------------------------------------------------------------------------------------
+# clocks sampler (nvidia-smi in the background; zero interference with the launching thread)
+# ----------------------------------------------------------------------------------------------
+class Clocks:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+                                       "-i", str(gpu_index)], stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self) -> dict:
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        for line in self.f.read().splitlines():
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1])); mx.append(float(c[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), c[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        os.unlink(self.f.name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------------------------
+# reference arm / cpu baseline: the reference's own CPU int8 path (Code/C-DAC Server/try.py:198-206,
+# :238-260): HF AutoModelForCausalLM -> quantize_dynamic({nn.Linear}, qint8) -> generate.
+# ----------------------------------------------------------------------------------------------
+def cpu_reference_run(model: str, prompt: int, new: int, steps: int, warmup: int):
+    """Times HF Llama (random init from the model's config; no checkpoints offline) +
+    torch.quantization.quantize_dynamic on the host cores at 2 and 4 of the model's layers and
+    extrapolates linearly in the layer count to the full depth (bounded sample)."""
+    import warnings
+    import torch
+    warnings.filterwarnings("ignore")
+    from transformers import LlamaConfig, LlamaForCausalLM
+    import importlib
+    cfg = importlib.import_module("llm-for-distributed-egde-devices_b200").get_config(model)
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    s_prompt, s_new = min(prompt, 256), min(new, 8)
+    times = {}
+    for L in (2, 4):
+        hc = LlamaConfig(vocab_size=cfg.vocab, hidden_size=cfg.d_model, intermediate_size=cfg.ffn, num_hidden_layers=L,
+                         num_attention_heads=cfg.n_heads, num_key_value_heads=cfg.n_kv_heads,
+                         max_position_embeddings=4096, rms_norm_eps=cfg.eps, tie_word_embeddings=False)
+        torch.manual_seed(0)
+        m = LlamaForCausalLM(hc).eval()
+        m = torch.quantization.quantize_dynamic(m, {torch.nn.Linear}, dtype=torch.qint8)     # try.py:205
+        ids = torch.randint(0, cfg.vocab, (1, s_prompt), generator=torch.Generator().manual_seed(1234))
+        ts = []
+        with torch.no_grad():
+            for i in range(warmup + steps):
+                t0 = time.perf_counter()
+                m.generate(input_ids=ids, attention_mask=torch.ones_like(ids), max_new_tokens=s_new, min_new_tokens=s_new,
+                           do_sample=False, pad_token_id=0)
+                if i >= warmup:
+                    ts.append(time.perf_counter() - t0)
+        times[L] = statistics.median(ts)
+        del m
+    per_layer = (times[4] - times[2]) / 2.0
+    fixed = max(times[2] - 2 * per_layer, 0.0)
+    t_full = fixed + per_layer * cfg.n_layers
+    toks = s_prompt + s_new
+    return dict(value=toks / t_full, unit=UNIT, cores=threads, kind="reference",
+                sample=(f"HF LlamaForCausalLM random-init + quantize_dynamic(qint8) [try.py:204-205], prompt {s_prompt} + "
+                        f"{s_new} greedy tokens, timed at 2 and 4 of {cfg.n_layers} layers ({times[2]:.2f}s, {times[4]:.2f}s), "
+                        f"extrapolated linearly to {cfg.n_layers} layers ({t_full:.2f}s)"),
+                ms_per_step=t_full * 1e3)
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    r = cpu_reference_run(a.model, a.prompt, a.new, max(1, a.steps), max(1, min(a.warmup, 1)))
+    line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "int8", "data": "synthetic",
+            "config": {"workload": f"{a.model} W8A8, B=1, prompt {a.prompt} + {a.new} greedy tokens (CPU sample, see cpu_baseline.sample)"},
+            "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------------------------
+# our arm
+# ----------------------------------------------------------------------------------------------
+def run_ours(a):
+    import numpy as np
+    import torch
+    import importlib
+    b2 = importlib.import_module("llm-for-distributed-egde-devices_b200")
+    from b200stage import ops
+    from b200stage.pipeline import DistPipeline, split_layers
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != a.gpus:
+        if world == 1 and a.gpus > 1:
+            raise SystemExit("launch with torch.distributed.run --nproc-per-node N for --gpus N")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    cfg = b2.get_config(a.model)
+    P, NEW, CH = a.prompt, a.new, a.chunk
+    max_seq = P + NEW
+    n_prompts = world                       # weak scaling: one prompt stream per stage
+    pipe = DistPipeline.load(cfg, rank, world, dev, seed=0, fast_init=True, max_rows=n_prompts, max_seq=max_seq)
+    stage = pipe.stage
+    g = torch.Generator(device="cpu").manual_seed(1234)
+    prompts_host = [torch.randint(0, cfg.vocab, (P,), generator=g, dtype=torch.int64).pin_memory() for _ in range(n_prompts)]
+    prompts_dev = [p.to(dev) for p in prompts_host]
+
+    def one_step(prompts, record=None):
+        """prefill all prompts (pipelined chunks), then NEW-1 decode rounds (first token comes
+        from the prefill logits).  Returns generated tokens [n_prompts, NEW] on rank 0 / last."""
+        ev = lambda: torch.cuda.Event(enable_timing=True)
+        e0, e1, e2 = ev(), ev(), ev()
+        e0.record()
+        lgs = pipe.prefill_stream(prompts if pipe.first else [None] * n_prompts, CH)
+        toks = []
+        for p in range(n_prompts):
+            t = None
+            if pipe.last:
+                t = torch.empty((1,), dtype=torch.int64, device=dev)
+                ops.argmax(lgs[p].view(1, -1), out=t)
+                stage.launches += 1
+            if pipe.first and not pipe.last:
+                t = torch.empty((1,), dtype=torch.int64, device=dev)
+            toks.append(pipe.return_tokens(t))
+        e1.record()
+        gen = [[t] for t in toks]
+        for i in range(1, NEW):
+            pos = [[P + i - 1] for _ in range(n_prompts)]
+            rows = [[p] for p in range(n_prompts)]
+            toks = pipe.decode_round(toks, pos, rows)
+            for p in range(n_prompts):
+                gen[p].append(toks[p])
+        e2.record()
+        if record is not None:
+            record.append((e0, e1, e2))
+        if pipe.first or pipe.last:
+            return torch.stack([torch.cat(x) for x in gen])
+        return None
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # prompt lengths are part of the workload description, known to every rank
+    pipe._bcast_len = lambda T: P
+    for _ in range(max(a.warmup, 3)):
+        one_step(prompts_dev)
+    barrier()
+    clocks = Clocks(local) if rank == 0 else None
+    l0 = stage.launches
+    rec = []
+    t_start, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t_start.record()
+    for _ in range(a.steps):
+        one_step(prompts_dev, rec)
+    t_end.record()
+    barrier()
+    ms_total = t_start.elapsed_time(t_end)
+    launches = stage.launches - l0
+    pre_ms = sum(e0.elapsed_time(e1) for e0, e1, _ in rec) / len(rec)
+    dec_ms = sum(e1.elapsed_time(e2) for _, e1, e2 in rec) / len(rec)
+    clk = clocks.stop() if clocks else None
+    # ---- e2e: host prompt (pinned) -> H2D -> generate -> D2H of the tokens, every step ---------
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        dp = [p.to(dev, non_blocking=True) for p in prompts_host] if pipe.first else prompts_dev
+        out = one_step(dp)
+        if pipe.first:
+            host_out = out.cpu()          # D2H read of the step's result
+        barrier()
+    e2e_s = (time.perf_counter() - t0) / a.steps
+    # max over ranks
+    vals = torch.tensor([ms_total, pre_ms, dec_ms, e2e_s, float(launches)], dtype=torch.float64, device=dev)
+    if dist is not None:
+        mx = vals.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = vals.clone()
+        dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        ms_total, pre_ms, dec_ms, e2e_s = (float(x) for x in mx[:4])
+        launches = int(sm[4])
+    ms_step = ms_total / a.steps
+    tokens_step = n_prompts * (P + NEW)
+    value = tokens_step / (ms_step / 1e3)
+
+    # ---- roofline of the dominant kernel (decode weight stream, gemv_i8_kernel<1>) -------------
+    pk = peaks()
+    roof, roof_pre = None, None
+    if rank == 0:
+        roof, roof_pre = roofline_pass(torch, ops, stage, cfg, pk, dev, CH)
+    line = None
+    if rank == 0:
+        n_layers_local = stage.layer_end - stage.layer_begin
+        dec_bytes = cfg.linear_params_per_layer() * cfg.n_layers + cfg.vocab * cfg.d_model * 2 \
+            + 2 * cfg.n_layers * cfg.n_kv_heads * cfg.head_dim * 2 * (P + NEW // 2)
+        dec_tok_s = n_prompts * (NEW - 1) / (dec_ms / 1e3)
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8",
+            "data": "synthetic",
+            "config": {"workload": f"{cfg.name} W8A8 (random-init, seeded), {n_prompts} prompt(s) x ({P} prefill in chunks of {CH} + "
+                                   f"{NEW} greedy decode), B=1 per prompt, {world} pipeline stage(s) x {n_layers_local} layers",
+                       "parallelism": f"pp{world}", "l2": "inputs larger than L2 (int8 weights 6.5 GB streamed per decode token)"},
+            "prefill_tokens_per_s": n_prompts * P / (pre_ms / 1e3), "decode_tokens_per_s": dec_tok_s,
+            "decode_hbm_frac_whole_step": (dec_bytes / 1e9) * dec_tok_s / (pk["hbm"] * world),
+            "gpu_launches": launches,
+            "e2e": {"value": tokens_step / e2e_s, "unit": UNIT, "h2d_bytes_per_step": n_prompts * P * 8,
+                    "d2h_bytes_per_step": n_prompts * NEW * 8},
+            "roofline": roof, "roofline_prefill": roof_pre, "clocks": clk, "peaks": pk["which"],
+        }
+        if not a.no_cpu_baseline and world == 1:
+            try:
+                r = cpu_reference_run(a.model, P, NEW, 1, 1)
+                line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
+            except Exception as e:   # the baseline must not take the GPU number down with it
+                line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "reference",
+                                        "sample": f"failed: {type(e).__name__}: {e}"}
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def roofline_pass(torch, ops, stage, cfg, pk, dev, chunk):
+    """CUDA-event timing of the dominant kernels on this stage's real weights, cycling through
+    the layers so every launch streams cold weights (6.5 GB >> 126 MB L2)."""
+    layers = stage.w["layers"]
+    d = cfg.d_model
+
+    def timed(fn, reps):
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        fn()
+        torch.cuda.synchronize()
+        s.record()
+        for _ in range(reps):
+            fn()
+        e.record()
+        torch.cuda.synchronize()
+        return s.elapsed_time(e) / reps
+
+    # decode: M = 1 weight stream over the biggest linear (gate_up), all layers back to back
+    x8 = torch.randint(-127, 128, (1, d), dtype=torch.int8, device=dev)
+    xs = torch.full((1,), 0.01, device=dev)
+    out = torch.empty((1, cfg.up_out), dtype=torch.float16, device=dev)
+
+    def dec():
+        for lw in layers:
+            ops.gemm_w8a8(x8, lw["wgu"], xs, lw["s_gu"], out=out)
+    ms = timed(dec, 5) / len(layers)
+    bytes_launch = cfg.up_out * d + d + cfg.up_out * 6
+    achieved = bytes_launch / (ms * 1e-3) / 1e9
+    roof = {"bound": "hbm", "kernel": "gemv_i8_kernel<1> (gate_up, M=1)", "achieved": achieved, "peak": pk["hbm"], "unit": "GB/s",
+            "frac": achieved / pk["hbm"], "traffic": None, "algorithmic_bytes_per_launch": bytes_launch,
+            "avg_launch_us": ms * 1e3, "peak_source": pk["which"]}
+    # prefill: M = chunk tokens through the same linear on the tensor cores
+    M = chunk
+    a8 = torch.randint(-127, 128, (M, d), dtype=torch.int8, device=dev)
+    as_ = torch.full((M,), 0.01, device=dev)
+    outp = torch.empty((M, cfg.up_out), dtype=torch.float16, device=dev)
+
+    def pre():
+        for lw in layers:
+            ops.gemm_w8a8(a8, lw["wgu"], as_, lw["s_gu"], out=outp)
+    msp = timed(pre, 3) / len(layers)
+    ops_launch = 2.0 * M * cfg.up_out * d
+    ach = ops_launch / (msp * 1e-3) / 1e12
+    peak_i8 = 2.0 * pk["bf16"]
+    roof_pre = {"bound": "tensor", "kernel": f"gemm_tc_kernel<int8> (gate_up, M={M})", "achieved": ach, "peak": peak_i8,
+                "unit": "TOP/s", "frac": ach / peak_i8, "avg_launch_us": msp * 1e3,
+                "peak_source": f"2 x {pk['which']} bf16 burst (no int8 peak in MEASURED_PEAKS.json; nominal int8 dense 4500)"}
+    return roof, roof_pre
+
+
+def main():
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)
+
+
+if __name__ == "__main__":
+    main()

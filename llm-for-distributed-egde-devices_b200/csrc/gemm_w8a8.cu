@@ -406,8 +406,8 @@ static int launch_gemv(const int8_t* A, const int8_t* W, const GemmParams& p, cu
 // =============================================================================================
 int gemm_w8a8(const int8_t* A, const int8_t* W, const float* a_scale, const float* w_scale, const void* bias,
               const void* residual, void* out, int32_t* acc_dump, int M, int N, int K, int schedule, cudaStream_t st) {
-  if (!A || !W || !a_scale || !w_scale || !out) return ERR_NULL_PTR;
   if (M == 0 || N == 0) return OK;
+  if (!A || !W || !a_scale || !w_scale || !out) return ERR_NULL_PTR;
   if (M < 0 || N < 0 || K <= 0 || (K & 15) || (N & 7)) return ERR_BAD_SHAPE;
   auto mis = [](const void* q) { return q && (reinterpret_cast<uintptr_t>(q) & 15); };
   if (mis(A) || mis(W) || mis(w_scale) || mis(bias) || mis(residual) || mis(out) || mis(acc_dump)) return ERR_BAD_ALIGN;
@@ -507,8 +507,8 @@ static int launch_gemv_f16(const __half* X, const __half* W, float* out, int M, 
 }
 
 int lm_head(const void* x, const void* W, float* logits, int M, int V, int d, cudaStream_t st) {
-  if (!x || !W || !logits) return ERR_NULL_PTR;
   if (M == 0 || V == 0) return OK;
+  if (!x || !W || !logits) return ERR_NULL_PTR;
   if (M < 0 || V < 0 || d <= 0 || (d & 7) || (V & 3)) return ERR_BAD_SHAPE;
   auto mis = [](const void* q) { return q && (reinterpret_cast<uintptr_t>(q) & 15); };
   if (mis(x) || mis(W) || mis(logits)) return ERR_BAD_ALIGN;

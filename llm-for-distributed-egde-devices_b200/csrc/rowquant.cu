@@ -203,6 +203,7 @@ static inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) 
 
 int norm_quant(const void* x, const void* gamma, const void* beta, const float* smooth, int8_t* q,
                float* row_scale, int T, int d, float eps, cudaStream_t st) {
+  if (T == 0) return OK;
   if (!x || !gamma || !q || !row_scale) return ERR_NULL_PTR;
   if (!al16(x) || !al16(gamma) || !al16(q) || (beta && !al16(beta)) || (smooth && !al16(smooth))) return ERR_BAD_ALIGN;
   if (beta)
@@ -213,6 +214,7 @@ int norm_quant(const void* x, const void* gamma, const void* beta, const float* 
 }
 
 int norm_f16(const void* x, const void* gamma, const void* beta, void* y, int T, int d, float eps, cudaStream_t st) {
+  if (T == 0) return OK;
   if (!x || !gamma || !y) return ERR_NULL_PTR;
   if (!al16(x) || !al16(gamma) || !al16(y) || (beta && !al16(beta))) return ERR_BAD_ALIGN;
   if (beta)
@@ -223,6 +225,7 @@ int norm_f16(const void* x, const void* gamma, const void* beta, void* y, int T,
 }
 
 int smooth_quant(const void* x, const float* smooth, int8_t* q, float* row_scale, int T, int K, cudaStream_t st) {
+  if (T == 0) return OK;
   if (!x || !q || !row_scale) return ERR_NULL_PTR;
   if (!al16(x) || !al16(q) || (smooth && !al16(smooth))) return ERR_BAD_ALIGN;
   return launch_rowquant<ROW_PLAIN, false>((const __half*)x, K, nullptr, nullptr, smooth, q, row_scale, nullptr, T, K,
@@ -232,6 +235,7 @@ int smooth_quant(const void* x, const float* smooth, int8_t* q, float* row_scale
 // act: 0 = silu(gate)*up, 1 = gelu_new(gate)*up, 2 = gelu_new(x) (ungated), 3 = silu(x) (ungated)
 int act_mul_quant(const void* gate_up, const float* smooth, int8_t* q, float* row_scale, int T, int F, int act,
                   cudaStream_t st) {
+  if (T == 0) return OK;
   if (!gate_up || !q || !row_scale) return ERR_NULL_PTR;
   if (!al16(gate_up) || !al16(q) || (smooth && !al16(smooth))) return ERR_BAD_ALIGN;
   const __half* x = (const __half*)gate_up;

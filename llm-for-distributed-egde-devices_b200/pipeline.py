@@ -1,0 +1,237 @@
+"""Pipeline: stages chained over contiguous layer ranges, with greedy ``generate``.
+
+Mirrors the subset of HF ``model.generate`` / ``model(**inputs).logits`` that the reference's
+scripts call (Code/Quantised Models/models_quant_updated.py:84-93 and :66-67) on top of Stage.
+Two forms:
+
+* ``Pipeline(stages)``      -- all stages live in this process (one GPU, or several GPUs driven
+  from one process; hidden states hop with a device-to-device copy).
+* ``DistPipeline(stage)``   -- one process per GPU (torchrun); the hidden-state hand-off that the
+  reference sketches as a gRPC hop between Jetsons (Code/gRPC/server.py:13-19, client.py:7-11;
+  "Deploy models across Jetson ..." in Presentations/review 1.pptx) is an NCCL send/recv over
+  NVLink.  The KV cache is stage-local and never moves.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import ops
+from .config import ModelConfig, get_config
+from .stage import Stage, KVCache
+
+
+def split_layers(n_layers: int, n_stages: int):
+    """Contiguous, near-equal layer ranges: stage i owns [b_i, e_i)."""
+    base, rem = divmod(n_layers, n_stages)
+    out, b = [], 0
+    for i in range(n_stages):
+        e = b + base + (1 if i < rem else 0)
+        out.append((b, e))
+        b = e
+    return out
+
+
+class Pipeline:
+    def __init__(self, stages):
+        if not stages or not stages[0].first or not stages[-1].last:
+            raise ValueError("need stages[0].first and stages[-1].last")
+        self.stages = list(stages)
+        self.cfg: ModelConfig = stages[0].cfg
+
+    @classmethod
+    def load(cls, model, n_stages: int = 1, devices=None, seed: int = 0, fast_init: bool = False) -> "Pipeline":
+        cfg = get_config(model)
+        devices = devices or ["cuda:0"] * n_stages
+        rngs = split_layers(cfg.n_layers, n_stages)
+        return cls([Stage.load(cfg, b, e, first=(i == 0), last=(i == n_stages - 1), device=devices[i], seed=seed,
+                               fast_init=fast_init) for i, (b, e) in enumerate(rngs)])
+
+    def new_caches(self, rows: int, max_seq: int):
+        return [s.new_kv_cache(rows, max_seq) for s in self.stages]
+
+    @property
+    def launches(self) -> int:
+        return sum(s.launches for s in self.stages)
+
+    # ------------------------------------------------------------------------------------------
+    def _run(self, x, caches, positions, seq_ids, logits):
+        for s, c in zip(self.stages, caches):
+            if x.device != s.device:
+                x = x.to(s.device, non_blocking=True)
+            x = s.forward(x, c, positions, seq_ids, logits=logits if s.last else "none")
+        return x
+
+    def prefill(self, ids, caches, row: int = 0, pos0: int = 0, chunk: int = 512, logits: str = "last"):
+        """Chunked prefill of one prompt into cache row `row`; returns the logits of the final
+        position ("last") or of every position ("all")."""
+        T = int(ids.shape[0])
+        outs = []
+        last = None
+        for c0 in range(0, T, chunk):
+            c1 = min(T, c0 + chunk)
+            pos = np.arange(pos0 + c0, pos0 + c1)
+            final = c1 == T
+            want = "all" if logits == "all" else ("last" if final else "none")
+            y = self._run(ids[c0:c1], caches, pos, np.full(c1 - c0, row), want)
+            if logits == "all":
+                outs.append(y)
+            elif final:
+                last = y
+        return torch.cat(outs, 0) if logits == "all" else last
+
+    def decode_step(self, tokens, caches, positions, rows=None):
+        """One token per sequence -> logits [B,V]."""
+        B = int(tokens.shape[0])
+        rows = np.arange(B) if rows is None else np.asarray(rows)
+        return self._run(tokens, caches, np.asarray(positions), rows if B > 1 else np.asarray(rows[:1]), "last")
+
+    @torch.no_grad()
+    def generate(self, input_ids, max_new_tokens: int = 32, do_sample: bool = False, chunk: int = 512,
+                 max_seq: int | None = None, caches=None, **sample_kwargs):
+        """Greedy continuation of one prompt; returns prompt + new tokens (int64, on the device),
+        like ``model.generate(**inputs, max_new_tokens=...)[0]`` (models_quant_updated.py:84-95)."""
+        if do_sample:
+            raise NotImplementedError("sampling (temperature/top-k/top-p) is the next scope row; greedy only")
+        dev = self.stages[0].device
+        ids = torch.as_tensor(input_ids, dtype=torch.int64).view(-1).to(dev)
+        T = int(ids.shape[0])
+        max_seq = max_seq or min(self.cfg.max_pos, T + max_new_tokens)
+        if T + max_new_tokens > max_seq:
+            raise ValueError("prompt + max_new_tokens exceeds max_seq")
+        caches = caches or self.new_caches(1, max_seq)
+        out = torch.empty((T + max_new_tokens,), dtype=torch.int64, device=dev)
+        out[:T] = ids
+        lg = self.prefill(ids, caches, 0, 0, chunk)
+        for i in range(max_new_tokens):
+            tok = out[T + i: T + i + 1]
+            ops.argmax(lg.view(1, -1).to(dev) if lg.device != dev else lg.view(1, -1), out=tok)
+            self.stages[-1].launches += 1
+            if i + 1 < max_new_tokens:
+                lg = self.decode_step(tok, caches, [T + i])
+        return out
+
+    @torch.no_grad()
+    def logits(self, input_ids, chunk: int = 512):
+        """All-position logits of one prompt: the ``model(**inputs).logits`` form that the
+        reference's confidence_score consumes (models_quant_updated.py:63-70)."""
+        dev = self.stages[0].device
+        ids = torch.as_tensor(input_ids, dtype=torch.int64).view(-1).to(dev)
+        caches = self.new_caches(1, int(ids.shape[0]))
+        return self.prefill(ids, caches, 0, 0, chunk, logits="all")
+
+
+def confidence_score(pipe: Pipeline, input_ids) -> float:
+    """mean over positions of max softmax probability (models_quant_updated.py:63-70)."""
+    lg = pipe.logits(input_ids)
+    return float(torch.softmax(lg.float(), dim=-1).max(dim=-1).values.mean().item())
+
+
+# ==============================================================================================
+# one process per GPU
+# ==============================================================================================
+class DistPipeline:
+    """Rank r owns stage r of `world` stages.  Hidden tiles [T,d] fp16 move r -> r+1 with
+    torch.distributed send/recv (NCCL on GPUs; gloo in the CPU schedule tests); the greedy token
+    moves from the last rank back to rank 0.  All ranks make the same sequence of calls.
+
+    `forward_fn(x, positions, seq_ids, logits)` abstracts the local stage so the scheduling and
+    messaging logic can be exercised on CPU with a stand-in stage (tests/test_pipeline_cpu.py).
+    """
+
+    def __init__(self, rank: int, world: int, d_model: int, device, forward_fn, vocab: int, group=None):
+        import torch.distributed as dist
+        self.dist, self.rank, self.world, self.d, self.device = dist, rank, world, d_model, device
+        self.fwd, self.vocab, self.group = forward_fn, vocab, group
+        self.first, self.last = rank == 0, rank == world - 1
+
+    @classmethod
+    def load(cls, model, rank: int, world: int, device, seed: int = 0, fast_init: bool = True, max_rows: int = 1,
+             max_seq: int = 4096):
+        cfg = get_config(model)
+        b, e = split_layers(cfg.n_layers, world)[rank]
+        stage = Stage.load(cfg, b, e, first=(rank == 0), last=(rank == world - 1), device=device, seed=seed,
+                           fast_init=fast_init)
+        cache = stage.new_kv_cache(max_rows, max_seq)
+        self = cls(rank, world, cfg.d_model, torch.device(device),
+                   lambda x, pos, seq, lg: stage.forward(x, cache, pos, seq, logits=lg), cfg.vocab)
+        self.stage, self.cache, self.cfg = stage, cache, cfg
+        return self
+
+    # -- one hop --------------------------------------------------------------------------------
+    def step(self, x, positions, seq_ids, want_logits: str):
+        """x: ids on rank 0 (ignored elsewhere).  Returns logits on the last rank, else None."""
+        T = len(positions)
+        if not self.first:
+            x = torch.empty((T, self.d), dtype=torch.float16, device=self.device)
+            self.dist.recv(x, src=self.rank - 1, group=self.group)
+        y = self.fwd(x, positions, seq_ids, want_logits if self.last else "none")
+        if not self.last:
+            self.dist.send(y, dst=self.rank + 1, group=self.group)
+            return None
+        return y
+
+    def return_tokens(self, tok):
+        """Greedy ids [B] int64: last rank -> rank 0.  Returns them on rank 0, None elsewhere
+        (the last rank keeps its own copy)."""
+        if self.world == 1:
+            return tok
+        if self.last:
+            self.dist.send(tok, dst=0, group=self.group)
+            return tok if self.first else None
+        if self.first:
+            t = torch.empty_like(tok) if tok is not None else None
+            self.dist.recv(t, src=self.world - 1, group=self.group)
+            return t
+        return None
+
+    # -- schedules --------------------------------------------------------------------------------
+    def prefill_stream(self, prompts, chunk: int, pos0: int = 0):
+        """Pipelined chunked prefill of several prompts (cache row i for prompt i).  Chunk c of
+        prompt p enters stage s as soon as stage s has finished the previous chunk; because send
+        and recv are stream-ordered, issuing the chunks in order on every rank IS the pipeline
+        schedule (chunk c on stage s at tick c+s).  Returns, on the last rank, the final-position
+        logits per prompt."""
+        outs = []
+        for p, ids in enumerate(prompts):
+            T = int(ids.shape[0]) if ids is not None else None
+            T = self._bcast_len(T)
+            for c0 in range(0, T, chunk):
+                c1 = min(T, c0 + chunk)
+                pos = np.arange(pos0 + c0, pos0 + c1)
+                y = self.step(ids[c0:c1] if self.first else None, pos, np.full(c1 - c0, p),
+                              "last" if c1 == T else "none")
+                if self.last and c1 == T:
+                    outs.append(y)
+        return outs
+
+    def _bcast_len(self, T):
+        # prompt lengths are part of the (synthetic) workload description known to every rank
+        return int(T)
+
+    def decode_round(self, tokens_per_group, positions_per_group, rows_per_group):
+        """One decode step for each of G independent micro-batches, pipelined: group g enters
+        stage 0 right after group g-1, so with G >= world all stages stay busy.  Returns the list
+        of greedy tokens per group on rank 0 and on the last rank."""
+        toks = []
+        for g, (tok, pos, rows) in enumerate(zip(tokens_per_group, positions_per_group, rows_per_group)):
+            lg = self.step(tok if self.first else None, pos, rows, "last")
+            t = None
+            if self.last:
+                t = torch.empty((len(pos),), dtype=torch.int64, device=self.device)
+                self._argmax(lg, t)
+            toks.append(t)
+        # tokens travel back after all groups are in flight (does not stall the forward wave)
+        back = []
+        for g, t in enumerate(toks):
+            if self.first and not self.last:
+                t = torch.empty((len(positions_per_group[g]),), dtype=torch.int64, device=self.device)
+            back.append(self.return_tokens(t))
+        return back
+
+    def _argmax(self, lg, out):
+        if lg.is_cuda:
+            ops.argmax(lg, out=out)
+            self.stage.launches += 1
+        else:   # CPU stand-in used only by the gloo schedule tests
+            out.copy_(lg.argmax(-1))

@@ -1,0 +1,120 @@
+"""Stage / Pipeline parity against the Tier-S oracle on small seeded models (three levels,
+SURVEY.md §8c): L1 int8 activations + GEMM outputs bit-exact wherever the inputs are identical
+(layer 0 up to attention); L2 fp16 hidden states per layer within max-abs <= 2^-7 * max|ref| and
+cosine >= 0.9999; L3 greedy tokens identical for 32 steps (oracle top-1 margin reported)."""
+import numpy as np
+import pytest
+import torch
+
+import b200stage
+from b200stage import weights
+from b200stage.pipeline import Pipeline, split_layers, confidence_score
+from b200stage.stage import Stage
+from oracle import w8a8 as O
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _oracle_stages(cfg, n_stages, seed):
+    out = []
+    for i, (b, e) in enumerate(split_layers(cfg.n_layers, n_stages)):
+        sw = weights.build_stage_weights(cfg, b, e, i == 0, i == n_stages - 1, seed, "cpu")
+        out.append(weights.to_numpy(sw))
+    return out
+
+
+def _close(got, ref, name):
+    got = got.astype(np.float64).ravel()
+    ref = ref.astype(np.float64).ravel()
+    err = np.abs(got - ref).max()
+    cos = float(got @ ref / (np.linalg.norm(got) * np.linalg.norm(ref) + 1e-30))
+    assert err <= 2.0 ** -7 * np.abs(ref).max() + 1e-6, (name, err, np.abs(ref).max())
+    assert cos >= 0.9999, (name, cos)
+
+
+@pytest.mark.parametrize("model", ["tiny-llama-test", "tiny-gqa-test", "tiny-window-test", "tiny-hd128-test"])
+def test_stage_prefill_then_decode_matches_oracle(model):
+    cfg = b200stage.get_config(model)
+    seed, T, S = 3, 70, 96
+    stage = Stage.load(cfg, 0, cfg.n_layers, first=True, last=True, device=DEV, seed=seed)
+    osw = _oracle_stages(cfg, 1, seed)[0]
+    ids = np.random.default_rng(5).integers(0, cfg.vocab, T)
+    cos, sin = O.rope_table(cfg.head_dim, cfg.max_pos, cfg.rope_theta)
+    ocache = O.KVCacheOracle(cfg.n_layers, 1, cfg.n_kv_heads, S, cfg.head_dim)
+    otrace = []
+    ref = O.stage_forward(ids, osw, cfg.kernel_cfg(), ocache, np.zeros(T, np.int64), np.arange(T), cos, sin, otrace)
+    cache = stage.new_kv_cache(1, S)
+    trace = []
+    got = stage.forward(torch.from_numpy(ids).to(DEV), cache, np.arange(T), logits="all", trace=trace)
+    # L1: layer 0, before attention, inputs identical -> bit-exact
+    assert np.array_equal(trace[0]["q1"].cpu().numpy(), otrace[0]["q1"])
+    assert np.array_equal(trace[0]["s1"].cpu().numpy(), otrace[0]["s1"])
+    assert np.array_equal(trace[0]["qkv"].cpu().numpy().view(np.uint16), otrace[0]["qkv"].view(np.uint16))
+    # L2: per layer
+    for li in range(cfg.n_layers):
+        for k in ("attn", "h1", "gu", "h2"):
+            _close(trace[li][k].cpu().numpy(), otrace[li][k].reshape(trace[li][k].shape), f"L{li}.{k}")
+    _close(got.cpu().numpy(), ref, "logits")
+    # KV cache contents
+    _close(cache.k[:, 0, :, :T].cpu().numpy(), ocache.k[:, 0, :, :T], "kcache")
+    # one decode step on top
+    nxt = np.array([int(ref[-1].argmax())])
+    ref2 = O.stage_forward(nxt, osw, cfg.kernel_cfg(), ocache, np.zeros(1, np.int64), np.array([T]), cos, sin)
+    got2 = stage.forward(torch.from_numpy(nxt).to(DEV), cache, [T])
+    _close(got2.cpu().numpy(), ref2, "decode logits")
+    assert int(got2.argmax()) == int(ref2.argmax())
+
+
+def test_chunked_prefill_equals_one_shot():
+    cfg = b200stage.get_config("tiny-gqa-test")
+    pipe = Pipeline.load(cfg, 1, seed=1)
+    ids = torch.from_numpy(np.random.default_rng(0).integers(0, cfg.vocab, 150)).to(DEV)
+    a = pipe.prefill(ids, pipe.new_caches(1, 160), chunk=512)
+    b = pipe.prefill(ids, pipe.new_caches(1, 160), chunk=64)
+    _close(b.cpu().numpy(), a.cpu().numpy(), "chunked")
+    assert int(a.argmax()) == int(b.argmax())
+
+
+@pytest.mark.parametrize("model,n_stages", [("tiny-llama-test", 1), ("tiny-gqa-test", 2), ("tiny-window-test", 2)])
+def test_greedy_tokens_identical(model, n_stages):
+    cfg = b200stage.get_config(model)
+    seed, T, NEW = 7, 40, 32
+    pipe = Pipeline.load(cfg, n_stages, seed=seed)
+    ids = np.random.default_rng(9).integers(0, cfg.vocab, T)
+    got = pipe.generate(ids, max_new_tokens=NEW, chunk=16).cpu().numpy()
+    ref, margins = O.greedy_generate(_oracle_stages(cfg, n_stages, seed), cfg.kernel_cfg(), ids, NEW, T + NEW)
+    print(f"{model}: min oracle top-1 margin {min(margins):.4f}")
+    assert np.array_equal(got, ref), (got[T:], ref[T:], min(margins))
+
+
+def test_batched_decode_matches_single():
+    cfg = b200stage.get_config("tiny-gqa-test")
+    pipe = Pipeline.load(cfg, 1, seed=2)
+    r = np.random.default_rng(1)
+    B, S = 3, 64
+    caches = pipe.new_caches(B, S)
+    lens = [20, 33, 7]
+    prompts = [torch.from_numpy(r.integers(0, cfg.vocab, L)).to(DEV) for L in lens]
+    singles = []
+    for b in range(B):
+        singles.append(pipe.prefill(prompts[b], caches, row=b))
+    toks = torch.stack([s.argmax(-1)[0] for s in singles])
+    lg = pipe.decode_step(toks, caches, lens, rows=np.arange(B))
+    for b in range(B):
+        c1 = pipe.new_caches(1, S)
+        pipe.prefill(prompts[b], c1)
+        one = pipe.decode_step(toks[b:b + 1], c1, [lens[b]])
+        _close(lg[b].cpu().numpy(), one[0].cpu().numpy(), f"row{b}")
+
+
+def test_confidence_score_runs():
+    cfg = b200stage.get_config("tiny-llama-test")
+    pipe = Pipeline.load(cfg, 1, seed=0)
+    c = confidence_score(pipe, np.arange(30) % cfg.vocab)
+    assert 0.0 < c <= 1.0
+
+
+def test_stage_refuses_cpu():
+    with pytest.raises(RuntimeError):
+        Stage.load("tiny-llama-test", 0, 1, first=True, last=False, device="cpu")
