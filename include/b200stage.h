@@ -37,6 +37,11 @@ extern "C" {
 int b2_version(void);
 /* Static string for an error code. */
 const char* b2_strerror(int code);
+/* One-time set-up on the current device: opts every kernel in to its dynamic shared-memory size
+ * and resolves cuTensorMapEncodeTiled.  Launch paths also do this lazily, but calling b2_init()
+ * first guarantees no launch has first-call side effects -- required before CUDA-graph capture.
+ * No counterpart in the reference (library housekeeping). */
+int b2_init(void);
 
 /* Fused (RMSNorm | LayerNorm) -> smoothing multiply -> per-token absmax int8 quantise.
  * x [T,d] fp16; gamma [d] fp16; beta [d] fp16 or NULL (NULL selects RMSNorm); smooth [d] fp32 or
@@ -107,12 +112,14 @@ size_t b2_decode_attn_workspace_bytes(int B, int H, int KV, int hd, int max_seql
 
 /* Causal (optionally sliding-window) attention for one contiguous chunk of T query tokens of one
  * sequence at positions [pos0, pos0+T), keys 0..pos0+T-1 read from cache row `row` (the chunk's
- * own k/v must already be appended).
+ * own k/v must already be appended).  positions: device int32 [T] or NULL; when given, pos0 is
+ * read from positions[0] on the device (lets a captured CUDA graph serve every chunk) and the host
+ * `pos0` argument is ignored.
  * Replaces: eager_attention_forward at q_len > 1 (modeling_llama.py:199-222): the prefill forward
  * of `generate` and the `model(**inputs).logits` pass of confidence_score
  * (models_quant_updated.py:63-70). */
 int b2_prefill_attn(const void* q, long long q_ld, const void* kcache, const void* vcache, void* out, long long o_ld,
-                    int T, int pos0, int row, int H, int KV, int hd, int Smax, float scale, int window, void* stream);
+                    const int* positions, int T, int pos0, int row, int H, int KV, int hd, int Smax, float scale, int window, void* stream);
 
 /* Token (+ learned position) embedding gather.  ids [T] int64; positions [T] int32 (only read
  * when pos_table != NULL); tables fp16 [vocab,d] / [max_pos,d]; out [T,d] fp16.

@@ -22,6 +22,7 @@ _vp, _i, _f, _ll, _sz = C.c_void_p, C.c_int, C.c_float, C.c_longlong, C.c_size_t
 SIGNATURES = {
     "b2_version": (_i, []),
     "b2_strerror": (C.c_char_p, [_i]),
+    "b2_init": (_i, []),
     "b2_norm_quant": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _f, _vp]),
     "b2_norm": (_i, [_vp, _vp, _vp, _vp, _i, _i, _f, _vp]),
     "b2_smooth_quant": (_i, [_vp, _vp, _vp, _vp, _i, _i, _vp]),
@@ -31,7 +32,7 @@ SIGNATURES = {
     "b2_rope_kv_append": (_i, [_vp, _ll, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "b2_decode_attn": (_i, [_vp, _ll, _vp, _vp, _vp, _vp, _vp, _ll, _vp, _sz, _i, _i, _i, _i, _i, _i, _f, _i, _vp]),
     "b2_decode_attn_workspace_bytes": (_sz, [_i, _i, _i, _i, _i, _i]),
-    "b2_prefill_attn": (_i, [_vp, _ll, _vp, _vp, _vp, _ll, _i, _i, _i, _i, _i, _i, _i, _f, _i, _vp]),
+    "b2_prefill_attn": (_i, [_vp, _ll, _vp, _vp, _vp, _ll, _vp, _i, _i, _i, _i, _i, _i, _i, _f, _i, _vp]),
     "b2_embed": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
     "b2_lm_head": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
     "b2_argmax": (_i, [_vp, _vp, _i, _i, _vp]),
@@ -73,6 +74,18 @@ def lib() -> C.CDLL:
             fn.argtypes = args
         _lib = L
     return _lib
+
+
+_inited = set()
+
+
+def init_device() -> None:
+    """b2_init() once per CUDA device (call with that device current)."""
+    import torch
+    dev = torch.cuda.current_device()
+    if dev not in _inited:
+        check(lib().b2_init(), "b2_init")
+        _inited.add(dev)
 
 
 class B2Error(RuntimeError):

@@ -16,8 +16,10 @@ int decode_attn(const void*, long long, const void*, const void*, const int*, co
                 size_t, int, int, int, int, int, int, float, int, cudaStream_t);
 int decode_attn_splits(int, int, int, int);
 size_t decode_attn_workspace_bytes(int, int, int, int);
-int prefill_attn(const void*, long long, const void*, const void*, void*, long long, int, int, int, int, int, int, int,
-                 float, int, cudaStream_t);
+int prefill_attn(const void*, long long, const void*, const void*, void*, long long, const int*, int, int, int, int,
+                 int, int, int, float, int, cudaStream_t);
+int init_gemm();
+int init_attn();
 int embed(const long long*, const int*, const void*, const void*, void*, int, int, int, cudaStream_t);
 int argmax_rows(const float*, long long*, int, int, cudaStream_t);
 }  // namespace b2
@@ -27,6 +29,12 @@ int argmax_rows(const float*, long long*, int, int, cudaStream_t);
 extern "C" {
 
 int b2_version(void) { return 100; }
+
+int b2_init(void) {
+  int rc = b2::init_gemm();
+  if (rc) return rc;
+  return b2::init_attn();
+}
 
 const char* b2_strerror(int code) {
   switch (code) {
@@ -88,8 +96,9 @@ size_t b2_decode_attn_workspace_bytes(int B, int H, int KV, int hd, int max_seql
   return b2::decode_attn_workspace_bytes(B, H, hd, b2::decode_attn_splits(B, KV, eff, sms));
 }
 int b2_prefill_attn(const void* q, long long q_ld, const void* kcache, const void* vcache, void* out, long long o_ld,
-                    int T, int pos0, int row, int H, int KV, int hd, int Smax, float scale, int window, void* stream) {
-  return b2::prefill_attn(q, q_ld, kcache, vcache, out, o_ld, T, pos0, row, H, KV, hd, Smax, scale, window, ST(stream));
+                    const int* positions, int T, int pos0, int row, int H, int KV, int hd, int Smax, float scale,
+                    int window, void* stream) {
+  return b2::prefill_attn(q, q_ld, kcache, vcache, out, o_ld, positions, T, pos0, row, H, KV, hd, Smax, scale, window, ST(stream));
 }
 int b2_embed(const long long* ids, const int* positions, const void* table, const void* pos_table, void* out, int T,
              int d, int vocab, void* stream) {

@@ -395,12 +395,15 @@ struct PfParams {
   const __half* q; long long q_ld;     // q[t] at q + t*q_ld
   const __half* k; const __half* v;
   __half* out; long long o_ld;
+  const int* pos_ptr;                  // device: positions of the chunk (pos0 = pos_ptr[0]) or nullptr
   int T, pos0, row, H, KV, Smax, window;
   float scale_log2;
 };
 
 template <int HD>
-__global__ void __launch_bounds__(PF_THREADS) prefill_attn_kernel(const PfParams p) {
+__global__ void __launch_bounds__(PF_THREADS) prefill_attn_kernel(const PfParams pin) {
+  PfParams p = pin;
+  if (p.pos_ptr) p.pos0 = p.pos_ptr[0];
   constexpr int LDS = HD + 8;
   constexpr int TILE_HALVES = PF_TK * LDS;
   extern __shared__ __align__(16) uint8_t smem_pf[];
@@ -560,15 +563,25 @@ static int launch_prefill(const PfParams& p, cudaStream_t st) {
   return launch_status();
 }
 
+int init_attn() {
+  sm_count_attn();
+  if (cudaFuncSetAttribute(decode_attn_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 2 * DEC_TK * (128 + 8) * 2) != cudaSuccess) return ERR_ARCH;
+  if (cudaFuncSetAttribute(decode_attn_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 2 * DEC_TK * (64 + 8) * 2) != cudaSuccess) return ERR_ARCH;
+  if (cudaFuncSetAttribute(prefill_attn_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 2 * PF_TK * (128 + 8) * 2) != cudaSuccess) return ERR_ARCH;
+  if (cudaFuncSetAttribute(prefill_attn_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 2 * PF_TK * (64 + 8) * 2) != cudaSuccess) return ERR_ARCH;
+  return OK;
+}
+
 int prefill_attn(const void* q, long long q_ld, const void* kcache, const void* vcache, void* out, long long o_ld,
-                 int T, int pos0, int row, int H, int KV, int hd, int Smax, float scale, int window, cudaStream_t st) {
+                 const int* positions, int T, int pos0, int row, int H, int KV, int hd, int Smax, float scale, int window,
+                 cudaStream_t st) {
   if (T == 0) return OK;
   if (!q || !kcache || !vcache || !out) return ERR_NULL_PTR;
-  if (T < 0 || pos0 < 0 || pos0 + T > Smax || H <= 0 || KV <= 0 || H % KV || (q_ld & 1) || (o_ld & 1)) return ERR_BAD_SHAPE;
+  if (T < 0 || (!positions && (pos0 < 0 || pos0 + T > Smax)) || H <= 0 || KV <= 0 || H % KV || (q_ld & 1) || (o_ld & 1)) return ERR_BAD_SHAPE;
   if (hd != 64 && hd != 128) return ERR_UNSUPPORTED;
   PfParams p;
   p.q = (const __half*)q; p.q_ld = q_ld; p.k = (const __half*)kcache; p.v = (const __half*)vcache;
-  p.out = (__half*)out; p.o_ld = o_ld; p.T = T; p.pos0 = pos0; p.row = row; p.H = H; p.KV = KV; p.Smax = Smax;
+  p.out = (__half*)out; p.o_ld = o_ld; p.pos_ptr = positions; p.T = T; p.pos0 = pos0; p.row = row; p.H = H; p.KV = KV; p.Smax = Smax;
   p.window = window; p.scale_log2 = scale * 1.4426950408889634f;
   return hd == 128 ? launch_prefill<128>(p, st) : launch_prefill<64>(p, st);
 }

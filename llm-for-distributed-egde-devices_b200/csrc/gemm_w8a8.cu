@@ -525,4 +525,36 @@ int lm_head(const void* x, const void* W, float* logits, int M, int V, int d, cu
   return launch_tc<64, 8, KIND_F16>(x, W, p, st);
 }
 
+// One-time set-up of every instantiation (dynamic shared-memory opt-in, driver entry point), so
+// that no launch path has first-call side effects -- required before capturing CUDA graphs.
+template <int BN, int STAGES, int KIND>
+static int init_tc() {
+  return cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES, KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                              GemmSmem<BN, STAGES>::TOTAL) == cudaSuccess ? OK : ERR_ARCH;
+}
+int init_gemm() {
+  if (!get_encode_fn()) return ERR_DRIVER;
+  sm_count();
+  int rc = OK;
+  if ((rc = init_tc<256, 4, KIND_I8>())) return rc;
+  if ((rc = init_tc<128, 6, KIND_I8>())) return rc;
+  if ((rc = init_tc<64, 8, KIND_I8>())) return rc;
+  if ((rc = init_tc<32, 8, KIND_I8>())) return rc;
+  if ((rc = init_tc<256, 4, KIND_F16>())) return rc;
+  if ((rc = init_tc<128, 6, KIND_F16>())) return rc;
+  if ((rc = init_tc<64, 8, KIND_F16>())) return rc;
+  const int big = 200 * 1024;
+  bool ok = true;
+  ok &= cudaFuncSetAttribute(gemv_i8_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, big) == cudaSuccess;
+  ok &= cudaFuncSetAttribute(gemv_i8_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, big) == cudaSuccess;
+  ok &= cudaFuncSetAttribute(gemv_i8_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, big) == cudaSuccess;
+  ok &= cudaFuncSetAttribute(gemv_i8_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, big) == cudaSuccess;
+  ok &= cudaFuncSetAttribute(gemv_f16_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, big) == cudaSuccess;
+  ok &= cudaFuncSetAttribute(gemv_f16_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, big) == cudaSuccess;
+  ok &= cudaFuncSetAttribute(gemv_f16_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, big) == cudaSuccess;
+  ok &= cudaFuncSetAttribute(gemv_f16_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, big) == cudaSuccess;
+  return ok ? OK : ERR_ARCH;
+}
+
+
 }  // namespace b2

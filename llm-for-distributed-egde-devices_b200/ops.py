@@ -110,13 +110,13 @@ def decode_attn(qkv, kcache, vcache, seqlens, H, KV, hd, max_seqlen, scale, wind
     return o
 
 
-def prefill_attn(qkv, kcache, vcache, pos0, row, H, KV, hd, scale, window=0, out=None):
+def prefill_attn(qkv, kcache, vcache, pos0, row, H, KV, hd, scale, window=0, out=None, positions=None):
     """Causal attention for one chunk of one sequence.  b2_prefill_attn."""
     _cuda(qkv, kcache, vcache, out)
     T = qkv.shape[0]
     Smax = kcache.shape[2]
     o = out if out is not None else torch.empty((T, H * hd), dtype=torch.float16, device=qkv.device)
-    check(_abi.lib().b2_prefill_attn(ptr(qkv), qkv.stride(0), ptr(kcache), ptr(vcache), ptr(o), o.stride(0), T,
+    check(_abi.lib().b2_prefill_attn(ptr(qkv), qkv.stride(0), ptr(kcache), ptr(vcache), ptr(o), o.stride(0), ptr(positions), T,
                                      int(pos0), int(row), H, KV, hd, Smax, float(scale), int(window),
                                      stream_handle()), "b2_prefill_attn")
     return o

@@ -38,6 +38,8 @@ class Pipeline:
             raise ValueError("need stages[0].first and stages[-1].last")
         self.stages = list(stages)
         self.cfg: ModelConfig = stages[0].cfg
+        self.use_graphs = True        # decode steps and full-size prefill chunks replay CUDA graphs
+        self._cache_pool = {}
 
     @classmethod
     def load(cls, model, n_stages: int = 1, devices=None, seed: int = 0, fast_init: bool = False) -> "Pipeline":
@@ -50,16 +52,30 @@ class Pipeline:
     def new_caches(self, rows: int, max_seq: int):
         return [s.new_kv_cache(rows, max_seq) for s in self.stages]
 
+    def pooled_caches(self, rows: int, max_seq: int):
+        """Caches owned by the pipeline and reused across generate() calls, so the CUDA graphs
+        captured against them are reused too."""
+        key = (rows, max_seq)
+        if key not in self._cache_pool:
+            self._cache_pool[key] = self.new_caches(rows, max_seq)
+        for c in self._cache_pool[key]:
+            c.reset()
+        return self._cache_pool[key]
+
     @property
     def launches(self) -> int:
         return sum(s.launches for s in self.stages)
 
     # ------------------------------------------------------------------------------------------
-    def _run(self, x, caches, positions, seq_ids, logits):
+    def _run(self, x, caches, positions, seq_ids, logits, graph_chunk: int = 0):
         for s, c in zip(self.stages, caches):
             if x.device != s.device:
                 x = x.to(s.device, non_blocking=True)
-            x = s.forward(x, c, positions, seq_ids, logits=logits if s.last else "none")
+            want = logits if s.last else "none"
+            if self.use_graphs:
+                x = s.forward_auto(x, c, positions, seq_ids, logits=want, graph_chunk=graph_chunk)
+            else:
+                x = s.forward(x, c, positions, seq_ids, logits=want)
         return x
 
     def prefill(self, ids, caches, row: int = 0, pos0: int = 0, chunk: int = 512, logits: str = "last"):
@@ -73,9 +89,9 @@ class Pipeline:
             pos = np.arange(pos0 + c0, pos0 + c1)
             final = c1 == T
             want = "all" if logits == "all" else ("last" if final else "none")
-            y = self._run(ids[c0:c1], caches, pos, np.full(c1 - c0, row), want)
+            y = self._run(ids[c0:c1], caches, pos, np.full(c1 - c0, row), want, graph_chunk=chunk if T > chunk else 0)
             if logits == "all":
-                outs.append(y)
+                outs.append(y.clone())
             elif final:
                 last = y
         return torch.cat(outs, 0) if logits == "all" else last
@@ -99,7 +115,7 @@ class Pipeline:
         max_seq = max_seq or min(self.cfg.max_pos, T + max_new_tokens)
         if T + max_new_tokens > max_seq:
             raise ValueError("prompt + max_new_tokens exceeds max_seq")
-        caches = caches or self.new_caches(1, max_seq)
+        caches = caches or self.pooled_caches(1, max_seq)
         out = torch.empty((T + max_new_tokens,), dtype=torch.int64, device=dev)
         out[:T] = ids
         lg = self.prefill(ids, caches, 0, 0, chunk)
@@ -153,9 +169,11 @@ class DistPipeline:
         stage = Stage.load(cfg, b, e, first=(rank == 0), last=(rank == world - 1), device=device, seed=seed,
                            fast_init=fast_init)
         cache = stage.new_kv_cache(max_rows, max_seq)
-        self = cls(rank, world, cfg.d_model, torch.device(device),
-                   lambda x, pos, seq, lg: stage.forward(x, cache, pos, seq, logits=lg), cfg.vocab)
+        self = cls(rank, world, cfg.d_model, torch.device(device), None, cfg.vocab)
         self.stage, self.cache, self.cfg = stage, cache, cfg
+        self.graph_chunk = 0          # set to the prefill chunk size to replay full chunks as graphs
+        self.fwd = lambda x, pos, seq, lg: stage.forward_auto(x, cache, pos, seq, logits=lg,
+                                                              graph_chunk=self.graph_chunk)
         return self
 
     # -- one hop --------------------------------------------------------------------------------

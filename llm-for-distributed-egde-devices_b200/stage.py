@@ -10,7 +10,11 @@ Build-defined drop-in boundary modelled on the reference's only
 ``x`` is ``input_ids [T] int64`` on the first stage, else ``hidden [T,d] fp16``; the result is
 ``hidden [T,d] fp16``, or ``logits fp32`` on the last stage.  ``kv_cache`` is caller-owned and
 updated in place.  Every arithmetic step is a call into libb200stage.so (ops.py); torch only owns
-device memory and streams.  There is no CPU path: loading on a non-CUDA device raises.
+device memory, streams and CUDA graphs.  There is no CPU path: loading on a non-CUDA device raises.
+
+Launch-bound shapes (decode steps, fixed-size prefill chunks) are captured once in a CUDA graph
+(`Stage.runner`): the kernels read positions / sequence lengths from device memory and the graph
+advances them itself, so one graph serves every step.
 """
 from __future__ import annotations
 
@@ -24,8 +28,8 @@ from .config import ModelConfig, get_config
 class KVCache:
     """Stage-local KV cache: k, v fp16 [n_layers][rows][KV][Smax][hd] plus per-row lengths.
 
-    Lengths live on the host (python ints drive launch geometry without device syncs) and are
-    mirrored to a device int32 vector that the decode-attention kernel reads.
+    Lengths live on the host (python ints drive launch geometry without device syncs); the
+    kernels get them through small device vectors owned by the Stage scratch / graph runners.
     """
 
     def __init__(self, cfg: ModelConfig, n_layers: int, rows: int, max_seq: int, device):
@@ -60,6 +64,7 @@ class _Scratch:
         self.pos = torch.empty((cap,), dtype=torch.int32, device=device)
         self.seq = torch.empty((cap,), dtype=torch.int32, device=device)
         self.lens = torch.empty((cap,), dtype=torch.int32, device=device)
+        self.ids = torch.empty((cap,), dtype=torch.int64, device=device)
         self.hn = torch.empty((cap, d), dtype=f16, device=device) if last else None
 
     def q8view(self, T, K):
@@ -71,6 +76,8 @@ class Stage:
         if torch.device(device).type != "cuda":
             raise RuntimeError("Stage runs only on a CUDA device: the hot path has no CPU fallback")
         ops._abi.lib()   # fail loudly now if the extension is missing
+        with torch.cuda.device(torch.device(device)):
+            ops._abi.init_device()
         self.cfg, self.w = cfg, sw
         self.first, self.last = bool(sw["first"]), bool(sw["last"])
         self.layer_begin, self.layer_end = layer_begin, layer_end
@@ -80,6 +87,7 @@ class Stage:
         self.scale = 1.0 / float(np.sqrt(cfg.head_dim))
         self._scratch = None
         self._ws = None
+        self._runners = {}
         self.launches = 0          # kernels of ours launched (bench.py's gpu_launches claim)
 
     # ------------------------------------------------------------------------------------------
@@ -110,8 +118,7 @@ class Stage:
 
     def _buffers(self, T: int) -> _Scratch:
         if self._scratch is None or self._scratch.cap < T:
-            cap = max(T, 8)
-            self._scratch = _Scratch(self.cfg, cap, self.device, self.last)
+            self._scratch = _Scratch(self.cfg, max(T, 8), self.device, self.last)
         return self._scratch
 
     def _workspace(self, nbytes: int):
@@ -122,8 +129,84 @@ class Stage:
         return self._ws
 
     # ------------------------------------------------------------------------------------------
+    # device-only core: every input already lives on the device, nothing here touches the host
+    # except launch geometry that depends on T alone -> capturable in a CUDA graph.
+    # ------------------------------------------------------------------------------------------
+    def _core(self, buf: _Scratch, x, T: int, kv_cache: KVCache, decode: bool, dpos, dseq, dlens, row0: int,
+              max_len: int, ws, logits: str, out, trace=None):
+        cfg = self.cfg
+        d, H, KV, hd, F = cfg.d_model, cfg.n_heads, cfg.n_kv_heads, cfg.head_dim, cfg.ffn
+        n = 0
+        if self.first:
+            h = ops.embed(x.view(-1), self.w["embed"], dpos if "pos_embed" in self.w else None,
+                          self.w.get("pos_embed"), out=buf.h[0][:T])
+            n += 1
+        else:
+            h = buf.h[0][:T]
+            if x.data_ptr() != h.data_ptr():
+                h.copy_(x.view(T, d))
+        h_alt = buf.h[1][:T]
+        qkv, attn, gu = buf.qkv[:T], buf.attn[:T], buf.gu[:T]
+        sc = buf.scale[:T]
+        act = (ops.ACT_SILU_MUL if cfg.act == "silu" else ops.ACT_GELU_MUL) if cfg.gated else \
+              (ops.ACT_GELU if cfg.act == "gelu_new" else ops.ACT_SILU)
+        for li, lw in enumerate(self.w["layers"]):
+            kc, vc = kv_cache.k[li], kv_cache.v[li]
+            q8 = buf.q8view(T, d)
+            ops.norm_quant(h, lw["ln1_g"], lw.get("ln1_b"), lw["sm_qkv"], cfg.eps, out_q=q8, out_scale=sc)
+            ops.gemm_w8a8(q8, lw["wqkv"], sc, lw["s_qkv"], lw.get("b_qkv"), None, out=qkv)
+            tr = None
+            if trace is not None:
+                tr = dict(q1=q8.clone(), s1=sc.clone(), qkv=qkv.clone())
+                trace.append(tr)
+            ops.rope_kv_append(qkv, self.cos, self.sin, dpos, kc, vc, H, KV, hd, seq_ids=dseq, seq0=row0,
+                               use_rope=cfg.rope)
+            if decode:
+                ops.decode_attn(qkv, kc, vc, dlens, H, KV, hd, max_len, self.scale, cfg.window, rows=dseq, out=attn,
+                                workspace=ws)
+                n += 1 if ws is None else 2
+            else:
+                ops.prefill_attn(qkv, kc, vc, 0, row0, H, KV, hd, self.scale, cfg.window, out=attn, positions=dpos)
+                n += 1
+            q8 = buf.q8view(T, H * hd)
+            ops.smooth_quant(attn, lw["sm_o"], out_q=q8, out_scale=sc)
+            ops.gemm_w8a8(q8, lw["wo"], sc, lw["s_o"], lw.get("b_o"), h, out=h_alt)
+            q8 = buf.q8view(T, d)
+            ops.norm_quant(h_alt, lw["ln2_g"], lw.get("ln2_b"), lw["sm_gu"], cfg.eps, out_q=q8, out_scale=sc)
+            ops.gemm_w8a8(q8, lw["wgu"], sc, lw["s_gu"], lw.get("b_gu"), None, out=gu)
+            q8 = buf.q8view(T, F)
+            ops.act_mul_quant(gu, lw["sm_d"], act, out_q=q8, out_scale=sc)
+            ops.gemm_w8a8(q8, lw["wd"], sc, lw["s_d"], lw.get("b_d"), h_alt, out=h)
+            n += 9
+            if tr is not None:
+                tr.update(attn=attn.clone(), h1=h_alt.clone(), gu=gu.clone(), q4=q8.clone(), s4=sc.clone(), h2=h.clone())
+        if not self.last or logits == "none":
+            if out is not None and out.data_ptr() != h.data_ptr():
+                out.copy_(h)
+            return (h if out is None else out), n
+        hsel = h if (logits == "all" or decode) else h[T - 1:T]
+        hn = ops.norm(hsel, self.w["lnf_g"], self.w.get("lnf_b"), cfg.eps, out=buf.hn[: hsel.shape[0]])
+        lg = ops.lm_head(hn, self.w["lm_head"], out=out)
+        return lg, n + 2
+
+    # ------------------------------------------------------------------------------------------
+    @staticmethod
+    def _classify(positions, seq_ids):
+        pos = np.asarray(positions, dtype=np.int64).reshape(-1)
+        T = int(pos.shape[0])
+        if T == 0:
+            raise ValueError("empty input")
+        rows = np.zeros((T,), dtype=np.int64) if seq_ids is None else np.asarray(seq_ids, dtype=np.int64).reshape(-1)
+        single_seq = bool((rows == rows[0]).all())
+        decode = (T == 1) or not single_seq
+        if decode and len(set(rows.tolist())) != T:
+            raise ValueError("batched decode needs one token per distinct cache row")
+        if not decode and not (np.diff(pos) == 1).all():
+            raise ValueError("a prefill chunk must cover consecutive positions")
+        return pos, rows, T, decode
+
     def forward(self, x, kv_cache: KVCache, positions, seq_ids=None, logits: str = "last", out=None, trace=None):
-        """Run this stage's layers over T tokens.
+        """Run this stage's layers over T tokens (eager launches).
 
         positions : host ints [T] (list / numpy / CPU tensor).
         seq_ids   : None -> all tokens belong to cache row 0 (T > 1 = one prefill chunk at
@@ -134,91 +217,146 @@ class Stage:
                     batched decode), "all" (every row; the `model(**inputs).logits` form used by
                     confidence_score, models_quant_updated.py:63-70) or "none" (hidden only).
         """
-        cfg = self.cfg
-        pos = np.asarray(positions, dtype=np.int64).reshape(-1)
-        T = int(pos.shape[0])
-        if T == 0:
-            raise ValueError("empty input")
-        if seq_ids is None:
-            rows = np.zeros((T,), dtype=np.int64)
-        else:
-            rows = np.asarray(seq_ids, dtype=np.int64).reshape(-1)
-        single_seq = bool((rows == rows[0]).all())
-        decode = (T == 1) or not single_seq
-        if decode and len(set(rows.tolist())) != T:
-            raise ValueError("batched decode needs one token per distinct cache row")
-        if not decode and not (np.diff(pos) == 1).all():
-            raise ValueError("a prefill chunk must cover consecutive positions")
+        pos, rows, T, decode = self._classify(positions, seq_ids)
         if int(pos.max()) >= kv_cache.max_seq:
             raise ValueError("position beyond the KV cache capacity")
         buf = self._buffers(T)
-        d, H, KV, hd, F = cfg.d_model, cfg.n_heads, cfg.n_kv_heads, cfg.head_dim, cfg.ffn
         dpos = buf.pos[:T]
-        dpos.copy_(torch.from_numpy(pos.astype(np.int32)), non_blocking=True)
-        dseq = None
+        dpos.copy_(torch.from_numpy(pos.astype(np.int32)))
+        dseq = dlens = ws = None
+        max_len = 0
         if decode:
             dseq = buf.seq[:T]
-            dseq.copy_(torch.from_numpy(rows.astype(np.int32)), non_blocking=True)
+            dseq.copy_(torch.from_numpy(rows.astype(np.int32)))
             lens_host = (pos + 1).astype(np.int32)
             dlens = buf.lens[:T]
-            dlens.copy_(torch.from_numpy(lens_host), non_blocking=True)
+            dlens.copy_(torch.from_numpy(lens_host))
             max_len = int(lens_host.max())
-            ws = self._workspace(ops.decode_attn_workspace_bytes(T, H, KV, hd, max_len, cfg.window))
-        # ---- input -----------------------------------------------------------------------------
-        if self.first:
-            ids = x if x.is_cuda else x.to(self.device, non_blocking=True)
-            h = ops.embed(ids.view(-1), self.w["embed"], dpos if "pos_embed" in self.w else None,
-                          self.w.get("pos_embed"), out=buf.h[0][:T])
-            self.launches += 1
-        else:
-            h = buf.h[0][:T]
-            h.copy_(x.view(T, d))
-        h_alt = buf.h[1][:T]
-        qkv, attn, gu = buf.qkv[:T], buf.attn[:T], buf.gu[:T]
-        sc = buf.scale[:T]
-        act = (ops.ACT_SILU_MUL if cfg.act == "silu" else ops.ACT_GELU_MUL) if cfg.gated else \
-              (ops.ACT_GELU if cfg.act == "gelu_new" else ops.ACT_SILU)
-        # ---- layers ----------------------------------------------------------------------------
-        for li, lw in enumerate(self.w["layers"]):
-            kc, vc = kv_cache.k[li], kv_cache.v[li]
-            q8 = buf.q8view(T, d)
-            ops.norm_quant(h, lw["ln1_g"], lw.get("ln1_b"), lw["sm_qkv"], cfg.eps, out_q=q8, out_scale=sc)
-            ops.gemm_w8a8(q8, lw["wqkv"], sc, lw["s_qkv"], lw.get("b_qkv"), None, out=qkv)
-            tr = None
-            if trace is not None:
-                tr = dict(q1=q8.clone(), s1=sc.clone(), qkv=qkv.clone())
-                trace.append(tr)
-            ops.rope_kv_append(qkv, self.cos, self.sin, dpos, kc, vc, H, KV, hd, seq_ids=dseq, seq0=int(rows[0]),
-                               use_rope=cfg.rope)
-            if decode:
-                ops.decode_attn(qkv, kc, vc, dlens, H, KV, hd, max_len, self.scale, cfg.window, rows=dseq, out=attn,
-                                workspace=ws)
-                self.launches += 1 if ws is None else 2
-            else:
-                ops.prefill_attn(qkv, kc, vc, int(pos[0]), int(rows[0]), H, KV, hd, self.scale, cfg.window, out=attn)
-                self.launches += 1
-            q8 = buf.q8view(T, H * hd)
-            ops.smooth_quant(attn, lw["sm_o"], out_q=q8, out_scale=sc)
-            ops.gemm_w8a8(q8, lw["wo"], sc, lw["s_o"], lw.get("b_o"), h, out=h_alt)
-            q8 = buf.q8view(T, d)
-            ops.norm_quant(h_alt, lw["ln2_g"], lw.get("ln2_b"), lw["sm_gu"], cfg.eps, out_q=q8, out_scale=sc)
-            ops.gemm_w8a8(q8, lw["wgu"], sc, lw["s_gu"], lw.get("b_gu"), None, out=gu)
-            q8 = buf.q8view(T, F)
-            ops.act_mul_quant(gu, lw["sm_d"], act, out_q=q8, out_scale=sc)
-            ops.gemm_w8a8(q8, lw["wd"], sc, lw["s_d"], lw.get("b_d"), h_alt, out=h)
-            self.launches += 9
-            if tr is not None:
-                tr.update(attn=attn.clone(), h1=h_alt.clone(), gu=gu.clone(), q4=q8.clone(), s4=sc.clone(), h2=h.clone())
+            ws = self._workspace(ops.decode_attn_workspace_bytes(T, self.cfg.n_heads, self.cfg.n_kv_heads,
+                                                                 self.cfg.head_dim, max_len, self.cfg.window))
+        if self.first and not x.is_cuda:
+            x = x.to(self.device, non_blocking=True)
+        y, n = self._core(buf, x, T, kv_cache, decode, dpos, dseq, dlens, int(rows[0]), max_len, ws, logits, out, trace)
+        self.launches += n
         for r_, p_ in zip(rows.tolist(), pos.tolist()):
             kv_cache.lens[r_] = max(kv_cache.lens[r_], p_ + 1)
-        # ---- output ----------------------------------------------------------------------------
-        if not self.last or logits == "none":
-            if out is not None:
-                out.copy_(h)
-                return out
-            return h.clone()
-        hsel = h if (logits == "all" or decode) else h[T - 1:T]
-        hn = ops.norm(hsel, self.w["lnf_g"], self.w.get("lnf_b"), cfg.eps, out=buf.hn[: hsel.shape[0]])
-        lg = ops.lm_head(hn, self.w["lm_head"], out=out)
-        self.launches += 2
-        return lg
+        if out is None and (not self.last or logits == "none"):
+            return y.clone()      # y aliases the scratch buffer
+        return y
+
+    # ------------------------------------------------------------------------------------------
+    def forward_auto(self, x, kv_cache: KVCache, positions, seq_ids=None, logits: str = "last", graph_chunk: int = 0):
+        """forward() through a captured CUDA graph when the shape is a repeating one: every decode
+        step, and prefill chunks of exactly `graph_chunk` tokens.  Anything else (ragged tails,
+        one-off shapes) launches eagerly.  The returned tensor may be the runner's static output
+        buffer: consume it before the next call with the same shape."""
+        pos, rows, T, decode = self._classify(positions, seq_ids)
+        if decode:
+            r = self.runner(kv_cache, T, decode=True, rows=rows.tolist(), logits=logits)
+            return r(x, pos)
+        if graph_chunk and T == graph_chunk:
+            r = self.runner(kv_cache, T, decode=False, rows=[int(rows[0])], logits=logits)
+            return r(x, pos)
+        return self.forward(x, kv_cache, positions, seq_ids, logits=logits)
+
+    def drop_runners(self):
+        """Release every captured graph (and the scratch buffers they pin)."""
+        self._runners.clear()
+
+    def runner(self, kv_cache: KVCache, T: int, *, decode: bool, rows=None, logits: str = "last") -> "GraphRunner":
+        """CUDA-graph runner for a fixed token count: a decode step over `rows` (one token per row)
+        or a prefill chunk of T consecutive positions of cache row rows[0]."""
+        rows_t = tuple(int(r) for r in (rows if rows is not None else ([0] * (1 if decode else T))))
+        if decode and len(rows_t) != T:
+            raise ValueError("decode runner needs one row per token")
+        key = (id(kv_cache), T, decode, rows_t if decode else rows_t[:1], logits)
+        r = self._runners.get(key)
+        if r is None:
+            r = GraphRunner(self, kv_cache, T, decode, rows_t, logits)
+            self._runners[key] = r
+        return r
+
+
+class GraphRunner:
+    """One captured CUDA graph = one stage forward at a fixed shape.
+
+    Static device state: input (ids or hidden), positions (and lengths for decode), output.  The
+    graph ends by advancing positions/lengths by its own token stride, so consecutive decode steps
+    (or consecutive chunks of one prompt) replay it with no host->device traffic besides the input.
+    `set_positions` re-seeds that state (start of a new prompt / after a ragged tail).
+    """
+
+    def __init__(self, stage: Stage, kv_cache: KVCache, T: int, decode: bool, rows, logits: str):
+        cfg, dev = stage.cfg, stage.device
+        self.stage, self.cache, self.T, self.decode, self.rows, self.logits = stage, kv_cache, T, decode, rows, logits
+        self.buf = _Scratch(cfg, max(T, 8), dev, stage.last)      # private: graphs pin their buffers
+        self.x = self.buf.ids[:T] if stage.first else self.buf.h[0][:T]
+        self.dpos = self.buf.pos[:T]
+        self.dseq = self.dlens = self.ws = None
+        self.max_len = 0
+        if decode:
+            self.dseq = self.buf.seq[:T]
+            self.dseq.copy_(torch.tensor(rows, dtype=torch.int32))
+            self.dlens = self.buf.lens[:T]
+            self.max_len = kv_cache.max_seq      # split count fixed for the whole graph lifetime
+            nb = ops.decode_attn_workspace_bytes(T, cfg.n_heads, cfg.n_kv_heads, cfg.head_dim, self.max_len, cfg.window)
+            self.ws = torch.empty((nb,), dtype=torch.uint8, device=dev) if nb else None
+        n_out = T if (decode or logits == "all") else 1
+        if stage.last and logits != "none":
+            self.out = torch.empty((n_out, cfg.vocab), dtype=torch.float32, device=dev)
+        else:
+            self.out = torch.empty((T, cfg.d_model), dtype=torch.float16, device=dev)
+        self.stride = 1 if decode else T
+        self.host_pos = None
+        self.set_positions(np.zeros(T, dtype=np.int64) if decode else np.arange(T))
+        self.graph = None
+        self.n_launch = 0
+        self._capture()
+
+    def _run_core(self):
+        _, n = self.stage._core(self.buf, self.x, self.T, self.cache, self.decode, self.dpos, self.dseq, self.dlens,
+                                self.rows[0], self.max_len, self.ws, self.logits, self.out)
+        self.dpos.add_(self.stride)
+        if self.dlens is not None:
+            self.dlens.add_(self.stride)
+        return n
+
+    def _capture(self):
+        # No warm-up run: it would write K/V into a cache that may already hold a prompt.  All
+        # one-time set-up was done by b2_init() (Stage.__init__), so the first launch of every
+        # kernel can happen under capture.
+        dev = self.stage.device
+        saved_pos = self.host_pos.copy()
+        torch.cuda.synchronize(dev)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.device(dev), torch.cuda.graph(g):
+            self.n_launch = self._run_core()
+        self.graph = g
+        self.set_positions(saved_pos)
+
+    def set_positions(self, positions):
+        pos = np.asarray(positions, dtype=np.int64).reshape(-1)
+        self.host_pos = pos.copy()
+        self.dpos.copy_(torch.from_numpy(pos.astype(np.int32)))
+        if self.dlens is not None:
+            self.dlens.copy_(torch.from_numpy((pos + 1).astype(np.int32)))
+
+    def __call__(self, x, positions=None):
+        """Replay.  x: ids [T] int64 (first stage) or hidden [T,d] fp16, on the device, or None if
+        the caller already wrote into `self.x`.  positions (host) only when they differ from the
+        graph's own running state.  Returns the static output tensor (valid until the next replay)."""
+        if positions is not None:
+            p = np.asarray(positions, dtype=np.int64).reshape(-1)
+            if not np.array_equal(p, self.host_pos):
+                self.set_positions(p)
+        if int(self.host_pos.max()) >= self.cache.max_seq:
+            raise ValueError("position beyond the KV cache capacity")
+        if x is not None and x.data_ptr() != self.x.data_ptr():
+            self.x.copy_(x.view(self.x.shape), non_blocking=True)
+        self.graph.replay()
+        self.stage.launches += self.n_launch
+        rows = self.rows if self.decode else [self.rows[0]] * self.T
+        for r_, p_ in zip(rows, self.host_pos.tolist()):
+            self.cache.lens[r_] = max(self.cache.lens[r_], p_ + 1)
+        self.host_pos = self.host_pos + self.stride
+        return self.out
