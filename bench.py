@@ -42,6 +42,7 @@ def parse():
     ap.add_argument("--new", type=int, default=128)
     ap.add_argument("--chunk", type=int, default=512)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--layers", type=int, default=0, help="PROFILING ONLY: truncate the model to this many layers")
     return ap.parse_args()
 
 
@@ -184,11 +185,15 @@ def run_ours(a):
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
     cfg = b2.get_config(a.model)
+    if a.layers:
+        import dataclasses
+        cfg = dataclasses.replace(cfg, n_layers=a.layers, name=f"{cfg.name}[TRUNCATED to {a.layers} layers: profiling only]")
     P, NEW, CH = a.prompt, a.new, a.chunk
     max_seq = P + NEW
     n_prompts = world                       # weak scaling: one prompt stream per stage
     pipe = DistPipeline.load(cfg, rank, world, dev, seed=0, fast_init=True, max_rows=n_prompts, max_seq=max_seq)
     stage = pipe.stage
+    pipe.graph_chunk = CH
     g = torch.Generator(device="cpu").manual_seed(1234)
     prompts_host = [torch.randint(0, cfg.vocab, (P,), generator=g, dtype=torch.int64).pin_memory() for _ in range(n_prompts)]
     prompts_dev = [p.to(dev) for p in prompts_host]

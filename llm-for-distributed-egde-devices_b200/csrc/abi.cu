@@ -20,6 +20,8 @@ int prefill_attn(const void*, long long, const void*, const void*, void*, long l
                  int, int, int, float, int, cudaStream_t);
 int init_gemm();
 int init_attn();
+int init_rowquant();
+int init_misc();
 int embed(const long long*, const int*, const void*, const void*, void*, int, int, int, cudaStream_t);
 int argmax_rows(const float*, long long*, int, int, cudaStream_t);
 }  // namespace b2
@@ -33,7 +35,9 @@ int b2_version(void) { return 100; }
 int b2_init(void) {
   int rc = b2::init_gemm();
   if (rc) return rc;
-  return b2::init_attn();
+  if ((rc = b2::init_attn())) return rc;
+  if ((rc = b2::init_rowquant())) return rc;
+  return b2::init_misc();
 }
 
 const char* b2_strerror(int code) {

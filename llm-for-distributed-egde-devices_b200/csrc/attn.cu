@@ -565,6 +565,13 @@ static int launch_prefill(const PfParams& p, cudaStream_t st) {
 
 int init_attn() {
   sm_count_attn();
+  {
+    cudaFuncAttributes fa;
+    bool ok = cudaFuncGetAttributes(&fa, rope_kv_append_kernel) == cudaSuccess;
+    ok &= cudaFuncGetAttributes(&fa, decode_merge_kernel<128>) == cudaSuccess;
+    ok &= cudaFuncGetAttributes(&fa, decode_merge_kernel<64>) == cudaSuccess;
+    if (!ok) return ERR_ARCH;
+  }
   if (cudaFuncSetAttribute(decode_attn_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 2 * DEC_TK * (128 + 8) * 2) != cudaSuccess) return ERR_ARCH;
   if (cudaFuncSetAttribute(decode_attn_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 2 * DEC_TK * (64 + 8) * 2) != cudaSuccess) return ERR_ARCH;
   if (cudaFuncSetAttribute(prefill_attn_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 2 * PF_TK * (128 + 8) * 2) != cudaSuccess) return ERR_ARCH;

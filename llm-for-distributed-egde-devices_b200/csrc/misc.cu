@@ -84,4 +84,11 @@ int argmax_rows(const float* logits, long long* out, int T, int V, cudaStream_t 
   return launch_status();
 }
 
+int init_misc() {
+  cudaFuncAttributes fa;
+  bool ok = cudaFuncGetAttributes(&fa, embed_kernel) == cudaSuccess;
+  ok &= cudaFuncGetAttributes(&fa, argmax_kernel) == cudaSuccess;
+  return ok ? OK : ERR_ARCH;
+}
+
 }  // namespace b2

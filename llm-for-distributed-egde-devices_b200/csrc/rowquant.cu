@@ -248,4 +248,22 @@ int act_mul_quant(const void* gate_up, const float* smooth, int8_t* q, float* ro
   }
 }
 
+// Force-load every instantiation (lazy module loading must not happen under graph capture).
+template <typename K>
+static bool touch(K kern) {
+  cudaFuncAttributes fa;
+  return cudaFuncGetAttributes(&fa, kern) == cudaSuccess;
+}
+template <int MODE, bool F16>
+static bool touch_mode() {
+  return touch(rowquant_kernel<MODE, 128, 4, F16>) && touch(rowquant_kernel<MODE, 256, 4, F16>) &&
+         touch(rowquant_kernel<MODE, 512, 4, F16>) && touch(rowquant_kernel<MODE, 1024, 4, F16>);
+}
+int init_rowquant() {
+  bool ok = touch_mode<ROW_PLAIN, false>() && touch_mode<ROW_RMS, false>() && touch_mode<ROW_LN, false>() &&
+            touch_mode<ROW_SILU_MUL, false>() && touch_mode<ROW_GELU_MUL, false>() && touch_mode<ROW_GELU, false>() &&
+            touch_mode<ROW_SILU, false>() && touch_mode<ROW_RMS, true>() && touch_mode<ROW_LN, true>();
+  return ok ? OK : ERR_ARCH;
+}
+
 }  // namespace b2

@@ -18,6 +18,8 @@ advances them itself, so one graph serves every step.
 """
 from __future__ import annotations
 
+import gc
+
 import numpy as np
 import torch
 
@@ -329,8 +331,17 @@ class GraphRunner:
         saved_pos = self.host_pos.copy()
         torch.cuda.synchronize(dev)
         g = torch.cuda.CUDAGraph()
-        with torch.cuda.device(dev), torch.cuda.graph(g):
-            self.n_launch = self._run_core()
+        # Garbage collection must not run inside the capture: freeing an older runner there
+        # destroys its CUDA graph, which is illegal while a stream is capturing.
+        gc.collect()
+        gc_was_on = gc.isenabled()
+        gc.disable()
+        try:
+            with torch.cuda.device(dev), torch.cuda.graph(g):
+                self.n_launch = self._run_core()
+        finally:
+            if gc_was_on:
+                gc.enable()
         self.graph = g
         self.set_positions(saved_pos)
 
