@@ -110,6 +110,30 @@ int b2_decode_attn(const void* q, long long q_ld, const void* kcache, const void
 /* Bytes of workspace b2_decode_attn wants for these sizes (0 if it will not split). */
 size_t b2_decode_attn_workspace_bytes(int B, int H, int KV, int hd, int max_seqlen, int window);
 
+/* b2_decode_attn for callers that cannot allocate device memory.  (No counterpart in the
+ * reference: it exists for hosts of this library, not to replace any reference routine.)
+ * Who needs it: a server that handed all of HBM to its KV-cache pool at start-up and runs with the
+ * allocator closed; a latency-critical decode thread in which cudaMalloc -- a device-wide
+ * synchronisation with no time bound -- is forbidden; a plugin host that owns device memory and
+ * does not let plugins allocate.  Such callers have no workspace to pass, so this variant keeps the
+ * split-KV partials in a fixed B2_DECODE_ATTN_STATIC_SCRATCH_BYTES (1 MiB) array inside the library image
+ * (every GPU that loads the library holds those bytes until the process exits).  The call itself
+ * allocates nothing: no cudaMalloc/cudaFree, no allocating library routine.
+ * Arguments and result are those of b2_decode_attn without workspace/workspace_bytes; the output is
+ * the same as b2_decode_attn's with a full-size workspace.
+ * - Sizes whose partials (b2_decode_attn_workspace_bytes) exceed the array are refused with
+ *   B2_ERR_TOO_LARGE; nothing is launched and the split count is never silently reduced.
+ * - The first call on each device looks up the array's device address (cudaGetSymbolAddress, with
+ *   that device current).  Make that first call before starting any stream capture.
+ * - All calls share the one array and it keeps the previous call's contents.  Nothing in it needs
+ *   to be zero on entry (each call writes every slot it later reads), but two calls whose kernels
+ *   can overlap on the GPU -- different streams, or concurrent host threads on one device -- race
+ *   on it and corrupt each other.  Serialise them (one stream, or events) or use b2_decode_attn. */
+#define B2_DECODE_ATTN_STATIC_SCRATCH_BYTES (1u << 20)
+int b2_decode_attn_static(const void* q, long long q_ld, const void* kcache, const void* vcache, const int* seqlens,
+                          const int* rows, void* out, long long o_ld, int B, int H, int KV, int hd, int Smax,
+                          int max_seqlen, float scale, int window, void* stream);
+
 /* Causal (optionally sliding-window) attention for one contiguous chunk of T query tokens of one
  * sequence at positions [pos0, pos0+T), keys 0..pos0+T-1 read from cache row `row` (the chunk's
  * own k/v must already be appended).  positions: device int32 [T] or NULL; when given, pos0 is

@@ -31,6 +31,7 @@ SIGNATURES = {
     "b2_gemm_w8a8_sched": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "b2_rope_kv_append": (_i, [_vp, _ll, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "b2_decode_attn": (_i, [_vp, _ll, _vp, _vp, _vp, _vp, _vp, _ll, _vp, _sz, _i, _i, _i, _i, _i, _i, _f, _i, _vp]),
+    "b2_decode_attn_static": (_i, [_vp, _ll, _vp, _vp, _vp, _vp, _vp, _ll, _i, _i, _i, _i, _i, _i, _f, _i, _vp]),
     "b2_decode_attn_workspace_bytes": (_sz, [_i, _i, _i, _i, _i, _i]),
     "b2_prefill_attn": (_i, [_vp, _ll, _vp, _vp, _vp, _ll, _vp, _i, _i, _i, _i, _i, _i, _i, _f, _i, _vp]),
     "b2_embed": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp]),

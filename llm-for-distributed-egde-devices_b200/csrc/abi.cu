@@ -14,6 +14,8 @@ int rope_kv_append(void*, long long, const float*, const float*, const int*, con
                    int, int, int, int, cudaStream_t);
 int decode_attn(const void*, long long, const void*, const void*, const int*, const int*, void*, long long, void*,
                 size_t, int, int, int, int, int, int, float, int, cudaStream_t);
+int decode_attn_static(const void*, long long, const void*, const void*, const int*, const int*, void*, long long, int,
+                       int, int, int, int, int, float, int, cudaStream_t);
 int decode_attn_splits(int, int, int, int);
 size_t decode_attn_workspace_bytes(int, int, int, int);
 int prefill_attn(const void*, long long, const void*, const void*, void*, long long, const int*, int, int, int, int,
@@ -89,6 +91,12 @@ int b2_decode_attn(const void* q, long long q_ld, const void* kcache, const void
                    int KV, int hd, int Smax, int max_seqlen, float scale, int window, void* stream) {
   return b2::decode_attn(q, q_ld, kcache, vcache, seqlens, rows, out, o_ld, workspace, workspace_bytes, B, H, KV, hd,
                          Smax, max_seqlen, scale, window, ST(stream));
+}
+int b2_decode_attn_static(const void* q, long long q_ld, const void* kcache, const void* vcache, const int* seqlens,
+                          const int* rows, void* out, long long o_ld, int B, int H, int KV, int hd, int Smax,
+                          int max_seqlen, float scale, int window, void* stream) {
+  return b2::decode_attn_static(q, q_ld, kcache, vcache, seqlens, rows, out, o_ld, B, H, KV, hd, Smax, max_seqlen, scale,
+                                window, ST(stream));
 }
 size_t b2_decode_attn_workspace_bytes(int B, int H, int KV, int hd, int max_seqlen, int window) {
   int dev = 0, sms = 148;

@@ -385,6 +385,69 @@ int decode_attn(const void* q, long long q_ld, const void* kcache, const void* v
 }
 
 // =============================================================================================
+// decode attention for callers that may not allocate
+// =============================================================================================
+// Some hosts of this library cannot hand us a workspace because they cannot obtain one: a serving
+// process that gave all of HBM to its KV-cache pool at start-up and runs with the allocator closed,
+// a latency-critical decode thread where cudaMalloc (which synchronises the device and has no
+// time bound) is banned, or a plugin host that owns device memory and forbids plugins to allocate.
+// For them the split-KV partials live in the fixed array below, which is part of the library
+// image: every GPU that loads libb200stage.so carries these bytes until the process exits.
+constexpr size_t DEC_STATIC_SCRATCH_BYTES = 1u << 20;   // 1 MiB, == B2_DECODE_ATTN_STATIC_SCRATCH_BYTES
+static __device__ __align__(256) unsigned char g_dec_static_scratch[DEC_STATIC_SCRATCH_BYTES];
+
+// `g_dec_static_scratch` named in HOST code is only the host-side handle of the symbol, not a
+// device address; the address a kernel may dereference is looked up per device, once, here.
+constexpr int DEC_STATIC_MAX_DEVICES = 64;
+static void* g_dec_static_addr[DEC_STATIC_MAX_DEVICES] = {nullptr};
+
+static int dec_static_scratch_ptr(void** out) {
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= DEC_STATIC_MAX_DEVICES) return ERR_ARCH;
+  void* p = __atomic_load_n(&g_dec_static_addr[dev], __ATOMIC_ACQUIRE);
+  if (!p) {
+    // First call on this device (it is the current device): resolve the symbol's device address.
+    // Racing first calls resolve the same address, so a plain publish is enough.
+    if (cudaGetSymbolAddress(&p, g_dec_static_scratch) != cudaSuccess || !p) {
+      cudaGetLastError();
+      return ERR_DRIVER;
+    }
+    __atomic_store_n(&g_dec_static_addr[dev], p, __ATOMIC_RELEASE);
+  }
+  *out = p;
+  return OK;
+}
+
+// Same computation and same kernels as decode_attn(); only where the partials live differs.
+// Nothing in the array has to start at zero: every (sequence, head, split) slot that the merge
+// kernel reads is written by the attention kernel of the same call, including empty splits.
+int decode_attn_static(const void* q, long long q_ld, const void* kcache, const void* vcache, const int* seqlens,
+                       const int* rows, void* out, long long o_ld, int B, int H, int KV, int hd, int Smax,
+                       int max_seqlen, float scale, int window, cudaStream_t st) {
+  if (B == 0) return OK;
+  if (!q || !kcache || !vcache || !seqlens || !out) return ERR_NULL_PTR;
+  if (B < 0 || H <= 0 || KV <= 0 || H % KV || H / KV > 8 || (q_ld & 1) || max_seqlen <= 0) return ERR_BAD_SHAPE;
+  if (hd != 64 && hd != 128) return ERR_UNSUPPORTED;
+  const int eff = (window > 0 && max_seqlen > window) ? window : max_seqlen;
+  const int splits = decode_attn_splits(B, KV, eff, sm_count_attn());
+  const size_t need = decode_attn_workspace_bytes(B, H, hd, splits);
+  if (need > DEC_STATIC_SCRATCH_BYTES) return ERR_TOO_LARGE;   // no silent shrink: the caller must know
+  void* scratch = nullptr;
+  if (need > 0) {
+    const int rc = dec_static_scratch_ptr(&scratch);
+    if (rc) return rc;
+  }
+  DecParams p;
+  p.q = (const __half*)q; p.q_ld = q_ld; p.k = (const __half*)kcache; p.v = (const __half*)vcache;
+  p.seqlens = seqlens; p.rows = rows; p.out = (__half*)out; p.o_ld = o_ld;
+  p.part_o = (float*)scratch;
+  p.part_ml = p.part_o ? p.part_o + (size_t)B * H * splits * hd : nullptr;
+  p.H = H; p.KV = KV; p.Smax = Smax; p.splits = splits; p.window = window;
+  p.scale_log2 = scale * 1.4426950408889634f;
+  return hd == 128 ? launch_decode<128>(p, B, st) : launch_decode<64>(p, B, st);
+}
+
+// =============================================================================================
 // prefill attention (one contiguous chunk of one sequence; causal, optional sliding window)
 // =============================================================================================
 constexpr int PF_BM = 64;     // query rows per CTA (16 per warp)

@@ -110,6 +110,23 @@ def decode_attn(qkv, kcache, vcache, seqlens, H, KV, hd, max_seqlen, scale, wind
     return o
 
 
+def decode_attn_static(qkv, kcache, vcache, seqlens, H, KV, hd, max_seqlen, scale, window=0, rows=None, out=None):
+    """decode_attn without a caller workspace, for hosts that cannot allocate device memory at
+    call time (allocator closed after start-up, cudaMalloc banned on the decode thread, memory
+    owned by a plugin host).  The split-KV partials use a fixed 1 MiB array inside the library;
+    bigger problems raise B2Error (too large).  Calls share that array, so do not let two of them
+    overlap on the GPU; make the first call on a device before any stream capture.
+    b2_decode_attn_static.  (`out` is allocated here only when the caller passes none.)"""
+    _cuda(qkv, kcache, vcache, seqlens, rows, out)
+    B = qkv.shape[0]
+    Smax = kcache.shape[2]
+    o = out if out is not None else torch.empty((B, H * hd), dtype=torch.float16, device=qkv.device)
+    check(_abi.lib().b2_decode_attn_static(ptr(qkv), qkv.stride(0), ptr(kcache), ptr(vcache), ptr(seqlens), ptr(rows),
+                                           ptr(o), o.stride(0), B, H, KV, hd, Smax, int(max_seqlen), float(scale),
+                                           int(window), stream_handle()), "b2_decode_attn_static")
+    return o
+
+
 def prefill_attn(qkv, kcache, vcache, pos0, row, H, KV, hd, scale, window=0, out=None, positions=None):
     """Causal attention for one chunk of one sequence.  b2_prefill_attn."""
     _cuda(qkv, kcache, vcache, out)
