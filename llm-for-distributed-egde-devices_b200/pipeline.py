@@ -196,7 +196,7 @@ class DistPipeline:
             return tok
         if self.last:
             self.dist.send(tok, dst=0, group=self.group)
-            return tok if self.first else None
+            return tok
         if self.first:
             t = torch.empty_like(tok) if tok is not None else None
             self.dist.recv(t, src=self.world - 1, group=self.group)

@@ -1,0 +1,106 @@
+"""Generate the golden fixtures in this directory (run in the build container, where transformers is
+importable; the GPU box never needs to run this).
+
+    python tests/golden/make_golden.py
+
+For each small seeded config it writes `<name>.npz` with
+
+  ids            prompt token ids
+  hf_logits      Tier R: fp32 logits of HF `LlamaForCausalLM` -- the class the reference's
+                 `AutoModelForCausalLM.from_pretrained` call instantiates for Llama-family
+                 checkpoints (Code/Quantised Models/models_quant_updated.py:34-38) -- loaded with the
+                 SAME synthetic fp32 weights the stage path quantises
+  hf_greedy      Tier R: `generate(do_sample=False)` continuation (the greedy subset of the
+                 reference's generate call, models_quant_updated.py:84-93)
+  hf_dyn_logits  Tier R': the same model after `torch.quantization.quantize_dynamic(model,
+                 {nn.Linear}, qint8)`, the reference's CPU int8 path (Code/C-DAC Server/try.py:204-205)
+  s_logits, s_greedy, s_margins
+                 Tier S: oracle/w8a8.py on the W8A8 weights (regression anchor for the oracle itself)
+
+Nothing here reads /root/reference; the reference contributes only the call sequence cited above.
+"""
+import os
+import sys
+import warnings
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+
+import b200stage  # noqa: E402
+from b200stage import weights  # noqa: E402
+from oracle import w8a8 as O  # noqa: E402
+
+CASES = [("tiny-llama-test", 3, 24, 8), ("tiny-gqa-test", 5, 20, 8)]
+
+
+def hf_model(cfg, seed):
+    from transformers import LlamaConfig, LlamaForCausalLM
+    hc = LlamaConfig(vocab_size=cfg.vocab, hidden_size=cfg.d_model, intermediate_size=cfg.ffn,
+                     num_hidden_layers=cfg.n_layers, num_attention_heads=cfg.n_heads,
+                     num_key_value_heads=cfg.n_kv_heads, head_dim=cfg.head_dim, max_position_embeddings=cfg.max_pos,
+                     rms_norm_eps=cfg.eps, rope_theta=cfg.rope_theta, tie_word_embeddings=False,
+                     attention_bias=False, mlp_bias=False)
+    m = LlamaForCausalLM(hc).eval().float()
+    sd = {}
+    H, KV, hd, F = cfg.n_heads, cfg.n_kv_heads, cfg.head_dim, cfg.ffn
+    h16 = lambda t: t.to(torch.float16).to(torch.float32)     # the stage path stores these in fp16
+    for li in range(cfg.n_layers):
+        w = weights.init_layer_fp32(cfg, li, seed)
+        p = f"model.layers.{li}."
+        sd[p + "self_attn.q_proj.weight"] = w["wqkv"][: H * hd]
+        sd[p + "self_attn.k_proj.weight"] = w["wqkv"][H * hd: (H + KV) * hd]
+        sd[p + "self_attn.v_proj.weight"] = w["wqkv"][(H + KV) * hd:]
+        sd[p + "self_attn.o_proj.weight"] = w["wo"]
+        sd[p + "mlp.gate_proj.weight"] = w["wgu"][:F]
+        sd[p + "mlp.up_proj.weight"] = w["wgu"][F:]
+        sd[p + "mlp.down_proj.weight"] = w["wd"]
+        sd[p + "input_layernorm.weight"] = h16(w["ln1_g"])
+        sd[p + "post_attention_layernorm.weight"] = h16(w["ln2_g"])
+    e = weights.init_embed_fp32(cfg, seed)
+    sd["model.embed_tokens.weight"] = h16(e["embed"])
+    sd["model.norm.weight"] = h16(e["lnf_g"])
+    sd["lm_head.weight"] = h16(e["lm_head"])
+    missing, unexpected = m.load_state_dict(sd, strict=False)
+    assert not unexpected and all("rotary" in k or "inv_freq" in k for k in missing), (missing, unexpected)
+    return m
+
+
+def main():
+    warnings.filterwarnings("ignore")
+    torch.set_num_threads(4)
+    for name, seed, T, new in CASES:
+        cfg = b200stage.get_config(name)
+        ids = np.random.default_rng(seed + 100).integers(0, cfg.vocab, T)
+        m = hf_model(cfg, seed)
+        tid = torch.from_numpy(ids)[None]
+        with torch.no_grad():
+            hf_logits = m(tid).logits[0].numpy()
+            hf_greedy = m.generate(input_ids=tid, attention_mask=torch.ones_like(tid), max_new_tokens=new,
+                                   min_new_tokens=new, do_sample=False, pad_token_id=0)[0].numpy()
+            mq = torch.quantization.quantize_dynamic(m, {torch.nn.Linear}, dtype=torch.qint8)
+            hf_dyn_logits = mq(tid).logits[0].numpy()
+        sw = weights.to_numpy(weights.build_stage_weights(cfg, 0, cfg.n_layers, True, True, seed, "cpu"))
+        cos, sin = O.rope_table(cfg.head_dim, cfg.max_pos, cfg.rope_theta)
+        cache = O.KVCacheOracle(cfg.n_layers, 1, cfg.n_kv_heads, T + new, cfg.head_dim)
+        s_logits = O.stage_forward(ids, sw, cfg.kernel_cfg(), cache, np.zeros(T, np.int64), np.arange(T), cos, sin)
+        s_greedy, margins = O.greedy_generate([sw], cfg.kernel_cfg(), ids, new, T + new)
+        out = os.path.join(HERE, f"{name}.npz")
+        np.savez_compressed(out, ids=ids, hf_logits=hf_logits.astype(np.float32), hf_greedy=hf_greedy,
+                            hf_dyn_logits=hf_dyn_logits.astype(np.float32), s_logits=s_logits.astype(np.float32),
+                            s_greedy=s_greedy, s_margins=np.array(margins, np.float32), seed=seed, new=new)
+        a, b = hf_logits.ravel().astype(np.float64), s_logits.ravel().astype(np.float64)
+        c = hf_dyn_logits.ravel().astype(np.float64)
+        print(f"{name}: cos(S,HF)={a @ b / np.linalg.norm(a) / np.linalg.norm(b):.6f} "
+              f"cos(dyn,HF)={a @ c / np.linalg.norm(a) / np.linalg.norm(c):.6f} "
+              f"maxabs(S-HF)={np.abs(a - b).max():.4f} max|HF|={np.abs(a).max():.2f} "
+              f"argmax agree={np.mean(hf_logits.argmax(-1) == s_logits.argmax(-1)):.3f} "
+              f"greedy equal={np.array_equal(hf_greedy, s_greedy)} min margin={min(margins):.3f} "
+              f"size={os.path.getsize(out) / 1024:.0f} KiB")
+
+
+if __name__ == "__main__":
+    main()
