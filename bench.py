@@ -323,28 +323,41 @@ def roofline_pass(torch, ops, stage, cfg, pk, dev, chunk):
     d = cfg.d_model
 
     def timed(fn, reps):
+        """fn() is captured once in a CUDA graph (as the real decode/prefill steps are) so that the
+        events bracket device time, not Python launch overhead."""
         s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         fn()
         torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            fn()
+        g.replay()
+        torch.cuda.synchronize()
         s.record()
         for _ in range(reps):
-            fn()
+            g.replay()
         e.record()
         torch.cuda.synchronize()
         return s.elapsed_time(e) / reps
 
-    # decode: M = 1 weight stream over the biggest linear (gate_up), all layers back to back
-    x8 = torch.randint(-127, 128, (1, d), dtype=torch.int8, device=dev)
-    xs = torch.full((1,), 0.01, device=dev)
-    out = torch.empty((1, cfg.up_out), dtype=torch.float16, device=dev)
+    # decode: the M = 1 fused linear (RMSNorm + quantise + weight stream + SiLU*up epilogue) over the
+    # biggest matrix (gate_up), all layers back to back -> every launch streams cold weights
+    xh = torch.randn((1, d), dtype=torch.float16, device=dev)
+    y32 = torch.empty((1, cfg.ffn), dtype=torch.float32, device=dev)
+    amax = torch.zeros((8,), dtype=torch.float32, device=dev)
+    xk = ops.X_LN if cfg.norm == "layernorm" else ops.X_RMS
 
     def dec():
         for lw in layers:
-            ops.gemm_w8a8(x8, lw["wgu"], xs, lw["s_gu"], out=out)
+            ops.fused_linear(xh, lw["wgu"], lw["s_gu"], x_kind=xk, gamma=lw["ln2_g"], beta=lw.get("ln2_b"),
+                             smooth=lw["sm_gu"], eps=cfg.eps, out=y32, out_kind=ops.O_GATED, out_smooth=lw["sm_d"],
+                             out_amax=amax)
     ms = timed(dec, 5) / len(layers)
-    bytes_launch = cfg.up_out * d + d + cfg.up_out * 6
+    # algorithmic bytes: int8 weights + fp16 x, gamma + fp32 smooth (in and out) + w_scale + fp32 y
+    bytes_launch = cfg.up_out * d + 2 * d * 2 + d * 4 + cfg.ffn * 4 + cfg.up_out * 4 + cfg.ffn * 4
     achieved = bytes_launch / (ms * 1e-3) / 1e9
-    roof = {"bound": "hbm", "kernel": "gemv_i8_kernel<1> (gate_up, M=1)", "achieved": achieved, "peak": pk["hbm"], "unit": "GB/s",
+    roof = {"bound": "hbm", "kernel": "fused_gemv_kernel<1,RMS,GATED> (norm+quant+gate_up GEMV+SiLU*up, M=1)",
+            "achieved": achieved, "peak": pk["hbm"], "unit": "GB/s",
             "frac": achieved / pk["hbm"], "traffic": None, "algorithmic_bytes_per_launch": bytes_launch,
             "avg_launch_us": ms * 1e3, "peak_source": pk["which"]}
     # prefill: M = chunk tokens through the same linear on the tensor cores

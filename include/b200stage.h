@@ -85,6 +85,41 @@ int b2_gemm_w8a8_sched(const int8_t* A, const int8_t* W, const float* a_scale, c
                        const void* bias, const void* residual, void* out, int32_t* acc_dump, int M, int N, int K,
                        int schedule, void* stream);
 
+/* Decode-time fused linear for M <= 8 tokens: activation prologue -> per-token int8 quantise ->
+ * W8A8 weight-streaming GEMV -> epilogue, in ONE launch (programmatic dependent launch: the weight
+ * prefetch overlaps the previous kernel's tail).  Bit-identical to the unfused entry points.
+ * x_kind: 0 = fp16 x + RMSNorm(gamma) [+smooth]   (== b2_norm_quant, beta NULL)
+ *         1 = fp16 x + LayerNorm(gamma, beta) [+smooth]
+ *         2 = fp16 x [+smooth]                    (== b2_smooth_quant)
+ *         3 = fp32 y [M,K] with row absmax x_amax [M], as written by an out_kind = 1 call
+ *             (== the quantise step of b2_act_mul_quant)
+ * out_kind: 0 = out fp16 [M,N] = dequantised result + bias + residual   (== b2_gemm_w8a8)
+ *           1 = W is the [gate; up] matrix (N = 2F rows): out is fp32 y [M,F] =
+ *               act(fp16(gate)) * fp16(up) * out_smooth[f] and out_amax[m] = max(out_amax[m], |y|)
+ *               (atomic; the caller -- or an earlier call through zero_amax -- zeroes it first).
+ *               act: 0 silu, 1 gelu_new.  residual must be NULL.
+ * zero_amax: optional [M] floats this launch sets to 0 (so a chain of calls needs no memset).
+ * x_ld: row stride of x in elements.  K % 16 == 0.  M > 8 returns B2_ERR_UNSUPPORTED (use the
+ * unfused entry points, which run the tensor-core schedule).
+ * Replaces: the same reference calls as b2_norm_quant + b2_gemm_w8a8 + b2_act_mul_quant, inside the
+ * decode loop of `model.generate` (models_quant_updated.py:84-93). */
+int b2_fused_linear(const void* x, long long x_ld, int x_kind, const void* gamma, const void* beta, const float* smooth,
+                    const float* x_amax, float eps, const int8_t* W, const float* w_scale, const void* bias,
+                    const void* residual, void* out, int out_kind, int act, const float* out_smooth, float* out_amax,
+                    float* zero_amax, int M, int N, int K, void* stream);
+
+/* Decode-time (M <= 8) qkv projection with everything around it fused: activation prologue
+ * (x_kind 0/1/2 as in b2_fused_linear) -> int8 quantise -> W8A8 GEMV over W = [q;k;v] ->
+ * dequantise + bias -> fp16 -> rotary embedding of q and k -> rotated q written to qkv_out
+ * [M,(H+2KV)*hd] (only the q columns are written), rotated k and v appended to the caches at
+ * (row seq_ids[m] or seq0, positions[m]).  Bit-identical to b2_fused_linear + b2_rope_kv_append.
+ * Replaces: q/k/v_proj + apply_rotary_pos_emb + DynamicCache.update (modeling_llama.py:251-289,
+ * :128-153) inside the decode loop of `generate` (models_quant_updated.py:84-93). */
+int b2_fused_qkv(const void* x, long long x_ld, int x_kind, const void* gamma, const void* beta, const float* smooth,
+                 float eps, const int8_t* W, const float* w_scale, const void* bias, void* qkv_out,
+                 const float* cos_table, const float* sin_table, const int* positions, const int* seq_ids, int seq0,
+                 void* kcache, void* vcache, int M, int H, int KV, int hd, int Smax, int K, int use_rope, void* stream);
+
 /* Rotary embedding of q and k (in fp32 from a caller-supplied cos/sin table [max_pos, hd/2] fp32)
  * and append of rotated k and v to the KV cache.  qkv [T, ld] fp16: q heads at columns
  * [0,H*hd), k at [H*hd,(H+KV)*hd), v after; q is rotated in place.  positions [T] int32;

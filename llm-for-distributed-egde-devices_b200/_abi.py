@@ -36,6 +36,10 @@ SIGNATURES = {
     "b2_prefill_attn": (_i, [_vp, _ll, _vp, _vp, _vp, _ll, _vp, _i, _i, _i, _i, _i, _i, _i, _f, _i, _vp]),
     "b2_embed": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
     "b2_lm_head": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
+    "b2_fused_linear": (_i, [_vp, _ll, _i, _vp, _vp, _vp, _vp, _f, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp,
+                             _i, _i, _i, _vp]),
+    "b2_fused_qkv": (_i, [_vp, _ll, _i, _vp, _vp, _vp, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp,
+                          _i, _i, _i, _i, _i, _i, _i, _vp]),
     "b2_argmax": (_i, [_vp, _vp, _i, _i, _vp]),
 }
 

@@ -24,6 +24,13 @@ int init_gemm();
 int init_attn();
 int init_rowquant();
 int init_misc();
+int init_fused();
+int fused_qkv(const void*, long long, int, const void*, const void*, const float*, float, const int8_t*, const float*,
+              const void*, void*, const float*, const float*, const int*, const int*, int, void*, void*, int, int, int,
+              int, int, int, int, cudaStream_t);
+int fused_linear(const void*, long long, int, const void*, const void*, const float*, const float*, float, const int8_t*,
+                 const float*, const void*, const void*, void*, int, int, const float*, float*, float*, int, int, int,
+                 cudaStream_t);
 int embed(const long long*, const int*, const void*, const void*, void*, int, int, int, cudaStream_t);
 int argmax_rows(const float*, long long*, int, int, cudaStream_t);
 }  // namespace b2
@@ -39,7 +46,8 @@ int b2_init(void) {
   if (rc) return rc;
   if ((rc = b2::init_attn())) return rc;
   if ((rc = b2::init_rowquant())) return rc;
-  return b2::init_misc();
+  if ((rc = b2::init_misc())) return rc;
+  return b2::init_fused();
 }
 
 const char* b2_strerror(int code) {
@@ -79,6 +87,20 @@ int b2_gemm_w8a8_sched(const int8_t* A, const int8_t* W, const float* a_scale, c
                        const void* residual, void* out, int32_t* acc_dump, int M, int N, int K, int schedule,
                        void* stream) {
   return b2::gemm_w8a8(A, W, a_scale, w_scale, bias, residual, out, acc_dump, M, N, K, schedule, ST(stream));
+}
+int b2_fused_linear(const void* x, long long x_ld, int x_kind, const void* gamma, const void* beta, const float* smooth,
+                    const float* x_amax, float eps, const int8_t* W, const float* w_scale, const void* bias,
+                    const void* residual, void* out, int out_kind, int act, const float* out_smooth, float* out_amax,
+                    float* zero_amax, int M, int N, int K, void* stream) {
+  return b2::fused_linear(x, x_ld, x_kind, gamma, beta, smooth, x_amax, eps, W, w_scale, bias, residual, out, out_kind,
+                          act, out_smooth, out_amax, zero_amax, M, N, K, ST(stream));
+}
+int b2_fused_qkv(const void* x, long long x_ld, int x_kind, const void* gamma, const void* beta, const float* smooth,
+                 float eps, const int8_t* W, const float* w_scale, const void* bias, void* qkv_out,
+                 const float* cos_table, const float* sin_table, const int* positions, const int* seq_ids, int seq0,
+                 void* kcache, void* vcache, int M, int H, int KV, int hd, int Smax, int K, int use_rope, void* stream) {
+  return b2::fused_qkv(x, x_ld, x_kind, gamma, beta, smooth, eps, W, w_scale, bias, qkv_out, cos_table, sin_table,
+                       positions, seq_ids, seq0, kcache, vcache, M, H, KV, hd, Smax, K, use_rope, ST(stream));
 }
 int b2_rope_kv_append(void* qkv, long long ld, const float* cos_table, const float* sin_table, const int* positions,
                       const int* seq_ids, int seq0, void* kcache, void* vcache, int T, int H, int KV, int hd, int Smax,

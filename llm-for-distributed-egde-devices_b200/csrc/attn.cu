@@ -118,7 +118,8 @@ int rope_kv_append(void* qkv, long long ld, const float* cosT, const float* sinT
 // =============================================================================================
 // decode attention
 // =============================================================================================
-constexpr int DEC_TK = 128;       // keys per stage (32 per warp)
+constexpr int DEC_TK = 64;        // keys per stage (16 per warp)
+constexpr int DEC_NST = 4;        // cp.async stages: up to 256 keys (K and V) in flight per CTA
 constexpr int DEC_THREADS = 128;
 
 struct DecParams {
@@ -138,8 +139,8 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) decode_attn_kernel(const DecPa
   constexpr int LDS = HD + 8;                       // padded row (halves): ldmatrix conflict-free
   constexpr int TILE_HALVES = DEC_TK * LDS;
   extern __shared__ __align__(16) uint8_t smem_dec[];
-  __half* sK = reinterpret_cast<__half*>(smem_dec);   // [2][TK][LDS]
-  __half* sV = sK + 2 * TILE_HALVES;                  // [2][TK][LDS]
+  __half* sK = reinterpret_cast<__half*>(smem_dec);   // [NST][TK][LDS]
+  __half* sV = sK + DEC_NST * TILE_HALVES;            // [NST][TK][LDS]
   const int kvh = blockIdx.x, b = blockIdx.y, split = blockIdx.z;
   const int G = p.H / p.KV;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -148,7 +149,7 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) decode_attn_kernel(const DecPa
   const int row = p.rows ? p.rows[b] : b;
   const int first = (p.window > 0 && seqlen > p.window) ? seqlen - p.window : 0;
   const int n = seqlen - first;
-  const int chunk = (((n + p.splits - 1) / p.splits) + 31) & ~31;
+  const int chunk = (((n + p.splits - 1) / p.splits) + 15) & ~15;
   const int kbeg = first + split * chunk;
   const int kend = min(seqlen, kbeg + chunk);
   const int ntiles = kend > kbeg ? (kend - kbeg + DEC_TK - 1) / DEC_TK : 0;
@@ -167,6 +168,12 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) decode_attn_kernel(const DecPa
       cp_async16(smem_u32(sV + soff), vg + goff, ok);
     }
   };
+  // fill the ring: one commit group per stage (empty groups keep the group count uniform)
+#pragma unroll
+  for (int sidx = 0; sidx < DEC_NST; ++sidx) {
+    if (sidx < ntiles) load_tile(sidx, sidx);
+    cp_async_commit();
+  }
 
   // Q fragments: rows 0..G-1 = the query heads of this kv group, rows >= G zero
   uint32_t qf[HD / 16][4];
@@ -185,24 +192,20 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) decode_attn_kernel(const DecPa
   for (int i = 0; i < HD / 8; ++i) { o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f; }
   float m_run = -INFINITY, l_run = 0.f;     // row g (rows g+8 are padding)
 
-  if (ntiles > 0) { load_tile(0, 0); }
-  cp_async_commit();
   for (int tile = 0; tile < ntiles; ++tile) {
-    const int stage = tile & 1;
-    if (tile + 1 < ntiles) load_tile(tile + 1, stage ^ 1);
-    cp_async_commit();
-    cp_async_wait<1>();
+    const int stage = tile % DEC_NST;
+    cp_async_wait<DEC_NST - 1>();           // the oldest outstanding group (= this tile) has landed
     __syncthreads();
-    const __half* tK = sK + stage * TILE_HALVES + warp * 32 * LDS;
-    const __half* tV = sV + stage * TILE_HALVES + warp * 32 * LDS;
-    // ---- S = Q K^T for this warp's 32 keys ----
-    float s[4][4];
+    const __half* tK = sK + stage * TILE_HALVES + warp * 16 * LDS;
+    const __half* tV = sV + stage * TILE_HALVES + warp * 16 * LDS;
+    // ---- S = Q K^T for this warp's 16 keys ----
+    float s[2][4];
 #pragma unroll
-    for (int nb = 0; nb < 4; ++nb) { s[nb][0] = s[nb][1] = s[nb][2] = s[nb][3] = 0.f; }
+    for (int nb = 0; nb < 2; ++nb) { s[nb][0] = s[nb][1] = s[nb][2] = s[nb][3] = 0.f; }
 #pragma unroll
     for (int kp = 0; kp < HD / 32; ++kp) {
 #pragma unroll
-      for (int nb = 0; nb < 4; ++nb) {
+      for (int nb = 0; nb < 2; ++nb) {
         uint32_t bf[4];
         const int r = nb * 8 + (lane & 7);
         const int c = kp * 32 + (lane >> 3) * 8;
@@ -212,10 +215,10 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) decode_attn_kernel(const DecPa
       }
     }
     // ---- mask + online softmax (row g only) ----
-    const int key0 = kbeg + tile * DEC_TK + warp * 32;
+    const int key0 = kbeg + tile * DEC_TK + warp * 16;
     float mx = -INFINITY;
 #pragma unroll
-    for (int nb = 0; nb < 4; ++nb) {
+    for (int nb = 0; nb < 2; ++nb) {
 #pragma unroll
       for (int e = 0; e < 2; ++e) {
         const int key = key0 + nb * 8 + 2 * t4 + e;
@@ -231,15 +234,15 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) decode_attn_kernel(const DecPa
     const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
     const float corr = exp2f(m_run - m_use);          // m_run = -inf -> 0
     float ls = 0.f;
-    uint32_t pf[2][4];
+    uint32_t pf[4];
 #pragma unroll
-    for (int nb = 0; nb < 4; ++nb) {
+    for (int nb = 0; nb < 2; ++nb) {
       const float p0 = exp2f(s[nb][0] - m_use);
       const float p1 = exp2f(s[nb][1] - m_use);
       ls += p0 + p1;
-      // C layout of S -> A layout of P: k-block kk2 = nb/2, regs {0,1} = cols 0-7, {2,3} = cols 8-15
-      pf[nb >> 1][(nb & 1) * 2] = f2_to_h2(p0, p1);
-      pf[nb >> 1][(nb & 1) * 2 + 1] = 0u;             // rows g+8: padding
+      // C layout of S -> A layout of P: regs {0,1} = key cols 0-7, {2,3} = cols 8-15
+      pf[nb * 2] = f2_to_h2(p0, p1);
+      pf[nb * 2 + 1] = 0u;                            // rows g+8: padding
     }
     ls += __shfl_xor_sync(0xffffffffu, ls, 1);
     ls += __shfl_xor_sync(0xffffffffu, ls, 2);
@@ -247,21 +250,20 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) decode_attn_kernel(const DecPa
     m_run = m_new;
 #pragma unroll
     for (int i = 0; i < HD / 8; ++i) { o[i][0] *= corr; o[i][1] *= corr; }
-    // ---- O += P V ----
+    // ---- O += P V (16 keys) ----
 #pragma unroll
-    for (int kk2 = 0; kk2 < 2; ++kk2) {
-#pragma unroll
-      for (int np = 0; np < HD / 16; ++np) {
-        uint32_t bf[4];
-        const int mat = lane >> 3;
-        const int r = kk2 * 16 + (mat & 1) * 8 + (lane & 7);
-        const int c = np * 16 + (mat >> 1) * 8;
-        ldsm_x4_t(bf, smem_u32(tV + r * LDS + c));
-        mma16816(o[2 * np], pf[kk2], bf[0], bf[1]);
-        mma16816(o[2 * np + 1], pf[kk2], bf[2], bf[3]);
-      }
+    for (int np = 0; np < HD / 16; ++np) {
+      uint32_t bf[4];
+      const int mat = lane >> 3;
+      const int r = (mat & 1) * 8 + (lane & 7);
+      const int c = np * 16 + (mat >> 1) * 8;
+      ldsm_x4_t(bf, smem_u32(tV + r * LDS + c));
+      mma16816(o[2 * np], pf, bf[0], bf[1]);
+      mma16816(o[2 * np + 1], pf, bf[2], bf[3]);
     }
     __syncthreads();   // all warps done with this stage before it is refilled
+    if (tile + DEC_NST < ntiles) load_tile(tile + DEC_NST, stage);
+    cp_async_commit();
   }
   cp_async_wait<0>();
   __syncthreads();
@@ -324,7 +326,7 @@ int decode_attn_splits(int B, int KV, int max_seqlen, int sms) {
   if (B <= 0 || KV <= 0) return 1;
   const int ctas = B * KV;
   int want = (2 * sms + ctas - 1) / ctas;
-  const int max_by_len = (max_seqlen + 2 * DEC_TK - 1) / (2 * DEC_TK);   // >= 256 keys per split
+  const int max_by_len = (max_seqlen + 255) / 256;   // >= 256 keys per split
   int s = want < max_by_len ? want : max_by_len;
   if (s < 1) s = 1;
   if (s > 64) s = 64;
@@ -347,7 +349,7 @@ static int sm_count_attn() {
 
 template <int HD>
 static int launch_decode(const DecParams& p, int B, cudaStream_t st) {
-  constexpr int SMEM = 2 * 2 * DEC_TK * (HD + 8) * 2;
+  constexpr int SMEM = DEC_NST * 2 * DEC_TK * (HD + 8) * 2;
   static bool attr_set = false;
   if (!attr_set) {
     if (cudaFuncSetAttribute(decode_attn_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM) != cudaSuccess)
@@ -635,8 +637,8 @@ int init_attn() {
     ok &= cudaFuncGetAttributes(&fa, decode_merge_kernel<64>) == cudaSuccess;
     if (!ok) return ERR_ARCH;
   }
-  if (cudaFuncSetAttribute(decode_attn_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 2 * DEC_TK * (128 + 8) * 2) != cudaSuccess) return ERR_ARCH;
-  if (cudaFuncSetAttribute(decode_attn_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 2 * DEC_TK * (64 + 8) * 2) != cudaSuccess) return ERR_ARCH;
+  if (cudaFuncSetAttribute(decode_attn_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_NST * 2 * DEC_TK * (128 + 8) * 2) != cudaSuccess) return ERR_ARCH;
+  if (cudaFuncSetAttribute(decode_attn_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_NST * 2 * DEC_TK * (64 + 8) * 2) != cudaSuccess) return ERR_ARCH;
   if (cudaFuncSetAttribute(prefill_attn_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 2 * PF_TK * (128 + 8) * 2) != cudaSuccess) return ERR_ARCH;
   if (cudaFuncSetAttribute(prefill_attn_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 2 * PF_TK * (64 + 8) * 2) != cudaSuccess) return ERR_ARCH;
   return OK;

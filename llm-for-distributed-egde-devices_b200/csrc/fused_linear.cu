@@ -1,0 +1,605 @@
+// Decode-time fused linear (M <= 8 tokens):   [norm | smoothing | act-requant] -> per-token int8
+// quantise -> W8A8 weight-streaming GEMV -> dequantising epilogue [-> act(gate)*up],  ONE kernel.
+//
+// Why: at M = 1 a 7B decoder layer streams 202 MB of weights in ~31 us at HBM speed, but the unfused
+// chain was 11 launches per layer, each with microseconds of launch + dependent-load latency.  Here
+// every CTA redoes the (tiny, L2-resident) activation prologue itself, so the quantised activation
+// never round-trips through HBM and four launches per layer disappear.  The kernel is launched with
+// programmatic dependent launch: it prefetches its first weight tiles BEFORE waiting on the
+// predecessor (weights never depend on it), so the launch/ramp latency hides under the previous
+// kernel's tail.
+//
+// Numerics are those of the unfused entry points, operation for operation (oracle/w8a8.py:
+// norm_quant / smooth_quant / act_mul_y + quant_rows, gemm_w8a8): results are bit-identical to
+// b2_norm_quant + b2_gemm_w8a8 etc.  (tests/test_kernels_gpu.py::test_fused_linear_*).
+//
+// Reference call sites replaced: the same as b2_norm_quant / b2_gemm_w8a8 / b2_act_mul_quant
+// (Code/Quantised Models/models_quant_updated.py:30-38, :84-93 decode loop).
+#include "common.cuh"
+
+namespace b2 {
+
+enum : int { X_RMS = 0, X_LN = 1, X_PLAIN = 2, X_Y32 = 3 };
+enum : int { O_F16 = 0, O_GATED = 1, O_QKV = 2 };
+
+struct FusedParams {
+  const void* x; long long x_ld;                 // fp16 (X_RMS/X_LN/X_PLAIN) or fp32 (X_Y32) [M, x_ld]
+  const __half* gamma; const __half* beta;       // norm parameters
+  const float* smooth;                           // [K] multiplier or nullptr
+  const float* x_amax;                           // X_Y32: row absmax [M] produced by the O_GATED kernel
+  float eps;
+  const int8_t* W; const float* w_scale; const __half* bias; const __half* residual;
+  void* out;                                     // O_F16: fp16 [M,N];  O_GATED: fp32 y [M,N/2]
+  const float* out_smooth;                       // O_GATED: [N/2] multiplier of the NEXT linear, or nullptr
+  float* out_amax;                               // O_GATED: [M] running absmax (atomicMax; caller zeroes)
+  float* zero_amax;                              // housekeeping: [M] floats this launch sets to 0, or nullptr
+  int M, N, K, act;
+  // O_QKV: rotary embedding + KV-cache append in the epilogue (q written rotated to `out`)
+  const float* cosT; const float* sinT; const int* positions; const int* seq_ids; int seq0;
+  __half* kcache; __half* vcache; int H, KV, hd, Smax, use_rope;
+};
+
+constexpr int FL_THREADS = 256, FL_WARPS = 8, FL_ROWS = 2, FL_UNR = 4;
+constexpr int FL_SMEM_FULL = 200 * 1024;
+
+B2_DEVINL void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+B2_DEVINL void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+B2_DEVINL void fl_cp_async16(void* smem_dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(src) : "memory");
+}
+B2_DEVINL double fl_block_sum_d(double v, double* sh) {
+  v = warp_sum_d(v);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+  __syncthreads();
+  double t = 0.0;
+#pragma unroll
+  for (int i = 0; i < FL_WARPS; ++i) t += sh[i];
+  return t;
+}
+B2_DEVINL float fl_block_max(float v, float* sh) {
+  v = warp_max(v);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float t = 0.0f;
+#pragma unroll
+  for (int i = 0; i < FL_WARPS; ++i) t = fmaxf(t, sh[i]);
+  return t;
+}
+
+// y[0..7] of 8-element chunk `ch` of one row, in the pinned operation order.
+template <int XK>
+B2_DEVINL void fl_load_y(const FusedParams& p, const void* xrow, int ch, float r, float mean, float (&y)[8]) {
+  if (XK == X_Y32) {
+    const float4 a = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(xrow) + ch * 8);
+    const float4 b = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(xrow) + ch * 8 + 4);
+    y[0] = a.x; y[1] = a.y; y[2] = a.z; y[3] = a.w; y[4] = b.x; y[5] = b.y; y[6] = b.z; y[7] = b.w;
+    return;                                       // smoothing was applied by the producer
+  }
+  const uint4 u = ld_v4(reinterpret_cast<const __half*>(xrow) + ch * 8);
+  const float2 a0 = h2_to_f2(u.x), a1 = h2_to_f2(u.y), a2 = h2_to_f2(u.z), a3 = h2_to_f2(u.w);
+  y[0] = a0.x; y[1] = a0.y; y[2] = a1.x; y[3] = a1.y; y[4] = a2.x; y[5] = a2.y; y[6] = a3.x; y[7] = a3.y;
+  if (XK == X_RMS || XK == X_LN) {
+    const uint4 g = ld_v4(p.gamma + ch * 8);
+    const float2 g0 = h2_to_f2(g.x), g1 = h2_to_f2(g.y), g2 = h2_to_f2(g.z), g3 = h2_to_f2(g.w);
+    const float gg[8] = {g0.x, g0.y, g1.x, g1.y, g2.x, g2.y, g3.x, g3.y};
+    float bb[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (XK == X_LN) {
+      const uint4 b = ld_v4(p.beta + ch * 8);
+      const float2 b0 = h2_to_f2(b.x), b1 = h2_to_f2(b.y), b2_ = h2_to_f2(b.z), b3 = h2_to_f2(b.w);
+      bb[0] = b0.x; bb[1] = b0.y; bb[2] = b1.x; bb[3] = b1.y; bb[4] = b2_.x; bb[5] = b2_.y; bb[6] = b3.x; bb[7] = b3.y;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float t = y[j];
+      if (XK == X_LN) t = sub_rn(t, mean);
+      t = mul_rn(mul_rn(t, r), gg[j]);
+      if (XK == X_LN) t = add_rn(t, bb[j]);
+      y[j] = t;
+    }
+  }
+  if (p.smooth != nullptr) {
+    const float4 sA = *reinterpret_cast<const float4*>(p.smooth + ch * 8);
+    const float4 sB = *reinterpret_cast<const float4*>(p.smooth + ch * 8 + 4);
+    y[0] = mul_rn(y[0], sA.x); y[1] = mul_rn(y[1], sA.y); y[2] = mul_rn(y[2], sA.z); y[3] = mul_rn(y[3], sA.w);
+    y[4] = mul_rn(y[4], sB.x); y[5] = mul_rn(y[5], sB.y); y[6] = mul_rn(y[6], sB.z); y[7] = mul_rn(y[7], sB.w);
+  }
+}
+
+template <int MT, int XK, int OKIND>
+__global__ void __launch_bounds__(FL_THREADS, 2) fused_gemv_kernel(const FusedParams p) {
+  extern __shared__ __align__(16) uint8_t xs[];        // int8 activations [MT][K]
+  __shared__ double shd[FL_WARPS];
+  __shared__ float shf[FL_WARPS];
+  __shared__ float s_scale[MT];
+  const int K = p.K, kvec = K >> 4, nchunk = K >> 3;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int F = p.N >> 1;
+  constexpr int STEP = FL_UNR * 32;                    // 16-byte vectors per row per batch
+  const int NB = (kvec + STEP - 1) / STEP;             // batches per work item
+  // A work item = the two weight rows one warp reduces together: two adjacent output columns
+  // (O_F16), the gate/up rows of one MLP column (O_GATED), or a rotary pair i, i+hd/2 (O_QKV).
+  const int items_total = (OKIND == O_F16) ? (p.N + 1) / 2 : F;
+  const int stride = gridDim.x * FL_WARPS;
+  const int half_hd = (OKIND == O_QKV) ? (p.hd >> 1) : 1;
+  struct Cur { int it, j; const int8_t* r0; const int8_t* r1; };
+  auto set_rows = [&](Cur& c) {
+    int n0, n1;
+    if (OKIND == O_GATED) { n0 = c.it; n1 = F + c.it; }
+    else if (OKIND == O_QKV) { const int hq = c.it / half_hd; n0 = hq * p.hd + (c.it - hq * half_hd); n1 = n0 + half_hd; }
+    else { n0 = 2 * c.it; n1 = min(n0 + 1, p.N - 1); }
+    c.r0 = p.W + (long long)n0 * K;
+    c.r1 = p.W + (long long)n1 * K;
+  };
+  auto advance = [&](Cur& c) {
+    if (++c.j == NB) { c.j = 0; c.it += stride; if (c.it < items_total) set_rows(c); }
+  };
+  auto load_batch = [&](uint4 (&dst)[FL_UNR][FL_ROWS], const Cur& c) {
+    if (c.it < items_total) {
+#pragma unroll
+      for (int u = 0; u < FL_UNR; ++u) {
+        const int idx = lane + c.j * STEP + u * 32;
+        const bool ok = idx < kvec;
+        dst[u][0] = ok ? ld_nc_v4(c.r0 + idx * 16) : make_uint4(0, 0, 0, 0);
+        dst[u][1] = ok ? ld_nc_v4(c.r1 + idx * 16) : make_uint4(0, 0, 0, 0);
+      }
+    }
+  };
+  // ---- 1. first two weight batches: independent of the predecessor kernel ----------------------
+  pdl_launch_dependents();
+  uint4 w[FL_UNR][FL_ROWS], w2[FL_UNR][FL_ROWS];
+  Cur cc;
+  cc.it = blockIdx.x * FL_WARPS + warp; cc.j = 0; cc.r0 = p.W; cc.r1 = p.W;
+  if (cc.it < items_total) set_rows(cc);
+  Cur lc = cc;
+  load_batch(w, lc); advance(lc);
+  load_batch(w2, lc); advance(lc);
+  // Norm gains / smoothing multipliers are weights too: stage them in shared memory with cp.async
+  // before the dependency wait, so the prologue's critical path is one L2 read of x plus two block
+  // reductions (fast path: rows of up to FP_MAXC*256*8 = 6144 elements held in registers).
+  constexpr int FP_MAXC = 3;
+  const bool fast = (XK != X_Y32) && (nchunk <= FP_MAXC * FL_THREADS);
+  uint8_t* aux = xs + (((size_t)MT * K + 127) & ~size_t(127));
+  __half* sg = reinterpret_cast<__half*>(aux);                         // gamma [K]
+  __half* sb = sg + K;                                                 // beta  [K]
+  float* ssm = reinterpret_cast<float*>(aux + (size_t)4 * K);          // smooth [K]
+  if (fast) {
+    if (XK == X_RMS || XK == X_LN)
+      for (int i = threadIdx.x; i < nchunk; i += FL_THREADS) fl_cp_async16(sg + i * 8, p.gamma + i * 8);
+    if (XK == X_LN)
+      for (int i = threadIdx.x; i < nchunk; i += FL_THREADS) fl_cp_async16(sb + i * 8, p.beta + i * 8);
+    if (p.smooth != nullptr)
+      for (int i = threadIdx.x; i < 2 * nchunk; i += FL_THREADS) fl_cp_async16(ssm + i * 4, p.smooth + i * 4);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  }
+  // ---- 2. everything below may read the predecessor's output ---------------------------------
+  pdl_wait();
+  if (p.zero_amax != nullptr && blockIdx.x == 0 && threadIdx.x < p.M) p.zero_amax[threadIdx.x] = 0.0f;
+  if (fast) {
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+  }
+  // ---- 3. activation prologue: quantise the M rows into shared memory ------------------------
+#pragma unroll 1
+  for (int m = 0; m < MT; ++m) {
+    uint2* qrow = reinterpret_cast<uint2*>(xs + (size_t)m * K);
+    if (m >= p.M) {
+      for (int ch = threadIdx.x; ch < nchunk; ch += FL_THREADS) qrow[ch] = make_uint2(0, 0);
+      continue;
+    }
+    const void* xrow = (XK == X_Y32)
+        ? static_cast<const void*>(reinterpret_cast<const float*>(p.x) + (long long)m * p.x_ld)
+        : static_cast<const void*>(reinterpret_cast<const __half*>(p.x) + (long long)m * p.x_ld);
+    float r = 0.f, mean = 0.f, amax = 0.f;
+    if (fast) {
+      // single pass: the row lives in registers between moments, absmax and quantise
+      float v[FP_MAXC][8];
+      double s1 = 0.0, s2 = 0.0;
+#pragma unroll
+      for (int c = 0; c < FP_MAXC; ++c) {
+        const int ch = threadIdx.x + c * FL_THREADS;
+        if (ch < nchunk) {
+          const uint4 u = ld_v4(reinterpret_cast<const __half*>(xrow) + ch * 8);
+          const float2 a0 = h2_to_f2(u.x), a1 = h2_to_f2(u.y), a2 = h2_to_f2(u.z), a3 = h2_to_f2(u.w);
+          v[c][0] = a0.x; v[c][1] = a0.y; v[c][2] = a1.x; v[c][3] = a1.y;
+          v[c][4] = a2.x; v[c][5] = a2.y; v[c][6] = a3.x; v[c][7] = a3.y;
+          if (XK == X_RMS || XK == X_LN) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const double dd = (double)v[c][j];
+              s2 += dd * dd;
+              if (XK == X_LN) s1 += dd;
+            }
+          }
+        }
+      }
+      if (XK == X_RMS || XK == X_LN) {
+        const double ss = fl_block_sum_d(s2, shd);
+        float var;
+        if (XK == X_LN) {
+          const double sm = fl_block_sum_d(s1, shd);
+          const double md = sm / (double)K;
+          double vd = ss / (double)K - md * md;
+          vd = vd > 0.0 ? vd : 0.0;
+          mean = (float)md; var = (float)vd;
+        } else {
+          var = (float)(ss / (double)K);
+        }
+        r = div_rn(1.0f, __fsqrt_rn(add_rn(var, p.eps)));
+      }
+#pragma unroll
+      for (int c = 0; c < FP_MAXC; ++c) {
+        const int ch = threadIdx.x + c * FL_THREADS;
+        if (ch < nchunk) {
+          float gg[8], bb[8], sv[8];
+          if (XK == X_RMS || XK == X_LN) {
+            const uint4 g = *reinterpret_cast<const uint4*>(sg + ch * 8);
+            const float2 g0 = h2_to_f2(g.x), g1 = h2_to_f2(g.y), g2 = h2_to_f2(g.z), g3 = h2_to_f2(g.w);
+            gg[0] = g0.x; gg[1] = g0.y; gg[2] = g1.x; gg[3] = g1.y; gg[4] = g2.x; gg[5] = g2.y; gg[6] = g3.x; gg[7] = g3.y;
+          }
+          if (XK == X_LN) {
+            const uint4 g = *reinterpret_cast<const uint4*>(sb + ch * 8);
+            const float2 g0 = h2_to_f2(g.x), g1 = h2_to_f2(g.y), g2 = h2_to_f2(g.z), g3 = h2_to_f2(g.w);
+            bb[0] = g0.x; bb[1] = g0.y; bb[2] = g1.x; bb[3] = g1.y; bb[4] = g2.x; bb[5] = g2.y; bb[6] = g3.x; bb[7] = g3.y;
+          }
+          if (p.smooth != nullptr) {
+            const float4 sA = *reinterpret_cast<const float4*>(ssm + ch * 8);
+            const float4 sB = *reinterpret_cast<const float4*>(ssm + ch * 8 + 4);
+            sv[0] = sA.x; sv[1] = sA.y; sv[2] = sA.z; sv[3] = sA.w; sv[4] = sB.x; sv[5] = sB.y; sv[6] = sB.z; sv[7] = sB.w;
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            float t = v[c][j];
+            if (XK == X_RMS || XK == X_LN) {
+              if (XK == X_LN) t = sub_rn(t, mean);
+              t = mul_rn(mul_rn(t, r), gg[j]);
+              if (XK == X_LN) t = add_rn(t, bb[j]);
+            }
+            if (p.smooth != nullptr) t = mul_rn(t, sv[j]);
+            v[c][j] = t;
+            amax = fmaxf(amax, fabsf(t));
+          }
+        }
+      }
+      amax = fl_block_max(amax, shf);
+      const bool nzf = amax > 0.0f;
+      const float invf = nzf ? div_rn(127.0f, amax) : 0.0f;
+      if (threadIdx.x == 0) s_scale[m] = nzf ? div_rn(amax, 127.0f) : 0.0f;
+#pragma unroll
+      for (int c = 0; c < FP_MAXC; ++c) {
+        const int ch = threadIdx.x + c * FL_THREADS;
+        if (ch < nchunk) {
+          uint2 o;
+          o.x = pack4(quant1(v[c][0], invf), quant1(v[c][1], invf), quant1(v[c][2], invf), quant1(v[c][3], invf));
+          o.y = pack4(quant1(v[c][4], invf), quant1(v[c][5], invf), quant1(v[c][6], invf), quant1(v[c][7], invf));
+          qrow[ch] = o;
+        }
+      }
+      continue;
+    }
+    if (XK == X_RMS || XK == X_LN) {
+      double s1 = 0.0, s2 = 0.0;
+      for (int ch = threadIdx.x; ch < nchunk; ch += FL_THREADS) {
+        const uint4 u = ld_v4(reinterpret_cast<const __half*>(xrow) + ch * 8);
+        const uint32_t* pu = &u.x;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 f = h2_to_f2(pu[e]);
+          const double d0 = (double)f.x, d1 = (double)f.y;
+          s2 += d0 * d0; s2 += d1 * d1;
+          if (XK == X_LN) { s1 += d0; s1 += d1; }
+        }
+      }
+      const double ss = fl_block_sum_d(s2, shd);
+      float var;
+      if (XK == X_LN) {
+        const double sm = fl_block_sum_d(s1, shd);
+        const double md = sm / (double)K;
+        double vd = ss / (double)K - md * md;
+        vd = vd > 0.0 ? vd : 0.0;
+        mean = (float)md; var = (float)vd;
+      } else {
+        var = (float)(ss / (double)K);
+      }
+      r = div_rn(1.0f, __fsqrt_rn(add_rn(var, p.eps)));
+    }
+    if (XK == X_Y32) {
+      amax = p.x_amax[m];
+    } else {
+      for (int ch = threadIdx.x; ch < nchunk; ch += FL_THREADS) {
+        float y[8];
+        fl_load_y<XK>(p, xrow, ch, r, mean, y);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) amax = fmaxf(amax, fabsf(y[j]));
+      }
+      amax = fl_block_max(amax, shf);
+    }
+    const bool nz = amax > 0.0f;
+    const float inv = nz ? div_rn(127.0f, amax) : 0.0f;
+    if (threadIdx.x == 0) s_scale[m] = nz ? div_rn(amax, 127.0f) : 0.0f;
+    for (int ch = threadIdx.x; ch < nchunk; ch += FL_THREADS) {
+      float y[8];
+      fl_load_y<XK>(p, xrow, ch, r, mean, y);
+      uint2 o;
+      o.x = pack4(quant1(y[0], inv), quant1(y[1], inv), quant1(y[2], inv), quant1(y[3], inv));
+      o.y = pack4(quant1(y[4], inv), quant1(y[5], inv), quant1(y[6], inv), quant1(y[7], inv));
+      qrow[ch] = o;
+    }
+  }
+  __syncthreads();
+  // ---- 4. persistent weight stream: two batches always in flight per lane ----------------------
+  int acc[FL_ROWS][MT];
+#pragma unroll
+  for (int r = 0; r < FL_ROWS; ++r)
+#pragma unroll
+    for (int m = 0; m < MT; ++m) acc[r][m] = 0;
+  auto consume = [&](const uint4 (&src)[FL_UNR][FL_ROWS], int j) {
+#pragma unroll
+    for (int u = 0; u < FL_UNR; ++u) {
+      const int idx = lane + j * STEP + u * 32;
+      if (idx < kvec) {
+#pragma unroll
+        for (int m = 0; m < MT; ++m) {
+          const uint4 x = reinterpret_cast<const uint4*>(xs)[m * kvec + idx];
+#pragma unroll
+          for (int r = 0; r < FL_ROWS; ++r) {
+            int a = acc[r][m];
+            a = __dp4a((int)src[u][r].x, (int)x.x, a);
+            a = __dp4a((int)src[u][r].y, (int)x.y, a);
+            a = __dp4a((int)src[u][r].z, (int)x.z, a);
+            a = __dp4a((int)src[u][r].w, (int)x.w, a);
+            acc[r][m] = a;
+          }
+        }
+      }
+    }
+  };
+  // Deferred, lane-parallel epilogue: a finished item's reduced sums are parked in lane
+  // (item count mod 32); when 32 are parked (or at the end) every lane finishes its own item, so the
+  // dependent scalar loads, the SiLU and the stores of up to 32 items overlap instead of serialising
+  // in one lane while the weight stream waits.
+  int res[FL_ROWS][MT];
+  int res_it = -1, parked = 0;
+  auto epilogue_lane = [&](int it) {
+    if (OKIND == O_F16) {
+      __half* out = reinterpret_cast<__half*>(p.out);
+#pragma unroll
+      for (int r = 0; r < FL_ROWS; ++r) {
+        const int n = 2 * it + r;
+        if (n < p.N) {
+          const float ws = p.w_scale[n];
+          const float bv = p.bias ? __half2float(p.bias[n]) : 0.f;
+#pragma unroll
+          for (int m = 0; m < MT; ++m) {
+            if (m < p.M) {
+              const long long off = (long long)m * p.N + n;
+              float v = mul_rn(mul_rn((float)res[r][m], s_scale[m]), ws);
+              if (p.bias) v = add_rn(v, bv);
+              if (p.residual) v = add_rn(v, __half2float(p.residual[off]));
+              out[off] = __float2half_rn(v);
+            }
+          }
+        }
+      }
+    } else if (OKIND == O_QKV) {
+      __half* out = reinterpret_cast<__half*>(p.out);
+      const int q_head = it / half_hd, q_i = it - q_head * half_hd;
+      const int n0 = q_head * p.hd + q_i, n1 = n0 + half_hd;
+      const float ws0 = p.w_scale[n0], ws1 = p.w_scale[n1];
+      const float b0 = p.bias ? __half2float(p.bias[n0]) : 0.f, b1 = p.bias ? __half2float(p.bias[n1]) : 0.f;
+#pragma unroll
+      for (int m = 0; m < MT; ++m) {
+        if (m < p.M) {
+          float v0 = mul_rn(mul_rn((float)res[0][m], s_scale[m]), ws0);
+          float v1 = mul_rn(mul_rn((float)res[1][m], s_scale[m]), ws1);
+          if (p.bias) { v0 = add_rn(v0, b0); v1 = add_rn(v1, b1); }
+          __half h0 = __float2half_rn(v0), h1 = __float2half_rn(v1);     // the fp16 qkv of the unfused path
+          const int pos = p.positions[m];
+          if (q_head < p.H + p.KV && p.use_rope) {
+            const float x1 = __half2float(h0), x2 = __half2float(h1);
+            const float c = p.cosT[(long long)pos * half_hd + q_i], sn = p.sinT[(long long)pos * half_hd + q_i];
+            h0 = __float2half_rn(sub_rn(mul_rn(x1, c), mul_rn(x2, sn)));
+            h1 = __float2half_rn(add_rn(mul_rn(x2, c), mul_rn(x1, sn)));
+          }
+          if (q_head < p.H) {
+            out[(long long)m * p.N + n0] = h0;
+            out[(long long)m * p.N + n1] = h1;
+          } else {
+            const bool isk = q_head < p.H + p.KV;
+            const int kvh = isk ? q_head - p.H : q_head - p.H - p.KV;
+            const int row = p.seq_ids ? p.seq_ids[m] : p.seq0;
+            __half* dst = (isk ? p.kcache : p.vcache) + (((long long)row * p.KV + kvh) * p.Smax + pos) * p.hd;
+            dst[q_i] = h0;
+            dst[q_i + half_hd] = h1;
+          }
+        }
+      }
+    } else {
+      float* out = reinterpret_cast<float*>(p.out);
+      const float wsg = p.w_scale[it], wsu = p.w_scale[F + it];
+      const float bg = p.bias ? __half2float(p.bias[it]) : 0.f, bu = p.bias ? __half2float(p.bias[F + it]) : 0.f;
+      const float osm = p.out_smooth ? p.out_smooth[it] : 1.0f;
+#pragma unroll
+      for (int m = 0; m < MT; ++m) {
+        if (m < p.M) {
+          float vg = mul_rn(mul_rn((float)res[0][m], s_scale[m]), wsg);
+          float vu = mul_rn(mul_rn((float)res[1][m], s_scale[m]), wsu);
+          if (p.bias) { vg = add_rn(vg, bg); vu = add_rn(vu, bu); }
+          const float g = __half2float(__float2half_rn(vg));      // the fp16 rounding of the unfused path
+          const float uu = __half2float(__float2half_rn(vu));
+          const float a = (p.act == 0) ? silu_det(g) : gelu_new_det(g);
+          float y = mul_rn(a, uu);
+          if (p.out_smooth) y = mul_rn(y, osm);
+          out[(long long)m * F + it] = y;
+          atomicMax(reinterpret_cast<int*>(p.out_amax + m), __float_as_int(fabsf(y)));   // |y| >= 0: int order == float order
+        }
+      }
+    }
+  };
+  auto flush = [&]() {
+    if (res_it >= 0) epilogue_lane(res_it);
+    res_it = -1;
+    parked = 0;
+  };
+  auto finish_item = [&](int it) {
+#pragma unroll
+    for (int r = 0; r < FL_ROWS; ++r)
+#pragma unroll
+      for (int m = 0; m < MT; ++m) {
+        const int v = warp_sum_i(acc[r][m]);
+        if (lane == parked) res[r][m] = v;
+        acc[r][m] = 0;
+      }
+    if (lane == parked) res_it = it;
+    if (++parked == 32) flush();
+  };
+  // one step: reduce the batch under the compute cursor, immediately re-arm its registers with the
+  // batch two ahead (the load cursor), then close the item if that was its last batch
+  auto step = [&](uint4 (&buf)[FL_UNR][FL_ROWS]) {
+    consume(buf, cc.j);
+    load_batch(buf, lc);
+    advance(lc);
+    const int it = cc.it;
+    const bool last = cc.j == NB - 1;
+    advance(cc);
+    if (last) finish_item(it);
+  };
+  while (cc.it < items_total) {
+    step(w);
+    if (cc.it >= items_total) break;
+    step(w2);
+  }
+  flush();
+}
+
+static int fl_sm_count() {
+  static int n = []() {
+    int dev = 0, v = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
+    return v > 0 ? v : 148;
+  }();
+  return n;
+}
+
+template <int MT, int XK, int OKIND>
+static int launch_fused(const FusedParams& pin, cudaStream_t st) {
+  size_t smem = ((size_t)MT * pin.K + 127) & ~size_t(127);
+  if (XK != X_Y32 && (pin.K >> 3) <= 3 * FL_THREADS) smem += (size_t)8 * pin.K;   // gamma, beta (fp16) + smooth (fp32) staging
+  if (smem > (size_t)FL_SMEM_FULL) return ERR_TOO_LARGE;
+  const FusedParams& p = pin;
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(fused_gemv_kernel<MT, XK, OKIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, FL_SMEM_FULL) != cudaSuccess)
+      return ERR_ARCH;
+    attr_set = true;
+  }
+  const int items = (OKIND == O_F16) ? (p.N + 1) / 2 : p.N / 2;
+  int grid = (items + FL_WARPS - 1) / FL_WARPS;
+  const int cap = fl_sm_count() * 2;                   // persistent: 2 CTAs per SM, prologue once per CTA
+  if (grid > cap) grid = cap;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(FL_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  if (cudaLaunchKernelEx(&cfg, fused_gemv_kernel<MT, XK, OKIND>, p) != cudaSuccess) {
+    cudaGetLastError();
+    return ERR_LAUNCH;
+  }
+  return OK;
+}
+
+template <int XK, int OKIND>
+static int dispatch_m(const FusedParams& p, cudaStream_t st) {
+  if (p.M == 1) return launch_fused<1, XK, OKIND>(p, st);
+  if (p.M == 2) return launch_fused<2, XK, OKIND>(p, st);
+  if (p.M <= 4) return launch_fused<4, XK, OKIND>(p, st);
+  return launch_fused<8, XK, OKIND>(p, st);
+}
+template <int OKIND>
+static int dispatch_x(int xk, const FusedParams& p, cudaStream_t st) {
+  switch (xk) {
+    case X_RMS: return dispatch_m<X_RMS, OKIND>(p, st);
+    case X_LN: return dispatch_m<X_LN, OKIND>(p, st);
+    case X_PLAIN: return dispatch_m<X_PLAIN, OKIND>(p, st);
+    case X_Y32: return dispatch_m<X_Y32, OKIND>(p, st);
+    default: return ERR_UNSUPPORTED;
+  }
+}
+
+int fused_linear(const void* x, long long x_ld, int x_kind, const void* gamma, const void* beta, const float* smooth,
+                 const float* x_amax, float eps, const int8_t* W, const float* w_scale, const void* bias,
+                 const void* residual, void* out, int out_kind, int act, const float* out_smooth, float* out_amax,
+                 float* zero_amax, int M, int N, int K, cudaStream_t st) {
+  if (M == 0 || N == 0) return OK;
+  if (!x || !W || !w_scale || !out) return ERR_NULL_PTR;
+  if (M < 0 || M > 8) return ERR_UNSUPPORTED;
+  if (N < 0 || K <= 0 || (K & 15) || (x_ld & 7)) return ERR_BAD_SHAPE;
+  if ((x_kind == X_RMS || x_kind == X_LN) && !gamma) return ERR_NULL_PTR;
+  if (x_kind == X_LN && !beta) return ERR_NULL_PTR;
+  if (x_kind == X_Y32 && !x_amax) return ERR_NULL_PTR;
+  if (out_kind == O_GATED && ((N & 1) || !out_amax || residual)) return ERR_BAD_SHAPE;
+  auto mis = [](const void* q) { return q && (reinterpret_cast<uintptr_t>(q) & 15); };
+  if (mis(x) || mis(W) || mis(gamma) || mis(beta) || mis(smooth)) return ERR_BAD_ALIGN;
+  FusedParams p = {};
+  p.x = x; p.x_ld = x_ld; p.gamma = (const __half*)gamma; p.beta = (const __half*)beta; p.smooth = smooth;
+  p.x_amax = x_amax; p.eps = eps; p.W = W; p.w_scale = w_scale; p.bias = (const __half*)bias;
+  p.residual = (const __half*)residual; p.out = out; p.out_smooth = out_smooth; p.out_amax = out_amax;
+  p.zero_amax = zero_amax; p.M = M; p.N = N; p.K = K; p.act = act;
+  if (out_kind == O_F16) return dispatch_x<O_F16>(x_kind, p, st);
+  if (out_kind == O_GATED) return dispatch_x<O_GATED>(x_kind, p, st);
+  return ERR_UNSUPPORTED;
+}
+
+// qkv projection with fused rotary embedding + KV append (decode, M <= 8)
+int fused_qkv(const void* x, long long x_ld, int x_kind, const void* gamma, const void* beta, const float* smooth,
+              float eps, const int8_t* W, const float* w_scale, const void* bias, void* qkv_out, const float* cosT,
+              const float* sinT, const int* positions, const int* seq_ids, int seq0, void* kcache, void* vcache, int M,
+              int H, int KV, int hd, int Smax, int K, int use_rope, cudaStream_t st) {
+  if (M == 0) return OK;
+  if (!x || !W || !w_scale || !qkv_out || !positions || !kcache || !vcache) return ERR_NULL_PTR;
+  if (use_rope && (!cosT || !sinT)) return ERR_NULL_PTR;
+  if (M < 0 || M > 8) return ERR_UNSUPPORTED;
+  if (x_kind != X_RMS && x_kind != X_LN && x_kind != X_PLAIN) return ERR_UNSUPPORTED;
+  if (H <= 0 || KV <= 0 || hd <= 0 || (hd & 1) || K <= 0 || (K & 15) || (x_ld & 7)) return ERR_BAD_SHAPE;
+  if ((x_kind == X_RMS || x_kind == X_LN) && !gamma) return ERR_NULL_PTR;
+  if (x_kind == X_LN && !beta) return ERR_NULL_PTR;
+  auto mis = [](const void* q) { return q && (reinterpret_cast<uintptr_t>(q) & 15); };
+  if (mis(x) || mis(W) || mis(gamma) || mis(beta) || mis(smooth)) return ERR_BAD_ALIGN;
+  FusedParams p = {};
+  p.x = x; p.x_ld = x_ld; p.gamma = (const __half*)gamma; p.beta = (const __half*)beta; p.smooth = smooth;
+  p.eps = eps; p.W = W; p.w_scale = w_scale; p.bias = (const __half*)bias; p.out = qkv_out;
+  p.M = M; p.N = (H + 2 * KV) * hd; p.K = K;
+  p.cosT = cosT; p.sinT = sinT; p.positions = positions; p.seq_ids = seq_ids; p.seq0 = seq0;
+  p.kcache = (__half*)kcache; p.vcache = (__half*)vcache; p.H = H; p.KV = KV; p.hd = hd; p.Smax = Smax;
+  p.use_rope = use_rope;
+  switch (x_kind) {
+    case X_RMS: return dispatch_m<X_RMS, O_QKV>(p, st);
+    case X_LN: return dispatch_m<X_LN, O_QKV>(p, st);
+    default: return dispatch_m<X_PLAIN, O_QKV>(p, st);
+  }
+}
+
+template <int MT>
+static bool fl_touch_m() {
+  cudaFuncAttributes fa;
+  bool ok = true;
+#define B2_T(XK, OKIND) ok &= cudaFuncGetAttributes(&fa, fused_gemv_kernel<MT, XK, OKIND>) == cudaSuccess && \
+    cudaFuncSetAttribute(fused_gemv_kernel<MT, XK, OKIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, FL_SMEM_FULL) == cudaSuccess;
+  B2_T(X_RMS, O_F16) B2_T(X_LN, O_F16) B2_T(X_PLAIN, O_F16) B2_T(X_Y32, O_F16)
+  B2_T(X_RMS, O_GATED) B2_T(X_LN, O_GATED) B2_T(X_PLAIN, O_GATED) B2_T(X_Y32, O_GATED)
+  B2_T(X_RMS, O_QKV) B2_T(X_LN, O_QKV) B2_T(X_PLAIN, O_QKV)
+#undef B2_T
+  return ok;
+}
+int init_fused() { fl_sm_count(); return (fl_touch_m<1>() && fl_touch_m<2>() && fl_touch_m<4>() && fl_touch_m<8>()) ? OK : ERR_ARCH; }
+
+}  // namespace b2

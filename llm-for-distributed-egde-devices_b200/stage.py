@@ -68,6 +68,9 @@ class _Scratch:
         self.lens = torch.empty((cap,), dtype=torch.int32, device=device)
         self.ids = torch.empty((cap,), dtype=torch.int64, device=device)
         self.hn = torch.empty((cap, d), dtype=f16, device=device) if last else None
+        # fused decode path (T <= 8): act(gate)*up in fp32 and its running row absmax
+        self.y32 = torch.empty((8, F), dtype=f32, device=device)
+        self.amax = torch.zeros((8,), dtype=f32, device=device)
 
     def q8view(self, T, K):
         return self.q8[: T * K].view(T, K)
@@ -91,6 +94,7 @@ class Stage:
         self._ws = None
         self._runners = {}
         self.launches = 0          # kernels of ours launched (bench.py's gpu_launches claim)
+        self.fuse_decode = True    # decode steps with <= 8 tokens use b2_fused_linear
 
     # ------------------------------------------------------------------------------------------
     @classmethod
@@ -152,8 +156,36 @@ class Stage:
         sc = buf.scale[:T]
         act = (ops.ACT_SILU_MUL if cfg.act == "silu" else ops.ACT_GELU_MUL) if cfg.gated else \
               (ops.ACT_GELU if cfg.act == "gelu_new" else ops.ACT_SILU)
+        fused = self.fuse_decode and decode and T <= 8 and trace is None
+        xk_norm = ops.X_LN if cfg.norm == "layernorm" else ops.X_RMS
         for li, lw in enumerate(self.w["layers"]):
             kc, vc = kv_cache.k[li], kv_cache.v[li]
+            if fused:
+                # 6-7 launches per layer: every linear redoes its (tiny) activation prologue in-kernel
+                ops.fused_qkv(h, lw["wqkv"], lw["s_qkv"], qkv, self.cos, self.sin, dpos, kc, vc, H, KV, hd,
+                              x_kind=xk_norm, gamma=lw["ln1_g"], beta=lw.get("ln1_b"), smooth=lw["sm_qkv"],
+                              eps=cfg.eps, bias=lw.get("b_qkv"), seq_ids=dseq, seq0=row0, use_rope=cfg.rope)
+                ops.decode_attn(qkv, kc, vc, dlens, H, KV, hd, max_len, self.scale, cfg.window, rows=dseq, out=attn,
+                                workspace=ws)
+                ops.fused_linear(attn, lw["wo"], lw["s_o"], x_kind=ops.X_PLAIN, smooth=lw["sm_o"], bias=lw.get("b_o"),
+                                 residual=h, out=h_alt, zero_amax=buf.amax)
+                n += 3 if ws is None else 4
+                if cfg.gated:
+                    ops.fused_linear(h_alt, lw["wgu"], lw["s_gu"], x_kind=xk_norm, gamma=lw["ln2_g"],
+                                     beta=lw.get("ln2_b"), smooth=lw["sm_gu"], eps=cfg.eps, bias=lw.get("b_gu"),
+                                     out=buf.y32[:T], out_kind=ops.O_GATED, act=0 if cfg.act == "silu" else 1,
+                                     out_smooth=lw["sm_d"], out_amax=buf.amax)
+                    ops.fused_linear(buf.y32[:T], lw["wd"], lw["s_d"], x_kind=ops.X_Y32, x_amax=buf.amax,
+                                     bias=lw.get("b_d"), residual=h_alt, out=h)
+                    n += 2
+                else:
+                    ops.fused_linear(h_alt, lw["wgu"], lw["s_gu"], x_kind=xk_norm, gamma=lw["ln2_g"],
+                                     beta=lw.get("ln2_b"), smooth=lw["sm_gu"], eps=cfg.eps, bias=lw.get("b_gu"), out=gu)
+                    q8 = buf.q8view(T, F)
+                    ops.act_mul_quant(gu, lw["sm_d"], act, out_q=q8, out_scale=sc)
+                    ops.gemm_w8a8(q8, lw["wd"], sc, lw["s_d"], lw.get("b_d"), h_alt, out=h)
+                    n += 3
+                continue
             q8 = buf.q8view(T, d)
             ops.norm_quant(h, lw["ln1_g"], lw.get("ln1_b"), lw["sm_qkv"], cfg.eps, out_q=q8, out_scale=sc)
             ops.gemm_w8a8(q8, lw["wqkv"], sc, lw["s_qkv"], lw.get("b_qkv"), None, out=qkv)

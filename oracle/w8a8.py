@@ -154,11 +154,9 @@ def smooth_quant(x16, smooth):
     return quant_rows(y)
 
 
-def act_mul_quant(gate_up16, smooth, act="silu"):
-    """act(gate)*up -> smoothing -> per-token int8 (kernel b2_act_mul_quant).
-
-    gate_up16: fp16 [T, 2F], gate in columns [0,F), up in [F,2F)  (modeling_llama.py:182-184).
-    """
+def act_mul_y(gate_up16, smooth, act="silu"):
+    """The fp32 values act(gate)*up*smooth that act_mul_quant quantises, and their row absmax
+    (what the fused decode kernel b2_fused_linear writes with out_kind = 1)."""
     gu = np.asarray(gate_up16, dtype=f16).astype(f32)
     F = gu.shape[1] // 2
     g, u = gu[:, :F], gu[:, F:]
@@ -166,6 +164,15 @@ def act_mul_quant(gate_up16, smooth, act="silu"):
     y = (a * u).astype(f32)
     if smooth is not None:
         y = (y * np.asarray(smooth, dtype=f32)[None, :]).astype(f32)
+    return y, np.max(np.abs(y), axis=-1).astype(f32)
+
+
+def act_mul_quant(gate_up16, smooth, act="silu"):
+    """act(gate)*up -> smoothing -> per-token int8 (kernel b2_act_mul_quant).
+
+    gate_up16: fp16 [T, 2F], gate in columns [0,F), up in [F,2F)  (modeling_llama.py:182-184).
+    """
+    y, _ = act_mul_y(gate_up16, smooth, act)
     return quant_rows(y)
 
 
