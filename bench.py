@@ -216,13 +216,9 @@ def run_ours(a):
                 t = torch.empty((1,), dtype=torch.int64, device=dev)
             toks.append(pipe.return_tokens(t))
         e1.record()
-        gen = [[t] for t in toks]
-        for i in range(1, NEW):
-            pos = [[P + i - 1] for _ in range(n_prompts)]
-            rows = [[p] for p in range(n_prompts)]
-            toks = pipe.decode_round(toks, pos, rows)
-            for p in range(n_prompts):
-                gen[p].append(toks[p])
+        # NEW-1 decode steps for the n_prompts sequences as one continuous pipeline (no round barrier)
+        out = pipe.decode_stream(toks, [[P] for _ in range(n_prompts)], [[p] for p in range(n_prompts)], NEW - 1)
+        gen = [[toks[p]] + out[p] for p in range(n_prompts)] if out is not None else None
         e2.record()
         if record is not None:
             record.append((e0, e1, e2))

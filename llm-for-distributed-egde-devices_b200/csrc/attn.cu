@@ -119,7 +119,7 @@ int rope_kv_append(void* qkv, long long ld, const float* cosT, const float* sinT
 // decode attention
 // =============================================================================================
 constexpr int DEC_TK = 64;        // keys per stage (16 per warp)
-constexpr int DEC_NST = 4;        // cp.async stages: up to 256 keys (K and V) in flight per CTA
+constexpr int DEC_NST = 3;        // cp.async stages: 192 keys (K and V) in flight per CTA, two CTAs per SM
 constexpr int DEC_THREADS = 128;
 
 struct DecParams {
@@ -134,8 +134,22 @@ struct DecParams {
   float scale_log2;
 };
 
-template <int HD>
-__global__ void __launch_bounds__(DEC_THREADS, 1) decode_attn_kernel(const DecParams p) {
+B2_DEVINL void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// read a float from the same shared-memory offset in CTA `rank` of this cluster (DSMEM)
+B2_DEVINL float ld_dsmem_f32(const float* local_ptr, uint32_t rank) {
+  uint32_t ra;
+  float v;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(smem_u32(local_ptr)), "r"(rank));
+  asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(ra) : "memory");
+  return v;
+}
+
+// CL = true: the `splits` CTAs of one (kv head, sequence) form a thread-block cluster (1,1,splits)
+// and are merged through distributed shared memory by rank 0 -- no workspace, no merge launch.
+template <int HD, bool CL>
+__global__ void __launch_bounds__(DEC_THREADS, 2) decode_attn_kernel(const DecParams p) {
   constexpr int LDS = HD + 8;                       // padded row (halves): ldmatrix conflict-free
   constexpr int TILE_HALVES = DEC_TK * LDS;
   extern __shared__ __align__(16) uint8_t smem_dec[];
@@ -161,13 +175,18 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) decode_attn_kernel(const DecPa
     constexpr int CPR = HD / 8;                       // 16-byte chunks per row
     for (int i = threadIdx.x; i < DEC_TK * CPR; i += DEC_THREADS) {
       const int r = i / CPR, c = i - r * CPR;
-      const bool ok = (k0 + r) < kend;
+      // the newest row (seqlen-1) is being written by the predecessor kernel: never prefetch it here,
+      // it is patched into shared memory after the dependency wait
+      const bool ok = (k0 + r) < kend && (k0 + r) != seqlen - 1;
       const long long goff = (long long)(ok ? k0 + r : kbeg) * HD + c * 8;
       const int soff = stage * TILE_HALVES + r * LDS + c * 8;
       cp_async16(smem_u32(sK + soff), kg + goff, ok);
       cp_async16(smem_u32(sV + soff), vg + goff, ok);
     }
   };
+  // Programmatic dependent launch: everything up to the wait touches only state older than the
+  // predecessor (sequence lengths, cache rows of earlier tokens).
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   // fill the ring: one commit group per stage (empty groups keep the group count uniform)
 #pragma unroll
   for (int sidx = 0; sidx < DEC_NST; ++sidx) {
@@ -175,6 +194,15 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) decode_attn_kernel(const DecPa
     cp_async_commit();
   }
 
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  // the newest key/value row, if it falls in this CTA's range: one 32-bit word of K and of V per thread
+  const bool has_new = (seqlen - 1) >= kbeg && (seqlen - 1) < kend;
+  uint32_t newk = 0u, newv = 0u;
+  if (has_new && threadIdx.x < HD / 2) {
+    newk = *reinterpret_cast<const uint32_t*>(kg + (long long)(seqlen - 1) * HD + threadIdx.x * 2);
+    newv = *reinterpret_cast<const uint32_t*>(vg + (long long)(seqlen - 1) * HD + threadIdx.x * 2);
+  }
+  const int new_tile = has_new ? (seqlen - 1 - kbeg) / DEC_TK : -1;
   // Q fragments: rows 0..G-1 = the query heads of this kv group, rows >= G zero
   uint32_t qf[HD / 16][4];
   {
@@ -195,6 +223,11 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) decode_attn_kernel(const DecPa
   for (int tile = 0; tile < ntiles; ++tile) {
     const int stage = tile % DEC_NST;
     cp_async_wait<DEC_NST - 1>();           // the oldest outstanding group (= this tile) has landed
+    if (tile == new_tile && threadIdx.x < HD / 2) {
+      const int r = (seqlen - 1 - kbeg) - tile * DEC_TK;
+      *reinterpret_cast<uint32_t*>(sK + stage * TILE_HALVES + r * LDS + threadIdx.x * 2) = newk;
+      *reinterpret_cast<uint32_t*>(sV + stage * TILE_HALVES + r * LDS + threadIdx.x * 2) = newv;
+    }
     __syncthreads();
     const __half* tK = sK + stage * TILE_HALVES + warp * 16 * LDS;
     const __half* tV = sV + stage * TILE_HALVES + warp * 16 * LDS;
@@ -293,13 +326,38 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) decode_attn_kernel(const DecPa
       }
     }
     const int h = kvh * G + gh;
-    if (p.splits == 1) {
+    if (CL) {
+      float* cO = sL + 32;                                   // [8][HD] CTA-level partial, read by rank 0
+      cO[idx] = acc;
+      if (d == 0) { cO[8 * HD + gh] = m; cO[8 * HD + 8 + gh] = l; }
+    } else if (p.splits == 1) {
       p.out[(long long)b * p.o_ld + h * HD + d] = __float2half_rn(l > 0.f ? acc / l : 0.f);
     } else {
       const long long po = (((long long)b * p.H + h) * p.splits + split);
       p.part_o[po * HD + d] = acc;
       if (d == 0) { p.part_ml[po * 2] = m; p.part_ml[po * 2 + 1] = l; }
     }
+  }
+  if (CL) {
+    const float* cO = sL + 32;
+    cluster_sync_all();                                      // every CTA's partial is in its shared memory
+    if (split == 0) {
+      for (int idx = threadIdx.x; idx < G * HD; idx += DEC_THREADS) {
+        const int gh = idx / HD, d = idx - gh * HD;
+        float m = -INFINITY;
+        for (int r = 0; r < p.splits; ++r) m = fmaxf(m, ld_dsmem_f32(cO + 8 * HD + gh, r));
+        float l = 0.f, acc = 0.f;
+        if (m != -INFINITY) {
+          for (int r = 0; r < p.splits; ++r) {
+            const float f = exp2f(ld_dsmem_f32(cO + 8 * HD + gh, r) - m);
+            l += ld_dsmem_f32(cO + 8 * HD + 8 + gh, r) * f;
+            acc += ld_dsmem_f32(cO + idx, r) * f;
+          }
+        }
+        p.out[(long long)b * p.o_ld + (kvh * G + gh) * HD + d] = __float2half_rn(l > 0.f ? acc / l : 0.f);
+      }
+    }
+    cluster_sync_all();                                      // peers stay resident until rank 0 has read them
   }
 }
 
@@ -329,6 +387,7 @@ int decode_attn_splits(int B, int KV, int max_seqlen, int sms) {
   const int max_by_len = (max_seqlen + 255) / 256;   // >= 256 keys per split
   int s = want < max_by_len ? want : max_by_len;
   if (s < 1) s = 1;
+  if (s > 8 && s <= 12) s = 8;      // a cluster of 8 merges in-kernel (DSMEM): cheaper than 9..12 + merge launch
   if (s > 64) s = 64;
   return s;
 }
@@ -348,15 +407,44 @@ static int sm_count_attn() {
 }
 
 template <int HD>
-static int launch_decode(const DecParams& p, int B, cudaStream_t st) {
+static int launch_decode(const DecParams& p, int B, cudaStream_t st, bool cluster = false) {
   constexpr int SMEM = DEC_NST * 2 * DEC_TK * (HD + 8) * 2;
   static bool attr_set = false;
   if (!attr_set) {
-    if (cudaFuncSetAttribute(decode_attn_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM) != cudaSuccess)
+    if (cudaFuncSetAttribute(decode_attn_kernel<HD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM) != cudaSuccess ||
+        cudaFuncSetAttribute(decode_attn_kernel<HD, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM) != cudaSuccess)
       return ERR_ARCH;
     attr_set = true;
   }
-  decode_attn_kernel<HD><<<dim3(p.KV, B, p.splits), DEC_THREADS, SMEM, st>>>(p);
+  if (cluster) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(p.KV, B, p.splits);
+    cfg.blockDim = dim3(DEC_THREADS);
+    cfg.dynamicSmemBytes = SMEM;
+    cfg.stream = st;
+    cudaLaunchAttribute at[2];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 1; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = p.splits;
+    at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 2;
+    if (cudaLaunchKernelEx(&cfg, decode_attn_kernel<HD, true>, p) != cudaSuccess) { cudaGetLastError(); return ERR_LAUNCH; }
+    return OK;
+  }
+  {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(p.KV, B, p.splits);
+    cfg.blockDim = dim3(DEC_THREADS);
+    cfg.dynamicSmemBytes = SMEM;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    if (cudaLaunchKernelEx(&cfg, decode_attn_kernel<HD, false>, p) != cudaSuccess) { cudaGetLastError(); return ERR_LAUNCH; }
+  }
   if (p.splits > 1) decode_merge_kernel<HD><<<dim3(p.H, B), HD, 0, st>>>(p);
   return launch_status();
 }
@@ -371,11 +459,14 @@ int decode_attn(const void* q, long long q_ld, const void* kcache, const void* v
   if (hd != 64 && hd != 128) return ERR_UNSUPPORTED;
   const int eff = (window > 0 && max_seqlen > window) ? window : max_seqlen;
   int splits = decode_attn_splits(B, KV, eff, sm_count_attn());
-  const size_t need = decode_attn_workspace_bytes(B, H, hd, splits);
+  // 2..8 splits: merged inside the kernel by a thread-block cluster over DSMEM (workspace unused).
+  const bool cluster = splits > 1 && splits <= 8;
+  const size_t need = cluster ? 0 : decode_attn_workspace_bytes(B, H, hd, splits);
   if (need > 0 && (!workspace || workspace_bytes < need)) {
-    // shrink to what the workspace allows rather than failing; 1 split needs none
-    while (splits > 1 && (!workspace || decode_attn_workspace_bytes(B, H, hd, splits) > workspace_bytes)) --splits;
+    // shrink to what the workspace allows rather than failing; <= 8 splits need none
+    while (splits > 8 && (!workspace || decode_attn_workspace_bytes(B, H, hd, splits) > workspace_bytes)) --splits;
   }
+  const bool use_cluster = splits > 1 && splits <= 8;
   DecParams p;
   p.q = (const __half*)q; p.q_ld = q_ld; p.k = (const __half*)kcache; p.v = (const __half*)vcache;
   p.seqlens = seqlens; p.rows = rows; p.out = (__half*)out; p.o_ld = o_ld;
@@ -383,7 +474,7 @@ int decode_attn(const void* q, long long q_ld, const void* kcache, const void* v
   p.part_ml = p.part_o ? p.part_o + (size_t)B * H * splits * hd : nullptr;
   p.H = H; p.KV = KV; p.Smax = Smax; p.splits = splits; p.window = window;
   p.scale_log2 = scale * 1.4426950408889634f;
-  return hd == 128 ? launch_decode<128>(p, B, st) : launch_decode<64>(p, B, st);
+  return hd == 128 ? launch_decode<128>(p, B, st, use_cluster) : launch_decode<64>(p, B, st, use_cluster);
 }
 
 // =============================================================================================
@@ -637,8 +728,10 @@ int init_attn() {
     ok &= cudaFuncGetAttributes(&fa, decode_merge_kernel<64>) == cudaSuccess;
     if (!ok) return ERR_ARCH;
   }
-  if (cudaFuncSetAttribute(decode_attn_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_NST * 2 * DEC_TK * (128 + 8) * 2) != cudaSuccess) return ERR_ARCH;
-  if (cudaFuncSetAttribute(decode_attn_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_NST * 2 * DEC_TK * (64 + 8) * 2) != cudaSuccess) return ERR_ARCH;
+  if (cudaFuncSetAttribute(decode_attn_kernel<128, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_NST * 2 * DEC_TK * (128 + 8) * 2) != cudaSuccess) return ERR_ARCH;
+  if (cudaFuncSetAttribute(decode_attn_kernel<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_NST * 2 * DEC_TK * (128 + 8) * 2) != cudaSuccess) return ERR_ARCH;
+  if (cudaFuncSetAttribute(decode_attn_kernel<64, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_NST * 2 * DEC_TK * (64 + 8) * 2) != cudaSuccess) return ERR_ARCH;
+  if (cudaFuncSetAttribute(decode_attn_kernel<64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_NST * 2 * DEC_TK * (64 + 8) * 2) != cudaSuccess) return ERR_ARCH;
   if (cudaFuncSetAttribute(prefill_attn_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 2 * PF_TK * (128 + 8) * 2) != cudaSuccess) return ERR_ARCH;
   if (cudaFuncSetAttribute(prefill_attn_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 2 * PF_TK * (64 + 8) * 2) != cudaSuccess) return ERR_ARCH;
   return OK;

@@ -41,6 +41,9 @@ struct FusedParams {
 
 constexpr int FL_THREADS = 256, FL_WARPS = 8, FL_ROWS = 2, FL_UNR = 4;
 constexpr int FL_SMEM_FULL = 200 * 1024;
+#ifndef FL_CTAS_PER_SM
+#define FL_CTAS_PER_SM 1
+#endif
 
 B2_DEVINL void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 B2_DEVINL void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
@@ -498,7 +501,7 @@ static int launch_fused(const FusedParams& pin, cudaStream_t st) {
   }
   const int items = (OKIND == O_F16) ? (p.N + 1) / 2 : p.N / 2;
   int grid = (items + FL_WARPS - 1) / FL_WARPS;
-  const int cap = fl_sm_count() * 2;                   // persistent: 2 CTAs per SM, prologue once per CTA
+  const int cap = fl_sm_count() * FL_CTAS_PER_SM;                   // persistent: 2 CTAs per SM, prologue once per CTA
   if (grid > cap) grid = cap;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);

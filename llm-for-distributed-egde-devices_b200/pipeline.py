@@ -174,33 +174,87 @@ class DistPipeline:
         self.graph_chunk = 0          # set to the prefill chunk size to replay full chunks as graphs
         self.fwd = lambda x, pos, seq, lg: stage.forward_auto(x, cache, pos, seq, logits=lg,
                                                               graph_chunk=self.graph_chunk)
+        if world > 1:
+            self.setup_groups()
         return self
+
+    # -- messaging --------------------------------------------------------------------------------
+    # On GPUs every receive is posted from a side stream (so NCCL does not make it wait for compute
+    # that is merely queued ahead of it) and every send runs on another side stream on a private
+    # copy of the tile (so compute never waits for a send, and a graph's static output buffer can be
+    # overwritten at once).  The compute stream waits only where it consumes received data.
+    def setup_groups(self):
+        """Collective: a separate communicator for the token return path, so that a token send
+        queued on one rank can never sit in front of a hidden-state transfer (and vice versa)."""
+        self.tok_group = self.dist.new_group(ranks=list(range(self.world))) if self.world > 1 else None
+        if self.device.type == "cuda":
+            self._rs, self._ss = torch.cuda.Stream(self.device), torch.cuda.Stream(self.device)
+            self._rs_tok, self._ss_tok = torch.cuda.Stream(self.device), torch.cuda.Stream(self.device)
+
+    def _recv(self, shape, dtype, src, tok=False):
+        buf = torch.empty(shape, dtype=dtype, device=self.device)
+        group = getattr(self, "tok_group", None) if tok else self.group
+        if self.device.type != "cuda" or not hasattr(self, "_rs"):
+            self.dist.recv(buf, src=src, group=group)
+            return buf
+        side = self._rs_tok if tok else self._rs
+        cur = torch.cuda.current_stream(self.device)
+        side.wait_stream(cur)              # the allocation above is stream-ordered on `cur`
+        with torch.cuda.stream(side):
+            self.dist.irecv(buf, src=src, group=group).wait()
+        cur.wait_stream(side)
+        buf.record_stream(side)
+        return buf
+
+    def _send(self, t, dst, tok=False):
+        group = getattr(self, "tok_group", None) if tok else self.group
+        if self.device.type != "cuda" or not hasattr(self, "_ss"):
+            # CPU (gloo tests): a blocking send could sit in front of the receive the peer needs
+            # first; post it without waiting and reap finished handles later
+            if not hasattr(self, "_pending"):
+                self._pending = []
+            self._pending = [(w, b) for w, b in self._pending if not w.is_completed()]
+            c = t.clone()
+            self._pending.append((self.dist.isend(c, dst=dst, group=group), c))
+            return
+        side = self._ss_tok if tok else self._ss
+        cur = torch.cuda.current_stream(self.device)
+        c = t.clone()                      # private copy: the caller may overwrite `t` immediately
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):
+            self.dist.isend(c, dst=dst, group=group).wait()
+        c.record_stream(side)
+
+    def drain(self):
+        """Wait for every message this rank has posted (call before tearing the group down)."""
+        for w, _ in getattr(self, "_pending", []):
+            w.wait()
+        self._pending = []
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
 
     # -- one hop --------------------------------------------------------------------------------
     def step(self, x, positions, seq_ids, want_logits: str):
         """x: ids on rank 0 (ignored elsewhere).  Returns logits on the last rank, else None."""
         T = len(positions)
         if not self.first:
-            x = torch.empty((T, self.d), dtype=torch.float16, device=self.device)
-            self.dist.recv(x, src=self.rank - 1, group=self.group)
+            x = self._recv((T, self.d), torch.float16, self.rank - 1)
         y = self.fwd(x, positions, seq_ids, want_logits if self.last else "none")
         if not self.last:
-            self.dist.send(y, dst=self.rank + 1, group=self.group)
+            self._send(y, self.rank + 1)
             return None
         return y
 
     def return_tokens(self, tok):
-        """Greedy ids [B] int64: last rank -> rank 0.  Returns them on rank 0, None elsewhere
-        (the last rank keeps its own copy)."""
+        """Greedy ids [B] int64: last rank -> rank 0.  Returns them on rank 0 and on the last rank,
+        None on the ranks in between."""
         if self.world == 1:
             return tok
         if self.last:
-            self.dist.send(tok, dst=0, group=self.group)
+            self._send(tok, 0, tok=True)
             return tok
         if self.first:
-            t = torch.empty_like(tok) if tok is not None else None
-            self.dist.recv(t, src=self.world - 1, group=self.group)
-            return t
+            return self._recv(tuple(tok.shape), torch.int64, self.world - 1, tok=True)
         return None
 
     # -- schedules --------------------------------------------------------------------------------
@@ -220,32 +274,47 @@ class DistPipeline:
                 y = self.step(ids[c0:c1] if self.first else None, pos, np.full(c1 - c0, p),
                               "last" if c1 == T else "none")
                 if self.last and c1 == T:
-                    outs.append(y)
+                    outs.append(y.clone())
         return outs
 
     def _bcast_len(self, T):
         # prompt lengths are part of the (synthetic) workload description known to every rank
         return int(T)
 
+    def decode_stream(self, first_tokens, start_positions, rows_per_group, steps: int):
+        """`steps` greedy decode steps for each of G independent groups as ONE continuous pipeline:
+        group g's token of step i-1 is awaited only right before group g's step i, so with
+        G >= world every stage is busy every tick (no round barrier).  first_tokens[g]: int64 [B_g]
+        (needed on rank 0).  Returns, on rank 0 and on the last rank, tokens[g] = list of `steps`
+        tensors [B_g]; None on the ranks in between."""
+        G = len(rows_per_group)
+        gen = [[] for _ in range(G)]
+        cur = list(first_tokens) if self.first else [None] * G
+        for i in range(steps):
+            for g in range(G):
+                rows = rows_per_group[g]
+                pos = [p + i for p in start_positions[g]]
+                if i > 0 and self.first and not self.last:
+                    cur[g] = self._recv((len(rows),), torch.int64, self.world - 1, tok=True)
+                    gen[g].append(cur[g])
+                lg = self.step(cur[g] if self.first else None, pos, rows, "last")
+                if self.last:
+                    t = torch.empty((len(rows),), dtype=torch.int64, device=self.device)
+                    self._argmax(lg, t)
+                    gen[g].append(t)
+                    if self.first:
+                        cur[g] = t
+                    else:
+                        self._send(t, 0, tok=True)
+        if self.first and not self.last:
+            for g in range(G):
+                gen[g].append(self._recv((len(rows_per_group[g]),), torch.int64, self.world - 1, tok=True))
+        return gen if (self.first or self.last) else None
+
     def decode_round(self, tokens_per_group, positions_per_group, rows_per_group):
-        """One decode step for each of G independent micro-batches, pipelined: group g enters
-        stage 0 right after group g-1, so with G >= world all stages stay busy.  Returns the list
-        of greedy tokens per group on rank 0 and on the last rank."""
-        toks = []
-        for g, (tok, pos, rows) in enumerate(zip(tokens_per_group, positions_per_group, rows_per_group)):
-            lg = self.step(tok if self.first else None, pos, rows, "last")
-            t = None
-            if self.last:
-                t = torch.empty((len(pos),), dtype=torch.int64, device=self.device)
-                self._argmax(lg, t)
-            toks.append(t)
-        # tokens travel back after all groups are in flight (does not stall the forward wave)
-        back = []
-        for g, t in enumerate(toks):
-            if self.first and not self.last:
-                t = torch.empty((len(positions_per_group[g]),), dtype=torch.int64, device=self.device)
-            back.append(self.return_tokens(t))
-        return back
+        """One decode step for each group (a decode_stream of a single step)."""
+        gen = self.decode_stream(tokens_per_group, positions_per_group, rows_per_group, 1)
+        return [x[0] for x in gen] if gen is not None else [None] * len(rows_per_group)
 
     def _argmax(self, lg, out):
         if lg.is_cuda:

@@ -153,13 +153,20 @@ def _worker(rank, world, port, prompts, chunk, new, q):
             t = lgs[p].argmax(-1).view(1) if pipe.last else (torch.empty(1, dtype=torch.int64) if pipe.first else None)
             toks.append(pipe.return_tokens(t))
         gen = [[int(t[0])] for t in toks] if (pipe.first or pipe.last) else None
-        for i in range(1, new):
+        pipe.setup_groups()
+        rows = [[p] for p in range(len(prompts))]
+        # two steps through decode_round (one step per call), the rest as one continuous stream
+        for i in range(1, 3):
             pos = [[lens[p] + i - 1] for p in range(len(prompts))]
-            rows = [[p] for p in range(len(prompts))]
             toks = pipe.decode_round(toks, pos, rows)
             if gen is not None:
                 for p in range(len(prompts)):
                     gen[p].append(int(toks[p][0]))
+        out = pipe.decode_stream(toks, [[lens[p] + 2] for p in range(len(prompts))], rows, new - 3)
+        if gen is not None:
+            for p in range(len(prompts)):
+                gen[p] += [int(t[0]) for t in out[p]]
+        pipe.drain()
         q.put((rank, gen))
     finally:
         dist.destroy_process_group()
@@ -177,7 +184,7 @@ def test_two_rank_pipeline_schedule_gloo():
     import torch.multiprocessing as mp
     g = torch.Generator().manual_seed(3)
     prompts = [torch.randint(0, V, (n,), generator=g) for n in (11, 7, 16)]     # ragged: chunks 4,4,3 / 4,3 / 4x4
-    chunk, new = 4, 5
+    chunk, new = 4, 7
     want = _single_process_reference(prompts, chunk, new)
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
