@@ -42,7 +42,7 @@ struct FusedParams {
 constexpr int FL_THREADS = 256, FL_WARPS = 8, FL_ROWS = 2, FL_UNR = 4;
 constexpr int FL_SMEM_FULL = 200 * 1024;
 #ifndef FL_CTAS_PER_SM
-#define FL_CTAS_PER_SM 1
+#define FL_CTAS_PER_SM 2
 #endif
 
 B2_DEVINL void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }

@@ -51,7 +51,11 @@ struct GemmParams {
 
 constexpr int KIND_I8 = 0, KIND_F16 = 1;
 
-template <int BN, int STAGES, int KIND>
+// CM > 1: CM CTAs (consecutive m-tiles, same n-tile) form a cluster; each loads 1/CM of the weight
+// tile and multicasts it to the whole cluster, so per-CTA operand traffic from L2 drops from
+// A + B to A + B/CM.  A stage is refilled only after every CTA of the cluster has consumed it:
+// the MMA commits are multicast to all empty barriers (count CM).
+template <int BN, int STAGES, int KIND, int CM>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const GemmParams p) {
@@ -69,7 +73,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int lane = threadIdx.x & 31;
   const int m_tiles = (p.M + BM - 1) / BM;
   const int n_tiles = (p.N + BN - 1) / BN;
-  const int num_tiles = m_tiles * n_tiles;
+  const int cta_rank = (CM > 1) ? (int)cluster_ctarank() : 0;
+  const int m_groups = (m_tiles + CM - 1) / CM;          // cluster tile = CM m-tiles x 1 n-tile
+  const int num_tiles = m_groups * n_tiles;              // per cluster
+  const int t_first = blockIdx.x / CM, t_step = gridDim.x / CM;
+  constexpr uint16_t MCAST = (uint16_t)((1u << CM) - 1);
   constexpr int BKE = (KIND == KIND_I8) ? BK : BK / 2;   // elements per 128-byte k-block
   const int kblocks = (p.K + BKE - 1) / BKE;
 
@@ -78,13 +86,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     tma_prefetch_desc(&tmB);
   }
   if (warp == 1 && lane == 0) {
-    for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], CM); }
     for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 4); }
     mbar_fence_init();
   }
   if (warp == 2) tmem_alloc<TMEM_COLS>(tmem_slot);
   tc_fence_before();
   __syncthreads();
+  if (CM > 1) cluster_sync();      // every CTA's barriers exist before any peer multicasts into them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -92,15 +101,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // ===================== TMA producer =====================
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-        const int mt = t % m_tiles, nt = t / m_tiles;
+      for (int t = t_first; t < num_tiles; t += t_step) {
+        const int mt = (t % m_groups) * CM + cta_rank, nt = t / m_groups;
         for (int kb = 0; kb < kblocks; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * S::STAGE_BYTES;
           uint8_t* sb = sa + S::A_BYTES;
           mbar_expect_tx(&full_bar[stage], S::STAGE_BYTES);
           tma_load_2d(sa, &tmA, &full_bar[stage], kb * BKE, mt * BM);
-          tma_load_2d(sb, &tmB, &full_bar[stage], kb * BKE, nt * BN);
+          if (CM == 1) {
+            tma_load_2d(sb, &tmB, &full_bar[stage], kb * BKE, nt * BN);
+          } else {   // my BN/CM rows of the weight tile, delivered to every CTA of the cluster
+            constexpr int SL = BN / CM;
+            tma_load_2d_mcast(sb + cta_rank * SL * BK, &tmB, &full_bar[stage], kb * BKE, nt * BN + cta_rank * SL, MCAST);
+          }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -112,7 +126,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                                                    : umma_idesc(IDESC_FMT_F32, IDESC_F16, IDESC_F16, BM, BN);
       int stage = 0; uint32_t phase = 0;
       int it = 0;
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+      for (int t = t_first; t < num_tiles; t += t_step, ++it) {
         const int buf = it & 1;
         const uint32_t bphase = (it >> 1) & 1;
         mbar_wait(&tempty_bar[buf], bphase ^ 1);
@@ -130,7 +144,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             if (KIND == KIND_I8) umma_i8(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
             else umma_f16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
           }
-          umma_commit(&empty_bar[stage]);
+          if (CM == 1) umma_commit(&empty_bar[stage]);
+          else umma_commit_mcast(&empty_bar[stage], MCAST);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
         umma_commit(&tfull_bar[buf]);
@@ -140,8 +155,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // ===================== epilogue =====================
     const int quad = warp & 3;
     int it = 0;
-    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
-      const int mt = t % m_tiles, nt = t / m_tiles;
+    for (int t = t_first; t < num_tiles; t += t_step, ++it) {
+      const int mt = (t % m_groups) * CM + cta_rank, nt = t / m_groups;
       const int buf = it & 1;
       const uint32_t bphase = (it >> 1) & 1;
       mbar_wait(&tfull_bar[buf], bphase);
@@ -218,6 +233,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
   tc_fence_before();
   __syncthreads();
+  if (CM > 1) cluster_sync();      // no CTA leaves while a peer may still multicast into it
   if (warp == 2) tmem_dealloc<TMEM_COLS>(tmem_base);
 }
 
@@ -266,12 +282,12 @@ static int sm_count() {
   return n;
 }
 
-template <int BN, int STAGES, int KIND>
+template <int BN, int STAGES, int KIND, int CM>
 static int launch_tc(const void* A, const void* W, const GemmParams& p, cudaStream_t st) {
   using S = GemmSmem<BN, STAGES>;
   static bool attr_set = false;
   if (!attr_set) {
-    if (cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES, KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL) !=
+    if (cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES, KIND, CM>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL) !=
         cudaSuccess)
       return ERR_ARCH;
     attr_set = true;
@@ -279,12 +295,27 @@ static int launch_tc(const void* A, const void* W, const GemmParams& p, cudaStre
   CUtensorMap tmA, tmB;
   int rc = make_tmap(&tmA, A, p.M, p.K, BM, KIND);
   if (rc) return rc;
-  rc = make_tmap(&tmB, W, p.N, p.K, BN, KIND);
+  rc = make_tmap(&tmB, W, p.N, p.K, BN / CM, KIND);          // each CTA loads BN/CM rows of the weight tile
   if (rc) return rc;
-  const int tiles = ((p.M + BM - 1) / BM) * ((p.N + BN - 1) / BN);
-  const int grid = tiles < sm_count() ? tiles : sm_count();
-  gemm_tc_kernel<BN, STAGES, KIND><<<grid, GEMM_THREADS, S::TOTAL, st>>>(tmA, tmB, p);
-  return launch_status();
+  const int m_groups = ((p.M + BM - 1) / BM + CM - 1) / CM;
+  const int ctiles = m_groups * ((p.N + BN - 1) / BN);
+  const int max_clusters = sm_count() / CM;
+  const int clusters = ctiles < max_clusters ? ctiles : max_clusters;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(clusters * CM);
+  cfg.blockDim = dim3(GEMM_THREADS);
+  cfg.dynamicSmemBytes = S::TOTAL;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = CM; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  if (cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, STAGES, KIND, CM>, tmA, tmB, p) != cudaSuccess) {
+    cudaGetLastError();
+    return ERR_LAUNCH;
+  }
+  return OK;
 }
 
 // =============================================================================================
@@ -414,6 +445,7 @@ int gemm_w8a8(const int8_t* A, const int8_t* W, const float* a_scale, const floa
   GemmParams p{a_scale, w_scale, (const __half*)bias, (const __half*)residual, (__half*)out, nullptr, acc_dump, M, N, K, N};
   // schedule: 0 = auto, 1 = force tensor-core path, 2 = force streaming path (M <= 8 only)
   const bool gemv = (schedule == 2) || (schedule == 0 && M <= GEMV_MAX_M);
+  if (schedule >= 10 && (N % 256 || schedule > 16)) return ERR_UNSUPPORTED;
   if (gemv) {
     if (M > GEMV_MAX_M) return ERR_UNSUPPORTED;
     if (M == 1) return launch_gemv<1>(A, W, p, st);
@@ -423,10 +455,20 @@ int gemm_w8a8(const int8_t* A, const int8_t* W, const float* a_scale, const floa
   }
   const int m_tiles = (M + BM - 1) / BM;
   const int sms = sm_count();
-  if (N >= 256 && m_tiles * ((N + 255) / 256) >= sms) return launch_tc<256, 4, KIND_I8>(A, W, p, st);
-  if (N >= 128 && m_tiles * ((N + 127) / 128) >= sms) return launch_tc<128, 6, KIND_I8>(A, W, p, st);
-  if (N >= 64) return launch_tc<64, 8, KIND_I8>(A, W, p, st);
-  return launch_tc<32, 8, KIND_I8>(A, W, p, st);
+  // schedule >= 10 (test hook): force a tile/cluster shape; 0/1: heuristic
+  if (schedule == 10) return launch_tc<256, 4, KIND_I8, 1>(A, W, p, st);
+  if (schedule == 11) return launch_tc<256, 4, KIND_I8, 2>(A, W, p, st);
+  if (schedule == 12) return launch_tc<256, 4, KIND_I8, 4>(A, W, p, st);
+  if (schedule == 13) return launch_tc<128, 6, KIND_I8, 4>(A, W, p, st);
+  if (schedule == 14) return launch_tc<128, 6, KIND_I8, 1>(A, W, p, st);
+  if (schedule == 15) return launch_tc<64, 8, KIND_I8, 1>(A, W, p, st);
+  if (schedule == 16) return launch_tc<128, 6, KIND_I8, 2>(A, W, p, st);
+  // Measured on B200 (tools/kbench.py, profiles/r01_*): the kernel is bound by operand latency /
+  // bytes in flight, not by L2 bandwidth, so 128x128 tiles with a 6-deep ring beat 128x256 with 4
+  // stages on every Llama-2-7B shape (1.4-1.66 vs 1.0-1.47 PTOP/s at M = 512).
+  if (N >= 128 && m_tiles * ((N + 127) / 128) >= sms / 2) return launch_tc<128, 6, KIND_I8, 1>(A, W, p, st);
+  if (N >= 64) return launch_tc<64, 8, KIND_I8, 1>(A, W, p, st);
+  return launch_tc<32, 8, KIND_I8, 1>(A, W, p, st);
 }
 
 // =============================================================================================
@@ -520,16 +562,16 @@ int lm_head(const void* x, const void* W, float* logits, int M, int V, int d, cu
   }
   GemmParams p{nullptr, nullptr, nullptr, nullptr, nullptr, logits, nullptr, M, V, d, V};
   const int m_tiles = (M + BM - 1) / BM;
-  if (V >= 256 && m_tiles * ((V + 255) / 256) >= sm_count()) return launch_tc<256, 4, KIND_F16>(x, W, p, st);
-  if (V >= 128) return launch_tc<128, 6, KIND_F16>(x, W, p, st);
-  return launch_tc<64, 8, KIND_F16>(x, W, p, st);
+  if (V >= 256 && m_tiles * ((V + 255) / 256) >= sm_count()) return launch_tc<256, 4, KIND_F16, 1>(x, W, p, st);
+  if (V >= 128) return launch_tc<128, 6, KIND_F16, 1>(x, W, p, st);
+  return launch_tc<64, 8, KIND_F16, 1>(x, W, p, st);
 }
 
 // One-time set-up of every instantiation (dynamic shared-memory opt-in, driver entry point), so
 // that no launch path has first-call side effects -- required before capturing CUDA graphs.
-template <int BN, int STAGES, int KIND>
+template <int BN, int STAGES, int KIND, int CM = 1>
 static int init_tc() {
-  return cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES, KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  return cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES, KIND, CM>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                               GemmSmem<BN, STAGES>::TOTAL) == cudaSuccess ? OK : ERR_ARCH;
 }
 int init_gemm() {
@@ -540,6 +582,10 @@ int init_gemm() {
   if ((rc = init_tc<128, 6, KIND_I8>())) return rc;
   if ((rc = init_tc<64, 8, KIND_I8>())) return rc;
   if ((rc = init_tc<32, 8, KIND_I8>())) return rc;
+  if ((rc = init_tc<256, 4, KIND_I8, 2>())) return rc;
+  if ((rc = init_tc<256, 4, KIND_I8, 4>())) return rc;
+  if ((rc = init_tc<128, 6, KIND_I8, 2>())) return rc;
+  if ((rc = init_tc<128, 6, KIND_I8, 4>())) return rc;
   if ((rc = init_tc<256, 4, KIND_F16>())) return rc;
   if ((rc = init_tc<128, 6, KIND_F16>())) return rc;
   if ((rc = init_tc<64, 8, KIND_F16>())) return rc;

@@ -110,8 +110,10 @@ if a.prefill:
         N = L[0][wk].shape[0]
         xin = x8[:, :K].contiguous()
         out = torch.empty((T, N), dtype=torch.float16, device=dev)
-        t = timed(lambda: [ops.gemm_w8a8(xin, lw[wk], st, lw[sk], out=out) for lw in L], 10)
-        report(f"gemm_tc {name} [{T}x{N}x{K}]", t, ops_=2.0 * T * N * K)
+        for sched, tag in ((0, "auto"), (10, "BN256 CM1"), (11, "BN256 CM2"), (12, "BN256 CM4"), (14, "BN128 CM1"),
+                           (16, "BN128 CM2"), (13, "BN128 CM4")):
+            t = timed(lambda: [ops.gemm_w8a8(xin, lw[wk], st, lw[sk], out=out, schedule=sched) for lw in L], 10)
+            report(f"gemm_tc {name} [{T}x{N}x{K}] {tag}", t, ops_=2.0 * T * N * K)
     qkvT = torch.randn((T, cfg.qkv_out), dtype=torch.float16, device=dev)
     outT = torch.empty((T, H * hd), dtype=torch.float16, device=dev)
     kcp = torch.randn((a.nl, 1, KV, a.seq + T, hd), dtype=torch.float16, device=dev)
