@@ -40,7 +40,7 @@ def parse():
     ap.add_argument("--model", default="llama-2-7b")
     ap.add_argument("--prompt", type=int, default=2048)
     ap.add_argument("--new", type=int, default=128)
-    ap.add_argument("--chunk", type=int, default=512)
+    ap.add_argument("--chunk", type=int, default=0, help="prefill chunk (0 = auto: whole prompt on one GPU, 512 when pipelining)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--layers", type=int, default=0, help="PROFILING ONLY: truncate the model to this many layers")
     return ap.parse_args()
@@ -182,13 +182,17 @@ def run_ours(a):
     dev = torch.device("cuda", local)
     dist = None
     if world > 1:
+        # NCCL_DEBUG=VERSION makes NCCL print a banner on stdout, ahead of the one JSON line
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
     cfg = b2.get_config(a.model)
     if a.layers:
         import dataclasses
         cfg = dataclasses.replace(cfg, n_layers=a.layers, name=f"{cfg.name}[TRUNCATED to {a.layers} layers: profiling only]")
-    P, NEW, CH = a.prompt, a.new, a.chunk
+    P, NEW = a.prompt, a.new
+    CH = a.chunk or (min(P, 2048) if world == 1 else 512)
     max_seq = P + NEW
     n_prompts = world                       # weak scaling: one prompt stream per stage
     pipe = DistPipeline.load(cfg, rank, world, dev, seed=0, fast_init=True, max_rows=n_prompts, max_seq=max_seq)
@@ -354,7 +358,11 @@ def roofline_pass(torch, ops, stage, cfg, pk, dev, chunk):
     achieved = bytes_launch / (ms * 1e-3) / 1e9
     roof = {"bound": "hbm", "kernel": "fused_gemv_kernel<1,RMS,GATED> (norm+quant+gate_up GEMV+SiLU*up, M=1)",
             "achieved": achieved, "peak": pk["hbm"], "unit": "GB/s",
-            "frac": achieved / pk["hbm"], "traffic": None, "algorithmic_bytes_per_launch": bytes_launch,
+            "frac": achieved / pk["hbm"],
+            # dram__bytes_read.sum + dram__bytes_write.sum per launch of this kernel at this shape, from the
+            # `ncu --set full` capture summarised in profiles/r01_ncu_full_summary.md (90.40 MB + 2.97 MB)
+            "traffic": 93367040 if (cfg.d_model, cfg.ffn) == (4096, 11008) else None,
+            "traffic_unit": "bytes/launch", "algorithmic_bytes_per_launch": bytes_launch,
             "avg_launch_us": ms * 1e3, "peak_source": pk["which"]}
     # prefill: M = chunk tokens through the same linear on the tensor cores
     M = chunk
