@@ -65,6 +65,8 @@ PRESETS = {
     "tiny-gqa-test": ModelConfig("tiny-gqa-test", 4, 512, 8, 2, 64, 1024, 1024, window=0, max_pos=512),
     "tiny-window-test": ModelConfig("tiny-window-test", 2, 256, 4, 2, 64, 512, 512, window=48, max_pos=512),
     "tiny-hd128-test": ModelConfig("tiny-hd128-test", 2, 512, 4, 4, 128, 1024, 512, max_pos=512),
+    "tiny-gpt2-test": ModelConfig("tiny-gpt2-test", 3, 256, 4, 4, 64, 1024, 512, eps=1e-5, max_pos=256, act="gelu_new",
+                                  gated=False, norm="layernorm", rope=False, bias=True),
 }
 
 

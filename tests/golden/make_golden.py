@@ -69,13 +69,46 @@ def hf_model(cfg, seed):
     return m
 
 
+def hf_gpt2(cfg, seed):
+    """HF GPT2LMHeadModel (BASELINE.json configs[0] family) with the same synthetic weights.
+    GPT-2 uses Conv1D: weight is [in, out] = our [out, in] transposed."""
+    from transformers import GPT2Config, GPT2LMHeadModel
+    hc = GPT2Config(vocab_size=cfg.vocab, n_positions=cfg.max_pos, n_embd=cfg.d_model, n_layer=cfg.n_layers,
+                    n_head=cfg.n_heads, n_inner=cfg.ffn, activation_function="gelu_new", layer_norm_epsilon=cfg.eps,
+                    resid_pdrop=0.0, embd_pdrop=0.0, attn_pdrop=0.0, tie_word_embeddings=True)
+    m = GPT2LMHeadModel(hc).eval().float()
+    h16 = lambda t: t.to(torch.float16).to(torch.float32)
+    sd = {}
+    for li in range(cfg.n_layers):
+        w = weights.init_layer_fp32(cfg, li, seed)
+        p = f"transformer.h.{li}."
+        sd[p + "attn.c_attn.weight"] = w["wqkv"].t().contiguous()
+        sd[p + "attn.c_attn.bias"] = h16(w["b_qkv"])
+        sd[p + "attn.c_proj.weight"] = w["wo"].t().contiguous()
+        sd[p + "attn.c_proj.bias"] = h16(w["b_o"])
+        sd[p + "mlp.c_fc.weight"] = w["wgu"].t().contiguous()
+        sd[p + "mlp.c_fc.bias"] = h16(w["b_gu"])
+        sd[p + "mlp.c_proj.weight"] = w["wd"].t().contiguous()
+        sd[p + "mlp.c_proj.bias"] = h16(w["b_d"])
+        sd[p + "ln_1.weight"], sd[p + "ln_1.bias"] = h16(w["ln1_g"]), h16(w["ln1_b"])
+        sd[p + "ln_2.weight"], sd[p + "ln_2.bias"] = h16(w["ln2_g"]), h16(w["ln2_b"])
+    e = weights.init_embed_fp32(cfg, seed)
+    sd["transformer.wte.weight"] = h16(e["embed"])
+    sd["transformer.wpe.weight"] = h16(e["pos_embed"])
+    sd["transformer.ln_f.weight"], sd["transformer.ln_f.bias"] = h16(e["lnf_g"]), h16(e["lnf_b"])
+    sd["lm_head.weight"] = h16(e["embed"])
+    missing, unexpected = m.load_state_dict(sd, strict=False)
+    assert not unexpected and all(("attn.bias" in k or "masked_bias" in k) for k in missing), (missing, unexpected)
+    return m
+
+
 def main():
     warnings.filterwarnings("ignore")
     torch.set_num_threads(4)
-    for name, seed, T, new in CASES:
+    for name, seed, T, new in CASES + [("tiny-gpt2-test", 9, 20, 8)]:
         cfg = b200stage.get_config(name)
         ids = np.random.default_rng(seed + 100).integers(0, cfg.vocab, T)
-        m = hf_model(cfg, seed)
+        m = hf_gpt2(cfg, seed) if not cfg.rope else hf_model(cfg, seed)
         tid = torch.from_numpy(ids)[None]
         with torch.no_grad():
             hf_logits = m(tid).logits[0].numpy()

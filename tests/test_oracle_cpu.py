@@ -118,7 +118,7 @@ def test_weight_quantiser_matches_oracle_statement():
 
 
 # ---- golden vectors --------------------------------------------------------------------------
-@pytest.mark.parametrize("name", ["tiny-llama-test", "tiny-gqa-test"])
+@pytest.mark.parametrize("name", ["tiny-llama-test", "tiny-gqa-test", "tiny-gpt2-test"])
 def test_oracle_against_golden(name):
     g = np.load(os.path.join(GOLD, f"{name}.npz"))
     cfg = b200stage.get_config(name)

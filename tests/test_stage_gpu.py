@@ -38,7 +38,7 @@ def _close(got, ref, name):
     assert cos >= 0.9995, (name, cos)
 
 
-@pytest.mark.parametrize("model", ["tiny-llama-test", "tiny-gqa-test", "tiny-window-test", "tiny-hd128-test"])
+@pytest.mark.parametrize("model", ["tiny-llama-test", "tiny-gqa-test", "tiny-window-test", "tiny-hd128-test", "tiny-gpt2-test"])
 def test_stage_prefill_then_decode_matches_oracle(model):
     cfg = b200stage.get_config(model)
     seed, T, S = 3, 70, 96
@@ -101,7 +101,7 @@ def test_chunked_prefill_equals_one_shot():
     assert int(a.argmax()) == int(b.argmax())
 
 
-@pytest.mark.parametrize("model,n_stages", [("tiny-llama-test", 1), ("tiny-gqa-test", 2), ("tiny-window-test", 2)])
+@pytest.mark.parametrize("model,n_stages", [("tiny-llama-test", 1), ("tiny-gqa-test", 2), ("tiny-window-test", 2), ("tiny-gpt2-test", 2)])
 def test_greedy_tokens_identical(model, n_stages):
     cfg = b200stage.get_config(model)
     seed, T, NEW = 7, 40, 32
