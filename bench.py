@@ -105,9 +105,15 @@ class Clocks:
 # :238-260): HF AutoModelForCausalLM -> quantize_dynamic({nn.Linear}, qint8) -> generate.
 # ----------------------------------------------------------------------------------------------
 def cpu_reference_run(model: str, prompt: int, new: int, steps: int, warmup: int):
-    """Times HF Llama (random init from the model's config; no checkpoints offline) +
-    torch.quantization.quantize_dynamic on the host cores at 2 and 4 of the model's layers and
-    extrapolates linearly in the layer count to the full depth (bounded sample)."""
+    """The reference's CPU int8 path on the host cores: HF Llama (random init from the model's
+    config; no checkpoints offline) -> torch.quantization.quantize_dynamic({nn.Linear}, qint8)
+    [try.py:204-205] -> greedy generate [try.py:247-256 with do_sample=False].
+
+    Bounded sample of the bench workload (`prompt` prefill + `new` decode tokens): the model is
+    built at 2 and at 4 of its layers; for each, a `s_prompt`-token prefill (generate with one new
+    token) and `s_new` decode steps are timed separately; per-layer and fixed costs are separated
+    by the two depths and extrapolated linearly to the full depth; the workload time is then
+    composed as prompt x (prefill s/token) + new x (decode s/token)."""
     import warnings
     import torch
     warnings.filterwarnings("ignore")
@@ -116,8 +122,8 @@ def cpu_reference_run(model: str, prompt: int, new: int, steps: int, warmup: int
     cfg = importlib.import_module("llm-for-distributed-egde-devices_b200").get_config(model)
     threads = os.cpu_count() or 1
     torch.set_num_threads(threads)
-    s_prompt, s_new = min(prompt, 256), min(new, 8)
-    times = {}
+    s_prompt, s_new = min(prompt, 256), min(max(new - 1, 1), 8)
+    t_pre, t_dec = {}, {}
     for L in (2, 4):
         hc = LlamaConfig(vocab_size=cfg.vocab, hidden_size=cfg.d_model, intermediate_size=cfg.ffn, num_hidden_layers=L,
                          num_attention_heads=cfg.n_heads, num_key_value_heads=cfg.n_kv_heads,
@@ -126,25 +132,37 @@ def cpu_reference_run(model: str, prompt: int, new: int, steps: int, warmup: int
         m = LlamaForCausalLM(hc).eval()
         m = torch.quantization.quantize_dynamic(m, {torch.nn.Linear}, dtype=torch.qint8)     # try.py:205
         ids = torch.randint(0, cfg.vocab, (1, s_prompt), generator=torch.Generator().manual_seed(1234))
-        ts = []
+        mask = torch.ones_like(ids)
+
+        def gen(n):
+            t0 = time.perf_counter()
+            m.generate(input_ids=ids, attention_mask=mask, max_new_tokens=n, min_new_tokens=n, do_sample=False, pad_token_id=0)
+            return time.perf_counter() - t0
+        pre, full = [], []
         with torch.no_grad():
             for i in range(warmup + steps):
-                t0 = time.perf_counter()
-                m.generate(input_ids=ids, attention_mask=torch.ones_like(ids), max_new_tokens=s_new, min_new_tokens=s_new,
-                           do_sample=False, pad_token_id=0)
+                a1, a2 = gen(1), gen(1 + s_new)
                 if i >= warmup:
-                    ts.append(time.perf_counter() - t0)
-        times[L] = statistics.median(ts)
+                    pre.append(a1)
+                    full.append(a2)
+        t_pre[L] = statistics.median(pre)
+        t_dec[L] = max(statistics.median(full) - t_pre[L], 1e-9)
         del m
-    per_layer = (times[4] - times[2]) / 2.0
-    fixed = max(times[2] - 2 * per_layer, 0.0)
-    t_full = fixed + per_layer * cfg.n_layers
-    toks = s_prompt + s_new
-    return dict(value=toks / t_full, unit=UNIT, cores=threads, kind="reference",
-                sample=(f"HF LlamaForCausalLM random-init + quantize_dynamic(qint8) [try.py:204-205], prompt {s_prompt} + "
-                        f"{s_new} greedy tokens, timed at 2 and 4 of {cfg.n_layers} layers ({times[2]:.2f}s, {times[4]:.2f}s), "
-                        f"extrapolated linearly to {cfg.n_layers} layers ({t_full:.2f}s)"),
-                ms_per_step=t_full * 1e3)
+
+    def extrapolate(t):
+        per_layer = (t[4] - t[2]) / 2.0
+        fixed = max(t[2] - 2 * per_layer, 0.0)
+        return fixed + per_layer * cfg.n_layers
+    pre_tok = extrapolate(t_pre) / s_prompt          # seconds per prompt token, full depth
+    dec_tok = extrapolate(t_dec) / s_new             # seconds per generated token, full depth
+    t_full = prompt * pre_tok + new * dec_tok
+    return dict(value=(prompt + new) / t_full, unit=UNIT, cores=threads, kind="reference",
+                sample=(f"HF LlamaForCausalLM random-init + quantize_dynamic(qint8) [try.py:204-205], greedy generate; "
+                        f"prefill of {s_prompt} tokens and {s_new} decode steps timed separately at 2 and 4 of {cfg.n_layers} "
+                        f"layers (prefill {t_pre[2]:.2f}s/{t_pre[4]:.2f}s, decode {t_dec[2]:.2f}s/{t_dec[4]:.2f}s), extrapolated "
+                        f"linearly to {cfg.n_layers} layers: {1 / pre_tok:.1f} prefill tok/s, {1 / dec_tok:.2f} decode tok/s, "
+                        f"composed for {prompt} + {new} tokens ({t_full:.1f}s)"),
+                ms_per_step=t_full * 1e3, prefill_tokens_per_s=1 / pre_tok, decode_tokens_per_s=1 / dec_tok)
 
 
 def run_reference(a):
@@ -156,6 +174,7 @@ def run_reference(a):
             "warmup": a.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "int8", "data": "synthetic",
             "config": {"workload": f"{a.model} W8A8, B=1, prompt {a.prompt} + {a.new} greedy tokens (CPU sample, see cpu_baseline.sample)"},
+            "prefill_tokens_per_s": r["prefill_tokens_per_s"], "decode_tokens_per_s": r["decode_tokens_per_s"],
             "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
