@@ -99,6 +99,9 @@ int b2_gemm_w8a8_sched(const int8_t* A, const int8_t* W, const float* a_scale, c
  *               (atomic; the caller -- or an earlier call through zero_amax -- zeroes it first).
  *               act: 0 silu, 1 gelu_new.  residual must be NULL.
  * zero_amax: optional [M] floats this launch sets to 0 (so a chain of calls needs no memset).
+ * prefetch0/1 (+_bytes): optional device ranges (NULL/0 = none) -- typically the first ~24 MB of the
+ * weight matrices the NEXT launches will stream; the kernel issues L2 bulk prefetches for them at
+ * its start so the successor's ramp-up hits L2 and HBM stays busy across the launch boundary.
  * x_ld: row stride of x in elements.  K % 16 == 0.  M > 8 returns B2_ERR_UNSUPPORTED (use the
  * unfused entry points, which run the tensor-core schedule).
  * Replaces: the same reference calls as b2_norm_quant + b2_gemm_w8a8 + b2_act_mul_quant, inside the
@@ -106,7 +109,8 @@ int b2_gemm_w8a8_sched(const int8_t* A, const int8_t* W, const float* a_scale, c
 int b2_fused_linear(const void* x, long long x_ld, int x_kind, const void* gamma, const void* beta, const float* smooth,
                     const float* x_amax, float eps, const int8_t* W, const float* w_scale, const void* bias,
                     const void* residual, void* out, int out_kind, int act, const float* out_smooth, float* out_amax,
-                    float* zero_amax, int M, int N, int K, void* stream);
+                    float* zero_amax, int M, int N, int K, const void* prefetch0, long long prefetch0_bytes,
+                    const void* prefetch1, long long prefetch1_bytes, void* stream);
 
 /* Decode-time (M <= 8) qkv projection with everything around it fused: activation prologue
  * (x_kind 0/1/2 as in b2_fused_linear) -> int8 quantise -> W8A8 GEMV over W = [q;k;v] ->
@@ -118,7 +122,9 @@ int b2_fused_linear(const void* x, long long x_ld, int x_kind, const void* gamma
 int b2_fused_qkv(const void* x, long long x_ld, int x_kind, const void* gamma, const void* beta, const float* smooth,
                  float eps, const int8_t* W, const float* w_scale, const void* bias, void* qkv_out,
                  const float* cos_table, const float* sin_table, const int* positions, const int* seq_ids, int seq0,
-                 void* kcache, void* vcache, int M, int H, int KV, int hd, int Smax, int K, int use_rope, void* stream);
+                 void* kcache, void* vcache, int M, int H, int KV, int hd, int Smax, int K, int use_rope,
+                 const void* prefetch0, long long prefetch0_bytes, const void* prefetch1, long long prefetch1_bytes,
+                 void* stream);
 
 /* Rotary embedding of q and k (in fp32 from a caller-supplied cos/sin table [max_pos, hd/2] fp32)
  * and append of rotated k and v to the KV cache.  qkv [T, ld] fp16: q heads at columns

@@ -37,9 +37,9 @@ SIGNATURES = {
     "b2_embed": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
     "b2_lm_head": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
     "b2_fused_linear": (_i, [_vp, _ll, _i, _vp, _vp, _vp, _vp, _f, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp,
-                             _i, _i, _i, _vp]),
+                             _i, _i, _i, _vp, _ll, _vp, _ll, _vp]),
     "b2_fused_qkv": (_i, [_vp, _ll, _i, _vp, _vp, _vp, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp,
-                          _i, _i, _i, _i, _i, _i, _i, _vp]),
+                          _i, _i, _i, _i, _i, _i, _i, _vp, _ll, _vp, _ll, _vp]),
     "b2_argmax": (_i, [_vp, _vp, _i, _i, _vp]),
 }
 

@@ -27,10 +27,10 @@ int init_misc();
 int init_fused();
 int fused_qkv(const void*, long long, int, const void*, const void*, const float*, float, const int8_t*, const float*,
               const void*, void*, const float*, const float*, const int*, const int*, int, void*, void*, int, int, int,
-              int, int, int, int, cudaStream_t);
+              int, int, int, int, const void*, long long, const void*, long long, cudaStream_t);
 int fused_linear(const void*, long long, int, const void*, const void*, const float*, const float*, float, const int8_t*,
                  const float*, const void*, const void*, void*, int, int, const float*, float*, float*, int, int, int,
-                 cudaStream_t);
+                 const void*, long long, const void*, long long, cudaStream_t);
 int embed(const long long*, const int*, const void*, const void*, void*, int, int, int, cudaStream_t);
 int argmax_rows(const float*, long long*, int, int, cudaStream_t);
 }  // namespace b2
@@ -91,16 +91,21 @@ int b2_gemm_w8a8_sched(const int8_t* A, const int8_t* W, const float* a_scale, c
 int b2_fused_linear(const void* x, long long x_ld, int x_kind, const void* gamma, const void* beta, const float* smooth,
                     const float* x_amax, float eps, const int8_t* W, const float* w_scale, const void* bias,
                     const void* residual, void* out, int out_kind, int act, const float* out_smooth, float* out_amax,
-                    float* zero_amax, int M, int N, int K, void* stream) {
+                    float* zero_amax, int M, int N, int K, const void* prefetch0, long long prefetch0_bytes,
+                    const void* prefetch1, long long prefetch1_bytes, void* stream) {
   return b2::fused_linear(x, x_ld, x_kind, gamma, beta, smooth, x_amax, eps, W, w_scale, bias, residual, out, out_kind,
-                          act, out_smooth, out_amax, zero_amax, M, N, K, ST(stream));
+                          act, out_smooth, out_amax, zero_amax, M, N, K, prefetch0, prefetch0_bytes, prefetch1,
+                          prefetch1_bytes, ST(stream));
 }
 int b2_fused_qkv(const void* x, long long x_ld, int x_kind, const void* gamma, const void* beta, const float* smooth,
                  float eps, const int8_t* W, const float* w_scale, const void* bias, void* qkv_out,
                  const float* cos_table, const float* sin_table, const int* positions, const int* seq_ids, int seq0,
-                 void* kcache, void* vcache, int M, int H, int KV, int hd, int Smax, int K, int use_rope, void* stream) {
+                 void* kcache, void* vcache, int M, int H, int KV, int hd, int Smax, int K, int use_rope,
+                 const void* prefetch0, long long prefetch0_bytes, const void* prefetch1, long long prefetch1_bytes,
+                 void* stream) {
   return b2::fused_qkv(x, x_ld, x_kind, gamma, beta, smooth, eps, W, w_scale, bias, qkv_out, cos_table, sin_table,
-                       positions, seq_ids, seq0, kcache, vcache, M, H, KV, hd, Smax, K, use_rope, ST(stream));
+                       positions, seq_ids, seq0, kcache, vcache, M, H, KV, hd, Smax, K, use_rope, prefetch0,
+                       prefetch0_bytes, prefetch1, prefetch1_bytes, ST(stream));
 }
 int b2_rope_kv_append(void* qkv, long long ld, const float* cos_table, const float* sin_table, const int* positions,
                       const int* seq_ids, int seq0, void* kcache, void* vcache, int T, int H, int KV, int hd, int Smax,

@@ -34,6 +34,8 @@ struct FusedParams {
   float* out_amax;                               // O_GATED: [M] running absmax (atomicMax; caller zeroes)
   float* zero_amax;                              // housekeeping: [M] floats this launch sets to 0, or nullptr
   int M, N, K, act;
+  // L2 prefetch hints: weights a LATER kernel will stream (issued at kernel start, split over the CTAs)
+  const uint8_t* pf0; long long pf0_bytes; const uint8_t* pf1; long long pf1_bytes;
   // O_QKV: rotary embedding + KV-cache append in the epilogue (q written rotated to `out`)
   const float* cosT; const float* sinT; const int* positions; const int* seq_ids; int seq0;
   __half* kcache; __half* vcache; int H, KV, hd, Smax, use_rope;
@@ -50,6 +52,17 @@ B2_DEVINL void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 B2_DEVINL void fl_cp_async16(void* smem_dst, const void* src) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(src) : "memory");
+}
+// this CTA's share of an L2 prefetch of [ptr, ptr+bytes): 16 KB bulk-prefetch requests
+B2_DEVINL void fl_prefetch_slice(const uint8_t* ptr, long long bytes) {
+  if (ptr == nullptr || bytes <= 0) return;
+  constexpr long long PIECE = 16 * 1024;
+  const long long npieces = (bytes + PIECE - 1) / PIECE;
+  for (long long i = blockIdx.x; i < npieces; i += gridDim.x) {
+    const long long off = i * PIECE;
+    const uint32_t n = (uint32_t)((bytes - off < PIECE ? bytes - off : PIECE) & ~15ll);
+    if (n) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(ptr + off), "r"(n) : "memory");
+  }
 }
 B2_DEVINL double fl_block_sum_d(double v, double* sh) {
   v = warp_sum_d(v);
@@ -152,6 +165,12 @@ __global__ void __launch_bounds__(FL_THREADS, 2) fused_gemv_kernel(const FusedPa
   };
   // ---- 1. first two weight batches: independent of the predecessor kernel ----------------------
   pdl_launch_dependents();
+  if (threadIdx.x == 0) {
+    // Pull the head of the next kernels' weights into L2 while this kernel streams its own: the
+    // successor's ramp-up then hits L2 and HBM never idles across the kernel boundary.
+    fl_prefetch_slice(p.pf0, p.pf0_bytes);
+    fl_prefetch_slice(p.pf1, p.pf1_bytes);
+  }
   uint4 w[FL_UNR][FL_ROWS], w2[FL_UNR][FL_ROWS];
   Cur cc;
   cc.it = blockIdx.x * FL_WARPS + warp; cc.j = 0; cc.r0 = p.W; cc.r1 = p.W;
@@ -541,7 +560,8 @@ static int dispatch_x(int xk, const FusedParams& p, cudaStream_t st) {
 int fused_linear(const void* x, long long x_ld, int x_kind, const void* gamma, const void* beta, const float* smooth,
                  const float* x_amax, float eps, const int8_t* W, const float* w_scale, const void* bias,
                  const void* residual, void* out, int out_kind, int act, const float* out_smooth, float* out_amax,
-                 float* zero_amax, int M, int N, int K, cudaStream_t st) {
+                 float* zero_amax, int M, int N, int K, const void* pf0, long long pf0_bytes, const void* pf1,
+                 long long pf1_bytes, cudaStream_t st) {
   if (M == 0 || N == 0) return OK;
   if (!x || !W || !w_scale || !out) return ERR_NULL_PTR;
   if (M < 0 || M > 8) return ERR_UNSUPPORTED;
@@ -557,6 +577,7 @@ int fused_linear(const void* x, long long x_ld, int x_kind, const void* gamma, c
   p.x_amax = x_amax; p.eps = eps; p.W = W; p.w_scale = w_scale; p.bias = (const __half*)bias;
   p.residual = (const __half*)residual; p.out = out; p.out_smooth = out_smooth; p.out_amax = out_amax;
   p.zero_amax = zero_amax; p.M = M; p.N = N; p.K = K; p.act = act;
+  p.pf0 = (const uint8_t*)pf0; p.pf0_bytes = pf0_bytes; p.pf1 = (const uint8_t*)pf1; p.pf1_bytes = pf1_bytes;
   if (out_kind == O_F16) return dispatch_x<O_F16>(x_kind, p, st);
   if (out_kind == O_GATED) return dispatch_x<O_GATED>(x_kind, p, st);
   return ERR_UNSUPPORTED;
@@ -566,7 +587,8 @@ int fused_linear(const void* x, long long x_ld, int x_kind, const void* gamma, c
 int fused_qkv(const void* x, long long x_ld, int x_kind, const void* gamma, const void* beta, const float* smooth,
               float eps, const int8_t* W, const float* w_scale, const void* bias, void* qkv_out, const float* cosT,
               const float* sinT, const int* positions, const int* seq_ids, int seq0, void* kcache, void* vcache, int M,
-              int H, int KV, int hd, int Smax, int K, int use_rope, cudaStream_t st) {
+              int H, int KV, int hd, int Smax, int K, int use_rope, const void* pf0, long long pf0_bytes,
+              const void* pf1, long long pf1_bytes, cudaStream_t st) {
   if (M == 0) return OK;
   if (!x || !W || !w_scale || !qkv_out || !positions || !kcache || !vcache) return ERR_NULL_PTR;
   if (use_rope && (!cosT || !sinT)) return ERR_NULL_PTR;
@@ -584,6 +606,7 @@ int fused_qkv(const void* x, long long x_ld, int x_kind, const void* gamma, cons
   p.cosT = cosT; p.sinT = sinT; p.positions = positions; p.seq_ids = seq_ids; p.seq0 = seq0;
   p.kcache = (__half*)kcache; p.vcache = (__half*)vcache; p.H = H; p.KV = KV; p.hd = hd; p.Smax = Smax;
   p.use_rope = use_rope;
+  p.pf0 = (const uint8_t*)pf0; p.pf0_bytes = pf0_bytes; p.pf1 = (const uint8_t*)pf1; p.pf1_bytes = pf1_bytes;
   switch (x_kind) {
     case X_RMS: return dispatch_m<X_RMS, O_QKV>(p, st);
     case X_LN: return dispatch_m<X_LN, O_QKV>(p, st);

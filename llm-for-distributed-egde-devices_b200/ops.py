@@ -86,32 +86,49 @@ X_RMS, X_LN, X_PLAIN, X_Y32 = 0, 1, 2, 3
 O_F16, O_GATED = 0, 1
 
 
+PREFETCH_BYTES = 24 << 20      # head of a weight matrix worth pulling into L2 ahead of its kernel
+
+
+def _pf(prefetch, i):
+    """(pointer, bytes) of the i-th prefetch hint: a tensor (its first PREFETCH_BYTES) or None."""
+    if prefetch is None or i >= len(prefetch) or prefetch[i] is None:
+        return None, 0
+    t = prefetch[i]
+    return ptr(t), min(t.numel() * t.element_size(), PREFETCH_BYTES)
+
+
 def fused_linear(x, w_q, w_scale, *, x_kind, out, gamma=None, beta=None, smooth=None, x_amax=None, eps=1e-5, bias=None,
-                 residual=None, out_kind=O_F16, act=0, out_smooth=None, out_amax=None, zero_amax=None):
+                 residual=None, out_kind=O_F16, act=0, out_smooth=None, out_amax=None, zero_amax=None, prefetch=None):
     """Decode-time (M <= 8) prologue + quantise + W8A8 GEMV + epilogue in one launch.  b2_fused_linear.
-    x: fp16 [M,K] (x_kind 0..2) or fp32 [M,K] (x_kind 3); out: fp16 [M,N] or fp32 [M,N/2] (gated)."""
+    x: fp16 [M,K] (x_kind 0..2) or fp32 [M,K] (x_kind 3); out: fp16 [M,N] or fp32 [M,N/2] (gated).
+    prefetch: up to two weight tensors of later launches whose heads are pulled into L2."""
     _cuda(w_q, w_scale, gamma, beta, smooth, x_amax, bias, residual, out, out_smooth, out_amax, zero_amax)
     if not x.is_cuda or x.stride(-1) != 1:
         raise ValueError("x must be a CUDA tensor with unit inner stride")
     M = x.shape[0]
     N, K = w_q.shape
+    p0, n0 = _pf(prefetch, 0)
+    p1, n1 = _pf(prefetch, 1)
     check(_abi.lib().b2_fused_linear(ptr(x), x.stride(0), int(x_kind), ptr(gamma), ptr(beta), ptr(smooth), ptr(x_amax),
                                      float(eps), ptr(w_q), ptr(w_scale), ptr(bias), ptr(residual), ptr(out), int(out_kind),
-                                     int(act), ptr(out_smooth), ptr(out_amax), ptr(zero_amax), M, N, K, stream_handle()),
+                                     int(act), ptr(out_smooth), ptr(out_amax), ptr(zero_amax), M, N, K, p0, n0, p1, n1,
+                                     stream_handle()),
           "b2_fused_linear")
     return out
 
 
 def fused_qkv(x, w_q, w_scale, qkv_out, cos, sin, positions, kcache, vcache, H, KV, hd, *, x_kind, gamma=None,
-              beta=None, smooth=None, eps=1e-5, bias=None, seq_ids=None, seq0=0, use_rope=True):
+              beta=None, smooth=None, eps=1e-5, bias=None, seq_ids=None, seq0=0, use_rope=True, prefetch=None):
     """Decode-time qkv projection + RoPE + KV append in one launch (M <= 8).  b2_fused_qkv."""
     _cuda(x, w_q, w_scale, qkv_out, cos, sin, positions, kcache, vcache, gamma, beta, smooth, bias, seq_ids)
     M, K = x.shape
     Smax = kcache.shape[2]
+    p0, n0 = _pf(prefetch, 0)
+    p1, n1 = _pf(prefetch, 1)
     check(_abi.lib().b2_fused_qkv(ptr(x), x.stride(0), int(x_kind), ptr(gamma), ptr(beta), ptr(smooth), float(eps),
                                   ptr(w_q), ptr(w_scale), ptr(bias), ptr(qkv_out), ptr(cos), ptr(sin), ptr(positions),
                                   ptr(seq_ids), int(seq0), ptr(kcache), ptr(vcache), M, H, KV, hd, Smax, K,
-                                  int(bool(use_rope)), stream_handle()), "b2_fused_qkv")
+                                  int(bool(use_rope)), p0, n0, p1, n1, stream_handle()), "b2_fused_qkv")
     return qkv_out
 
 

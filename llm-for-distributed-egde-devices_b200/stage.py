@@ -95,6 +95,7 @@ class Stage:
         self._runners = {}
         self.launches = 0          # kernels of ours launched (bench.py's gpu_launches claim)
         self.fuse_decode = True    # decode steps with <= 8 tokens use b2_fused_linear
+        self.l2_prefetch = True    # fused decode kernels pull the head of the next weights into L2
 
     # ------------------------------------------------------------------------------------------
     @classmethod
@@ -158,13 +159,15 @@ class Stage:
               (ops.ACT_GELU if cfg.act == "gelu_new" else ops.ACT_SILU)
         fused = self.fuse_decode and decode and T <= 8 and trace is None
         xk_norm = ops.X_LN if cfg.norm == "layernorm" else ops.X_RMS
-        for li, lw in enumerate(self.w["layers"]):
+        layers = self.w["layers"]
+        for li, lw in enumerate(layers):
             kc, vc = kv_cache.k[li], kv_cache.v[li]
             if fused:
                 # 6-7 launches per layer: every linear redoes its (tiny) activation prologue in-kernel
                 ops.fused_qkv(h, lw["wqkv"], lw["s_qkv"], qkv, self.cos, self.sin, dpos, kc, vc, H, KV, hd,
                               x_kind=xk_norm, gamma=lw["ln1_g"], beta=lw.get("ln1_b"), smooth=lw["sm_qkv"],
-                              eps=cfg.eps, bias=lw.get("b_qkv"), seq_ids=dseq, seq0=row0, use_rope=cfg.rope)
+                              eps=cfg.eps, bias=lw.get("b_qkv"), seq_ids=dseq, seq0=row0, use_rope=cfg.rope,
+                              prefetch=(lw["wo"], lw["wgu"]) if self.l2_prefetch else None)
                 ops.decode_attn(qkv, kc, vc, dlens, H, KV, hd, max_len, self.scale, cfg.window, rows=dseq, out=attn,
                                 workspace=ws)
                 ops.fused_linear(attn, lw["wo"], lw["s_o"], x_kind=ops.X_PLAIN, smooth=lw["sm_o"], bias=lw.get("b_o"),
@@ -174,9 +177,12 @@ class Stage:
                     ops.fused_linear(h_alt, lw["wgu"], lw["s_gu"], x_kind=xk_norm, gamma=lw["ln2_g"],
                                      beta=lw.get("ln2_b"), smooth=lw["sm_gu"], eps=cfg.eps, bias=lw.get("b_gu"),
                                      out=buf.y32[:T], out_kind=ops.O_GATED, act=0 if cfg.act == "silu" else 1,
-                                     out_smooth=lw["sm_d"], out_amax=buf.amax)
+                                     out_smooth=lw["sm_d"], out_amax=buf.amax,
+                                     prefetch=(lw["wd"],) if self.l2_prefetch else None)
+                    nxt = layers[li + 1]["wqkv"] if li + 1 < len(layers) else self.w.get("lm_head")
                     ops.fused_linear(buf.y32[:T], lw["wd"], lw["s_d"], x_kind=ops.X_Y32, x_amax=buf.amax,
-                                     bias=lw.get("b_d"), residual=h_alt, out=h)
+                                     bias=lw.get("b_d"), residual=h_alt, out=h,
+                                     prefetch=(nxt,) if self.l2_prefetch else None)
                     n += 2
                 else:
                     ops.fused_linear(h_alt, lw["wgu"], lw["s_gu"], x_kind=xk_norm, gamma=lw["ln2_g"],
