@@ -126,6 +126,36 @@ int b2_fused_qkv(const void* x, long long x_ld, int x_kind, const void* gamma, c
                  const void* prefetch0, long long prefetch0_bytes, const void* prefetch1, long long prefetch1_bytes,
                  void* stream);
 
+/* One fused linear of a decode-time chain: the arguments of b2_fused_linear / b2_fused_qkv as a plain
+ * struct (unused fields zero / NULL).  out_kind 2 = qkv projection with rotary + KV append
+ * (b2_fused_qkv semantics: N = (H+2KV)*hd, `out` = the qkv buffer). */
+typedef struct b2_fused_desc {
+  const void* x; long long x_ld; int x_kind;
+  const void* gamma; const void* beta; const float* smooth; const float* x_amax; float eps;
+  const int8_t* W; const float* w_scale; const void* bias; const void* residual;
+  void* out; int out_kind; int act; const float* out_smooth; float* out_amax; float* zero_amax;
+  int N, K;
+  const float* cos_table; const float* sin_table; const int* positions; const int* seq_ids; int seq0;
+  void* kcache; void* vcache; int H, KV, hd, Smax, use_rope;
+  const void* prefetch0; long long prefetch0_bytes; const void* prefetch1; long long prefetch1_bytes;
+} b2_fused_desc;
+
+/* The dependent tail of a gated decoder layer for M <= 8 tokens in ONE persistent launch:
+ *   o_proj (x_kind 2, out_kind 0) -> gate_up (x_kind 0|1, out_kind 1) -> down (x_kind 3, out_kind 0)
+ *   [-> next_qkv (x_kind 0|1, out_kind 2), may be NULL]
+ * Each phase consumes the previous phase's output; phases are separated by grid-wide barriers and
+ * every phase starts streaming its weights before the barrier that precedes it.  Results are
+ * bit-identical to the same linears issued one by one.
+ * counters: device, 4 x uint32, ALL ZERO on entry (three barrier counters + an error flag; the
+ * caller zeroes them again before reusing them; counters[3] != 0 afterwards means a barrier timed
+ * out, i.e. the launch was not fully co-resident).  The launch sizes its grid from the occupancy
+ * so that all CTAs are resident at once; do not run it concurrently with kernels that would take
+ * whole SMs away from it.
+ * Replaces: the same reference calls as b2_fused_linear / b2_fused_qkv (decode loop of
+ * `model.generate`, models_quant_updated.py:84-93). */
+int b2_fused_layer_tail(const b2_fused_desc* o_proj, const b2_fused_desc* gate_up, const b2_fused_desc* down,
+                        const b2_fused_desc* next_qkv, int M, unsigned int* counters, void* stream);
+
 /* Rotary embedding of q and k (in fp32 from a caller-supplied cos/sin table [max_pos, hd/2] fp32)
  * and append of rotated k and v to the KV cache.  qkv [T, ld] fp16: q heads at columns
  * [0,H*hd), k at [H*hd,(H+KV)*hd), v after; q is rotated in place.  positions [T] int32;

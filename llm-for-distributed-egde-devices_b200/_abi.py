@@ -40,8 +40,25 @@ SIGNATURES = {
                              _i, _i, _i, _vp, _ll, _vp, _ll, _vp]),
     "b2_fused_qkv": (_i, [_vp, _ll, _i, _vp, _vp, _vp, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp,
                           _i, _i, _i, _i, _i, _i, _i, _vp, _ll, _vp, _ll, _vp]),
+    "b2_fused_layer_tail": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp]),
     "b2_argmax": (_i, [_vp, _vp, _i, _i, _vp]),
 }
+
+
+
+class FusedDesc(C.Structure):
+    """struct b2_fused_desc (include/b200stage.h)."""
+    _fields_ = [
+        ("x", _vp), ("x_ld", _ll), ("x_kind", _i),
+        ("gamma", _vp), ("beta", _vp), ("smooth", _vp), ("x_amax", _vp), ("eps", _f),
+        ("W", _vp), ("w_scale", _vp), ("bias", _vp), ("residual", _vp),
+        ("out", _vp), ("out_kind", _i), ("act", _i), ("out_smooth", _vp), ("out_amax", _vp), ("zero_amax", _vp),
+        ("N", _i), ("K", _i),
+        ("cos_table", _vp), ("sin_table", _vp), ("positions", _vp), ("seq_ids", _vp), ("seq0", _i),
+        ("kcache", _vp), ("vcache", _vp), ("H", _i), ("KV", _i), ("hd", _i), ("Smax", _i), ("use_rope", _i),
+        ("prefetch0", _vp), ("prefetch0_bytes", _ll), ("prefetch1", _vp), ("prefetch1_bytes", _ll),
+    ]
+
 
 _lib = None
 

@@ -25,6 +25,8 @@ int init_attn();
 int init_rowquant();
 int init_misc();
 int init_fused();
+int fused_layer_tail(const b2_fused_desc*, const b2_fused_desc*, const b2_fused_desc*, const b2_fused_desc*, int, unsigned*,
+                     cudaStream_t);
 int fused_qkv(const void*, long long, int, const void*, const void*, const float*, float, const int8_t*, const float*,
               const void*, void*, const float*, const float*, const int*, const int*, int, void*, void*, int, int, int,
               int, int, int, int, const void*, long long, const void*, long long, cudaStream_t);
@@ -106,6 +108,10 @@ int b2_fused_qkv(const void* x, long long x_ld, int x_kind, const void* gamma, c
   return b2::fused_qkv(x, x_ld, x_kind, gamma, beta, smooth, eps, W, w_scale, bias, qkv_out, cos_table, sin_table,
                        positions, seq_ids, seq0, kcache, vcache, M, H, KV, hd, Smax, K, use_rope, prefetch0,
                        prefetch0_bytes, prefetch1, prefetch1_bytes, ST(stream));
+}
+int b2_fused_layer_tail(const b2_fused_desc* o_proj, const b2_fused_desc* gate_up, const b2_fused_desc* down,
+                        const b2_fused_desc* next_qkv, int M, unsigned int* counters, void* stream) {
+  return b2::fused_layer_tail(o_proj, gate_up, down, next_qkv, M, counters, ST(stream));
 }
 int b2_rope_kv_append(void* qkv, long long ld, const float* cos_table, const float* sin_table, const int* positions,
                       const int* seq_ids, int seq0, void* kcache, void* vcache, int T, int H, int KV, int hd, int Smax,

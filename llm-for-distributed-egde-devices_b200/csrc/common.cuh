@@ -75,6 +75,11 @@ B2_DEVINL uint4 ld_nc_v4(const void* p) {   // streaming read-only, no L1 alloca
   return r;
 }
 B2_DEVINL uint4 ld_v4(const void* p) { return *reinterpret_cast<const uint4*>(p); }
+B2_DEVINL uint4 ld_cg_v4(const void* p) {    // L2-coherent: data another CTA of the same launch may have written
+  uint4 r;
+  asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+  return r;
+}
 B2_DEVINL void st_v4(void* p, const uint4& v) { *reinterpret_cast<uint4*>(p) = v; }
 B2_DEVINL uint2 ld_nc_v2(const void* p) {
   uint2 r;

@@ -15,7 +15,9 @@
 //
 // Reference call sites replaced: the same as b2_norm_quant / b2_gemm_w8a8 / b2_act_mul_quant
 // (Code/Quantised Models/models_quant_updated.py:30-38, :84-93 decode loop).
+#include <algorithm>
 #include "common.cuh"
+#include "../../include/b200stage.h"
 
 namespace b2 {
 
@@ -89,12 +91,12 @@ B2_DEVINL float fl_block_max(float v, float* sh) {
 template <int XK>
 B2_DEVINL void fl_load_y(const FusedParams& p, const void* xrow, int ch, float r, float mean, float (&y)[8]) {
   if (XK == X_Y32) {
-    const float4 a = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(xrow) + ch * 8);
-    const float4 b = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(xrow) + ch * 8 + 4);
+    const float4 a = __ldcg(reinterpret_cast<const float4*>(reinterpret_cast<const float*>(xrow) + ch * 8));
+    const float4 b = __ldcg(reinterpret_cast<const float4*>(reinterpret_cast<const float*>(xrow) + ch * 8 + 4));
     y[0] = a.x; y[1] = a.y; y[2] = a.z; y[3] = a.w; y[4] = b.x; y[5] = b.y; y[6] = b.z; y[7] = b.w;
     return;                                       // smoothing was applied by the producer
   }
-  const uint4 u = ld_v4(reinterpret_cast<const __half*>(xrow) + ch * 8);
+  const uint4 u = ld_cg_v4(reinterpret_cast<const __half*>(xrow) + ch * 8);
   const float2 a0 = h2_to_f2(u.x), a1 = h2_to_f2(u.y), a2 = h2_to_f2(u.z), a3 = h2_to_f2(u.w);
   y[0] = a0.x; y[1] = a0.y; y[2] = a1.x; y[3] = a1.y; y[4] = a2.x; y[5] = a2.y; y[6] = a3.x; y[7] = a3.y;
   if (XK == X_RMS || XK == X_LN) {
@@ -124,9 +126,14 @@ B2_DEVINL void fl_load_y(const FusedParams& p, const void* xrow, int ch, float r
   }
 }
 
-template <int MT, int XK, int OKIND>
-__global__ void __launch_bounds__(FL_THREADS, 2) fused_gemv_kernel(const FusedParams p) {
-  extern __shared__ __align__(16) uint8_t xs[];        // int8 activations [MT][K]
+// One fused linear = one "phase".  SYNC is what separates the part that may run ahead of the
+// producer of x (cursor set-up, first weight batches, staging of gains/multipliers) from the part that
+// consumes x: griddepcontrol.wait when the phase is a kernel of its own, a grid barrier when it is a
+// later phase of a multi-phase persistent kernel.  FIRST = false inserts the CTA barrier that
+// protects the previous phase's shared memory.  Activations written by other CTAs are read with
+// L2-coherent (.cg) loads: L1 is not invalidated between phases of one kernel.
+template <int MT, int XK, int OKIND, bool FIRST, class SYNC>
+B2_DEVINL void fused_phase(const FusedParams& p, uint8_t* xs, SYNC sync_fn, bool trigger) {
   __shared__ double shd[FL_WARPS];
   __shared__ float shf[FL_WARPS];
   __shared__ float s_scale[MT];
@@ -164,7 +171,7 @@ __global__ void __launch_bounds__(FL_THREADS, 2) fused_gemv_kernel(const FusedPa
     }
   };
   // ---- 1. first two weight batches: independent of the predecessor kernel ----------------------
-  pdl_launch_dependents();
+  if (trigger) pdl_launch_dependents();
   if (threadIdx.x == 0) {
     // Pull the head of the next kernels' weights into L2 while this kernel streams its own: the
     // successor's ramp-up then hits L2 and HBM never idles across the kernel boundary.
@@ -178,6 +185,7 @@ __global__ void __launch_bounds__(FL_THREADS, 2) fused_gemv_kernel(const FusedPa
   Cur lc = cc;
   load_batch(w, lc); advance(lc);
   load_batch(w2, lc); advance(lc);
+  if (!FIRST) __syncthreads();     // every warp has left the previous phase: its shared memory may be reused
   // Norm gains / smoothing multipliers are weights too: stage them in shared memory with cp.async
   // before the dependency wait, so the prologue's critical path is one L2 read of x plus two block
   // reductions (fast path: rows of up to FP_MAXC*256*8 = 6144 elements held in registers).
@@ -197,7 +205,7 @@ __global__ void __launch_bounds__(FL_THREADS, 2) fused_gemv_kernel(const FusedPa
     asm volatile("cp.async.commit_group;" ::: "memory");
   }
   // ---- 2. everything below may read the predecessor's output ---------------------------------
-  pdl_wait();
+  sync_fn();
   if (p.zero_amax != nullptr && blockIdx.x == 0 && threadIdx.x < p.M) p.zero_amax[threadIdx.x] = 0.0f;
   if (fast) {
     asm volatile("cp.async.wait_group 0;" ::: "memory");
@@ -223,7 +231,7 @@ __global__ void __launch_bounds__(FL_THREADS, 2) fused_gemv_kernel(const FusedPa
       for (int c = 0; c < FP_MAXC; ++c) {
         const int ch = threadIdx.x + c * FL_THREADS;
         if (ch < nchunk) {
-          const uint4 u = ld_v4(reinterpret_cast<const __half*>(xrow) + ch * 8);
+          const uint4 u = ld_cg_v4(reinterpret_cast<const __half*>(xrow) + ch * 8);
           const float2 a0 = h2_to_f2(u.x), a1 = h2_to_f2(u.y), a2 = h2_to_f2(u.z), a3 = h2_to_f2(u.w);
           v[c][0] = a0.x; v[c][1] = a0.y; v[c][2] = a1.x; v[c][3] = a1.y;
           v[c][4] = a2.x; v[c][5] = a2.y; v[c][6] = a3.x; v[c][7] = a3.y;
@@ -304,7 +312,7 @@ __global__ void __launch_bounds__(FL_THREADS, 2) fused_gemv_kernel(const FusedPa
     if (XK == X_RMS || XK == X_LN) {
       double s1 = 0.0, s2 = 0.0;
       for (int ch = threadIdx.x; ch < nchunk; ch += FL_THREADS) {
-        const uint4 u = ld_v4(reinterpret_cast<const __half*>(xrow) + ch * 8);
+        const uint4 u = ld_cg_v4(reinterpret_cast<const __half*>(xrow) + ch * 8);
         const uint32_t* pu = &u.x;
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
@@ -328,7 +336,7 @@ __global__ void __launch_bounds__(FL_THREADS, 2) fused_gemv_kernel(const FusedPa
       r = div_rn(1.0f, __fsqrt_rn(add_rn(var, p.eps)));
     }
     if (XK == X_Y32) {
-      amax = p.x_amax[m];
+      amax = __ldcg(p.x_amax + m);
     } else {
       for (int ch = threadIdx.x; ch < nchunk; ch += FL_THREADS) {
         float y[8];
@@ -399,7 +407,7 @@ __global__ void __launch_bounds__(FL_THREADS, 2) fused_gemv_kernel(const FusedPa
               const long long off = (long long)m * p.N + n;
               float v = mul_rn(mul_rn((float)res[r][m], s_scale[m]), ws);
               if (p.bias) v = add_rn(v, bv);
-              if (p.residual) v = add_rn(v, __half2float(p.residual[off]));
+              if (p.residual) v = add_rn(v, __half2float(__ushort_as_half(__ldcg(reinterpret_cast<const unsigned short*>(p.residual + off)))));
               out[off] = __float2half_rn(v);
             }
           }
@@ -494,6 +502,54 @@ __global__ void __launch_bounds__(FL_THREADS, 2) fused_gemv_kernel(const FusedPa
     step(w2);
   }
   flush();
+}
+
+struct SyncPDL {
+  B2_DEVINL void operator()() const { pdl_wait(); }
+};
+// Barrier across all CTAs of a persistent launch (all co-resident: the launcher sizes the grid
+// from the occupancy).  `ctr` starts at 0 (zeroed by the caller before the launch) and is used once.
+// The spin is bounded so that a broken residency assumption ends as an error flag, not as a hung GPU.
+struct SyncGrid {
+  unsigned* ctr;
+  unsigned* err;
+  B2_DEVINL void operator()() const {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      atomicAdd(ctr, 1u);
+      unsigned v, spins = 0;
+      do {
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
+        if (v >= gridDim.x) break;
+        // no back-off: the wait is short and latency matters more than the polling traffic
+      } while (++spins < (1u << 24));
+      if (v < gridDim.x && err) atomicExch(err, 1u);
+      __threadfence();
+    }
+    __syncthreads();
+  }
+};
+
+template <int MT, int XK, int OKIND>
+__global__ void __launch_bounds__(FL_THREADS, 2) fused_gemv_kernel(const FusedParams p) {
+  extern __shared__ __align__(16) uint8_t xs[];        // int8 activations [MT][K] + staging
+  fused_phase<MT, XK, OKIND, true>(p, xs, SyncPDL{}, true);
+}
+
+// The dependent tail of a decoder layer in ONE persistent launch:
+//   o_proj (+residual) | gate_up (+act*up) | down (+residual) | [next layer's qkv (+rope, KV append)]
+// Each phase issues its first weight batches and its L2 hints BEFORE the grid barrier that ends the
+// previous phase, so the HBM stream does not stop at the three dependency points.
+template <int MT, int NORMK, bool QKV>
+__global__ void __launch_bounds__(FL_THREADS, 2)
+fused_tail_kernel(const FusedParams po, const FusedParams pg, const FusedParams pd, const FusedParams pq, unsigned* ctr) {
+  extern __shared__ __align__(16) uint8_t xs[];
+  unsigned* err = ctr + 3;
+  fused_phase<MT, X_PLAIN, O_F16, true>(po, xs, SyncPDL{}, false);
+  fused_phase<MT, NORMK, O_GATED, false>(pg, xs, SyncGrid{ctr + 0, err}, false);
+  fused_phase<MT, X_Y32, O_F16, false>(pd, xs, SyncGrid{ctr + 1, err}, !QKV);
+  if (QKV) fused_phase<MT, NORMK, O_QKV, false>(pq, xs, SyncGrid{ctr + 2, err}, true);
 }
 
 static int fl_sm_count() {
@@ -612,6 +668,100 @@ int fused_qkv(const void* x, long long x_ld, int x_kind, const void* gamma, cons
     case X_LN: return dispatch_m<X_LN, O_QKV>(p, st);
     default: return dispatch_m<X_PLAIN, O_QKV>(p, st);
   }
+}
+
+// ---------------------------------------------------------------------------------------------
+// multi-phase tail
+// ---------------------------------------------------------------------------------------------
+static int desc_to_params(const b2_fused_desc* d, int M, int want_xk_mask, int want_ok, FusedParams* out) {
+  if (!d || !d->x || !d->W || !d->w_scale || !d->out) return ERR_NULL_PTR;
+  if (d->out_kind != want_ok || !((1 << d->x_kind) & want_xk_mask)) return ERR_UNSUPPORTED;
+  if (d->N <= 0 || d->K <= 0 || (d->K & 15) || (d->x_ld & 7)) return ERR_BAD_SHAPE;
+  if ((d->x_kind == X_RMS || d->x_kind == X_LN) && !d->gamma) return ERR_NULL_PTR;
+  if (d->x_kind == X_LN && !d->beta) return ERR_NULL_PTR;
+  if (d->x_kind == X_Y32 && !d->x_amax) return ERR_NULL_PTR;
+  if (d->out_kind == O_GATED && ((d->N & 1) || !d->out_amax || d->residual)) return ERR_BAD_SHAPE;
+  if (d->out_kind == O_QKV && (!d->positions || !d->kcache || !d->vcache || (d->use_rope && (!d->cos_table || !d->sin_table))))
+    return ERR_NULL_PTR;
+  FusedParams p = {};
+  p.x = d->x; p.x_ld = d->x_ld; p.gamma = (const __half*)d->gamma; p.beta = (const __half*)d->beta; p.smooth = d->smooth;
+  p.x_amax = d->x_amax; p.eps = d->eps; p.W = d->W; p.w_scale = d->w_scale; p.bias = (const __half*)d->bias;
+  p.residual = (const __half*)d->residual; p.out = d->out; p.out_smooth = d->out_smooth; p.out_amax = d->out_amax;
+  p.zero_amax = d->zero_amax; p.M = M; p.N = d->N; p.K = d->K; p.act = d->act;
+  p.cosT = d->cos_table; p.sinT = d->sin_table; p.positions = d->positions; p.seq_ids = d->seq_ids; p.seq0 = d->seq0;
+  p.kcache = (__half*)d->kcache; p.vcache = (__half*)d->vcache; p.H = d->H; p.KV = d->KV; p.hd = d->hd; p.Smax = d->Smax;
+  p.use_rope = d->use_rope;
+  p.pf0 = (const uint8_t*)d->prefetch0; p.pf0_bytes = d->prefetch0_bytes;
+  p.pf1 = (const uint8_t*)d->prefetch1; p.pf1_bytes = d->prefetch1_bytes;
+  if (d->out_kind == O_QKV && p.N != (p.H + 2 * p.KV) * p.hd) return ERR_BAD_SHAPE;
+  *out = p;
+  return OK;
+}
+
+static size_t phase_smem(int MT, int xk, int K) {
+  size_t smem = ((size_t)MT * K + 127) & ~size_t(127);
+  if (xk != X_Y32 && (K >> 3) <= 3 * FL_THREADS) smem += (size_t)8 * K;
+  return smem;
+}
+
+template <int MT, int NORMK, bool QKV>
+static int launch_tail(const FusedParams& po, const FusedParams& pg, const FusedParams& pd, const FusedParams& pq,
+                       unsigned* ctr, cudaStream_t st) {
+  size_t smem = phase_smem(MT, X_PLAIN, po.K);
+  smem = std::max(smem, phase_smem(MT, NORMK, pg.K));
+  smem = std::max(smem, phase_smem(MT, X_Y32, pd.K));
+  if (QKV) smem = std::max(smem, phase_smem(MT, NORMK, pq.K));
+  if (smem > (size_t)FL_SMEM_FULL) return ERR_TOO_LARGE;
+  auto kern = fused_tail_kernel<MT, NORMK, QKV>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, FL_SMEM_FULL) != cudaSuccess) return ERR_ARCH;
+    attr_set = true;
+  }
+  // all CTAs must be resident at once (grid barriers): size the grid from the occupancy
+  int occ = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, FL_THREADS, smem) != cudaSuccess || occ < 1) return ERR_ARCH;
+  if (occ > FL_CTAS_PER_SM) occ = FL_CTAS_PER_SM;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(fl_sm_count() * occ);
+  cfg.blockDim = dim3(FL_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  if (cudaLaunchKernelEx(&cfg, kern, po, pg, pd, pq, ctr) != cudaSuccess) {
+    cudaGetLastError();
+    return ERR_LAUNCH;
+  }
+  return OK;
+}
+
+template <int MT>
+static int dispatch_tail(int normk, bool qkv, const FusedParams& po, const FusedParams& pg, const FusedParams& pd,
+                         const FusedParams& pq, unsigned* ctr, cudaStream_t st) {
+  if (normk == X_RMS) return qkv ? launch_tail<MT, X_RMS, true>(po, pg, pd, pq, ctr, st) : launch_tail<MT, X_RMS, false>(po, pg, pd, pq, ctr, st);
+  return qkv ? launch_tail<MT, X_LN, true>(po, pg, pd, pq, ctr, st) : launch_tail<MT, X_LN, false>(po, pg, pd, pq, ctr, st);
+}
+
+int fused_layer_tail(const b2_fused_desc* o, const b2_fused_desc* gu, const b2_fused_desc* down, const b2_fused_desc* qkv,
+                     int M, unsigned* counters, cudaStream_t st) {
+  if (M == 0) return OK;
+  if (!counters) return ERR_NULL_PTR;
+  if (M < 0 || M > 8) return ERR_UNSUPPORTED;
+  FusedParams po, pg, pd, pq = {};
+  int rc;
+  if ((rc = desc_to_params(o, M, 1 << X_PLAIN, O_F16, &po))) return rc;
+  if ((rc = desc_to_params(gu, M, (1 << X_RMS) | (1 << X_LN), O_GATED, &pg))) return rc;
+  if ((rc = desc_to_params(down, M, 1 << X_Y32, O_F16, &pd))) return rc;
+  if (qkv && (rc = desc_to_params(qkv, M, 1 << gu->x_kind, O_QKV, &pq))) return rc;
+  const int normk = gu->x_kind;
+  if (M == 1) return dispatch_tail<1>(normk, qkv != nullptr, po, pg, pd, pq, counters, st);
+  if (M == 2) return dispatch_tail<2>(normk, qkv != nullptr, po, pg, pd, pq, counters, st);
+  if (M <= 4) return dispatch_tail<4>(normk, qkv != nullptr, po, pg, pd, pq, counters, st);
+  return dispatch_tail<8>(normk, qkv != nullptr, po, pg, pd, pq, counters, st);
 }
 
 template <int MT>

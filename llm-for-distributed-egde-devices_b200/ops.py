@@ -83,7 +83,7 @@ def gemm_w8a8(a_q, w_q, a_scale, w_scale, bias=None, residual=None, out=None, ac
 
 
 X_RMS, X_LN, X_PLAIN, X_Y32 = 0, 1, 2, 3
-O_F16, O_GATED = 0, 1
+O_F16, O_GATED, O_QKV = 0, 1, 2
 
 
 PREFETCH_BYTES = 24 << 20      # head of a weight matrix worth pulling into L2 ahead of its kernel
@@ -130,6 +130,46 @@ def fused_qkv(x, w_q, w_scale, qkv_out, cos, sin, positions, kcache, vcache, H, 
                                   ptr(seq_ids), int(seq0), ptr(kcache), ptr(vcache), M, H, KV, hd, Smax, K,
                                   int(bool(use_rope)), p0, n0, p1, n1, stream_handle()), "b2_fused_qkv")
     return qkv_out
+
+
+def fused_desc(x, w_q, w_scale, *, x_kind, out, out_kind=O_F16, gamma=None, beta=None, smooth=None, x_amax=None,
+               eps=1e-5, bias=None, residual=None, act=0, out_smooth=None, out_amax=None, zero_amax=None,
+               rope=None, prefetch=None):
+    """b2_fused_desc for one phase of fused_layer_tail.  `rope` (out_kind 2 only) =
+    dict(cos, sin, positions, seq_ids, seq0, kcache, vcache, H, KV, hd, use_rope).
+    Returns (struct, keep-alive list)."""
+    d = _abi.FusedDesc()
+    keep = [x, w_q, w_scale, gamma, beta, smooth, x_amax, bias, residual, out, out_smooth, out_amax, zero_amax, prefetch]
+    pv = lambda t: None if t is None else t.data_ptr()
+    d.x, d.x_ld, d.x_kind = pv(x), x.stride(0), int(x_kind)
+    d.gamma, d.beta, d.smooth, d.x_amax, d.eps = pv(gamma), pv(beta), pv(smooth), pv(x_amax), float(eps)
+    d.W, d.w_scale, d.bias, d.residual = pv(w_q), pv(w_scale), pv(bias), pv(residual)
+    d.out, d.out_kind, d.act = pv(out), int(out_kind), int(act)
+    d.out_smooth, d.out_amax, d.zero_amax = pv(out_smooth), pv(out_amax), pv(zero_amax)
+    d.N, d.K = int(w_q.shape[0]), int(w_q.shape[1])
+    if rope is not None:
+        keep.append(rope)
+        d.cos_table, d.sin_table, d.positions = pv(rope["cos"]), pv(rope["sin"]), pv(rope["positions"])
+        d.seq_ids, d.seq0 = pv(rope.get("seq_ids")), int(rope.get("seq0", 0))
+        d.kcache, d.vcache = pv(rope["kcache"]), pv(rope["vcache"])
+        d.H, d.KV, d.hd, d.Smax = int(rope["H"]), int(rope["KV"]), int(rope["hd"]), int(rope["kcache"].shape[2])
+        d.use_rope = int(bool(rope.get("use_rope", True)))
+    for i in (0, 1):
+        p_, n_ = _pf(prefetch, i)
+        setattr(d, f"prefetch{i}", None if p_ is None else p_.value)
+        setattr(d, f"prefetch{i}_bytes", n_)
+    return d, keep
+
+
+def fused_layer_tail(o_proj, gate_up, down, next_qkv, M, counters):
+    """o_proj -> gate_up -> down [-> next layer's qkv] as one persistent launch (M <= 8).
+    Each argument is the (struct, keep) pair of fused_desc (next_qkv may be None); `counters` is a
+    zeroed uint32[4] device tensor.  b2_fused_layer_tail."""
+    import ctypes as C
+    _cuda(counters)
+    ref = lambda pair: None if pair is None else C.byref(pair[0])
+    check(_abi.lib().b2_fused_layer_tail(ref(o_proj), ref(gate_up), ref(down), ref(next_qkv), int(M), ptr(counters),
+                                         stream_handle()), "b2_fused_layer_tail")
 
 
 def rope_kv_append(qkv, cos, sin, positions, kcache, vcache, H, KV, hd, seq_ids=None, seq0=0, use_rope=True):

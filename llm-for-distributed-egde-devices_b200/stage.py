@@ -71,6 +71,8 @@ class _Scratch:
         # fused decode path (T <= 8): act(gate)*up in fp32 and its running row absmax
         self.y32 = torch.empty((8, F), dtype=f32, device=device)
         self.amax = torch.zeros((8,), dtype=f32, device=device)
+        # grid-barrier counters of the persistent layer-tail kernel: 4 x uint32 per layer, zeroed per forward
+        self.ctr = torch.zeros((256 * 4,), dtype=torch.int32, device=device)
 
     def q8view(self, T, K):
         return self.q8[: T * K].view(T, K)
@@ -96,6 +98,9 @@ class Stage:
         self.launches = 0          # kernels of ours launched (bench.py's gpu_launches claim)
         self.fuse_decode = True    # decode steps with <= 8 tokens use b2_fused_linear
         self.l2_prefetch = True    # fused decode kernels pull the head of the next weights into L2
+        # o_proj -> gate_up -> down -> next qkv as one persistent launch with grid barriers: exact, but measured
+        # SLOWER than four PDL-chained launches on B200 (38.0 vs 33.8 us per layer tail), so off by default
+        self.fuse_tail = False
 
     # ------------------------------------------------------------------------------------------
     @classmethod
@@ -162,6 +167,40 @@ class Stage:
         layers = self.w["layers"]
         for li, lw in enumerate(layers):
             kc, vc = kv_cache.k[li], kv_cache.v[li]
+            if fused and cfg.gated and self.fuse_tail:
+                # 2 launches per layer: attention, then ONE persistent kernel for
+                # o_proj -> gate_up -> down -> next layer's qkv (grid barriers between the phases)
+                pf = self.l2_prefetch
+                rope = lambda k_, v_: dict(cos=self.cos, sin=self.sin, positions=dpos, seq_ids=dseq, seq0=row0,
+                                           kcache=k_, vcache=v_, H=H, KV=KV, hd=hd, use_rope=cfg.rope)
+                if li == 0:
+                    buf.ctr.zero_()
+                    ops.fused_qkv(h, lw["wqkv"], lw["s_qkv"], qkv, self.cos, self.sin, dpos, kc, vc, H, KV, hd,
+                                  x_kind=xk_norm, gamma=lw["ln1_g"], beta=lw.get("ln1_b"), smooth=lw["sm_qkv"],
+                                  eps=cfg.eps, bias=lw.get("b_qkv"), seq_ids=dseq, seq0=row0, use_rope=cfg.rope,
+                                  prefetch=(lw["wo"], lw["wgu"]) if pf else None)
+                    n += 1
+                ops.decode_attn(qkv, kc, vc, dlens, H, KV, hd, max_len, self.scale, cfg.window, rows=dseq, out=attn,
+                                workspace=ws)
+                nl = layers[li + 1] if li + 1 < len(layers) else None
+                d_o = ops.fused_desc(attn, lw["wo"], lw["s_o"], x_kind=ops.X_PLAIN, smooth=lw["sm_o"], bias=lw.get("b_o"),
+                                     residual=h, out=h_alt, zero_amax=buf.amax)
+                d_g = ops.fused_desc(h_alt, lw["wgu"], lw["s_gu"], x_kind=xk_norm, gamma=lw["ln2_g"], beta=lw.get("ln2_b"),
+                                     smooth=lw["sm_gu"], eps=cfg.eps, bias=lw.get("b_gu"), out=buf.y32[:T],
+                                     out_kind=ops.O_GATED, act=0 if cfg.act == "silu" else 1, out_smooth=lw["sm_d"],
+                                     out_amax=buf.amax, prefetch=(lw["wd"],) if pf else None)
+                nxt_w = nl["wqkv"] if nl is not None else self.w.get("lm_head")
+                d_d = ops.fused_desc(buf.y32[:T], lw["wd"], lw["s_d"], x_kind=ops.X_Y32, x_amax=buf.amax,
+                                     bias=lw.get("b_d"), residual=h_alt, out=h, prefetch=(nxt_w,) if pf else None)
+                d_q = None
+                if nl is not None:
+                    d_q = ops.fused_desc(h, nl["wqkv"], nl["s_qkv"], x_kind=xk_norm, gamma=nl["ln1_g"], beta=nl.get("ln1_b"),
+                                         smooth=nl["sm_qkv"], eps=cfg.eps, bias=nl.get("b_qkv"), out=qkv, out_kind=ops.O_QKV,
+                                         rope=rope(kv_cache.k[li + 1], kv_cache.v[li + 1]),
+                                         prefetch=(nl["wo"], nl["wgu"]) if pf else None)
+                ops.fused_layer_tail(d_o, d_g, d_d, d_q, T, buf.ctr[li * 4: li * 4 + 4])
+                n += 2 if ws is None else 3
+                continue
             if fused:
                 # 6-7 launches per layer: every linear redoes its (tiny) activation prologue in-kernel
                 ops.fused_qkv(h, lw["wqkv"], lw["s_qkv"], qkv, self.cos, self.sin, dpos, kc, vc, H, KV, hd,
@@ -174,12 +213,14 @@ class Stage:
                                  residual=h, out=h_alt, zero_amax=buf.amax)
                 n += 3 if ws is None else 4
                 if cfg.gated:
+                    nxt = layers[li + 1]["wqkv"] if li + 1 < len(layers) else self.w.get("lm_head")
                     ops.fused_linear(h_alt, lw["wgu"], lw["s_gu"], x_kind=xk_norm, gamma=lw["ln2_g"],
                                      beta=lw.get("ln2_b"), smooth=lw["sm_gu"], eps=cfg.eps, bias=lw.get("b_gu"),
                                      out=buf.y32[:T], out_kind=ops.O_GATED, act=0 if cfg.act == "silu" else 1,
                                      out_smooth=lw["sm_d"], out_amax=buf.amax,
                                      prefetch=(lw["wd"],) if self.l2_prefetch else None)
-                    nxt = layers[li + 1]["wqkv"] if li + 1 < len(layers) else self.w.get("lm_head")
+                    # (also tried on B200 and rejected: prefetching the next layer's K/V block here, 442 vs
+                    #  480 tok/s, and an L2 evict-first policy on the weight stream, 459 vs 480 tok/s)
                     ops.fused_linear(buf.y32[:T], lw["wd"], lw["s_d"], x_kind=ops.X_Y32, x_amax=buf.amax,
                                      bias=lw.get("b_d"), residual=h_alt, out=h,
                                      prefetch=(nxt,) if self.l2_prefetch else None)

@@ -106,12 +106,13 @@ def test_fused_decode_equals_unfused_decode(model):
     cfg = b200stage.get_config(model)
     ids = np.random.default_rng(8).integers(0, cfg.vocab, 37)
     outs = {}
-    for fuse in (False, True):
+    for fuse in (False, True, "tail"):       # "tail": o_proj -> gate_up -> down -> next qkv in one persistent launch
         for graphs in (False, True):
             pipe = Pipeline.load(cfg, 2, seed=11)
             pipe.use_graphs = graphs
             for s in pipe.stages:
-                s.fuse_decode = fuse
+                s.fuse_decode = bool(fuse)
+                s.fuse_tail = fuse == "tail"
             toks = pipe.generate(ids, max_new_tokens=10, chunk=16)
             caches = pipe.new_caches(3, 64)
             for b in range(3):
@@ -157,3 +158,63 @@ def test_fused_qkv_rope_append_exact(M, H, KV, hd, d):
         assert np.array_equal(kcn[seq[i], :, pos[i]].view(np.uint16), k_ref[i].view(np.uint16))
         assert np.array_equal(vcn[seq[i], :, pos[i]].view(np.uint16), v_ref[i].view(np.uint16))
     assert int((kcn != 0).any(-1).sum()) == M * KV          # nothing else in the cache was touched
+
+
+@pytest.mark.parametrize("M", [1, 3, 8])
+@pytest.mark.parametrize("with_qkv", [False, True])
+def test_fused_layer_tail_equals_separate_launches(M, with_qkv):
+    """o_proj -> gate_up -> down [-> next qkv] as one persistent launch (grid barriers) == the same
+    four fused launches one after the other, bit for bit; no barrier time-out flag."""
+    r = np.random.default_rng(M + 7)
+    d, F, H, KV, hd, Smax = 1024, 2816, 8, 2, 128, 64
+    N = (H + 2 * KV) * hd
+    attn = t(r.standard_normal((M, d)).astype(np.float16))
+    h = t(r.standard_normal((M, d)).astype(np.float16))
+    g2 = t((1 + 0.1 * r.standard_normal(d)).astype(np.float16))
+    g1n = t((1 + 0.1 * r.standard_normal(d)).astype(np.float16))
+    sm_o, sm_gu, sm_q = (t(r.uniform(0.5, 2, d).astype(np.float32)) for _ in range(3))
+    sm_d = t(r.uniform(0.5, 2, F).astype(np.float32))
+    wo, so = map(t, _w(r, d, d))
+    wgu, sgu = _w(r, 2 * F, d)
+    wgu, sgu = t(wgu), t(sgu * 4)
+    wd, sd = map(t, _w(r, d, F))
+    wq, sq = _w(r, N, d)
+    wq, sq = t(wq), t(sq * 3)
+    cos, sin = (t(x) for x in O.rope_table(hd, Smax))
+    pos = t(r.permutation(Smax)[:M].astype(np.int32))
+    seq = t(np.arange(M, dtype=np.int32))
+    res = {}
+    for mode in ("separate", "tail"):
+        kc = torch.zeros((M, KV, Smax, hd), dtype=torch.float16, device=DEV)
+        vc = torch.zeros_like(kc)
+        h1 = torch.empty((M, d), dtype=torch.float16, device=DEV)
+        h2 = torch.empty((M, d), dtype=torch.float16, device=DEV)
+        y = torch.empty((M, F), dtype=torch.float32, device=DEV)
+        amax = torch.full((8,), 5.0, device=DEV)
+        qkv = torch.zeros((M, N), dtype=torch.float16, device=DEV)
+        rope = dict(cos=cos, sin=sin, positions=pos, seq_ids=seq, kcache=kc, vcache=vc, H=H, KV=KV, hd=hd)
+        if mode == "separate":
+            ops.fused_linear(attn, wo, so, x_kind=ops.X_PLAIN, smooth=sm_o, residual=h, out=h1, zero_amax=amax)
+            ops.fused_linear(h1, wgu, sgu, x_kind=ops.X_RMS, gamma=g2, smooth=sm_gu, out=y, out_kind=ops.O_GATED,
+                             out_smooth=sm_d, out_amax=amax)
+            ops.fused_linear(y, wd, sd, x_kind=ops.X_Y32, x_amax=amax, residual=h1, out=h2)
+            if with_qkv:
+                ops.fused_qkv(h2, wq, sq, qkv, cos, sin, pos, kc, vc, H, KV, hd, x_kind=ops.X_RMS, gamma=g1n, smooth=sm_q,
+                              seq_ids=seq)
+        else:
+            ctr = torch.zeros(4, dtype=torch.int32, device=DEV)
+            d_o = ops.fused_desc(attn, wo, so, x_kind=ops.X_PLAIN, smooth=sm_o, residual=h, out=h1, zero_amax=amax)
+            d_g = ops.fused_desc(h1, wgu, sgu, x_kind=ops.X_RMS, gamma=g2, smooth=sm_gu, out=y, out_kind=ops.O_GATED,
+                                 out_smooth=sm_d, out_amax=amax, prefetch=(wd,))
+            d_d = ops.fused_desc(y, wd, sd, x_kind=ops.X_Y32, x_amax=amax, residual=h1, out=h2)
+            d_q = ops.fused_desc(h2, wq, sq, x_kind=ops.X_RMS, gamma=g1n, smooth=sm_q, out=qkv, out_kind=ops.O_QKV,
+                                 rope=rope) if with_qkv else None
+            for _ in range(3):                      # replays must be idempotent given re-zeroed counters
+                ctr.zero_()
+                ops.fused_layer_tail(d_o, d_g, d_d, d_q, M, ctr)
+            torch.cuda.synchronize()
+            assert int(ctr[3]) == 0, "grid barrier timed out"
+            assert ctr[:3].tolist() == ([ctr[0].item()] * 3 if with_qkv else [ctr[0].item(), ctr[0].item(), 0])
+        res[mode] = [x.clone() for x in (h1, y, amax[:M], h2, qkv[:, :H * hd], kc, vc)]
+    for a, b in zip(res["separate"], res["tail"]):
+        assert torch.equal(a, b)

@@ -89,6 +89,27 @@ t = timed(lambda: [ops.fused_linear(h, lw["wgu"], lw["s_gu"], x_kind=ops.X_RMS, 
 report("fused gate_up (norm+quant+GEMV+SiLU*up)", t, 2 * F * d)
 t = timed(lambda: [ops.fused_linear(y32, lw["wd"], lw["s_d"], x_kind=ops.X_Y32, x_amax=amax, residual=h, out=h2) for lw in L])
 report("fused down (requant+GEMV+residual)", t, d * F)
+ctr = torch.zeros((a.nl, 4), dtype=torch.int32, device=dev)
+
+
+def tail_all(with_qkv):
+    ctr.zero_()
+    for i, lw in enumerate(L):
+        nl = L[(i + 1) % len(L)]
+        d_o = ops.fused_desc(attn, lw["wo"], lw["s_o"], x_kind=ops.X_PLAIN, smooth=lw["sm_o"], residual=h, out=h2, zero_amax=amax)
+        d_g = ops.fused_desc(h2, lw["wgu"], lw["s_gu"], x_kind=ops.X_RMS, gamma=lw["ln2_g"], smooth=lw["sm_gu"], out=y32,
+                             out_kind=ops.O_GATED, out_smooth=lw["sm_d"], out_amax=amax)
+        d_d = ops.fused_desc(y32, lw["wd"], lw["s_d"], x_kind=ops.X_Y32, x_amax=amax, residual=h2, out=h)
+        d_q = ops.fused_desc(h, nl["wqkv"], nl["s_qkv"], x_kind=ops.X_RMS, gamma=nl["ln1_g"], smooth=nl["sm_qkv"], out=qkv,
+                             out_kind=ops.O_QKV, rope=dict(cos=cos, sin=sin, positions=pos, seq_ids=seq, kcache=kc[i], vcache=vc[i],
+                                                           H=H, KV=KV, hd=hd)) if with_qkv else None
+        ops.fused_layer_tail(d_o, d_g, d_d, d_q, M, ctr[i])
+
+
+t = timed(lambda: tail_all(False))
+report("layer tail, 3 phases (o + gate_up + down)", t, d * H * hd + 2 * F * d + d * F)
+t = timed(lambda: tail_all(True))
+report("layer tail, 4 phases (+ next qkv)", t, d * H * hd + 2 * F * d + d * F + cfg.qkv_out * d)
 q8 = torch.randint(-127, 128, (M, d), dtype=torch.int8, device=dev)
 sc = torch.full((M,), 0.01, device=dev)
 gu = torch.empty((M, 2 * F), dtype=torch.float16, device=dev)
