@@ -201,9 +201,9 @@ def run_ours(a):
     dev = torch.device("cuda", local)
     dist = None
     if world > 1:
-        # NCCL_DEBUG=VERSION makes NCCL print a banner on stdout, ahead of the one JSON line
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"
+        # NCCL prints its version banner (NCCL_DEBUG >= VERSION) on stdout, ahead of the one JSON line:
+        # send NCCL's debug output to stderr instead
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
     cfg = b2.get_config(a.model)
