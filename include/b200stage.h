@@ -230,6 +230,19 @@ int b2_lm_head(const void* x, const void* W, float* logits, int M, int V, int d,
  * Replaces: the greedy (do_sample=False) token selection of `generate`. */
 int b2_argmax(const float* logits, long long* out, int T, int V, void* stream);
 
+/* Sampling with the reference's real generate kwargs (do_sample=True; temperature, top_k, top_p,
+ * repetition_penalty: Code/Quantised Models/models_quant_updated.py:84-93, Code/others/config.yaml:3-7).
+ * logits [B, ld >= V] fp32; history [B, hist_ld] int64 = every token id seen so far per row (prompt +
+ * generated), hist_len [B] int32 valid entries per row (history NULL = no repetition penalty);
+ * out [B] int64.  Processor chain and order are HF's (repetition penalty -> temperature -> top-k with
+ * ties kept -> top-p on the ascending cumulative softmax, at least one token kept); the draw is an
+ * inverse CDF over the kept tokens with a counter-based uniform of (seed, step, row), step read from
+ * *step_ptr when step_ptr != NULL (device) else `step`.  top_k <= 0 or > 1024 is capped at 1024
+ * candidates.  Replaces: the sampling branch of `model.generate` that the reference always takes. */
+int b2_sample(const float* logits, long long ld, const long long* history, const int* hist_len, long long hist_ld,
+              long long* out, int B, int V, float temperature, int top_k, float top_p, float repetition_penalty,
+              unsigned long long seed, const unsigned long long* step_ptr, unsigned long long step, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

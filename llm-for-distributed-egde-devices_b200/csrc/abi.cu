@@ -25,6 +25,9 @@ int init_attn();
 int init_rowquant();
 int init_misc();
 int init_fused();
+int init_sample();
+int sample(const float*, long long, const long long*, const int*, long long, long long*, int, int, float, int, float, float,
+           unsigned long long, const unsigned long long*, unsigned long long, cudaStream_t);
 int fused_layer_tail(const b2_fused_desc*, const b2_fused_desc*, const b2_fused_desc*, const b2_fused_desc*, int, unsigned*,
                      cudaStream_t);
 int fused_qkv(const void*, long long, int, const void*, const void*, const float*, float, const int8_t*, const float*,
@@ -49,7 +52,8 @@ int b2_init(void) {
   if ((rc = b2::init_attn())) return rc;
   if ((rc = b2::init_rowquant())) return rc;
   if ((rc = b2::init_misc())) return rc;
-  return b2::init_fused();
+  if ((rc = b2::init_fused())) return rc;
+  return b2::init_sample();
 }
 
 const char* b2_strerror(int code) {
@@ -112,6 +116,12 @@ int b2_fused_qkv(const void* x, long long x_ld, int x_kind, const void* gamma, c
 int b2_fused_layer_tail(const b2_fused_desc* o_proj, const b2_fused_desc* gate_up, const b2_fused_desc* down,
                         const b2_fused_desc* next_qkv, int M, unsigned int* counters, void* stream) {
   return b2::fused_layer_tail(o_proj, gate_up, down, next_qkv, M, counters, ST(stream));
+}
+int b2_sample(const float* logits, long long ld, const long long* history, const int* hist_len, long long hist_ld,
+              long long* out, int B, int V, float temperature, int top_k, float top_p, float repetition_penalty,
+              unsigned long long seed, const unsigned long long* step_ptr, unsigned long long step, void* stream) {
+  return b2::sample(logits, ld, history, hist_len, hist_ld, out, B, V, temperature, top_k, top_p, repetition_penalty, seed,
+                    step_ptr, step, ST(stream));
 }
 int b2_rope_kv_append(void* qkv, long long ld, const float* cos_table, const float* sin_table, const int* positions,
                       const int* seq_ids, int seq0, void* kcache, void* vcache, int T, int H, int KV, int hd, int Smax,

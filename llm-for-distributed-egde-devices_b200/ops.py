@@ -257,3 +257,19 @@ def argmax(logits, out=None):
     o = out if out is not None else torch.empty((T,), dtype=torch.int64, device=logits.device)
     check(_abi.lib().b2_argmax(ptr(logits), ptr(o), T, V, stream_handle()), "b2_argmax")
     return o
+
+
+def sample(logits, *, temperature=1.0, top_k=50, top_p=1.0, repetition_penalty=1.0, seed=0, step=0, history=None,
+           hist_len=None, step_tensor=None, out=None):
+    """logits [B,V] fp32 -> sampled ids int64 [B] with HF's processor chain (repetition penalty ->
+    temperature -> top-k -> top-p) and a counter-based draw.  history [B,Hmax] int64 + hist_len [B]
+    int32 = the ids seen so far per row; step_tensor: optional device uint64 counter read instead of
+    `step`.  b2_sample."""
+    _cuda(logits, history, hist_len, step_tensor, out)
+    B, V = logits.shape
+    o = out if out is not None else torch.empty((B,), dtype=torch.int64, device=logits.device)
+    check(_abi.lib().b2_sample(ptr(logits), logits.stride(0), ptr(history), ptr(hist_len),
+                               0 if history is None else history.stride(0), ptr(o), B, V, float(temperature), int(top_k),
+                               float(top_p), float(repetition_penalty), int(seed) & 0xFFFFFFFFFFFFFFFF, ptr(step_tensor),
+                               int(step), stream_handle()), "b2_sample")
+    return o

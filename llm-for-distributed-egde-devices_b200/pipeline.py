@@ -107,8 +107,14 @@ class Pipeline:
                  max_seq: int | None = None, caches=None, **sample_kwargs):
         """Greedy continuation of one prompt; returns prompt + new tokens (int64, on the device),
         like ``model.generate(**inputs, max_new_tokens=...)[0]`` (models_quant_updated.py:84-95)."""
-        if do_sample:
-            raise NotImplementedError("sampling (temperature/top-k/top-p) is the next scope row; greedy only")
+        temperature = float(sample_kwargs.pop("temperature", 1.0))
+        top_k = int(sample_kwargs.pop("top_k", 50))
+        top_p = float(sample_kwargs.pop("top_p", 1.0))
+        rep = float(sample_kwargs.pop("repetition_penalty", 1.0))
+        seed = int(sample_kwargs.pop("seed", 0))
+        sample_kwargs.pop("pad_token_id", None)          # accepted for call compatibility with HF; unused
+        if sample_kwargs:
+            raise TypeError(f"unsupported generate() arguments: {sorted(sample_kwargs)}")
         dev = self.stages[0].device
         ids = torch.as_tensor(input_ids, dtype=torch.int64).view(-1).to(dev)
         T = int(ids.shape[0])
@@ -119,9 +125,19 @@ class Pipeline:
         out = torch.empty((T + max_new_tokens,), dtype=torch.int64, device=dev)
         out[:T] = ids
         lg = self.prefill(ids, caches, 0, 0, chunk)
+        hist2d = out.view(1, -1)
+        hlen = torch.empty((1,), dtype=torch.int32, device=dev) if do_sample else None
         for i in range(max_new_tokens):
             tok = out[T + i: T + i + 1]
-            ops.argmax(lg.view(1, -1).to(dev) if lg.device != dev else lg.view(1, -1), out=tok)
+            lgd = lg.view(1, -1).to(dev) if lg.device != dev else lg.view(1, -1)
+            if do_sample:
+                # the reference's call: do_sample=True, temperature, top_k, top_p, repetition_penalty
+                # (models_quant_updated.py:84-93); the penalty sees prompt + everything generated so far
+                hlen.fill_(T + i)
+                ops.sample(lgd, temperature=temperature, top_k=top_k, top_p=top_p, repetition_penalty=rep, seed=seed,
+                           step=i, history=hist2d, hist_len=hlen, out=tok)
+            else:
+                ops.argmax(lgd, out=tok)
             self.stages[-1].launches += 1
             if i + 1 < max_new_tokens:
                 lg = self.decode_step(tok, caches, [T + i])

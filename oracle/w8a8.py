@@ -410,3 +410,77 @@ def greedy_generate(stages, cfg, ids, max_new_tokens, max_seq, chunk=None):
             break
         logits = run(np.array([nxt]), np.array([len(toks) - 1]))
     return np.array(toks, dtype=np.int64), margins
+
+
+# ----------------------------------------------------------------------------------------
+# sampling: the reference's real generate kwargs (do_sample=True, temperature, top_k, top_p,
+# repetition_penalty -- Code/Quantised Models/models_quant_updated.py:84-93, Code/others/config.yaml:3-7)
+# ----------------------------------------------------------------------------------------
+_U64 = np.uint64
+
+
+def rng_uniform(seed: int, step: int, row: int) -> np.float32:
+    """Counter-based uniform in [0,1): splitmix64 finaliser of (seed, step, row), top 24 bits.
+    torch.multinomial's generator cannot be reproduced on the device, so the draw is build-defined;
+    everything before the draw follows HF."""
+    m = (1 << 64) - 1
+    x = (int(seed) ^ ((int(step) * 0xD1B54A32D192ED03) & m) ^ (((int(row) + 1) * 0x9E3779B97F4A7C15) & m)) & m
+    x ^= x >> 30
+    x = (x * 0xBF58476D1CE4E5B9) & m
+    x ^= x >> 27
+    x = (x * 0x94D049BB133111EB) & m
+    x ^= x >> 31
+    return f32((x >> 40) * (1.0 / 16777216.0))
+
+
+def sample_filter(logits_row, history, temperature, top_k, top_p, repetition_penalty):
+    """HF's processor chain on one row of fp32 logits, in HF's order
+    (transformers/generation/utils.py:1089,1214,1219,1223; logits_process.py):
+      RepetitionPenaltyLogitsProcessor (:371-392)  score<0 ? score*p : score/p for every id in history
+      TemperatureLogitsWarper (:297-299)           score / temperature
+      TopKLogitsWarper (:581-586)                  keep score >= k-th largest (ties kept)
+      TopPLogitsWarper (:521-533)                  ascending cumsum of softmax; drop cum <= 1 - top_p; keep >= 1
+    Returns (token ids kept, their scores), ordered by (score desc, id asc); fp32, individually
+    rounded operations, exp via exp_det -- the order the kernel b2_sample reproduces bit for bit."""
+    x = np.asarray(logits_row, dtype=f32).copy()
+    if history is not None and len(history) and repetition_penalty != 1.0:
+        ids = np.unique(np.asarray(history, dtype=np.int64))
+        s = x[ids]
+        x[ids] = np.where(s < 0, (s * f32(repetition_penalty)).astype(f32), (s / f32(repetition_penalty)).astype(f32))
+    x = (x / f32(temperature)).astype(f32)
+    k = min(int(top_k), x.shape[0])
+    kth = np.sort(x)[-k]
+    cand = np.nonzero(x >= kth)[0]
+    order = np.lexsort((cand, -x[cand].astype(np.float64)))       # score desc, id asc
+    cand = cand[order]
+    sc = x[cand]
+    # softmax over the candidates, summed in ascending-score order (sequential fp32)
+    e = exp_det((sc - sc[0]).astype(f32))
+    z = f32(0.0)
+    for v in e[::-1]:
+        z = f32(z + v)
+    cum = f32(0.0)
+    keep = np.ones(len(cand), dtype=bool)
+    thr = f32(f32(1.0) - f32(top_p))
+    for j in range(len(cand) - 1, -1, -1):                        # ascending score order
+        cum = f32(cum + f32(e[j] / z))
+        if j != 0 and cum <= thr:
+            keep[j] = False
+    return cand[keep], sc[keep]
+
+
+def sample_det(logits_row, history, temperature, top_k, top_p, repetition_penalty, seed, step, row):
+    """One sampled token id: sample_filter, then inverse-CDF over the kept tokens in
+    (score desc, id asc) order with the counter-based uniform."""
+    ids, sc = sample_filter(logits_row, history, temperature, top_k, top_p, repetition_penalty)
+    e = exp_det((sc - sc[0]).astype(f32))
+    z = f32(0.0)
+    for v in e:
+        z = f32(z + v)
+    target = f32(rng_uniform(seed, step, row) * z)
+    acc = f32(0.0)
+    for j in range(len(ids)):
+        acc = f32(acc + e[j])
+        if acc > target:
+            return int(ids[j])
+    return int(ids[-1])

@@ -155,3 +155,40 @@ def test_two_stage_split_equals_one_stage():
     t1, _ = O.greedy_generate(one, cfg.kernel_cfg(), ids, 4, 16)
     t2, _ = O.greedy_generate(two, cfg.kernel_cfg(), ids, 4, 16, chunk=5)
     assert np.array_equal(t1, t2)
+
+
+# ---- sampler oracle vs HF's own logits processors (Tier R for the generate kwargs) -------------
+@pytest.mark.parametrize("params", [(0.7, 50, 0.9, 1.1), (0.5, 30, 0.85, 1.2), (1.0, 5, 0.5, 1.0), (0.5, 30, 0.9, 1.1)])
+def test_sample_filter_keeps_what_hf_keeps(params):
+    """The set of tokens that survives the oracle's chain == the set HF's processors leave finite,
+    run here in HF's order (generation/utils.py:1089,1214,1219,1223) with the reference's own
+    parameter values (config.yaml:3-7, try.py:308-314)."""
+    import torch
+    from transformers.generation.logits_process import (RepetitionPenaltyLogitsProcessor, TemperatureLogitsWarper,
+                                                        TopKLogitsWarper, TopPLogitsWarper)
+    T, k, p, pen = params
+    r = np.random.default_rng(int(T * 100) + k)
+    for trial in range(10):
+        V = 3000
+        lg = (r.standard_normal(V) * 3).astype(np.float32)
+        hist = r.integers(0, V, 80)
+        ids, sc = O.sample_filter(lg, hist, T, k, p, pen)
+        s, h = torch.from_numpy(lg)[None].clone(), torch.from_numpy(hist)[None]
+        for proc in (RepetitionPenaltyLogitsProcessor(pen), TemperatureLogitsWarper(T), TopKLogitsWarper(k), TopPLogitsWarper(p)):
+            s = proc(h, s)
+        kept = torch.nonzero(torch.isfinite(s[0])).flatten().numpy()
+        assert set(kept.tolist()) == set(ids.tolist())
+        assert np.allclose(s[0, ids].numpy(), sc, rtol=1e-6)          # same processed scores
+        assert (np.diff(sc) <= 0).all()                               # ordered by score, descending
+
+
+def test_sample_det_is_a_valid_reproducible_draw():
+    r = np.random.default_rng(3)
+    lg = (r.standard_normal(500) * 2).astype(np.float32)
+    ids, _ = O.sample_filter(lg, None, 0.7, 50, 0.9, 1.0)
+    draws = [O.sample_det(lg, None, 0.7, 50, 0.9, 1.0, 11, s, 0) for s in range(200)]
+    assert set(draws) <= set(ids.tolist()) and len(set(draws)) > 3
+    assert draws == [O.sample_det(lg, None, 0.7, 50, 0.9, 1.0, 11, s, 0) for s in range(200)]
+    assert O.sample_det(lg, None, 1.0, 1, 1.0, 1.0, 0, 0, 0) == int(lg.argmax())
+    u = [float(O.rng_uniform(5, s, 0)) for s in range(2000)]
+    assert 0.0 <= min(u) and max(u) < 1.0 and abs(np.mean(u) - 0.5) < 0.03
