@@ -173,11 +173,15 @@ int b2_rope_kv_append(void* qkv, long long ld, const float* cos_table, const flo
  * max_seqlen: host-side upper bound of seqlens (chooses the kv split count without a device read).
  * workspace: scratch for the split-KV partials, at least b2_decode_attn_workspace_bytes(...) bytes;
  * may be NULL/short, in which case fewer splits are used.
+ * prefetch0/1 (+ _bytes): optional L2 hints, as in b2_fused_linear: weights that LATER launches will
+ * stream.  Decode attention leaves about half of the HBM bandwidth idle, so this is where the
+ * o_proj / gate_up weights of the same layer are best pulled into L2.
  * Replaces: eager_attention_forward at q_len = 1 (modeling_llama.py:199-222) inside the decode
  * loop of `model.generate` (models_quant_updated.py:84-93). */
 int b2_decode_attn(const void* q, long long q_ld, const void* kcache, const void* vcache, const int* seqlens,
                    const int* rows, void* out, long long o_ld, void* workspace, size_t workspace_bytes, int B, int H,
-                   int KV, int hd, int Smax, int max_seqlen, float scale, int window, void* stream);
+                   int KV, int hd, int Smax, int max_seqlen, float scale, int window, const void* prefetch0,
+                   long long prefetch0_bytes, const void* prefetch1, long long prefetch1_bytes, void* stream);
 /* Bytes of workspace b2_decode_attn wants for these sizes (0 if it will not split). */
 size_t b2_decode_attn_workspace_bytes(int B, int H, int KV, int hd, int max_seqlen, int window);
 
@@ -187,7 +191,7 @@ size_t b2_decode_attn_workspace_bytes(int B, int H, int KV, int hd, int max_seql
  * allocator closed; a latency-critical decode thread in which cudaMalloc -- a device-wide
  * synchronisation with no time bound -- is forbidden; a plugin host that owns device memory and
  * does not let plugins allocate.  Such callers have no workspace to pass, so this variant keeps the
- * split-KV partials in a fixed B2_DECODE_ATTN_STATIC_SCRATCH_BYTES (1 MiB) array inside the library image
+ * split-KV partials in a fixed B2_DECODE_ATTN_STATIC_SCRATCH_BYTES (512 KiB) array inside the library image
  * (every GPU that loads the library holds those bytes until the process exits).  The call itself
  * allocates nothing: no cudaMalloc/cudaFree, no allocating library routine.
  * Arguments and result are those of b2_decode_attn without workspace/workspace_bytes; the output is
@@ -200,7 +204,7 @@ size_t b2_decode_attn_workspace_bytes(int B, int H, int KV, int hd, int max_seql
  *   to be zero on entry (each call writes every slot it later reads), but two calls whose kernels
  *   can overlap on the GPU -- different streams, or concurrent host threads on one device -- race
  *   on it and corrupt each other.  Serialise them (one stream, or events) or use b2_decode_attn. */
-#define B2_DECODE_ATTN_STATIC_SCRATCH_BYTES (1u << 20)
+#define B2_DECODE_ATTN_STATIC_SCRATCH_BYTES (1u << 19)
 int b2_decode_attn_static(const void* q, long long q_ld, const void* kcache, const void* vcache, const int* seqlens,
                           const int* rows, void* out, long long o_ld, int B, int H, int KV, int hd, int Smax,
                           int max_seqlen, float scale, int window, void* stream);

@@ -13,7 +13,8 @@ import re
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200stage.so")
+# B2_LIBRARY: load another build of the same ABI (the -DB2_TIMELINE probe build of tools/timeline.py)
+LIB_PATH = os.environ.get("B2_LIBRARY") or os.path.join(_HERE, "libb200stage.so")
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "b200stage.h")
 
 _vp, _i, _f, _ll, _sz = C.c_void_p, C.c_int, C.c_float, C.c_longlong, C.c_size_t
@@ -30,7 +31,8 @@ SIGNATURES = {
     "b2_gemm_w8a8": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
     "b2_gemm_w8a8_sched": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "b2_rope_kv_append": (_i, [_vp, _ll, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
-    "b2_decode_attn": (_i, [_vp, _ll, _vp, _vp, _vp, _vp, _vp, _ll, _vp, _sz, _i, _i, _i, _i, _i, _i, _f, _i, _vp]),
+    "b2_decode_attn": (_i, [_vp, _ll, _vp, _vp, _vp, _vp, _vp, _ll, _vp, _sz, _i, _i, _i, _i, _i, _i, _f, _i, _vp, _ll, _vp,
+                             _ll, _vp]),
     "b2_decode_attn_static": (_i, [_vp, _ll, _vp, _vp, _vp, _vp, _vp, _ll, _i, _i, _i, _i, _i, _i, _f, _i, _vp]),
     "b2_decode_attn_workspace_bytes": (_sz, [_i, _i, _i, _i, _i, _i]),
     "b2_prefill_attn": (_i, [_vp, _ll, _vp, _vp, _vp, _ll, _vp, _i, _i, _i, _i, _i, _i, _i, _f, _i, _vp]),

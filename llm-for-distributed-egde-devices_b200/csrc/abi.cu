@@ -13,7 +13,8 @@ int lm_head(const void*, const void*, float*, int, int, int, cudaStream_t);
 int rope_kv_append(void*, long long, const float*, const float*, const int*, const int*, int, void*, void*, int, int,
                    int, int, int, int, cudaStream_t);
 int decode_attn(const void*, long long, const void*, const void*, const int*, const int*, void*, long long, void*,
-                size_t, int, int, int, int, int, int, float, int, cudaStream_t);
+                size_t, int, int, int, int, int, int, float, int, const void*, long long, const void*, long long,
+                cudaStream_t);
 int decode_attn_static(const void*, long long, const void*, const void*, const int*, const int*, void*, long long, int,
                        int, int, int, int, int, float, int, cudaStream_t);
 int decode_attn_splits(int, int, int, int);
@@ -131,9 +132,11 @@ int b2_rope_kv_append(void* qkv, long long ld, const float* cos_table, const flo
 }
 int b2_decode_attn(const void* q, long long q_ld, const void* kcache, const void* vcache, const int* seqlens,
                    const int* rows, void* out, long long o_ld, void* workspace, size_t workspace_bytes, int B, int H,
-                   int KV, int hd, int Smax, int max_seqlen, float scale, int window, void* stream) {
+                   int KV, int hd, int Smax, int max_seqlen, float scale, int window, const void* prefetch0,
+                   long long prefetch0_bytes, const void* prefetch1, long long prefetch1_bytes, void* stream) {
   return b2::decode_attn(q, q_ld, kcache, vcache, seqlens, rows, out, o_ld, workspace, workspace_bytes, B, H, KV, hd,
-                         Smax, max_seqlen, scale, window, ST(stream));
+                         Smax, max_seqlen, scale, window, prefetch0, prefetch0_bytes, prefetch1, prefetch1_bytes,
+                         ST(stream));
 }
 int b2_decode_attn_static(const void* q, long long q_ld, const void* kcache, const void* vcache, const int* seqlens,
                           const int* rows, void* out, long long o_ld, int B, int H, int KV, int hd, int Smax,

@@ -132,22 +132,37 @@ struct DecParams {
   float* part_ml;                      // [B][H][splits][2]
   int H, KV, Smax, splits, window;
   float scale_log2;
+  // L2 hints for weights later launches stream (this kernel leaves HBM bandwidth to spare)
+  const uint8_t* pf0; long long pf0_bytes; const uint8_t* pf1; long long pf1_bytes;
 };
+// this CTA's share of an L2 prefetch of [ptr, ptr+bytes): 16 KB bulk-prefetch requests
+B2_DEVINL void dec_prefetch_slice(const uint8_t* ptr, long long bytes, int cta, int nctas) {
+  if (ptr == nullptr || bytes <= 0) return;
+  constexpr long long PIECE = 16 * 1024;
+  const long long npieces = (bytes + PIECE - 1) / PIECE;
+  for (long long i = cta; i < npieces; i += nctas) {
+    const long long off = i * PIECE;
+    const uint32_t n = (uint32_t)((bytes - off < PIECE ? bytes - off : PIECE) & ~15ll);
+    if (n) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(ptr + off), "r"(n) : "memory");
+  }
+}
 
 B2_DEVINL void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
-// read a float from the same shared-memory offset in CTA `rank` of this cluster (DSMEM)
-B2_DEVINL float ld_dsmem_f32(const float* local_ptr, uint32_t rank) {
+B2_DEVINL void cluster_arrive_release() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+B2_DEVINL void cluster_wait_acquire() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+// write a float to the same shared-memory offset in CTA `rank` of this cluster (DSMEM)
+B2_DEVINL void st_dsmem_f32(float* local_ptr, uint32_t rank, float v) {
   uint32_t ra;
-  float v;
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(smem_u32(local_ptr)), "r"(rank));
-  asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(ra) : "memory");
-  return v;
+  asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(ra), "f"(v) : "memory");
 }
 
-// CL = true: the `splits` CTAs of one (kv head, sequence) form a thread-block cluster (1,1,splits)
-// and are merged through distributed shared memory by rank 0 -- no workspace, no merge launch.
+// CL = true: the `splits` CTAs of one (kv head, sequence) form a thread-block cluster (1,1,splits).
+// Every CTA PUSHES its partial into a landing zone behind rank 0's K/V ring (remote shared-memory
+// stores), arrives at the cluster barrier and exits; rank 0 waits once and merges from its own
+// shared memory -- no workspace, no merge launch, one barrier, no remote loads.
 template <int HD, bool CL>
 __global__ void __launch_bounds__(DEC_THREADS, 2) decode_attn_kernel(const DecParams p) {
   constexpr int LDS = HD + 8;                       // padded row (halves): ldmatrix conflict-free
@@ -186,6 +201,7 @@ __global__ void __launch_bounds__(DEC_THREADS, 2) decode_attn_kernel(const DecPa
   };
   // Programmatic dependent launch: everything up to the wait touches only state older than the
   // predecessor (sequence lengths, cache rows of earlier tokens).
+  tl_mark(1, 0);
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   // fill the ring: one commit group per stage (empty groups keep the group count uniform)
 #pragma unroll
@@ -193,8 +209,16 @@ __global__ void __launch_bounds__(DEC_THREADS, 2) decode_attn_kernel(const DecPa
     if (sidx < ntiles) load_tile(sidx, sidx);
     cp_async_commit();
   }
+  if (threadIdx.x == DEC_THREADS - 1) {
+    const int cta = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+    const int nctas = gridDim.x * gridDim.y * gridDim.z;
+    dec_prefetch_slice(p.pf0, p.pf0_bytes, cta, nctas);
+    dec_prefetch_slice(p.pf1, p.pf1_bytes, cta, nctas);
+  }
 
+  tl_mark(1, 1);
   asm volatile("griddepcontrol.wait;" ::: "memory");
+  tl_mark(1, 2);
   // the newest key/value row, if it falls in this CTA's range: one 32-bit word of K and of V per thread
   const bool has_new = (seqlen - 1) >= kbeg && (seqlen - 1) < kend;
   uint32_t newk = 0u, newv = 0u;
@@ -300,6 +324,7 @@ __global__ void __launch_bounds__(DEC_THREADS, 2) decode_attn_kernel(const DecPa
   }
   cp_async_wait<0>();
   __syncthreads();
+  tl_mark(1, 4);
   // ---- merge the 4 warps through shared memory (reuse the K buffers) ----
   float* sO = reinterpret_cast<float*>(smem_dec);          // [4][8][HD]
   float* sM = sO + 4 * 8 * HD;                             // [4][8]
@@ -327,9 +352,9 @@ __global__ void __launch_bounds__(DEC_THREADS, 2) decode_attn_kernel(const DecPa
     }
     const int h = kvh * G + gh;
     if (CL) {
-      float* cO = sL + 32;                                   // [8][HD] CTA-level partial, read by rank 0
-      cO[idx] = acc;
-      if (d == 0) { cO[8 * HD + gh] = m; cO[8 * HD + 8 + gh] = l; }
+      float* slot = reinterpret_cast<float*>(smem_dec + DEC_NST * 2 * TILE_HALVES * 2) + split * (G * (HD + 2));
+      st_dsmem_f32(slot + idx, 0, acc);
+      if (d == 0) { st_dsmem_f32(slot + G * HD + gh, 0, m); st_dsmem_f32(slot + G * HD + G + gh, 0, l); }
     } else if (p.splits == 1) {
       p.out[(long long)b * p.o_ld + h * HD + d] = __float2half_rn(l > 0.f ? acc / l : 0.f);
     } else {
@@ -339,26 +364,29 @@ __global__ void __launch_bounds__(DEC_THREADS, 2) decode_attn_kernel(const DecPa
     }
   }
   if (CL) {
-    const float* cO = sL + 32;
-    cluster_sync_all();                                      // every CTA's partial is in its shared memory
+    cluster_arrive_release();                                // this CTA's partial is on its way to rank 0
     if (split == 0) {
+      cluster_wait_acquire();                                // ... and everybody's has landed
+      const float* land = reinterpret_cast<const float*>(smem_dec + DEC_NST * 2 * TILE_HALVES * 2);
+      const int slot = G * (HD + 2);
       for (int idx = threadIdx.x; idx < G * HD; idx += DEC_THREADS) {
         const int gh = idx / HD, d = idx - gh * HD;
         float m = -INFINITY;
-        for (int r = 0; r < p.splits; ++r) m = fmaxf(m, ld_dsmem_f32(cO + 8 * HD + gh, r));
+        for (int r = 0; r < p.splits; ++r) m = fmaxf(m, land[r * slot + G * HD + gh]);
         float l = 0.f, acc = 0.f;
         if (m != -INFINITY) {
           for (int r = 0; r < p.splits; ++r) {
-            const float f = exp2f(ld_dsmem_f32(cO + 8 * HD + gh, r) - m);
-            l += ld_dsmem_f32(cO + 8 * HD + 8 + gh, r) * f;
-            acc += ld_dsmem_f32(cO + idx, r) * f;
+            const float f = exp2f(land[r * slot + G * HD + gh] - m);
+            l += land[r * slot + G * HD + G + gh] * f;
+            acc += land[r * slot + idx] * f;
           }
         }
         p.out[(long long)b * p.o_ld + (kvh * G + gh) * HD + d] = __float2half_rn(l > 0.f ? acc / l : 0.f);
       }
     }
-    cluster_sync_all();                                      // peers stay resident until rank 0 has read them
   }
+  tl_mark(1, 5);
+  tl_flush(1, 0x37u);
 }
 
 template <int HD>
@@ -383,7 +411,11 @@ __global__ void __launch_bounds__(HD) decode_merge_kernel(const DecParams p) {
 int decode_attn_splits(int B, int KV, int max_seqlen, int sms) {
   if (B <= 0 || KV <= 0) return 1;
   const int ctas = B * KV;
-  int want = (2 * sms + ctas - 1) / ctas;
+  // About 1.25 CTAs per SM.  Measured on B200 at B*KV = 32, 2.1k keys (decode us/token over 8 layers):
+  // 3 splits 586, 4: 562, 5: 545, 6: 537, 7: 536, 8: 571 -- with 8 the 32 clusters of 8 only just fit
+  // the GPCs and one or two regularly wait for a whole wave (tools/timeline.py), fewer leave too few
+  // bytes in flight.
+  int want = (5 * sms / 4 + ctas / 2) / ctas;
   const int max_by_len = (max_seqlen + 255) / 256;   // >= 256 keys per split
   int s = want < max_by_len ? want : max_by_len;
   if (s < 1) s = 1;
@@ -409,10 +441,11 @@ static int sm_count_attn() {
 template <int HD>
 static int launch_decode(const DecParams& p, int B, cudaStream_t st, bool cluster = false) {
   constexpr int SMEM = DEC_NST * 2 * DEC_TK * (HD + 8) * 2;
+  constexpr int SMEM_CL_MAX = SMEM + 8 * 8 * (HD + 2) * 4;      // + landing zone: 8 splits x 8 heads of a group
   static bool attr_set = false;
   if (!attr_set) {
     if (cudaFuncSetAttribute(decode_attn_kernel<HD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM) != cudaSuccess ||
-        cudaFuncSetAttribute(decode_attn_kernel<HD, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM) != cudaSuccess)
+        cudaFuncSetAttribute(decode_attn_kernel<HD, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_CL_MAX) != cudaSuccess)
       return ERR_ARCH;
     attr_set = true;
   }
@@ -420,7 +453,7 @@ static int launch_decode(const DecParams& p, int B, cudaStream_t st, bool cluste
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(p.KV, B, p.splits);
     cfg.blockDim = dim3(DEC_THREADS);
-    cfg.dynamicSmemBytes = SMEM;
+    cfg.dynamicSmemBytes = SMEM + p.splits * (p.H / p.KV) * (HD + 2) * 4;
     cfg.stream = st;
     cudaLaunchAttribute at[2];
     at[0].id = cudaLaunchAttributeClusterDimension;
@@ -452,7 +485,8 @@ static int launch_decode(const DecParams& p, int B, cudaStream_t st, bool cluste
 // max_seqlen: upper bound of seqlens[] known to the host (sizes the split count; no device read)
 int decode_attn(const void* q, long long q_ld, const void* kcache, const void* vcache, const int* seqlens,
                 const int* rows, void* out, long long o_ld, void* workspace, size_t workspace_bytes, int B, int H,
-                int KV, int hd, int Smax, int max_seqlen, float scale, int window, cudaStream_t st) {
+                int KV, int hd, int Smax, int max_seqlen, float scale, int window, const void* pf0, long long pf0_bytes,
+                const void* pf1, long long pf1_bytes, cudaStream_t st) {
   if (B == 0) return OK;
   if (!q || !kcache || !vcache || !seqlens || !out) return ERR_NULL_PTR;
   if (B < 0 || H <= 0 || KV <= 0 || H % KV || H / KV > 8 || (q_ld & 1) || max_seqlen <= 0) return ERR_BAD_SHAPE;
@@ -474,6 +508,7 @@ int decode_attn(const void* q, long long q_ld, const void* kcache, const void* v
   p.part_ml = p.part_o ? p.part_o + (size_t)B * H * splits * hd : nullptr;
   p.H = H; p.KV = KV; p.Smax = Smax; p.splits = splits; p.window = window;
   p.scale_log2 = scale * 1.4426950408889634f;
+  p.pf0 = (const uint8_t*)pf0; p.pf0_bytes = pf0_bytes; p.pf1 = (const uint8_t*)pf1; p.pf1_bytes = pf1_bytes;
   return hd == 128 ? launch_decode<128>(p, B, st, use_cluster) : launch_decode<64>(p, B, st, use_cluster);
 }
 
@@ -486,7 +521,7 @@ int decode_attn(const void* q, long long q_ld, const void* kcache, const void* v
 // time bound) is banned, or a plugin host that owns device memory and forbids plugins to allocate.
 // For them the split-KV partials live in the fixed array below, which is part of the library
 // image: every GPU that loads libb200stage.so carries these bytes until the process exits.
-constexpr size_t DEC_STATIC_SCRATCH_BYTES = 1u << 20;   // 1 MiB, == B2_DECODE_ATTN_STATIC_SCRATCH_BYTES
+constexpr size_t DEC_STATIC_SCRATCH_BYTES = 1u << 19;   // 512 KiB, == B2_DECODE_ATTN_STATIC_SCRATCH_BYTES
 static __device__ __align__(256) unsigned char g_dec_static_scratch[DEC_STATIC_SCRATCH_BYTES];
 
 // `g_dec_static_scratch` named in HOST code is only the host-side handle of the symbol, not a
@@ -537,13 +572,14 @@ int decode_attn_static(const void* q, long long q_ld, const void* kcache, const 
   p.part_ml = p.part_o ? p.part_o + (size_t)B * H * splits * hd : nullptr;
   p.H = H; p.KV = KV; p.Smax = Smax; p.splits = splits; p.window = window;
   p.scale_log2 = scale * 1.4426950408889634f;
+  p.pf0 = nullptr; p.pf0_bytes = 0; p.pf1 = nullptr; p.pf1_bytes = 0;
   return hd == 128 ? launch_decode<128>(p, B, st) : launch_decode<64>(p, B, st);
 }
 
 // =============================================================================================
 // prefill attention (one contiguous chunk of one sequence; causal, optional sliding window)
 // =============================================================================================
-constexpr int PF_BM = 64;     // query rows per CTA (16 per warp)
+constexpr int PF_BM = 128;    // query rows per CTA: 4 warps x 32 rows (two 16-row MMA blocks per warp)
 constexpr int PF_TK = 64;     // keys per stage
 constexpr int PF_THREADS = 128;
 
@@ -557,33 +593,38 @@ struct PfParams {
 };
 
 template <int HD>
+constexpr int pf_smem_bytes() { return (PF_BM + 2 * 2 * PF_TK) * (HD + 8) * 2; }
+
+// FA2-style: every K (and V) fragment fetched with ldmatrix is used by both 16-row blocks of the
+// warp, the Q tile lives in shared memory and its fragments are re-read per key tile (keeping them
+// in registers next to two O accumulators would not fit).
+template <int HD>
 __global__ void __launch_bounds__(PF_THREADS) prefill_attn_kernel(const PfParams pin) {
   PfParams p = pin;
   if (p.pos_ptr) p.pos0 = p.pos_ptr[0];
   constexpr int LDS = HD + 8;
   constexpr int TILE_HALVES = PF_TK * LDS;
   extern __shared__ __align__(16) uint8_t smem_pf[];
-  __half* sK = reinterpret_cast<__half*>(smem_pf);
-  __half* sV = sK + 2 * TILE_HALVES;
-  const int qt = gridDim.x - 1 - blockIdx.x;          // heavy (late) query tiles first
+  __half* sQ = reinterpret_cast<__half*>(smem_pf);     // [PF_BM][LDS]
+  __half* sK = sQ + PF_BM * LDS;                       // [2][TK][LDS]
+  __half* sV = sK + 2 * TILE_HALVES;                   // [2][TK][LDS]
+  const int qt = gridDim.x - 1 - blockIdx.x;           // heavy (late) query tiles first
   const int h = blockIdx.y;
   const int kvh = h / (p.H / p.KV);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = lane >> 2, t4 = lane & 3;
   const int q0 = qt * PF_BM;
-  const int r0 = q0 + warp * 16 + g, r1 = r0 + 8;     // this thread's two query rows (chunk-relative)
-  const int pos_r0 = p.pos0 + r0, pos_r1 = p.pos0 + r1;
   const int last_q = min(q0 + PF_BM, p.T) - 1;
-  const int kend = p.pos0 + last_q + 1;               // exclusive
+  const int kend = p.pos0 + last_q + 1;                // exclusive
   int kfirst = 0;
   if (p.window > 0) { kfirst = p.pos0 + q0 - p.window + 1; kfirst = kfirst > 0 ? (kfirst / PF_TK) * PF_TK : 0; }
   const int ntiles = (kend - kfirst + PF_TK - 1) / PF_TK;
   const __half* kg = p.k + ((long long)p.row * p.KV + kvh) * p.Smax * HD;
   const __half* vg = p.v + ((long long)p.row * p.KV + kvh) * p.Smax * HD;
+  constexpr int CPR = HD / 8;
 
   auto load_tile = [&](int tile, int stage) {
     const int k0 = kfirst + tile * PF_TK;
-    constexpr int CPR = HD / 8;
     for (int i = threadIdx.x; i < PF_TK * CPR; i += PF_THREADS) {
       const int r = i / CPR, c = i - r * CPR;
       const bool ok = (k0 + r) < kend;
@@ -593,27 +634,32 @@ __global__ void __launch_bounds__(PF_THREADS) prefill_attn_kernel(const PfParams
       cp_async16(smem_u32(sV + soff), vg + goff, ok);
     }
   };
-
-  uint32_t qf[HD / 16][4];
-  {
-    const __half* qa = p.q + (long long)r0 * p.q_ld + h * HD;
-    const __half* qb = p.q + (long long)r1 * p.q_ld + h * HD;
-    const bool ok0 = r0 < p.T, ok1 = r1 < p.T;
-#pragma unroll
-    for (int kk = 0; kk < HD / 16; ++kk) {
-      qf[kk][0] = ok0 ? *reinterpret_cast<const uint32_t*>(qa + kk * 16 + 2 * t4) : 0u;
-      qf[kk][1] = ok1 ? *reinterpret_cast<const uint32_t*>(qb + kk * 16 + 2 * t4) : 0u;
-      qf[kk][2] = ok0 ? *reinterpret_cast<const uint32_t*>(qa + kk * 16 + 8 + 2 * t4) : 0u;
-      qf[kk][3] = ok1 ? *reinterpret_cast<const uint32_t*>(qb + kk * 16 + 8 + 2 * t4) : 0u;
-    }
+  // Q tile (rows beyond T zero-filled) travels with the first K/V tile
+  for (int i = threadIdx.x; i < PF_BM * CPR; i += PF_THREADS) {
+    const int r = i / CPR, c = i - r * CPR;
+    const bool ok = (q0 + r) < p.T;
+    cp_async16(smem_u32(sQ + r * LDS + c * 8), p.q + (long long)(ok ? q0 + r : q0) * p.q_ld + h * HD + c * 8, ok);
   }
-  float o[HD / 8][4];
-#pragma unroll
-  for (int i = 0; i < HD / 8; ++i) { o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f; }
-  float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
-
   load_tile(0, 0);
   cp_async_commit();
+
+  float o[2][HD / 8][4];
+#pragma unroll
+  for (int mb = 0; mb < 2; ++mb)
+#pragma unroll
+    for (int i = 0; i < HD / 8; ++i) { o[mb][i][0] = o[mb][i][1] = o[mb][i][2] = o[mb][i][3] = 0.f; }
+  float m_run[2][2], l_run[2][2];
+#pragma unroll
+  for (int mb = 0; mb < 2; ++mb) { m_run[mb][0] = m_run[mb][1] = -INFINITY; l_run[mb][0] = l_run[mb][1] = 0.f; }
+  // absolute positions of this thread's four query rows: [mb][0] = row g, [mb][1] = row g + 8
+  int qpos[2][2];
+#pragma unroll
+  for (int mb = 0; mb < 2; ++mb) {
+    qpos[mb][0] = p.pos0 + q0 + warp * 32 + mb * 16 + g;
+    qpos[mb][1] = qpos[mb][0] + 8;
+  }
+  const __half* wQ = sQ + (warp * 32) * LDS;
+
   for (int tile = 0; tile < ntiles; ++tile) {
     const int stage = tile & 1;
     if (tile + 1 < ntiles) load_tile(tile + 1, stage ^ 1);
@@ -623,92 +669,119 @@ __global__ void __launch_bounds__(PF_THREADS) prefill_attn_kernel(const PfParams
     const __half* tK = sK + stage * TILE_HALVES;
     const __half* tV = sV + stage * TILE_HALVES;
     const int key0 = kfirst + tile * PF_TK;
-    float s[PF_TK / 8][4];
+    // warp-uniform skip: a key tile entirely above this warp's last query row contributes nothing
+    const bool live = key0 <= p.pos0 + q0 + warp * 32 + 31;
+    if (live) {
+      float s[2][PF_TK / 8][4];
 #pragma unroll
-    for (int nb = 0; nb < PF_TK / 8; ++nb) { s[nb][0] = s[nb][1] = s[nb][2] = s[nb][3] = 0.f; }
+      for (int mb = 0; mb < 2; ++mb)
 #pragma unroll
-    for (int kp = 0; kp < HD / 32; ++kp) {
+        for (int nb = 0; nb < PF_TK / 8; ++nb) { s[mb][nb][0] = s[mb][nb][1] = s[mb][nb][2] = s[mb][nb][3] = 0.f; }
 #pragma unroll
-      for (int nb = 0; nb < PF_TK / 8; ++nb) {
-        uint32_t bf[4];
-        const int r = nb * 8 + (lane & 7);
-        const int c = kp * 32 + (lane >> 3) * 8;
-        ldsm_x4(bf, smem_u32(tK + r * LDS + c));
-        mma16816(s[nb], qf[2 * kp], bf[0], bf[1]);
-        mma16816(s[nb], qf[2 * kp + 1], bf[2], bf[3]);
+      for (int kp = 0; kp < HD / 32; ++kp) {
+        uint32_t qa[2][2][4];            // [mb][k-block within the pair][regs]
+#pragma unroll
+        for (int mb = 0; mb < 2; ++mb)
+#pragma unroll
+          for (int kb = 0; kb < 2; ++kb) {
+            const int mat = lane >> 3;
+            const int r = mb * 16 + (mat & 1) * 8 + (lane & 7);
+            const int c = kp * 32 + kb * 16 + (mat >> 1) * 8;
+            ldsm_x4(qa[mb][kb], smem_u32(wQ + r * LDS + c));
+          }
+#pragma unroll
+        for (int nb = 0; nb < PF_TK / 8; ++nb) {
+          uint32_t bf[4];
+          const int r = nb * 8 + (lane & 7);
+          const int c = kp * 32 + (lane >> 3) * 8;
+          ldsm_x4(bf, smem_u32(tK + r * LDS + c));
+#pragma unroll
+          for (int mb = 0; mb < 2; ++mb) {
+            mma16816(s[mb][nb], qa[mb][0], bf[0], bf[1]);
+            mma16816(s[mb][nb], qa[mb][1], bf[2], bf[3]);
+          }
+        }
       }
-    }
-    float mx0 = -INFINITY, mx1 = -INFINITY;
+      uint32_t pf[2][PF_TK / 16][4];
 #pragma unroll
-    for (int nb = 0; nb < PF_TK / 8; ++nb) {
+      for (int mb = 0; mb < 2; ++mb) {
+        float mx0 = -INFINITY, mx1 = -INFINITY;
 #pragma unroll
-      for (int e = 0; e < 2; ++e) {
-        const int key = key0 + nb * 8 + 2 * t4 + e;
-        const bool v0 = key <= pos_r0 && (p.window == 0 || key > pos_r0 - p.window);
-        const bool v1 = key <= pos_r1 && (p.window == 0 || key > pos_r1 - p.window);
-        const float a = v0 ? s[nb][e] * p.scale_log2 : -INFINITY;
-        const float c = v1 ? s[nb][2 + e] * p.scale_log2 : -INFINITY;
-        s[nb][e] = a; s[nb][2 + e] = c;
-        mx0 = fmaxf(mx0, a); mx1 = fmaxf(mx1, c);
+        for (int nb = 0; nb < PF_TK / 8; ++nb) {
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            const int key = key0 + nb * 8 + 2 * t4 + e;
+            const bool v0 = key <= qpos[mb][0] && (p.window == 0 || key > qpos[mb][0] - p.window);
+            const bool v1 = key <= qpos[mb][1] && (p.window == 0 || key > qpos[mb][1] - p.window);
+            const float a = v0 ? s[mb][nb][e] * p.scale_log2 : -INFINITY;
+            const float c = v1 ? s[mb][nb][2 + e] * p.scale_log2 : -INFINITY;
+            s[mb][nb][e] = a; s[mb][nb][2 + e] = c;
+            mx0 = fmaxf(mx0, a); mx1 = fmaxf(mx1, c);
+          }
+        }
+        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+        const float mn0 = fmaxf(m_run[mb][0], mx0), mn1 = fmaxf(m_run[mb][1], mx1);
+        const float mu0 = (mn0 == -INFINITY) ? 0.f : mn0, mu1 = (mn1 == -INFINITY) ? 0.f : mn1;
+        const float c0 = exp2f(m_run[mb][0] - mu0), c1 = exp2f(m_run[mb][1] - mu1);
+        float ls0 = 0.f, ls1 = 0.f;
+#pragma unroll
+        for (int nb = 0; nb < PF_TK / 8; ++nb) {
+          const float p00 = exp2f(s[mb][nb][0] - mu0), p01 = exp2f(s[mb][nb][1] - mu0);
+          const float p10 = exp2f(s[mb][nb][2] - mu1), p11 = exp2f(s[mb][nb][3] - mu1);
+          ls0 += p00 + p01; ls1 += p10 + p11;
+          pf[mb][nb >> 1][(nb & 1) * 2] = f2_to_h2(p00, p01);
+          pf[mb][nb >> 1][(nb & 1) * 2 + 1] = f2_to_h2(p10, p11);
+        }
+        ls0 += __shfl_xor_sync(0xffffffffu, ls0, 1); ls0 += __shfl_xor_sync(0xffffffffu, ls0, 2);
+        ls1 += __shfl_xor_sync(0xffffffffu, ls1, 1); ls1 += __shfl_xor_sync(0xffffffffu, ls1, 2);
+        l_run[mb][0] = l_run[mb][0] * c0 + ls0; l_run[mb][1] = l_run[mb][1] * c1 + ls1;
+        m_run[mb][0] = mn0; m_run[mb][1] = mn1;
+#pragma unroll
+        for (int i = 0; i < HD / 8; ++i) { o[mb][i][0] *= c0; o[mb][i][1] *= c0; o[mb][i][2] *= c1; o[mb][i][3] *= c1; }
       }
-    }
-    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
-    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
-    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
-    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
-    const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);
-    const float mu0 = (mn0 == -INFINITY) ? 0.f : mn0, mu1 = (mn1 == -INFINITY) ? 0.f : mn1;
-    const float c0 = exp2f(m0 - mu0), c1 = exp2f(m1 - mu1);
-    float ls0 = 0.f, ls1 = 0.f;
-    uint32_t pf[PF_TK / 16][4];
 #pragma unroll
-    for (int nb = 0; nb < PF_TK / 8; ++nb) {
-      const float p00 = exp2f(s[nb][0] - mu0), p01 = exp2f(s[nb][1] - mu0);
-      const float p10 = exp2f(s[nb][2] - mu1), p11 = exp2f(s[nb][3] - mu1);
-      ls0 += p00 + p01; ls1 += p10 + p11;
-      pf[nb >> 1][(nb & 1) * 2] = f2_to_h2(p00, p01);
-      pf[nb >> 1][(nb & 1) * 2 + 1] = f2_to_h2(p10, p11);
-    }
-    ls0 += __shfl_xor_sync(0xffffffffu, ls0, 1); ls0 += __shfl_xor_sync(0xffffffffu, ls0, 2);
-    ls1 += __shfl_xor_sync(0xffffffffu, ls1, 1); ls1 += __shfl_xor_sync(0xffffffffu, ls1, 2);
-    l0 = l0 * c0 + ls0; l1 = l1 * c1 + ls1;
-    m0 = mn0; m1 = mn1;
+      for (int kk2 = 0; kk2 < PF_TK / 16; ++kk2) {
 #pragma unroll
-    for (int i = 0; i < HD / 8; ++i) { o[i][0] *= c0; o[i][1] *= c0; o[i][2] *= c1; o[i][3] *= c1; }
+        for (int np = 0; np < HD / 16; ++np) {
+          uint32_t bf[4];
+          const int mat = lane >> 3;
+          const int r = kk2 * 16 + (mat & 1) * 8 + (lane & 7);
+          const int c = np * 16 + (mat >> 1) * 8;
+          ldsm_x4_t(bf, smem_u32(tV + r * LDS + c));
 #pragma unroll
-    for (int kk2 = 0; kk2 < PF_TK / 16; ++kk2) {
-#pragma unroll
-      for (int np = 0; np < HD / 16; ++np) {
-        uint32_t bf[4];
-        const int mat = lane >> 3;
-        const int r = kk2 * 16 + (mat & 1) * 8 + (lane & 7);
-        const int c = np * 16 + (mat >> 1) * 8;
-        ldsm_x4_t(bf, smem_u32(tV + r * LDS + c));
-        mma16816(o[2 * np], pf[kk2], bf[0], bf[1]);
-        mma16816(o[2 * np + 1], pf[kk2], bf[2], bf[3]);
+          for (int mb = 0; mb < 2; ++mb) {
+            mma16816(o[mb][2 * np], pf[mb][kk2], bf[0], bf[1]);
+            mma16816(o[mb][2 * np + 1], pf[mb][kk2], bf[2], bf[3]);
+          }
+        }
       }
     }
     __syncthreads();
   }
   cp_async_wait<0>();
-  const float i0 = l0 > 0.f ? 1.f / l0 : 0.f, i1 = l1 > 0.f ? 1.f / l1 : 0.f;
-  if (r0 < p.T) {
-    __half* op = p.out + (long long)r0 * p.o_ld + h * HD;
 #pragma unroll
-    for (int i = 0; i < HD / 8; ++i)
-      *reinterpret_cast<uint32_t*>(op + i * 8 + 2 * t4) = f2_to_h2(o[i][0] * i0, o[i][1] * i0);
-  }
-  if (r1 < p.T) {
-    __half* op = p.out + (long long)r1 * p.o_ld + h * HD;
+  for (int mb = 0; mb < 2; ++mb) {
 #pragma unroll
-    for (int i = 0; i < HD / 8; ++i)
-      *reinterpret_cast<uint32_t*>(op + i * 8 + 2 * t4) = f2_to_h2(o[i][2] * i1, o[i][3] * i1);
+    for (int hf = 0; hf < 2; ++hf) {
+      const int r = q0 + warp * 32 + mb * 16 + g + hf * 8;
+      if (r < p.T) {
+        const float l = l_run[mb][hf];
+        const float inv = l > 0.f ? 1.f / l : 0.f;
+        __half* op = p.out + (long long)r * p.o_ld + h * HD;
+#pragma unroll
+        for (int i = 0; i < HD / 8; ++i)
+          *reinterpret_cast<uint32_t*>(op + i * 8 + 2 * t4) = f2_to_h2(o[mb][i][2 * hf] * inv, o[mb][i][2 * hf + 1] * inv);
+      }
+    }
   }
 }
 
 template <int HD>
 static int launch_prefill(const PfParams& p, cudaStream_t st) {
-  constexpr int SMEM = 2 * 2 * PF_TK * (HD + 8) * 2;
+  constexpr int SMEM = pf_smem_bytes<HD>();
   static bool attr_set = false;
   if (!attr_set) {
     if (cudaFuncSetAttribute(prefill_attn_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM) != cudaSuccess)
@@ -729,11 +802,11 @@ int init_attn() {
     if (!ok) return ERR_ARCH;
   }
   if (cudaFuncSetAttribute(decode_attn_kernel<128, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_NST * 2 * DEC_TK * (128 + 8) * 2) != cudaSuccess) return ERR_ARCH;
-  if (cudaFuncSetAttribute(decode_attn_kernel<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_NST * 2 * DEC_TK * (128 + 8) * 2) != cudaSuccess) return ERR_ARCH;
+  if (cudaFuncSetAttribute(decode_attn_kernel<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_NST * 2 * DEC_TK * (128 + 8) * 2 + 8 * 8 * (128 + 2) * 4) != cudaSuccess) return ERR_ARCH;
   if (cudaFuncSetAttribute(decode_attn_kernel<64, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_NST * 2 * DEC_TK * (64 + 8) * 2) != cudaSuccess) return ERR_ARCH;
-  if (cudaFuncSetAttribute(decode_attn_kernel<64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_NST * 2 * DEC_TK * (64 + 8) * 2) != cudaSuccess) return ERR_ARCH;
-  if (cudaFuncSetAttribute(prefill_attn_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 2 * PF_TK * (128 + 8) * 2) != cudaSuccess) return ERR_ARCH;
-  if (cudaFuncSetAttribute(prefill_attn_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 2 * PF_TK * (64 + 8) * 2) != cudaSuccess) return ERR_ARCH;
+  if (cudaFuncSetAttribute(decode_attn_kernel<64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_NST * 2 * DEC_TK * (64 + 8) * 2 + 8 * 8 * (64 + 2) * 4) != cudaSuccess) return ERR_ARCH;
+  if (cudaFuncSetAttribute(prefill_attn_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, pf_smem_bytes<128>()) != cudaSuccess) return ERR_ARCH;
+  if (cudaFuncSetAttribute(prefill_attn_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, pf_smem_bytes<64>()) != cudaSuccess) return ERR_ARCH;
   return OK;
 }
 
@@ -752,3 +825,5 @@ int prefill_attn(const void* q, long long q_ld, const void* kcache, const void* 
 }
 
 }  // namespace b2
+
+B2_TL_DEFINE_DUMP(b2_tl_dump_attn)

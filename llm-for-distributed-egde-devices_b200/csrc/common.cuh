@@ -327,4 +327,62 @@ constexpr uint32_t umma_idesc(uint32_t dfmt, uint32_t afmt, uint32_t bfmt, uint3
 }
 constexpr uint32_t IDESC_FMT_S32 = 2, IDESC_FMT_F32 = 1, IDESC_S8 = 1, IDESC_F16 = 0;
 
+// ---------------------------------------------------------------------------------------------
+// Timeline probe (tools/timeline.py; `make timeline` builds libb200stage_tl.so with -DB2_TIMELINE).
+// Thread 0 of every CTA stamps %globaltimer at named points of a kernel into a per-translation-unit
+// device array; the product build compiles tl_mark() to nothing.
+// ---------------------------------------------------------------------------------------------
+#ifdef B2_TIMELINE
+constexpr unsigned TL_CAP = 1u << 20;
+struct TlEvent { unsigned long long t; unsigned tag; unsigned cta; };
+static __device__ TlEvent g_tl[TL_CAP];
+static __device__ unsigned g_tl_n;
+// A mark only stores the timer into shared memory; the CTA's marks go to global memory together at
+// tl_flush() (one atomic per CTA, after the last point), so the probe adds no memory round trip
+// between the points it measures.
+constexpr unsigned TL_POINTS = 8;
+B2_DEVINL unsigned long long* tl_slots() {
+  __shared__ unsigned long long s_tl[TL_POINTS];
+  return s_tl;
+}
+B2_DEVINL void tl_mark(unsigned kernel_id, unsigned point) {
+  if (threadIdx.x == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    tl_slots()[point] = t;
+  }
+}
+B2_DEVINL void tl_flush(unsigned kernel_id, unsigned point_mask) {
+  if (threadIdx.x == 0) {
+    const unsigned n = __popc(point_mask);
+    unsigned i = atomicAdd(&g_tl_n, n);
+    unsigned smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    const unsigned cta = (smid << 20) | (blockIdx.x + blockIdx.y * gridDim.x + blockIdx.z * gridDim.x * gridDim.y);
+    for (unsigned pt = 0; pt < TL_POINTS; ++pt) {
+      if (!((point_mask >> pt) & 1u)) continue;
+      if (i < TL_CAP) { g_tl[i].t = tl_slots()[pt]; g_tl[i].tag = (kernel_id << 8) | pt; g_tl[i].cta = cta; }
+      ++i;
+    }
+  }
+}
+// copies the events to `host` (cap events), resets the counter, returns the number recorded
+#define B2_TL_DEFINE_DUMP(fn)                                                              \
+  extern "C" int fn(void* host, int cap) {                                                 \
+    unsigned n = 0;                                                                        \
+    cudaDeviceSynchronize();                                                               \
+    cudaMemcpyFromSymbol(&n, b2::g_tl_n, sizeof(n));                                       \
+    if (n > b2::TL_CAP) n = b2::TL_CAP;                                                    \
+    if ((int)n > cap) n = cap;                                                             \
+    if (host && n) cudaMemcpyFromSymbol(host, b2::g_tl, (size_t)n * sizeof(b2::TlEvent));  \
+    const unsigned z = 0;                                                                  \
+    cudaMemcpyToSymbol(b2::g_tl_n, &z, sizeof(z));                                         \
+    return (int)n;                                                                         \
+  }
+#else
+#define tl_mark(kernel_id, point) ((void)0)
+#define tl_flush(kernel_id, point_mask) ((void)0)
+#define B2_TL_DEFINE_DUMP(fn)
+#endif
+
 }  // namespace b2

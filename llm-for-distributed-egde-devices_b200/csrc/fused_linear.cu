@@ -171,6 +171,8 @@ B2_DEVINL void fused_phase(const FusedParams& p, uint8_t* xs, SYNC sync_fn, bool
     }
   };
   // ---- 1. first two weight batches: independent of the predecessor kernel ----------------------
+  constexpr unsigned TLK = 16 + OKIND * 4 + XK;     // timeline probe id (tools/timeline.py)
+  tl_mark(TLK, 0);
   if (trigger) pdl_launch_dependents();
   if (threadIdx.x == 0) {
     // Pull the head of the next kernels' weights into L2 while this kernel streams its own: the
@@ -205,7 +207,9 @@ B2_DEVINL void fused_phase(const FusedParams& p, uint8_t* xs, SYNC sync_fn, bool
     asm volatile("cp.async.commit_group;" ::: "memory");
   }
   // ---- 2. everything below may read the predecessor's output ---------------------------------
+  tl_mark(TLK, 1);
   sync_fn();
+  tl_mark(TLK, 2);
   if (p.zero_amax != nullptr && blockIdx.x == 0 && threadIdx.x < p.M) p.zero_amax[threadIdx.x] = 0.0f;
   if (fast) {
     asm volatile("cp.async.wait_group 0;" ::: "memory");
@@ -359,6 +363,7 @@ B2_DEVINL void fused_phase(const FusedParams& p, uint8_t* xs, SYNC sync_fn, bool
     }
   }
   __syncthreads();
+  tl_mark(TLK, 3);
   // ---- 4. persistent weight stream: two batches always in flight per lane ----------------------
   int acc[FL_ROWS][MT];
 #pragma unroll
@@ -501,7 +506,10 @@ B2_DEVINL void fused_phase(const FusedParams& p, uint8_t* xs, SYNC sync_fn, bool
     if (cc.it >= items_total) break;
     step(w2);
   }
+  tl_mark(TLK, 4);
   flush();
+  tl_mark(TLK, 5);
+  tl_flush(TLK, 0x3Fu);
 }
 
 struct SyncPDL {
@@ -779,3 +787,5 @@ static bool fl_touch_m() {
 int init_fused() { fl_sm_count(); return (fl_touch_m<1>() && fl_touch_m<2>() && fl_touch_m<4>() && fl_touch_m<8>()) ? OK : ERR_ARCH; }
 
 }  // namespace b2
+
+B2_TL_DEFINE_DUMP(b2_tl_dump_fused)

@@ -466,6 +466,14 @@ int gemm_w8a8(const int8_t* A, const int8_t* W, const float* a_scale, const floa
   // Measured on B200 (tools/kbench.py, profiles/r01_*): the kernel is bound by operand latency /
   // bytes in flight, not by L2 bandwidth, so 128x128 tiles with a 6-deep ring beat 128x256 with 4
   // stages on every Llama-2-7B shape (1.4-1.66 vs 1.0-1.47 PTOP/s at M = 512).
+  // With enough row tiles the picture flips: at M = 2048 a 128x256 tile (half the A re-reads, twice
+  // the MMA work per staged A tile) wins whenever its tiles still fill the persistent grid's waves
+  // (gate_up 174 vs 188 us, down 83 vs 98 us), i.e. wave efficiency tiles/(ceil(tiles/SMs)*SMs) >= 0.8.
+  if (N % 256 == 0) {
+    const int t256 = m_tiles * (N / 256);
+    const int waves = (t256 + sms - 1) / sms;
+    if (t256 * 5 >= waves * sms * 4) return launch_tc<256, 4, KIND_I8, 1>(A, W, p, st);
+  }
   if (N >= 128 && m_tiles * ((N + 127) / 128) >= sms / 2) return launch_tc<128, 6, KIND_I8, 1>(A, W, p, st);
   if (N >= 64) return launch_tc<64, 8, KIND_I8, 1>(A, W, p, st);
   return launch_tc<32, 8, KIND_I8, 1>(A, W, p, st);

@@ -5,6 +5,8 @@ torch's job here) and forwards raw pointers.  All compute happens in libb200stag
 """
 from __future__ import annotations
 
+import ctypes as C
+
 import torch
 
 from . import _abi
@@ -90,7 +92,14 @@ PREFETCH_BYTES = 24 << 20      # head of a weight matrix worth pulling into L2 a
 
 
 def _pf(prefetch, i):
-    """(pointer, bytes) of the i-th prefetch hint: a tensor (its first PREFETCH_BYTES) or None."""
+    """(pointer, bytes) of the i-th prefetch hint: a tensor (its first PREFETCH_BYTES), a
+    (tensor, byte_offset, bytes) slice of one, or None."""
+    if prefetch is not None and i < len(prefetch) and isinstance(prefetch[i], tuple):
+        t, off, nb = prefetch[i]
+        total = t.numel() * t.element_size()
+        off = min(int(off), total) & ~15
+        nb = max(0, min(int(nb), total - off)) & ~15
+        return (C.c_void_p(t.data_ptr() + off), nb) if nb else (None, 0)
     if prefetch is None or i >= len(prefetch) or prefetch[i] is None:
         return None, 0
     t = prefetch[i]
@@ -187,23 +196,26 @@ def decode_attn_workspace_bytes(B, H, KV, hd, max_seqlen, window=0):
 
 
 def decode_attn(qkv, kcache, vcache, seqlens, H, KV, hd, max_seqlen, scale, window=0, rows=None, out=None,
-                workspace=None):
-    """One query token per sequence; q read in place from the qkv buffer.  b2_decode_attn."""
+                workspace=None, prefetch=None):
+    """One query token per sequence; q read in place from the qkv buffer.  b2_decode_attn.
+    prefetch: up to two L2 hints (see _pf) for weights that later launches stream."""
     _cuda(qkv, kcache, vcache, seqlens, rows, out, workspace)
     B = qkv.shape[0]
     Smax = kcache.shape[2]
     o = out if out is not None else torch.empty((B, H * hd), dtype=torch.float16, device=qkv.device)
     wsb = 0 if workspace is None else workspace.numel() * workspace.element_size()
+    p0, n0 = _pf(prefetch, 0)
+    p1, n1 = _pf(prefetch, 1)
     check(_abi.lib().b2_decode_attn(ptr(qkv), qkv.stride(0), ptr(kcache), ptr(vcache), ptr(seqlens), ptr(rows), ptr(o),
                                     o.stride(0), ptr(workspace), wsb, B, H, KV, hd, Smax, int(max_seqlen),
-                                    float(scale), int(window), stream_handle()), "b2_decode_attn")
+                                    float(scale), int(window), p0, n0, p1, n1, stream_handle()), "b2_decode_attn")
     return o
 
 
 def decode_attn_static(qkv, kcache, vcache, seqlens, H, KV, hd, max_seqlen, scale, window=0, rows=None, out=None):
     """decode_attn without a caller workspace, for hosts that cannot allocate device memory at
     call time (allocator closed after start-up, cudaMalloc banned on the decode thread, memory
-    owned by a plugin host).  The split-KV partials use a fixed 1 MiB array inside the library;
+    owned by a plugin host).  The split-KV partials use a fixed 512 KiB array inside the library;
     bigger problems raise B2Error (too large).  Calls share that array, so do not let two of them
     overlap on the GPU; make the first call on a device before any stream capture.
     b2_decode_attn_static.  (`out` is allocated here only when the caller passes none.)"""

@@ -19,12 +19,29 @@ advances them itself, so one graph serves every step.
 from __future__ import annotations
 
 import gc
+import os
 
 import numpy as np
 import torch
 
 from . import ops, weights
 from .config import ModelConfig, get_config
+
+
+# Measured on B200 (tools/envsweep.sh): see DESIGN.md "L2 hint plan".
+DEFAULT_PF_PLAN = "qkv=wo:0:24,wgu:0:24;gu=wd:0:24;down=nqkv:0:24"
+
+
+def _parse_pf_plan(text: str):
+    """'launch=weight:offMB:MB,weight:offMB:MB;launch=...' -> {launch: [(weight, offMB, MB)]}."""
+    plan = {}
+    for part in filter(None, (x.strip() for x in text.split(";"))):
+        launch, _, items = part.partition("=")
+        plan[launch.strip()] = []
+        for item in filter(None, (x.strip() for x in items.split(","))):
+            name, off, mb = item.split(":")
+            plan[launch.strip()].append((name, float(off), float(mb)))
+    return plan
 
 
 class KVCache:
@@ -98,6 +115,9 @@ class Stage:
         self.launches = 0          # kernels of ours launched (bench.py's gpu_launches claim)
         self.fuse_decode = True    # decode steps with <= 8 tokens use b2_fused_linear
         self.l2_prefetch = True    # fused decode kernels pull the head of the next weights into L2
+        # which launch of a decoder layer hints which later weights into L2: launch -> [(weight, MB offset, MB)]
+        # ("nqkv" = the next layer's wqkv, or the LM head after the last layer)
+        self.pf_plan = _parse_pf_plan(os.environ.get("B2_PF_PLAN", DEFAULT_PF_PLAN))
         # o_proj -> gate_up -> down -> next qkv as one persistent launch with grid barriers: exact, but measured
         # SLOWER than four PDL-chained launches on B200 (38.0 vs 33.8 us per layer tail), so off by default
         self.fuse_tail = False
@@ -206,24 +226,23 @@ class Stage:
                 ops.fused_qkv(h, lw["wqkv"], lw["s_qkv"], qkv, self.cos, self.sin, dpos, kc, vc, H, KV, hd,
                               x_kind=xk_norm, gamma=lw["ln1_g"], beta=lw.get("ln1_b"), smooth=lw["sm_qkv"],
                               eps=cfg.eps, bias=lw.get("b_qkv"), seq_ids=dseq, seq0=row0, use_rope=cfg.rope,
-                              prefetch=(lw["wo"], lw["wgu"]) if self.l2_prefetch else None)
+                              prefetch=self._hints("qkv", lw, li))
                 ops.decode_attn(qkv, kc, vc, dlens, H, KV, hd, max_len, self.scale, cfg.window, rows=dseq, out=attn,
-                                workspace=ws)
+                                workspace=ws, prefetch=self._hints("attn", lw, li))
                 ops.fused_linear(attn, lw["wo"], lw["s_o"], x_kind=ops.X_PLAIN, smooth=lw["sm_o"], bias=lw.get("b_o"),
-                                 residual=h, out=h_alt, zero_amax=buf.amax)
+                                 residual=h, out=h_alt, zero_amax=buf.amax, prefetch=self._hints("o", lw, li))
                 n += 3 if ws is None else 4
                 if cfg.gated:
-                    nxt = layers[li + 1]["wqkv"] if li + 1 < len(layers) else self.w.get("lm_head")
                     ops.fused_linear(h_alt, lw["wgu"], lw["s_gu"], x_kind=xk_norm, gamma=lw["ln2_g"],
                                      beta=lw.get("ln2_b"), smooth=lw["sm_gu"], eps=cfg.eps, bias=lw.get("b_gu"),
                                      out=buf.y32[:T], out_kind=ops.O_GATED, act=0 if cfg.act == "silu" else 1,
                                      out_smooth=lw["sm_d"], out_amax=buf.amax,
-                                     prefetch=(lw["wd"],) if self.l2_prefetch else None)
+                                     prefetch=self._hints("gu", lw, li))
                     # (also tried on B200 and rejected: prefetching the next layer's K/V block here, 442 vs
                     #  480 tok/s, and an L2 evict-first policy on the weight stream, 459 vs 480 tok/s)
                     ops.fused_linear(buf.y32[:T], lw["wd"], lw["s_d"], x_kind=ops.X_Y32, x_amax=buf.amax,
                                      bias=lw.get("b_d"), residual=h_alt, out=h,
-                                     prefetch=(nxt,) if self.l2_prefetch else None)
+                                     prefetch=self._hints("down", lw, li))
                     n += 2
                 else:
                     ops.fused_linear(h_alt, lw["wgu"], lw["s_gu"], x_kind=xk_norm, gamma=lw["ln2_g"],
@@ -269,6 +288,21 @@ class Stage:
         hn = ops.norm(hsel, self.w["lnf_g"], self.w.get("lnf_b"), cfg.eps, out=buf.hn[: hsel.shape[0]])
         lg = ops.lm_head(hn, self.w["lm_head"], out=out)
         return lg, n + 2
+
+    def _hints(self, launch: str, lw, li: int):
+        """The (up to two) L2 hints the `launch` kernel of layer li issues, per self.pf_plan."""
+        if not self.l2_prefetch:
+            return None
+        out = []
+        layers = self.w["layers"]
+        for name, off_mb, mb in self.pf_plan.get(launch, [])[:2]:
+            if name == "nqkv":
+                t = layers[li + 1]["wqkv"] if li + 1 < len(layers) else self.w.get("lm_head")
+            else:
+                t = lw.get(name)
+            if t is not None and mb > 0:
+                out.append((t, int(off_mb * (1 << 20)), int(mb * (1 << 20))))
+        return tuple(out) if out else None
 
     # ------------------------------------------------------------------------------------------
     @staticmethod

@@ -41,8 +41,8 @@ def test_error_strings_and_argument_checks_need_no_gpu():
     assert L.b2_gemm_w8a8(C.c_void_p(p.value + 1), p, p, p, None, None, p, None, 4, 16, 16, None) == -2
     assert L.b2_norm_quant(None, None, None, None, None, None, 0, 64, 1e-5, None) == 0
     assert L.b2_norm_quant(None, None, None, None, None, None, 3, 64, 1e-5, None) == -3
-    assert L.b2_decode_attn(p, 64, p, p, p, None, p, 64, None, 0, 1, 6, 4, 64, 16, 8, 0.1, 0, None) == -1  # H % KV
-    assert L.b2_decode_attn(p, 64, p, p, p, None, p, 64, None, 0, 1, 4, 4, 80, 16, 8, 0.1, 0, None) == -6  # head_dim
+    assert L.b2_decode_attn(p, 64, p, p, p, None, p, 64, None, 0, 1, 6, 4, 64, 16, 8, 0.1, 0, None, 0, None, 0, None) == -1  # H % KV
+    assert L.b2_decode_attn(p, 64, p, p, p, None, p, 64, None, 0, 1, 4, 4, 80, 16, 8, 0.1, 0, None, 0, None, 0, None) == -6  # head_dim
     assert L.b2_lm_head(None, None, None, 0, 8, 8, None) == 0
 
 
