@@ -43,10 +43,10 @@ struct FusedParams {
   __half* kcache; __half* vcache; int H, KV, hd, Smax, use_rope;
 };
 
-constexpr int FL_THREADS = 256, FL_WARPS = 8, FL_ROWS = 2, FL_UNR = 4;
+constexpr int FL_THREADS = 512, FL_WARPS = 16, FL_ROWS = 2, FL_UNR = 4;
 constexpr int FL_SMEM_FULL = 200 * 1024;
 #ifndef FL_CTAS_PER_SM
-#define FL_CTAS_PER_SM 2
+#define FL_CTAS_PER_SM 1
 #endif
 
 B2_DEVINL void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
@@ -540,7 +540,7 @@ struct SyncGrid {
 };
 
 template <int MT, int XK, int OKIND>
-__global__ void __launch_bounds__(FL_THREADS, 2) fused_gemv_kernel(const FusedParams p) {
+__global__ void __launch_bounds__(FL_THREADS, FL_CTAS_PER_SM) fused_gemv_kernel(const FusedParams p) {
   extern __shared__ __align__(16) uint8_t xs[];        // int8 activations [MT][K] + staging
   fused_phase<MT, XK, OKIND, true>(p, xs, SyncPDL{}, true);
 }
@@ -550,7 +550,7 @@ __global__ void __launch_bounds__(FL_THREADS, 2) fused_gemv_kernel(const FusedPa
 // Each phase issues its first weight batches and its L2 hints BEFORE the grid barrier that ends the
 // previous phase, so the HBM stream does not stop at the three dependency points.
 template <int MT, int NORMK, bool QKV>
-__global__ void __launch_bounds__(FL_THREADS, 2)
+__global__ void __launch_bounds__(FL_THREADS, FL_CTAS_PER_SM)
 fused_tail_kernel(const FusedParams po, const FusedParams pg, const FusedParams pd, const FusedParams pq, unsigned* ctr) {
   extern __shared__ __align__(16) uint8_t xs[];
   unsigned* err = ctr + 3;

@@ -116,12 +116,12 @@ for k in np.unique(kid):
     p = pt[kid == k]
     ncta = int((e["cta"] & 0xFFFFF).max()) + 1
     per = {}
-    for q in range(6):
+    for q in range(8):
         eq = e[p == q]
         if len(eq):
-            # flush order keeps a CTA's points adjacent: sort by (cta, time) within each launch
             per[q] = eq
-    qs = sorted(per)
+    # points 6 and 7 sit inside the activation prologue: 6 = x loaded and squared, 7 = norm statistics reduced
+    qs = sorted(per, key=lambda q: {6: 2.3, 7: 2.6}.get(q, q))
     nl = len(per[qs[0]]) // ncta
     line = [f"{NAMES.get(int(k), k):22s}"]
     for qa, qb in zip(qs[:-1], qs[1:]):
