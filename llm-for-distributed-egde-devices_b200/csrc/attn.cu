@@ -140,7 +140,9 @@ B2_DEVINL void dec_prefetch_slice(const uint8_t* ptr, long long bytes, int cta, 
   if (ptr == nullptr || bytes <= 0) return;
   constexpr long long PIECE = 16 * 1024;
   const long long npieces = (bytes + PIECE - 1) / PIECE;
-  for (long long i = cta; i < npieces; i += nctas) {
+  if (threadIdx.x & 31) return;                      // lane 0 of each warp: the requests serialise within a warp
+  const int warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  for (long long i = cta + (long long)nctas * warp; i < npieces; i += (long long)nctas * nwarps) {
     const long long off = i * PIECE;
     const uint32_t n = (uint32_t)((bytes - off < PIECE ? bytes - off : PIECE) & ~15ll);
     if (n) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(ptr + off), "r"(n) : "memory");
@@ -209,7 +211,7 @@ __global__ void __launch_bounds__(DEC_THREADS, 2) decode_attn_kernel(const DecPa
     if (sidx < ntiles) load_tile(sidx, sidx);
     cp_async_commit();
   }
-  if (threadIdx.x == DEC_THREADS - 1) {
+  {
     const int cta = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
     const int nctas = gridDim.x * gridDim.y * gridDim.z;
     dec_prefetch_slice(p.pf0, p.pf0_bytes, cta, nctas);

@@ -55,12 +55,16 @@ B2_DEVINL void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 B2_DEVINL void fl_cp_async16(void* smem_dst, const void* src) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(src) : "memory");
 }
-// this CTA's share of an L2 prefetch of [ptr, ptr+bytes): 16 KB bulk-prefetch requests
+// this CTA's share of an L2 prefetch of [ptr, ptr+bytes): 16 KB bulk-prefetch requests, dealt out to
+// lane 0 of successive warps (a bulk prefetch takes 50-100 ns to issue and they serialise within a
+// warp: ten in one thread held that warp's first weight loads back by more than a microsecond,
+// tools/timeline.py)
 B2_DEVINL void fl_prefetch_slice(const uint8_t* ptr, long long bytes) {
-  if (ptr == nullptr || bytes <= 0) return;
+  if (ptr == nullptr || bytes <= 0 || (threadIdx.x & 31)) return;
   constexpr long long PIECE = 16 * 1024;
   const long long npieces = (bytes + PIECE - 1) / PIECE;
-  for (long long i = blockIdx.x; i < npieces; i += gridDim.x) {
+  const int warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  for (long long i = blockIdx.x + (long long)gridDim.x * warp; i < npieces; i += (long long)gridDim.x * nwarps) {
     const long long off = i * PIECE;
     const uint32_t n = (uint32_t)((bytes - off < PIECE ? bytes - off : PIECE) & ~15ll);
     if (n) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(ptr + off), "r"(n) : "memory");
@@ -148,6 +152,11 @@ B2_DEVINL void fused_phase(const FusedParams& p, uint8_t* xs, SYNC sync_fn, bool
   const int stride = gridDim.x * FL_WARPS;
   const int half_hd = (OKIND == O_QKV) ? (p.hd >> 1) : 1;
   struct Cur { int it, j; const int8_t* r0; const int8_t* r1; };
+  // Item schedule: warp w of CTA c takes items c*16 + w + k*stride.  Two "fairer" schedules were
+  // measured on B200 and are slower: w*grid + c everywhere (518 vs 508 us per 8-layer token: a CTA's
+  // 16 warps then touch 32 different 2 MB pages), and dealing only the partial last round out evenly
+  // (530 us): when every CTA finishes at the same moment the successor kernel's CTA launch wave and
+  // pre-wait loads are fully exposed, whereas CTAs that skip the last round hand their SM over early.
   auto set_rows = [&](Cur& c) {
     int n0, n1;
     if (OKIND == O_GATED) { n0 = c.it; n1 = F + c.it; }
@@ -174,12 +183,7 @@ B2_DEVINL void fused_phase(const FusedParams& p, uint8_t* xs, SYNC sync_fn, bool
   constexpr unsigned TLK = 16 + OKIND * 4 + XK;     // timeline probe id (tools/timeline.py)
   tl_mark(TLK, 0);
   if (trigger) pdl_launch_dependents();
-  if (threadIdx.x == 0) {
-    // Pull the head of the next kernels' weights into L2 while this kernel streams its own: the
-    // successor's ramp-up then hits L2 and HBM never idles across the kernel boundary.
-    fl_prefetch_slice(p.pf0, p.pf0_bytes);
-    fl_prefetch_slice(p.pf1, p.pf1_bytes);
-  }
+  tl_mark(TLK, 6);
   uint4 w[FL_UNR][FL_ROWS], w2[FL_UNR][FL_ROWS];
   Cur cc;
   cc.it = blockIdx.x * FL_WARPS + warp; cc.j = 0; cc.r0 = p.W; cc.r1 = p.W;
@@ -187,6 +191,13 @@ B2_DEVINL void fused_phase(const FusedParams& p, uint8_t* xs, SYNC sync_fn, bool
   Cur lc = cc;
   load_batch(w, lc); advance(lc);
   load_batch(w2, lc); advance(lc);
+  tl_mark(TLK, 7);
+  {
+    // Pull the head of the next kernels' weights into L2 while this kernel streams its own: the
+    // successor's ramp-up then hits L2 and HBM never idles across the kernel boundary.
+    fl_prefetch_slice(p.pf0, p.pf0_bytes);
+    fl_prefetch_slice(p.pf1, p.pf1_bytes);
+  }
   if (!FIRST) __syncthreads();     // every warp has left the previous phase: its shared memory may be reused
   // Norm gains / smoothing multipliers are weights too: stage them in shared memory with cp.async
   // before the dependency wait, so the prologue's critical path is one L2 read of x plus two block
@@ -509,7 +520,7 @@ B2_DEVINL void fused_phase(const FusedParams& p, uint8_t* xs, SYNC sync_fn, bool
   tl_mark(TLK, 4);
   flush();
   tl_mark(TLK, 5);
-  tl_flush(TLK, 0x3Fu);
+  tl_flush(TLK, 0xFFu);
 }
 
 struct SyncPDL {
@@ -584,7 +595,7 @@ static int launch_fused(const FusedParams& pin, cudaStream_t st) {
   }
   const int items = (OKIND == O_F16) ? (p.N + 1) / 2 : p.N / 2;
   int grid = (items + FL_WARPS - 1) / FL_WARPS;
-  const int cap = fl_sm_count() * FL_CTAS_PER_SM;                   // persistent: 2 CTAs per SM, prologue once per CTA
+  const int cap = fl_sm_count() * FL_CTAS_PER_SM;                   // persistent: one 512-thread CTA per SM (grids of 104..140 CTAs measured slower)
   if (grid > cap) grid = cap;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);

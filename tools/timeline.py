@@ -121,7 +121,7 @@ for k in np.unique(kid):
         if len(eq):
             per[q] = eq
     # points 6 and 7 sit inside the activation prologue: 6 = x loaded and squared, 7 = norm statistics reduced
-    qs = sorted(per, key=lambda q: {6: 2.3, 7: 2.6}.get(q, q))
+    qs = sorted(per, key=lambda q: {6: 0.3, 7: 0.6}.get(q, q))
     nl = len(per[qs[0]]) // ncta
     line = [f"{NAMES.get(int(k), k):22s}"]
     for qa, qb in zip(qs[:-1], qs[1:]):
