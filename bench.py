@@ -240,7 +240,11 @@ def run_ours(a):
             toks.append(pipe.return_tokens(t))
         e1.record()
         # NEW-1 decode steps for the n_prompts sequences as one continuous pipeline (no round barrier)
+        t_cpu0 = time.perf_counter()
         out = pipe.decode_stream(toks, [[P] for _ in range(n_prompts)], [[p] for p in range(n_prompts)], NEW - 1)
+        if os.environ.get("B2_BENCH_DEBUG"):      # host enqueue time of the decode phase vs its device time
+            print(f"[rank {rank}] decode enqueue {1e3 * (time.perf_counter() - t_cpu0):.1f} ms for {(NEW - 1) * n_prompts} ticks",
+                  file=sys.stderr, flush=True)
         gen = [[toks[p]] + out[p] for p in range(n_prompts)] if out is not None else None
         e2.record()
         if record is not None:
