@@ -203,13 +203,20 @@ class DistPipeline:
         """Collective: a separate communicator for the token return path, so that a token send
         queued on one rank can never sit in front of a hidden-state transfer (and vice versa)."""
         self.tok_group = self.dist.new_group(ranks=list(range(self.world))) if self.world > 1 else None
+        # Two more communicators for the hidden-state edges, alternating along the pipeline (edge r -> r+1
+        # uses number r % 2), so that a stage's receive from its predecessor and its send to its successor
+        # never queue behind each other on one communicator's stream.
+        self._edge_groups = [self.dist.new_group(ranks=list(range(self.world))) for _ in range(2)] if self.world > 1 else None
+        if self._edge_groups is not None:
+            self.group_in = self._edge_groups[(self.rank - 1) % 2]
+            self.group_out = self._edge_groups[self.rank % 2]
         if self.device.type == "cuda":
             self._rs, self._ss = torch.cuda.Stream(self.device), torch.cuda.Stream(self.device)
             self._rs_tok, self._ss_tok = torch.cuda.Stream(self.device), torch.cuda.Stream(self.device)
 
     def _recv(self, shape, dtype, src, tok=False):
         buf = torch.empty(shape, dtype=dtype, device=self.device)
-        group = getattr(self, "tok_group", None) if tok else self.group
+        group = getattr(self, "tok_group", None) if tok else getattr(self, "group_in", self.group)
         if self.device.type != "cuda" or not hasattr(self, "_rs"):
             self.dist.recv(buf, src=src, group=group)
             return buf
@@ -223,7 +230,7 @@ class DistPipeline:
         return buf
 
     def _send(self, t, dst, tok=False):
-        group = getattr(self, "tok_group", None) if tok else self.group
+        group = getattr(self, "tok_group", None) if tok else getattr(self, "group_out", self.group)
         if self.device.type != "cuda" or not hasattr(self, "_ss"):
             # CPU (gloo tests): a blocking send could sit in front of the receive the peer needs
             # first; post it without waiting and reap finished handles later
@@ -304,6 +311,8 @@ class DistPipeline:
         (needed on rank 0).  Returns, on rank 0 and on the last rank, tokens[g] = list of `steps`
         tensors [B_g]; None on the ranks in between."""
         G = len(rows_per_group)
+        if self.device.type == "cuda" and getattr(self, "stage", None) is not None and getattr(self, "use_graphs", True):
+            return self._decode_stream_graphs(first_tokens, start_positions, rows_per_group, steps)
         gen = [[] for _ in range(G)]
         cur = list(first_tokens) if self.first else [None] * G
         for i in range(steps):
@@ -326,6 +335,90 @@ class DistPipeline:
             for g in range(G):
                 gen[g].append(self._recv((len(rows_per_group[g]),), torch.int64, self.world - 1, tok=True))
         return gen if (self.first or self.last) else None
+
+    def _decode_stream_graphs(self, first_tokens, start_positions, rows_per_group, steps: int):
+        """decode_stream on GPUs with as little host work per pipeline tick as possible (at 8 stages
+        a tick is ~260 us of device time; the generic path spends ~250 us of Python on it).  Each
+        group owns a captured graph (`GraphRunner`); hidden states are received straight into the
+        graph's static input and sent straight from its static output, tokens are written into a
+        preallocated [steps, B] tensor; sends are ordered with per-group events."""
+        dev = self.device
+        cur = torch.cuda.current_stream(dev)
+        G = len(rows_per_group)
+        want = "last" if self.last else "none"
+        runners = []
+        for g in range(G):
+            r = self.stage.runner(self.cache, len(rows_per_group[g]), decode=True, rows=list(rows_per_group[g]), logits=want)
+            pos = np.asarray(start_positions[g], dtype=np.int64).reshape(-1)
+            if int(pos.max()) + steps > self.cache.max_seq:
+                raise ValueError("decode would run past the KV cache capacity")
+            if not np.array_equal(pos, r.host_pos):
+                r.set_positions(pos)
+            if self.first:
+                r.x.copy_(first_tokens[g].view(r.x.shape))
+            runners.append(r)
+        keep = self.first or self.last
+        gen = [torch.empty((steps, len(rows_per_group[g])), dtype=torch.int64, device=dev) for g in range(G)] if keep else None
+        multi = self.world > 1
+        if multi:
+            # the buffers used below were last touched by work queued on `cur` (earlier calls, the allocations above)
+            for side in (self._rs, self._ss, self._rs_tok, self._ss_tok):
+                side.wait_stream(cur)
+        ev_sent = [None] * G        # on the send stream: runner g's output has left (the next replay may overwrite it)
+        Event = torch.cuda.Event
+
+        def recv_into(buf, src, group, side, g, then_copy_to=None):
+            # Post the receive behind everything already queued on `cur`, not earlier: NCCL's receive
+            # kernel polls on an SM until the data arrives, and the fused decode kernels put one
+            # CTA on every SM -- a receive posted a whole tick ahead costs them a second wave
+            # (measured at 2 stages: 946 vs 1045 tok/s).
+            side.wait_stream(cur)
+            with torch.cuda.stream(side):
+                self.dist.irecv(buf, src=src, group=group).wait()
+                if then_copy_to is not None:
+                    then_copy_to.copy_(buf.view(then_copy_to.shape))
+                e = Event()
+                e.record(side)
+            cur.wait_event(e)
+
+        for i in range(steps):
+            for g in range(G):
+                r = runners[g]
+                if multi and self.first and i > 0:
+                    recv_into(gen[g][i - 1], self.world - 1, self.tok_group, self._rs_tok, g, then_copy_to=r.x)
+                elif multi and not self.first:
+                    recv_into(r.x, self.rank - 1, self.group_in, self._rs, g)
+                if ev_sent[g] is not None:
+                    cur.wait_event(ev_sent[g])
+                r.replay()
+                if self.last:
+                    ops.argmax(r.out, out=gen[g][i])
+                    self.stage.launches += 1
+                    if self.first:
+                        r.x.copy_(gen[g][i].view(r.x.shape))
+                if not multi:
+                    continue
+                ef = Event()
+                ef.record(cur)
+                if not self.last:
+                    with torch.cuda.stream(self._ss):
+                        self._ss.wait_event(ef)
+                        self.dist.isend(r.out, dst=self.rank + 1, group=self.group_out).wait()
+                        es = Event()
+                        es.record(self._ss)
+                    ev_sent[g] = es
+                else:
+                    with torch.cuda.stream(self._ss_tok):
+                        self._ss_tok.wait_event(ef)
+                        self.dist.isend(gen[g][i], dst=0, group=self.tok_group).wait()
+        if multi and self.first:
+            for g in range(G):
+                recv_into(gen[g][steps - 1], self.world - 1, self.tok_group, self._rs_tok, g)
+        if multi:
+            # side streams may still hold sends of this call: later work on `cur` (another call's buffers) follows them
+            cur.wait_stream(self._ss)
+            cur.wait_stream(self._ss_tok)
+        return [list(gen[g].unbind(0)) for g in range(G)] if keep else None
 
     def decode_round(self, tokens_per_group, positions_per_group, rows_per_group):
         """One decode step for each group (a decode_stream of a single step)."""

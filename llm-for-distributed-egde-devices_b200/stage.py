@@ -465,6 +465,18 @@ class GraphRunner:
         if self.dlens is not None:
             self.dlens.copy_(torch.from_numpy((pos + 1).astype(np.int32)))
 
+    def replay(self):
+        """Replay on the state the graph itself maintains (input already in `self.x`, positions
+        advanced by the previous replay): the per-tick path of DistPipeline's decode stream."""
+        self.graph.replay()
+        self.stage.launches += self.n_launch
+        lens = self.cache.lens
+        for r_, p_ in zip(self.rows, self.host_pos.tolist()):
+            if lens[r_] < p_ + 1:
+                lens[r_] = p_ + 1
+        self.host_pos = self.host_pos + self.stride
+        return self.out
+
     def __call__(self, x, positions=None):
         """Replay.  x: ids [T] int64 (first stage) or hidden [T,d] fp16, on the device, or None if
         the caller already wrote into `self.x`.  positions (host) only when they differ from the
