@@ -219,6 +219,10 @@ int b2_decode_attn_static(const void* q, long long q_ld, const void* kcache, con
  * (models_quant_updated.py:63-70). */
 int b2_prefill_attn(const void* q, long long q_ld, const void* kcache, const void* vcache, void* out, long long o_ld,
                     const int* positions, int T, int pos0, int row, int H, int KV, int hd, int Smax, float scale, int window, void* stream);
+/* Test hook (no reference counterpart): which kernel b2_prefill_attn uses from now on, process-wide.
+ * 0 = choose (the tcgen05/TMEM kernel for head_dim 128 without a window and T >= 64, else the
+ * mma.sync kernel), 1 = always the mma.sync kernel, 2 = the tcgen05 kernel or B2_ERR_UNSUPPORTED. */
+int b2_set_prefill_attn_impl(int impl);
 
 /* Token (+ learned position) embedding gather.  ids [T] int64; positions [T] int32 (only read
  * when pos_table != NULL); tables fp16 [vocab,d] / [max_pos,d]; out [T,d] fp16.

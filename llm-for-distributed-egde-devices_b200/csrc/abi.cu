@@ -23,6 +23,8 @@ int prefill_attn(const void*, long long, const void*, const void*, void*, long l
                  int, int, int, float, int, cudaStream_t);
 int init_gemm();
 int init_attn();
+int init_attn_tc();
+void set_prefill_attn_impl(int);
 int init_rowquant();
 int init_misc();
 int init_fused();
@@ -51,6 +53,7 @@ int b2_init(void) {
   int rc = b2::init_gemm();
   if (rc) return rc;
   if ((rc = b2::init_attn())) return rc;
+  if ((rc = b2::init_attn_tc())) return rc;
   if ((rc = b2::init_rowquant())) return rc;
   if ((rc = b2::init_misc())) return rc;
   if ((rc = b2::init_fused())) return rc;
@@ -157,6 +160,11 @@ int b2_prefill_attn(const void* q, long long q_ld, const void* kcache, const voi
                     const int* positions, int T, int pos0, int row, int H, int KV, int hd, int Smax, float scale,
                     int window, void* stream) {
   return b2::prefill_attn(q, q_ld, kcache, vcache, out, o_ld, positions, T, pos0, row, H, KV, hd, Smax, scale, window, ST(stream));
+}
+int b2_set_prefill_attn_impl(int impl) {
+  if (impl < 0 || impl > 2) return b2::ERR_UNSUPPORTED;
+  b2::set_prefill_attn_impl(impl);
+  return b2::OK;
 }
 int b2_embed(const long long* ids, const int* positions, const void* table, const void* pos_table, void* out, int T,
              int d, int vocab, void* stream) {

@@ -50,10 +50,25 @@ argmax_kernel(const float* __restrict__ logits, long long* __restrict__ out, int
   const float* row = logits + (long long)blockIdx.x * V;
   float best = -INFINITY;
   int bi = 0x7fffffff;
-  for (int i = threadIdx.x; i < V; i += blockDim.x) {
-    const float v = row[i];
-    if (v > best || (v == best && i < bi)) { best = v; bi = i; }
+  auto take = [&](float v, int i) { if (v > best || (v == best && i < bi)) { best = v; bi = i; } };
+  // 128-bit loads, four in flight per thread (the row is 128 KB: latency-, not bandwidth-bound)
+  const bool vec = ((reinterpret_cast<uintptr_t>(row) & 15) == 0);
+  const int V4 = vec ? (V >> 2) : 0;
+  const float4* row4 = reinterpret_cast<const float4*>(row);
+  for (int i0 = threadIdx.x; i0 < V4; i0 += 4 * blockDim.x) {
+    float4 q[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = i0 + u * blockDim.x;
+      q[u] = i < V4 ? __ldg(row4 + i) : make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = (i0 + u * blockDim.x) * 4;
+      take(q[u].x, i); take(q[u].y, i + 1); take(q[u].z, i + 2); take(q[u].w, i + 3);
+    }
   }
+  for (int i = V4 * 4 + threadIdx.x; i < V; i += blockDim.x) take(row[i], i);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     const float ov = __shfl_xor_sync(0xffffffffu, best, o);

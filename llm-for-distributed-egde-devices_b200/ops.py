@@ -229,6 +229,11 @@ def decode_attn_static(qkv, kcache, vcache, seqlens, H, KV, hd, max_seqlen, scal
     return o
 
 
+def set_prefill_attn_impl(impl: int):
+    """Test hook: 0 = choose, 1 = always the mma.sync kernel, 2 = the tcgen05 kernel or an error."""
+    check(_abi.lib().b2_set_prefill_attn_impl(int(impl)), "b2_set_prefill_attn_impl")
+
+
 def prefill_attn(qkv, kcache, vcache, pos0, row, H, KV, hd, scale, window=0, out=None, positions=None):
     """Causal attention for one chunk of one sequence.  b2_prefill_attn."""
     _cuda(qkv, kcache, vcache, out)
