@@ -6,15 +6,20 @@
 // (transformers modeling_llama.py:199-222) inside the prefill forward of `generate`
 // (reference call site Code/Quantised Models/models_quant_updated.py:84-93).
 //
-// One CTA = 128 query rows of one head, 6 warps:
+// One CTA = 128 query rows of one head, three warpgroups:
 //   warp 0      TMA producer: Q once, then K/V tiles of 128 keys through a 2-stage ring
-//   warp 1      MMA issuer (one thread) + TMEM owner:  S = Q K^T  (128x128x128, kind::f16, fp32 in TMEM,
-//               two S buffers so the next tile's QK^T runs under this tile's softmax), then
-//               PV = P V (P from shared memory, V as an MN-major B operand straight from the cache layout)
-//   warps 2-5   softmax: thread = query row = TMEM lane.  Two passes over S with tcgen05.ld (row max, then
+//   warp 1      MMA issuer (one thread) + TMEM owner:  S = Q K^T  (128x128x128, kind::f16, fp32 in TMEM)
+//               and PV = P V (P from shared memory, V as an MN-major B operand straight from the
+//               cache layout); S, P and PV are double-buffered
+//   warps 4-7   softmax group A: the EVEN key tiles;   warps 8-11  softmax group B: the ODD key tiles.
+//               Thread = query row = TMEM lane.  Two passes over S with tcgen05.ld (row max, then
 //               exp2 / row sum / fp16 P written in the 128B-swizzled K-major layout the MMA reads),
 //               then O = O*corr + PV with O kept in registers (128 fp32 per thread) -- no TMEM
-//               read-modify-write for the online-softmax rescale.
+//               read-modify-write for the online-softmax rescale.  The two groups keep separate
+//               (max, sum, O) states over their halves of the keys, so one group's exponentials
+//               run under the other group's PV product; the states are merged once at the end
+//               (as for split-KV decode).  384 threads x 168 registers: with 16-column TMEM reads the
+//               softmax threads fit without setmaxnreg (which made the TMA/MMA warps spill instead).
 // Numerics: fp32 scores and accumulation, P rounded to fp16 before the PV product, exp2f -- the
 // same as the mma.sync kernel; compared with the oracle within the attention tolerance.
 #include <cuda.h>
@@ -25,16 +30,16 @@ namespace b2 {
 constexpr int TC_BM = 128;        // query rows per CTA
 constexpr int TC_BN = 128;        // keys per tile
 constexpr int TC_HD = 128;
-constexpr int TC_THREADS = 192;
+constexpr int TC_THREADS = 384;
 constexpr int TC_ATOM = TC_BM * 128;                 // one [128 rows][128 B] swizzle-atom column: 16 KB
 constexpr int TC_TILE = 2 * TC_ATOM;                 // a 128 x 128 fp16 tile: 32 KB
 constexpr int TC_KV_STAGES = 2;
-// shared memory: Q | K[2] | V[2] | P | barriers
+// shared memory: Q | K[2] | V[2] | P[2] | barriers
 constexpr int TC_OFF_Q = 0;
 constexpr int TC_OFF_K = TC_OFF_Q + TC_TILE;
 constexpr int TC_OFF_V = TC_OFF_K + TC_KV_STAGES * TC_TILE;
 constexpr int TC_OFF_P = TC_OFF_V + TC_KV_STAGES * TC_TILE;
-constexpr int TC_OFF_BAR = TC_OFF_P + TC_TILE;
+constexpr int TC_OFF_BAR = TC_OFF_P + 2 * TC_TILE;
 constexpr int TC_SMEM = TC_OFF_BAR + 256 + 1024;     // + alignment slack
 
 struct TcAttnParams {
@@ -56,6 +61,12 @@ B2_DEVINL uint64_t umma_desc_sw128_mn(uint32_t smem_addr) {
   return d;
 }
 
+B2_DEVINL float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 __global__ void __launch_bounds__(TC_THREADS, 1)
 prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                        const __grid_constant__ CUtensorMap tmV, const TcAttnParams pin) {
@@ -69,10 +80,10 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
   uint64_t* v_empty = bars + 7;     // [2]
   uint64_t* s_full = bars + 9;      // [2]  MMA -> softmax
   uint64_t* s_empty = bars + 11;    // [2]  softmax -> MMA (4 warps)
-  uint64_t* p_full = bars + 13;     //      softmax -> MMA (4 warps)
-  uint64_t* pv_full = bars + 14;    //      MMA -> softmax
-  uint64_t* pv_empty = bars + 15;   //      softmax -> MMA (4 warps)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
+  uint64_t* p_full = bars + 13;     // [2]  softmax -> MMA (4 warps)
+  uint64_t* pv_full = bars + 15;    // [2]  MMA -> softmax
+  uint64_t* pv_empty = bars + 17;   // [2]  softmax -> MMA (4 warps)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 19);
 
   TcAttnParams p = pin;
   if (p.pos_ptr) p.pos0 = p.pos_ptr[0];
@@ -93,8 +104,8 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
       mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], 1);
       mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1);
       mbar_init(&s_full[i], 1); mbar_init(&s_empty[i], 4);
+      mbar_init(&p_full[i], 4); mbar_init(&pv_full[i], 1); mbar_init(&pv_empty[i], 4);
     }
-    mbar_init(p_full, 4); mbar_init(pv_full, 1); mbar_init(pv_empty, 4);
     mbar_fence_init();
   }
   if (warp == 1) tmem_alloc<512>(tmem_slot);
@@ -148,122 +159,148 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
       };
       mbar_wait(q_full, 0);
       issue_qk(0);
+      if (nt > 1) issue_qk(1);
       for (int j = 0; j < nt; ++j) {
-        if (j + 1 < nt) issue_qk(j + 1);
         const int s = j & 1;
         const uint32_t ph = (j >> 1) & 1;
-        mbar_wait(p_full, j & 1);
+        mbar_wait(&p_full[s], ph);
         mbar_wait(&v_full[s], ph);
-        mbar_wait(pv_empty, (j & 1) ^ 1);
+        mbar_wait(&pv_empty[s], ph ^ 1);
         tc_fence_after();
         const uint32_t sV = smem_u32(smem + TC_OFF_V + s * TC_TILE);
 #pragma unroll
         for (int k = 0; k < TC_BN / 16; ++k) {
           // A = P (K-major, K = keys): as above.  B = V (MN-major): a k-step is 16 key rows = 2048 B.
           const uint32_t aoff = (k >> 2) * TC_ATOM + (k & 3) * 32;
-          umma_f16(tmem_O, umma_desc_sw128(sP + aoff), umma_desc_sw128_mn(sV + k * 2048), idesc_pv, k != 0);
+          umma_f16(tmem_O + s * TC_HD, umma_desc_sw128(sP + s * TC_TILE + aoff), umma_desc_sw128_mn(sV + k * 2048), idesc_pv,
+                   k != 0);
         }
         umma_commit(&v_empty[s]);
-        umma_commit(pv_full);
+        umma_commit(&pv_full[s]);
+        if (j + 2 < nt) issue_qk(j + 2);       // S[s] was released before P[s] was announced
       }
     }
-  } else {
-    // ===================== softmax / accumulate / store =====================
+  } else if (warp >= 4) {
+    // ===================== softmax / accumulate / merge / store =====================
+    const int grp = (warp >> 2) - 1;                    // 0: even key tiles, 1: odd key tiles
     const int quad = warp & 3;                          // TMEM lane quadrant this warp may read
     const int r = quad * 32 + lane;                     // query row within the tile
     const int qpos = p.pos0 + q0 + r;
     const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
-    uint8_t* sP = smem + TC_OFF_P;
+    uint8_t* sP = smem + TC_OFF_P + grp * TC_TILE;
     const uint32_t prow = (uint32_t)(r >> 3) * 1024 + (uint32_t)(r & 7) * 128;
+    const uint32_t ts = tmem_S + lane_addr + grp * TC_BN;
+    const uint32_t to = tmem_O + lane_addr + grp * TC_HD;
     float o[TC_HD];
 #pragma unroll
     for (int i = 0; i < TC_HD; ++i) o[i] = 0.f;
     float m_run = -INFINITY, l_run = 0.f;
-    for (int j = 0; j < nt; ++j) {
-      const int s = j & 1;
-      const uint32_t ph = (j >> 1) & 1;
+    int it = 0;
+    for (int j = grp; j < nt; j += 2, ++it) {
+      const uint32_t ph = it & 1;
       const int key0 = j * TC_BN;
-      const bool need_mask = key0 + TC_BN - 1 > p.pos0 + q0;      // tile reaches past the first row's position
-      mbar_wait(&s_full[s], ph);
+      // keys beyond a row's own position are masked; only tiles that reach past the first row's position have any
+      const int lim = (key0 + TC_BN - 1 > p.pos0 + q0) ? qpos - key0 : TC_BN;     // this row keeps keys [0, lim] of the tile
+      mbar_wait(&s_full[grp], ph);
       tc_fence_after();
-      const uint32_t ts = tmem_S + lane_addr + s * TC_BN;
       // ---- pass 1: row maximum ----
       float mx = -INFINITY;
 #pragma unroll 1
-      for (int c = 0; c < TC_BN / 32; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32(ts + c * 32, v);
+      for (int c = 0; c < TC_BN / 16; ++c) {
+        uint32_t v[16];
+        tmem_ld_32x16(ts + c * 16, v);
         tmem_ld_wait();
+        if (c * 16 + 15 <= lim) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float x = __uint_as_float(v[i]);
-          if (need_mask && key0 + c * 32 + i > qpos) x = -INFINITY;
-          mx = fmaxf(mx, x);
+          for (int i = 0; i < 16; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
+        } else {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) mx = fmaxf(mx, (c * 16 + i <= lim) ? __uint_as_float(v[i]) : -INFINITY);
         }
       }
-      const float m_new = fmaxf(m_run, mx * p.scale_log2);        // key 0 is never masked: finite from tile 0 on
-      const float corr = exp2f(m_run - m_new);                    // m_run = -inf -> 0
+      // (a group's first tile may be fully masked for a row: odd tile 1 when pos0 + q0 < 128)
+      const float m_new = fmaxf(m_run, mx * p.scale_log2);
+      const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
+      const float corr = ex2_approx(m_run - m_use);               // m_run = -inf -> 0
       // ---- pass 2: P = exp2(s*scale - m), row sum, fp16 P into the swizzled A-operand layout ----
       float ls = 0.f;
 #pragma unroll 1
-      for (int c = 0; c < TC_BN / 32; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32(ts + c * 32, v);
+      for (int c = 0; c < TC_BN / 16; ++c) {
+        uint32_t v[16];
+        tmem_ld_32x16(ts + c * 16, v);
         tmem_ld_wait();
-        uint32_t pk[16];
+        uint32_t pk[8];
+        const bool full = c * 16 + 15 <= lim;
 #pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          float x0 = __uint_as_float(v[i]) * p.scale_log2 - m_new;
-          float x1 = __uint_as_float(v[i + 1]) * p.scale_log2 - m_new;
-          float e0 = exp2f(x0), e1 = exp2f(x1);
-          if (need_mask) {
-            if (key0 + c * 32 + i > qpos) e0 = 0.f;
-            if (key0 + c * 32 + i + 1 > qpos) e1 = 0.f;
+        for (int i = 0; i < 16; i += 2) {
+          float e0 = ex2_approx(fmaf(__uint_as_float(v[i]), p.scale_log2, -m_use));
+          float e1 = ex2_approx(fmaf(__uint_as_float(v[i + 1]), p.scale_log2, -m_use));
+          if (!full) {
+            if (c * 16 + i > lim) e0 = 0.f;
+            if (c * 16 + i + 1 > lim) e1 = 0.f;
           }
-          // the sum runs over the fp16-rounded probabilities the PV product will use
-          const __half2 hh = __floats2half2_rn(e0, e1);
-          const float2 back = __half22float2(hh);
-          ls += back.x + back.y;
-          pk[i >> 1] = *reinterpret_cast<const uint32_t*>(&hh);
+          // (row sum in fp32 of the unrounded values, as in the mma.sync kernel: converting the fp16 P back
+          //  costs one XU-pipe op per element, and XU -- ex2 + conversions -- is this kernel's busiest pipe)
+          ls += e0 + e1;
+          pk[i >> 1] = f2_to_h2(e0, e1);
         }
-        // keys c*32 .. c*32+31 = atom column c/2, 16-byte chunks (c%2)*4 .. +3 of this row
-        uint8_t* base = sP + (c >> 1) * TC_ATOM + prow;
+        // keys c*16 .. c*16+15 = atom column c/4, 16-byte chunks (c%4)*2, +1 of this row
+        uint8_t* base = sP + (c >> 2) * TC_ATOM + prow;
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const uint32_t chunk = (uint32_t)((c & 1) * 4 + q) ^ (uint32_t)(r & 7);
+        for (int q = 0; q < 2; ++q) {
+          const uint32_t chunk = (uint32_t)((c & 3) * 2 + q) ^ (uint32_t)(r & 7);
           *reinterpret_cast<uint4*>(base + chunk * 16) = make_uint4(pk[q * 4], pk[q * 4 + 1], pk[q * 4 + 2], pk[q * 4 + 3]);
         }
       }
-      // S[s] may be overwritten by the QK^T of tile j+2; P is complete
+      // S[grp] may be overwritten by the QK^T of tile j+2; P[grp] is complete
       tc_fence_before();
       fence_proxy_async();
       __syncwarp();
-      if (lane == 0) { mbar_arrive(&s_empty[s]); mbar_arrive(p_full); }
+      if (lane == 0) { mbar_arrive(&s_empty[grp]); mbar_arrive(&p_full[grp]); }
       l_run = l_run * corr + ls;
       m_run = m_new;
-      // ---- O = O*corr + P V ----
-      mbar_wait(pv_full, j & 1);
+      // ---- O = O*corr + P V  (the other group's softmax runs while this PV product is in flight) ----
+      mbar_wait(&pv_full[grp], ph);
       tc_fence_after();
 #pragma unroll
-      for (int c = 0; c < TC_HD / 32; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32(tmem_O + lane_addr + c * 32, v);
+      for (int c = 0; c < TC_HD / 16; ++c) {
+        uint32_t v[16];
+        tmem_ld_32x16(to + c * 16, v);
         tmem_ld_wait();
 #pragma unroll
-        for (int i = 0; i < 32; ++i) o[c * 32 + i] = fmaf(o[c * 32 + i], corr, __uint_as_float(v[i]));
+        for (int i = 0; i < 16; ++i) o[c * 16 + i] = fmaf(o[c * 16 + i], corr, __uint_as_float(v[i]));
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(pv_empty);
+      if (lane == 0) mbar_arrive(&pv_empty[grp]);
     }
-    if (q0 + r < p.T) {
-      const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
+    // ---- merge the two groups' states (B -> shared memory -> A), normalise, store ----
+    // Both groups have seen their last S tile, so every QK^T product has completed and the K ring is free.
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    float* sO = reinterpret_cast<float*>(smem + TC_OFF_K);       // [128 columns][128 rows]: conflict-free for thread = row
+    float* sML = reinterpret_cast<float*>(smem + TC_OFF_V);      // [2][128]
+    if (grp == 1) {
+#pragma unroll
+      for (int i = 0; i < TC_HD; ++i) sO[i * TC_BM + r] = o[i];
+      sML[r] = m_run;
+      sML[TC_BM + r] = l_run;
+    }
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    if (grp == 0 && q0 + r < p.T) {
+      const float mb = sML[r], lb = sML[TC_BM + r];
+      const float m = fmaxf(m_run, mb);                          // finite: tile 0 holds key 0 for every row
+      const float wa = ex2_approx(m_run - m), wb = ex2_approx(mb - m);
+      const float l = l_run * wa + lb * wb;
+      const float inv = l > 0.f ? 1.f / l : 0.f;
+      const float ca = wa * inv, cb = wb * inv;
       __half* op = p.out + (long long)(q0 + r) * p.o_ld + h * TC_HD;
 #pragma unroll
       for (int i = 0; i < TC_HD; i += 8) {
+        float y[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) y[e] = fmaf(o[i + e], ca, sO[(i + e) * TC_BM + r] * cb);
         uint4 u;
-        u.x = f2_to_h2(o[i] * inv, o[i + 1] * inv); u.y = f2_to_h2(o[i + 2] * inv, o[i + 3] * inv);
-        u.z = f2_to_h2(o[i + 4] * inv, o[i + 5] * inv); u.w = f2_to_h2(o[i + 6] * inv, o[i + 7] * inv);
+        u.x = f2_to_h2(y[0], y[1]); u.y = f2_to_h2(y[2], y[3]); u.z = f2_to_h2(y[4], y[5]); u.w = f2_to_h2(y[6], y[7]);
         st_v4(op + i, u);
       }
     }

@@ -1,5 +1,5 @@
 """Small fixed workload for `ncu`: a few launches of the dominant kernels at Llama-2-7B shapes.
-usage: python tools/ncu_target.py [gemm|gemv|attn|all]"""
+usage: python tools/ncu_target.py [gemm|gemv|attn|pattn|all]"""
 import os
 import sys
 
@@ -26,7 +26,7 @@ if what in ("gemv", "all"):
         ops.fused_linear(h, lw["wgu"], lw["s_gu"], x_kind=ops.X_RMS, gamma=lw["ln2_g"], smooth=lw["sm_gu"], out=y32,
                          out_kind=ops.O_GATED, out_smooth=lw["sm_d"], out_amax=amax)
 if what in ("gemm", "all"):
-    T = 512
+    T = 2048
     x8 = torch.randint(-127, 128, (T, d), dtype=torch.int8, device=dev)
     st = torch.full((T,), 0.01, device=dev)
     out = torch.empty((T, 2 * F), dtype=torch.float16, device=dev)
@@ -42,12 +42,13 @@ if what in ("attn", "all"):
     attn = torch.empty((1, H * hd), dtype=torch.float16, device=dev)
     for i in range(NL):
         ops.decode_attn(qkv, kc[i], vc[i], lens, H, KV, hd, S, hd ** -0.5, 0, out=attn)
-    T = 512
+if what in ("pattn", "all"):
+    T = 2048                                   # the whole bench prompt as one chunk (N = 1 bench)
     qkvT = torch.randn((T, cfg.qkv_out), dtype=torch.float16, device=dev)
     outT = torch.empty((T, H * hd), dtype=torch.float16, device=dev)
-    kcp = torch.randn((NL, 1, KV, 2048 + T, hd), dtype=torch.float16, device=dev)
+    kcp = torch.randn((2, 1, KV, T + 8, hd), dtype=torch.float16, device=dev)
     vcp = torch.randn_like(kcp)
-    for i in range(NL):
-        ops.prefill_attn(qkvT, kcp[i], vcp[i], 1536, 0, H, KV, hd, hd ** -0.5, 0, out=outT)
+    for i in range(2):
+        ops.prefill_attn(qkvT, kcp[i], vcp[i], 0, 0, H, KV, hd, hd ** -0.5, 0, out=outT)
 torch.cuda.synchronize()
 print("done")
