@@ -168,7 +168,7 @@ class DistPipeline:
     moves from the last rank back to rank 0.  All ranks make the same sequence of calls.
 
     `forward_fn(x, positions, seq_ids, logits)` abstracts the local stage so the scheduling and
-    messaging logic can be exercised on CPU with a stand-in stage (tests/test_pipeline_cpu.py).
+    messaging logic can be exercised on CPU with a stand-in stage (tests/test_host_cpu.py).
     """
 
     def __init__(self, rank: int, world: int, d_model: int, device, forward_fn, vocab: int, group=None):
