@@ -79,8 +79,12 @@ int b2_act_mul_quant(const void* gate_up, const float* smooth, int8_t* q, float*
  * or torch.ao dynamic qint8 Linear (try.py:205). */
 int b2_gemm_w8a8(const int8_t* A, const int8_t* W, const float* a_scale, const float* w_scale, const void* bias,
                  const void* residual, void* out, int32_t* acc_dump, int M, int N, int K, void* stream);
-/* Same, with the schedule forced: 1 = tcgen05 tensor-core path, 2 = dp4a streaming path (M <= 8).
- * Test hook so both schedules are checked on the same inputs. */
+/* Same, with the schedule forced: 0 = choose (what b2_gemm_w8a8 does), 1 = tcgen05 tensor-core path with
+ * the tile heuristic, 2 = dp4a streaming path (M <= 8).  Test hook so both schedules are checked
+ * on the same inputs.  10..16 pin the tcgen05 tile / cluster shape (N % 256 == 0 required):
+ * 10/11/12 = 128x256 tile, 4 stages, cluster of 1/2/4 CTAs multicasting the weight tile;
+ * 14/16/13 = 128x128 tile, 6 stages, cluster of 1/2/4; 15 = 128x64 tile, 8 stages.
+ * Other values: B2_ERR_UNSUPPORTED. */
 int b2_gemm_w8a8_sched(const int8_t* A, const int8_t* W, const float* a_scale, const float* w_scale,
                        const void* bias, const void* residual, void* out, int32_t* acc_dump, int M, int N, int K,
                        int schedule, void* stream);
