@@ -31,6 +31,9 @@ class ModelConfig:
     rope: bool = True          # False -> learned absolute positions (GPT-2)
     bias: bool = False         # linear layers carry a bias (GPT-2)
     tie_embeddings: bool = True
+    # HF `rope_scaling` of type "llama3" (Llama-3.1/3.2): ("llama3", factor, low_freq_factor,
+    # high_freq_factor, original_max_position_embeddings); () = plain RoPE
+    rope_scaling: tuple = ()
 
     @property
     def qkv_out(self) -> int:
@@ -47,7 +50,8 @@ class ModelConfig:
     def kernel_cfg(self) -> dict:
         """The plain-dict view the oracle consumes."""
         return dict(n_heads=self.n_heads, n_kv_heads=self.n_kv_heads, head_dim=self.head_dim, eps=self.eps,
-                    rope_theta=self.rope_theta, window=self.window, act=self.act, gated=self.gated, rope=self.rope)
+                    rope_theta=self.rope_theta, window=self.window, act=self.act, gated=self.gated, rope=self.rope,
+                    rope_scaling=self.rope_scaling)
 
     def to_dict(self) -> dict:
         return asdict(self)
@@ -59,11 +63,16 @@ PRESETS = {
     "tinyllama-1.1b": ModelConfig("tinyllama-1.1b", 22, 2048, 32, 4, 64, 5632, 32000, max_pos=2048),
     "llama-2-7b": ModelConfig("llama-2-7b", 32, 4096, 32, 32, 128, 11008, 32000, max_pos=4096),
     "llama-2-13b": ModelConfig("llama-2-13b", 40, 5120, 40, 40, 128, 13824, 32000, max_pos=4096),
+    # the refiner of the reference's three-model pipeline (combiner_quant_updated.py:177-203; try.py:303)
+    "llama-3.2-1b": ModelConfig("llama-3.2-1b", 16, 2048, 32, 8, 64, 8192, 128256, rope_theta=500000.0, max_pos=8192,
+                                rope_scaling=("llama3", 32.0, 1.0, 4.0, 8192)),
     "mistral-7b": ModelConfig("mistral-7b", 32, 4096, 32, 8, 128, 14336, 32000, window=4096, max_pos=32768),
     # small shapes for tests (same structure, seconds on the CPU oracle)
     "tiny-llama-test": ModelConfig("tiny-llama-test", 4, 256, 4, 4, 64, 512, 512, max_pos=512),
     "tiny-gqa-test": ModelConfig("tiny-gqa-test", 4, 512, 8, 2, 64, 1024, 1024, window=0, max_pos=512),
     "tiny-window-test": ModelConfig("tiny-window-test", 2, 256, 4, 2, 64, 512, 512, window=48, max_pos=512),
+    "tiny-llama3-test": ModelConfig("tiny-llama3-test", 3, 256, 4, 2, 64, 512, 640, rope_theta=500000.0, max_pos=512,
+                                    rope_scaling=("llama3", 8.0, 1.0, 4.0, 64)),
     "tiny-hd128-test": ModelConfig("tiny-hd128-test", 2, 512, 4, 4, 128, 1024, 512, max_pos=512),
     "tiny-gpt2-test": ModelConfig("tiny-gpt2-test", 3, 256, 4, 4, 64, 1024, 512, eps=1e-5, max_pos=256, act="gelu_new",
                                   gated=False, norm="layernorm", rope=False, bias=True),
@@ -95,8 +104,14 @@ def from_hf_dict(c: dict) -> ModelConfig:
                            c["vocab_size"], eps=c.get("layer_norm_epsilon", 1e-5), max_pos=c.get("n_positions", 1024),
                            act="gelu_new", gated=False, norm="layernorm", rope=False, bias=True)
     d, h = c["hidden_size"], c["num_attention_heads"]
+    rs = c.get("rope_scaling") or {}
+    kind = rs.get("rope_type", rs.get("type"))
+    if kind not in (None, "default", "llama3"):
+        raise ValueError(f"rope_scaling type {kind!r} is not supported")
+    scaling = ("llama3", float(rs["factor"]), float(rs["low_freq_factor"]), float(rs["high_freq_factor"]),
+               int(rs["original_max_position_embeddings"])) if kind == "llama3" else ()
     return ModelConfig(c.get("_name_or_path", c.get("model_type", "llama")), c["num_hidden_layers"], d, h,
                        c.get("num_key_value_heads", h), c.get("head_dim") or d // h, c["intermediate_size"],
                        c["vocab_size"], eps=c.get("rms_norm_eps", 1e-5), rope_theta=c.get("rope_theta", 10000.0),
                        window=c.get("sliding_window") or 0, max_pos=c.get("max_position_embeddings", 4096),
-                       tie_embeddings=c.get("tie_word_embeddings", False))
+                       tie_embeddings=c.get("tie_word_embeddings", False), rope_scaling=scaling)

@@ -106,7 +106,7 @@ class Stage:
         self.first, self.last = bool(sw["first"]), bool(sw["last"])
         self.layer_begin, self.layer_end = layer_begin, layer_end
         self.device = torch.device(device)
-        cos, sin = weights.rope_table(cfg.head_dim, cfg.max_pos, cfg.rope_theta)
+        cos, sin = weights.rope_table(cfg.head_dim, cfg.max_pos, cfg.rope_theta, cfg.rope_scaling)
         self.cos, self.sin = cos.to(self.device), sin.to(self.device)
         self.scale = 1.0 / float(np.sqrt(cfg.head_dim))
         self._scratch = None
@@ -120,7 +120,7 @@ class Stage:
         self.pf_plan = _parse_pf_plan(os.environ.get("B2_PF_PLAN", DEFAULT_PF_PLAN))
         # o_proj -> gate_up -> down -> next qkv as one persistent launch with grid barriers: exact, but measured
         # SLOWER than four PDL-chained launches on B200 (38.0 vs 33.8 us per layer tail), so off by default
-        self.fuse_tail = False
+        self.fuse_tail = os.environ.get("B2_FUSE_TAIL", "0") == "1"
 
     # ------------------------------------------------------------------------------------------
     @classmethod

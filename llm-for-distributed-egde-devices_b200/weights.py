@@ -188,11 +188,25 @@ def to_numpy(sw: dict) -> dict:
     return out
 
 
-def rope_table(head_dim: int, max_pos: int, theta: float = 10000.0):
+def rope_table(head_dim: int, max_pos: int, theta: float = 10000.0, scaling: tuple = ()):
     """cos/sin fp32 [max_pos, head_dim/2]: angle formed in fp32 as HF does
     (modeling_llama.py:100-126), cos/sin evaluated in fp64 and rounded once.  Host-side table; the
-    kernels only read it, so device and oracle use bit-identical values."""
+    kernels only read it, so device and oracle use bit-identical values.
+    scaling = ("llama3", factor, low_freq_factor, high_freq_factor, original_max_pos): the frequency
+    remap of Llama-3.1/3.2 (transformers modeling_rope_utils.py `_compute_llama3_parameters`), in fp32 like HF."""
     i = np.arange(0, head_dim, 2, dtype=np.float64)
-    inv_freq = (1.0 / (theta ** (i / head_dim))).astype(np.float32).astype(np.float64)
+    inv_freq = (1.0 / (theta ** (i / head_dim))).astype(np.float32)
+    if scaling:
+        kind, factor, low_f, high_f, old_ctx = scaling
+        if kind != "llama3":
+            raise ValueError(f"rope scaling {kind!r} is not supported")
+        f32 = np.float32
+        wavelen = (f32(2.0 * np.pi) / inv_freq).astype(f32)
+        low_wl, high_wl = f32(old_ctx / low_f), f32(old_ctx / high_f)
+        scaled = np.where(wavelen > low_wl, inv_freq / f32(factor), inv_freq).astype(f32)
+        smooth = ((f32(old_ctx) / wavelen - f32(low_f)) / f32(high_f - low_f)).astype(f32)
+        mid = ((f32(1.0) - smooth) * scaled / f32(factor) + smooth * scaled).astype(f32)
+        inv_freq = np.where((wavelen >= high_wl) & (wavelen <= low_wl), mid, scaled).astype(f32)
+    inv_freq = inv_freq.astype(np.float64)
     ang = (np.arange(max_pos, dtype=np.float64)[:, None] * inv_freq[None, :]).astype(np.float32).astype(np.float64)
     return torch.from_numpy(np.cos(ang).astype(np.float32)), torch.from_numpy(np.sin(ang).astype(np.float32))

@@ -233,12 +233,32 @@ def gemm_w8a8(q, wq, a_scale, w_scale, bias16=None, residual16=None):
 # ----------------------------------------------------------------------------------------
 # rotary embedding, KV cache append, attention
 # ----------------------------------------------------------------------------------------
-def rope_table(head_dim: int, max_pos: int, theta: float = 10000.0):
+def llama3_inv_freq(inv_freq: np.ndarray, factor, low_freq_factor, high_freq_factor, old_ctx) -> np.ndarray:
+    """The "llama3" rope_scaling remap of Llama-3.1/3.2 (transformers modeling_rope_utils.py,
+    `_compute_llama3_parameters`), fp32 like HF: wavelengths longer than old_ctx/low_freq_factor are
+    stretched by `factor`, shorter than old_ctx/high_freq_factor kept, the band between blended."""
+    inv = np.asarray(inv_freq, f32)
+    wavelen = (f32(2.0 * np.pi) / inv).astype(f32)
+    low_wl = f32(old_ctx / low_freq_factor)
+    high_wl = f32(old_ctx / high_freq_factor)
+    out = np.where(wavelen > low_wl, inv / f32(factor), inv).astype(f32)
+    smooth = ((f32(old_ctx) / wavelen - f32(low_freq_factor)) / f32(high_freq_factor - low_freq_factor)).astype(f32)
+    blended = ((f32(1.0) - smooth) * out / f32(factor) + smooth * out).astype(f32)
+    medium = ~(wavelen < high_wl) & ~(wavelen > low_wl)
+    return np.where(medium, blended, out).astype(f32)
+
+
+def rope_table(head_dim: int, max_pos: int, theta: float = 10000.0, scaling=()):
     """cos/sin tables fp32 [max_pos, head_dim/2] (modeling_llama.py:100-153: inv_freq =
-    theta^(-2i/hd), angle = pos*inv_freq).  Computed in fp64, rounded once; the GPU reads
-    this exact table, so no device-side sincos is involved."""
+    theta^(-2i/hd), angle = pos*inv_freq; optional ("llama3", factor, low, high, old_ctx) remap).
+    Computed in fp64, rounded once; the GPU reads this exact table, so no device-side sincos is
+    involved."""
     i = np.arange(0, head_dim, 2, dtype=np.float64)
-    inv_freq = (1.0 / (theta ** (i / head_dim))).astype(f32).astype(np.float64)
+    inv_freq = (1.0 / (theta ** (i / head_dim))).astype(f32)
+    if scaling:
+        assert scaling[0] == "llama3", scaling
+        inv_freq = llama3_inv_freq(inv_freq, *scaling[1:])
+    inv_freq = inv_freq.astype(np.float64)
     ang = np.arange(max_pos, dtype=np.float64)[:, None] * inv_freq[None, :]
     ang = ang.astype(f32).astype(np.float64)   # HF forms the angle in fp32
     return np.cos(ang).astype(f32), np.sin(ang).astype(f32)
@@ -382,7 +402,7 @@ def greedy_generate(stages, cfg, ids, max_new_tokens, max_seq, chunk=None):
     """Greedy decode through a list of stage-weight dicts (prefill, then one token a step).
     Returns (tokens [len(ids)+max_new_tokens], top-1 margins per generated token)."""
     hd = cfg["head_dim"]
-    cos, sin = rope_table(hd, max_seq, cfg.get("rope_theta", 10000.0))
+    cos, sin = rope_table(hd, max_seq, cfg.get("rope_theta", 10000.0), cfg.get("rope_scaling", ()))
     caches = [KVCacheOracle(len(s["layers"]), 1, cfg["n_kv_heads"], max_seq, hd) for s in stages]
     toks = list(int(t) for t in ids)
     margins = []

@@ -34,7 +34,7 @@ import b200stage  # noqa: E402
 from b200stage import weights  # noqa: E402
 from oracle import w8a8 as O  # noqa: E402
 
-CASES = [("tiny-llama-test", 3, 24, 8), ("tiny-gqa-test", 5, 20, 8)]
+CASES = [("tiny-llama-test", 3, 24, 8), ("tiny-gqa-test", 5, 20, 8), ("tiny-llama3-test", 7, 200, 8)]
 
 
 def hf_model(cfg, seed):
@@ -43,7 +43,10 @@ def hf_model(cfg, seed):
                      num_hidden_layers=cfg.n_layers, num_attention_heads=cfg.n_heads,
                      num_key_value_heads=cfg.n_kv_heads, head_dim=cfg.head_dim, max_position_embeddings=cfg.max_pos,
                      rms_norm_eps=cfg.eps, rope_theta=cfg.rope_theta, tie_word_embeddings=False,
-                     attention_bias=False, mlp_bias=False)
+                     attention_bias=False, mlp_bias=False,
+                     rope_scaling=dict(rope_type="llama3", factor=cfg.rope_scaling[1], low_freq_factor=cfg.rope_scaling[2],
+                                       high_freq_factor=cfg.rope_scaling[3],
+                                       original_max_position_embeddings=cfg.rope_scaling[4]) if cfg.rope_scaling else None)
     m = LlamaForCausalLM(hc).eval().float()
     sd = {}
     H, KV, hd, F = cfg.n_heads, cfg.n_kv_heads, cfg.head_dim, cfg.ffn
@@ -105,7 +108,10 @@ def hf_gpt2(cfg, seed):
 def main():
     warnings.filterwarnings("ignore")
     torch.set_num_threads(4)
+    only = sys.argv[1:]                       # optional: regenerate just the named cases
     for name, seed, T, new in CASES + [("tiny-gpt2-test", 9, 20, 8)]:
+        if only and name not in only:
+            continue
         cfg = b200stage.get_config(name)
         ids = np.random.default_rng(seed + 100).integers(0, cfg.vocab, T)
         m = hf_gpt2(cfg, seed) if not cfg.rope else hf_model(cfg, seed)
@@ -117,7 +123,7 @@ def main():
             mq = torch.quantization.quantize_dynamic(m, {torch.nn.Linear}, dtype=torch.qint8)
             hf_dyn_logits = mq(tid).logits[0].numpy()
         sw = weights.to_numpy(weights.build_stage_weights(cfg, 0, cfg.n_layers, True, True, seed, "cpu"))
-        cos, sin = O.rope_table(cfg.head_dim, cfg.max_pos, cfg.rope_theta)
+        cos, sin = O.rope_table(cfg.head_dim, cfg.max_pos, cfg.rope_theta, cfg.rope_scaling)
         cache = O.KVCacheOracle(cfg.n_layers, 1, cfg.n_kv_heads, T + new, cfg.head_dim)
         s_logits = O.stage_forward(ids, sw, cfg.kernel_cfg(), cache, np.zeros(T, np.int64), np.arange(T), cos, sin)
         s_greedy, margins = O.greedy_generate([sw], cfg.kernel_cfg(), ids, new, T + new)

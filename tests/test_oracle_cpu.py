@@ -86,6 +86,29 @@ def test_rope_preserves_norm_and_identity_at_zero():
     assert np.array_equal(c2.numpy(), cos) and np.array_equal(s2.numpy(), sin)
 
 
+def test_llama3_rope_scaling_matches_hf_and_host_table():
+    """The "llama3" frequency remap (Llama-3.2-1B is the refiner of the reference's pipeline,
+    combiner_quant_updated.py:177-203): oracle == transformers' own `_compute_llama3_parameters`,
+    and the host table the kernels read == the oracle's, bit for bit."""
+    from transformers import LlamaConfig
+    from transformers.modeling_rope_utils import ROPE_INIT_FUNCTIONS
+    for hd, theta, sc in [(64, 500000.0, ("llama3", 32.0, 1.0, 4.0, 8192)), (64, 500000.0, ("llama3", 8.0, 1.0, 4.0, 64)),
+                          (128, 10000.0, ("llama3", 8.0, 1.0, 4.0, 512))]:
+        hc = LlamaConfig(hidden_size=hd * 4, num_attention_heads=4, head_dim=hd, rope_theta=theta,
+                         max_position_embeddings=16384,
+                         rope_scaling=dict(rope_type="llama3", factor=sc[1], low_freq_factor=sc[2], high_freq_factor=sc[3],
+                                           original_max_position_embeddings=sc[4]))
+        hf_inv, att = ROPE_INIT_FUNCTIONS["llama3"](hc, "cpu")
+        base = (1.0 / (theta ** (np.arange(0, hd, 2, dtype=np.float64) / hd))).astype(np.float32)
+        mine = O.llama3_inv_freq(base, *sc[1:])
+        assert att == 1.0
+        assert np.allclose(mine, hf_inv.numpy(), rtol=2e-6, atol=0)
+        assert not np.allclose(mine, base)                      # the remap does something at these sizes
+        cos, sin = O.rope_table(hd, 300, theta, sc)
+        c2, s2 = weights.rope_table(hd, 300, theta, sc)
+        assert np.array_equal(c2.numpy(), cos) and np.array_equal(s2.numpy(), sin)
+
+
 def test_attention_causal_window_and_gqa():
     r = np.random.default_rng(3)
     S, H, KV, hd = 12, 4, 2, 16
@@ -118,14 +141,14 @@ def test_weight_quantiser_matches_oracle_statement():
 
 
 # ---- golden vectors --------------------------------------------------------------------------
-@pytest.mark.parametrize("name", ["tiny-llama-test", "tiny-gqa-test", "tiny-gpt2-test"])
+@pytest.mark.parametrize("name", ["tiny-llama-test", "tiny-gqa-test", "tiny-gpt2-test", "tiny-llama3-test"])
 def test_oracle_against_golden(name):
     g = np.load(os.path.join(GOLD, f"{name}.npz"))
     cfg = b200stage.get_config(name)
     seed, new, ids = int(g["seed"]), int(g["new"]), g["ids"]
     T = len(ids)
     sw = weights.to_numpy(weights.build_stage_weights(cfg, 0, cfg.n_layers, True, True, seed, "cpu"))
-    cos, sin = O.rope_table(cfg.head_dim, cfg.max_pos, cfg.rope_theta)
+    cos, sin = O.rope_table(cfg.head_dim, cfg.max_pos, cfg.rope_theta, cfg.rope_scaling)
     cache = O.KVCacheOracle(cfg.n_layers, 1, cfg.n_kv_heads, T + new, cfg.head_dim)
     logits = O.stage_forward(ids, sw, cfg.kernel_cfg(), cache, np.zeros(T, np.int64), np.arange(T), cos, sin)
     # regression anchor: the oracle reproduces its own committed output (BLAS order may differ

@@ -38,14 +38,15 @@ def _close(got, ref, name):
     assert cos >= 0.9995, (name, cos)
 
 
-@pytest.mark.parametrize("model", ["tiny-llama-test", "tiny-gqa-test", "tiny-window-test", "tiny-hd128-test", "tiny-gpt2-test"])
+@pytest.mark.parametrize("model", ["tiny-llama-test", "tiny-gqa-test", "tiny-window-test", "tiny-hd128-test", "tiny-gpt2-test",
+                                   "tiny-llama3-test"])
 def test_stage_prefill_then_decode_matches_oracle(model):
     cfg = b200stage.get_config(model)
     seed, T, S = 3, 70, 96
     stage = Stage.load(cfg, 0, cfg.n_layers, first=True, last=True, device=DEV, seed=seed)
     osw = _oracle_stages(cfg, 1, seed)[0]
     ids = np.random.default_rng(5).integers(0, cfg.vocab, T)
-    cos, sin = O.rope_table(cfg.head_dim, cfg.max_pos, cfg.rope_theta)
+    cos, sin = O.rope_table(cfg.head_dim, cfg.max_pos, cfg.rope_theta, cfg.rope_scaling)
     ocache = O.KVCacheOracle(cfg.n_layers, 1, cfg.n_kv_heads, S, cfg.head_dim)
     otrace = []
     ref = O.stage_forward(ids, osw, cfg.kernel_cfg(), ocache, np.zeros(T, np.int64), np.arange(T), cos, sin, otrace)
