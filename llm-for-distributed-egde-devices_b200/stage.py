@@ -120,7 +120,8 @@ class Stage:
         self.pf_plan = _parse_pf_plan(os.environ.get("B2_PF_PLAN", DEFAULT_PF_PLAN))
         # o_proj -> gate_up -> down -> next qkv as one persistent launch with grid barriers: exact, but measured
         # SLOWER than four PDL-chained launches on B200 (38.0 vs 33.8 us per layer tail), so off by default
-        self.fuse_tail = os.environ.get("B2_FUSE_TAIL", "0") == "1"
+        # (also slower on the small models: TinyLlama 1271 vs 1584 tok/s, Llama-3.2-1B 1506 vs 1857)
+        self.fuse_tail = False
 
     # ------------------------------------------------------------------------------------------
     @classmethod
