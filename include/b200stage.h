@@ -223,6 +223,26 @@ int b2_decode_attn_static(const void* q, long long q_ld, const void* kcache, con
  * (models_quant_updated.py:63-70). */
 int b2_prefill_attn(const void* q, long long q_ld, const void* kcache, const void* vcache, void* out, long long o_ld,
                     const int* positions, int T, int pos0, int row, int H, int KV, int hd, int Smax, float scale, int window, void* stream);
+/* ---- LLM.int8() mixed decomposition -------------------------------------
+ * What `BitsAndBytesConfig(load_in_8bit=True)` (models_quant_updated.py:30-32, combiner_quant_updated.py:37;
+ * bitsandbytes Linear8bitLt, threshold 6.0) makes of one nn.Linear, as three calls around b2_gemm_w8a8:
+ *   b2_outlier_scan(y)                    which activation columns hold a value of magnitude >= threshold
+ *   b2_smooth_quant(y, smooth = mask)     per-row absmax int8 of the other columns
+ *   b2_gemm_w8a8(...)                     int8 product, dequantised (+ bias) to fp16
+ *   b2_outlier_side(out, y, W, ...)       out += fp16(y[:,cols] . fp16(W[:,cols]*w_scale)^T); out += residual
+ * Arithmetic pinned by oracle/w8a8.py llm_int8_linear. */
+
+/* act(gate)*up (act 0/1) or act(x) (act 2/3) as fp16 [T,F], not quantised (same act codes as b2_act_mul_quant). */
+int b2_act_mul(const void* gate_up, void* y, int T, int F, int act, void* stream);
+/* y [T,K] fp16 (row pitch ld): mask [K] fp32 = 0 for columns with any |y| >= threshold else 1; cols [K] int32 =
+ * the outlier columns in ascending order; count [1] int32; flags = K/8 words of scratch.  All device memory. */
+int b2_outlier_scan(const void* y, long long ld, int T, int K, float threshold, float* mask, int* cols, int* count,
+                    unsigned* flags, void* stream);
+/* out [T,N] fp16 in place: + the fp16 side product over the `count` columns in `cols` (skipped when 0), then
+ * + residual [T,N] fp16 (or NULL).  W [N,K] int8 with row scales w_scale [N]. */
+int b2_outlier_side(void* out, const void* y, long long ld, const int8_t* W, const float* w_scale, const int* cols,
+                    const int* count, const void* residual, int T, int N, int K, void* stream);
+
 /* Test hook (no reference counterpart): which kernel b2_prefill_attn uses from now on, process-wide.
  * 0 = choose (the tcgen05/TMEM kernel for head_dim 128 without a window and T >= 64, else the
  * mma.sync kernel), 1 = always the mma.sync kernel, 2 = the tcgen05 kernel or B2_ERR_UNSUPPORTED. */

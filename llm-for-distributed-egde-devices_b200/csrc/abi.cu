@@ -22,6 +22,11 @@ size_t decode_attn_workspace_bytes(int, int, int, int);
 int prefill_attn(const void*, long long, const void*, const void*, void*, long long, const int*, int, int, int, int,
                  int, int, int, float, int, cudaStream_t);
 int init_gemm();
+int act_mul_f16(const void*, void*, int, int, int, cudaStream_t);
+int outlier_scan(const void*, long long, int, int, float, float*, int*, int*, unsigned*, cudaStream_t);
+int outlier_side(void*, const void*, long long, const int8_t*, const float*, const int*, const int*, const void*, int, int,
+                 int, cudaStream_t);
+int init_outlier();
 int init_attn();
 int init_attn_tc();
 void set_prefill_attn_impl(int);
@@ -54,6 +59,7 @@ int b2_init(void) {
   if (rc) return rc;
   if ((rc = b2::init_attn())) return rc;
   if ((rc = b2::init_attn_tc())) return rc;
+  if ((rc = b2::init_outlier())) return rc;
   if ((rc = b2::init_rowquant())) return rc;
   if ((rc = b2::init_misc())) return rc;
   if ((rc = b2::init_fused())) return rc;
@@ -160,6 +166,17 @@ int b2_prefill_attn(const void* q, long long q_ld, const void* kcache, const voi
                     const int* positions, int T, int pos0, int row, int H, int KV, int hd, int Smax, float scale,
                     int window, void* stream) {
   return b2::prefill_attn(q, q_ld, kcache, vcache, out, o_ld, positions, T, pos0, row, H, KV, hd, Smax, scale, window, ST(stream));
+}
+int b2_act_mul(const void* gate_up, void* y, int T, int F, int act, void* stream) {
+  return b2::act_mul_f16(gate_up, y, T, F, act, ST(stream));
+}
+int b2_outlier_scan(const void* y, long long ld, int T, int K, float threshold, float* mask, int* cols, int* count,
+                    unsigned* flags, void* stream) {
+  return b2::outlier_scan(y, ld, T, K, threshold, mask, cols, count, flags, ST(stream));
+}
+int b2_outlier_side(void* out, const void* y, long long ld, const int8_t* W, const float* w_scale, const int* cols,
+                    const int* count, const void* residual, int T, int N, int K, void* stream) {
+  return b2::outlier_side(out, y, ld, W, w_scale, cols, count, residual, T, N, K, ST(stream));
 }
 int b2_set_prefill_attn_impl(int impl) {
   if (impl < 0 || impl > 2) return b2::ERR_UNSUPPORTED;

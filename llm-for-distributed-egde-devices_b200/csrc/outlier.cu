@@ -1,0 +1,129 @@
+// LLM.int8() mixed decomposition around the W8A8 GEMM.
+//
+// What the reference's `BitsAndBytesConfig(load_in_8bit=True)` (Code/Quantised Models/
+// models_quant_updated.py:30-32, combiner_quant_updated.py:37) makes every nn.Linear do
+// (bitsandbytes Linear8bitLt / MatMul8bitLt, threshold 6.0): activation COLUMNS that hold any value
+// of magnitude >= threshold are taken out of the int8 product and multiplied in fp16 against the
+// dequantised weight columns; the remaining columns are quantised per row (absmax) and go through the
+// int8 GEMM.  bitsandbytes is not installable here (no CUDA wheel offline), so the arithmetic is
+// pinned by oracle/w8a8.py llm_int8_linear ("parity unpinned").
+//
+//   b2_outlier_scan : y fp16 [T,K] -> mask fp32 [K] (0 for outlier columns, 1 otherwise: it is passed
+//                     as the `smooth` vector of b2_smooth_quant, which then quantises exactly the
+//                     sub-matrix), the ascending list of outlier columns and their count (device)
+//   b2_outlier_side : out += fp16( y[:,cols] . dequant(W[:,cols])^T ), then out += residual
+// Everything is device-resident (the count is read by the kernels), so the chain can be captured in
+// a CUDA graph.
+#include "common.cuh"
+
+namespace b2 {
+
+constexpr int OS_ROWS = 64;          // rows per CTA in the flag pass
+
+// flags[k/8] bit (k%8) |= any |y[t,k]| >= thr over this CTA's rows
+__global__ void __launch_bounds__(128)
+outlier_flag_kernel(const __half* __restrict__ y, long long ld, int T, int K, float thr, unsigned* __restrict__ flags) {
+  const int ch = blockIdx.x * blockDim.x + threadIdx.x;      // 8-column chunk
+  if (ch >= (K >> 3)) return;
+  const int t0 = blockIdx.y * OS_ROWS, t1 = min(T, t0 + OS_ROWS);
+  unsigned bits = 0u;
+  for (int t = t0; t < t1; ++t) {
+    const uint4 u = ld_nc_v4(y + (long long)t * ld + ch * 8);
+    const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 f = h2_to_f2(w[e]);
+      if (fabsf(f.x) >= thr) bits |= 1u << (2 * e);
+      if (fabsf(f.y) >= thr) bits |= 1u << (2 * e + 1);
+    }
+  }
+  if (bits) atomicOr(flags + ch, bits);
+}
+
+// one CTA: mask[k], ascending cols[], count
+__global__ void __launch_bounds__(1024)
+outlier_compact_kernel(const unsigned* __restrict__ flags, int K, float* __restrict__ mask, int* __restrict__ cols,
+                       int* __restrict__ count) {
+  __shared__ int s_warp[32];
+  __shared__ int s_base;
+  if (threadIdx.x == 0) s_base = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int k0 = 0; k0 < K; k0 += 1024) {
+    const int k = k0 + threadIdx.x;
+    const bool out = k < K && ((flags[k >> 3] >> (k & 7)) & 1u);
+    if (k < K) mask[k] = out ? 0.0f : 1.0f;
+    const unsigned bal = __ballot_sync(0xffffffffu, out);
+    if (lane == 0) s_warp[warp] = __popc(bal);
+    __syncthreads();
+    int before = 0, total = 0;
+    for (int w = 0; w < 32; ++w) { const int c = s_warp[w]; if (w < warp) before += c; total += c; }
+    if (out) cols[s_base + before + __popc(bal & ((1u << lane) - 1u))] = k;
+    __syncthreads();
+    if (threadIdx.x == 0) s_base += total;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *count = s_base;
+}
+
+// out[t,n] = fp16( fp32(out[t,n]) + fp32(fp16( sum_j y[t,cols[j]] * fp16(W[n,cols[j]] * w_scale[n]) )) )  if count > 0
+// out[t,n] = fp16( fp32(out[t,n]) + fp32(residual[t,n]) )                                                    if residual
+__global__ void __launch_bounds__(256)
+outlier_side_kernel(__half* __restrict__ out, const __half* __restrict__ y, long long ld, const int8_t* __restrict__ W,
+                    const float* __restrict__ w_scale, const int* __restrict__ cols, const int* __restrict__ count,
+                    const __half* __restrict__ residual, int N, int K) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  const int t = blockIdx.y;
+  if (n >= N) return;
+  const int cnt = *count;
+  const long long off = (long long)t * N + n;
+  float o = __half2float(out[off]);
+  if (cnt > 0) {
+    const float ws = w_scale[n];
+    const __half* yr = y + (long long)t * ld;
+    const int8_t* wr = W + (long long)n * K;
+    float s = 0.0f;
+    for (int j = 0; j < cnt; ++j) {
+      const int k = cols[j];
+      const float w16 = __half2float(__float2half_rn(mul_rn((float)wr[k], ws)));
+      s = add_rn(s, mul_rn(__half2float(yr[k]), w16));
+    }
+    o = __half2float(__float2half_rn(add_rn(o, __half2float(__float2half_rn(s)))));
+  }
+  if (residual) o = add_rn(o, __half2float(residual[off]));
+  out[off] = __float2half_rn(o);
+}
+
+int outlier_scan(const void* y, long long ld, int T, int K, float threshold, float* mask, int* cols, int* count,
+                 unsigned* flags, cudaStream_t st) {
+  if (K <= 0 || (K & 7) || T < 0 || (ld & 7)) return ERR_BAD_SHAPE;
+  if (!mask || !cols || !count || !flags || (T > 0 && !y)) return ERR_NULL_PTR;
+  if (reinterpret_cast<uintptr_t>(y) & 15) return ERR_BAD_ALIGN;
+  if (cudaMemsetAsync(flags, 0, (size_t)(K >> 3) * sizeof(unsigned), st) != cudaSuccess) return ERR_LAUNCH;
+  if (T > 0) {
+    const dim3 grid(((K >> 3) + 127) / 128, (T + OS_ROWS - 1) / OS_ROWS);
+    outlier_flag_kernel<<<grid, 128, 0, st>>>((const __half*)y, ld, T, K, threshold, flags);
+  }
+  outlier_compact_kernel<<<1, 1024, 0, st>>>(flags, K, mask, cols, count);
+  return launch_status();
+}
+
+int outlier_side(void* out, const void* y, long long ld, const int8_t* W, const float* w_scale, const int* cols,
+                 const int* count, const void* residual, int T, int N, int K, cudaStream_t st) {
+  if (T == 0 || N == 0) return OK;
+  if (!out || !y || !W || !w_scale || !cols || !count) return ERR_NULL_PTR;
+  if (T < 0 || N < 0 || K <= 0) return ERR_BAD_SHAPE;
+  outlier_side_kernel<<<dim3((N + 255) / 256, T), 256, 0, st>>>((__half*)out, (const __half*)y, ld, W, w_scale, cols, count,
+                                                               (const __half*)residual, N, K);
+  return launch_status();
+}
+
+int init_outlier() {
+  cudaFuncAttributes fa;
+  bool ok = cudaFuncGetAttributes(&fa, outlier_flag_kernel) == cudaSuccess;
+  ok &= cudaFuncGetAttributes(&fa, outlier_compact_kernel) == cudaSuccess;
+  ok &= cudaFuncGetAttributes(&fa, outlier_side_kernel) == cudaSuccess;
+  return ok ? OK : ERR_ARCH;
+}
+
+}  // namespace b2

@@ -248,6 +248,22 @@ int act_mul_quant(const void* gate_up, const float* smooth, int8_t* q, float* ro
   }
 }
 
+// act(gate)*up (or act(x)) as fp16, no quantisation: the LLM.int8() path looks for outlier columns in the
+// fp16 activation before it quantises (outlier.cu)
+int act_mul_f16(const void* gate_up, void* y, int T, int F, int act, cudaStream_t st) {
+  if (T == 0) return OK;
+  if (!gate_up || !y) return ERR_NULL_PTR;
+  if (!al16(gate_up) || !al16(y)) return ERR_BAD_ALIGN;
+  const __half* x = (const __half*)gate_up;
+  switch (act) {
+    case 0: return launch_rowquant<ROW_SILU_MUL, true>(x, 2LL * F, nullptr, nullptr, nullptr, nullptr, nullptr, (__half*)y, T, F, 0.f, st);
+    case 1: return launch_rowquant<ROW_GELU_MUL, true>(x, 2LL * F, nullptr, nullptr, nullptr, nullptr, nullptr, (__half*)y, T, F, 0.f, st);
+    case 2: return launch_rowquant<ROW_GELU, true>(x, F, nullptr, nullptr, nullptr, nullptr, nullptr, (__half*)y, T, F, 0.f, st);
+    case 3: return launch_rowquant<ROW_SILU, true>(x, F, nullptr, nullptr, nullptr, nullptr, nullptr, (__half*)y, T, F, 0.f, st);
+    default: return ERR_UNSUPPORTED;
+  }
+}
+
 // Force-load every instantiation (lazy module loading must not happen under graph capture).
 template <typename K>
 static bool touch(K kern) {
@@ -262,7 +278,9 @@ static bool touch_mode() {
 int init_rowquant() {
   bool ok = touch_mode<ROW_PLAIN, false>() && touch_mode<ROW_RMS, false>() && touch_mode<ROW_LN, false>() &&
             touch_mode<ROW_SILU_MUL, false>() && touch_mode<ROW_GELU_MUL, false>() && touch_mode<ROW_GELU, false>() &&
-            touch_mode<ROW_SILU, false>() && touch_mode<ROW_RMS, true>() && touch_mode<ROW_LN, true>();
+            touch_mode<ROW_SILU, false>() && touch_mode<ROW_RMS, true>() && touch_mode<ROW_LN, true>() &&
+            touch_mode<ROW_SILU_MUL, true>() && touch_mode<ROW_GELU_MUL, true>() && touch_mode<ROW_GELU, true>() &&
+            touch_mode<ROW_SILU, true>();
   return ok ? OK : ERR_ARCH;
 }
 

@@ -229,6 +229,62 @@ def decode_attn_static(qkv, kcache, vcache, seqlens, H, KV, hd, max_seqlen, scal
     return o
 
 
+# ---- LLM.int8() mixed decomposition ------------------------------------------------------------
+LLM_INT8_THRESHOLD = 6.0      # bitsandbytes' default `llm_int8_threshold`
+
+
+def act_mul(gate_up, F, act, out=None):
+    """act(gate)*up (act 0/1: input [T,2F]) or act(x) (act 2/3: input [T,F]) as fp16 [T,F].  b2_act_mul."""
+    _cuda(gate_up, out)
+    T = gate_up.shape[0]
+    o = out if out is not None else torch.empty((T, F), dtype=torch.float16, device=gate_up.device)
+    check(_abi.lib().b2_act_mul(ptr(gate_up), ptr(o), T, F, int(act), stream_handle()), "b2_act_mul")
+    return o
+
+
+class OutlierScratch:
+    """Device buffers of one LLM.int8() linear: mask [K] fp32, cols [K] int32, count [1] int32, flags [K/8] u32."""
+
+    def __init__(self, K: int, device):
+        self.K = K
+        self.mask = torch.empty((K,), dtype=torch.float32, device=device)
+        self.cols = torch.empty((K,), dtype=torch.int32, device=device)
+        self.count = torch.zeros((1,), dtype=torch.int32, device=device)
+        self.flags = torch.empty((K // 8,), dtype=torch.int32, device=device)
+
+
+def outlier_scan(y, scratch: OutlierScratch, threshold=LLM_INT8_THRESHOLD):
+    """Outlier columns of y [T,K] fp16 (any |y| >= threshold) into `scratch`.  b2_outlier_scan."""
+    _cuda(y)
+    T, K = y.shape
+    check(_abi.lib().b2_outlier_scan(ptr(y), y.stride(0), T, K, float(threshold), ptr(scratch.mask), ptr(scratch.cols),
+                                     ptr(scratch.count), ptr(scratch.flags), stream_handle()), "b2_outlier_scan")
+    return scratch
+
+
+def outlier_side(out, y, w_q, w_scale, scratch: OutlierScratch, residual=None):
+    """out += fp16 side product over the outlier columns, then += residual (in place).  b2_outlier_side."""
+    _cuda(out, y, w_q, w_scale, residual)
+    T, N = out.shape
+    check(_abi.lib().b2_outlier_side(ptr(out), ptr(y), y.stride(0), ptr(w_q), ptr(w_scale), ptr(scratch.cols),
+                                     ptr(scratch.count), ptr(residual), T, N, w_q.shape[1], stream_handle()),
+          "b2_outlier_side")
+    return out
+
+
+def llm_int8_linear(y, w_q, w_scale, scratch: OutlierScratch, bias=None, residual=None, out=None, q_buf=None,
+                    scale_buf=None, threshold=LLM_INT8_THRESHOLD):
+    """One nn.Linear the way bitsandbytes' Linear8bitLt computes it (reference: load_in_8bit=True,
+    models_quant_updated.py:30-32): outlier columns of the fp16 activation in fp16, the rest W8A8."""
+    T, K = y.shape
+    outlier_scan(y, scratch, threshold)
+    q = q_buf if q_buf is not None else torch.empty((T, K), dtype=torch.int8, device=y.device)
+    sc = scale_buf if scale_buf is not None else torch.empty((T,), dtype=torch.float32, device=y.device)
+    smooth_quant(y, scratch.mask, out_q=q, out_scale=sc)
+    o = gemm_w8a8(q, w_q, sc, w_scale, bias, None, out=out)
+    return outlier_side(o, y, w_q, w_scale, scratch, residual)
+
+
 def set_prefill_attn_impl(impl: int):
     """Test hook: 0 = choose, 1 = always the mma.sync kernel, 2 = the tcgen05 kernel or an error."""
     check(_abi.lib().b2_set_prefill_attn_impl(int(impl)), "b2_set_prefill_attn_impl")

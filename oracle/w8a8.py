@@ -248,6 +248,47 @@ def llama3_inv_freq(inv_freq: np.ndarray, factor, low_freq_factor, high_freq_fac
     return np.where(medium, blended, out).astype(f32)
 
 
+# ----------------------------------------------------------------------------------------------
+# LLM.int8() mixed decomposition
+# ----------------------------------------------------------------------------------------------
+LLM_INT8_THRESHOLD = 6.0
+
+
+def outlier_columns(y16, threshold=LLM_INT8_THRESHOLD) -> np.ndarray:
+    """Columns of the fp16 activation that hold any value of magnitude >= threshold, ascending
+    (bitsandbytes int8_vectorwise_quant's `outlier_cols`; the reference asks for it with
+    BitsAndBytesConfig(load_in_8bit=True), models_quant_updated.py:30-32, default threshold 6.0)."""
+    y = np.asarray(y16, f16).astype(f32)
+    if y.shape[0] == 0:
+        return np.zeros((0,), np.int32)
+    return np.nonzero((np.abs(y) >= f32(threshold)).any(axis=0))[0].astype(np.int32)
+
+
+def llm_int8_linear(y16, w_q, w_scale, bias16=None, residual16=None, threshold=LLM_INT8_THRESHOLD):
+    """bitsandbytes MatMul8bitLt.forward restated (the package is not installable here: PARITY UNPINNED):
+    1. outlier columns O of the fp16 activation;  2. the other columns: per-row absmax int8 (vectorwise);
+    3. int8 x int8 -> int32, dequantised with row scale x weight-row scale (+ bias) to fp16;
+    4. + fp16( y[:,O] . fp16(W_q[:,O] * w_scale)^T ) accumulated in fp32 in ascending column order, fp16;
+    5. + residual (fp16 add, as the decoder layer does outside the linear).
+    Returns (out fp16 [T,N], acc int32 [T,N], O)."""
+    y = np.asarray(y16, f16)
+    cols = outlier_columns(y, threshold)
+    mask = np.ones((y.shape[1],), f32)
+    mask[cols] = 0.0
+    q, s = smooth_quant(y, mask)
+    out, acc = gemm_w8a8(q, w_q, s, w_scale, bias16, None)
+    if len(cols):
+        yf = y.astype(f32)
+        side = np.zeros(out.shape, f32)
+        for k in cols:
+            w16 = (w_q[:, k].astype(f32) * np.asarray(w_scale, f32)).astype(f16).astype(f32)
+            side = (side + (yf[:, k:k + 1] * w16[None, :]).astype(f32)).astype(f32)
+        out = (out.astype(f32) + side.astype(f16).astype(f32)).astype(f16)
+    if residual16 is not None:
+        out = (out.astype(f32) + np.asarray(residual16, f16).astype(f32)).astype(f16)
+    return out, acc, cols
+
+
 def rope_table(head_dim: int, max_pos: int, theta: float = 10000.0, scaling=()):
     """cos/sin tables fp32 [max_pos, head_dim/2] (modeling_llama.py:100-153: inv_freq =
     theta^(-2i/hd), angle = pos*inv_freq; optional ("llama3", factor, low, high, old_ctx) remap).

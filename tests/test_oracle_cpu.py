@@ -5,6 +5,7 @@ import os
 
 import numpy as np
 import pytest
+import torch
 
 import b200stage
 from b200stage import weights
@@ -215,3 +216,30 @@ def test_sample_det_is_a_valid_reproducible_draw():
     assert O.sample_det(lg, None, 1.0, 1, 1.0, 1.0, 0, 0, 0) == int(lg.argmax())
     u = [float(O.rng_uniform(5, s, 0)) for s in range(2000)]
     assert 0.0 <= min(u) and max(u) < 1.0 and abs(np.mean(u) - 0.5) < 0.03
+
+
+# ---- LLM.int8() mixed decomposition ------------------------------------------------------------
+def test_llm_int8_linear_oracle_properties():
+    """No outlier -> exactly the plain W8A8 linear; with outliers -> the outlier columns leave the
+    int8 product (so the row scales shrink and the result gets CLOSER to the fp32 product)."""
+    r = np.random.default_rng(21)
+    T, N, K = 6, 96, 256
+    W = (0.05 * r.standard_normal((N, K))).astype(np.float32)
+    wq, ws = weights.quantize_weight(torch.from_numpy(W), torch.ones(K))
+    wq, ws = wq.numpy(), ws.numpy()
+    y = np.clip(r.standard_normal((T, K)), -4, 4).astype(f16)
+    out, acc, cols = O.llm_int8_linear(y, wq, ws)
+    q, s = O.smooth_quant(y, None)
+    ref, acc_ref = O.gemm_w8a8(q, wq, s, ws, None, None)
+    assert len(cols) == 0 and np.array_equal(acc, acc_ref) and np.array_equal(out.view(np.uint16), ref.view(np.uint16))
+    y2 = y.copy()
+    y2[1, 10], y2[4, 10], y2[0, 77] = 30.0, -12.0, 6.0
+    out2, _, cols2 = O.llm_int8_linear(y2, wq, ws)
+    assert cols2.tolist() == [10, 77]
+    exact = y2.astype(np.float64) @ (wq.astype(np.float64) * ws[:, None].astype(np.float64)).T
+    q2, s2 = O.smooth_quant(y2, None)
+    plain, _ = O.gemm_w8a8(q2, wq, s2, ws, None, None)
+    assert np.abs(out2.astype(np.float64) - exact).max() < np.abs(plain.astype(np.float64) - exact).max()
+    res = r.standard_normal((T, N)).astype(f16)
+    out3, _, _ = O.llm_int8_linear(y2, wq, ws, None, res)
+    assert np.array_equal(out3, (out2.astype(f32) + res.astype(f32)).astype(f16))
