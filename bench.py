@@ -43,6 +43,9 @@ def parse():
     ap.add_argument("--chunk", type=int, default=0, help="prefill chunk (0 = auto: whole prompt on one GPU, 512 when pipelining)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--layers", type=int, default=0, help="PROFILING ONLY: truncate the model to this many layers")
+    ap.add_argument("--quant", default="w8a8", choices=["w8a8", "llm_int8"],
+                    help="w8a8 = the headline SmoothQuant-style path; llm_int8 = bitsandbytes-style mixed decomposition "
+                         "(SURVEY 8(f) rank 2; a side measurement, not the BASELINE metric)")
     return ap.parse_args()
 
 
@@ -214,7 +217,8 @@ def run_ours(a):
     CH = a.chunk or (min(P, 2048) if world == 1 else 512)
     max_seq = P + NEW
     n_prompts = world                       # weak scaling: one prompt stream per stage
-    pipe = DistPipeline.load(cfg, rank, world, dev, seed=0, fast_init=True, max_rows=n_prompts, max_seq=max_seq)
+    pipe = DistPipeline.load(cfg, rank, world, dev, seed=0, fast_init=True, max_rows=n_prompts, max_seq=max_seq,
+                             quant=a.quant)
     stage = pipe.stage
     pipe.graph_chunk = CH
     g = torch.Generator(device="cpu").manual_seed(1234)
@@ -316,7 +320,8 @@ def run_ours(a):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8",
             "data": "synthetic",
-            "config": {"workload": f"{cfg.name} W8A8 (random-init, seeded), {n_prompts} prompt(s) x ({P} prefill in chunks of {CH} + "
+            "config": {"workload": f"{cfg.name} {'W8A8' if a.quant == 'w8a8' else 'LLM.int8() mixed int8/fp16'} (random-init, seeded), "
+                                   f"{n_prompts} prompt(s) x ({P} prefill in chunks of {CH} + "
                                    f"{NEW} greedy decode), B=1 per prompt, {world} pipeline stage(s) x {n_layers_local} layers",
                        "parallelism": f"pp{world}", "l2": "inputs larger than L2 (int8 weights 6.5 GB streamed per decode token)"},
             "prefill_tokens_per_s": n_prompts * P / (pre_ms / 1e3), "decode_tokens_per_s": dec_tok_s,
@@ -373,7 +378,7 @@ def roofline_pass(torch, ops, stage, cfg, pk, dev, chunk):
     def dec():
         for lw in layers:
             ops.fused_linear(xh, lw["wgu"], lw["s_gu"], x_kind=xk, gamma=lw["ln2_g"], beta=lw.get("ln2_b"),
-                             smooth=lw["sm_gu"], eps=cfg.eps, out=y32, out_kind=ops.O_GATED, out_smooth=lw["sm_d"],
+                             smooth=lw.get("sm_gu"), eps=cfg.eps, out=y32, out_kind=ops.O_GATED, out_smooth=lw.get("sm_d"),
                              out_amax=amax)
     ms = timed(dec, 5) / len(layers)
     # algorithmic bytes: int8 weights + fp16 x, gamma + fp32 smooth (in and out) + w_scale + fp32 y

@@ -243,6 +243,13 @@ int b2_outlier_scan(const void* y, long long ld, int T, int K, float threshold, 
 int b2_outlier_side(void* out, const void* y, long long ld, const int8_t* W, const float* w_scale, const int* cols,
                     const int* count, const void* residual, int T, int N, int K, void* stream);
 
+/* b2_outlier_side for long batches, where most columns qualify as outliers (over a 2048-token chunk nearly every
+ * column of the MLP intermediate holds a value >= 6): the side product as a tcgen05 fp16 GEMM over y with its
+ * NON-outlier columns zeroed (mask from b2_outlier_scan) and W dequantised to fp16 per call.  Same result up
+ * to the fp32 summation order.  Caller scratch: ysub [T,K] fp16, wdeq [N,K] fp16, side [T,N] fp32.  K % 16 == 0. */
+int b2_outlier_side_dense(void* out, const void* y, long long ld, const int8_t* W, const float* w_scale, const float* mask,
+                          const void* residual, void* ysub, void* wdeq, float* side, int T, int N, int K, void* stream);
+
 /* Test hook (no reference counterpart): which kernel b2_prefill_attn uses from now on, process-wide.
  * 0 = choose (the tcgen05/TMEM kernel for head_dim 128 without a window and T >= 64, else the
  * mma.sync kernel), 1 = always the mma.sync kernel, 2 = the tcgen05 kernel or B2_ERR_UNSUPPORTED. */

@@ -38,6 +38,7 @@ SIGNATURES = {
     "b2_set_prefill_attn_impl": (_i, [_i]),
     "b2_act_mul": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "b2_outlier_scan": (_i, [_vp, _ll, _i, _i, _f, _vp, _vp, _vp, _vp, _vp]),
+    "b2_outlier_side_dense": (_i, [_vp, _vp, _ll, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
     "b2_outlier_side": (_i, [_vp, _vp, _ll, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
     "b2_prefill_attn": (_i, [_vp, _ll, _vp, _vp, _vp, _ll, _vp, _i, _i, _i, _i, _i, _i, _i, _f, _i, _vp]),
     "b2_embed": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp]),

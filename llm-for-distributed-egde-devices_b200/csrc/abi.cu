@@ -26,6 +26,8 @@ int act_mul_f16(const void*, void*, int, int, int, cudaStream_t);
 int outlier_scan(const void*, long long, int, int, float, float*, int*, int*, unsigned*, cudaStream_t);
 int outlier_side(void*, const void*, long long, const int8_t*, const float*, const int*, const int*, const void*, int, int,
                  int, cudaStream_t);
+int outlier_side_dense(void*, const void*, long long, const int8_t*, const float*, const float*, const void*, void*, void*,
+                       float*, int, int, int, cudaStream_t);
 int init_outlier();
 int init_attn();
 int init_attn_tc();
@@ -177,6 +179,10 @@ int b2_outlier_scan(const void* y, long long ld, int T, int K, float threshold, 
 int b2_outlier_side(void* out, const void* y, long long ld, const int8_t* W, const float* w_scale, const int* cols,
                     const int* count, const void* residual, int T, int N, int K, void* stream) {
   return b2::outlier_side(out, y, ld, W, w_scale, cols, count, residual, T, N, K, ST(stream));
+}
+int b2_outlier_side_dense(void* out, const void* y, long long ld, const int8_t* W, const float* w_scale, const float* mask,
+                          const void* residual, void* ysub, void* wdeq, float* side, int T, int N, int K, void* stream) {
+  return b2::outlier_side_dense(out, y, ld, W, w_scale, mask, residual, ysub, wdeq, side, T, N, K, ST(stream));
 }
 int b2_set_prefill_attn_impl(int impl) {
   if (impl < 0 || impl > 2) return b2::ERR_UNSUPPORTED;

@@ -118,11 +118,91 @@ int outlier_side(void* out, const void* y, long long ld, const int8_t* W, const 
   return launch_status();
 }
 
+// ---------------------------------------------------------------------------------------------
+// Dense side product for long batches.  Over a 2048-token prefill chunk most columns of the MLP
+// intermediate hold at least one value >= 6, so the "few outlier columns" become thousands and the
+// scalar kernel above turns into a naive GEMM.  Then: zero the NON-outlier columns of y, dequantise W
+// to fp16 once per call, and run the side product as a tcgen05 fp16 GEMM (the lm_head kernel,
+// fp32 accumulators), followed by one combine pass.  Summation order differs from the scalar kernel,
+// so this path is compared with the oracle within a tolerance, not bit for bit.
+// ---------------------------------------------------------------------------------------------
+int lm_head(const void* x, const void* W, float* logits, int M, int V, int d, cudaStream_t st);   // gemm_w8a8.cu
+
+__global__ void __launch_bounds__(256)
+outlier_keep_kernel(const __half* __restrict__ y, long long ld, const float* __restrict__ mask, __half* __restrict__ ysub, int K) {
+  const int t = blockIdx.y;
+  const int ch = blockIdx.x * blockDim.x + threadIdx.x;
+  if (ch >= (K >> 3)) return;
+  uint4 u = ld_nc_v4(y + (long long)t * ld + ch * 8);
+  const float4 m0 = *reinterpret_cast<const float4*>(mask + ch * 8);
+  const float4 m1 = *reinterpret_cast<const float4*>(mask + ch * 8 + 4);
+  // mask = 1 marks a column that went through the int8 product: drop it here
+  if (m0.x != 0.f) u.x &= 0xffff0000u; if (m0.y != 0.f) u.x &= 0x0000ffffu;
+  if (m0.z != 0.f) u.y &= 0xffff0000u; if (m0.w != 0.f) u.y &= 0x0000ffffu;
+  if (m1.x != 0.f) u.z &= 0xffff0000u; if (m1.y != 0.f) u.z &= 0x0000ffffu;
+  if (m1.z != 0.f) u.w &= 0xffff0000u; if (m1.w != 0.f) u.w &= 0x0000ffffu;
+  st_v4(ysub + (long long)t * K + ch * 8, u);
+}
+
+__global__ void __launch_bounds__(256)
+dequant_w_kernel(const int8_t* __restrict__ W, const float* __restrict__ w_scale, __half* __restrict__ wd, int K) {
+  const int n = blockIdx.y;
+  const int ch = blockIdx.x * blockDim.x + threadIdx.x;      // 16-element chunk
+  if (ch >= (K >> 4)) return;
+  const uint4 u = ld_nc_v4(W + (long long)n * K + ch * 16);
+  const float ws = w_scale[n];
+  const uint32_t w4[4] = {u.x, u.y, u.z, u.w};
+  uint32_t o[8];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const int b0 = (int)(int8_t)(w4[e] & 0xff), b1 = (int)(int8_t)((w4[e] >> 8) & 0xff);
+    const int b2_ = (int)(int8_t)((w4[e] >> 16) & 0xff), b3 = (int)(int8_t)((w4[e] >> 24) & 0xff);
+    o[2 * e] = f2_to_h2(mul_rn((float)b0, ws), mul_rn((float)b1, ws));
+    o[2 * e + 1] = f2_to_h2(mul_rn((float)b2_, ws), mul_rn((float)b3, ws));
+  }
+  __half* dst = wd + (long long)n * K + ch * 16;
+  st_v4(dst, make_uint4(o[0], o[1], o[2], o[3]));
+  st_v4(dst + 8, make_uint4(o[4], o[5], o[6], o[7]));
+}
+
+__global__ void __launch_bounds__(256)
+outlier_combine_kernel(__half* __restrict__ out, const float* __restrict__ side, const __half* __restrict__ residual,
+                       long long total) {
+  const long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i >= total) return;
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    if (i + e < total) {
+      float o = __half2float(__float2half_rn(add_rn(__half2float(out[i + e]), __half2float(__float2half_rn(side[i + e])))));
+      if (residual) o = add_rn(o, __half2float(residual[i + e]));
+      out[i + e] = __float2half_rn(o);
+    }
+  }
+}
+
+// scratch: ysub [T,K] fp16, wdeq [N,K] fp16, side [T,N] fp32 (caller-owned)
+int outlier_side_dense(void* out, const void* y, long long ld, const int8_t* W, const float* w_scale, const float* mask,
+                       const void* residual, void* ysub, void* wdeq, float* side, int T, int N, int K, cudaStream_t st) {
+  if (T == 0 || N == 0) return OK;
+  if (!out || !y || !W || !w_scale || !mask || !ysub || !wdeq || !side) return ERR_NULL_PTR;
+  if (T < 0 || N < 0 || K <= 0 || (K & 15) || (ld & 7)) return ERR_BAD_SHAPE;
+  outlier_keep_kernel<<<dim3(((K >> 3) + 255) / 256, T), 256, 0, st>>>((const __half*)y, ld, mask, (__half*)ysub, K);
+  dequant_w_kernel<<<dim3(((K >> 4) + 255) / 256, N), 256, 0, st>>>(W, w_scale, (__half*)wdeq, K);
+  const int rc = lm_head(ysub, wdeq, side, T, N, K, st);
+  if (rc) return rc;
+  const long long total = (long long)T * N;
+  outlier_combine_kernel<<<(unsigned)((total / 4 + 255) / 256), 256, 0, st>>>((__half*)out, side, (const __half*)residual, total);
+  return launch_status();
+}
+
 int init_outlier() {
   cudaFuncAttributes fa;
   bool ok = cudaFuncGetAttributes(&fa, outlier_flag_kernel) == cudaSuccess;
   ok &= cudaFuncGetAttributes(&fa, outlier_compact_kernel) == cudaSuccess;
   ok &= cudaFuncGetAttributes(&fa, outlier_side_kernel) == cudaSuccess;
+  ok &= cudaFuncGetAttributes(&fa, outlier_keep_kernel) == cudaSuccess;
+  ok &= cudaFuncGetAttributes(&fa, dequant_w_kernel) == cudaSuccess;
+  ok &= cudaFuncGetAttributes(&fa, outlier_combine_kernel) == cudaSuccess;
   return ok ? OK : ERR_ARCH;
 }
 

@@ -272,8 +272,30 @@ def outlier_side(out, y, w_q, w_scale, scratch: OutlierScratch, residual=None):
     return out
 
 
+class DenseSideScratch:
+    """Buffers of the tensor-core side product (b2_outlier_side_dense), sized for the largest linear of a model:
+    ysub [T,Kmax] fp16, wdeq [max N*K] fp16, side [T, Nmax] fp32."""
+
+    def __init__(self, T: int, kmax: int, nmax: int, nk_max: int, device):
+        self.T = T
+        self.ysub = torch.empty((T * kmax,), dtype=torch.float16, device=device)
+        self.wdeq = torch.empty((nk_max,), dtype=torch.float16, device=device)
+        self.side = torch.empty((T * nmax,), dtype=torch.float32, device=device)
+
+
+def outlier_side_dense(out, y, w_q, w_scale, scratch: OutlierScratch, dense: DenseSideScratch, residual=None):
+    """out += side product over the outlier columns as an fp16 tensor-core GEMM, then += residual."""
+    _cuda(out, y, w_q, w_scale, residual)
+    T, N = out.shape
+    K = w_q.shape[1]
+    check(_abi.lib().b2_outlier_side_dense(ptr(out), ptr(y), y.stride(0), ptr(w_q), ptr(w_scale), ptr(scratch.mask),
+                                           ptr(residual), ptr(dense.ysub), ptr(dense.wdeq), ptr(dense.side), T, N, K,
+                                           stream_handle()), "b2_outlier_side_dense")
+    return out
+
+
 def llm_int8_linear(y, w_q, w_scale, scratch: OutlierScratch, bias=None, residual=None, out=None, q_buf=None,
-                    scale_buf=None, threshold=LLM_INT8_THRESHOLD):
+                    scale_buf=None, threshold=LLM_INT8_THRESHOLD, dense: DenseSideScratch | None = None):
     """One nn.Linear the way bitsandbytes' Linear8bitLt computes it (reference: load_in_8bit=True,
     models_quant_updated.py:30-32): outlier columns of the fp16 activation in fp16, the rest W8A8."""
     T, K = y.shape
@@ -282,6 +304,8 @@ def llm_int8_linear(y, w_q, w_scale, scratch: OutlierScratch, bias=None, residua
     sc = scale_buf if scale_buf is not None else torch.empty((T,), dtype=torch.float32, device=y.device)
     smooth_quant(y, scratch.mask, out_q=q, out_scale=sc)
     o = gemm_w8a8(q, w_q, sc, w_scale, bias, None, out=out)
+    if dense is not None:       # long batches: thousands of outlier columns -> tensor-core side product
+        return outlier_side_dense(o, y, w_q, w_scale, scratch, dense, residual)
     return outlier_side(o, y, w_q, w_scale, scratch, residual)
 
 

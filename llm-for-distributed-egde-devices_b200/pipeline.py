@@ -42,12 +42,13 @@ class Pipeline:
         self._cache_pool = {}
 
     @classmethod
-    def load(cls, model, n_stages: int = 1, devices=None, seed: int = 0, fast_init: bool = False) -> "Pipeline":
+    def load(cls, model, n_stages: int = 1, devices=None, seed: int = 0, fast_init: bool = False,
+             quant: str = "w8a8") -> "Pipeline":
         cfg = get_config(model)
         devices = devices or ["cuda:0"] * n_stages
         rngs = split_layers(cfg.n_layers, n_stages)
         return cls([Stage.load(cfg, b, e, first=(i == 0), last=(i == n_stages - 1), device=devices[i], seed=seed,
-                               fast_init=fast_init) for i, (b, e) in enumerate(rngs)])
+                               fast_init=fast_init, quant=quant) for i, (b, e) in enumerate(rngs)])
 
     def new_caches(self, rows: int, max_seq: int):
         return [s.new_kv_cache(rows, max_seq) for s in self.stages]
@@ -179,11 +180,11 @@ class DistPipeline:
 
     @classmethod
     def load(cls, model, rank: int, world: int, device, seed: int = 0, fast_init: bool = True, max_rows: int = 1,
-             max_seq: int = 4096):
+             max_seq: int = 4096, quant: str = "w8a8"):
         cfg = get_config(model)
         b, e = split_layers(cfg.n_layers, world)[rank]
         stage = Stage.load(cfg, b, e, first=(rank == 0), last=(rank == world - 1), device=device, seed=seed,
-                           fast_init=fast_init)
+                           fast_init=fast_init, quant=quant)
         cache = stage.new_kv_cache(max_rows, max_seq)
         self = cls(rank, world, cfg.d_model, torch.device(device), None, cfg.vocab)
         self.stage, self.cache, self.cfg = stage, cache, cfg

@@ -28,6 +28,9 @@ from . import ops, weights
 from .config import ModelConfig, get_config
 
 
+# LLM.int8() mode: batches longer than this use the tensor-core side product (ops.outlier_side_dense)
+LLM_INT8_DENSE_SIDE_ABOVE = 64
+
 # Measured on B200 (tools/envsweep.sh): see DESIGN.md "L2 hint plan".
 DEFAULT_PF_PLAN = "qkv=wo:0:24,wgu:0:24;gu=wd:0:24;down=nqkv:0:24"
 
@@ -94,6 +97,24 @@ class _Scratch:
     def q8view(self, T, K):
         return self.q8[: T * K].view(T, K)
 
+    def llm_int8(self, cfg, device):
+        """Extra buffers of the LLM.int8() path (made on first use): fp16 norm output, fp16 act*up, and the
+        outlier scratch (mask / column list / count) per distinct input width."""
+        if getattr(self, "_int8x", None) is None:
+            f16 = torch.float16
+            self._int8x = dict(
+                y=torch.empty((self.cap, cfg.d_model), dtype=f16, device=device),
+                hm=torch.empty((self.cap, cfg.ffn), dtype=f16, device=device),
+                scr_d=ops.OutlierScratch(cfg.d_model, device),
+                scr_o=ops.OutlierScratch(cfg.n_heads * cfg.head_dim, device),
+                scr_f=ops.OutlierScratch(cfg.ffn, device), dense=None)
+            if self.cap > LLM_INT8_DENSE_SIDE_ABOVE:
+                hk = cfg.n_heads * cfg.head_dim
+                shapes = [(cfg.qkv_out, cfg.d_model), (cfg.d_model, hk), (cfg.up_out, cfg.d_model), (cfg.d_model, cfg.ffn)]
+                self._int8x["dense"] = ops.DenseSideScratch(self.cap, max(k for _, k in shapes), max(n for n, _ in shapes),
+                                                            max(n * k for n, k in shapes), device)
+        return self._int8x
+
 
 class Stage:
     def __init__(self, cfg: ModelConfig, sw: dict, layer_begin: int, layer_end: int, device):
@@ -122,6 +143,9 @@ class Stage:
         # SLOWER than four PDL-chained launches on B200 (38.0 vs 33.8 us per layer tail), so off by default
         # (also slower on the small models: TinyLlama 1271 vs 1584 tok/s, Llama-3.2-1B 1506 vs 1857)
         self.fuse_tail = False
+        # "w8a8" (SmoothQuant-style, the north-star path) or "llm_int8" (bitsandbytes' mixed decomposition:
+        # outlier activation columns in fp16, the rest int8 -- what the reference's load_in_8bit=True computes)
+        self.quant = sw.get("quant", "w8a8")
 
     # ------------------------------------------------------------------------------------------
     @classmethod
@@ -129,15 +153,15 @@ class Stage:
              device="cuda", quant: str = "w8a8", seed: int = 0, fast_init: bool = False, act_stats=None) -> "Stage":
         """Load (here: synthesise under `seed`, no checkpoints exist offline) the W8A8 shard for
         layers [layer_begin, layer_end).  `fast_init` generates on the device (benchmarks)."""
-        if quant != "w8a8":
-            raise ValueError("only quant='w8a8' is implemented")
+        if quant not in ("w8a8", "llm_int8"):
+            raise ValueError("quant must be 'w8a8' or 'llm_int8'")
         cfg = get_config(model_dir_or_config)
         if not (0 <= layer_begin < layer_end <= cfg.n_layers):
             raise ValueError(f"bad layer range [{layer_begin},{layer_end}) for {cfg.n_layers} layers")
         if fast_init:
-            sw = weights.build_stage_weights_fast(cfg, layer_begin, layer_end, first, last, seed, device)
+            sw = weights.build_stage_weights_fast(cfg, layer_begin, layer_end, first, last, seed, device, quant=quant)
         else:
-            sw = weights.build_stage_weights(cfg, layer_begin, layer_end, first, last, seed, device, act_stats)
+            sw = weights.build_stage_weights(cfg, layer_begin, layer_end, first, last, seed, device, act_stats, quant=quant)
         return cls(cfg, sw, layer_begin, layer_end, device)
 
     def new_kv_cache(self, rows: int, max_seq: int) -> KVCache:
@@ -188,6 +212,10 @@ class Stage:
         layers = self.w["layers"]
         for li, lw in enumerate(layers):
             kc, vc = kv_cache.k[li], kv_cache.v[li]
+            if self.quant == "llm_int8":
+                n += self._layer_llm_int8(buf, lw, h, h_alt, T, kc, vc, decode, dpos, dseq, dlens, row0, max_len, ws, act,
+                                          trace)
+                continue
             if fused and cfg.gated and self.fuse_tail:
                 # 2 launches per layer: attention, then ONE persistent kernel for
                 # o_proj -> gate_up -> down -> next layer's qkv (grid barriers between the phases)
@@ -289,6 +317,40 @@ class Stage:
         hn = ops.norm(hsel, self.w["lnf_g"], self.w.get("lnf_b"), cfg.eps, out=buf.hn[: hsel.shape[0]])
         lg = ops.lm_head(hn, self.w["lm_head"], out=out)
         return lg, n + 2
+
+    def _layer_llm_int8(self, buf, lw, h, h_alt, T, kc, vc, decode, dpos, dseq, dlens, row0, max_len, ws, act, trace):
+        """One decoder layer with every linear computed as bitsandbytes' Linear8bitLt does (ops.llm_int8_linear;
+        reference: BitsAndBytesConfig(load_in_8bit=True), models_quant_updated.py:30-38).  h -> h (h_alt = the
+        hidden state after attention).  Returns the number of kernels launched."""
+        cfg = self.cfg
+        d, H, KV, hd, F = cfg.d_model, cfg.n_heads, cfg.n_kv_heads, cfg.head_dim, cfg.ffn
+        x = buf.llm_int8(cfg, self.device)
+        y, hm, sc = x["y"][:T], x["hm"][:T], buf.scale[:T]
+        # long batches: most columns of a wide activation hold some value >= 6 -> side product on the tensor cores
+        dense = x["dense"] if T > LLM_INT8_DENSE_SIDE_ABOVE else None
+        qkv, attn, gu = buf.qkv[:T], buf.attn[:T], buf.gu[:T]
+        ops.norm(h, lw["ln1_g"], lw.get("ln1_b"), cfg.eps, out=y)
+        ops.llm_int8_linear(y, lw["wqkv"], lw["s_qkv"], x["scr_d"], bias=lw.get("b_qkv"), out=qkv,
+                            q_buf=buf.q8view(T, d), scale_buf=sc, dense=dense)
+        qkv_pre = qkv.clone() if trace is not None else None          # q and k are rotated in place below
+        ops.rope_kv_append(qkv, self.cos, self.sin, dpos, kc, vc, H, KV, hd, seq_ids=dseq, seq0=row0, use_rope=cfg.rope)
+        if decode:
+            ops.decode_attn(qkv, kc, vc, dlens, H, KV, hd, max_len, self.scale, cfg.window, rows=dseq, out=attn, workspace=ws)
+        else:
+            ops.prefill_attn(qkv, kc, vc, 0, row0, H, KV, hd, self.scale, cfg.window, out=attn, positions=dpos)
+        ops.llm_int8_linear(attn, lw["wo"], lw["s_o"], x["scr_o"], bias=lw.get("b_o"), residual=h, out=h_alt,
+                            q_buf=buf.q8view(T, H * hd), scale_buf=sc, dense=dense)
+        ops.norm(h_alt, lw["ln2_g"], lw.get("ln2_b"), cfg.eps, out=y)
+        ops.llm_int8_linear(y, lw["wgu"], lw["s_gu"], x["scr_d"], bias=lw.get("b_gu"), out=gu,
+                            q_buf=buf.q8view(T, d), scale_buf=sc, dense=dense)
+        ops.act_mul(gu, F, act, out=hm)
+        ops.llm_int8_linear(hm, lw["wd"], lw["s_d"], x["scr_f"], bias=lw.get("b_d"), residual=h_alt, out=h,
+                            q_buf=buf.q8view(T, F), scale_buf=sc, dense=dense)
+        if trace is not None:
+            trace.append(dict(qkv=qkv_pre, attn=attn.clone(), h1=h_alt.clone(), gu=gu.clone(), hm=hm.clone(), h2=h.clone(),
+                              n_out=[int(x[k].count.item()) for k in ("scr_d", "scr_o", "scr_f")]))
+        # per linear: 2 scan kernels + quantise + GEMM + side; plus 2 norms, rope, attention (+ merge), act
+        return 4 * 5 + 5 + (1 if (decode and ws is not None) else 0)
 
     def _hints(self, launch: str, lw, li: int):
         """The (up to two) L2 hints the `launch` kernel of layer li issues, per self.pf_plan."""

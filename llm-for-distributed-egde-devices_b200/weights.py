@@ -87,8 +87,28 @@ def quantize_weight(W: torch.Tensor, s: torch.Tensor | None):
     return Wq.contiguous(), scale.to(torch.float32).contiguous()
 
 
-def quantize_layer(cfg: ModelConfig, w: dict, act_stats: dict | None = None, alpha: float = ALPHA) -> dict:
+# LLM.int8() mode: real LLMs carry a few "outlier" feature channels; the synthetic models get them as
+# large norm gains on OUTLIER_CHANNELS channels per norm, so the fp16 side path of the decomposition runs.
+OUTLIER_CHANNELS = 3
+OUTLIER_GAIN = 9.0
+
+
+def outlier_gain_channels(d: int, layer: int, which: int):
+    """The channels of norm `which` (0 = ln1, 1 = ln2) of `layer` that get OUTLIER_GAIN (deterministic)."""
+    return [(37 * layer + 101 * which + 53 * j + 11) % d for j in range(OUTLIER_CHANNELS)]
+
+
+def add_outlier_gains(w: dict, d: int, layer: int) -> dict:
+    for which, key in enumerate(("ln1_g", "ln2_g")):
+        for c in outlier_gain_channels(d, layer, which):
+            w[key][c] = OUTLIER_GAIN
+    return w
+
+
+def quantize_layer(cfg: ModelConfig, w: dict, act_stats: dict | None = None, alpha: float = ALPHA,
+                   smooth: bool = True) -> dict:
     """fp32 layer dict -> W8A8 layer dict (torch tensors on w's device).
+    smooth = False: plain per-output-row absmax int8 (bitsandbytes' weight format), no sm_* vectors.
 
     act_stats (optional): per-input-channel activation absmax for 'qkv', 'o', 'gu', 'd' gathered by
     a calibration pass; absent -> weight-only smoothing statistics.
@@ -97,6 +117,9 @@ def quantize_layer(cfg: ModelConfig, w: dict, act_stats: dict | None = None, alp
     out = {}
     for name, wk, smk, sk in (("qkv", "wqkv", "sm_qkv", "s_qkv"), ("o", "wo", "sm_o", "s_o"),
                               ("gu", "wgu", "sm_gu", "s_gu"), ("d", "wd", "sm_d", "s_d")):
+        if not smooth:
+            out[wk], out[sk] = quantize_weight(w[wk], None)
+            continue
         s = _smooth_vec(w[wk], st.get(name), alpha)
         out[wk], out[sk] = quantize_weight(w[wk], s)
         out[smk] = (1.0 / s).to(torch.float32).contiguous()
@@ -107,12 +130,15 @@ def quantize_layer(cfg: ModelConfig, w: dict, act_stats: dict | None = None, alp
 
 
 def build_stage_weights(cfg: ModelConfig, layer_begin: int, layer_end: int, first: bool, last: bool,
-                        seed: int = 0, device="cpu", act_stats: list | None = None) -> dict:
+                        seed: int = 0, device="cpu", act_stats: list | None = None, quant: str = "w8a8") -> dict:
     """Seeded synthetic W8A8 shard for layers [layer_begin, layer_end) (CPU generation, exact
     and reproducible; used by the parity tests so the oracle sees identical weights)."""
-    sw = dict(first=first, last=last, layers=[])
+    sw = dict(first=first, last=last, layers=[], quant=quant)
     for li in range(layer_begin, layer_end):
-        lw = quantize_layer(cfg, init_layer_fp32(cfg, li, seed), None if act_stats is None else act_stats[li])
+        w32 = init_layer_fp32(cfg, li, seed)
+        if quant == "llm_int8":
+            add_outlier_gains(w32, cfg.d_model, li)
+        lw = quantize_layer(cfg, w32, None if act_stats is None else act_stats[li], smooth=(quant != "llm_int8"))
         sw["layers"].append({k: v.to(device) for k, v in lw.items()})
     if first or last:
         e = init_embed_fp32(cfg, seed)
@@ -129,13 +155,13 @@ def build_stage_weights(cfg: ModelConfig, layer_begin: int, layer_end: int, firs
 
 
 def build_stage_weights_fast(cfg: ModelConfig, layer_begin: int, layer_end: int, first: bool, last: bool,
-                             seed: int = 0, device="cuda") -> dict:
+                             seed: int = 0, device="cuda", quant: str = "w8a8") -> dict:
     """Same structure generated directly on `device` with torch's device RNG (benchmarks: the
     7B/13B shapes would take minutes through the CPU generator).  Statistically identical,
     not bit-identical to build_stage_weights."""
     dev = torch.device(device)
     g = torch.Generator(device=dev)
-    sw = dict(first=first, last=last, layers=[])
+    sw = dict(first=first, last=last, layers=[], quant=quant)
     d, F = cfg.d_model, cfg.ffn
     for li in range(layer_begin, layer_end):
         g.manual_seed(seed * 1000003 + li)
@@ -148,11 +174,16 @@ def build_stage_weights_fast(cfg: ModelConfig, layer_begin: int, layer_end: int,
         for wk, shape in (("wqkv", (cfg.qkv_out, d)), ("wo", (d, cfg.n_heads * cfg.head_dim)),
                           ("wgu", (cfg.up_out, d)), ("wd", (d, F))):
             W = rn(*shape)
-            s = _smooth_vec(W, None, ALPHA)
             sfx = wk[1:]
-            lw[wk], lw["s_" + sfx] = quantize_weight(W, s)
-            lw["sm_" + sfx] = (1.0 / s).contiguous()
+            if quant == "llm_int8":
+                lw[wk], lw["s_" + sfx] = quantize_weight(W, None)
+            else:
+                s = _smooth_vec(W, None, ALPHA)
+                lw[wk], lw["s_" + sfx] = quantize_weight(W, s)
+                lw["sm_" + sfx] = (1.0 / s).contiguous()
             del W
+        if quant == "llm_int8":
+            add_outlier_gains(w, d, li)
         lw["ln1_g"] = w["ln1_g"].to(torch.float16)
         lw["ln2_g"] = w["ln2_g"].to(torch.float16)
         if cfg.norm == "layernorm":

@@ -407,6 +407,59 @@ def block_forward(h16, lw, cfg, cache: KVCacheOracle, li, seq_ids, positions, co
     return h2
 
 
+def _attend(qkv, cfg, cache, li, seq_ids, positions, cos, sin):
+    """RoPE + KV append + attention over the cache for the fp16 qkv rows of one layer (shared by the modes)."""
+    H, KV, hd = cfg["n_heads"], cfg["n_kv_heads"], cfg["head_dim"]
+    T = qkv.shape[0]
+    qh = qkv[:, : H * hd].reshape(T, H, hd)
+    kh = qkv[:, H * hd: (H + KV) * hd].reshape(T, KV, hd)
+    vh = qkv[:, (H + KV) * hd:].reshape(T, KV, hd)
+    if cfg.get("rope", True):
+        qh = apply_rope(qh, positions, cos, sin)
+        kh = apply_rope(kh, positions, cos, sin)
+    for t in range(T):
+        cache.k[li, seq_ids[t], :, positions[t], :] = kh[t]
+        cache.v[li, seq_ids[t], :, positions[t], :] = vh[t]
+    attn = np.zeros((T, H, hd), dtype=f16)
+    scale = 1.0 / np.sqrt(hd)
+    for b in np.unique(seq_ids):
+        idx = np.nonzero(seq_ids == b)[0]
+        S = int(positions[idx].max()) + 1
+        kb = np.transpose(cache.k[li, b, :, :S, :], (1, 0, 2))
+        vb = np.transpose(cache.v[li, b, :, :S, :], (1, 0, 2))
+        attn[idx] = attention(qh[idx], kb, vb, positions[idx], scale, cfg.get("window", 0))
+    return attn.reshape(T, H * hd)
+
+
+def block_forward_llm_int8(h16, lw, cfg, cache: KVCacheOracle, li, seq_ids, positions, cos, sin, trace=None):
+    """One decoder layer with every nn.Linear computed the LLM.int8() way (llm_int8_linear): the
+    layer structure of modeling_llama.py:303-334 as the reference runs it under
+    BitsAndBytesConfig(load_in_8bit=True) (models_quant_updated.py:30-38).  Norms and act*up produce
+    fp16 activations (the tensors bitsandbytes sees), residual adds are fp16 adds outside the linear."""
+    eps = cfg["eps"]
+
+    def norm16(x, g, b):
+        y = rmsnorm_rows(x, g, eps) if b is None else layernorm_rows(x, g, b, eps)
+        return y.astype(f16)
+
+    y1 = norm16(h16, lw["ln1_g"], lw.get("ln1_b"))
+    qkv, _, c1 = llm_int8_linear(y1, lw["wqkv"], lw["s_qkv"], lw.get("b_qkv"), None)
+    attn = _attend(qkv, cfg, cache, li, seq_ids, positions, cos, sin)
+    h1, _, c2 = llm_int8_linear(attn, lw["wo"], lw["s_o"], lw.get("b_o"), h16)
+    y2 = norm16(h1, lw["ln2_g"], lw.get("ln2_b"))
+    gu, _, c3 = llm_int8_linear(y2, lw["wgu"], lw["s_gu"], lw.get("b_gu"), None)
+    if cfg.get("gated", True):
+        hm = act_mul_y(gu, None, cfg.get("act", "silu"))[0].astype(f16)
+    else:
+        g = np.asarray(gu, f16).astype(f32)
+        hm = (gelu_new_det(g) if cfg.get("act", "gelu_new") == "gelu_new" else silu_det(g)).astype(f16)
+    h2, _, c4 = llm_int8_linear(hm, lw["wd"], lw["s_d"], lw.get("b_d"), h1)
+    if trace is not None:
+        trace.append(dict(y1=y1, qkv=qkv, attn=attn.reshape(h16.shape[0], cfg["n_heads"], cfg["head_dim"]), h1=h1, y2=y2,
+                          gu=gu, hm=hm, h2=h2, cols=(c1, c2, c3, c4)))
+    return h2
+
+
 def final_norm(h16, g16, b16, eps):
     y = rmsnorm_rows(h16, g16, eps) if b16 is None else layernorm_rows(h16, g16, b16, eps)
     return y.astype(f16)
@@ -429,8 +482,9 @@ def stage_forward(x, sw, cfg, cache, seq_ids, positions, cos, sin, trace=None, l
             h = (h.astype(f32) + np.asarray(sw["pos_embed"], f16)[positions].astype(f32)).astype(f16)
     else:
         h = np.asarray(x, f16)
+    block = block_forward_llm_int8 if sw.get("quant", "w8a8") == "llm_int8" else block_forward
     for li, lw in enumerate(sw["layers"]):
-        h = block_forward(h, lw, cfg, cache, li, seq_ids, positions, cos, sin, trace)
+        h = block(h, lw, cfg, cache, li, seq_ids, positions, cos, sin, trace)
     if not sw["last"]:
         return h
     if logits_rows is not None:

@@ -91,3 +91,61 @@ def test_act_mul_f16_matches_oracle(act, gated):
         xf = x.astype(np.float32)
         want = O.gelu_new_det(xf) if act == 2 else O.silu_det(xf)
     assert np.array_equal(got.view(np.uint16), want.astype(np.float16).view(np.uint16))
+
+
+# ---- the whole stage in LLM.int8() mode ----------------------------------------------------------
+@pytest.mark.parametrize("model,n_stages", [("tiny-llama-test", 1), ("tiny-gqa-test", 2), ("tiny-gpt2-test", 1)])
+def test_stage_llm_int8_matches_oracle(model, n_stages):
+    from b200stage.pipeline import Pipeline, split_layers
+    cfg = b200stage.get_config(model)
+    seed, T, new = 2, 40, 10
+    ids = np.random.default_rng(8).integers(0, cfg.vocab, T)
+    osw = [weights.to_numpy(weights.build_stage_weights(cfg, b, e, i == 0, i == n_stages - 1, seed, "cpu", quant="llm_int8"))
+           for i, (b, e) in enumerate(split_layers(cfg.n_layers, n_stages))]
+    kc = cfg.kernel_cfg()
+    # one-stage trace of the oracle: outliers really occur, and where
+    one = weights.to_numpy(weights.build_stage_weights(cfg, 0, cfg.n_layers, True, True, seed, "cpu", quant="llm_int8"))
+    cos, sin = O.rope_table(cfg.head_dim, cfg.max_pos, cfg.rope_theta, cfg.rope_scaling)
+    cache = O.KVCacheOracle(cfg.n_layers, 1, cfg.n_kv_heads, T + new, cfg.head_dim)
+    otrace = []
+    ref = O.stage_forward(ids, one, kc, cache, np.zeros(T, np.int64), np.arange(T), cos, sin, otrace)
+    assert all(len(tr["cols"][0]) > 0 for tr in otrace)
+    pipe = Pipeline.load(cfg, n_stages, seed=seed, quant="llm_int8")
+    if n_stages == 1:
+        st = pipe.stages[0]
+        trace = []
+        got = st.forward(torch.from_numpy(ids).to(DEV), st.new_kv_cache(1, T + new), np.arange(T), logits="all", trace=trace)
+        # layer 0 up to the attention input: identical inputs -> bit-exact
+        assert np.array_equal(trace[0]["qkv"].cpu().numpy().view(np.uint16), otrace[0]["qkv"].view(np.uint16))
+        for li in range(cfg.n_layers):
+            assert trace[li]["n_out"][0] == len(otrace[li]["cols"][2])           # scratch of width d: last used by gate_up
+            a = trace[li]["h2"].cpu().numpy().astype(np.float64).ravel()
+            b = otrace[li]["h2"].astype(np.float64).ravel()
+            assert np.abs(a - b).max() <= 2.0 ** -5 * np.abs(b).max()
+            assert a @ b / (np.linalg.norm(a) * np.linalg.norm(b)) >= 0.9995
+        g = got.cpu().numpy()
+        assert np.abs(g - ref).max() <= 0.02 * np.abs(ref).max()
+        assert np.array_equal(g.argmax(-1), ref.argmax(-1))
+    toks, margins = O.greedy_generate(osw, kc, ids, new, T + new)
+    out = pipe.generate(torch.from_numpy(ids).to(DEV), max_new_tokens=new, chunk=16).cpu().numpy()
+    assert np.array_equal(out, toks), (out[T:], toks[T:], min(margins))
+
+
+@pytest.mark.parametrize("T,N,K,nout,res", [(96, 512, 1024, 700, True), (300, 768, 2048, 40, False), (130, 256, 512, 0, True)])
+def test_dense_side_product_matches_oracle_within_tolerance(T, N, K, nout, res):
+    """The tensor-core side product (long batches: hundreds of outlier columns) against the oracle: same
+    mask / int8 part bit for bit, fp16 result within fp32-summation-order tolerance of the side term."""
+    r = np.random.default_rng(T + N + nout)
+    wq, ws = _weights(r, N, K)
+    y16, cols = _acts(r, T, K, nout)
+    r16 = r.standard_normal((T, N)).astype(np.float16) if res else None
+    want, _, ocols = O.llm_int8_linear(y16, wq, ws, None, r16)
+    assert len(ocols) == nout
+    sc = ops.OutlierScratch(K, DEV)
+    dense = ops.DenseSideScratch(T, K, N, N * K, DEV)
+    got = ops.llm_int8_linear(t(y16), t(wq), t(ws), sc, residual=None if r16 is None else t(r16), dense=dense).cpu().numpy()
+    assert int(sc.count.item()) == nout
+    a, b = got.astype(np.float64), want.astype(np.float64)
+    assert np.abs(a - b).max() <= 2e-3 * np.abs(b).max() + 2e-3, np.abs(a - b).max()
+    if nout == 0:
+        assert np.array_equal(got.view(np.uint16), want.view(np.uint16))       # zero side term: exact
