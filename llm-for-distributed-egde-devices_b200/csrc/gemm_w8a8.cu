@@ -455,6 +455,15 @@ int gemm_w8a8(const int8_t* A, const int8_t* W, const float* a_scale, const floa
   }
   const int m_tiles = (M + BM - 1) / BM;
   const int sms = sm_count();
+  // The cluster schedules multicast the weight tile with TMA.  TMA multicast loads here read only this GPU's
+  // memory, since on B200 a TMA multicast load from another GPU's memory hung the GPU: refuse a W that is not
+  // plain device memory of the current device (every default path uses CM = 1 and is not concerned).
+  if (schedule == 11 || schedule == 12 || schedule == 13 || schedule == 16) {
+    int dev = -1;
+    cudaPointerAttributes pa;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaPointerGetAttributes(&pa, W) != cudaSuccess) { cudaGetLastError(); return ERR_UNSUPPORTED; }
+    if (pa.type != cudaMemoryTypeDevice || pa.device != dev) return ERR_UNSUPPORTED;
+  }
   // schedule >= 10 (test hook): force a tile/cluster shape; 0/1: heuristic
   if (schedule == 10) return launch_tc<256, 4, KIND_I8, 1>(A, W, p, st);
   if (schedule == 11) return launch_tc<256, 4, KIND_I8, 2>(A, W, p, st);
