@@ -28,9 +28,13 @@ constexpr int BK = 128;         // int8 elements per k-block = one 128-byte swiz
 constexpr int UMMA_K = 32;      // int8
 constexpr int GEMM_THREADS = 256;
 
-template <int BN, int STAGES>
+// ABOX = rows of A that TMA stages per k-block.  The MMA always reads 128 rows; with ABOX < 128 (decode
+// batches of up to ABOX tokens) rows ABOX..127 of the A operand alias the B tile behind it: they produce
+// accumulator rows that are never stored, and the ring holds more weight bytes in flight instead of
+// zero-filled activation rows.
+template <int BN, int STAGES, int ABOX = BM>
 struct GemmSmem {
-  static constexpr int A_BYTES = BM * BK;
+  static constexpr int A_BYTES = ABOX * BK;
   static constexpr int B_BYTES = BN * BK;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int BAR_OFF = STAGES * STAGE_BYTES;
@@ -55,11 +59,13 @@ constexpr int KIND_I8 = 0, KIND_F16 = 1;
 // tile and multicasts it to the whole cluster, so per-CTA operand traffic from L2 drops from
 // A + B to A + B/CM.  A stage is refilled only after every CTA of the cluster has consumed it:
 // the MMA commits are multicast to all empty barriers (count CM).
-template <int BN, int STAGES, int KIND, int CM>
+template <int BN, int STAGES, int KIND, int CM, int ABOX = BM>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const GemmParams p) {
-  using S = GemmSmem<BN, STAGES>;
+  using S = GemmSmem<BN, STAGES, ABOX>;
+  static_assert((ABOX * BK) % 1024 == 0, "the B tile behind A must stay 1024-byte aligned");
+  static_assert((ABOX + BN) * BK >= BM * BK, "the 128 A rows the MMA reads must stay inside the stage");
   constexpr int TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -282,18 +288,19 @@ static int sm_count() {
   return n;
 }
 
-template <int BN, int STAGES, int KIND, int CM>
+template <int BN, int STAGES, int KIND, int CM, int ABOX = BM>
 static int launch_tc(const void* A, const void* W, const GemmParams& p, cudaStream_t st) {
-  using S = GemmSmem<BN, STAGES>;
+  using S = GemmSmem<BN, STAGES, ABOX>;
+  if (ABOX < BM && p.M > ABOX) return ERR_UNSUPPORTED;
   static bool attr_set = false;
   if (!attr_set) {
-    if (cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES, KIND, CM>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL) !=
+    if (cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES, KIND, CM, ABOX>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL) !=
         cudaSuccess)
       return ERR_ARCH;
     attr_set = true;
   }
   CUtensorMap tmA, tmB;
-  int rc = make_tmap(&tmA, A, p.M, p.K, BM, KIND);
+  int rc = make_tmap(&tmA, A, p.M, p.K, ABOX, KIND);
   if (rc) return rc;
   rc = make_tmap(&tmB, W, p.N, p.K, BN / CM, KIND);          // each CTA loads BN/CM rows of the weight tile
   if (rc) return rc;
@@ -311,7 +318,7 @@ static int launch_tc(const void* A, const void* W, const GemmParams& p, cudaStre
   at[0].val.clusterDim.x = CM; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
   cfg.attrs = at;
   cfg.numAttrs = 1;
-  if (cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, STAGES, KIND, CM>, tmA, tmB, p) != cudaSuccess) {
+  if (cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, STAGES, KIND, CM, ABOX>, tmA, tmB, p) != cudaSuccess) {
     cudaGetLastError();
     return ERR_LAUNCH;
   }
@@ -445,7 +452,7 @@ int gemm_w8a8(const int8_t* A, const int8_t* W, const float* a_scale, const floa
   GemmParams p{a_scale, w_scale, (const __half*)bias, (const __half*)residual, (__half*)out, nullptr, acc_dump, M, N, K, N};
   // schedule: 0 = auto, 1 = force tensor-core path, 2 = force streaming path (M <= 8 only)
   const bool gemv = (schedule == 2) || (schedule == 0 && M <= GEMV_MAX_M);
-  if (schedule >= 10 && (N % 256 || schedule > 16)) return ERR_UNSUPPORTED;
+  if (schedule >= 10 && (N % 256 || schedule > 19)) return ERR_UNSUPPORTED;
   if (gemv) {
     if (M > GEMV_MAX_M) return ERR_UNSUPPORTED;
     if (M == 1) return launch_gemv<1>(A, W, p, st);
@@ -472,9 +479,16 @@ int gemm_w8a8(const int8_t* A, const int8_t* W, const float* a_scale, const floa
   if (schedule == 14) return launch_tc<128, 6, KIND_I8, 1>(A, W, p, st);
   if (schedule == 15) return launch_tc<64, 8, KIND_I8, 1>(A, W, p, st);
   if (schedule == 16) return launch_tc<128, 6, KIND_I8, 2>(A, W, p, st);
+  if (schedule == 17) return launch_tc<32, 8, KIND_I8, 1>(A, W, p, st);
+  if (schedule == 18) return launch_tc<128, 10, KIND_I8, 1, 32>(A, W, p, st);     // M <= 32
+  if (schedule == 19) return launch_tc<128, 8, KIND_I8, 1, 64>(A, W, p, st);      // M <= 64
   // Measured on B200 (tools/kbench.py, profiles/r01_*): the kernel is bound by operand latency /
   // bytes in flight, not by L2 bandwidth, so 128x128 tiles with a 6-deep ring beat 128x256 with 4
   // stages on every Llama-2-7B shape (1.4-1.66 vs 1.0-1.47 PTOP/s at M = 512).
+  // Decode batches of 9..16 tokens: a 32-row A box leaves room for 10 stages of 128-row weight tiles
+  // (measured at M = 16 on the 7B shapes: qkv 17.6 vs 23.0 us, gate_up 29.1 vs 33.4, o 15.8 vs 17.3; no gain from
+  // M = 32 up, and none for K = 11008 where the 64-row tile's extra CTAs matter more).
+  if (M <= 16 && N >= 1024 && K <= 8192) return launch_tc<128, 10, KIND_I8, 1, 32>(A, W, p, st);
   // With enough row tiles the picture flips: at M = 2048 a 128x256 tile (half the A re-reads, twice
   // the MMA work per staged A tile) wins whenever its tiles still fill the persistent grid's waves
   // (gate_up 174 vs 188 us, down 83 vs 98 us), i.e. wave efficiency tiles/(ceil(tiles/SMs)*SMs) >= 0.8.
@@ -586,10 +600,10 @@ int lm_head(const void* x, const void* W, float* logits, int M, int V, int d, cu
 
 // One-time set-up of every instantiation (dynamic shared-memory opt-in, driver entry point), so
 // that no launch path has first-call side effects -- required before capturing CUDA graphs.
-template <int BN, int STAGES, int KIND, int CM = 1>
+template <int BN, int STAGES, int KIND, int CM = 1, int ABOX = BM>
 static int init_tc() {
-  return cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES, KIND, CM>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                              GemmSmem<BN, STAGES>::TOTAL) == cudaSuccess ? OK : ERR_ARCH;
+  return cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES, KIND, CM, ABOX>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                              GemmSmem<BN, STAGES, ABOX>::TOTAL) == cudaSuccess ? OK : ERR_ARCH;
 }
 int init_gemm() {
   if (!get_encode_fn()) return ERR_DRIVER;
@@ -599,6 +613,8 @@ int init_gemm() {
   if ((rc = init_tc<128, 6, KIND_I8>())) return rc;
   if ((rc = init_tc<64, 8, KIND_I8>())) return rc;
   if ((rc = init_tc<32, 8, KIND_I8>())) return rc;
+  if ((rc = init_tc<128, 10, KIND_I8, 1, 32>())) return rc;
+  if ((rc = init_tc<128, 8, KIND_I8, 1, 64>())) return rc;
   if ((rc = init_tc<256, 4, KIND_I8, 2>())) return rc;
   if ((rc = init_tc<256, 4, KIND_I8, 4>())) return rc;
   if ((rc = init_tc<128, 6, KIND_I8, 2>())) return rc;

@@ -34,6 +34,33 @@ def test_gemm_cluster_schedules_exact(sched, M, N, K):
     assert np.array_equal(out.cpu().numpy().view(np.uint16), ref.view(np.uint16))
 
 
+@pytest.mark.parametrize("sched,M", [(18, 1), (18, 9), (18, 16), (18, 32), (19, 33), (19, 64), (17, 40), (0, 12), (0, 16)])
+@pytest.mark.parametrize("N,K", [(1024, 1024), (4096, 4096), (22016, 512), (512, 11008)])
+def test_gemm_small_batch_schedules_exact(sched, M, N, K):
+    """Decode-batch schedules (only 32 / 64 activation rows staged, the MMA's other A rows alias weight bytes and
+    are never stored) and the heuristic that picks them: exact accumulators and outputs, several tiles per CTA."""
+    r = np.random.default_rng(sched * 100 + M + N + K)
+    a = r.integers(-127, 128, (M, K), dtype=np.int8)
+    w = r.integers(-127, 128, (N, K), dtype=np.int8)
+    sa = r.uniform(1e-3, 5e-2, M).astype(np.float32)
+    sw = r.uniform(1e-4, 2e-3, N).astype(np.float32)
+    res = r.standard_normal((M, N)).astype(np.float16)
+    ref, acc_ref = O.gemm_w8a8(a, w, sa, sw, None, res)
+    acc = torch.full((M, N), -5, dtype=torch.int32, device=DEV)
+    out = ops.gemm_w8a8(t(a), t(w), t(sa), t(sw), None, t(res), acc_dump=acc, schedule=sched)
+    torch.cuda.synchronize()
+    assert np.array_equal(acc.cpu().numpy(), acc_ref)
+    assert np.array_equal(out.cpu().numpy().view(np.uint16), ref.view(np.uint16))
+
+
+def test_small_batch_schedule_refuses_a_batch_it_cannot_stage():
+    a = torch.zeros((40, 256), dtype=torch.int8, device=DEV)
+    w = torch.zeros((256, 256), dtype=torch.int8, device=DEV)
+    s1, s2 = torch.ones(40, device=DEV), torch.ones(256, device=DEV)
+    with pytest.raises(ops._abi.B2Error):
+        ops.gemm_w8a8(a, w, s1, s2, schedule=18)
+
+
 def test_gemm_cluster_many_tiles_per_cluster():
     """More cluster tiles than clusters: the persistent loop and the ring phases wrap several times."""
     M, N, K = 512, 22016, 512
