@@ -94,11 +94,70 @@ outlier_side_kernel(__half* __restrict__ out, const __half* __restrict__ y, long
   out[off] = __float2half_rn(o);
 }
 
+// Decode batches (T <= OS_SMALL_T rows): flags and ordered compaction in ONE launch of one CTA -- a decode step
+// runs four of these scans per layer, and each extra launch costs more than the scan itself.
+constexpr int OS_SMALL_T = 8;
+__global__ void __launch_bounds__(1024)
+outlier_scan_small_kernel(const __half* __restrict__ y, long long ld, int T, int K, float thr, float* __restrict__ mask,
+                          int* __restrict__ cols, int* __restrict__ count) {
+  __shared__ int s_warp[32];
+  __shared__ int s_base;
+  if (threadIdx.x == 0) s_base = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nchunk = K >> 3;                                  // 8 columns (16 bytes) per thread and round
+  for (int c0 = 0; c0 < nchunk; c0 += 1024) {
+    const int ch = c0 + threadIdx.x;
+    unsigned bits = 0u;
+    if (ch < nchunk) {
+      for (int t = 0; t < T; ++t) {
+        const uint4 u = ld_nc_v4(y + (long long)t * ld + ch * 8);
+        const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 f = h2_to_f2(w[e]);
+          if (fabsf(f.x) >= thr) bits |= 1u << (2 * e);
+          if (fabsf(f.y) >= thr) bits |= 1u << (2 * e + 1);
+        }
+      }
+      float m[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) m[e] = ((bits >> e) & 1u) ? 0.0f : 1.0f;
+      *reinterpret_cast<float4*>(mask + ch * 8) = make_float4(m[0], m[1], m[2], m[3]);
+      *reinterpret_cast<float4*>(mask + ch * 8 + 4) = make_float4(m[4], m[5], m[6], m[7]);
+    }
+    // ordered compaction: exclusive prefix of the per-thread counts (warp scan, then over the warps)
+    const int mine = __popc(bits);
+    int incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    int before = 0, total = 0;
+    for (int w = 0; w < 32; ++w) { const int c = s_warp[w]; if (w < warp) before += c; total += c; }
+    int pos = s_base + before + incl - mine;
+#pragma unroll
+    for (int e = 0; e < 8; ++e)
+      if ((bits >> e) & 1u) cols[pos++] = ch * 8 + e;
+    __syncthreads();
+    if (threadIdx.x == 0) s_base += total;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *count = s_base;
+}
+
 int outlier_scan(const void* y, long long ld, int T, int K, float threshold, float* mask, int* cols, int* count,
                  unsigned* flags, cudaStream_t st) {
   if (K <= 0 || (K & 7) || T < 0 || (ld & 7)) return ERR_BAD_SHAPE;
   if (!mask || !cols || !count || !flags || (T > 0 && !y)) return ERR_NULL_PTR;
   if (reinterpret_cast<uintptr_t>(y) & 15) return ERR_BAD_ALIGN;
+  if (T > 0 && T <= OS_SMALL_T) {
+    outlier_scan_small_kernel<<<1, 1024, 0, st>>>((const __half*)y, ld, T, K, threshold, mask, cols, count);
+    return launch_status();
+  }
   if (cudaMemsetAsync(flags, 0, (size_t)(K >> 3) * sizeof(unsigned), st) != cudaSuccess) return ERR_LAUNCH;
   if (T > 0) {
     const dim3 grid(((K >> 3) + 127) / 128, (T + OS_ROWS - 1) / OS_ROWS);
@@ -200,6 +259,7 @@ int init_outlier() {
   bool ok = cudaFuncGetAttributes(&fa, outlier_flag_kernel) == cudaSuccess;
   ok &= cudaFuncGetAttributes(&fa, outlier_compact_kernel) == cudaSuccess;
   ok &= cudaFuncGetAttributes(&fa, outlier_side_kernel) == cudaSuccess;
+  ok &= cudaFuncGetAttributes(&fa, outlier_scan_small_kernel) == cudaSuccess;
   ok &= cudaFuncGetAttributes(&fa, outlier_keep_kernel) == cudaSuccess;
   ok &= cudaFuncGetAttributes(&fa, dequant_w_kernel) == cudaSuccess;
   ok &= cudaFuncGetAttributes(&fa, outlier_combine_kernel) == cudaSuccess;

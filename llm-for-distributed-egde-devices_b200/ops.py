@@ -295,11 +295,17 @@ def outlier_side_dense(out, y, w_q, w_scale, scratch: OutlierScratch, dense: Den
 
 
 def llm_int8_linear(y, w_q, w_scale, scratch: OutlierScratch, bias=None, residual=None, out=None, q_buf=None,
-                    scale_buf=None, threshold=LLM_INT8_THRESHOLD, dense: DenseSideScratch | None = None):
+                    scale_buf=None, threshold=LLM_INT8_THRESHOLD, dense: DenseSideScratch | None = None,
+                    fused_decode: bool = False):
     """One nn.Linear the way bitsandbytes' Linear8bitLt computes it (reference: load_in_8bit=True,
     models_quant_updated.py:30-32): outlier columns of the fp16 activation in fp16, the rest W8A8."""
     T, K = y.shape
     outlier_scan(y, scratch, threshold)
+    if fused_decode and T <= 8 and dense is None:
+        # decode: masked quantise + int8 GEMV + dequantising epilogue in one launch (bit-identical to the two below)
+        o = out if out is not None else torch.empty((T, w_q.shape[0]), dtype=torch.float16, device=y.device)
+        fused_linear(y, w_q, w_scale, x_kind=X_PLAIN, smooth=scratch.mask, bias=bias, out=o)
+        return outlier_side(o, y, w_q, w_scale, scratch, residual)
     q = q_buf if q_buf is not None else torch.empty((T, K), dtype=torch.int8, device=y.device)
     sc = scale_buf if scale_buf is not None else torch.empty((T,), dtype=torch.float32, device=y.device)
     smooth_quant(y, scratch.mask, out_q=q, out_scale=sc)

@@ -328,10 +328,11 @@ class Stage:
         y, hm, sc = x["y"][:T], x["hm"][:T], buf.scale[:T]
         # long batches: most columns of a wide activation hold some value >= 6 -> side product on the tensor cores
         dense = x["dense"] if T > LLM_INT8_DENSE_SIDE_ABOVE else None
+        fd = decode and T <= 8 and trace is None and self.fuse_decode
         qkv, attn, gu = buf.qkv[:T], buf.attn[:T], buf.gu[:T]
         ops.norm(h, lw["ln1_g"], lw.get("ln1_b"), cfg.eps, out=y)
         ops.llm_int8_linear(y, lw["wqkv"], lw["s_qkv"], x["scr_d"], bias=lw.get("b_qkv"), out=qkv,
-                            q_buf=buf.q8view(T, d), scale_buf=sc, dense=dense)
+                            q_buf=buf.q8view(T, d), scale_buf=sc, dense=dense, fused_decode=fd)
         qkv_pre = qkv.clone() if trace is not None else None          # q and k are rotated in place below
         ops.rope_kv_append(qkv, self.cos, self.sin, dpos, kc, vc, H, KV, hd, seq_ids=dseq, seq0=row0, use_rope=cfg.rope)
         if decode:
@@ -339,18 +340,19 @@ class Stage:
         else:
             ops.prefill_attn(qkv, kc, vc, 0, row0, H, KV, hd, self.scale, cfg.window, out=attn, positions=dpos)
         ops.llm_int8_linear(attn, lw["wo"], lw["s_o"], x["scr_o"], bias=lw.get("b_o"), residual=h, out=h_alt,
-                            q_buf=buf.q8view(T, H * hd), scale_buf=sc, dense=dense)
+                            q_buf=buf.q8view(T, H * hd), scale_buf=sc, dense=dense, fused_decode=fd)
         ops.norm(h_alt, lw["ln2_g"], lw.get("ln2_b"), cfg.eps, out=y)
         ops.llm_int8_linear(y, lw["wgu"], lw["s_gu"], x["scr_d"], bias=lw.get("b_gu"), out=gu,
-                            q_buf=buf.q8view(T, d), scale_buf=sc, dense=dense)
+                            q_buf=buf.q8view(T, d), scale_buf=sc, dense=dense, fused_decode=fd)
         ops.act_mul(gu, F, act, out=hm)
         ops.llm_int8_linear(hm, lw["wd"], lw["s_d"], x["scr_f"], bias=lw.get("b_d"), residual=h_alt, out=h,
-                            q_buf=buf.q8view(T, F), scale_buf=sc, dense=dense)
+                            q_buf=buf.q8view(T, F), scale_buf=sc, dense=dense, fused_decode=fd)
         if trace is not None:
             trace.append(dict(qkv=qkv_pre, attn=attn.clone(), h1=h_alt.clone(), gu=gu.clone(), hm=hm.clone(), h2=h.clone(),
                               n_out=[int(x[k].count.item()) for k in ("scr_d", "scr_o", "scr_f")]))
-        # per linear: 2 scan kernels + quantise + GEMM + side; plus 2 norms, rope, attention (+ merge), act
-        return 4 * 5 + 5 + (1 if (decode and ws is not None) else 0)
+        # per linear: scan (1 launch for decode batches, else 2 + memset) + quantise + GEMM (one fused launch in
+        # decode) + side; plus 2 norms, rope, attention (+ merge), act
+        return 4 * (3 if fd else 5) + 5 + (1 if (decode and ws is not None) else 0)
 
     def _hints(self, launch: str, lw, li: int):
         """The (up to two) L2 hints the `launch` kernel of layer li issues, per self.pf_plan."""

@@ -62,6 +62,24 @@ def test_llm_int8_linear_bit_exact(T, N, K, nout, bias, res):
     assert np.array_equal(got.cpu().numpy().view(np.uint16), want.view(np.uint16))
 
 
+@pytest.mark.parametrize("T,N,K,nout,bias,res", [(1, 512, 4096, 4, False, True), (3, 256, 1024, 0, True, False),
+                                                  (8, 768, 2048, 9, True, True), (5, 1024, 11008, 2, False, True)])
+def test_llm_int8_linear_decode_path_bit_exact(T, N, K, nout, bias, res):
+    """Decode batches: one-launch scan + fused masked-quantise/GEMV kernel: the same bits as the oracle."""
+    r = np.random.default_rng(T * 3 + N + K + nout)
+    wq, ws = _weights(r, N, K)
+    y16, cols = _acts(r, T, K, nout)
+    b16 = (0.1 * r.standard_normal(N)).astype(np.float16) if bias else None
+    r16 = r.standard_normal((T, N)).astype(np.float16) if res else None
+    want, _, ocols = O.llm_int8_linear(y16, wq, ws, b16, r16)
+    sc = ops.OutlierScratch(K, DEV)
+    got = ops.llm_int8_linear(t(y16), t(wq), t(ws), sc, bias=None if b16 is None else t(b16),
+                              residual=None if r16 is None else t(r16), fused_decode=True)
+    n = int(sc.count.item())
+    assert n == len(ocols) and np.array_equal(sc.cols[:n].cpu().numpy(), ocols)
+    assert np.array_equal(got.cpu().numpy().view(np.uint16), want.view(np.uint16))
+
+
 def test_threshold_is_inclusive_and_scratch_is_reusable():
     r = np.random.default_rng(3)
     K, N = 256, 128
