@@ -67,6 +67,21 @@ B2_DEVINL float ex2_approx(float x) {
   return y;
 }
 
+// Packed fp32x2 arithmetic (sm_100): the softmax warps are issue-bound, and one FFMA2 / FADD2 does the work of two
+// scalar instructions.  (d0,d1) = (a0,a1) * b + (c0,c1);  (d0,d1) += (a0,a1).
+B2_DEVINL void ffma2(float& d0, float& d1, float a0, float a1, float b, float c0, float c1) {
+  asm("{\n\t.reg .b64 ra, rb, rc, rd;\n\t"
+      "mov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %4};\n\tmov.b64 rc, {%5, %6};\n\t"
+      "fma.rn.f32x2 rd, ra, rb, rc;\n\tmov.b64 {%0, %1}, rd;\n\t}"
+      : "=f"(d0), "=f"(d1) : "f"(a0), "f"(a1), "f"(b), "f"(c0), "f"(c1));
+}
+B2_DEVINL void fadd2(float& d0, float& d1, float a0, float a1) {
+  asm("{\n\t.reg .b64 ra, rd;\n\t"
+      "mov.b64 ra, {%2, %3};\n\tmov.b64 rd, {%0, %1};\n\t"
+      "add.rn.f32x2 rd, rd, ra;\n\tmov.b64 {%0, %1}, rd;\n\t}"
+      : "+f"(d0), "+f"(d1) : "f"(a0), "f"(a1));
+}
+
 __global__ void __launch_bounds__(TC_THREADS, 1)
 prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                        const __grid_constant__ CUtensorMap tmV, const TcAttnParams pin) {
@@ -223,7 +238,7 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
       const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
       const float corr = ex2_approx(m_run - m_use);               // m_run = -inf -> 0
       // ---- pass 2: P = exp2(s*scale - m), row sum, fp16 P into the swizzled A-operand layout ----
-      float ls = 0.f;
+      float ls = 0.f, ls1 = 0.f;
 #pragma unroll 1
       for (int c = 0; c < TC_BN / 16; ++c) {
         uint32_t v[16];
@@ -233,15 +248,17 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         const bool full = c * 16 + 15 <= lim;
 #pragma unroll
         for (int i = 0; i < 16; i += 2) {
-          float e0 = ex2_approx(fmaf(__uint_as_float(v[i]), p.scale_log2, -m_use));
-          float e1 = ex2_approx(fmaf(__uint_as_float(v[i + 1]), p.scale_log2, -m_use));
+          float x0, x1;
+          ffma2(x0, x1, __uint_as_float(v[i]), __uint_as_float(v[i + 1]), p.scale_log2, -m_use, -m_use);
+          float e0 = ex2_approx(x0);
+          float e1 = ex2_approx(x1);
           if (!full) {
             if (c * 16 + i > lim) e0 = 0.f;
             if (c * 16 + i + 1 > lim) e1 = 0.f;
           }
           // (row sum in fp32 of the unrounded values, as in the mma.sync kernel: converting the fp16 P back
           //  costs one XU-pipe op per element, and XU -- ex2 + conversions -- is this kernel's busiest pipe)
-          ls += e0 + e1;
+          fadd2(ls, ls1, e0, e1);
           pk[i >> 1] = f2_to_h2(e0, e1);
         }
         // keys c*16 .. c*16+15 = atom column c/4, 16-byte chunks (c%4)*2, +1 of this row
@@ -257,7 +274,7 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) { mbar_arrive(&s_empty[grp]); mbar_arrive(&p_full[grp]); }
-      l_run = l_run * corr + ls;
+      l_run = l_run * corr + (ls + ls1);
       m_run = m_new;
       // ---- O = O*corr + P V  (the other group's softmax runs while this PV product is in flight) ----
       mbar_wait(&pv_full[grp], ph);
@@ -268,7 +285,9 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         tmem_ld_32x16(to + c * 16, v);
         tmem_ld_wait();
 #pragma unroll
-        for (int i = 0; i < 16; ++i) o[c * 16 + i] = fmaf(o[c * 16 + i], corr, __uint_as_float(v[i]));
+        for (int i = 0; i < 16; i += 2)
+          ffma2(o[c * 16 + i], o[c * 16 + i + 1], o[c * 16 + i], o[c * 16 + i + 1], corr, __uint_as_float(v[i]),
+                __uint_as_float(v[i + 1]));
       }
       tc_fence_before();
       __syncwarp();
