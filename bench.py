@@ -168,6 +168,31 @@ def cpu_reference_run(model: str, prompt: int, new: int, steps: int, warmup: int
                 ms_per_step=t_full * 1e3, prefill_tokens_per_s=1 / pre_tok, decode_tokens_per_s=1 / dec_tok)
 
 
+def grpc_cpu_pipeline_run(steps: int = 3, warmup: int = 3) -> dict:
+    """BASELINE.json configs[0], the CPU arm north_star asks to be timed beside the GPU pipeline: GPT-2 small
+    fp32 in two layer-range stage servers over localhost gRPC (conventions of Code/gRPC/server.py:13-19 and
+    client.py:7-11), 128-token synthetic prompt, 32 greedy tokens, on this box's host cores."""
+    from oracle import grpc_stages
+    r = grpc_stages.timed_run("gpt2-small", 2, 128, 32, steps=steps, warmup=warmup)
+    return {k: r[k] for k in ("value", "unit", "cores", "kind", "prefill_tokens_per_s", "decode_tokens_per_s", "sample")}
+
+
+def grpc_config_on_gpu(torch, b2, dev, steps: int = 3, warmup: int = 3) -> dict:
+    """The same configs[0] workload (GPT-2 small, two layer-range stages, 128-token prompt + 32 greedy tokens)
+    through this repo's public API on one GPU, W8A8, host prompt in / host tokens out every generation."""
+    pipe = b2.Pipeline.load("gpt2", n_stages=2, devices=[dev, dev], seed=0, fast_init=True)
+    ids = torch.randint(0, pipe.cfg.vocab, (128,), generator=torch.Generator().manual_seed(1234), dtype=torch.int64).pin_memory()
+    ts = []
+    for i in range(warmup + steps):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        out = pipe.generate(ids, max_new_tokens=32, chunk=128).cpu()
+        ts.append(time.perf_counter() - t0)
+    t = statistics.median(ts[warmup:])
+    return {"value": 160 / t, "unit": UNIT, "ms_per_generation": t * 1e3,
+            "workload": "gpt2 (124M) W8A8, 2 layer-range stages on one GPU, 128-token prompt + 32 greedy tokens, host ids in / host tokens out"}
+
+
 def run_reference(a):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -180,6 +205,11 @@ def run_reference(a):
             "prefill_tokens_per_s": r["prefill_tokens_per_s"], "decode_tokens_per_s": r["decode_tokens_per_s"],
             "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    if not a.no_cpu_baseline:
+        try:
+            line["cpu_grpc_pipeline"] = grpc_cpu_pipeline_run()
+        except Exception as e:
+            line["cpu_grpc_pipeline"] = {"value": None, "sample": f"failed: {type(e).__name__}: {e}"}
     print(json.dumps(line), flush=True)
 
 
@@ -340,6 +370,12 @@ def run_ours(a):
             except Exception as e:   # the baseline must not take the GPU number down with it
                 line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "reference",
                                         "sample": f"failed: {type(e).__name__}: {e}"}
+            # configs[0]: the CPU gRPC stage pipeline, and the same workload through the GPU path, side by side
+            try:
+                line["cpu_grpc_pipeline"] = grpc_cpu_pipeline_run()
+                line["cpu_grpc_pipeline"]["same_workload_on_gpu"] = grpc_config_on_gpu(torch, b2, dev)
+            except Exception as e:
+                line.setdefault("cpu_grpc_pipeline", {})["error"] = f"{type(e).__name__}: {e}"
         print(json.dumps(line), flush=True)
     if dist is not None:
         dist.barrier()
