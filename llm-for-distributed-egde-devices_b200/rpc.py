@@ -366,3 +366,30 @@ class Client:
 
     def close(self):
         self.channel.close()
+
+
+# ------------------------------------------------------------------------------------------------
+# REST twin (Code/gRPC/rest_api.py:6-15: a FastAPI app, one JSON object per call, uvicorn on 0.0.0.0:8000)
+# ------------------------------------------------------------------------------------------------
+def rest_app(generate_servicer: GenerateServicer):
+    """FastAPI app over the same GenerateServicer: `GET /` -> {"model", "current_time"} (the reference's
+    endpoint, with the model name beside the time stamp), `POST /generate` with the GenerateRequest fields as
+    JSON -> the GenerateReply fields as JSON.  Run it like the reference does: ``uvicorn.run(app,
+    host="0.0.0.0", port=8000)``."""
+    from fastapi import Body, FastAPI, HTTPException
+    app = FastAPI()
+
+    @app.get("/")
+    def status():
+        return {"model": generate_servicer.pipe.cfg.name, "current_time": time.strftime("%Y-%m-%d %H:%M:%S")}
+
+    @app.post("/generate")
+    def generate(req: dict = Body(...)):
+        unknown = set(req) - set(_GEN_DEFAULTS)
+        if unknown:
+            raise HTTPException(status_code=422, detail=f"unknown fields: {sorted(unknown)}")
+        try:
+            return decode_generate_reply(generate_servicer.generate(encode_generate_request(**req)))
+        except (ValueError, TypeError) as e:
+            raise HTTPException(status_code=400, detail=str(e))
+    return app

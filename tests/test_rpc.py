@@ -124,6 +124,72 @@ def test_stage_service_over_localhost_with_a_stand_in_stage():
         s0.stop(0), s1.stop(0)
 
 
+class _FakePipe:
+    """generate() appends max_new_tokens copies of (last id + 1); enough to see every field arrive."""
+    cfg = types.SimpleNamespace(name="fake-model")
+    stages = [types.SimpleNamespace(device="cpu")]
+
+    def generate(self, ids, max_new_tokens=32, **kw):
+        self.kw = kw
+        return torch.cat([ids, torch.full((max_new_tokens,), int(ids[-1]) + 1)])
+
+
+def test_generate_service_and_rest_twin_with_a_stand_in_pipeline(monkeypatch):
+    import json
+    import socket
+    import threading
+    import urllib.error
+    import urllib.request
+    import uvicorn
+    monkeypatch.setattr(torch.cuda, "synchronize", lambda *a, **k: None)
+    pipe = _FakePipe()
+    sv = rpc.GenerateServicer(pipe)
+    server, port = rpc.serve(generate_servicer=sv, port=0)
+    try:
+        c = rpc.Client(f"127.0.0.1:{port}")
+        r = c.generate([4, 5, 6], max_new_tokens=3)
+        assert r["output_ids"] == [4, 5, 6, 7, 7, 7] and pipe.kw == {} and r["seconds"] > 0
+        assert abs(r["tokens_per_second"] - 6 / r["seconds"]) < 1e-6          # prompt + new, as models_quant_updated.py:95-96
+        c.generate([1], max_new_tokens=1, do_sample=True, temperature=0.7, top_p=0.9, seed=2)
+        assert pipe.kw == dict(do_sample=True, temperature=0.7, top_k=50, top_p=0.9, repetition_penalty=1.0, seed=2)
+        import grpc
+        with pytest.raises(grpc.RpcError) as e:
+            c.generate([], prompt="text needs a tokenizer")
+        assert e.value.code() == grpc.StatusCode.INVALID_ARGUMENT
+        c.close()
+    finally:
+        server.stop(0)
+    # REST twin on an ephemeral port
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        hport = s.getsockname()[1]
+    us = uvicorn.Server(uvicorn.Config(rpc.rest_app(sv), host="127.0.0.1", port=hport, log_level="error"))
+    th = threading.Thread(target=us.run, daemon=True)
+    th.start()
+    try:
+        import time
+        for _ in range(200):
+            if us.started:
+                break
+            time.sleep(0.05)
+        base = f"http://127.0.0.1:{hport}"
+        st = json.load(urllib.request.urlopen(base + "/"))
+        assert st["model"] == "fake-model" and len(st["current_time"]) == 19
+
+        def post(body):
+            rq = urllib.request.Request(base + "/generate", data=json.dumps(body).encode(), headers={"Content-Type": "application/json"})
+            return json.load(urllib.request.urlopen(rq))
+        r = post({"input_ids": [9, 10], "max_new_tokens": 2})
+        assert r["output_ids"] == [9, 10, 11, 11] and r["tokens_per_second"] > 0
+        for bad, code in (({"input_ids": [1], "num_beams": 4}, 422), ({"input_ids": []}, 400)):
+            with pytest.raises(urllib.error.HTTPError) as e:
+                post(bad)
+            assert e.value.code == code
+    finally:
+        us.should_exit = True
+        th.join(timeout=10)
+
+
 # ---- GPU ---------------------------------------------------------------------------------------
 @pytest.mark.gpu
 def test_gpu_stages_and_generate_behind_grpc_match_direct_calls():
