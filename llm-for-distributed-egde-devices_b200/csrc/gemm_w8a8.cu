@@ -180,7 +180,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (KIND == KIND_F16) {
           if (row_ok && col0 < p.N) {
             float* op = p.out_f32 + (long long)row * p.ldo + col0;
-            if (col0 + 32 <= p.N) {
+            if (col0 + 32 <= p.N && (p.ldo & 3) == 0) {   // 128-bit stores need a 16-byte aligned row pitch
 #pragma unroll
               for (int j = 0; j < 32; j += 4)
                 *reinterpret_cast<uint4*>(op + j) = make_uint4(r[j], r[j + 1], r[j + 2], r[j + 3]);
@@ -582,7 +582,7 @@ static int launch_gemv_f16(const __half* X, const __half* W, float* out, int M, 
 int lm_head(const void* x, const void* W, float* logits, int M, int V, int d, cudaStream_t st) {
   if (M == 0 || V == 0) return OK;
   if (!x || !W || !logits) return ERR_NULL_PTR;
-  if (M < 0 || V < 0 || d <= 0 || (d & 7) || (V & 3)) return ERR_BAD_SHAPE;
+  if (M < 0 || V < 0 || d <= 0 || (d & 7)) return ERR_BAD_SHAPE;      // any V: GPT-2's vocabulary is 50257
   auto mis = [](const void* q) { return q && (reinterpret_cast<uintptr_t>(q) & 15); };
   if (mis(x) || mis(W) || mis(logits)) return ERR_BAD_ALIGN;
   if (M <= GEMV_MAX_M) {

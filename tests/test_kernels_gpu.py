@@ -272,6 +272,23 @@ def test_embed_lm_head_argmax():
         assert np.array_equal(n(am), n(logits).argmax(-1))
 
 
+@pytest.mark.parametrize("V", [1001, 50257])
+def test_lm_head_argmax_sample_any_vocabulary_size(V):
+    """GPT-2's vocabulary (50257) is odd: the logits row pitch is then not a multiple of 16 bytes."""
+    r = rng(13)
+    d = 64
+    table = (0.16 * r.standard_normal((V, d))).astype(np.float16)
+    for M in (1, 3, 8, 9, 140):
+        x = r.standard_normal((M, d)).astype(np.float16)
+        logits = ops.lm_head(t(x), t(table))
+        ref = O.lm_head(x, table)
+        assert logits.shape == (M, V) and np.abs(n(logits) - ref).max() <= 1e-3 * np.abs(ref).max()
+        assert np.array_equal(n(ops.argmax(logits)), n(logits).argmax(-1))
+    got = ops.sample(logits[:3], temperature=0.9, top_k=40, top_p=0.95, seed=3, step=7)     # rows at an odd pitch
+    lg = n(logits)
+    assert [int(x) for x in got] == [O.sample_det(lg[b], np.zeros((0,), np.int64), 0.9, 40, 0.95, 1.0, 3, 7, b) for b in range(3)]
+
+
 def test_embed_with_positions_exact():
     r = rng(12)
     V, d, P = 300, 768, 64
