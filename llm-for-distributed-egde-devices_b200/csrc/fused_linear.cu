@@ -91,6 +91,19 @@ B2_DEVINL float fl_block_max(float v, float* sh) {
   return t;
 }
 
+// D[16x8] += A[16x32] * B[32x8], int8 x int8 -> int32 (exact: the order of the k terms does not matter)
+B2_DEVINL void fl_mma_s8(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
+               : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+// Token batches of 2..8 (MT > 1) stream the weights through mma.sync instead of dp4a -- see section 4b.
+constexpr int FL_PART_BYTES = 2 * FL_WARPS * 32 * 16;    // two buffers of per-warp partial accumulators
+constexpr int FL_XS_PAD = 64;                            // row pitch K + 64: the 8 token rows of a B fragment hit distinct banks
+__host__ __device__ constexpr size_t fl_act_bytes(int MT, int K) {
+  return MT > 1 ? (size_t)FL_PART_BYTES + (((size_t)MT * (K + FL_XS_PAD) + 127) & ~size_t(127)) : (((size_t)MT * K + 127) & ~size_t(127));
+}
+
 // y[0..7] of 8-element chunk `ch` of one row, in the pinned operation order.
 template <int XK>
 B2_DEVINL void fl_load_y(const FusedParams& p, const void* xrow, int ch, float r, float mean, float (&y)[8]) {
@@ -144,12 +157,21 @@ B2_DEVINL void fused_phase(const FusedParams& p, uint8_t* xs, SYNC sync_fn, bool
   const int K = p.K, kvec = K >> 4, nchunk = K >> 3;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int F = p.N >> 1;
+  constexpr bool TCM = MT > 1;                         // 2..8 tokens: tensor-core stream (section 4b)
+  uint8_t* const part = xs;                            // TCM: partial accumulators of the 16 warps, double-buffered
+  if (TCM) xs += FL_PART_BYTES;
+  const int XS = TCM ? K + FL_XS_PAD : K;              // pitch of a quantised activation row in shared memory
+  const int g8 = lane >> 2, t4 = lane & 3;             // mma fragment coordinates of this lane
   constexpr int STEP = FL_UNR * 32;                    // 16-byte vectors per row per batch
-  const int NB = (kvec + STEP - 1) / STEP;             // batches per work item
+  // batches per work item.  TCM: a unit's K is dealt out to the 16 warps in 64-byte pieces
+  const int NB = TCM ? (((kvec + 3) >> 2) + FL_WARPS * FL_UNR - 1) / (FL_WARPS * FL_UNR) : (kvec + STEP - 1) / STEP;
   // A work item = the two weight rows one warp reduces together: two adjacent output columns
   // (O_F16), the gate/up rows of one MLP column (O_GATED), or a rotary pair i, i+hd/2 (O_QKV).
+  // TCM: a work UNIT = 8 consecutive items = the 16 rows of one mma A tile (rows 0-7: the items' first
+  // rows, 8-15: their second rows); the whole CTA works on one unit, each warp on 1/16 of its K.
   const int items_total = (OKIND == O_F16) ? (p.N + 1) / 2 : F;
-  const int stride = gridDim.x * FL_WARPS;
+  const int work_total = TCM ? (items_total + 7) >> 3 : items_total;
+  const int stride = TCM ? gridDim.x : gridDim.x * FL_WARPS;
   const int half_hd = (OKIND == O_QKV) ? (p.hd >> 1) : 1;
   struct Cur { int it, j; const int8_t* r0; const int8_t* r1; };
   // Item schedule: warp w of CTA c takes items c*16 + w + k*stride.  Two "fairer" schedules were
@@ -159,20 +181,23 @@ B2_DEVINL void fused_phase(const FusedParams& p, uint8_t* xs, SYNC sync_fn, bool
   // pre-wait loads are fully exposed, whereas CTAs that skip the last round hand their SM over early.
   auto set_rows = [&](Cur& c) {
     int n0, n1;
-    if (OKIND == O_GATED) { n0 = c.it; n1 = F + c.it; }
-    else if (OKIND == O_QKV) { const int hq = c.it / half_hd; n0 = hq * p.hd + (c.it - hq * half_hd); n1 = n0 + half_hd; }
-    else { n0 = 2 * c.it; n1 = min(n0 + 1, p.N - 1); }
+    const int item = TCM ? min(c.it * 8 + g8, items_total - 1) : c.it;    // TCM: lane (g, t) streams the rows of item 8*unit + g
+    if (OKIND == O_GATED) { n0 = item; n1 = F + item; }
+    else if (OKIND == O_QKV) { const int hq = item / half_hd; n0 = hq * p.hd + (item - hq * half_hd); n1 = n0 + half_hd; }
+    else { n0 = 2 * item; n1 = min(n0 + 1, p.N - 1); }
     c.r0 = p.W + (long long)n0 * K;
     c.r1 = p.W + (long long)n1 * K;
   };
   auto advance = [&](Cur& c) {
-    if (++c.j == NB) { c.j = 0; c.it += stride; if (c.it < items_total) set_rows(c); }
+    if (++c.j == NB) { c.j = 0; c.it += stride; if (c.it < work_total) set_rows(c); }
   };
   auto load_batch = [&](uint4 (&dst)[FL_UNR][FL_ROWS], const Cur& c) {
-    if (c.it < items_total) {
+    if (c.it < work_total) {
 #pragma unroll
       for (int u = 0; u < FL_UNR; ++u) {
-        const int idx = lane + c.j * STEP + u * 32;
+        // TCM: 64-byte piece (warp + 16*(u + 4j)) of the row, this lane's 16 bytes of it: one warp-wide
+        // load covers 8 rows x 64 contiguous bytes, the 16 warps together 1 KB of each row
+        const int idx = TCM ? 4 * (warp + FL_WARPS * (u + FL_UNR * c.j)) + t4 : lane + c.j * STEP + u * 32;
         const bool ok = idx < kvec;
         dst[u][0] = ok ? ld_nc_v4(c.r0 + idx * 16) : make_uint4(0, 0, 0, 0);
         dst[u][1] = ok ? ld_nc_v4(c.r1 + idx * 16) : make_uint4(0, 0, 0, 0);
@@ -186,8 +211,8 @@ B2_DEVINL void fused_phase(const FusedParams& p, uint8_t* xs, SYNC sync_fn, bool
   tl_mark(TLK, 6);
   uint4 w[FL_UNR][FL_ROWS], w2[FL_UNR][FL_ROWS];
   Cur cc;
-  cc.it = blockIdx.x * FL_WARPS + warp; cc.j = 0; cc.r0 = p.W; cc.r1 = p.W;
-  if (cc.it < items_total) set_rows(cc);
+  cc.it = TCM ? blockIdx.x : blockIdx.x * FL_WARPS + warp; cc.j = 0; cc.r0 = p.W; cc.r1 = p.W;
+  if (cc.it < work_total) set_rows(cc);
   Cur lc = cc;
   load_batch(w, lc); advance(lc);
   load_batch(w2, lc); advance(lc);
@@ -203,8 +228,8 @@ B2_DEVINL void fused_phase(const FusedParams& p, uint8_t* xs, SYNC sync_fn, bool
   // before the dependency wait, so the prologue's critical path is one L2 read of x plus two block
   // reductions (fast path: rows of up to FP_MAXC*256*8 = 6144 elements held in registers).
   constexpr int FP_MAXC = 3;
-  const bool fast = (XK != X_Y32) && (nchunk <= FP_MAXC * FL_THREADS);
-  uint8_t* aux = xs + (((size_t)MT * K + 127) & ~size_t(127));
+  const bool fast = !TCM && (XK != X_Y32) && (nchunk <= FP_MAXC * FL_THREADS);
+  uint8_t* aux = xs + (((size_t)MT * XS + 127) & ~size_t(127));
   __half* sg = reinterpret_cast<__half*>(aux);                         // gamma [K]
   __half* sb = sg + K;                                                 // beta  [K]
   float* ssm = reinterpret_cast<float*>(aux + (size_t)4 * K);          // smooth [K]
@@ -227,9 +252,88 @@ B2_DEVINL void fused_phase(const FusedParams& p, uint8_t* xs, SYNC sync_fn, bool
     __syncthreads();
   }
   // ---- 3. activation prologue: quantise the M rows into shared memory ------------------------
+  if constexpr (TCM) {
+    // Token batches: the rows are quantised SIDE BY SIDE, 16/MT warps per row, with two CTA-wide
+    // reductions in total (one row after the other cost 1.5-2.4 us of dependent L2 latency and four
+    // barriers per row: 12-19 us per launch at 8 tokens).  Three passes over the (L2-resident) row:
+    // moments, absmax, quantise; the fp64 moment sums do not depend on the order of the terms.
+    __shared__ double shd1[FL_WARPS];
+    constexpr int WPR = FL_WARPS / MT, RT = WPR * 32;
+    const int m = warp / WPR, tr = (warp - m * WPR) * 32 + lane;
+    const bool rowok = m < p.M;
+    uint2* qrow = reinterpret_cast<uint2*>(xs + (size_t)m * XS);
+    const void* xrow = (XK == X_Y32)
+        ? static_cast<const void*>(reinterpret_cast<const float*>(p.x) + (long long)m * p.x_ld)
+        : static_cast<const void*>(reinterpret_cast<const __half*>(p.x) + (long long)m * p.x_ld);
+    float r = 0.f, mean = 0.f, amax = 0.f;
+    if (XK == X_RMS || XK == X_LN) {
+      double s1 = 0.0, s2 = 0.0;
+      if (rowok) {
+        for (int ch = tr; ch < nchunk; ch += RT) {
+          const uint4 u = ld_cg_v4(reinterpret_cast<const __half*>(xrow) + ch * 8);
+          const uint32_t* pu = &u.x;
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float2 f = h2_to_f2(pu[e]);
+            const double d0 = (double)f.x, d1 = (double)f.y;
+            s2 += d0 * d0; s2 += d1 * d1;
+            if (XK == X_LN) { s1 += d0; s1 += d1; }
+          }
+        }
+      }
+      s2 = warp_sum_d(s2);
+      if (XK == X_LN) s1 = warp_sum_d(s1);
+      if (lane == 0) { shd[warp] = s2; shd1[warp] = s1; }
+      __syncthreads();
+      double ss = 0.0, sm = 0.0;
+#pragma unroll
+      for (int i = 0; i < WPR; ++i) { ss += shd[m * WPR + i]; sm += shd1[m * WPR + i]; }
+      float var;
+      if (XK == X_LN) {
+        const double md = sm / (double)K;
+        double vd = ss / (double)K - md * md;
+        vd = vd > 0.0 ? vd : 0.0;
+        mean = (float)md; var = (float)vd;
+      } else {
+        var = (float)(ss / (double)K);
+      }
+      r = div_rn(1.0f, __fsqrt_rn(add_rn(var, p.eps)));
+    }
+    if (XK == X_Y32) {
+      amax = rowok ? __ldcg(p.x_amax + m) : 0.f;
+    } else {
+      if (rowok) {
+        for (int ch = tr; ch < nchunk; ch += RT) {
+          float y[8];
+          fl_load_y<XK>(p, xrow, ch, r, mean, y);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) amax = fmaxf(amax, fabsf(y[j]));
+        }
+      }
+      amax = warp_max(amax);
+      if (lane == 0) shf[warp] = amax;
+      __syncthreads();
+      amax = 0.f;
+#pragma unroll
+      for (int i = 0; i < WPR; ++i) amax = fmaxf(amax, shf[m * WPR + i]);
+    }
+    const bool nz = amax > 0.0f;
+    const float inv = nz ? div_rn(127.0f, amax) : 0.0f;
+    if (tr == 0) s_scale[m] = nz ? div_rn(amax, 127.0f) : 0.0f;
+    for (int ch = tr; ch < nchunk; ch += RT) {
+      uint2 o = make_uint2(0, 0);
+      if (rowok) {
+        float y[8];
+        fl_load_y<XK>(p, xrow, ch, r, mean, y);
+        o.x = pack4(quant1(y[0], inv), quant1(y[1], inv), quant1(y[2], inv), quant1(y[3], inv));
+        o.y = pack4(quant1(y[4], inv), quant1(y[5], inv), quant1(y[6], inv), quant1(y[7], inv));
+      }
+      qrow[ch] = o;
+    }
+  } else
 #pragma unroll 1
   for (int m = 0; m < MT; ++m) {
-    uint2* qrow = reinterpret_cast<uint2*>(xs + (size_t)m * K);
+    uint2* qrow = reinterpret_cast<uint2*>(xs + (size_t)m * XS);
     if (m >= p.M) {
       for (int ch = threadIdx.x; ch < nchunk; ch += FL_THREADS) qrow[ch] = make_uint2(0, 0);
       continue;
@@ -375,7 +479,64 @@ B2_DEVINL void fused_phase(const FusedParams& p, uint8_t* xs, SYNC sync_fn, bool
   }
   __syncthreads();
   tl_mark(TLK, 3);
-  // ---- 4. persistent weight stream: two batches always in flight per lane ----------------------
+  // ---- epilogue of ONE (item, token): v0 / v1 = the int32 sums of the item's two rows ------------
+  auto epi_tok = [&](int it, int m, int v0i, int v1i) {
+    if (OKIND == O_F16) {
+      __half* out = reinterpret_cast<__half*>(p.out);
+#pragma unroll
+      for (int r = 0; r < FL_ROWS; ++r) {
+        const int n = 2 * it + r;
+        if (n < p.N) {
+          const float ws = p.w_scale[n];
+          const long long off = (long long)m * p.N + n;
+          float v = mul_rn(mul_rn((float)(r ? v1i : v0i), s_scale[m]), ws);
+          if (p.bias) v = add_rn(v, __half2float(p.bias[n]));
+          if (p.residual) v = add_rn(v, __half2float(__ushort_as_half(__ldcg(reinterpret_cast<const unsigned short*>(p.residual + off)))));
+          out[off] = __float2half_rn(v);
+        }
+      }
+    } else if (OKIND == O_QKV) {
+      __half* out = reinterpret_cast<__half*>(p.out);
+      const int q_head = it / half_hd, q_i = it - q_head * half_hd;
+      const int n0 = q_head * p.hd + q_i, n1 = n0 + half_hd;
+      float v0 = mul_rn(mul_rn((float)v0i, s_scale[m]), p.w_scale[n0]);
+      float v1 = mul_rn(mul_rn((float)v1i, s_scale[m]), p.w_scale[n1]);
+      if (p.bias) { v0 = add_rn(v0, __half2float(p.bias[n0])); v1 = add_rn(v1, __half2float(p.bias[n1])); }
+      __half h0 = __float2half_rn(v0), h1 = __float2half_rn(v1);     // the fp16 qkv of the unfused path
+      const int pos = p.positions[m];
+      if (q_head < p.H + p.KV && p.use_rope) {
+        const float x1 = __half2float(h0), x2 = __half2float(h1);
+        const float c = p.cosT[(long long)pos * half_hd + q_i], sn = p.sinT[(long long)pos * half_hd + q_i];
+        h0 = __float2half_rn(sub_rn(mul_rn(x1, c), mul_rn(x2, sn)));
+        h1 = __float2half_rn(add_rn(mul_rn(x2, c), mul_rn(x1, sn)));
+      }
+      if (q_head < p.H) {
+        out[(long long)m * p.N + n0] = h0;
+        out[(long long)m * p.N + n1] = h1;
+      } else {
+        const bool isk = q_head < p.H + p.KV;
+        const int kvh = isk ? q_head - p.H : q_head - p.H - p.KV;
+        const int row = p.seq_ids ? p.seq_ids[m] : p.seq0;
+        __half* dst = (isk ? p.kcache : p.vcache) + (((long long)row * p.KV + kvh) * p.Smax + pos) * p.hd;
+        dst[q_i] = h0;
+        dst[q_i + half_hd] = h1;
+      }
+    } else {
+      float* out = reinterpret_cast<float*>(p.out);
+      float vg = mul_rn(mul_rn((float)v0i, s_scale[m]), p.w_scale[it]);
+      float vu = mul_rn(mul_rn((float)v1i, s_scale[m]), p.w_scale[F + it]);
+      if (p.bias) { vg = add_rn(vg, __half2float(p.bias[it])); vu = add_rn(vu, __half2float(p.bias[F + it])); }
+      const float g = __half2float(__float2half_rn(vg));      // the fp16 rounding of the unfused path
+      const float uu = __half2float(__float2half_rn(vu));
+      const float a = (p.act == 0) ? silu_det(g) : gelu_new_det(g);
+      float y = mul_rn(a, uu);
+      if (p.out_smooth) y = mul_rn(y, p.out_smooth[it]);
+      out[(long long)m * F + it] = y;
+      atomicMax(reinterpret_cast<int*>(p.out_amax + m), __float_as_int(fabsf(y)));   // |y| >= 0: int order == float order
+    }
+  };
+  if constexpr (!TCM) {
+  // ---- 4a. one token: persistent dp4a weight stream, two batches always in flight per lane ------
   int acc[FL_ROWS][MT];
 #pragma unroll
   for (int r = 0; r < FL_ROWS; ++r)
@@ -408,84 +569,12 @@ B2_DEVINL void fused_phase(const FusedParams& p, uint8_t* xs, SYNC sync_fn, bool
   // in one lane while the weight stream waits.
   int res[FL_ROWS][MT];
   int res_it = -1, parked = 0;
-  auto epilogue_lane = [&](int it) {
-    if (OKIND == O_F16) {
-      __half* out = reinterpret_cast<__half*>(p.out);
-#pragma unroll
-      for (int r = 0; r < FL_ROWS; ++r) {
-        const int n = 2 * it + r;
-        if (n < p.N) {
-          const float ws = p.w_scale[n];
-          const float bv = p.bias ? __half2float(p.bias[n]) : 0.f;
-#pragma unroll
-          for (int m = 0; m < MT; ++m) {
-            if (m < p.M) {
-              const long long off = (long long)m * p.N + n;
-              float v = mul_rn(mul_rn((float)res[r][m], s_scale[m]), ws);
-              if (p.bias) v = add_rn(v, bv);
-              if (p.residual) v = add_rn(v, __half2float(__ushort_as_half(__ldcg(reinterpret_cast<const unsigned short*>(p.residual + off)))));
-              out[off] = __float2half_rn(v);
-            }
-          }
-        }
-      }
-    } else if (OKIND == O_QKV) {
-      __half* out = reinterpret_cast<__half*>(p.out);
-      const int q_head = it / half_hd, q_i = it - q_head * half_hd;
-      const int n0 = q_head * p.hd + q_i, n1 = n0 + half_hd;
-      const float ws0 = p.w_scale[n0], ws1 = p.w_scale[n1];
-      const float b0 = p.bias ? __half2float(p.bias[n0]) : 0.f, b1 = p.bias ? __half2float(p.bias[n1]) : 0.f;
-#pragma unroll
-      for (int m = 0; m < MT; ++m) {
-        if (m < p.M) {
-          float v0 = mul_rn(mul_rn((float)res[0][m], s_scale[m]), ws0);
-          float v1 = mul_rn(mul_rn((float)res[1][m], s_scale[m]), ws1);
-          if (p.bias) { v0 = add_rn(v0, b0); v1 = add_rn(v1, b1); }
-          __half h0 = __float2half_rn(v0), h1 = __float2half_rn(v1);     // the fp16 qkv of the unfused path
-          const int pos = p.positions[m];
-          if (q_head < p.H + p.KV && p.use_rope) {
-            const float x1 = __half2float(h0), x2 = __half2float(h1);
-            const float c = p.cosT[(long long)pos * half_hd + q_i], sn = p.sinT[(long long)pos * half_hd + q_i];
-            h0 = __float2half_rn(sub_rn(mul_rn(x1, c), mul_rn(x2, sn)));
-            h1 = __float2half_rn(add_rn(mul_rn(x2, c), mul_rn(x1, sn)));
-          }
-          if (q_head < p.H) {
-            out[(long long)m * p.N + n0] = h0;
-            out[(long long)m * p.N + n1] = h1;
-          } else {
-            const bool isk = q_head < p.H + p.KV;
-            const int kvh = isk ? q_head - p.H : q_head - p.H - p.KV;
-            const int row = p.seq_ids ? p.seq_ids[m] : p.seq0;
-            __half* dst = (isk ? p.kcache : p.vcache) + (((long long)row * p.KV + kvh) * p.Smax + pos) * p.hd;
-            dst[q_i] = h0;
-            dst[q_i + half_hd] = h1;
-          }
-        }
-      }
-    } else {
-      float* out = reinterpret_cast<float*>(p.out);
-      const float wsg = p.w_scale[it], wsu = p.w_scale[F + it];
-      const float bg = p.bias ? __half2float(p.bias[it]) : 0.f, bu = p.bias ? __half2float(p.bias[F + it]) : 0.f;
-      const float osm = p.out_smooth ? p.out_smooth[it] : 1.0f;
-#pragma unroll
-      for (int m = 0; m < MT; ++m) {
-        if (m < p.M) {
-          float vg = mul_rn(mul_rn((float)res[0][m], s_scale[m]), wsg);
-          float vu = mul_rn(mul_rn((float)res[1][m], s_scale[m]), wsu);
-          if (p.bias) { vg = add_rn(vg, bg); vu = add_rn(vu, bu); }
-          const float g = __half2float(__float2half_rn(vg));      // the fp16 rounding of the unfused path
-          const float uu = __half2float(__float2half_rn(vu));
-          const float a = (p.act == 0) ? silu_det(g) : gelu_new_det(g);
-          float y = mul_rn(a, uu);
-          if (p.out_smooth) y = mul_rn(y, osm);
-          out[(long long)m * F + it] = y;
-          atomicMax(reinterpret_cast<int*>(p.out_amax + m), __float_as_int(fabsf(y)));   // |y| >= 0: int order == float order
-        }
-      }
-    }
-  };
   auto flush = [&]() {
-    if (res_it >= 0) epilogue_lane(res_it);
+    if (res_it >= 0) {
+#pragma unroll
+      for (int m = 0; m < MT; ++m)
+        if (m < p.M) epi_tok(res_it, m, res[0][m], res[1][m]);
+    }
     res_it = -1;
     parked = 0;
   };
@@ -519,6 +608,83 @@ B2_DEVINL void fused_phase(const FusedParams& p, uint8_t* xs, SYNC sync_fn, bool
   }
   tl_mark(TLK, 4);
   flush();
+  } else {
+  // ---- 4b. 2..8 tokens: the same register-double-buffered stream feeding mma.sync.m16n8k32 -------
+  // With dp4a a batch of 8 tokens costs 32 integer instructions and 8 shared-memory loads per 16 weight
+  // bytes per row, and the stream turns compute-bound (gate_up of Llama-2-7B: 45 us against 16 at one
+  // token).  Here the 16 rows of a unit are the M dimension of the tile and the tokens its N dimension:
+  // lane (g, t) holds 16 contiguous bytes of rows g and g+8, which are two k-slices of its A fragment
+  // for two MMAs (the k order inside a tile is free as long as A and B agree, and int32 accumulation
+  // is exact in any order: results stay bit-identical to the dp4a path), and the matching 16 bytes of
+  // token g's activation row are its B fragments: 1 shared load + 2 MMAs per 2 weight loads.
+  // The accumulator fragment is already one value per (row, token): no shuffle reduction.  The 16
+  // warps' partial sums (each warp has 1/16 of K) meet in shared memory; 64 threads add them up and
+  // run the epilogue of one (item, token) each while the others stream on.
+  int c4[4] = {0, 0, 0, 0};
+  int ui = 0;
+  // Deferred epilogue, as in 4a: the reduced sums of up to 8 units are parked in shared memory, then
+  // all 512 threads finish one (item, token) each, so the dependent scale loads, the SiLU and the
+  // stores of 8 units overlap instead of holding two warps -- and with them every unit's barrier -- back.
+  __shared__ int s_park[8][64][2];
+  const int unit0 = blockIdx.x;
+  auto flush_units = [&](int first_ui, int count) {       // units first_ui .. first_ui+count-1 (CTA-local numbering)
+    __syncthreads();
+    const int slot = threadIdx.x >> 6, e = threadIdx.x & 63;
+    if (slot < count) {
+      const int g = e >> 3, m = e & 7;
+      const int it = (unit0 + (first_ui + slot) * stride) * 8 + g;
+      if (it < items_total && m < p.M) epi_tok(it, m, s_park[slot][e][0], s_park[slot][e][1]);
+    }
+  };
+  auto consume = [&](const uint4 (&src)[FL_UNR][FL_ROWS], int j) {
+#pragma unroll
+    for (int u = 0; u < FL_UNR; ++u) {
+      const int q4 = 4 * (warp + FL_WARPS * (u + FL_UNR * j));
+      if (q4 < kvec) {                                   // warp-uniform
+        const int idx = q4 + t4;
+        uint4 b = make_uint4(0, 0, 0, 0);
+        if (g8 < MT && idx < kvec) b = *reinterpret_cast<const uint4*>(xs + (size_t)g8 * XS + (size_t)idx * 16);
+        fl_mma_s8(c4, src[u][0].x, src[u][1].x, src[u][0].y, src[u][1].y, b.x, b.y);
+        fl_mma_s8(c4, src[u][0].z, src[u][1].z, src[u][0].w, src[u][1].w, b.z, b.w);
+      }
+    }
+  };
+  auto finish_unit = [&](int unit) {
+    int4* pb = reinterpret_cast<int4*>(part) + (ui & 1) * (FL_WARPS * 32);
+    pb[warp * 32 + lane] = make_int4(c4[0], c4[1], c4[2], c4[3]);
+    c4[0] = c4[1] = c4[2] = c4[3] = 0;
+    ++ui;
+    // One barrier per unit: the buffer written now is read below and written again two units later,
+    // after every thread has passed the next unit's barrier.
+    __syncthreads();
+    if (threadIdx.x < 64) {
+      const int g = threadIdx.x >> 3, m = threadIdx.x & 7;          // accumulator (row g | g+8, token m) sits in lane 4g + m/2
+      const int* pi = reinterpret_cast<const int*>(pb) + (g * 4 + (m >> 1)) * 4 + (m & 1);
+      int v0 = 0, v1 = 0;
+#pragma unroll
+      for (int w_ = 0; w_ < FL_WARPS; ++w_) { v0 += pi[w_ * 128]; v1 += pi[w_ * 128 + 2]; }
+      s_park[(ui - 1) & 7][threadIdx.x][0] = v0;
+      s_park[(ui - 1) & 7][threadIdx.x][1] = v1;
+    }
+    if ((ui & 7) == 0) flush_units(ui - 8, 8);
+  };
+  auto step = [&](uint4 (&buf)[FL_UNR][FL_ROWS]) {
+    consume(buf, cc.j);
+    load_batch(buf, lc);
+    advance(lc);
+    const int unit = cc.it;
+    const bool last = cc.j == NB - 1;
+    advance(cc);
+    if (last) finish_unit(unit);
+  };
+  while (cc.it < work_total) {
+    step(w);
+    if (cc.it >= work_total) break;
+    step(w2);
+  }
+  tl_mark(TLK, 4);
+  if (ui & 7) flush_units(ui & ~7, ui & 7);
+  }
   tl_mark(TLK, 5);
   tl_flush(TLK, 0xFFu);
 }
@@ -583,7 +749,7 @@ static int fl_sm_count() {
 
 template <int MT, int XK, int OKIND>
 static int launch_fused(const FusedParams& pin, cudaStream_t st) {
-  size_t smem = ((size_t)MT * pin.K + 127) & ~size_t(127);
+  size_t smem = fl_act_bytes(MT, pin.K);
   if (XK != X_Y32 && (pin.K >> 3) <= 3 * FL_THREADS) smem += (size_t)8 * pin.K;   // gamma, beta (fp16) + smooth (fp32) staging
   if (smem > (size_t)FL_SMEM_FULL) return ERR_TOO_LARGE;
   const FusedParams& p = pin;
@@ -594,7 +760,7 @@ static int launch_fused(const FusedParams& pin, cudaStream_t st) {
     attr_set = true;
   }
   const int items = (OKIND == O_F16) ? (p.N + 1) / 2 : p.N / 2;
-  int grid = (items + FL_WARPS - 1) / FL_WARPS;
+  int grid = MT > 1 ? (items + 7) / 8 : (items + FL_WARPS - 1) / FL_WARPS;    // MT > 1: the whole CTA works on 8 items at a time
   const int cap = fl_sm_count() * FL_CTAS_PER_SM;                   // persistent: one 512-thread CTA per SM (grids of 104..140 CTAs measured slower)
   if (grid > cap) grid = cap;
   cudaLaunchConfig_t cfg = {};
@@ -718,7 +884,7 @@ static int desc_to_params(const b2_fused_desc* d, int M, int want_xk_mask, int w
 }
 
 static size_t phase_smem(int MT, int xk, int K) {
-  size_t smem = ((size_t)MT * K + 127) & ~size_t(127);
+  size_t smem = fl_act_bytes(MT, K);
   if (xk != X_Y32 && (K >> 3) <= 3 * FL_THREADS) smem += (size_t)8 * K;
   return smem;
 }

@@ -20,11 +20,14 @@ ap.add_argument("--model", default="llama-2-13b")
 ap.add_argument("--batch", type=int, default=32)
 ap.add_argument("--ctx", type=int, default=4000)
 ap.add_argument("--layers", type=int, default=2)
+ap.add_argument("--fuse-tail", type=int, default=-1, help="override Stage.fuse_tail (0/1)")
 a = ap.parse_args()
 full = b200stage.get_config(a.model)
 cfg = dataclasses.replace(full, n_layers=a.layers)
 dev = "cuda"
 st = Stage.load(cfg, 0, a.layers, first=False, last=False, device=dev, fast_init=True)
+if a.fuse_tail >= 0:
+    st.fuse_tail = bool(a.fuse_tail)
 B = a.batch
 cache = st.new_kv_cache(B, a.ctx + 64)
 cache.k.normal_()

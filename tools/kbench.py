@@ -21,6 +21,7 @@ ap.add_argument("--seq", type=int, default=2100)
 ap.add_argument("--m", type=int, default=1)
 ap.add_argument("--prefill", type=int, default=512)
 ap.add_argument("--nl", type=int, default=8)
+ap.add_argument("--chains", default="qaogd,qogd,qa,ao,og,gd,dq")
 a = ap.parse_args()
 dev = "cuda"
 cfg = b200stage.get_config(a.model)
@@ -89,6 +90,27 @@ t = timed(lambda: [ops.fused_linear(h, lw["wgu"], lw["s_gu"], x_kind=ops.X_RMS, 
 report("fused gate_up (norm+quant+GEMV+SiLU*up)", t, 2 * F * d)
 t = timed(lambda: [ops.fused_linear(y32, lw["wd"], lw["s_d"], x_kind=ops.X_Y32, x_amax=amax, residual=h, out=h2) for lw in L])
 report("fused down (requant+GEMV+residual)", t, d * F)
+
+
+def chain(parts):
+    """The real per-layer launch order (Stage._core, fused branch, no L2 hints), restricted to `parts`."""
+    for i, lw in enumerate(L):
+        if "q" in parts:
+            ops.fused_qkv(h, lw["wqkv"], lw["s_qkv"], qkv, cos, sin, pos, kc[i], vc[i], H, KV, hd, x_kind=ops.X_RMS,
+                          gamma=lw["ln1_g"], smooth=lw["sm_qkv"], seq_ids=seq)
+        if "a" in parts:
+            ops.decode_attn(qkv, kc[i], vc[i], lens, H, KV, hd, a.seq, hd ** -0.5, cfg.window, rows=seq, out=attn, workspace=ws)
+        if "o" in parts:
+            ops.fused_linear(attn, lw["wo"], lw["s_o"], x_kind=ops.X_PLAIN, smooth=lw["sm_o"], residual=h, out=h2, zero_amax=amax)
+        if "g" in parts:
+            ops.fused_linear(h2, lw["wgu"], lw["s_gu"], x_kind=ops.X_RMS, gamma=lw["ln2_g"], smooth=lw["sm_gu"], out=y32,
+                             out_kind=ops.O_GATED, out_smooth=lw["sm_d"], out_amax=amax)
+        if "d" in parts:
+            ops.fused_linear(y32, lw["wd"], lw["s_d"], x_kind=ops.X_Y32, x_amax=amax, residual=h2, out=h)
+
+
+for parts in a.chains.split(","):
+    report(f"chain [{parts}] per layer", timed(lambda: chain(parts)))
 ctr = torch.zeros((a.nl, 4), dtype=torch.int32, device=dev)
 
 

@@ -31,6 +31,7 @@ ap.add_argument("--model", default="llama-2-7b")
 ap.add_argument("--layers", type=int, default=4)
 ap.add_argument("--ctx", type=int, default=2100)
 ap.add_argument("--steps", type=int, default=3, help="decode steps recorded (the last one is printed)")
+ap.add_argument("--batch", type=int, default=1, help="sequences decoded together (one group)")
 ap.add_argument("--raw", default="", help="write the raw events of the printed step to this .npy")
 a = ap.parse_args()
 
@@ -43,7 +44,8 @@ cfg = b200stage.get_config(a.model)
 cfg = dataclasses.replace(cfg, n_layers=a.layers, name=f"{cfg.name}[{a.layers} layers]")
 dev = torch.device("cuda:0")
 torch.cuda.set_device(dev)
-pipe = DistPipeline.load(cfg, 0, 1, dev, max_rows=1, max_seq=a.ctx + 64)
+B = a.batch
+pipe = DistPipeline.load(cfg, 0, 1, dev, max_rows=B, max_seq=a.ctx + 64)
 lib = _abi.lib()
 EV = np.dtype([("t", "<u8"), ("tag", "<u4"), ("cta", "<u4")])
 
@@ -61,16 +63,17 @@ def dump():
 
 # fill the cache to ctx tokens (the values do not matter for timing), then decode
 ids = torch.randint(0, cfg.vocab, (a.ctx,), device=dev)
-pipe.prefill_stream([ids], 512)
-tok = [torch.zeros(1, dtype=torch.int64, device=dev)]
-pipe.decode_stream(tok, [[a.ctx]], [[0]], 4)          # graph capture + warm
+pipe.prefill_stream([ids] * B, 512)
+tok = [torch.zeros(B, dtype=torch.int64, device=dev)]
+rows = [list(range(B))]
+pipe.decode_stream(tok, [[a.ctx] * B], rows, 4)          # graph capture + warm
 torch.cuda.synchronize()
 dump()
 pos = a.ctx + 4
 for _ in range(a.steps):
     torch.cuda.synchronize()
     dump()
-    pipe.decode_stream(tok, [[pos]], [[0]], 1)
+    pipe.decode_stream(tok, [[pos] * B], rows, 1)
     pos += 1
 torch.cuda.synchronize()
 ev = dump()
