@@ -1,5 +1,5 @@
 """Small fixed workload for `ncu`: a few launches of the dominant kernels at Llama-2-7B shapes.
-usage: python tools/ncu_target.py [gemm|gemv|attn|pattn|all]"""
+usage: python tools/ncu_target.py [gemm|gemv|gemv8|attn|pattn|all]"""
 import os
 import sys
 
@@ -21,6 +21,13 @@ torch.cuda.synchronize()
 if what in ("gemv", "all"):
     h = torch.randn((1, d), dtype=torch.float16, device=dev)
     y32 = torch.empty((1, F), dtype=torch.float32, device=dev)
+    amax = torch.zeros((8,), dtype=torch.float32, device=dev)
+    for lw in L:
+        ops.fused_linear(h, lw["wgu"], lw["s_gu"], x_kind=ops.X_RMS, gamma=lw["ln2_g"], smooth=lw["sm_gu"], out=y32,
+                         out_kind=ops.O_GATED, out_smooth=lw["sm_d"], out_amax=amax)
+if what == "gemv8":       # the token-batch (mma.sync) variant of the same kernel, 8 tokens
+    h = torch.randn((8, d), dtype=torch.float16, device=dev)
+    y32 = torch.empty((8, F), dtype=torch.float32, device=dev)
     amax = torch.zeros((8,), dtype=torch.float32, device=dev)
     for lw in L:
         ops.fused_linear(h, lw["wgu"], lw["s_gu"], x_kind=ops.X_RMS, gamma=lw["ln2_g"], smooth=lw["sm_gu"], out=y32,
