@@ -47,6 +47,26 @@ def test_fused_norm_linear_exact(M, N, K, ln):
     assert np.array_equal(n(out).view(np.uint16), ref.view(np.uint16))
 
 
+@pytest.mark.parametrize("M", [2, 5, 8])
+@pytest.mark.parametrize("N,K", [(47360, 256), (45058, 208), (37890, 1040)])
+def test_fused_batch_stream_many_units_per_cta(M, N, K):
+    """The token-batch (mma.sync) stream with 10-20 sixteen-row units per CTA: both partial-sum buffers, several
+    full rounds of 8 parked units and a partial last round, a ragged last unit (N/2 not a multiple of 8), K not a
+    multiple of 64 (a 64-byte piece that only some lanes load) and K spanning two batches per unit.  Three runs
+    must agree bit for bit with the oracle (a shared-memory race would show as run-to-run differences)."""
+    r = np.random.default_rng(M + N + K)
+    x = (r.standard_normal((M, K)) * r.uniform(0.2, 3, (M, 1))).astype(np.float16)
+    g = (1 + 0.1 * r.standard_normal(K)).astype(np.float16)
+    sm = r.uniform(0.3, 3, K).astype(np.float32)
+    w, ws = _w(r, N, K)
+    q, s = O.norm_quant(x, g, None, sm, 1e-5)
+    ref, _ = O.gemm_w8a8(q, w, s, ws)
+    for _ in range(3):
+        out = torch.zeros((M, N), dtype=torch.float16, device=DEV)
+        ops.fused_linear(t(x), t(w), t(ws), x_kind=ops.X_RMS, gamma=t(g), smooth=t(sm), eps=1e-5, out=out)
+        assert np.array_equal(n(out).view(np.uint16), ref.view(np.uint16))
+
+
 @pytest.mark.parametrize("M,N,K", [(1, 4096, 4096), (5, 512, 1024), (8, 2048, 256)])
 def test_fused_plain_linear_exact_and_zeroing(M, N, K):
     r = np.random.default_rng(M + N + K)
