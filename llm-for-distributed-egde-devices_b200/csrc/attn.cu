@@ -812,10 +812,10 @@ int init_attn() {
   return OK;
 }
 
-// attn_tc.cu: the tcgen05 kernel (head_dim 128, no window)
+// attn_tc.cu: the tcgen05 kernel (head_dim 128, causal, optional sliding window)
 bool prefill_attn_tc_supported(int T, int hd, int window, long long q_ld, const void* q, const void* k, const void* v);
 int prefill_attn_tc(const void* q, long long q_ld, const void* kcache, const void* vcache, void* out, long long o_ld,
-                    const int* pos_ptr, int T, int pos0, int row, int H, int KV, int Smax, float scale, cudaStream_t st);
+                    const int* pos_ptr, int T, int pos0, int row, int H, int KV, int Smax, float scale, int window, cudaStream_t st);
 // test hook: 0 = choose (tcgen05 where supported), 1 = always the mma.sync kernel, 2 = tcgen05 or fail
 static int g_prefill_impl = 0;
 void set_prefill_attn_impl(int impl) { g_prefill_impl = impl; }
@@ -831,7 +831,7 @@ int prefill_attn(const void* q, long long q_ld, const void* kcache, const void* 
                      !(reinterpret_cast<uintptr_t>(out) & 15);
   if (g_prefill_impl == 2 && !tc_ok) return ERR_UNSUPPORTED;
   if (tc_ok && g_prefill_impl != 1)
-    return prefill_attn_tc(q, q_ld, kcache, vcache, out, o_ld, positions, T, pos0, row, H, KV, Smax, scale, st);
+    return prefill_attn_tc(q, q_ld, kcache, vcache, out, o_ld, positions, T, pos0, row, H, KV, Smax, scale, window, st);
   PfParams p;
   p.q = (const __half*)q; p.q_ld = q_ld; p.k = (const __half*)kcache; p.v = (const __half*)vcache;
   p.out = (__half*)out; p.o_ld = o_ld; p.pos_ptr = positions; p.T = T; p.pos0 = pos0; p.row = row; p.H = H; p.KV = KV; p.Smax = Smax;

@@ -45,7 +45,7 @@ constexpr int TC_SMEM = TC_OFF_BAR + 256 + 1024;     // + alignment slack
 struct TcAttnParams {
   __half* out; long long o_ld;
   const int* pos_ptr;
-  int T, pos0, row, H, KV, Smax;
+  int T, pos0, row, H, KV, Smax, window;
   float scale_log2;
 };
 
@@ -108,7 +108,12 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
   const int kvh = h / (p.H / p.KV);
   const int q0 = qt * TC_BM;
   const int last_q = min(q0 + TC_BM, p.T) - 1;
-  const int nt = (p.pos0 + last_q) / TC_BN + 1;         // key tiles 0 .. nt-1 cover keys 0 .. pos0+last_q
+  const int nt_end = (p.pos0 + last_q) / TC_BN + 1;     // key tiles 0 .. nt_end-1 cover keys 0 .. pos0+last_q
+  // sliding window (key > qpos - window): the first key any row of this tile needs is pos0 + q0 - window + 1; whole
+  // tiles before it are skipped, the rest of the lower bound is masked per row.  Tiles are numbered from jt0 below.
+  int jt0 = 0;
+  if (p.window > 0) { const int kf = p.pos0 + q0 - p.window + 1; jt0 = kf > 0 ? kf / TC_BN : 0; }
+  const int nt = nt_end - jt0;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV);
@@ -142,12 +147,12 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         const uint32_t ph = (j >> 1) & 1;
         mbar_wait(&k_empty[s], ph ^ 1);
         mbar_expect_tx(&k_full[s], TC_TILE);
-        tma_load_2d(smem + TC_OFF_K + s * TC_TILE, &tmK, &k_full[s], 0, kv_row0 + j * TC_BN);
-        tma_load_2d(smem + TC_OFF_K + s * TC_TILE + TC_ATOM, &tmK, &k_full[s], 64, kv_row0 + j * TC_BN);
+        tma_load_2d(smem + TC_OFF_K + s * TC_TILE, &tmK, &k_full[s], 0, kv_row0 + (jt0 + j) * TC_BN);
+        tma_load_2d(smem + TC_OFF_K + s * TC_TILE + TC_ATOM, &tmK, &k_full[s], 64, kv_row0 + (jt0 + j) * TC_BN);
         mbar_wait(&v_empty[s], ph ^ 1);
         mbar_expect_tx(&v_full[s], TC_TILE);
-        tma_load_2d(smem + TC_OFF_V + s * TC_TILE, &tmV, &v_full[s], 0, kv_row0 + j * TC_BN);
-        tma_load_2d(smem + TC_OFF_V + s * TC_TILE + TC_ATOM, &tmV, &v_full[s], 64, kv_row0 + j * TC_BN);
+        tma_load_2d(smem + TC_OFF_V + s * TC_TILE, &tmV, &v_full[s], 0, kv_row0 + (jt0 + j) * TC_BN);
+        tma_load_2d(smem + TC_OFF_V + s * TC_TILE + TC_ATOM, &tmV, &v_full[s], 64, kv_row0 + (jt0 + j) * TC_BN);
       }
     }
   } else if (warp == 1) {
@@ -213,9 +218,10 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
     int it = 0;
     for (int j = grp; j < nt; j += 2, ++it) {
       const uint32_t ph = it & 1;
-      const int key0 = j * TC_BN;
+      const int key0 = (jt0 + j) * TC_BN;
       // keys beyond a row's own position are masked; only tiles that reach past the first row's position have any
-      const int lim = (key0 + TC_BN - 1 > p.pos0 + q0) ? qpos - key0 : TC_BN;     // this row keeps keys [0, lim] of the tile
+      const int lim = (key0 + TC_BN - 1 > p.pos0 + q0) ? qpos - key0 : TC_BN;     // this row keeps keys [lo, lim] of the tile
+      const int lo = (p.window > 0) ? qpos - p.window + 1 - key0 : 0;              // <= 0: no lower bound inside this tile
       mbar_wait(&s_full[grp], ph);
       tc_fence_after();
       // ---- pass 1: row maximum ----
@@ -225,12 +231,13 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         uint32_t v[16];
         tmem_ld_32x16(ts + c * 16, v);
         tmem_ld_wait();
-        if (c * 16 + 15 <= lim) {
+        if (c * 16 + 15 <= lim && c * 16 >= lo) {
 #pragma unroll
           for (int i = 0; i < 16; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
         } else {
 #pragma unroll
-          for (int i = 0; i < 16; ++i) mx = fmaxf(mx, (c * 16 + i <= lim) ? __uint_as_float(v[i]) : -INFINITY);
+          for (int i = 0; i < 16; ++i)
+            mx = fmaxf(mx, (c * 16 + i <= lim && c * 16 + i >= lo) ? __uint_as_float(v[i]) : -INFINITY);
         }
       }
       // (a group's first tile may be fully masked for a row: odd tile 1 when pos0 + q0 < 128)
@@ -245,7 +252,7 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         tmem_ld_32x16(ts + c * 16, v);
         tmem_ld_wait();
         uint32_t pk[8];
-        const bool full = c * 16 + 15 <= lim;
+        const bool full = c * 16 + 15 <= lim && c * 16 >= lo;
 #pragma unroll
         for (int i = 0; i < 16; i += 2) {
           float x0, x1;
@@ -253,8 +260,8 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
           float e0 = ex2_approx(x0);
           float e1 = ex2_approx(x1);
           if (!full) {
-            if (c * 16 + i > lim) e0 = 0.f;
-            if (c * 16 + i + 1 > lim) e1 = 0.f;
+            if (c * 16 + i > lim || c * 16 + i < lo) e0 = 0.f;
+            if (c * 16 + i + 1 > lim || c * 16 + i + 1 < lo) e1 = 0.f;
           }
           // (row sum in fp32 of the unrounded values, as in the mma.sync kernel: converting the fp16 P back
           //  costs one XU-pipe op per element, and XU -- ex2 + conversions -- is this kernel's busiest pipe)
@@ -362,11 +369,11 @@ static int tc_make_tmap(CUtensorMap* tm, const void* base, long long rows, long 
 // Shapes this kernel takes; everything else stays on the mma.sync kernel.
 bool prefill_attn_tc_supported(int T, int hd, int window, long long q_ld, const void* q, const void* k, const void* v) {
   auto al = [](const void* x) { return (reinterpret_cast<uintptr_t>(x) & 15) == 0; };
-  return hd == TC_HD && window == 0 && T >= 64 && (q_ld % 8) == 0 && al(q) && al(k) && al(v);
+  return hd == TC_HD && window >= 0 && T >= 64 && (q_ld % 8) == 0 && al(q) && al(k) && al(v);
 }
 
 int prefill_attn_tc(const void* q, long long q_ld, const void* kcache, const void* vcache, void* out, long long o_ld,
-                    const int* pos_ptr, int T, int pos0, int row, int H, int KV, int Smax, float scale, cudaStream_t st) {
+                    const int* pos_ptr, int T, int pos0, int row, int H, int KV, int Smax, float scale, int window, cudaStream_t st) {
   CUtensorMap tmQ, tmK, tmV;
   int rc = tc_make_tmap(&tmQ, q, T, (long long)H * TC_HD, q_ld);
   if (rc) return rc;
@@ -382,7 +389,7 @@ int prefill_attn_tc(const void* q, long long q_ld, const void* kcache, const voi
   }
   TcAttnParams p;
   p.out = (__half*)out; p.o_ld = o_ld; p.pos_ptr = pos_ptr; p.T = T; p.pos0 = pos0; p.row = row; p.H = H; p.KV = KV;
-  p.Smax = Smax; p.scale_log2 = scale * 1.4426950408889634f;
+  p.Smax = Smax; p.window = window; p.scale_log2 = scale * 1.4426950408889634f;
   prefill_attn_tc_kernel<<<dim3((T + TC_BM - 1) / TC_BM, H), TC_THREADS, TC_SMEM, st>>>(tmQ, tmK, tmV, p);
   return launch_status();
 }
