@@ -82,6 +82,9 @@ B2_DEVINL void fadd2(float& d0, float& d1, float a0, float a1) {
       : "+f"(d0), "+f"(d1) : "f"(a0), "f"(a1));
 }
 
+// WIN = sliding window (a separate instantiation: the softmax warps are issue-bound, and the two extra compares per
+// 16 keys cost the full-attention path 10 % when they were unconditional)
+template <bool WIN>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                        const __grid_constant__ CUtensorMap tmV, const TcAttnParams pin) {
@@ -112,7 +115,7 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
   // sliding window (key > qpos - window): the first key any row of this tile needs is pos0 + q0 - window + 1; whole
   // tiles before it are skipped, the rest of the lower bound is masked per row.  Tiles are numbered from jt0 below.
   int jt0 = 0;
-  if (p.window > 0) { const int kf = p.pos0 + q0 - p.window + 1; jt0 = kf > 0 ? kf / TC_BN : 0; }
+  if (WIN) { const int kf = p.pos0 + q0 - p.window + 1; jt0 = kf > 0 ? kf / TC_BN : 0; }
   const int nt = nt_end - jt0;
 
   if (warp == 0 && lane == 0) {
@@ -221,7 +224,7 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
       const int key0 = (jt0 + j) * TC_BN;
       // keys beyond a row's own position are masked; only tiles that reach past the first row's position have any
       const int lim = (key0 + TC_BN - 1 > p.pos0 + q0) ? qpos - key0 : TC_BN;     // this row keeps keys [lo, lim] of the tile
-      const int lo = (p.window > 0) ? qpos - p.window + 1 - key0 : 0;              // <= 0: no lower bound inside this tile
+      const int lo = WIN ? qpos - p.window + 1 - key0 : 0;                         // <= 0: no lower bound inside this tile
       mbar_wait(&s_full[grp], ph);
       tc_fence_after();
       // ---- pass 1: row maximum ----
@@ -231,13 +234,13 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         uint32_t v[16];
         tmem_ld_32x16(ts + c * 16, v);
         tmem_ld_wait();
-        if (c * 16 + 15 <= lim && c * 16 >= lo) {
+        if (c * 16 + 15 <= lim && (!WIN || c * 16 >= lo)) {
 #pragma unroll
           for (int i = 0; i < 16; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
         } else {
 #pragma unroll
           for (int i = 0; i < 16; ++i)
-            mx = fmaxf(mx, (c * 16 + i <= lim && c * 16 + i >= lo) ? __uint_as_float(v[i]) : -INFINITY);
+            mx = fmaxf(mx, (c * 16 + i <= lim && (!WIN || c * 16 + i >= lo)) ? __uint_as_float(v[i]) : -INFINITY);
         }
       }
       // (a group's first tile may be fully masked for a row: odd tile 1 when pos0 + q0 < 128)
@@ -252,7 +255,7 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         tmem_ld_32x16(ts + c * 16, v);
         tmem_ld_wait();
         uint32_t pk[8];
-        const bool full = c * 16 + 15 <= lim && c * 16 >= lo;
+        const bool full = c * 16 + 15 <= lim && (!WIN || c * 16 >= lo);
 #pragma unroll
         for (int i = 0; i < 16; i += 2) {
           float x0, x1;
@@ -260,8 +263,8 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
           float e0 = ex2_approx(x0);
           float e1 = ex2_approx(x1);
           if (!full) {
-            if (c * 16 + i > lim || c * 16 + i < lo) e0 = 0.f;
-            if (c * 16 + i + 1 > lim || c * 16 + i + 1 < lo) e1 = 0.f;
+            if (c * 16 + i > lim || (WIN && c * 16 + i < lo)) e0 = 0.f;
+            if (c * 16 + i + 1 > lim || (WIN && c * 16 + i + 1 < lo)) e1 = 0.f;
           }
           // (row sum in fp32 of the unrounded values, as in the mma.sync kernel: converting the fp16 P back
           //  costs one XU-pipe op per element, and XU -- ex2 + conversions -- is this kernel's busiest pipe)
@@ -383,21 +386,26 @@ int prefill_attn_tc(const void* q, long long q_ld, const void* kcache, const voi
   if ((rc = tc_make_tmap(&tmV, vcache, kv_rows, TC_HD, TC_HD))) return rc;
   static bool attr_set = false;
   if (!attr_set) {
-    if (cudaFuncSetAttribute(prefill_attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM) != cudaSuccess)
+    if (cudaFuncSetAttribute(prefill_attn_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM) != cudaSuccess ||
+        cudaFuncSetAttribute(prefill_attn_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM) != cudaSuccess)
       return ERR_ARCH;
     attr_set = true;
   }
   TcAttnParams p;
   p.out = (__half*)out; p.o_ld = o_ld; p.pos_ptr = pos_ptr; p.T = T; p.pos0 = pos0; p.row = row; p.H = H; p.KV = KV;
   p.Smax = Smax; p.window = window; p.scale_log2 = scale * 1.4426950408889634f;
-  prefill_attn_tc_kernel<<<dim3((T + TC_BM - 1) / TC_BM, H), TC_THREADS, TC_SMEM, st>>>(tmQ, tmK, tmV, p);
+  const dim3 grid((T + TC_BM - 1) / TC_BM, H);
+  if (window > 0) prefill_attn_tc_kernel<true><<<grid, TC_THREADS, TC_SMEM, st>>>(tmQ, tmK, tmV, p);
+  else prefill_attn_tc_kernel<false><<<grid, TC_THREADS, TC_SMEM, st>>>(tmQ, tmK, tmV, p);
   return launch_status();
 }
 
 int init_attn_tc() {
   cudaFuncAttributes fa;
-  if (cudaFuncGetAttributes(&fa, prefill_attn_tc_kernel) != cudaSuccess) return ERR_ARCH;
-  if (cudaFuncSetAttribute(prefill_attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM) != cudaSuccess)
+  if (cudaFuncGetAttributes(&fa, prefill_attn_tc_kernel<false>) != cudaSuccess ||
+      cudaFuncGetAttributes(&fa, prefill_attn_tc_kernel<true>) != cudaSuccess) return ERR_ARCH;
+  if (cudaFuncSetAttribute(prefill_attn_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM) != cudaSuccess ||
+      cudaFuncSetAttribute(prefill_attn_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM) != cudaSuccess)
     return ERR_ARCH;
   return tc_encode_fn() ? OK : ERR_DRIVER;
 }
