@@ -254,7 +254,7 @@ int b2_outlier_side_dense(void* out, const void* y, long long ld, const int8_t* 
                           const void* residual, void* ysub, void* wdeq, float* side, int T, int N, int K, void* stream);
 
 /* Test hook (no reference counterpart): which kernel b2_prefill_attn uses from now on, process-wide.
- * 0 = choose (the tcgen05/TMEM kernel for head_dim 128 without a window and T >= 64, else the
+ * 0 = choose (the tcgen05/TMEM kernel for head_dim 128 and T >= 64, with or without a sliding window, else the
  * mma.sync kernel), 1 = always the mma.sync kernel, 2 = the tcgen05 kernel or B2_ERR_UNSUPPORTED. */
 int b2_set_prefill_attn_impl(int impl);
 
@@ -265,6 +265,7 @@ int b2_embed(const long long* ids, const int* positions, const void* table, cons
              int d, int vocab, void* stream);
 
 /* Unquantised lm_head: logits [M,V] fp32 = x [M,d] fp16 . W [V,d]^T fp16 (fp32 accumulate).
+ * Any V (GPT-2's 50257 included; d % 8 == 0): streaming GEMV for M <= 4, the tcgen05 fp16 tile above.
  * Replaces: `lm_head` (left unquantised by load_in_8bit; models_quant_updated.py:66-67 `.logits`). */
 int b2_lm_head(const void* x, const void* W, float* logits, int M, int V, int d, void* stream);
 
