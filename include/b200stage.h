@@ -86,8 +86,9 @@ int b2_gemm_w8a8(const int8_t* A, const int8_t* W, const float* a_scale, const f
  * 14/16/13 = 128x128 tile, 6 stages, cluster of 1/2/4; 15 = 128x64 tile, 8 stages.
  * 17 = 128x32 tile, 8 stages; 18 / 19 = 128x128 tile with only 32 / 64 activation rows staged per k-block
  * (decode batches: M <= 32 / 64, else B2_ERR_UNSUPPORTED) and 10 / 8 stages.
- * The cluster schedules (11, 12, 13, 16) need W in the current device's own memory (TMA multicast loads here
- * read only this GPU's memory) and return B2_ERR_UNSUPPORTED otherwise.  Other values: B2_ERR_UNSUPPORTED. */
+ * The cluster schedules (11, 12, 13, 16) need every byte of W in the current device's own memory (TMA multicast
+ * loads here read only this GPU's memory; the whole span is checked, not its first byte) and return
+ * B2_ERR_UNSUPPORTED otherwise.  Other values: B2_ERR_UNSUPPORTED. */
 int b2_gemm_w8a8_sched(const int8_t* A, const int8_t* W, const float* a_scale, const float* w_scale,
                        const void* bias, const void* residual, void* out, int32_t* acc_dump, int M, int N, int K,
                        int schedule, void* stream);

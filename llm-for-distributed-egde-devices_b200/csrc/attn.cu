@@ -430,26 +430,18 @@ size_t decode_attn_workspace_bytes(int B, int H, int hd, int splits) {
   return (size_t)B * H * splits * (hd + 2) * sizeof(float);
 }
 
-static int sm_count_attn() {
-  static int n = []() {
-    int dev = 0, v = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
-    return v > 0 ? v : 148;
-  }();
-  return n;
-}
+static int sm_count_attn() { return device_sm_count(); }
 
 template <int HD>
 static int launch_decode(const DecParams& p, int B, cudaStream_t st, bool cluster = false) {
   constexpr int SMEM = DEC_NST * 2 * DEC_TK * (HD + 8) * 2;
   constexpr int SMEM_CL_MAX = SMEM + 8 * 8 * (HD + 2) * 4;      // + landing zone: 8 splits x 8 heads of a group
-  static bool attr_set = false;
-  if (!attr_set) {
+  static DeviceOnce attr_once;
+  if (!attr_once.get()) {
     if (cudaFuncSetAttribute(decode_attn_kernel<HD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM) != cudaSuccess ||
         cudaFuncSetAttribute(decode_attn_kernel<HD, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_CL_MAX) != cudaSuccess)
       return ERR_ARCH;
-    attr_set = true;
+    attr_once.set();
   }
   if (cluster) {
     cudaLaunchConfig_t cfg = {};
@@ -784,11 +776,11 @@ __global__ void __launch_bounds__(PF_THREADS) prefill_attn_kernel(const PfParams
 template <int HD>
 static int launch_prefill(const PfParams& p, cudaStream_t st) {
   constexpr int SMEM = pf_smem_bytes<HD>();
-  static bool attr_set = false;
-  if (!attr_set) {
+  static DeviceOnce attr_once;
+  if (!attr_once.get()) {
     if (cudaFuncSetAttribute(prefill_attn_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM) != cudaSuccess)
       return ERR_ARCH;
-    attr_set = true;
+    attr_once.set();
   }
   prefill_attn_kernel<HD><<<dim3((p.T + PF_BM - 1) / PF_BM, p.H), PF_THREADS, SMEM, st>>>(p);
   return launch_status();

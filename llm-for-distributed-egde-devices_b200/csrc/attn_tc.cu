@@ -384,12 +384,12 @@ int prefill_attn_tc(const void* q, long long q_ld, const void* kcache, const voi
   const long long kv_rows = (long long)(row + 1) * KV * Smax;
   if ((rc = tc_make_tmap(&tmK, kcache, kv_rows, TC_HD, TC_HD))) return rc;
   if ((rc = tc_make_tmap(&tmV, vcache, kv_rows, TC_HD, TC_HD))) return rc;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static DeviceOnce attr_once;
+  if (!attr_once.get()) {
     if (cudaFuncSetAttribute(prefill_attn_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM) != cudaSuccess ||
         cudaFuncSetAttribute(prefill_attn_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM) != cudaSuccess)
       return ERR_ARCH;
-    attr_set = true;
+    attr_once.set();
   }
   TcAttnParams p;
   p.out = (__half*)out; p.o_ld = o_ld; p.pos_ptr = pos_ptr; p.T = T; p.pos0 = pos0; p.row = row; p.H = H; p.KV = KV;

@@ -32,6 +32,39 @@ static inline int launch_status() {
 }
 
 // ---------------------------------------------------------------------------------------------
+// per-device host state: function attributes and the SM count belong to the device that is current
+// when a launch path runs, not to the process (one process may drive several GPUs)
+// ---------------------------------------------------------------------------------------------
+constexpr int MAX_DEVICES = 64;
+static inline int current_device() {
+  int d = 0;
+  if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d >= MAX_DEVICES) return 0;
+  return d;
+}
+static inline int device_sm_count() {
+  static int n[MAX_DEVICES] = {};
+  const int d = current_device();
+  if (n[d] == 0) {
+    int v = 0;
+    cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, d);
+    n[d] = v > 0 ? v : 148;
+  }
+  return n[d];
+}
+// `static DeviceOnce once; if (!once.get()) { ...set attributes...; once.set(); }` (idempotent work: a race repeats it)
+struct DeviceOnce {
+  bool done[MAX_DEVICES] = {};
+  bool get() const { return done[current_device()]; }
+  void set() { done[current_device()] = true; }
+};
+template <typename T>
+struct DeviceValue {
+  T v[MAX_DEVICES];
+  bool init[MAX_DEVICES] = {};
+  T& get(T dflt) { const int d = current_device(); if (!init[d]) { v[d] = dflt; init[d] = true; } return v[d]; }
+};
+
+// ---------------------------------------------------------------------------------------------
 // warp helpers
 // ---------------------------------------------------------------------------------------------
 B2_DEVINL float warp_max(float v) {

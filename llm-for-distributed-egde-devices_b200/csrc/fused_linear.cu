@@ -737,15 +737,7 @@ fused_tail_kernel(const FusedParams po, const FusedParams pg, const FusedParams 
   if (QKV) fused_phase<MT, NORMK, O_QKV, false>(pq, xs, SyncGrid{ctr + 2, err}, true);
 }
 
-static int fl_sm_count() {
-  static int n = []() {
-    int dev = 0, v = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
-    return v > 0 ? v : 148;
-  }();
-  return n;
-}
+static int fl_sm_count() { return device_sm_count(); }
 
 template <int MT, int XK, int OKIND>
 static int launch_fused(const FusedParams& pin, cudaStream_t st) {
@@ -753,11 +745,11 @@ static int launch_fused(const FusedParams& pin, cudaStream_t st) {
   if (XK != X_Y32 && (pin.K >> 3) <= 3 * FL_THREADS) smem += (size_t)8 * pin.K;   // gamma, beta (fp16) + smooth (fp32) staging
   if (smem > (size_t)FL_SMEM_FULL) return ERR_TOO_LARGE;
   const FusedParams& p = pin;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static DeviceOnce attr_once;
+  if (!attr_once.get()) {
     if (cudaFuncSetAttribute(fused_gemv_kernel<MT, XK, OKIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, FL_SMEM_FULL) != cudaSuccess)
       return ERR_ARCH;
-    attr_set = true;
+    attr_once.set();
   }
   const int items = (OKIND == O_F16) ? (p.N + 1) / 2 : p.N / 2;
   int grid = MT > 1 ? (items + 7) / 8 : (items + FL_WARPS - 1) / FL_WARPS;    // MT > 1: the whole CTA works on 8 items at a time
@@ -898,10 +890,10 @@ static int launch_tail(const FusedParams& po, const FusedParams& pg, const Fused
   if (QKV) smem = std::max(smem, phase_smem(MT, NORMK, pq.K));
   if (smem > (size_t)FL_SMEM_FULL) return ERR_TOO_LARGE;
   auto kern = fused_tail_kernel<MT, NORMK, QKV>;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static DeviceOnce attr_once;
+  if (!attr_once.get()) {
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, FL_SMEM_FULL) != cudaSuccess) return ERR_ARCH;
-    attr_set = true;
+    attr_once.set();
   }
   // all CTAs must be resident at once (grid barriers): size the grid from the occupancy
   int occ = 0;

@@ -278,26 +278,18 @@ static int make_tmap(CUtensorMap* tm, const void* base, int rows, int K, int box
   return r == CUDA_SUCCESS ? OK : ERR_DRIVER;
 }
 
-static int sm_count() {
-  static int n = []() {
-    int dev = 0, v = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
-    return v > 0 ? v : 148;
-  }();
-  return n;
-}
+static int sm_count() { return device_sm_count(); }
 
 template <int BN, int STAGES, int KIND, int CM, int ABOX = BM>
 static int launch_tc(const void* A, const void* W, const GemmParams& p, cudaStream_t st) {
   using S = GemmSmem<BN, STAGES, ABOX>;
   if (ABOX < BM && p.M > ABOX) return ERR_UNSUPPORTED;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static DeviceOnce attr_once;
+  if (!attr_once.get()) {
     if (cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES, KIND, CM, ABOX>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL) !=
         cudaSuccess)
       return ERR_ARCH;
-    attr_set = true;
+    attr_once.set();
   }
   CUtensorMap tmA, tmB;
   int rc = make_tmap(&tmA, A, p.M, p.K, ABOX, KIND);
@@ -426,7 +418,8 @@ gemv_i8_kernel(const int8_t* __restrict__ A, const int8_t* __restrict__ W, const
 template <int MT>
 static int launch_gemv(const int8_t* A, const int8_t* W, const GemmParams& p, cudaStream_t st) {
   const size_t smem = (size_t)MT * p.K;
-  static size_t attr = 48 * 1024;
+  static DeviceValue<size_t> attr_v;
+  size_t& attr = attr_v.get(48 * 1024);
   if (smem > attr) {
     if (smem > 200 * 1024) return ERR_TOO_LARGE;
     if (cudaFuncSetAttribute(gemv_i8_kernel<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(200 * 1024)) != cudaSuccess)
@@ -442,6 +435,26 @@ static int launch_gemv(const int8_t* A, const int8_t* W, const GemmParams& p, cu
 // =============================================================================================
 // entry
 // =============================================================================================
+// true iff every byte of [p, p + bytes) is ordinary device memory that physically lives on the current device.
+// One allocation made with cudaMalloc lies on one device, but a virtual range assembled with cuMemMap can start
+// on this GPU and continue on another: the pointer is queried at its first byte, at every 64 KiB boundary inside
+// the span (below any mapping granularity) and at its last byte.
+static bool span_on_current_device(const void* p, size_t bytes) {
+  int dev = -1;
+  if (!p || bytes == 0 || cudaGetDevice(&dev) != cudaSuccess) return false;
+  const uintptr_t lo = reinterpret_cast<uintptr_t>(p), hi = lo + bytes - 1;
+  constexpr uintptr_t STEP = 64 * 1024;
+  auto ok_at = [dev](uintptr_t a) {
+    cudaPointerAttributes pa;
+    if (cudaPointerGetAttributes(&pa, reinterpret_cast<const void*>(a)) != cudaSuccess) { cudaGetLastError(); return false; }
+    return pa.type == cudaMemoryTypeDevice && pa.device == dev;
+  };
+  if (!ok_at(lo) || !ok_at(hi)) return false;
+  for (uintptr_t a = (lo / STEP + 1) * STEP; a < hi; a += STEP)
+    if (!ok_at(a)) return false;
+  return true;
+}
+
 int gemm_w8a8(const int8_t* A, const int8_t* W, const float* a_scale, const float* w_scale, const void* bias,
               const void* residual, void* out, int32_t* acc_dump, int M, int N, int K, int schedule, cudaStream_t st) {
   if (M == 0 || N == 0) return OK;
@@ -463,13 +476,10 @@ int gemm_w8a8(const int8_t* A, const int8_t* W, const float* a_scale, const floa
   const int m_tiles = (M + BM - 1) / BM;
   const int sms = sm_count();
   // The cluster schedules multicast the weight tile with TMA.  TMA multicast loads here read only this GPU's
-  // memory, since on B200 a TMA multicast load from another GPU's memory hung the GPU: refuse a W that is not
-  // plain device memory of the current device (every default path uses CM = 1 and is not concerned).
+  // memory, since on B200 a TMA multicast load from another GPU's memory hung the GPU: refuse a W of which any
+  // part is not plain device memory of the current device (every default path uses CM = 1 and is not concerned).
   if (schedule == 11 || schedule == 12 || schedule == 13 || schedule == 16) {
-    int dev = -1;
-    cudaPointerAttributes pa;
-    if (cudaGetDevice(&dev) != cudaSuccess || cudaPointerGetAttributes(&pa, W) != cudaSuccess) { cudaGetLastError(); return ERR_UNSUPPORTED; }
-    if (pa.type != cudaMemoryTypeDevice || pa.device != dev) return ERR_UNSUPPORTED;
+    if (!span_on_current_device(W, (size_t)N * K)) return ERR_UNSUPPORTED;
   }
   // schedule >= 10 (test hook): force a tile/cluster shape; 0/1: heuristic
   if (schedule == 10) return launch_tc<256, 4, KIND_I8, 1>(A, W, p, st);
@@ -567,7 +577,8 @@ gemv_f16_kernel(const __half* __restrict__ X, const __half* __restrict__ W, floa
 template <int MT>
 static int launch_gemv_f16(const __half* X, const __half* W, float* out, int M, int N, int K, cudaStream_t st) {
   const size_t smem = (size_t)MT * K * 2;
-  static size_t attr = 48 * 1024;
+  static DeviceValue<size_t> attr_v;
+  size_t& attr = attr_v.get(48 * 1024);
   if (smem > attr) {
     if (smem > 200 * 1024) return ERR_TOO_LARGE;
     if (cudaFuncSetAttribute(gemv_f16_kernel<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(200 * 1024)) != cudaSuccess)

@@ -164,10 +164,10 @@ int sample(const float* logits, long long ld, const long long* history, const in
   if (top_k <= 0 || top_k > SMP_CAP) top_k = SMP_CAP;     // top_k = 0 ("off" in HF) is capped at SMP_CAP candidates
   const size_t smem = (size_t)((V + 31) / 32) * 4;
   if (smem > 160 * 1024) return ERR_TOO_LARGE;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static DeviceOnce attr_once;
+  if (!attr_once.get()) {
     if (cudaFuncSetAttribute(sample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024) != cudaSuccess) return ERR_ARCH;
-    attr_set = true;
+    attr_once.set();
   }
   SampleParams p;
   p.logits = logits; p.ld = ld; p.history = history; p.hist_len = hist_len; p.hist_ld = hist_ld; p.out = out;
