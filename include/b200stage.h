@@ -88,10 +88,38 @@ int b2_gemm_w8a8(const int8_t* A, const int8_t* W, const float* a_scale, const f
  * (decode batches: M <= 32 / 64, else B2_ERR_UNSUPPORTED) and 10 / 8 stages.
  * The cluster schedules (11, 12, 13, 16) need every byte of W in the current device's own memory (TMA multicast
  * loads here read only this GPU's memory; the whole span is checked, not its first byte) and return
- * B2_ERR_UNSUPPORTED otherwise.  Other values: B2_ERR_UNSUPPORTED. */
+ * B2_ERR_UNSUPPORTED otherwise.  20 = the CTA-pair kernel (tcgen05 cta_group::2, 256x256 tile per two SMs;
+ * N % 32 == 0), which schedule 0 takes by itself for M > 128, N >= 256.  Other values: B2_ERR_UNSUPPORTED. */
 int b2_gemm_w8a8_sched(const int8_t* A, const int8_t* W, const float* a_scale, const float* w_scale,
                        const void* bias, const void* residual, void* out, int32_t* acc_dump, int M, int N, int K,
                        int schedule, void* stream);
+
+/* Prefill gate/up projection with the activation fused into the GEMM epilogue (CTA-pair tcgen05 kernel).
+ * A [M,K] int8, a_scale [M]; W [2F,K] int8 = [gate rows; up rows], w_scale [2F], bias [2F] fp16 or NULL.
+ * y32 [M,F] fp32 = act(fp16(gate)) * fp16(up) * out_smooth[f] (out_smooth [F] fp32 or NULL), amax [M] fp32 = the
+ * row absmax of y32 (zeroed by this call on `stream`, then raised with atomic max).  act: 0 silu, 1 gelu_new.
+ * F % 32 == 0, K % 16 == 0.  Followed by b2_quant_f32 the pair is bit-identical to
+ * b2_gemm_w8a8 + b2_act_mul_quant without the [M,2F] fp16 round trip through HBM.
+ * Replaces: `act_fn(gate_proj(x)) * up_proj(x)` (modeling_llama.py:182-184) with both projections as the int8
+ * linears requested at models_quant_updated.py:30-38, in the prefill forward of `generate` (:84-93). */
+int b2_gemm_gated_act(const int8_t* A, const int8_t* W, const float* a_scale, const float* w_scale, const void* bias,
+                      const float* out_smooth, float* y32, float* amax, int M, int F, int K, int act, void* stream);
+/* y32 [T,F] fp32 with its row absmax amax [T] (as written by b2_gemm_gated_act) -> q [T,F] int8, row_scale [T]
+ * (amax/127): the quantise step of b2_act_mul_quant.  F % 16 == 0.
+ * Replaces: the activation quantisation of `down_proj` (Linear8bitLt, models_quant_updated.py:30-38). */
+int b2_quant_f32(const float* y32, const float* amax, int8_t* q, float* row_scale, int T, int F, void* stream);
+
+/* Prefill q/k/v projection with rotary embedding and the KV-cache append fused into the GEMM epilogue
+ * (CTA-pair tcgen05 kernel).  A [M,K] int8, a_scale [M]; W [(H+2KV)*hd, K] int8 = [q; k; v] rows, w_scale, bias
+ * likewise.  Rotated q goes to qkv_out [M, ld] (only its q columns [0,H*hd) are written), rotated k and v to the
+ * caches [rows][KV][Smax][hd] at (seq_ids[m] or seq0, positions[m]).  hd 64 or 128.  Bit-identical to
+ * b2_gemm_w8a8 + b2_rope_kv_append.
+ * Replaces: q/k/v_proj + apply_rotary_pos_emb + DynamicCache.update (modeling_llama.py:128-153, :251-289) in the
+ * prefill forward of `generate` (models_quant_updated.py:84-93) and of confidence_score (:63-70). */
+int b2_gemm_qkv_rope(const int8_t* A, const int8_t* W, const float* a_scale, const float* w_scale, const void* bias,
+                     void* qkv_out, long long ld, const float* cos_table, const float* sin_table, const int* positions,
+                     const int* seq_ids, int seq0, void* kcache, void* vcache, int M, int H, int KV, int hd, int Smax, int K,
+                     int use_rope, void* stream);
 
 /* Decode-time fused linear for M <= 8 tokens: activation prologue -> per-token int8 quantise ->
  * W8A8 weight-streaming GEMV -> epilogue, in ONE launch (programmatic dependent launch: the weight

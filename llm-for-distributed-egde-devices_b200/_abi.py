@@ -30,6 +30,10 @@ SIGNATURES = {
     "b2_act_mul_quant": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
     "b2_gemm_w8a8": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
     "b2_gemm_w8a8_sched": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
+    "b2_gemm_gated_act": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
+    "b2_quant_f32": (_i, [_vp, _vp, _vp, _vp, _i, _i, _vp]),
+    "b2_gemm_qkv_rope": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _ll, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _i, _i,
+                              _i, _vp]),
     "b2_rope_kv_append": (_i, [_vp, _ll, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "b2_decode_attn": (_i, [_vp, _ll, _vp, _vp, _vp, _vp, _vp, _ll, _vp, _sz, _i, _i, _i, _i, _i, _i, _f, _i, _vp, _ll, _vp,
                              _ll, _vp]),

@@ -10,6 +10,15 @@ int act_mul_quant(const void*, const float*, int8_t*, float*, int, int, int, cud
 int gemm_w8a8(const int8_t*, const int8_t*, const float*, const float*, const void*, const void*, void*, int32_t*, int,
               int, int, int, cudaStream_t);
 int lm_head(const void*, const void*, float*, int, int, int, cudaStream_t);
+bool gemm2_supported(int, int, int);
+int gemm2_plain(const int8_t*, const int8_t*, const float*, const float*, const void*, const void*, void*, int32_t*, int, int,
+                int, cudaStream_t);
+int gemm2_gated(const int8_t*, const int8_t*, const float*, const float*, const void*, const float*, float*, float*, int, int,
+                int, int, cudaStream_t);
+int gemm2_qkv(const int8_t*, const int8_t*, const float*, const float*, const void*, void*, long long, const float*,
+              const float*, const int*, const int*, int, void*, void*, int, int, int, int, int, int, int, cudaStream_t);
+int quant_f32(const float*, const float*, int8_t*, float*, int, int, cudaStream_t);
+int init_gemm2();
 int rope_kv_append(void*, long long, const float*, const float*, const int*, const int*, int, void*, void*, int, int,
                    int, int, int, int, cudaStream_t);
 int decode_attn(const void*, long long, const void*, const void*, const int*, const int*, void*, long long, void*,
@@ -59,6 +68,7 @@ int b2_version(void) { return 100; }
 int b2_init(void) {
   int rc = b2::init_gemm();
   if (rc) return rc;
+  if ((rc = b2::init_gemm2())) return rc;
   if ((rc = b2::init_attn())) return rc;
   if ((rc = b2::init_attn_tc())) return rc;
   if ((rc = b2::init_outlier())) return rc;
@@ -99,12 +109,31 @@ int b2_act_mul_quant(const void* gate_up, const float* smooth, int8_t* q, float*
 }
 int b2_gemm_w8a8(const int8_t* A, const int8_t* W, const float* a_scale, const float* w_scale, const void* bias,
                  const void* residual, void* out, int32_t* acc_dump, int M, int N, int K, void* stream) {
+  if (b2::gemm2_supported(M, N, K))
+    return b2::gemm2_plain(A, W, a_scale, w_scale, bias, residual, out, acc_dump, M, N, K, ST(stream));
   return b2::gemm_w8a8(A, W, a_scale, w_scale, bias, residual, out, acc_dump, M, N, K, 0, ST(stream));
 }
 int b2_gemm_w8a8_sched(const int8_t* A, const int8_t* W, const float* a_scale, const float* w_scale, const void* bias,
                        const void* residual, void* out, int32_t* acc_dump, int M, int N, int K, int schedule,
                        void* stream) {
+  if (schedule == 20) return b2::gemm2_plain(A, W, a_scale, w_scale, bias, residual, out, acc_dump, M, N, K, ST(stream));
+  if (schedule == 0 && b2::gemm2_supported(M, N, K))
+    return b2::gemm2_plain(A, W, a_scale, w_scale, bias, residual, out, acc_dump, M, N, K, ST(stream));
   return b2::gemm_w8a8(A, W, a_scale, w_scale, bias, residual, out, acc_dump, M, N, K, schedule, ST(stream));
+}
+int b2_gemm_gated_act(const int8_t* A, const int8_t* W, const float* a_scale, const float* w_scale, const void* bias,
+                      const float* out_smooth, float* y32, float* amax, int M, int F, int K, int act, void* stream) {
+  return b2::gemm2_gated(A, W, a_scale, w_scale, bias, out_smooth, y32, amax, M, F, K, act, ST(stream));
+}
+int b2_quant_f32(const float* y32, const float* amax, int8_t* q, float* row_scale, int T, int F, void* stream) {
+  return b2::quant_f32(y32, amax, q, row_scale, T, F, ST(stream));
+}
+int b2_gemm_qkv_rope(const int8_t* A, const int8_t* W, const float* a_scale, const float* w_scale, const void* bias,
+                     void* qkv_out, long long ld, const float* cos_table, const float* sin_table, const int* positions,
+                     const int* seq_ids, int seq0, void* kcache, void* vcache, int M, int H, int KV, int hd, int Smax, int K,
+                     int use_rope, void* stream) {
+  return b2::gemm2_qkv(A, W, a_scale, w_scale, bias, qkv_out, ld, cos_table, sin_table, positions, seq_ids, seq0, kcache,
+                       vcache, M, H, KV, hd, Smax, K, use_rope, ST(stream));
 }
 int b2_fused_linear(const void* x, long long x_ld, int x_kind, const void* gamma, const void* beta, const float* smooth,
                     const float* x_amax, float eps, const int8_t* W, const float* w_scale, const void* bias,

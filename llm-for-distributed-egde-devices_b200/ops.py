@@ -84,6 +84,39 @@ def gemm_w8a8(a_q, w_q, a_scale, w_scale, bias=None, residual=None, out=None, ac
     return o
 
 
+def gemm_gated_act(a_q, w_q, a_scale, w_scale, *, y32, amax, bias=None, out_smooth=None, act=0):
+    """a_q [M,K] int8, w_q [2F,K] = [gate; up] -> y32 [M,F] fp32 = act(gate)*up*out_smooth, amax [M].  b2_gemm_gated_act."""
+    _cuda(a_q, w_q, a_scale, w_scale, bias, out_smooth, y32, amax)
+    M, K = a_q.shape
+    F = w_q.shape[0] // 2
+    check(_abi.lib().b2_gemm_gated_act(ptr(a_q), ptr(w_q), ptr(a_scale), ptr(w_scale), ptr(bias), ptr(out_smooth), ptr(y32),
+                                       ptr(amax), M, F, K, int(act), stream_handle()), "b2_gemm_gated_act")
+    return y32, amax
+
+
+def quant_f32(y32, amax, out_q=None, out_scale=None):
+    """y32 [T,F] fp32 + row absmax -> (q [T,F] int8, scale [T]).  b2_quant_f32."""
+    _cuda(y32, amax, out_q, out_scale)
+    T, F = y32.shape
+    q = out_q if out_q is not None else torch.empty((T, F), dtype=torch.int8, device=y32.device)
+    s = out_scale if out_scale is not None else torch.empty((T,), dtype=torch.float32, device=y32.device)
+    check(_abi.lib().b2_quant_f32(ptr(y32), ptr(amax), ptr(q), ptr(s), T, F, stream_handle()), "b2_quant_f32")
+    return q, s
+
+
+def gemm_qkv_rope(a_q, w_q, a_scale, w_scale, qkv_out, cos, sin, positions, kcache, vcache, H, KV, hd, *, bias=None,
+                  seq_ids=None, seq0=0, use_rope=True):
+    """Prefill qkv projection + RoPE + KV append in one launch.  b2_gemm_qkv_rope."""
+    _cuda(a_q, w_q, a_scale, w_scale, qkv_out, cos, sin, positions, kcache, vcache, bias, seq_ids)
+    M, K = a_q.shape
+    Smax = kcache.shape[2]
+    check(_abi.lib().b2_gemm_qkv_rope(ptr(a_q), ptr(w_q), ptr(a_scale), ptr(w_scale), ptr(bias), ptr(qkv_out),
+                                      qkv_out.stride(0), ptr(cos), ptr(sin), ptr(positions), ptr(seq_ids), int(seq0),
+                                      ptr(kcache), ptr(vcache), M, H, KV, hd, Smax, K, int(bool(use_rope)),
+                                      stream_handle()), "b2_gemm_qkv_rope")
+    return qkv_out
+
+
 X_RMS, X_LN, X_PLAIN, X_Y32 = 0, 1, 2, 3
 O_F16, O_GATED, O_QKV = 0, 1, 2
 

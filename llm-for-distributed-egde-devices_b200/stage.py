@@ -91,6 +91,9 @@ class _Scratch:
         # fused decode path (T <= 8): act(gate)*up in fp32 and its running row absmax
         self.y32 = torch.empty((8, F), dtype=f32, device=device)
         self.amax = torch.zeros((8,), dtype=f32, device=device)
+        # prefill: row absmax of act(gate)*up, raised atomically by the gate/up GEMM epilogue (the fp32 product itself
+        # lives in `gu`'s storage: [cap,F] fp32 is as large as [cap,2F] fp16)
+        self.amax_p = torch.zeros((cap,), dtype=f32, device=device)
         # grid-barrier counters of the persistent layer-tail kernel: 4 x uint32 per layer, zeroed per forward
         self.ctr = torch.zeros((256 * 4,), dtype=torch.int32, device=device)
 
@@ -143,6 +146,9 @@ class Stage:
         # SLOWER than four PDL-chained launches on B200 (38.0 vs 33.8 us per layer tail), so off by default
         # (also slower on the small models: TinyLlama 1271 vs 1584 tok/s, Llama-3.2-1B 1506 vs 1857)
         self.fuse_tail = False
+        # prefill chunks of more than 128 tokens: RoPE + KV append and act(gate)*up run as epilogues of the
+        # CTA-pair GEMM (b2_gemm_qkv_rope, b2_gemm_gated_act + b2_quant_f32); bit-identical to the unfused calls
+        self.fuse_prefill = True
         # "w8a8" (SmoothQuant-style, the north-star path) or "llm_int8" (bitsandbytes' mixed decomposition:
         # outlier activation columns in fp16, the rest int8 -- what the reference's load_in_8bit=True computes)
         self.quant = sw.get("quant", "w8a8")
@@ -281,15 +287,21 @@ class Stage:
                     ops.gemm_w8a8(q8, lw["wd"], sc, lw["s_d"], lw.get("b_d"), h_alt, out=h)
                     n += 3
                 continue
+            pair = self.fuse_prefill and not decode and trace is None and T > 128
             q8 = buf.q8view(T, d)
             ops.norm_quant(h, lw["ln1_g"], lw.get("ln1_b"), lw["sm_qkv"], cfg.eps, out_q=q8, out_scale=sc)
-            ops.gemm_w8a8(q8, lw["wqkv"], sc, lw["s_qkv"], lw.get("b_qkv"), None, out=qkv)
             tr = None
-            if trace is not None:
-                tr = dict(q1=q8.clone(), s1=sc.clone(), qkv=qkv.clone())
-                trace.append(tr)
-            ops.rope_kv_append(qkv, self.cos, self.sin, dpos, kc, vc, H, KV, hd, seq_ids=dseq, seq0=row0,
-                               use_rope=cfg.rope)
+            if pair and hd in (64, 128):
+                ops.gemm_qkv_rope(q8, lw["wqkv"], sc, lw["s_qkv"], qkv, self.cos, self.sin, dpos, kc, vc, H, KV, hd,
+                                  bias=lw.get("b_qkv"), seq_ids=dseq, seq0=row0, use_rope=cfg.rope)
+                n -= 1
+            else:
+                ops.gemm_w8a8(q8, lw["wqkv"], sc, lw["s_qkv"], lw.get("b_qkv"), None, out=qkv)
+                if trace is not None:
+                    tr = dict(q1=q8.clone(), s1=sc.clone(), qkv=qkv.clone())
+                    trace.append(tr)
+                ops.rope_kv_append(qkv, self.cos, self.sin, dpos, kc, vc, H, KV, hd, seq_ids=dseq, seq0=row0,
+                                   use_rope=cfg.rope)
             if decode:
                 ops.decode_attn(qkv, kc, vc, dlens, H, KV, hd, max_len, self.scale, cfg.window, rows=dseq, out=attn,
                                 workspace=ws)
@@ -302,9 +314,17 @@ class Stage:
             ops.gemm_w8a8(q8, lw["wo"], sc, lw["s_o"], lw.get("b_o"), h, out=h_alt)
             q8 = buf.q8view(T, d)
             ops.norm_quant(h_alt, lw["ln2_g"], lw.get("ln2_b"), lw["sm_gu"], cfg.eps, out_q=q8, out_scale=sc)
-            ops.gemm_w8a8(q8, lw["wgu"], sc, lw["s_gu"], lw.get("b_gu"), None, out=gu)
-            q8 = buf.q8view(T, F)
-            ops.act_mul_quant(gu, lw["sm_d"], act, out_q=q8, out_scale=sc)
+            if pair and cfg.gated and F % 32 == 0:
+                y32 = gu.view(torch.float32)                     # [T,F] fp32 in the storage of the fp16 [T,2F] buffer
+                am = buf.amax_p[:T]
+                ops.gemm_gated_act(q8, lw["wgu"], sc, lw["s_gu"], y32=y32, amax=am, bias=lw.get("b_gu"),
+                                   out_smooth=lw["sm_d"], act=0 if cfg.act == "silu" else 1)
+                q8 = buf.q8view(T, F)
+                ops.quant_f32(y32, am, out_q=q8, out_scale=sc)
+            else:
+                ops.gemm_w8a8(q8, lw["wgu"], sc, lw["s_gu"], lw.get("b_gu"), None, out=gu)
+                q8 = buf.q8view(T, F)
+                ops.act_mul_quant(gu, lw["sm_d"], act, out_q=q8, out_scale=sc)
             ops.gemm_w8a8(q8, lw["wd"], sc, lw["s_d"], lw.get("b_d"), h_alt, out=h)
             n += 9
             if tr is not None:

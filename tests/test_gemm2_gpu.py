@@ -1,0 +1,279 @@
+"""The CTA-pair (tcgen05 cta_group::2) prefill GEMM and its fused epilogues: b2_gemm_w8a8 at M > 128,
+b2_gemm_gated_act + b2_quant_f32, b2_gemm_qkv_rope.
+
+Bar: bit-exact.  Against the Tier-S oracle (oracle/w8a8.py) on seeded inputs at sizes numpy finishes in
+seconds, and at the BASELINE (Llama-2-7B, 2048-token) sizes against the unfused entry points, which
+tests/test_kernels_gpu.py pins to the same oracle.
+"""
+import numpy as np
+import pytest
+import torch
+
+from b200stage import ops
+from oracle import w8a8 as O
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+PAIR = 20           # b2_gemm_w8a8_sched: force the CTA-pair kernel
+
+
+def t(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(DEV)
+
+
+def n(x):
+    return x.detach().cpu().numpy()
+
+
+def bits(x):
+    return n(x).view(np.uint16)
+
+
+def _inputs(M, N, K, seed, bias):
+    r = np.random.default_rng(seed)
+    a = r.integers(-127, 128, (M, K), dtype=np.int8)
+    w = r.integers(-127, 128, (N, K), dtype=np.int8)
+    sa = r.uniform(1e-3, 5e-2, M).astype(np.float32)
+    sw = r.uniform(1e-4, 2e-3, N).astype(np.float32)
+    b = (0.1 * r.standard_normal(N)).astype(np.float16) if bias else None
+    return r, a, w, sa, sw, b
+
+
+# ----------------------------------------------------------------------------------------------
+# plain epilogue
+# ----------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("M,N,K", [(129, 256, 128), (256, 512, 256), (300, 384, 1040), (1, 256, 128), (640, 2304, 768),
+                                   (257, 288, 4096), (512, 1024, 11008)])
+@pytest.mark.parametrize("bias,resid", [(False, False), (True, True)])
+def test_pair_gemm_exact_vs_oracle(M, N, K, bias, resid):
+    r, a, w, sa, sw, b = _inputs(M, N, K, M + N + K, bias)
+    res = r.standard_normal((M, N)).astype(np.float16) if resid else None
+    ref, acc_ref = O.gemm_w8a8(a, w, sa, sw, b, res)
+    acc = torch.full((M, N), -7, dtype=torch.int32, device=DEV)
+    out = ops.gemm_w8a8(t(a), t(w), t(sa), t(sw), None if b is None else t(b), None if res is None else t(res),
+                        acc_dump=acc, schedule=PAIR)
+    assert np.array_equal(n(acc), acc_ref), "int32 accumulators differ from the oracle"
+    assert np.array_equal(bits(out), ref.view(np.uint16)), "fp16 outputs differ from the oracle"
+
+
+def test_pair_gemm_is_the_default_above_128_rows_and_matches_single_cta():
+    """Llama-2-7B o_proj / down_proj shapes at the bench's 2048-token chunk: the default schedule (pair kernel)
+    and the single-CTA tcgen05 kernel (schedule 10) give the same accumulators and fp16 outputs."""
+    g = torch.Generator(device=DEV).manual_seed(3)
+    for N, K in ((4096, 4096), (4096, 11008)):
+        M = 2048
+        a = torch.randint(-127, 128, (M, K), dtype=torch.int8, device=DEV, generator=g)
+        w = torch.randint(-127, 128, (N, K), dtype=torch.int8, device=DEV, generator=g)
+        sa = torch.rand(M, device=DEV, generator=g) * 0.05 + 1e-3
+        sw = torch.rand(N, device=DEV, generator=g) * 2e-3 + 1e-4
+        res = torch.randn((M, N), device=DEV, generator=g).half()
+        acc0 = torch.zeros((M, N), dtype=torch.int32, device=DEV)
+        acc1 = torch.ones((M, N), dtype=torch.int32, device=DEV)
+        o0 = ops.gemm_w8a8(a, w, sa, sw, None, res, acc_dump=acc0)                 # default: pair kernel
+        o1 = ops.gemm_w8a8(a, w, sa, sw, None, res, acc_dump=acc1, schedule=10)    # single-CTA 128x256
+        assert torch.equal(acc0, acc1)
+        assert torch.equal(o0.view(torch.int16), o1.view(torch.int16))
+        # checksum of checksums against exact integer arithmetic: column sums of A times row sums of W
+        tot = int(acc0.sum(dtype=torch.int64).item())
+        ref = int((a.sum(0, dtype=torch.int64) * w.sum(0, dtype=torch.int64)).sum().item())
+        assert tot == ref
+
+
+def test_pair_gemm_many_tiles_per_pair():
+    """More tiles than CTA pairs, so every pair walks several tiles through both accumulator buffers
+    and the ring wraps many times (K = 11008 = 86 k-blocks)."""
+    M, N, K = 2048, 22016, 4096
+    g = torch.Generator(device=DEV).manual_seed(5)
+    a = torch.randint(-127, 128, (M, K), dtype=torch.int8, device=DEV, generator=g)
+    w = torch.randint(-127, 128, (N, K), dtype=torch.int8, device=DEV, generator=g)
+    sa = torch.rand(M, device=DEV, generator=g) * 0.05 + 1e-3
+    sw = torch.rand(N, device=DEV, generator=g) * 2e-3 + 1e-4
+    o0 = ops.gemm_w8a8(a, w, sa, sw, schedule=PAIR)
+    o1 = ops.gemm_w8a8(a, w, sa, sw, schedule=10)
+    assert torch.equal(o0.view(torch.int16), o1.view(torch.int16))
+
+
+# ----------------------------------------------------------------------------------------------
+# gate/up projection with act(gate)*up in the epilogue
+# ----------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("M,F,K,act", [(130, 128, 256, 0), (300, 352, 512, 0), (256, 1024, 1024, 1), (64, 96, 128, 0)])
+@pytest.mark.parametrize("bias,smooth", [(False, True), (True, False)])
+def test_gated_epilogue_exact_vs_oracle(M, F, K, act, bias, smooth):
+    r, a, w, sa, sw, b = _inputs(M, 2 * F, K, M + F + K + act, bias)
+    sa *= 0.02                       # keep gate/up in the range where silu is not saturated everywhere
+    sm = r.uniform(0.2, 5.0, F).astype(np.float32) if smooth else None
+    gu_ref, _ = O.gemm_w8a8(a, w, sa, sw, b, None)
+    name = "silu" if act == 0 else "gelu_new"
+    y_ref, amax_ref = O.act_mul_y(gu_ref, sm, name)
+    q_ref, s_ref = O.act_mul_quant(gu_ref, sm, name)
+    y32 = torch.full((M, F), 7.0, dtype=torch.float32, device=DEV)
+    amax = torch.full((M,), 9.0, dtype=torch.float32, device=DEV)          # the call must zero it
+    ops.gemm_gated_act(t(a), t(w), t(sa), t(sw), y32=y32, amax=amax, bias=None if b is None else t(b),
+                       out_smooth=None if sm is None else t(sm), act=act)
+    assert np.array_equal(n(y32).view(np.uint32), y_ref.view(np.uint32))
+    assert np.array_equal(n(amax), amax_ref)
+    q, s = ops.quant_f32(y32, amax)
+    assert np.array_equal(n(s), s_ref) and np.array_equal(n(q), q_ref)
+
+
+def test_gated_epilogue_full_size_matches_unfused():
+    """Llama-2-7B gate_up at 2048 tokens: fused epilogue + b2_quant_f32 == b2_gemm_w8a8 + b2_act_mul_quant."""
+    M, F, K = 2048, 11008, 4096
+    g = torch.Generator(device=DEV).manual_seed(11)
+    a = torch.randint(-127, 128, (M, K), dtype=torch.int8, device=DEV, generator=g)
+    w = torch.randint(-127, 128, (2 * F, K), dtype=torch.int8, device=DEV, generator=g)
+    sa = torch.rand(M, device=DEV, generator=g) * 1e-3 + 1e-4
+    sw = torch.rand(2 * F, device=DEV, generator=g) * 2e-3 + 1e-4
+    sm = torch.rand(F, device=DEV, generator=g) * 4 + 0.2
+    gu = ops.gemm_w8a8(a, w, sa, sw, schedule=10)
+    q_ref, s_ref = ops.act_mul_quant(gu, sm, ops.ACT_SILU_MUL)
+    y32 = torch.empty((M, F), dtype=torch.float32, device=DEV)
+    amax = torch.empty((M,), dtype=torch.float32, device=DEV)
+    ops.gemm_gated_act(a, w, sa, sw, y32=y32, amax=amax, out_smooth=sm, act=0)
+    q, s = ops.quant_f32(y32, amax)
+    assert torch.equal(s, s_ref) and torch.equal(q, q_ref)
+    assert float(s.min()) > 0
+
+
+def test_gated_zero_rows():
+    M, F, K = 140, 64, 128
+    r, a, w, sa, sw, _ = _inputs(M, 2 * F, K, 1, False)
+    a[3] = 0
+    a[139] = 0
+    y32 = torch.empty((M, F), dtype=torch.float32, device=DEV)
+    amax = torch.empty((M,), dtype=torch.float32, device=DEV)
+    ops.gemm_gated_act(t(a), t(w), t(sa), t(sw), y32=y32, amax=amax)
+    q, s = ops.quant_f32(y32, amax)
+    assert n(s)[3] == 0 and n(s)[139] == 0 and not n(q)[3].any()
+    gu_ref, _ = O.gemm_w8a8(a, w, sa, sw)
+    q_ref, s_ref = O.act_mul_quant(gu_ref, None, "silu")
+    assert np.array_equal(n(s), s_ref) and np.array_equal(n(q), q_ref)
+
+
+# ----------------------------------------------------------------------------------------------
+# q/k/v projection with rotary embedding + KV append in the epilogue
+# ----------------------------------------------------------------------------------------------
+def _qkv_case(M, H, KV, hd, K, pos0, bias, use_rope, seed, Smax=None, rows=2, seq0=1):
+    N = (H + 2 * KV) * hd
+    r, a, w, sa, sw, b = _inputs(M, N, K, seed, bias)
+    Smax = Smax or (pos0 + M + 5)
+    cos, sin = O.rope_table(hd, Smax, 10000.0)
+    pos = np.arange(pos0, pos0 + M, dtype=np.int32)
+    args = [t(a), t(w), t(sa), t(sw)]
+    tb = None if b is None else t(b)
+    # unfused: GEMM (single-CTA kernel, pinned to the oracle elsewhere) then b2_rope_kv_append
+    qkv_ref = ops.gemm_w8a8(*args, tb, None, schedule=1)
+    kc_ref = torch.zeros((rows, KV, Smax, hd), dtype=torch.float16, device=DEV)
+    vc_ref = torch.zeros_like(kc_ref)
+    ops.rope_kv_append(qkv_ref, t(cos), t(sin), t(pos), kc_ref, vc_ref, H, KV, hd, seq0=seq0, use_rope=use_rope)
+    # fused
+    qkv = torch.full((M, N), 3.0, dtype=torch.float16, device=DEV)
+    kc = torch.zeros_like(kc_ref)
+    vc = torch.zeros_like(kc_ref)
+    ops.gemm_qkv_rope(*args, qkv, t(cos), t(sin), t(pos), kc, vc, H, KV, hd, bias=tb, seq0=seq0, use_rope=use_rope)
+    assert torch.equal(qkv[:, : H * hd].view(torch.int16), qkv_ref[:, : H * hd].view(torch.int16)), "rotated q differs"
+    assert torch.equal(kc.view(torch.int16), kc_ref.view(torch.int16)), "k cache differs"
+    assert torch.equal(vc.view(torch.int16), vc_ref.view(torch.int16)), "v cache differs"
+    assert bool((qkv[:, H * hd:] == 3.0).all()), "k/v columns of the qkv buffer must stay untouched"
+    return a, w, sa, sw, b, cos, sin, pos, qkv, kc, vc
+
+
+@pytest.mark.parametrize("M,H,KV,hd,K,pos0", [(130, 4, 4, 128, 256, 0), (300, 8, 2, 128, 512, 37), (256, 8, 2, 64, 256, 5),
+                                              (70, 6, 2, 64, 384, 0), (512, 32, 8, 128, 1024, 1000)])
+@pytest.mark.parametrize("bias", [False, True])
+def test_qkv_epilogue_matches_unfused(M, H, KV, hd, K, pos0, bias):
+    _qkv_case(M, H, KV, hd, K, pos0, bias, True, M + H + K)
+
+
+def test_qkv_epilogue_vs_oracle_and_no_rope():
+    M, H, KV, hd, K = 150, 4, 2, 128, 256
+    a, w, sa, sw, b, cos, sin, pos, qkv, kc, vc = _qkv_case(M, H, KV, hd, K, 9, True, True, 77)
+    ref, _ = O.gemm_w8a8(a, w, sa, sw, b, None)
+    q_ref = O.apply_rope(ref[:, : H * hd].reshape(M, H, hd), pos, cos, sin).reshape(M, H * hd)
+    k_ref = O.apply_rope(ref[:, H * hd:(H + KV) * hd].reshape(M, KV, hd), pos, cos, sin)
+    v_ref = ref[:, (H + KV) * hd:].reshape(M, KV, hd)
+    assert np.array_equal(bits(qkv[:, : H * hd]), q_ref.view(np.uint16))
+    assert np.array_equal(bits(kc[1, :, 9:9 + M]), np.ascontiguousarray(k_ref.transpose(1, 0, 2)).view(np.uint16))
+    assert np.array_equal(bits(vc[1, :, 9:9 + M]), np.ascontiguousarray(v_ref.transpose(1, 0, 2)).view(np.uint16))
+    _qkv_case(M, H, KV, hd, K, 0, False, False, 78)      # GPT-2 style: no rotation, scatter only
+
+
+def test_qkv_epilogue_full_size():
+    """Llama-2-7B qkv at a 2048-token chunk starting at position 2048 of a 4096-slot cache."""
+    _qkv_case(2048, 32, 32, 128, 4096, 2048, False, True, 5, Smax=4096, rows=1, seq0=0)
+
+
+# ----------------------------------------------------------------------------------------------
+# stage level: the fused prefill chain == the unfused one, bit for bit; and both against the oracle at
+# BASELINE dimensions
+# ----------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("model,T", [("tiny-gqa-test", 300), ("tiny-hd128-test", 257), ("tiny-gpt2-test", 200),
+                                     ("tiny-window-test", 400)])
+def test_fused_prefill_chain_equals_unfused(model, T):
+    import b200stage
+    from b200stage.stage import Stage
+    cfg = b200stage.get_config(model)
+    stage = Stage.load(cfg, 0, cfg.n_layers, first=True, last=True, device=DEV, seed=4)
+    ids = torch.from_numpy(np.random.default_rng(2).integers(0, cfg.vocab, T)).to(DEV)
+    outs = []
+    for fuse in (False, True):
+        stage.fuse_prefill = fuse
+        cache = stage.new_kv_cache(1, T + 8)
+        lg = stage.forward(ids, cache, np.arange(T), logits="all").clone()
+        outs.append((lg, cache.k.clone(), cache.v.clone()))
+    assert torch.equal(outs[0][0], outs[1][0]), "logits differ between the fused and the unfused prefill chain"
+    assert torch.equal(outs[0][1], outs[1][1]) and torch.equal(outs[0][2], outs[1][2]), "KV caches differ"
+
+
+def _close(got, ref, name, tol=2.0 ** -5, cos_min=0.9995):
+    got = got.astype(np.float64).ravel()
+    ref = ref.astype(np.float64).ravel()
+    err = np.abs(got - ref).max()
+    cos = float(got @ ref / (np.linalg.norm(got) * np.linalg.norm(ref) + 1e-30))
+    assert err <= tol * np.abs(ref).max() + 1e-6, (name, err, np.abs(ref).max())
+    assert cos >= cos_min, (name, cos)
+
+
+@pytest.mark.parametrize("model", ["llama-2-7b", "mistral-7b"])
+def test_stage_at_baseline_dimensions_vs_oracle(model):
+    """One decoder layer at the BASELINE dimensions (d 4096, 32 heads of 128, F 11008 / 14336 with 8 kv heads),
+    160-token prefill (the CTA-pair kernels with fused epilogues) + 2 decode steps (the fused decode chain) against
+    oracle.stage_forward.  Tolerances: L1 bit-exact before the first attention (unfused trace run), L2
+    max-abs <= 2^-5 max|ref| and cosine >= 0.9995 per tensor (tests/test_stage_gpu.py explains why not tighter)."""
+    import dataclasses
+    import b200stage
+    from b200stage import weights
+    from b200stage.stage import Stage
+    cfg = dataclasses.replace(b200stage.get_config(model), n_layers=1, vocab=2048, window=min(b200stage.get_config(model).window, 96))
+    seed, T, S = 2, 160, 192
+    osw = weights.to_numpy(weights.build_stage_weights(cfg, 0, 1, True, False, seed, "cpu"))
+    stage = Stage.load(cfg, 0, 1, first=True, last=False, device=DEV, seed=seed)
+    ids = np.random.default_rng(5).integers(0, cfg.vocab, T)
+    cos, sin = O.rope_table(cfg.head_dim, cfg.max_pos, cfg.rope_theta, cfg.rope_scaling)
+    ocache = O.KVCacheOracle(1, 1, cfg.n_kv_heads, S, cfg.head_dim)
+    otrace = []
+    ref = O.stage_forward(ids, osw, cfg.kernel_cfg(), ocache, np.zeros(T, np.int64), np.arange(T), cos, sin, otrace)
+    # unfused run with the trace: L1 bit-exact on layer 0, L2 per tensor
+    cache = stage.new_kv_cache(1, S)
+    trace = []
+    got_u = stage.forward(torch.from_numpy(ids).to(DEV), cache, np.arange(T), trace=trace)
+    assert np.array_equal(n(trace[0]["q1"]), otrace[0]["q1"])
+    assert np.array_equal(n(trace[0]["s1"]), otrace[0]["s1"])
+    assert np.array_equal(bits(trace[0]["qkv"]), otrace[0]["qkv"].view(np.uint16))
+    for k in ("attn", "h1", "gu", "h2"):
+        _close(n(trace[0][k]), otrace[0][k].reshape(trace[0][k].shape), k)
+    # fused run (no trace): identical to the unfused one, hence the same distance to the oracle
+    cache_f = stage.new_kv_cache(1, S)
+    got_f = stage.forward(torch.from_numpy(ids).to(DEV), cache_f, np.arange(T))
+    assert torch.equal(got_f, got_u)
+    assert torch.equal(cache_f.k, cache.k) and torch.equal(cache_f.v, cache.v)
+    _close(n(got_f), ref, "hidden after prefill")
+    _close(n(cache_f.k[0, 0, :, :T]), ocache.k[0, 0, :, :T], "kcache")
+    _close(n(cache_f.v[0, 0, :, :T]), ocache.v[0, 0, :, :T], "vcache")
+    # two decode steps through the fused decode chain
+    r = np.random.default_rng(6)
+    for step in range(2):
+        tok = r.integers(0, cfg.vocab, 1)
+        ref_d = O.stage_forward(tok, osw, cfg.kernel_cfg(), ocache, np.zeros(1, np.int64), np.array([T + step]), cos, sin)
+        got_d = stage.forward(torch.from_numpy(tok).to(DEV), cache_f, [T + step])
+        _close(n(got_d), ref_d, f"decode step {step}")
