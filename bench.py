@@ -107,35 +107,65 @@ class Clocks:
 # reference arm / cpu baseline: the reference's own CPU int8 path (Code/C-DAC Server/try.py:198-206,
 # :238-260): HF AutoModelForCausalLM -> quantize_dynamic({nn.Linear}, qint8) -> generate.
 # ----------------------------------------------------------------------------------------------
-def cpu_reference_run(model: str, prompt: int, new: int, steps: int, warmup: int):
-    """The reference's CPU int8 path on the host cores: HF Llama (random init from the model's
-    config; no checkpoints offline) -> torch.quantization.quantize_dynamic({nn.Linear}, qint8)
-    [try.py:204-205] -> greedy generate [try.py:247-256 with do_sample=False].
+def _cpu_llama_int8(cfg, n_layers: int):
+    """HF LlamaForCausalLM at `n_layers` of the model's config -> quantize_dynamic({nn.Linear}, qint8) [try.py:204-205].
+    No checkpoint exists offline, so the weights are random: one decoder layer is drawn (N(0, 0.02), HF's default
+    init) and copied into the others -- the int8 kernels' time does not depend on the values, and drawing 6.5 G
+    normals on the host would take longer than the measurement itself."""
+    import torch
+    from transformers import LlamaConfig, LlamaForCausalLM
+    hc = LlamaConfig(vocab_size=cfg.vocab, hidden_size=cfg.d_model, intermediate_size=cfg.ffn, num_hidden_layers=n_layers,
+                     num_attention_heads=cfg.n_heads, num_key_value_heads=cfg.n_kv_heads, head_dim=cfg.head_dim,
+                     max_position_embeddings=max(4096, cfg.max_pos), rms_norm_eps=cfg.eps, rope_theta=cfg.rope_theta,
+                     tie_word_embeddings=False)
+    with torch.device("meta"):
+        m = LlamaForCausalLM(hc)
+    m = m.to_empty(device="cpu")
+    g = torch.Generator().manual_seed(0)
+    with torch.no_grad():
+        first = m.model.layers[0]
+        for name, p_ in first.named_parameters():
+            if p_.dim() == 1:
+                p_.fill_(1.0)
+            else:
+                p_.normal_(0.0, 0.02, generator=g)
+        sd = first.state_dict()
+        for layer in m.model.layers[1:]:
+            layer.load_state_dict(sd)
+        m.model.embed_tokens.weight.normal_(0.0, 0.02, generator=g)
+        m.lm_head.weight.normal_(0.0, 0.02, generator=g)
+        m.model.norm.weight.fill_(1.0)
+        # buffers (rotary inv_freq) were created on the meta device: rebuild them
+        for mod in m.modules():
+            if hasattr(mod, "inv_freq") and hasattr(mod, "rope_init_fn"):
+                inv, _ = mod.rope_init_fn(mod.config, "cpu")
+                mod.inv_freq = inv
+                if hasattr(mod, "original_inv_freq"):
+                    mod.original_inv_freq = inv
+    m.eval()
+    return torch.quantization.quantize_dynamic(m, {torch.nn.Linear}, dtype=torch.qint8, inplace=True)     # try.py:205
 
-    Bounded sample of the bench workload (`prompt` prefill + `new` decode tokens): the model is
-    built at 2 and at 4 of its layers; for each, a `s_prompt`-token prefill (generate with one new
-    token) and `s_new` decode steps are timed separately; per-layer and fixed costs are separated
-    by the two depths and extrapolated linearly to the full depth; the workload time is then
-    composed as prompt x (prefill s/token) + new x (decode s/token)."""
+
+def cpu_reference_run(model: str, prompt: int, new: int, reps: int, warmup: int, depths=None):
+    """The reference's CPU int8 path on the host cores: HF Llama -> torch.quantization.quantize_dynamic({nn.Linear},
+    qint8) [try.py:204-205] -> greedy generate [try.py:247-256 with do_sample=False], on the bench's own shape:
+    a `prompt`-token prompt and `new` generated tokens, B = 1, all host threads.
+
+    depths = None: the full model, measured directly (`reps` generations after `warmup`, median).
+    depths = (a, b): a bounded sample for the in-line cpu_baseline of the GPU arm -- the same generation at a and b
+    of the model's layers, extended linearly in depth to the full model (stated in `sample`, `extrapolated` true)."""
     import warnings
     import torch
     warnings.filterwarnings("ignore")
-    from transformers import LlamaConfig, LlamaForCausalLM
     import importlib
     cfg = importlib.import_module("llm-for-distributed-egde-devices_b200").get_config(model)
     threads = os.cpu_count() or 1
     torch.set_num_threads(threads)
-    s_prompt, s_new = min(prompt, 256), min(max(new - 1, 1), 8)
-    t_pre, t_dec = {}, {}
-    for L in (2, 4):
-        hc = LlamaConfig(vocab_size=cfg.vocab, hidden_size=cfg.d_model, intermediate_size=cfg.ffn, num_hidden_layers=L,
-                         num_attention_heads=cfg.n_heads, num_key_value_heads=cfg.n_kv_heads,
-                         max_position_embeddings=4096, rms_norm_eps=cfg.eps, tie_word_embeddings=False)
-        torch.manual_seed(0)
-        m = LlamaForCausalLM(hc).eval()
-        m = torch.quantization.quantize_dynamic(m, {torch.nn.Linear}, dtype=torch.qint8)     # try.py:205
-        ids = torch.randint(0, cfg.vocab, (1, s_prompt), generator=torch.Generator().manual_seed(1234))
-        mask = torch.ones_like(ids)
+    ids = torch.randint(0, cfg.vocab, (1, prompt), generator=torch.Generator().manual_seed(1234))
+    mask = torch.ones_like(ids)
+
+    def measure(n_layers):
+        m = _cpu_llama_int8(cfg, n_layers)
 
         def gen(n):
             t0 = time.perf_counter()
@@ -143,29 +173,44 @@ def cpu_reference_run(model: str, prompt: int, new: int, steps: int, warmup: int
             return time.perf_counter() - t0
         pre, full = [], []
         with torch.no_grad():
-            for i in range(warmup + steps):
-                a1, a2 = gen(1), gen(1 + s_new)
+            for i in range(warmup + reps):
+                a1 = gen(1)              # prefill + first token
+                a2 = gen(new)            # the whole generation
                 if i >= warmup:
                     pre.append(a1)
                     full.append(a2)
-        t_pre[L] = statistics.median(pre)
-        t_dec[L] = max(statistics.median(full) - t_pre[L], 1e-9)
         del m
+        return statistics.median(pre), statistics.median(full), (max(full) - min(full)) / statistics.median(full)
 
-    def extrapolate(t):
-        per_layer = (t[4] - t[2]) / 2.0
-        fixed = max(t[2] - 2 * per_layer, 0.0)
-        return fixed + per_layer * cfg.n_layers
-    pre_tok = extrapolate(t_pre) / s_prompt          # seconds per prompt token, full depth
-    dec_tok = extrapolate(t_dec) / s_new             # seconds per generated token, full depth
-    t_full = prompt * pre_tok + new * dec_tok
-    return dict(value=(prompt + new) / t_full, unit=UNIT, cores=threads, kind="reference",
-                sample=(f"HF LlamaForCausalLM random-init + quantize_dynamic(qint8) [try.py:204-205], greedy generate; "
-                        f"prefill of {s_prompt} tokens and {s_new} decode steps timed separately at 2 and 4 of {cfg.n_layers} "
-                        f"layers (prefill {t_pre[2]:.2f}s/{t_pre[4]:.2f}s, decode {t_dec[2]:.2f}s/{t_dec[4]:.2f}s), extrapolated "
-                        f"linearly to {cfg.n_layers} layers: {1 / pre_tok:.1f} prefill tok/s, {1 / dec_tok:.2f} decode tok/s, "
-                        f"composed for {prompt} + {new} tokens ({t_full:.1f}s)"),
-                ms_per_step=t_full * 1e3, prefill_tokens_per_s=1 / pre_tok, decode_tokens_per_s=1 / dec_tok)
+    if depths is None:
+        t_pre, t_full, spread = measure(cfg.n_layers)
+        how = (f"all {cfg.n_layers} layers measured directly, median of {reps} generation(s) after {warmup} warm-up "
+               f"(spread {100 * spread:.1f} %)")
+        extrap = False
+    else:
+        a_, b_ = depths
+        pa, fa, _ = measure(a_)
+        pb, fb, _ = measure(b_)
+
+        def ext(ta, tb):
+            per_layer = (tb - ta) / (b_ - a_)
+            if per_layer <= 0.0:                 # timing noise at toy sizes: fall back to proportional scaling
+                return tb / b_ * cfg.n_layers
+            return max(ta - a_ * per_layer, 0.0) + per_layer * cfg.n_layers
+        t_pre, t_full = ext(pa, pb), ext(fa, fb)
+        how = (f"bounded sample: the same generation at {a_} and {b_} of {cfg.n_layers} layers ({fa:.2f}s / {fb:.2f}s), "
+               f"extended linearly in depth to {cfg.n_layers} layers")
+        extrap = True
+    t_dec = max(t_full - t_pre, 1e-9)
+    out = dict(value=(prompt + new) / t_full, unit=UNIT, cores=threads, kind="reference",
+               sample=(f"HF LlamaForCausalLM ({model} shape, random weights) + quantize_dynamic(qint8) [try.py:204-205], greedy "
+                       f"generate of {new} tokens after a {prompt}-token prompt, B=1, {threads} threads; {how}: "
+                       f"{prompt / t_pre:.1f} prefill tok/s, {(new - 1) / t_dec:.2f} decode tok/s, {t_full:.1f}s per generation"),
+               ms_per_step=t_full * 1e3, prefill_tokens_per_s=prompt / t_pre, decode_tokens_per_s=(new - 1) / t_dec,
+               extrapolated=extrap)
+    if depths is not None:
+        out["depths"] = list(depths)
+    return out
 
 
 def grpc_cpu_pipeline_run(steps: int = 3, warmup: int = 3) -> dict:
@@ -193,19 +238,43 @@ def grpc_config_on_gpu(torch, b2, dev, steps: int = 3, warmup: int = 3) -> dict:
             "workload": "gpt2 (124M) W8A8, 2 layer-range stages on one GPU, 128-token prompt + 32 greedy tokens, host ids in / host tokens out"}
 
 
+def workload_config(cfg_name: str, quant: str, n_prompts: int, P: int, NEW: int) -> dict:
+    """The `config` object of the JSON line: the same for both arms (the GPU arm adds how it ran it)."""
+    return {"workload": f"{cfg_name} {'W8A8' if quant == 'w8a8' else 'LLM.int8() mixed int8/fp16'} (random-init, seeded), "
+                        f"{n_prompts} prompt(s) x ({P} prefill + {NEW} greedy decode), B=1 per prompt"}
+
+
 def run_reference(a):
+    """The reference's own CPU implementation of the path, measured on the bench workload itself: the full-depth
+    model, the full prompt and all generated tokens.  One generation takes seconds to tens of seconds on the host,
+    so the repetitions actually timed are capped (and reported as `steps`); at N > 1 the workload is N independent
+    prompts, which the single CPU model would run one after the other: tokens/s is that of one prompt."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    r = cpu_reference_run(a.model, a.prompt, a.new, max(1, a.steps), max(1, min(a.warmup, 1)))
-    line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
-            "warmup": a.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+    reps, warm = max(1, min(a.steps, 3)), 1
+    import importlib
+    cfg = importlib.import_module("llm-for-distributed-egde-devices_b200").get_config(a.model)
+    try:
+        import psutil
+        need = cfg.linear_params_per_layer() * cfg.n_layers * 5.5 + 4e9      # fp32 model + int8 copy + slack
+        depths = None if psutil.virtual_memory().available > need else (cfg.n_layers // 4, cfg.n_layers // 2)
+    except Exception:
+        depths = None
+    r = cpu_reference_run(a.model, a.prompt, a.new, reps, warm, depths)
+    line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": a.gpus, "steps": reps,
+            "warmup": warm, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "int8", "data": "synthetic",
-            "config": {"workload": f"{a.model} W8A8, B=1, prompt {a.prompt} + {a.new} greedy tokens (CPU sample, see cpu_baseline.sample)"},
+            "config": workload_config(cfg.name, a.quant, a.gpus, a.prompt, a.new),
             "prefill_tokens_per_s": r["prefill_tokens_per_s"], "decode_tokens_per_s": r["decode_tokens_per_s"],
+            "extrapolated": r["extrapolated"], "requested_steps": a.steps, "requested_warmup": a.warmup,
+            "note": ("steps/warmup are the generations actually timed; ms_per_step is one prompt's generation -- with N > 1 "
+                     "prompts in the workload the CPU model runs them back to back at this same tokens/s"),
             "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    if not a.no_cpu_baseline:
+    if r.get("depths"):
+        line["depths"] = r["depths"]
+    if not a.no_cpu_baseline and a.gpus == 1:
         try:
             line["cpu_grpc_pipeline"] = grpc_cpu_pipeline_run()
         except Exception as e:
@@ -352,10 +421,9 @@ def run_ours(a):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8",
             "data": "synthetic",
-            "config": {"workload": f"{cfg.name} {'W8A8' if a.quant == 'w8a8' else 'LLM.int8() mixed int8/fp16'} (random-init, seeded), "
-                                   f"{n_prompts} prompt(s) x ({P} prefill in chunks of {CH} + "
-                                   f"{NEW} greedy decode), B=1 per prompt, {world} pipeline stage(s) x {n_layers_local} layers",
-                       "parallelism": f"pp{world}", "l2": "inputs larger than L2 (int8 weights 6.5 GB streamed per decode token)"},
+            "config": dict(workload_config(cfg.name, a.quant, n_prompts, P, NEW),
+                           run=f"prefill in chunks of {CH}, {world} pipeline stage(s) x {n_layers_local} layers",
+                           parallelism=f"pp{world}", l2="inputs larger than L2 (int8 weights 6.5 GB streamed per decode token)"),
             "prefill_tokens_per_s": n_prompts * P / (pre_ms / 1e3), "decode_tokens_per_s": dec_tok_s,
             "decode_hbm_frac_whole_step": (dec_bytes / 1e9) * dec_tok_s / (pk["hbm"] * world),
             "gpu_launches": launches,
@@ -363,9 +431,10 @@ def run_ours(a):
                     "d2h_bytes_per_step": n_prompts * NEW * 8},
             "roofline": roof, "roofline_prefill": roof_pre, "clocks": clk, "peaks": pk["which"],
         }
+        line.update(token_check(host_out, cfg.name, a.quant, P, NEW, bool(a.layers)))
         if not a.no_cpu_baseline and world == 1:
             try:
-                r = cpu_reference_run(a.model, P, NEW, 1, 1)
+                r = cpu_reference_run(a.model, P, NEW, 1, 1, depths=(max(1, cfg.n_layers // 8), max(2, cfg.n_layers // 4)))
                 line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
             except Exception as e:   # the baseline must not take the GPU number down with it
                 line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "reference",
@@ -380,6 +449,30 @@ def run_ours(a):
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
+    if line is not None and line.get("tokens_match_n1") is False:
+        raise SystemExit(f"generated tokens of prompt 0 differ from the stored single-GPU run ({line['token_key']})")
+
+
+GOLDEN_TOKENS = os.path.join(ROOT, "tests", "golden", "bench_tokens.json")
+
+
+def token_check(host_out, model: str, quant: str, P: int, NEW: int, truncated: bool) -> dict:
+    """crc32 of every prompt's generated ids (the last end-to-end step's D2H result) and, for prompt 0 -- the same
+    prompt at every N, since prompts are drawn in order from one seeded generator -- a comparison with the value a
+    single-GPU run of the same workload stored in tests/golden/bench_tokens.json: the N-stage NCCL pipeline must
+    decode exactly the tokens one GPU decodes."""
+    import zlib
+    sums = [zlib.crc32(row.numpy().tobytes()) for row in host_out]
+    out = {"token_checksums": sums, "tokens_match_n1": None}
+    key = f"{model}|{quant}|prompt{P}|new{NEW}|seed1234"
+    if not truncated and os.path.exists(GOLDEN_TOKENS):
+        with open(GOLDEN_TOKENS) as f:
+            gold = json.load(f)
+        if key in gold:
+            out["tokens_match_n1"] = bool(gold[key]["crc32_prompt0"] == sums[0])
+            out["tokens_first8_prompt0"] = [int(x) for x in host_out[0][:8]]
+    out["token_key"] = key
+    return out
 
 
 def roofline_pass(torch, ops, stage, cfg, pk, dev, chunk):

@@ -105,15 +105,19 @@ class Pipeline:
 
     @torch.no_grad()
     def generate(self, input_ids, max_new_tokens: int = 32, do_sample: bool = False, chunk: int = 512,
-                 max_seq: int | None = None, caches=None, **sample_kwargs):
-        """Greedy continuation of one prompt; returns prompt + new tokens (int64, on the device),
-        like ``model.generate(**inputs, max_new_tokens=...)[0]`` (models_quant_updated.py:84-95)."""
+                 max_seq: int | None = None, caches=None, eos_token_id=None, pad_token_id=None, **sample_kwargs):
+        """Continuation of one prompt; returns prompt + new tokens (int64, on the device), like
+        ``model.generate(**inputs, max_new_tokens=...)[0]`` (models_quant_updated.py:84-95): greedy, or with
+        do_sample=True the reference's temperature / top_k / top_p / repetition_penalty chain.
+        eos_token_id (int or list) stops the generation as HF does for one sequence: the result ends with the first
+        EOS token produced.  The decode loop stays asynchronous; the host looks for an EOS every 8 steps.
+        pad_token_id is accepted for call compatibility (one sequence is never padded).
+        Sampling note: top_k <= 0 ("off" in HF) or > 1024 is capped at 1024 candidates (b2_sample)."""
         temperature = float(sample_kwargs.pop("temperature", 1.0))
         top_k = int(sample_kwargs.pop("top_k", 50))
         top_p = float(sample_kwargs.pop("top_p", 1.0))
         rep = float(sample_kwargs.pop("repetition_penalty", 1.0))
         seed = int(sample_kwargs.pop("seed", 0))
-        sample_kwargs.pop("pad_token_id", None)          # accepted for call compatibility with HF; unused
         if sample_kwargs:
             raise TypeError(f"unsupported generate() arguments: {sorted(sample_kwargs)}")
         dev = self.stages[0].device
@@ -122,27 +126,38 @@ class Pipeline:
         max_seq = max_seq or min(self.cfg.max_pos, T + max_new_tokens)
         if T + max_new_tokens > max_seq:
             raise ValueError("prompt + max_new_tokens exceeds max_seq")
+        eos = None
+        if eos_token_id is not None:
+            eos = torch.as_tensor([eos_token_id] if isinstance(eos_token_id, int) else list(eos_token_id),
+                                  dtype=torch.int64, device=dev)
         caches = caches or self.pooled_caches(1, max_seq)
         out = torch.empty((T + max_new_tokens,), dtype=torch.int64, device=dev)
         out[:T] = ids
         lg = self.prefill(ids, caches, 0, 0, chunk)
         hist2d = out.view(1, -1)
         hlen = torch.empty((1,), dtype=torch.int32, device=dev) if do_sample else None
+        n_done = max_new_tokens
         for i in range(max_new_tokens):
             tok = out[T + i: T + i + 1]
-            lgd = lg.view(1, -1).to(dev) if lg.device != dev else lg.view(1, -1)
-            if do_sample:
-                # the reference's call: do_sample=True, temperature, top_k, top_p, repetition_penalty
-                # (models_quant_updated.py:84-93); the penalty sees prompt + everything generated so far
-                hlen.fill_(T + i)
-                ops.sample(lgd, temperature=temperature, top_k=top_k, top_p=top_p, repetition_penalty=rep, seed=seed,
-                           step=i, history=hist2d, hist_len=hlen, out=tok)
-            else:
-                ops.argmax(lgd, out=tok)
+            with torch.cuda.device(dev):
+                lgd = lg.view(1, -1).to(dev) if lg.device != dev else lg.view(1, -1)
+                if do_sample:
+                    # the reference's call: do_sample=True, temperature, top_k, top_p, repetition_penalty
+                    # (models_quant_updated.py:84-93); the penalty sees prompt + everything generated so far
+                    hlen.fill_(T + i)
+                    ops.sample(lgd, temperature=temperature, top_k=top_k, top_p=top_p, repetition_penalty=rep, seed=seed,
+                               step=i, history=hist2d, hist_len=hlen, out=tok)
+                else:
+                    ops.argmax(lgd, out=tok)
             self.stages[-1].launches += 1
+            if eos is not None and (i % 8 == 7 or i + 1 == max_new_tokens):
+                hit = torch.isin(out[T: T + i + 1], eos).nonzero()
+                if hit.numel():
+                    n_done = int(hit[0]) + 1
+                    break
             if i + 1 < max_new_tokens:
                 lg = self.decode_step(tok, caches, [T + i])
-        return out
+        return out[: T + n_done]
 
     @torch.no_grad()
     def logits(self, input_ids, chunk: int = 512):

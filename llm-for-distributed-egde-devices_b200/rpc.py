@@ -271,9 +271,13 @@ class StageServicer:
                     raise RuntimeError("too many open requests; release one with an empty tensor")
                 c = self.caches[rid] = self.free.pop() if self.free else st.new_kv_cache(1, self.max_seq)
             T, p0 = int(arr.shape[0]), int(c.lens[0])
-            x = torch.from_numpy(arr.copy()).to(st.device)
-            y = st.forward(x, c, np.arange(p0, p0 + T), logits="last" if st.last else "none")
-            out = y.view(1, -1).float().cpu().numpy() if st.last else y.cpu().numpy()
+            import contextlib
+            on_gpu = torch.device(st.device).type == "cuda"      # (tests drive the servicer with a CPU stand-in stage)
+            # gRPC pool threads start with device 0 current
+            with (torch.cuda.device(st.device) if on_gpu else contextlib.nullcontext()):
+                x = torch.from_numpy(arr.copy()).to(st.device)
+                y = st.forward(x, c, np.arange(p0, p0 + T), logits="last" if st.last else "none")
+                out = y.view(1, -1).float().cpu().numpy() if st.last else y.cpu().numpy()
         return encode_tensor(out, rid)
 
 

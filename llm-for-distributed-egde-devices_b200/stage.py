@@ -406,6 +406,13 @@ class Stage:
         return pos, rows, T, decode
 
     def forward(self, x, kv_cache: KVCache, positions, seq_ids=None, logits: str = "last", out=None, trace=None):
+        """Run this stage's layers over T tokens (eager launches), on this stage's device whatever device is
+        current in the calling thread (one process may hold stages on several GPUs; gRPC handler threads start
+        with device 0 current).  See `_forward` for the arguments."""
+        with torch.cuda.device(self.device):
+            return self._forward(x, kv_cache, positions, seq_ids, logits, out, trace)
+
+    def _forward(self, x, kv_cache: KVCache, positions, seq_ids=None, logits: str = "last", out=None, trace=None):
         """Run this stage's layers over T tokens (eager launches).
 
         positions : host ints [T] (list / numpy / CPU tensor).
@@ -496,7 +503,8 @@ class GraphRunner:
         self.max_len = 0
         if decode:
             self.dseq = self.buf.seq[:T]
-            self.dseq.copy_(torch.tensor(rows, dtype=torch.int32))
+            with torch.cuda.device(dev):
+                self.dseq.copy_(torch.tensor(rows, dtype=torch.int32))
             self.dlens = self.buf.lens[:T]
             self.max_len = kv_cache.max_seq      # split count fixed for the whole graph lifetime
             nb = ops.decode_attn_workspace_bytes(T, cfg.n_heads, cfg.n_kv_heads, cfg.head_dim, self.max_len, cfg.window)
@@ -546,14 +554,16 @@ class GraphRunner:
     def set_positions(self, positions):
         pos = np.asarray(positions, dtype=np.int64).reshape(-1)
         self.host_pos = pos.copy()
-        self.dpos.copy_(torch.from_numpy(pos.astype(np.int32)))
-        if self.dlens is not None:
-            self.dlens.copy_(torch.from_numpy((pos + 1).astype(np.int32)))
+        with torch.cuda.device(self.stage.device):
+            self.dpos.copy_(torch.from_numpy(pos.astype(np.int32)))
+            if self.dlens is not None:
+                self.dlens.copy_(torch.from_numpy((pos + 1).astype(np.int32)))
 
     def replay(self):
         """Replay on the state the graph itself maintains (input already in `self.x`, positions
         advanced by the previous replay): the per-tick path of DistPipeline's decode stream."""
-        self.graph.replay()
+        with torch.cuda.device(self.stage.device):      # the graph launches on the current device's current stream
+            self.graph.replay()
         self.stage.launches += self.n_launch
         lens = self.cache.lens
         for r_, p_ in zip(self.rows, self.host_pos.tolist()):
@@ -572,9 +582,10 @@ class GraphRunner:
                 self.set_positions(p)
         if int(self.host_pos.max()) >= self.cache.max_seq:
             raise ValueError("position beyond the KV cache capacity")
-        if x is not None and x.data_ptr() != self.x.data_ptr():
-            self.x.copy_(x.view(self.x.shape), non_blocking=True)
-        self.graph.replay()
+        with torch.cuda.device(self.stage.device):
+            if x is not None and x.data_ptr() != self.x.data_ptr():
+                self.x.copy_(x.view(self.x.shape), non_blocking=True)
+            self.graph.replay()
         self.stage.launches += self.n_launch
         rows = self.rows if self.decode else [self.rows[0]] * self.T
         for r_, p_ in zip(rows, self.host_pos.tolist()):
