@@ -302,6 +302,14 @@ int b2_lm_head(const void* x, const void* W, float* logits, int M, int V, int d,
  * Replaces: the greedy (do_sample=False) token selection of `generate`. */
 int b2_argmax(const float* logits, long long* out, int T, int V, void* stream);
 
+/* Confidence score of a forward pass: out[0] = mean over the T rows of the largest softmax probability,
+ * i.e. mean_t 1 / sum_v exp(logits[t,v] - max_v logits[t,v]).  logits [T, ld >= V] fp32; row_pmax [T] fp32 scratch
+ * (receives the per-row value); out [1] fp32.  Exponentials in the pinned fp32 sequence, sums in fp64 in a fixed
+ * order (oracle/w8a8.py confidence).
+ * Replaces: `torch.softmax(logits, dim=-1).max(dim=-1).values.mean()` of confidence_score
+ * (Code/Quantised Models/models_quant_updated.py:63-70). */
+int b2_confidence(const float* logits, long long ld, float* row_pmax, float* out, int T, int V, void* stream);
+
 /* Sampling with the reference's real generate kwargs (do_sample=True; temperature, top_k, top_p,
  * repetition_penalty: Code/Quantised Models/models_quant_updated.py:84-93, Code/others/config.yaml:3-7).
  * logits [B, ld >= V] fp32; history [B, hist_ld] int64 = every token id seen so far per row (prompt +

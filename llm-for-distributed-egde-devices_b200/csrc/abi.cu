@@ -57,6 +57,7 @@ int fused_linear(const void*, long long, int, const void*, const void*, const fl
                  const void*, long long, const void*, long long, cudaStream_t);
 int embed(const long long*, const int*, const void*, const void*, void*, int, int, int, cudaStream_t);
 int argmax_rows(const float*, long long*, int, int, cudaStream_t);
+int confidence(const float*, long long, float*, float*, int, int, cudaStream_t);
 }  // namespace b2
 
 #define ST(s) reinterpret_cast<cudaStream_t>(s)
@@ -120,6 +121,9 @@ int b2_gemm_w8a8_sched(const int8_t* A, const int8_t* W, const float* a_scale, c
   if (schedule == 0 && b2::gemm2_supported(M, N, K))
     return b2::gemm2_plain(A, W, a_scale, w_scale, bias, residual, out, acc_dump, M, N, K, ST(stream));
   return b2::gemm_w8a8(A, W, a_scale, w_scale, bias, residual, out, acc_dump, M, N, K, schedule, ST(stream));
+}
+int b2_confidence(const float* logits, long long ld, float* row_pmax, float* out, int T, int V, void* stream) {
+  return b2::confidence(logits, ld, row_pmax, out, T, V, ST(stream));
 }
 int b2_gemm_gated_act(const int8_t* A, const int8_t* W, const float* a_scale, const float* w_scale, const void* bias,
                       const float* out_smooth, float* y32, float* amax, int M, int F, int K, int act, void* stream) {

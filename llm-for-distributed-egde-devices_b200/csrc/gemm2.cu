@@ -14,13 +14,13 @@
 // shared memory, and the ring is 6 stages of 32 KB instead of 4 of 48 KB.
 //
 // One cluster = 2 CTAs (ranks 0 = leader, 1 = peer), 384 threads each:
-//   warp 0   TMA producer (each CTA loads its own A rows and its own half of the weight tile; both signal the
-//            LEADER's `full` barrier -- cp.async.bulk.tensor ... .cta_group::2)
-//   warp 1   MMA issuer (leader only): waits `full`, issues 4 x tcgen05.mma per 128-byte k-block, commits to the
-//            `empty` barrier of BOTH CTAs (tcgen05.commit ... multicast::cluster) and, per tile, to `tfull` of both
-//   warp 2   TMEM allocator (512 columns = two 256-column accumulator buffers, allocated by the pair)
-//   warps 4..11  epilogue: TMEM lane quadrant = warp % 4, column half = (warp - 4) / 4; arrive on the leader's
+//   warps 0..7  epilogue: TMEM lane quadrant = warp % 4, column half = warp / 4; arrive on the leader's
 //            `tempty` when a buffer is drained (remote mbarrier arrive from the peer)
+//   warp 8   TMA producer (each CTA loads its own A rows and its own half of the weight tile; both signal the
+//            LEADER's `full` barrier -- cp.async.bulk.tensor ... .cta_group::2)
+//   warp 9   MMA issuer (leader only): waits `full`, issues 4 x tcgen05.mma per 128-byte k-block, commits to the
+//            `empty` barrier of BOTH CTAs (tcgen05.commit ... multicast::cluster) and, per tile, to `tfull` of both
+//   warp 10  TMEM allocator (512 columns = two 256-column accumulator buffers, allocated by the pair)
 // The accumulator of CTA r holds rows [128 r, 128 r + 128) of the pair's tile and all 256 columns; columns
 // [0,128) come from the leader's weight rows, [128,256) from the peer's.
 //
@@ -41,6 +41,11 @@ constexpr int G2_BM = 256;       // rows per CTA pair (128 per CTA)
 constexpr int G2_BN = 256;       // columns per tile
 constexpr int G2_BK = 128;       // int8 per k-block = one 128-byte swizzle atom
 constexpr int G2_THREADS = 384;
+// Warp roles.  The epilogue warps take the LOW warp ids: when several warps of a scheduler are ready the SM issues
+// the highest warp id first, and an ALU-heavy epilogue (SiLU, rotary) is ready nearly every cycle -- with the
+// producer and the MMA issuer below it they waited for issue slots and the tensor pipe ran dry (measured: the gated
+// epilogue cost 14 % of the GEMM with the control warps at ids 0..2).
+constexpr int G2_WARP_TMA = 8, G2_WARP_MMA = 9, G2_WARP_ALLOC = 10;     // warps 0..7 = epilogue, 11 idle
 constexpr int G2_TMEM_COLS = 512;
 constexpr int G2_STAGE_BYTES = 128 * G2_BK * 2;   // per CTA: A 128 x 128 B + W 128 x 128 B
 
@@ -177,23 +182,23 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   const int t_first = blockIdx.x >> 1, t_step = gridDim.x >> 1;
   const int kblocks = (p.K + G2_BK - 1) / G2_BK;
 
-  if (warp == 0 && lane == 0) {
+  if (warp == G2_WARP_TMA && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
   }
-  if (warp == 1 && lane == 0) {
+  if (warp == G2_WARP_MMA && lane == 0) {
     for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 16); }   // 8 epilogue warps x 2 CTAs
     mbar_fence_init();
   }
-  if (warp == 2) tmem_alloc_pair(tmem_slot);
+  if (warp == G2_WARP_ALLOC) tmem_alloc_pair(tmem_slot);
   tc_fence_before();
   __syncthreads();
   cluster_sync();                  // both CTAs' barriers exist before any remote arrive / multicast commit
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp == 0) {
+  if (warp == G2_WARP_TMA) {
     // ===================== TMA producer (both CTAs) =====================
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
@@ -215,7 +220,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         }
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == G2_WARP_MMA) {
     // ===================== MMA issuer (leader only) =====================
     if (rank == 0 && lane == 0) {
       constexpr uint32_t idesc = umma_idesc(IDESC_FMT_S32, IDESC_S8, IDESC_S8, G2_BM, G2_BN);
@@ -242,10 +247,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         umma_commit_pair(&tfull_bar[buf], 3);
       }
     }
-  } else if (warp >= 4) {
+  } else if (warp < 8) {
     // ===================== epilogue (both CTAs) =====================
     const int quad = warp & 3;
-    const int half = (warp - 4) >> 2;
+    const int half = warp >> 2;
     int it = 0;
     for (int t = t_first; t < num_tiles; t += t_step, ++it) {
       const int mt = t % m_tiles, nt = t / m_tiles;
@@ -399,7 +404,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   tc_fence_before();
   __syncthreads();
   cluster_sync();                  // the leader's MMAs read the peer's shared memory and write its TMEM
-  if (warp == 2) tmem_dealloc_pair(tmem_base);
+  if (warp == G2_WARP_ALLOC) tmem_dealloc_pair(tmem_base);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -508,8 +513,15 @@ static int g2_launch(const int8_t* A, const int8_t* W, long long w_rows, const G
 
 static inline bool g2_mis(const void* q) { return q && (reinterpret_cast<uintptr_t>(q) & 15); }
 
-// shapes the pair kernel takes (the caller falls back to the single-CTA kernel otherwise)
-bool gemm2_supported(int M, int N, int K) { return M > 128 && N >= 256 && (N & 31) == 0 && K >= 128 && (K & 15) == 0; }
+// Shapes for which the default schedule takes the pair kernel (the single-CTA kernel otherwise).  Measured on B200
+// (tools/gemm_bench.py, Llama-2-7B shapes): with at least ~48 pair tiles the pair kernel wins (M = 256: qkv 21.6 vs
+// 28.6 us, gate_up 33.6 vs 38.8; M = 2048: 318 vs 409 us for the four linears), with 16-32 tiles (N = 4096 at
+// M = 256 / 512) the 128 x 128 single-CTA tiles fill more SMs (o 17.6 / 18.7 vs 21.6 / 22.1 us).
+bool gemm2_supported(int M, int N, int K) {
+  if (!(M > 128 && N >= 256 && (N & 31) == 0 && K >= 128 && (K & 15) == 0)) return false;
+  const long long tiles = (long long)((M + G2_BM - 1) / G2_BM) * ((N + G2_BN - 1) / G2_BN);
+  return tiles >= 40;
+}
 
 int gemm2_plain(const int8_t* A, const int8_t* W, const float* a_scale, const float* w_scale, const void* bias,
                 const void* residual, void* out, int32_t* acc_dump, int M, int N, int K, cudaStream_t st) {

@@ -99,10 +99,69 @@ int argmax_rows(const float* logits, long long* out, int T, int V, cudaStream_t 
   return launch_status();
 }
 
+// ---------------------------------------------------------------------------------------------
+// confidence score: mean over rows of the largest softmax probability = mean_t 1 / sum_v exp(x[t,v] - max_v x[t,v])
+// (the reference's confidence_score: softmax -> max over the vocabulary -> mean over positions,
+// Code/Quantised Models/models_quant_updated.py:63-70).  One CTA per row: row maximum (exact), then the
+// exponentials in the pinned fp32 sequence (exp_det) summed in fp64; a second one-CTA launch averages the rows in
+// fp64.  Both reductions run in a fixed order, so the result is reproducible run to run.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(512)
+row_pmax_kernel(const float* __restrict__ logits, long long ld, float* __restrict__ pmax, int V) {
+  __shared__ float smax[16];
+  __shared__ double ssum[16];
+  const float* row = logits + (long long)blockIdx.x * ld;
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  float m = -INFINITY;
+  for (int i = threadIdx.x; i < V; i += blockDim.x) m = fmaxf(m, row[i]);
+  m = warp_max(m);
+  if (l == 0) smax[w] = m;
+  __syncthreads();
+  m = smax[0];
+#pragma unroll
+  for (int i = 1; i < 16; ++i) m = fmaxf(m, smax[i]);
+  double s = 0.0;
+  for (int i = threadIdx.x; i < V; i += blockDim.x) s += (double)exp_det(sub_rn(row[i], m));
+  s = warp_sum_d(s);
+  if (l == 0) ssum[w] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) t += ssum[i];
+    pmax[blockIdx.x] = (float)(1.0 / t);
+  }
+}
+__global__ void __launch_bounds__(512) mean_rows_kernel(const float* __restrict__ v, float* __restrict__ out, int T) {
+  __shared__ double ssum[16];
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  double s = 0.0;
+  for (int i = threadIdx.x; i < T; i += blockDim.x) s += (double)v[i];
+  s = warp_sum_d(s);
+  if (l == 0) ssum[w] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) t += ssum[i];
+    out[0] = (float)(t / (double)T);
+  }
+}
+
+int confidence(const float* logits, long long ld, float* row_pmax, float* out, int T, int V, cudaStream_t st) {
+  if (!logits || !row_pmax || !out) return ERR_NULL_PTR;
+  if (T <= 0 || V <= 0 || ld < V) return ERR_BAD_SHAPE;
+  row_pmax_kernel<<<T, 512, 0, st>>>(logits, ld, row_pmax, V);
+  mean_rows_kernel<<<1, 512, 0, st>>>(row_pmax, out, T);
+  return launch_status();
+}
+
 int init_misc() {
   cudaFuncAttributes fa;
   bool ok = cudaFuncGetAttributes(&fa, embed_kernel) == cudaSuccess;
   ok &= cudaFuncGetAttributes(&fa, argmax_kernel) == cudaSuccess;
+  ok &= cudaFuncGetAttributes(&fa, row_pmax_kernel) == cudaSuccess;
+  ok &= cudaFuncGetAttributes(&fa, mean_rows_kernel) == cudaSuccess;
   return ok ? OK : ERR_ARCH;
 }
 

@@ -395,6 +395,19 @@ def argmax(logits, out=None):
     return o
 
 
+def confidence(logits):
+    """logits [T,V] fp32 -> (mean over rows of the largest softmax probability [1] fp32, per-row values [T]).
+    b2_confidence."""
+    _cuda(logits)
+    if logits.dtype != torch.float32:
+        raise ValueError("confidence needs fp32 logits")
+    T, V = logits.shape
+    pm = torch.empty((T,), dtype=torch.float32, device=logits.device)
+    out = torch.empty((1,), dtype=torch.float32, device=logits.device)
+    check(_abi.lib().b2_confidence(ptr(logits), logits.stride(0), ptr(pm), ptr(out), T, V, stream_handle()), "b2_confidence")
+    return out, pm
+
+
 def sample(logits, *, temperature=1.0, top_k=50, top_p=1.0, repetition_penalty=1.0, seed=0, step=0, history=None,
            hist_len=None, step_tensor=None, out=None):
     """logits [B,V] fp32 -> sampled ids int64 [B] with HF's processor chain (repetition penalty ->

@@ -470,6 +470,17 @@ def lm_head(hn16, w16):
     return (np.asarray(hn16, f16).astype(f32) @ np.asarray(w16, f16).astype(f32).T).astype(f32)
 
 
+def confidence(logits) -> np.float32:
+    """mean over positions of the largest softmax probability (the reference's confidence_score,
+    models_quant_updated.py:63-70: softmax(logits) -> max over V -> mean over positions) as kernel b2_confidence
+    computes it: exp_det of (x - rowmax) in fp32, row sums and the final mean in fp64."""
+    x = np.asarray(logits, dtype=f32)
+    m = x.max(axis=-1, keepdims=True)
+    e = exp_det((x - m).astype(f32))
+    p = (1.0 / e.astype(np.float64).sum(axis=-1)).astype(f32)
+    return f32(p.astype(np.float64).sum() / p.shape[0])
+
+
 def stage_forward(x, sw, cfg, cache, seq_ids, positions, cos, sin, trace=None, logits_rows=None):
     """Forward over a contiguous layer range (the build-defined Stage contract).
 

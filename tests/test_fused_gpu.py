@@ -84,7 +84,7 @@ def test_fused_plain_linear_exact_and_zeroing(M, N, K):
 
 
 @pytest.mark.parametrize("M", [1, 3, 8])
-@pytest.mark.parametrize("d,F", [(4096, 11008), (2048, 5632), (256, 512)])
+@pytest.mark.parametrize("d,F", [(4096, 11008), (2048, 5632), (256, 512), (4096, 14336), (5120, 13824)])
 def test_fused_gated_mlp_exact(M, d, F):
     """norm -> gate_up GEMV with act epilogue -> y32/amax -> down GEMV, against the oracle's
     norm_quant -> gemm -> act_mul_quant -> gemm chain."""
@@ -146,7 +146,8 @@ def test_fused_decode_equals_unfused_decode(model):
 
 
 @pytest.mark.parametrize("M", [1, 3, 8])
-@pytest.mark.parametrize("H,KV,hd,d", [(4, 4, 64, 256), (8, 2, 64, 512), (32, 8, 128, 1024)])
+@pytest.mark.parametrize("H,KV,hd,d", [(4, 4, 64, 256), (8, 2, 64, 512), (32, 8, 128, 1024), (32, 8, 128, 4096),
+                                       (40, 40, 128, 5120)])
 def test_fused_qkv_rope_append_exact(M, H, KV, hd, d):
     """qkv GEMV with rotary + KV append in the epilogue == oracle norm_quant -> gemm -> apply_rope
     -> cache write, bit for bit (q columns of the output buffer, k/v rows of the caches)."""

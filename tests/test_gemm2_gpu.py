@@ -268,12 +268,22 @@ def test_stage_at_baseline_dimensions_vs_oracle(model):
     assert torch.equal(got_f, got_u)
     assert torch.equal(cache_f.k, cache.k) and torch.equal(cache_f.v, cache.v)
     _close(n(got_f), ref, "hidden after prefill")
-    _close(n(cache_f.k[0, 0, :, :T]), ocache.k[0, 0, :, :T], "kcache")
-    _close(n(cache_f.v[0, 0, :, :T]), ocache.v[0, 0, :, :T], "vcache")
-    # two decode steps through the fused decode chain
+    # one layer: k and v come from embeddings -> norm -> GEMM -> RoPE only, all bit-exact steps
+    assert np.array_equal(bits(cache_f.k[0, 0, :, :T]), ocache.k[0, 0, :, :T].view(np.uint16)), "k cache not bit-exact"
+    assert np.array_equal(bits(cache_f.v[0, 0, :, :T]), ocache.v[0, 0, :, :T].view(np.uint16)), "v cache not bit-exact"
+    # two decode steps: the unfused chain with a trace (L1 exact up to attention, L2 after it) and the fused decode
+    # chain, which must reproduce the unfused one bit for bit
     r = np.random.default_rng(6)
     for step in range(2):
         tok = r.integers(0, cfg.vocab, 1)
-        ref_d = O.stage_forward(tok, osw, cfg.kernel_cfg(), ocache, np.zeros(1, np.int64), np.array([T + step]), cos, sin)
+        odt = []
+        ref_d = O.stage_forward(tok, osw, cfg.kernel_cfg(), ocache, np.zeros(1, np.int64), np.array([T + step]), cos, sin, odt)
+        tr = []
+        got_u = stage.forward(torch.from_numpy(tok).to(DEV), cache, [T + step], trace=tr)
+        assert np.array_equal(n(tr[0]["q1"]), odt[0]["q1"]) and np.array_equal(n(tr[0]["s1"]), odt[0]["s1"])
+        assert np.array_equal(bits(tr[0]["qkv"]), odt[0]["qkv"].view(np.uint16))
+        for k in ("attn", "h1", "gu", "h2"):
+            _close(n(tr[0][k]), odt[0][k].reshape(tr[0][k].shape), f"decode step {step} {k}")
         got_d = stage.forward(torch.from_numpy(tok).to(DEV), cache_f, [T + step])
+        assert torch.equal(got_d, got_u), f"fused decode step {step} differs from the unfused chain"
         _close(n(got_d), ref_d, f"decode step {step}")

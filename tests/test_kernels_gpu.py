@@ -215,7 +215,8 @@ def _attn_tol(got, ref):
 
 @pytest.mark.parametrize("H,KV,hd,B,S,window", [
     (4, 4, 64, 2, 70, 0), (8, 2, 64, 3, 300, 0), (32, 32, 128, 1, 1500, 0), (32, 8, 128, 2, 2100, 0),
-    (32, 4, 64, 1, 513, 0), (8, 2, 128, 2, 700, 256), (4, 4, 64, 1, 1, 0), (40, 40, 128, 4, 33, 0)])
+    (32, 4, 64, 1, 513, 0), (8, 2, 128, 2, 700, 256), (4, 4, 64, 1, 1, 0), (40, 40, 128, 4, 33, 0),
+    (32, 8, 128, 1, 161, 96), (32, 8, 128, 1, 8000, 4096)])
 def test_decode_attn(H, KV, hd, B, S, window):
     r = rng(H * 3 + S)
     Smax = S + 8

@@ -134,11 +134,31 @@ def test_batched_decode_matches_single():
         _close(lg[b].cpu().numpy(), one[0].cpu().numpy(), f"row{b}")
 
 
-def test_confidence_score_runs():
+def test_confidence_score_matches_oracle():
+    """confidence_score (models_quant_updated.py:63-70): the [S,V] softmax -> max -> mean reduction runs in
+    b2_confidence; its value is checked against the oracle's statement of the same reduction on the same logits
+    (fp64 sums in a different order: 1e-6 relative, normally identical) and against torch's softmax."""
+    from b200stage import ops
     cfg = b200stage.get_config("tiny-llama-test")
     pipe = Pipeline.load(cfg, 1, seed=0)
-    c = confidence_score(pipe, np.arange(30) % cfg.vocab)
+    ids = np.arange(30) % cfg.vocab
+    c = confidence_score(pipe, ids)
+    lg = pipe.logits(ids)
+    ref = float(O.confidence(lg.cpu().numpy()))
+    assert abs(c - ref) <= 1e-6 * ref, (c, ref)
+    tref = float(torch.softmax(lg.float(), dim=-1).max(dim=-1).values.mean().item())
+    assert abs(c - tref) <= 1e-5 * tref, (c, tref)
     assert 0.0 < c <= 1.0
+    # wide rows, a padded row pitch and extreme logits
+    r = np.random.default_rng(3)
+    x = (r.standard_normal((37, 32000)) * 6).astype(np.float32)
+    x[0, 5] = 80.0
+    x[1] = -3.0
+    xt = torch.from_numpy(np.pad(x, ((0, 0), (0, 16)))).to(DEV)[:, :32000]
+    out, pm = ops.confidence(xt) if xt.is_contiguous() else ops.confidence(xt.contiguous())
+    ref = float(O.confidence(x))
+    assert abs(float(out) - ref) <= 1e-6 * ref
+    assert abs(float(pm[1]) - 1.0 / 32000) <= 1e-6 / 32000 * 10
 
 
 def test_stage_refuses_cpu():
