@@ -302,6 +302,15 @@ int b2_lm_head(const void* x, const void* W, float* logits, int M, int V, int d,
  * Replaces: the greedy (do_sample=False) token selection of `generate`. */
 int b2_argmax(const float* logits, long long* out, int T, int V, void* stream);
 
+/* Greedy selection over one vocabulary shard (the lm_head split between two pipeline stages): logits [T, ld >= V]
+ * fp32 hold columns [idx_offset, idx_offset + V) of the full logits; out_idx [T] = idx_offset + row argmax (ties to
+ * the lowest index), out_val [T] fp32 = the row maximum (or NULL).  With other_val / other_idx ([T] each, both or
+ * neither) the row's winner is merged with another shard's (value, global index) under the same tie rule, so two
+ * shards reproduce b2_argmax over the whole row exactly.
+ * Replaces: the greedy token selection of `generate`, as b2_argmax. */
+int b2_argmax_shard(const float* logits, long long ld, long long* out_idx, float* out_val, long long idx_offset,
+                    const float* other_val, const long long* other_idx, int T, int V, void* stream);
+
 /* Confidence score of a forward pass: out[0] = mean over the T rows of the largest softmax probability,
  * i.e. mean_t 1 / sum_v exp(logits[t,v] - max_v logits[t,v]).  logits [T, ld >= V] fp32; row_pmax [T] fp32 scratch
  * (receives the per-row value); out [1] fp32.  Exponentials in the pinned fp32 sequence, sums in fp64 in a fixed

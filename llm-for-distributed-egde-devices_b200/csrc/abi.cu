@@ -58,6 +58,7 @@ int fused_linear(const void*, long long, int, const void*, const void*, const fl
 int embed(const long long*, const int*, const void*, const void*, void*, int, int, int, cudaStream_t);
 int argmax_rows(const float*, long long*, int, int, cudaStream_t);
 int confidence(const float*, long long, float*, float*, int, int, cudaStream_t);
+int argmax_shard(const float*, long long, long long*, float*, long long, const float*, const long long*, int, int, cudaStream_t);
 }  // namespace b2
 
 #define ST(s) reinterpret_cast<cudaStream_t>(s)
@@ -121,6 +122,10 @@ int b2_gemm_w8a8_sched(const int8_t* A, const int8_t* W, const float* a_scale, c
   if (schedule == 0 && b2::gemm2_supported(M, N, K))
     return b2::gemm2_plain(A, W, a_scale, w_scale, bias, residual, out, acc_dump, M, N, K, ST(stream));
   return b2::gemm_w8a8(A, W, a_scale, w_scale, bias, residual, out, acc_dump, M, N, K, schedule, ST(stream));
+}
+int b2_argmax_shard(const float* logits, long long ld, long long* out_idx, float* out_val, long long idx_offset,
+                    const float* other_val, const long long* other_idx, int T, int V, void* stream) {
+  return b2::argmax_shard(logits, ld, out_idx, out_val, idx_offset, other_val, other_idx, T, V, ST(stream));
 }
 int b2_confidence(const float* logits, long long ld, float* row_pmax, float* out, int T, int V, void* stream) {
   return b2::confidence(logits, ld, row_pmax, out, T, V, ST(stream));

@@ -44,10 +44,12 @@ int embed(const long long* ids, const int* positions, const void* table, const v
 
 // one CTA per row; ties resolve to the lowest index (torch.argmax / HF greedy convention)
 __global__ void __launch_bounds__(1024)
-argmax_kernel(const float* __restrict__ logits, long long* __restrict__ out, int V) {
+argmax_kernel(const float* __restrict__ logits, long long ld, long long* __restrict__ out, int V,
+              float* __restrict__ out_val, long long idx_offset, const float* __restrict__ other_val,
+              const long long* __restrict__ other_idx) {
   __shared__ float sv[32];
   __shared__ int si[32];
-  const float* row = logits + (long long)blockIdx.x * V;
+  const float* row = logits + (long long)blockIdx.x * ld;
   float best = -INFINITY;
   int bi = 0x7fffffff;
   auto take = [&](float v, int i) { if (v > best || (v == best && i < bi)) { best = v; bi = i; } };
@@ -87,7 +89,16 @@ argmax_kernel(const float* __restrict__ logits, long long* __restrict__ out, int
       const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
       if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
     }
-    if (l == 0) out[blockIdx.x] = bi == 0x7fffffff ? 0 : bi;
+    if (l == 0) {
+      long long idx = (bi == 0x7fffffff ? 0 : bi) + idx_offset;
+      if (other_val != nullptr) {          // merge with the winner of another vocabulary shard: same tie rule
+        const float ov = other_val[blockIdx.x];
+        const long long oi = other_idx[blockIdx.x];
+        if (ov > best || (ov == best && oi < idx)) { best = ov; idx = oi; }
+      }
+      out[blockIdx.x] = idx;
+      if (out_val != nullptr) out_val[blockIdx.x] = best;
+    }
   }
 }
 
@@ -95,7 +106,18 @@ int argmax_rows(const float* logits, long long* out, int T, int V, cudaStream_t 
   if (T == 0) return OK;
   if (!logits || !out) return ERR_NULL_PTR;
   if (T < 0 || V <= 0) return ERR_BAD_SHAPE;
-  argmax_kernel<<<T, 1024, 0, st>>>(logits, out, V);
+  argmax_kernel<<<T, 1024, 0, st>>>(logits, V, out, V, nullptr, 0, nullptr, nullptr);
+  return launch_status();
+}
+
+// argmax over one vocabulary shard: out_idx = idx_offset + argmax (ties to the lowest index), out_val = the
+// maximum (optional), and optionally merged with another shard's (value, global index) winner per row.
+int argmax_shard(const float* logits, long long ld, long long* out_idx, float* out_val, long long idx_offset,
+                 const float* other_val, const long long* other_idx, int T, int V, cudaStream_t st) {
+  if (T == 0) return OK;
+  if (!logits || !out_idx || ((other_val == nullptr) != (other_idx == nullptr))) return ERR_NULL_PTR;
+  if (T < 0 || V <= 0 || ld < V) return ERR_BAD_SHAPE;
+  argmax_kernel<<<T, 1024, 0, st>>>(logits, ld, out_idx, V, out_val, idx_offset, other_val, other_idx);
   return launch_status();
 }
 

@@ -395,6 +395,18 @@ def argmax(logits, out=None):
     return o
 
 
+def argmax_shard(logits, idx_offset=0, out_idx=None, out_val=None, other=None):
+    """Row argmax of a vocabulary shard [T,V] fp32 whose first column is global index `idx_offset`; `other` =
+    (values [T] fp32, global indices [T] int64) of another shard to merge with.  b2_argmax_shard."""
+    _cuda(logits, out_idx, out_val)
+    T, V = logits.shape
+    o = out_idx if out_idx is not None else torch.empty((T,), dtype=torch.int64, device=logits.device)
+    ov, oi = other if other is not None else (None, None)
+    check(_abi.lib().b2_argmax_shard(ptr(logits), logits.stride(0), ptr(o), ptr(out_val), int(idx_offset), ptr(ov), ptr(oi),
+                                     T, V, stream_handle()), "b2_argmax_shard")
+    return o
+
+
 def confidence(logits):
     """logits [T,V] fp32 -> (mean over rows of the largest softmax probability [1] fp32, per-row values [T]).
     b2_confidence."""
