@@ -13,12 +13,14 @@ Two forms:
 """
 from __future__ import annotations
 
+import os
+
 import numpy as np
 import torch
 
 from . import ops
 from .config import ModelConfig, get_config
-from .stage import Stage, KVCache
+from .stage import Stage, KVCache, head_message
 
 
 def split_layers(n_layers: int, n_stages: int):
@@ -207,6 +209,12 @@ class DistPipeline:
         self = cls(rank, world, cfg.d_model, torch.device(device), None, cfg.vocab)
         self.stage, self.cache, self.cfg = stage, cache, cfg
         self.graph_chunk = 0          # set to the prefill chunk size to replay full chunks as graphs
+        # Decode with two or more stages: the last stage streams its layers AND the fp16 lm_head (Llama-2-7B: 262 MB
+        # on top of 4 x 202 MB at eight stages), so the pipeline ticks at its pace.  With tied embeddings the first
+        # stage already holds the same matrix: it takes the lower half of the vocabulary, the last stage the upper
+        # half, and instead of the token the last stage returns its normed hidden state plus its shard's winner.
+        # Exact: a row's argmax is the better of the two shard winners under the lowest-index tie rule.
+        self.split_head = world > 1 and cfg.tie_embeddings and os.environ.get("B2_SPLIT_HEAD", "1") != "0"
         self.fwd = lambda x, pos, seq, lg: stage.forward_auto(x, cache, pos, seq, logits=lg,
                                                               graph_chunk=self.graph_chunk)
         if world > 1:
@@ -327,8 +335,8 @@ class DistPipeline:
         """`steps` greedy decode steps for each of G independent groups as ONE continuous pipeline:
         group g's token of step i-1 is awaited only right before group g's step i, so with
         G >= world every stage is busy every tick (no round barrier).  first_tokens[g]: int64 [B_g]
-        (needed on rank 0).  Returns, on rank 0 and on the last rank, tokens[g] = list of `steps`
-        tensors [B_g]; None on the ranks in between."""
+        (needed on rank 0).  Returns, on rank 0 (and on the last rank unless the lm_head is shared with the first
+        stage, `split_head`), tokens[g] = list of `steps` tensors [B_g]; None on the other ranks."""
         G = len(rows_per_group)
         if self.device.type == "cuda" and getattr(self, "stage", None) is not None and getattr(self, "use_graphs", True):
             return self._decode_stream_graphs(first_tokens, start_positions, rows_per_group, steps)
@@ -364,7 +372,9 @@ class DistPipeline:
         dev = self.device
         cur = torch.cuda.current_stream(dev)
         G = len(rows_per_group)
-        want = "last" if self.last else "none"
+        multi = self.world > 1
+        split = multi and getattr(self, "split_head", False)
+        want = ("split" if split else "last") if self.last else "none"
         runners = []
         for g in range(G):
             r = self.stage.runner(self.cache, len(rows_per_group[g]), decode=True, rows=list(rows_per_group[g]), logits=want)
@@ -376,9 +386,13 @@ class DistPipeline:
             if self.first:
                 r.x.copy_(first_tokens[g].view(r.x.shape))
             runners.append(r)
-        keep = self.first or self.last
+        keep = self.first or (self.last and not split)
         gen = [torch.empty((steps, len(rows_per_group[g])), dtype=torch.int64, device=dev) for g in range(G)] if keep else None
-        multi = self.world > 1
+        if split and self.first:
+            # per group: the last stage's message (hidden | shard maxima | indices) and the lower-shard logits
+            inbox = [head_message(len(rows_per_group[g]), self.d, dev) for g in range(G)]
+            lg_lo = [torch.empty((len(rows_per_group[g]), self.stage.head_split()), dtype=torch.float32, device=dev)
+                     for g in range(G)]
         if multi:
             # the buffers used below were last touched by work queued on `cur` (earlier calls, the allocations above)
             for side in (self._rs, self._ss, self._rs_tok, self._ss_tok):
@@ -400,17 +414,27 @@ class DistPipeline:
                 e.record(side)
             cur.wait_event(e)
 
+        def token_from_head(g, step):
+            """first stage, shared head: receive (hidden, upper-shard winner) of `step`, finish the argmax here."""
+            msg, hn, val, idx = inbox[g]
+            recv_into(msg, self.world - 1, self.tok_group, self._rs_tok, g)
+            self.stage.head_lower(hn, val, idx, gen[g][step], lg_lo[g])
+
         for i in range(steps):
             for g in range(G):
                 r = runners[g]
                 if multi and self.first and i > 0:
-                    recv_into(gen[g][i - 1], self.world - 1, self.tok_group, self._rs_tok, g, then_copy_to=r.x)
+                    if split:
+                        token_from_head(g, i - 1)
+                        r.x.copy_(gen[g][i - 1].view(r.x.shape))
+                    else:
+                        recv_into(gen[g][i - 1], self.world - 1, self.tok_group, self._rs_tok, g, then_copy_to=r.x)
                 elif multi and not self.first:
                     recv_into(r.x, self.rank - 1, self.group_in, self._rs, g)
                 if ev_sent[g] is not None:
                     cur.wait_event(ev_sent[g])
                 r.replay()
-                if self.last:
+                if self.last and not split:
                     ops.argmax(r.out, out=gen[g][i])
                     self.stage.launches += 1
                     if self.first:
@@ -429,10 +453,17 @@ class DistPipeline:
                 else:
                     with torch.cuda.stream(self._ss_tok):
                         self._ss_tok.wait_event(ef)
-                        self.dist.isend(gen[g][i], dst=0, group=self.tok_group).wait()
+                        self.dist.isend(r.msg if split else gen[g][i], dst=0, group=self.tok_group).wait()
+                        if split:               # r.msg is the runner's static buffer: the next replay must wait for the send
+                            es = Event()
+                            es.record(self._ss_tok)
+                            ev_sent[g] = es
         if multi and self.first:
             for g in range(G):
-                recv_into(gen[g][steps - 1], self.world - 1, self.tok_group, self._rs_tok, g)
+                if split:
+                    token_from_head(g, steps - 1)
+                else:
+                    recv_into(gen[g][steps - 1], self.world - 1, self.tok_group, self._rs_tok, g)
         if multi:
             # side streams may still hold sends of this call: later work on `cur` (another call's buffers) follows them
             cur.wait_stream(self._ss)

@@ -196,7 +196,7 @@ class Stage:
     # except launch geometry that depends on T alone -> capturable in a CUDA graph.
     # ------------------------------------------------------------------------------------------
     def _core(self, buf: _Scratch, x, T: int, kv_cache: KVCache, decode: bool, dpos, dseq, dlens, row0: int,
-              max_len: int, ws, logits: str, out, trace=None):
+              max_len: int, ws, logits: str, out, trace=None, hn_out=None):
         cfg = self.cfg
         d, H, KV, hd, F = cfg.d_model, cfg.n_heads, cfg.n_kv_heads, cfg.head_dim, cfg.ffn
         n = 0
@@ -333,10 +333,31 @@ class Stage:
             if out is not None and out.data_ptr() != h.data_ptr():
                 out.copy_(h)
             return (h if out is None else out), n
-        hsel = h if (logits == "all" or decode) else h[T - 1:T]
-        hn = ops.norm(hsel, self.w["lnf_g"], self.w.get("lnf_b"), cfg.eps, out=buf.hn[: hsel.shape[0]])
-        lg = ops.lm_head(hn, self.w["lm_head"], out=out)
+        hsel = h if (logits in ("all", "split") or decode) else h[T - 1:T]
+        hn = ops.norm(hsel, self.w["lnf_g"], self.w.get("lnf_b"), cfg.eps,
+                      out=hn_out if hn_out is not None else buf.hn[: hsel.shape[0]])
+        if logits == "split":
+            # the upper vocabulary shard only: the first stage computes the lower one from the normed hidden state
+            lg = ops.lm_head(hn, self.w["lm_head"][self.head_split():], out=out)
+        else:
+            lg = ops.lm_head(hn, self.w["lm_head"], out=out)
         return lg, n + 2
+
+    def head_split(self) -> int:
+        """First vocabulary row of the upper lm_head shard when the head is shared between the first and the last
+        pipeline stage (DistPipeline.split_head): rows [0, split) on the first stage, [split, V) on the last."""
+        return (self.cfg.vocab // 2 + 7) & ~7
+
+    def head_lower(self, hn, other_val, other_idx, out_tok, lg_buf):
+        """First stage: logits of the lower vocabulary shard from the last stage's normed hidden state hn [B,d] (the
+        embedding table doubles as lm_head when the model ties them), then the greedy token over the whole
+        vocabulary by merging with the upper shard's winner (other_val, other_idx) -> out_tok [B] int64."""
+        if "embed" not in self.w or not self.cfg.tie_embeddings:
+            raise RuntimeError("head_lower needs the first stage of a model with tied embeddings")
+        lg = ops.lm_head(hn, self.w["embed"][: self.head_split()], out=lg_buf)
+        ops.argmax_shard(lg, 0, out_idx=out_tok, other=(other_val, other_idx))
+        self.launches += 2
+        return out_tok
 
     def _layer_llm_int8(self, buf, lw, h, h_alt, T, kc, vc, decode, dpos, dseq, dlens, row0, max_len, ws, act, trace):
         """One decoder layer with every linear computed as bitsandbytes' Linear8bitLt does (ops.llm_int8_linear;
@@ -484,6 +505,16 @@ class Stage:
         return r
 
 
+def head_message(T: int, d: int, device):
+    """The buffer the last stage sends to the first one per decode step when they share the lm_head, and its three
+    views: normed hidden [T,d] fp16, upper-shard maxima [T] fp32, their global indices [T] int64."""
+    off_val = T * d * 2
+    off_idx = off_val + ((T * 4 + 7) & ~7)
+    msg = torch.zeros((off_idx + T * 8,), dtype=torch.uint8, device=device)
+    return (msg, msg[:off_val].view(torch.float16).view(T, d), msg[off_val: off_val + T * 4].view(torch.float32),
+            msg[off_idx:].view(torch.int64))
+
+
 class GraphRunner:
     """One captured CUDA graph = one stage forward at a fixed shape.
 
@@ -509,8 +540,13 @@ class GraphRunner:
             self.max_len = kv_cache.max_seq      # split count fixed for the whole graph lifetime
             nb = ops.decode_attn_workspace_bytes(T, cfg.n_heads, cfg.n_kv_heads, cfg.head_dim, self.max_len, cfg.window)
             self.ws = torch.empty((nb,), dtype=torch.uint8, device=dev) if nb else None
-        n_out = T if (decode or logits == "all") else 1
-        if stage.last and logits != "none":
+        n_out = T if (decode or logits in ("all", "split")) else 1
+        self.msg = self.hn_msg = self.val_msg = self.idx_msg = None
+        if stage.last and logits == "split":
+            # one message to the first stage per step: normed hidden [T,d] fp16 | shard maxima [T] fp32 | indices [T] int64
+            self.out = torch.empty((n_out, cfg.vocab - stage.head_split()), dtype=torch.float32, device=dev)
+            self.msg, self.hn_msg, self.val_msg, self.idx_msg = head_message(T, cfg.d_model, dev)
+        elif stage.last and logits != "none":
             self.out = torch.empty((n_out, cfg.vocab), dtype=torch.float32, device=dev)
         else:
             self.out = torch.empty((T, cfg.d_model), dtype=torch.float16, device=dev)
@@ -523,7 +559,10 @@ class GraphRunner:
 
     def _run_core(self):
         _, n = self.stage._core(self.buf, self.x, self.T, self.cache, self.decode, self.dpos, self.dseq, self.dlens,
-                                self.rows[0], self.max_len, self.ws, self.logits, self.out)
+                                self.rows[0], self.max_len, self.ws, self.logits, self.out, hn_out=self.hn_msg)
+        if self.msg is not None:
+            ops.argmax_shard(self.out, self.stage.head_split(), out_idx=self.idx_msg, out_val=self.val_msg)
+            n += 1
         self.dpos.add_(self.stride)
         if self.dlens is not None:
             self.dlens.add_(self.stride)

@@ -1,0 +1,56 @@
+"""Multi-GPU parity, run whenever two or more GPUs are visible (`gpurun --gpus 2`; skipped on a one-GPU box):
+
+* the NCCL layer-range pipeline (one process per GPU, chunked prefill stream + continuous decode stream) decodes
+  exactly the tokens of a single-stage, single-process run of the same seeded model -- north_star's "greedy-decoded
+  tokens identical" for the path bench.py times at N > 1 -- with the lm_head shared between the first and the last
+  stage (the default) and with the whole head on the last stage;
+* one process driving two stages on two different GPUs (`Pipeline`) does the same: every Stage entry point runs on
+  its own device whatever device is current in the calling thread.
+"""
+import os
+import socket
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+needs2 = pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+@needs2
+@pytest.mark.parametrize("model", ["tiny-llama-test", "tiny-gqa-test"])
+@pytest.mark.parametrize("split_head", ["1", "0"])
+def test_nccl_pipeline_tokens_identical_to_single_stage(model, split_head):
+    n = min(torch.cuda.device_count(), 4 if model == "tiny-gqa-test" else 2)
+    env = dict(os.environ, B2_SPLIT_HEAD=split_head)
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
+                        "--master-addr", "127.0.0.1", "--master-port", str(_free_port()),
+                        os.path.join(ROOT, "tools", "check_pp_tokens.py"), model],
+                       capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "pass 1:" in r.stdout, r.stdout[-2000:]
+
+
+@needs2
+def test_single_process_pipeline_on_two_devices():
+    import b200stage
+    from b200stage.pipeline import Pipeline
+    cfg = b200stage.get_config("tiny-gqa-test")
+    ids = np.random.default_rng(3).integers(0, cfg.vocab, 3 * 32 + 7)       # full chunks (graphs) and a ragged tail (eager)
+    one = Pipeline.load(cfg, 1, devices=["cuda:0"], seed=5).generate(ids, max_new_tokens=16, chunk=32).cpu().numpy()
+    torch.cuda.set_device(0)                                                # stage 1 lives on cuda:1, current device stays 0
+    two = Pipeline.load(cfg, 2, devices=["cuda:0", "cuda:1"], seed=5)
+    for graphs in (True, False):
+        two.use_graphs = graphs
+        got = two.generate(ids, max_new_tokens=16, chunk=32).cpu().numpy()
+        assert np.array_equal(got, one), (graphs, got[-16:], one[-16:])
