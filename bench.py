@@ -43,6 +43,11 @@ def parse():
     ap.add_argument("--chunk", type=int, default=0, help="prefill chunk (0 = auto: whole prompt on one GPU, 1024 on 2-4 stages, 512 beyond)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--layers", type=int, default=0, help="PROFILING ONLY: truncate the model to this many layers")
+    ap.add_argument("--batch", type=int, default=0,
+                    help="decode-only workload (BASELINE configs[3]): this many sequences, each with --kv tokens of context "
+                         "already in the KV cache, decode --new tokens each; the sequences run as --batch/--micro groups")
+    ap.add_argument("--kv", type=int, default=4096, help="with --batch: context length per sequence at the END of the run")
+    ap.add_argument("--micro", type=int, default=0, help="with --batch: sequences per micro-batch (0 = batch / stages, at most 8)")
     ap.add_argument("--quant", default="w8a8", choices=["w8a8", "llm_int8"],
                     help="w8a8 = the headline SmoothQuant-style path; llm_int8 = bitsandbytes-style mixed decomposition "
                          "(SURVEY 8(f) rank 2; a side measurement, not the BASELINE metric)")
@@ -575,10 +580,121 @@ def roofline_pass(torch, ops, stage, cfg, pk, dev, chunk):
     return roof, roof_pre
 
 
+def run_decode_batch(a):
+    """BASELINE configs[3]-style workload: batched decode over a long, already filled KV cache, the batch split into
+    micro-batches that travel through the layer-range stages as one continuous pipeline (DistPipeline.decode_stream).
+    One step = every sequence decodes --new tokens.  The KV cache is pre-filled with N(0,1) fp16 (seed 4321): decode
+    attention streams it whatever it holds."""
+    import torch
+    import importlib
+    b2 = importlib.import_module("llm-for-distributed-egde-devices_b200")
+    from b200stage.pipeline import DistPipeline
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    cfg = b2.get_config(a.model)
+    B, S, NEW = a.batch, a.kv, a.new
+    micro = a.micro or max(1, min(8, B // max(world, 1)))
+    if B % micro:
+        raise SystemExit("--batch must be a multiple of --micro")
+    G = B // micro
+    pipe = DistPipeline.load(cfg, rank, world, dev, seed=0, fast_init=True, max_rows=B, max_seq=S, quant=a.quant)
+    stage = pipe.stage
+    g = torch.Generator(device=dev).manual_seed(4321 + rank)
+    for t in (pipe.cache.k, pipe.cache.v):                 # [layers][rows][KV][Smax][hd]
+        for li in range(t.shape[0]):
+            for r0 in range(0, B, 8):
+                t[li, r0:r0 + 8].normal_(generator=g)
+    start = S - NEW                                         # the last decoded token lands at position S - 1
+    rows = [list(range(i * micro, (i + 1) * micro)) for i in range(G)]
+    first = [torch.randint(0, cfg.vocab, (micro,), device=dev, generator=g) for _ in range(G)]
+    pos0 = [[start] * micro for _ in range(G)]
+
+    def one_step():
+        return pipe.decode_stream(first, pos0, rows, NEW)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+    for _ in range(max(a.warmup, 3)):
+        one_step()
+    barrier()
+    clocks = Clocks(local) if rank == 0 else None
+    l0 = stage.launches
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t0.record()
+    for _ in range(a.steps):
+        out = one_step()
+    t1.record()
+    barrier()
+    ms_total = t0.elapsed_time(t1)
+    launches = stage.launches - l0
+    clk = clocks.stop() if clocks else None
+    # e2e: first tokens from pinned host memory in, generated ids out to the host, every step
+    first_host = [f.cpu().pin_memory() for f in first]
+    barrier()
+    w0 = time.perf_counter()
+    for _ in range(a.steps):
+        if pipe.first:
+            first = [f.to(dev, non_blocking=True) for f in first_host]
+        out = one_step()
+        if out is not None and pipe.first:
+            host_out = torch.stack([torch.stack(o) for o in out]).cpu()
+        barrier()
+    e2e_s = (time.perf_counter() - w0) / a.steps
+    vals = torch.tensor([ms_total, e2e_s, float(launches)], dtype=torch.float64, device=dev)
+    if dist is not None:
+        mx = vals.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = vals.clone()
+        dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        ms_total, e2e_s = float(mx[0]), float(mx[1])
+        launches = int(sm[2])
+    if rank == 0:
+        pk = peaks()
+        ms_step = ms_total / a.steps
+        tok_s = B * NEW / (ms_step / 1e3)
+        w_bytes = cfg.linear_params_per_layer() * cfg.n_layers + cfg.vocab * cfg.d_model * 2
+        kv_tok = 2 * cfg.n_layers * cfg.n_kv_heads * cfg.head_dim * 2 * (min(cfg.window, S) if cfg.window else (S - NEW // 2))
+        alg = (w_bytes + kv_tok * B) / B                     # weights read once per step of the whole batch
+        act = (w_bytes * G + kv_tok * B) / B                 # as run: every micro-batch re-reads the stage weights
+        line = {"metric": f"decode tokens/sec, {cfg.name} W8A8, batch {B}, {S}-token KV cache", "value": tok_s, "unit": UNIT,
+                "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "int8", "data": "synthetic",
+                "config": {"workload": f"{cfg.name} W8A8 (random-init, seeded), decode of {NEW} tokens for each of {B} sequences "
+                                       f"ending at a {S}-token KV cache (pre-filled N(0,1) fp16)",
+                           "run": f"{G} micro-batches x {micro} sequences through {world} pipeline stage(s) x "
+                                  f"{stage.layer_end - stage.layer_begin} layers", "parallelism": f"pp{world}",
+                           "l2": f"inputs larger than L2 (KV cache {kv_tok * B / 1e9:.1f} GB + weights {w_bytes / 1e9:.1f} GB per step)"},
+                "gpu_launches": launches,
+                "e2e": {"value": B * NEW / e2e_s, "unit": UNIT, "h2d_bytes_per_step": B * 8, "d2h_bytes_per_step": B * NEW * 8},
+                "roofline": {"bound": "hbm", "kernel": "whole decode step (decode attention over the KV cache + weight streams)",
+                             "achieved": alg * tok_s / 1e9 / world, "peak": pk["hbm"], "unit": "GB/s per GPU",
+                             "frac": alg * tok_s / 1e9 / world / pk["hbm"], "algorithmic_bytes_per_token": alg,
+                             "bytes_per_token_as_run": act, "frac_as_run": act * tok_s / 1e9 / world / pk["hbm"],
+                             "traffic": None, "peak_source": pk["which"]},
+                "clocks": clk, "peaks": pk["which"]}
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def main():
     a = parse()
     if a.impl == "reference":
         run_reference(a)
+    elif a.batch:
+        run_decode_batch(a)
     else:
         run_ours(a)
 

@@ -231,7 +231,9 @@ size_t b2_decode_attn_workspace_bytes(int B, int H, int KV, int hd, int max_seql
  * (every GPU that loads the library holds those bytes until the process exits).  The call itself
  * allocates nothing: no cudaMalloc/cudaFree, no allocating library routine.
  * Arguments and result are those of b2_decode_attn without workspace/workspace_bytes; the output is
- * the same as b2_decode_attn's with a full-size workspace.
+ * the same as b2_decode_attn's with a full-size workspace.  It is the slower of the two: it always writes the
+ * partials to the array and merges them in a second launch, also for up to 8 splits, where b2_decode_attn merges
+ * inside a thread-block cluster without touching global memory.
  * - Sizes whose partials (b2_decode_attn_workspace_bytes) exceed the array are refused with
  *   B2_ERR_TOO_LARGE; nothing is launched and the split count is never silently reduced.
  * - The first call on each device looks up the array's device address (cudaGetSymbolAddress, with

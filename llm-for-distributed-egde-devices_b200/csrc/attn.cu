@@ -205,6 +205,9 @@ __global__ void __launch_bounds__(DEC_THREADS, 2) decode_attn_kernel(const DecPa
   // predecessor (sequence lengths, cache rows of earlier tokens).
   tl_mark(1, 0);
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  // Cluster variant: remote shared-memory stores are only defined once every CTA of the cluster has started.
+  // Arrive now, wait just before the first remote store -- the K/V loop in between hides the latency.
+  if (CL) asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
   // fill the ring: one commit group per stage (empty groups keep the group count uniform)
 #pragma unroll
   for (int sidx = 0; sidx < DEC_NST; ++sidx) {
@@ -338,6 +341,7 @@ __global__ void __launch_bounds__(DEC_THREADS, 2) decode_attn_kernel(const DecPa
   }
   if (t4 == 0) { sM[warp * 8 + g] = m_run; sL[warp * 8 + g] = l_run; }
   __syncthreads();
+  if (CL) asm volatile("barrier.cluster.wait.aligned;" ::: "memory");     // phase 1: every CTA of the cluster is running
   for (int idx = threadIdx.x; idx < G * HD; idx += DEC_THREADS) {
     const int gh = idx / HD, d = idx - gh * HD;
     float m = -INFINITY;

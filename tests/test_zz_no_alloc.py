@@ -59,6 +59,14 @@ def _both(seed, B, H, KV, hd, S):
     torch.cuda.synchronize()
     _check(got, ref)
     assert torch.equal(got, ref), "same kernels, same inputs: expected identical bits"
+    # and against the CPU oracle on this variant's own shapes, not only against its sibling entry point
+    from oracle import w8a8 as O
+    q_h, k_h, v_h = qkv.cpu().numpy(), kc.cpu().numpy(), vc.cpu().numpy()
+    for b in range(B):
+        L = int(lens[b])
+        want = O.attention(q_h[b:b + 1, :H * hd].reshape(1, H, hd), np.transpose(k_h[b, :, :L], (1, 0, 2)),
+                           np.transpose(v_h[b, :, :L], (1, 0, 2)), np.array([L - 1]), scale, 0)
+        _check(got[b].cpu().reshape(H, hd), torch.from_numpy(want[0].astype(np.float32)))
     return need
 
 
