@@ -45,12 +45,18 @@ class Pipeline:
 
     @classmethod
     def load(cls, model, n_stages: int = 1, devices=None, seed: int = 0, fast_init: bool = False,
-             quant: str = "w8a8") -> "Pipeline":
+             quant: str = "w8a8", act_stats=None, calibrate_with=None) -> "Pipeline":
+        """`model`: a Hugging Face model directory (its tensors are read per layer range), or a preset name /
+        ModelConfig for the seeded synthetic model.  calibrate_with: prompts for the SmoothQuant statistics."""
+        from . import loader
         cfg = get_config(model)
         devices = devices or ["cuda:0"] * n_stages
         rngs = split_layers(cfg.n_layers, n_stages)
-        return cls([Stage.load(cfg, b, e, first=(i == 0), last=(i == n_stages - 1), device=devices[i], seed=seed,
-                               fast_init=fast_init, quant=quant) for i, (b, e) in enumerate(rngs)])
+        if calibrate_with is not None and act_stats is None:
+            act_stats = loader.calibrate(model, calibrate_with, seed, devices[0])
+        spec = model if loader.is_checkpoint_dir(model) else cfg
+        return cls([Stage.load(spec, b, e, first=(i == 0), last=(i == n_stages - 1), device=devices[i], seed=seed,
+                               fast_init=fast_init, quant=quant, act_stats=act_stats) for i, (b, e) in enumerate(rngs)])
 
     def new_caches(self, rows: int, max_seq: int):
         return [s.new_kv_cache(rows, max_seq) for s in self.stages]
@@ -201,10 +207,12 @@ class DistPipeline:
     @classmethod
     def load(cls, model, rank: int, world: int, device, seed: int = 0, fast_init: bool = True, max_rows: int = 1,
              max_seq: int = 4096, quant: str = "w8a8"):
+        from . import loader
         cfg = get_config(model)
         b, e = split_layers(cfg.n_layers, world)[rank]
-        stage = Stage.load(cfg, b, e, first=(rank == 0), last=(rank == world - 1), device=device, seed=seed,
-                           fast_init=fast_init, quant=quant)
+        from_dir = loader.is_checkpoint_dir(model)
+        stage = Stage.load(model if from_dir else cfg, b, e, first=(rank == 0), last=(rank == world - 1), device=device,
+                           seed=seed, fast_init=fast_init and not from_dir, quant=quant)
         cache = stage.new_kv_cache(max_rows, max_seq)
         self = cls(rank, world, cfg.d_model, torch.device(device), None, cfg.vocab)
         self.stage, self.cache, self.cfg = stage, cache, cfg

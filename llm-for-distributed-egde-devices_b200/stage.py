@@ -156,15 +156,35 @@ class Stage:
     # ------------------------------------------------------------------------------------------
     @classmethod
     def load(cls, model_dir_or_config, layer_begin: int, layer_end: int, *, first: bool, last: bool,
-             device="cuda", quant: str = "w8a8", seed: int = 0, fast_init: bool = False, act_stats=None) -> "Stage":
-        """Load (here: synthesise under `seed`, no checkpoints exist offline) the W8A8 shard for
-        layers [layer_begin, layer_end).  `fast_init` generates on the device (benchmarks)."""
+             device="cuda", quant: str = "w8a8", seed: int = 0, fast_init: bool = False, act_stats=None,
+             calibrate_with=None) -> "Stage":
+        """Load the W8A8 shard for layers [layer_begin, layer_end).
+
+        model_dir_or_config: a Hugging Face model DIRECTORY (the reference's `from_pretrained(model_path)`
+        convention, models_quant_updated.py:34-38): only this range's tensors are read from its *.safetensors /
+        pytorch_model*.bin shards and quantised on load (loader.py); a directory without weight files is an error.
+        A preset name, ModelConfig or config dict instead builds the seeded synthetic model of that shape
+        (`seed`; `fast_init` generates on the device for the benchmarks).
+        act_stats: per-layer activation maxima for SmoothQuant (loader.calibrate); calibrate_with: prompts (list of
+        id arrays) to gather them from here, over the fp32 model up to layer_end.  Without either, a checkpoint
+        directory's saved statistics (loader.save_stats) are used if present, else weight-only statistics."""
+        from . import loader
         if quant not in ("w8a8", "llm_int8"):
             raise ValueError("quant must be 'w8a8' or 'llm_int8'")
         cfg = get_config(model_dir_or_config)
         if not (0 <= layer_begin < layer_end <= cfg.n_layers):
             raise ValueError(f"bad layer range [{layer_begin},{layer_end}) for {cfg.n_layers} layers")
-        if fast_init:
+        if torch.device(device).type != "cuda":
+            raise RuntimeError("Stage runs only on a CUDA device: the hot path has no CPU fallback")
+        from_dir = loader.is_checkpoint_dir(model_dir_or_config)
+        if calibrate_with is not None and act_stats is None:
+            if fast_init and not from_dir:
+                raise ValueError("calibration needs the fp32 weights: not available with fast_init")
+            act_stats = loader.calibrate(model_dir_or_config, calibrate_with, seed, device, layers=layer_end)
+        if from_dir:
+            sw = loader.build_stage_weights_from_checkpoint(str(model_dir_or_config), layer_begin, layer_end, first, last,
+                                                            device, act_stats, quant)
+        elif fast_init:
             sw = weights.build_stage_weights_fast(cfg, layer_begin, layer_end, first, last, seed, device, quant=quant)
         else:
             sw = weights.build_stage_weights(cfg, layer_begin, layer_end, first, last, seed, device, act_stats, quant=quant)

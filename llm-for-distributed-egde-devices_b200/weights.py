@@ -1,4 +1,5 @@
-"""Layer-range shard construction: synthetic (seeded) or checkpoint weights -> W8A8 stage weights.
+"""Layer-range shard construction: fp32 layer weights -> W8A8 stage weights, and the seeded synthetic models.
+(Real checkpoints are read by loader.py, which feeds the same quantiser.)
 
 Counterpart of the reference's loaders ``load_int8_model`` (Code/Quantised Models/models_quant_updated.py:25-40)
 and ``load_model_int8_cpu`` (Code/C-DAC Server/try.py:198-206), which load a *whole* model and let
@@ -75,7 +76,7 @@ def _smooth_vec(W: torch.Tensor, act_amax: torch.Tensor | None, alpha: float) ->
 
 def quantize_weight(W: torch.Tensor, s: torch.Tensor | None):
     """W [N,K] fp32 (any device) -> (Wq int8 [N,K], s_w fp32 [N]).  Same formula as
-    oracle/w8a8.py:quantize_weight (checked in tests/test_weights.py)."""
+    oracle/w8a8.py:quantize_weight (checked in tests/test_oracle_cpu.py)."""
     W = W.to(torch.float32)
     if s is not None:
         W = W * s[None, :]

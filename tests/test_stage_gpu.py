@@ -164,3 +164,28 @@ def test_confidence_score_matches_oracle():
 def test_stage_refuses_cpu():
     with pytest.raises(RuntimeError):
         Stage.load("tiny-llama-test", 0, 1, first=True, last=False, device="cpu")
+
+
+def test_pipeline_from_a_checkpoint_directory(tmp_path):
+    """Stage.load(model_dir): the reference's `from_pretrained(model_path)` convention (models_quant_updated.py:34-38).
+    A tiny HF Llama checkpoint written here (the seeded synthetic weights in the HF module, `save_pretrained`) is
+    read per layer range by two stages and must decode the tokens of the oracle on the same weights; a directory
+    with a config but no weights must raise instead of yielding a random model."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden"))
+    import make_golden
+    cfg = b200stage.get_config("tiny-gqa-test")
+    seed, T, NEW = 6, 33, 16
+    make_golden.hf_model(cfg, seed).save_pretrained(tmp_path)
+    pipe = Pipeline.load(str(tmp_path), 2)
+    assert pipe.stages[0].w["source"] == str(tmp_path) and pipe.stages[1].layer_begin == cfg.n_layers // 2
+    ids = np.random.default_rng(2).integers(0, cfg.vocab, T)
+    got = pipe.generate(ids, max_new_tokens=NEW, chunk=16).cpu().numpy()
+    ref, margins = O.greedy_generate(_oracle_stages(cfg, 2, seed), cfg.kernel_cfg(), ids, NEW, T + NEW)
+    assert np.array_equal(got, ref), (got[T:], ref[T:], min(margins))
+    empty = tmp_path / "config_only"
+    empty.mkdir()
+    make_golden.hf_model(cfg, seed).config.save_pretrained(empty)
+    with pytest.raises(FileNotFoundError):
+        Stage.load(str(empty), 0, 1, first=True, last=False, device=DEV)
