@@ -435,6 +435,9 @@ def run_ours(a):
             "e2e": {"value": tokens_step / e2e_s, "unit": UNIT, "h2d_bytes_per_step": n_prompts * P * 8,
                     "d2h_bytes_per_step": n_prompts * NEW * 8},
             "roofline": roof, "roofline_prefill": roof_pre, "clocks": clk, "peaks": pk["which"],
+            "decode_handoff": (pipe.p2p["how"] + ": peer-memory store + flag kernels (b2_p2p_send / b2_p2p_wait)") if getattr(pipe, "p2p", None)
+            else ("NCCL send/recv" if world > 1 else "none (one stage)"),
+            "shared_lm_head": bool(getattr(pipe, "split_head", False)),
         }
         line.update(token_check(host_out, cfg.name, a.quant, P, NEW, bool(a.layers)))
         if not a.no_cpu_baseline and world == 1:
@@ -451,6 +454,7 @@ def run_ours(a):
             except Exception as e:
                 line.setdefault("cpu_grpc_pipeline", {})["error"] = f"{type(e).__name__}: {e}"
         print(json.dumps(line), flush=True)
+    pipe.drain()            # raises if a peer-memory hand-off ever timed out
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()

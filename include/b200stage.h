@@ -304,6 +304,20 @@ int b2_lm_head(const void* x, const void* W, float* logits, int M, int V, int d,
  * Replaces: the greedy (do_sample=False) token selection of `generate`. */
 int b2_argmax(const float* logits, long long* out, int T, int V, void* stream);
 
+/* Stage-to-stage hand-off of a decode step through NVLink peer memory (one kernel at each end, no host, no NCCL).
+ * b2_p2p_send: copy `bytes` (a multiple of 16, 16-byte aligned) from local `src` to `dst_peer` -- a pointer into the
+ * receiving GPU's memory mapped into this process (CUDA IPC / symmetric memory; the caller owns the mapping) --
+ * then publish `seq` at `flag_peer` (also in the receiver's memory) with release semantics at system scope.
+ * b2_p2p_wait: on the receiving GPU, wait until *flag has reached `seq` (wrap-safe), then copy the message from the
+ * local inbox `src` to `dst` (dst NULL: no copy, later kernels read the inbox in place).  The wait is bounded (about
+ * 30 s); on expiry it sets *err (device, may be NULL) to 1 instead of hanging.  Sequence numbers are the caller's:
+ * one counter per (edge, slot), incremented identically at both ends.  A slot must not be re-sent before the
+ * receiver has consumed it (in the layer-range pipeline the token's round trip guarantees that).
+ * Replaces: the device-to-device hop the reference sketches over gRPC (Code/gRPC/server.py:13-19, client.py:7-11). */
+int b2_p2p_send(const void* src, void* dst_peer, long long bytes, unsigned int* flag_peer, unsigned int seq, void* stream);
+int b2_p2p_wait(const unsigned int* flag, unsigned int seq, const void* src, void* dst, long long bytes, unsigned int* err,
+                void* stream);
+
 /* Greedy selection over one vocabulary shard (the lm_head split between two pipeline stages): logits [T, ld >= V]
  * fp32 hold columns [idx_offset, idx_offset + V) of the full logits; out_idx [T] = idx_offset + row argmax (ties to
  * the lowest index), out_val [T] fp32 = the row maximum (or NULL).  With other_val / other_idx ([T] each, both or

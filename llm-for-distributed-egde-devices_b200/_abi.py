@@ -54,6 +54,8 @@ SIGNATURES = {
     "b2_fused_layer_tail": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp]),
     "b2_sample": (_i, [_vp, _ll, _vp, _vp, _ll, _vp, _i, _i, _f, _i, _f, _f, C.c_ulonglong, _vp, C.c_ulonglong, _vp]),
     "b2_argmax": (_i, [_vp, _vp, _i, _i, _vp]),
+    "b2_p2p_send": (_i, [_vp, _vp, _ll, _vp, C.c_uint, _vp]),
+    "b2_p2p_wait": (_i, [_vp, C.c_uint, _vp, _vp, _ll, _vp, _vp]),
     "b2_argmax_shard": (_i, [_vp, _ll, _vp, _vp, _ll, _vp, _vp, _i, _i, _vp]),
     "b2_confidence": (_i, [_vp, _ll, _vp, _vp, _i, _i, _vp]),
 }

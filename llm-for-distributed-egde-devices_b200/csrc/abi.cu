@@ -19,6 +19,9 @@ int gemm2_qkv(const int8_t*, const int8_t*, const float*, const float*, const vo
               const float*, const int*, const int*, int, void*, void*, int, int, int, int, int, int, int, cudaStream_t);
 int quant_f32(const float*, const float*, int8_t*, float*, int, int, cudaStream_t);
 int init_gemm2();
+int p2p_send(const void*, void*, long long, unsigned*, unsigned, cudaStream_t);
+int p2p_wait(const unsigned*, unsigned, const void*, void*, long long, unsigned*, cudaStream_t);
+int init_p2p();
 int rope_kv_append(void*, long long, const float*, const float*, const int*, const int*, int, void*, void*, int, int,
                    int, int, int, int, cudaStream_t);
 int decode_attn(const void*, long long, const void*, const void*, const int*, const int*, void*, long long, void*,
@@ -71,6 +74,7 @@ int b2_init(void) {
   int rc = b2::init_gemm();
   if (rc) return rc;
   if ((rc = b2::init_gemm2())) return rc;
+  if ((rc = b2::init_p2p())) return rc;
   if ((rc = b2::init_attn())) return rc;
   if ((rc = b2::init_attn_tc())) return rc;
   if ((rc = b2::init_outlier())) return rc;
@@ -122,6 +126,13 @@ int b2_gemm_w8a8_sched(const int8_t* A, const int8_t* W, const float* a_scale, c
   if (schedule == 0 && b2::gemm2_supported(M, N, K))
     return b2::gemm2_plain(A, W, a_scale, w_scale, bias, residual, out, acc_dump, M, N, K, ST(stream));
   return b2::gemm_w8a8(A, W, a_scale, w_scale, bias, residual, out, acc_dump, M, N, K, schedule, ST(stream));
+}
+int b2_p2p_send(const void* src, void* dst_peer, long long bytes, unsigned int* flag_peer, unsigned int seq, void* stream) {
+  return b2::p2p_send(src, dst_peer, bytes, flag_peer, seq, ST(stream));
+}
+int b2_p2p_wait(const unsigned int* flag, unsigned int seq, const void* src, void* dst, long long bytes, unsigned int* err,
+                void* stream) {
+  return b2::p2p_wait(flag, seq, src, dst, bytes, err, ST(stream));
 }
 int b2_argmax_shard(const float* logits, long long ld, long long* out_idx, float* out_val, long long idx_offset,
                     const float* other_val, const long long* other_idx, int T, int V, void* stream) {

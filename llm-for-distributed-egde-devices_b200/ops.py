@@ -395,6 +395,22 @@ def argmax(logits, out=None):
     return o
 
 
+def p2p_send(src, dst_peer, flag_peer, seq: int):
+    """Store the bytes of local `src` into the peer-mapped tensor `dst_peer`, then publish `seq` at `flag_peer`
+    (a one-element uint32/int32 view of the receiver's memory).  b2_p2p_send."""
+    nb = src.numel() * src.element_size()
+    check(_abi.lib().b2_p2p_send(ptr(src), ptr(dst_peer), nb, ptr(flag_peer), int(seq) & 0xFFFFFFFF, stream_handle()),
+          "b2_p2p_send")
+
+
+def p2p_wait(flag, seq: int, src=None, dst=None, err=None):
+    """Wait (on the device) until the local `flag` has reached `seq`; then copy inbox `src` to `dst` if given.
+    b2_p2p_wait."""
+    nb = 0 if dst is None else dst.numel() * dst.element_size()
+    check(_abi.lib().b2_p2p_wait(ptr(flag), int(seq) & 0xFFFFFFFF, ptr(src) if dst is not None else None, ptr(dst), nb,
+                                 ptr(err), stream_handle()), "b2_p2p_wait")
+
+
 def argmax_shard(logits, idx_offset=0, out_idx=None, out_val=None, other=None):
     """Row argmax of a vocabulary shard [T,V] fp32 whose first column is global index `idx_offset`; `other` =
     (values [T] fp32, global indices [T] int64) of another shard to merge with.  b2_argmax_shard."""

@@ -20,7 +20,7 @@ import torch
 
 from . import ops
 from .config import ModelConfig, get_config
-from .stage import Stage, KVCache, head_message
+from .stage import Stage, KVCache, head_message, head_message_views, head_message_bytes
 
 
 def split_layers(n_layers: int, n_stages: int):
@@ -227,7 +227,69 @@ class DistPipeline:
                                                               graph_chunk=self.graph_chunk)
         if world > 1:
             self.setup_groups()
+            self.setup_p2p(max_rows)
         return self
+
+    # -- peer-memory hand-off -----------------------------------------------------------------------
+    def setup_p2p(self, max_rows: int):
+        """Collective.  Give every stage an inbox in its own HBM that its neighbours can store into over NVLink
+        (decode steps only; prefill chunks keep NCCL, they are bandwidth- not latency-bound): per cache row one slot
+        for the incoming hidden state and, on the first stage, one for the last stage's head message or token, plus
+        a sequence flag per group and edge.  The mapping comes from torch's symmetric memory, else from CUDA IPC
+        handles exchanged through the process group; if neither works on this box the hand-off stays on NCCL
+        send/recv (self.p2p is None).  B2_HANDOFF=nccl forces that."""
+        self.p2p = None
+        if self.world < 2 or self.device.type != "cuda" or os.environ.get("B2_HANDOFF", "p2p") == "nccl":
+            return
+        dist, dev, R = self.dist, self.device, int(max_rows)
+        slot = (2 * self.d + 16 + 255) & ~255
+        off_head, off_flags = R * slot, 2 * R * slot
+        nbytes = off_flags + 2 * R * 4 + 256
+
+        def agree(ok: bool) -> bool:       # every rank takes the same branch
+            t = torch.tensor([1 if ok else 0], dtype=torch.int32, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MIN)
+            return bool(t.item())
+        need = sorted({0 if self.last else self.rank + 1})          # the one peer this rank stores into
+        buf, peers, how = None, {}, None
+        try:
+            import torch.distributed._symmetric_memory as symm
+            buf = symm.empty(nbytes, dtype=torch.uint8, device=dev)
+            hdl = symm.rendezvous(buf, dist.group.WORLD)
+            peers = {r: hdl.get_buffer(r, (nbytes,), torch.uint8) for r in need}
+            ok, how = True, "torch symmetric memory"
+        except Exception as e:          # noqa: BLE001
+            ok, why = False, repr(e)[:200]
+        if not agree(ok):
+            buf, peers = None, {}
+            try:
+                from torch.multiprocessing.reductions import reduce_tensor
+                buf = torch.zeros((nbytes,), dtype=torch.uint8, device=dev)
+                objs = [None] * self.world
+                dist.all_gather_object(objs, reduce_tensor(buf))
+                for r in need:
+                    fn, args = objs[r]
+                    peers[r] = fn(*args)
+                    torch.empty((16,), dtype=torch.uint8, device=dev).copy_(peers[r][:16])     # enables peer access
+                ok, how = True, "CUDA IPC handles"
+            except Exception as e:      # noqa: BLE001
+                ok, why = False, repr(e)[:200]
+            if not agree(ok):
+                return
+        buf.zero_()
+        torch.cuda.synchronize(dev)
+        dist.barrier()
+        err = torch.zeros((1,), dtype=torch.int32, device=dev)
+        self.p2p = dict(buf=buf, peer=peers[need[0]], slot=slot, off_head=off_head, off_flags=off_flags, rows=R, how=how,
+                        err=err, base_h={}, base_t={})
+
+    def _p2p_views(self, buf, g: int, row0: int, B: int):
+        """(hidden slot, head slot, hidden flag, head flag) of group g in `buf` (this rank's inbox or a peer's)."""
+        P = self.p2p
+        hs = buf[row0 * P["slot"]: row0 * P["slot"] + B * self.d * 2]
+        ts = buf[P["off_head"] + row0 * P["slot"]: P["off_head"] + row0 * P["slot"] + head_message_bytes(B, self.d)]
+        fl = buf[P["off_flags"]: P["off_flags"] + 2 * P["rows"] * 4].view(torch.int32)
+        return hs, ts, fl[g: g + 1], fl[P["rows"] + g: P["rows"] + g + 1]
 
     # -- messaging --------------------------------------------------------------------------------
     # On GPUs every receive is posted from a side stream (so NCCL does not make it wait for compute
@@ -290,6 +352,9 @@ class DistPipeline:
         self._pending = []
         if self.device.type == "cuda":
             torch.cuda.synchronize(self.device)
+            P = getattr(self, "p2p", None)
+            if P is not None and int(P["err"].item()) != 0:
+                raise RuntimeError("a peer-memory hand-off timed out: a neighbouring stage never published its step")
 
     # -- one hop --------------------------------------------------------------------------------
     def step(self, x, positions, seq_ids, want_logits: str):
@@ -396,9 +461,21 @@ class DistPipeline:
             runners.append(r)
         keep = self.first or (self.last and not split)
         gen = [torch.empty((steps, len(rows_per_group[g])), dtype=torch.int64, device=dev) for g in range(G)] if keep else None
+        P = getattr(self, "p2p", None) if multi else None
+        if P is not None and (not split or sum(len(r_) for r_ in rows_per_group) > P["rows"] or G > P["rows"]):
+            P = None            # (the token-only return path and oversize batches stay on NCCL)
+        if P is not None:
+            row0 = np.concatenate([[0], np.cumsum([len(r_) for r_ in rows_per_group])]).astype(int)
+            mine = [self._p2p_views(P["buf"], g, int(row0[g]), len(rows_per_group[g])) for g in range(G)]
+            peer = [self._p2p_views(P["peer"], g, int(row0[g]), len(rows_per_group[g])) for g in range(G)]
+            bh = [P["base_h"].get(g, 0) for g in range(G)]
+            bt = [P["base_t"].get(g, 0) for g in range(G)]
         if split and self.first:
             # per group: the last stage's message (hidden | shard maxima | indices) and the lower-shard logits
-            inbox = [head_message(len(rows_per_group[g]), self.d, dev) for g in range(G)]
+            if P is not None:       # the message lands in this GPU's inbox slot: read it in place
+                inbox = [(mine[g][1],) + head_message_views(mine[g][1], len(rows_per_group[g]), self.d) for g in range(G)]
+            else:
+                inbox = [head_message(len(rows_per_group[g]), self.d, dev) for g in range(G)]
             lg_lo = [torch.empty((len(rows_per_group[g]), self.stage.head_split()), dtype=torch.float32, device=dev)
                      for g in range(G)]
         if multi:
@@ -425,7 +502,11 @@ class DistPipeline:
         def token_from_head(g, step):
             """first stage, shared head: receive (hidden, upper-shard winner) of `step`, finish the argmax here."""
             msg, hn, val, idx = inbox[g]
-            recv_into(msg, self.world - 1, self.tok_group, self._rs_tok, g)
+            if P is not None:
+                ops.p2p_wait(mine[g][3], bt[g] + step + 1, err=P["err"])
+                self.stage.launches += 1
+            else:
+                recv_into(msg, self.world - 1, self.tok_group, self._rs_tok, g)
             self.stage.head_lower(hn, val, idx, gen[g][step], lg_lo[g])
 
         for i in range(steps):
@@ -438,7 +519,11 @@ class DistPipeline:
                     else:
                         recv_into(gen[g][i - 1], self.world - 1, self.tok_group, self._rs_tok, g, then_copy_to=r.x)
                 elif multi and not self.first:
-                    recv_into(r.x, self.rank - 1, self.group_in, self._rs, g)
+                    if P is not None:       # wait for step i of group g in this GPU's inbox, then fetch it into the graph's input
+                        ops.p2p_wait(mine[g][2], bh[g] + i + 1, src=mine[g][0], dst=r.x, err=P["err"])
+                        self.stage.launches += 1
+                    else:
+                        recv_into(r.x, self.rank - 1, self.group_in, self._rs, g)
                 if ev_sent[g] is not None:
                     cur.wait_event(ev_sent[g])
                 r.replay()
@@ -448,6 +533,15 @@ class DistPipeline:
                     if self.first:
                         r.x.copy_(gen[g][i].view(r.x.shape))
                 if not multi:
+                    continue
+                if P is not None:
+                    # store the result straight into the next stage's inbox (the first stage's, from the last one) and
+                    # publish its sequence number: one small kernel behind the graph, on the same stream
+                    if not self.last:
+                        ops.p2p_send(r.out, peer[g][0], peer[g][2], bh[g] + i + 1)
+                    else:
+                        ops.p2p_send(r.msg, peer[g][1], peer[g][3], bt[g] + i + 1)
+                    self.stage.launches += 1
                     continue
                 ef = Event()
                 ef.record(cur)
@@ -472,6 +566,10 @@ class DistPipeline:
                     token_from_head(g, steps - 1)
                 else:
                     recv_into(gen[g][steps - 1], self.world - 1, self.tok_group, self._rs_tok, g)
+        if P is not None:
+            for g in range(G):
+                P["base_h"][g] = bh[g] + steps
+                P["base_t"][g] = bt[g] + steps
         if multi:
             # side streams may still hold sends of this call: later work on `cur` (another call's buffers) follows them
             cur.wait_stream(self._ss)

@@ -530,9 +530,21 @@ def head_message(T: int, d: int, device):
     views: normed hidden [T,d] fp16, upper-shard maxima [T] fp32, their global indices [T] int64."""
     off_val = T * d * 2
     off_idx = off_val + ((T * 4 + 7) & ~7)
-    msg = torch.zeros((off_idx + T * 8,), dtype=torch.uint8, device=device)
-    return (msg, msg[:off_val].view(torch.float16).view(T, d), msg[off_val: off_val + T * 4].view(torch.float32),
-            msg[off_idx:].view(torch.int64))
+    total = (off_idx + T * 8 + 15) & ~15
+    msg = torch.zeros((total,), dtype=torch.uint8, device=device)
+    return (msg,) + head_message_views(msg, T, d)
+
+
+def head_message_views(msg, T: int, d: int):
+    """(hidden [T,d] fp16, maxima [T] fp32, indices [T] int64) views of a head message held in the uint8 buffer `msg`."""
+    off_val = T * d * 2
+    off_idx = off_val + ((T * 4 + 7) & ~7)
+    return (msg[:off_val].view(torch.float16).view(T, d), msg[off_val: off_val + T * 4].view(torch.float32),
+            msg[off_idx: off_idx + T * 8].view(torch.int64))
+
+
+def head_message_bytes(T: int, d: int) -> int:
+    return (T * d * 2 + ((T * 4 + 7) & ~7) + T * 8 + 15) & ~15
 
 
 class GraphRunner:

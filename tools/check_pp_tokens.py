@@ -23,6 +23,8 @@ cfg = b200stage.get_config(model)
 P, NEW, NP = 40, 24, world + 1               # more prompts than stages
 pipe = DistPipeline.load(cfg, rank, world, dev, seed=3, fast_init=True, max_rows=NP, max_seq=P + NEW + 8)
 pipe._bcast_len = lambda T: P
+if rank == 0:
+    print(f"handoff: {pipe.p2p['how'] if getattr(pipe, 'p2p', None) else 'NCCL send/recv'}; shared lm_head: {pipe.split_head}", flush=True)
 rng = np.random.default_rng(11)
 prompts = [torch.from_numpy(rng.integers(0, cfg.vocab, P)).to(dev) for _ in range(NP)]
 for rep in range(2):                           # second pass re-uses the captured graphs
