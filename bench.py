@@ -249,6 +249,35 @@ def workload_config(cfg_name: str, quant: str, n_prompts: int, P: int, NEW: int)
                         f"{n_prompts} prompt(s) x ({P} prefill + {NEW} greedy decode), B=1 per prompt"}
 
 
+def side_config_on_gpu(torch, b2, dev, model: str, prompt: int, new: int, pk, steps: int = 3, warmup: int = 2) -> dict:
+    """Another BASELINE.json configuration through the public API on this GPU, reported inside the N = 1 line so that
+    it is driver-visible: host prompt ids in, host tokens out, prefill and decode rates split by timing a one-token
+    generation beside the full one (median of `steps` after `warmup`)."""
+    pipe = b2.Pipeline.load(model, n_stages=1, devices=[dev], seed=0, fast_init=True)
+    cfg = pipe.cfg
+    ids = torch.randint(0, cfg.vocab, (prompt,), generator=torch.Generator().manual_seed(1234), dtype=torch.int64).pin_memory()
+    t1, tn = [], []
+    for i in range(warmup + steps):
+        for n_new, acc in ((1, t1), (new, tn)):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            pipe.generate(ids, max_new_tokens=n_new, chunk=prompt).cpu()
+            if i >= warmup:
+                acc.append(time.perf_counter() - t0)
+    pre, full = statistics.median(t1), statistics.median(tn)
+    dec = max(full - pre, 1e-9)
+    dec_tok_s = (new - 1) / dec
+    dec_bytes = cfg.linear_params_per_layer() * cfg.n_layers + cfg.vocab * cfg.d_model * 2 \
+        + 2 * cfg.n_layers * cfg.n_kv_heads * cfg.head_dim * 2 * (prompt + new // 2)
+    out = {"workload": f"{cfg.name} W8A8 (random-init, seeded), 1 GPU, {prompt}-token prefill + {new} greedy tokens, batch 1, "
+                       "host ids in / host tokens out", "value": (prompt + new) / full, "unit": UNIT,
+           "prefill_tokens_per_s": prompt / pre, "decode_tokens_per_s": dec_tok_s,
+           "decode_hbm_frac_whole_step": (dec_bytes / 1e9) * dec_tok_s / pk["hbm"], "ms_per_generation": full * 1e3}
+    del pipe
+    torch.cuda.empty_cache()
+    return out
+
+
 def run_reference(a):
     """The reference's own CPU implementation of the path, measured on the bench workload itself: the full-depth
     model, the full prompt and all generated tokens.  One generation takes seconds to tens of seconds on the host,
@@ -447,6 +476,12 @@ def run_ours(a):
             except Exception as e:   # the baseline must not take the GPU number down with it
                 line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "reference",
                                         "sample": f"failed: {type(e).__name__}: {e}"}
+            # configs[1]: TinyLlama-1.1B on one GPU, 512-token prefill and batch-1 decode
+            if cfg.name == "llama-2-7b":
+                try:
+                    line["configs1_tinyllama"] = side_config_on_gpu(torch, b2, dev, "tinyllama-1.1b", 512, 128, pk)
+                except Exception as e:
+                    line["configs1_tinyllama"] = {"error": f"{type(e).__name__}: {e}"}
             # configs[0]: the CPU gRPC stage pipeline, and the same workload through the GPU path, side by side
             try:
                 line["cpu_grpc_pipeline"] = grpc_cpu_pipeline_run()

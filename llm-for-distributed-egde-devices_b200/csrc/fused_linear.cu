@@ -160,16 +160,11 @@ B2_DEVINL void fused_phase(const FusedParams& p, uint8_t* xs, SYNC sync_fn, bool
   constexpr bool TCM = MT > 1;                         // 2..8 tokens: tensor-core stream (section 4b)
   uint8_t* const part = xs;                            // TCM: partial accumulators of the 16 warps, double-buffered
   if (TCM) xs += FL_PART_BYTES;
-  const bool wide_k = TCM && (K & 31) == 0 && (reinterpret_cast<uintptr_t>(p.W) & 31) == 0;    // 256-bit weight loads, see load_batch
-  // pitch of a quantised activation row in shared memory: K + 64 (K + 16 with 256-bit loads) keeps the 8 token
-  // rows of a B fragment on distinct banks
-  const int XS = TCM ? K + (wide_k ? 16 : FL_XS_PAD) : K;
+  const int XS = TCM ? K + FL_XS_PAD : K;              // pitch of a quantised activation row in shared memory
   const int g8 = lane >> 2, t4 = lane & 3;             // mma fragment coordinates of this lane
   constexpr int STEP = FL_UNR * 32;                    // 16-byte vectors per row per batch
   // batches per work item.  TCM: a unit's K is dealt out to the 16 warps in 64-byte pieces
-  const int NB = TCM ? (wide_k ? (((kvec + 7) >> 3) + FL_WARPS * (FL_UNR / 2) - 1) / (FL_WARPS * (FL_UNR / 2))
-                               : (((kvec + 3) >> 2) + FL_WARPS * FL_UNR - 1) / (FL_WARPS * FL_UNR))
-                     : (kvec + STEP - 1) / STEP;
+  const int NB = TCM ? (((kvec + 3) >> 2) + FL_WARPS * FL_UNR - 1) / (FL_WARPS * FL_UNR) : (kvec + STEP - 1) / STEP;
   // A work item = the two weight rows one warp reduces together: two adjacent output columns
   // (O_F16), the gate/up rows of one MLP column (O_GATED), or a rotary pair i, i+hd/2 (O_QKV).
   // TCM: a work UNIT = 8 consecutive items = the 16 rows of one mma A tile (rows 0-7: the items' first
@@ -196,28 +191,7 @@ B2_DEVINL void fused_phase(const FusedParams& p, uint8_t* xs, SYNC sync_fn, bool
   auto advance = [&](Cur& c) {
     if (++c.j == NB) { c.j = 0; c.it += stride; if (c.it < work_total) set_rows(c); }
   };
-  // TCM, K % 32 == 0: 256-bit loads.  A lane then takes 32 contiguous bytes of its row, so one warp-wide load
-  // covers 8 rows x one full 128-byte line instead of 8 rows x 64 bytes: half the requests per byte in flight
-  // (the request rate per SM, not HBM, held the 64-byte form at 28 us against 16 us at one token on gate_up).
-  // The register batch is the same size: FL_UNR/2 loads of 32 bytes per row instead of FL_UNR of 16.
-  const bool wide = wide_k;
   auto load_batch = [&](uint4 (&dst)[FL_UNR][FL_ROWS], const Cur& c) {
-    if (TCM && wide) {
-      if (c.it < work_total) {
-#pragma unroll
-        for (int u2 = 0; u2 < FL_UNR / 2; ++u2) {
-          // 128-byte piece (warp + 16*(u2 + 2j)) of the row, this lane's 32 bytes of it
-          const int idx = 8 * (warp + FL_WARPS * (u2 + (FL_UNR / 2) * c.j)) + 2 * t4;     // in 16-byte vectors
-          if (idx < kvec) {
-            ld_nc_v8(c.r0 + idx * 16, dst[2 * u2][0], dst[2 * u2 + 1][0]);
-            ld_nc_v8(c.r1 + idx * 16, dst[2 * u2][1], dst[2 * u2 + 1][1]);
-          } else {
-            dst[2 * u2][0] = dst[2 * u2 + 1][0] = dst[2 * u2][1] = dst[2 * u2 + 1][1] = make_uint4(0, 0, 0, 0);
-          }
-        }
-      }
-      return;
-    }
     if (c.it < work_total) {
 #pragma unroll
       for (int u = 0; u < FL_UNR; ++u) {
@@ -663,24 +637,6 @@ B2_DEVINL void fused_phase(const FusedParams& p, uint8_t* xs, SYNC sync_fn, bool
     }
   };
   auto consume = [&](const uint4 (&src)[FL_UNR][FL_ROWS], int j) {
-    if (wide) {
-#pragma unroll
-      for (int u2 = 0; u2 < FL_UNR / 2; ++u2) {
-        const int idx = 8 * (warp + FL_WARPS * (u2 + (FL_UNR / 2) * j)) + 2 * t4;
-        if (8 * (warp + FL_WARPS * (u2 + (FL_UNR / 2) * j)) < kvec) {       // warp-uniform
-          uint4 b0 = make_uint4(0, 0, 0, 0), b1 = make_uint4(0, 0, 0, 0);
-          if (g8 < MT && idx < kvec) {
-            b0 = *reinterpret_cast<const uint4*>(xs + (size_t)g8 * XS + (size_t)idx * 16);
-            b1 = *reinterpret_cast<const uint4*>(xs + (size_t)g8 * XS + (size_t)idx * 16 + 16);
-          }
-          fl_mma_s8(c4, src[2 * u2][0].x, src[2 * u2][1].x, src[2 * u2][0].y, src[2 * u2][1].y, b0.x, b0.y);
-          fl_mma_s8(c4, src[2 * u2][0].z, src[2 * u2][1].z, src[2 * u2][0].w, src[2 * u2][1].w, b0.z, b0.w);
-          fl_mma_s8(c4, src[2 * u2 + 1][0].x, src[2 * u2 + 1][1].x, src[2 * u2 + 1][0].y, src[2 * u2 + 1][1].y, b1.x, b1.y);
-          fl_mma_s8(c4, src[2 * u2 + 1][0].z, src[2 * u2 + 1][1].z, src[2 * u2 + 1][0].w, src[2 * u2 + 1][1].w, b1.z, b1.w);
-        }
-      }
-      return;
-    }
 #pragma unroll
     for (int u = 0; u < FL_UNR; ++u) {
       const int q4 = 4 * (warp + FL_WARPS * (u + FL_UNR * j));
