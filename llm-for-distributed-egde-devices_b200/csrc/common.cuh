@@ -107,11 +107,6 @@ B2_DEVINL uint4 ld_nc_v4(const void* p) {   // streaming read-only, no L1 alloca
                : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
   return r;
 }
-// 256-bit streaming load (sm_100: LDG.256): 32 contiguous bytes, 32-byte aligned
-B2_DEVINL void ld_nc_v8(const void* p, uint4& lo, uint4& hi) {
-  asm volatile("ld.global.nc.L1::no_allocate.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-               : "=r"(lo.x), "=r"(lo.y), "=r"(lo.z), "=r"(lo.w), "=r"(hi.x), "=r"(hi.y), "=r"(hi.z), "=r"(hi.w) : "l"(p));
-}
 B2_DEVINL uint4 ld_v4(const void* p) { return *reinterpret_cast<const uint4*>(p); }
 B2_DEVINL uint4 ld_cg_v4(const void* p) {    // L2-coherent: data another CTA of the same launch may have written
   uint4 r;

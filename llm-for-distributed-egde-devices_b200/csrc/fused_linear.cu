@@ -610,6 +610,10 @@ B2_DEVINL void fused_phase(const FusedParams& p, uint8_t* xs, SYNC sync_fn, bool
   flush();
   } else {
   // ---- 4b. 2..8 tokens: the same register-double-buffered stream feeding mma.sync.m16n8k32 -------
+  // (Round 2, measured and dropped: 256-bit loads -- 32 bytes per lane, so one warp-wide request covers 8 rows x a
+  //  full 128-byte line instead of 8 x 64 bytes, same register batch -- left every shape where it was: gate_up
+  //  28.7 vs 28.3 us, qkv 19.2 vs 18.9, o 10.3 vs 10.0, down 18.5 vs 19.3 at 8 tokens.  The request count is not
+  //  what holds the batch stream at half the one-token rate.)
   // With dp4a a batch of 8 tokens costs 32 integer instructions and 8 shared-memory loads per 16 weight
   // bytes per row, and the stream turns compute-bound (gate_up of Llama-2-7B: 45 us against 16 at one
   // token).  Here the 16 rows of a unit are the M dimension of the tile and the tokens its N dimension:
