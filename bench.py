@@ -40,7 +40,7 @@ def parse():
     ap.add_argument("--model", default="llama-2-7b")
     ap.add_argument("--prompt", type=int, default=2048)
     ap.add_argument("--new", type=int, default=128)
-    ap.add_argument("--chunk", type=int, default=0, help="prefill chunk (0 = auto: whole prompt on one GPU, 1024 on 2-4 stages, 512 beyond)")
+    ap.add_argument("--chunk", type=int, default=0, help="prefill chunk (0 = auto: whole prompt on one GPU, 1024 on several stages)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--layers", type=int, default=0, help="PROFILING ONLY: truncate the model to this many layers")
     ap.add_argument("--batch", type=int, default=0,
@@ -349,7 +349,8 @@ def run_ours(a):
     P, NEW = a.prompt, a.new
     # measured (value tok/s): N = 2: 512 -> 16 120, 1024 -> 16 267, 2048 -> 16 180; N = 4: 512 -> 29 632, 1024 -> 29 805
     # (bigger chunks run the GEMMs closer to peak, smaller ones fill the pipeline faster)
-    CH = a.chunk or (min(P, 2048) if world == 1 else min(P, 1024) if world <= 4 else 512)
+    # round 2, N = 8 with the CTA-pair GEMM: 512 -> 54 602, 1024 -> 55 526 (the pair kernel needs >= 48 tiles per launch)
+    CH = a.chunk or (min(P, 2048) if world == 1 else min(P, 1024))
     max_seq = P + NEW
     n_prompts = world                       # weak scaling: one prompt stream per stage
     pipe = DistPipeline.load(cfg, rank, world, dev, seed=0, fast_init=True, max_rows=n_prompts, max_seq=max_seq,
