@@ -300,6 +300,11 @@ int b2_embed(const long long* ids, const int* positions, const void* table, cons
  * Replaces: `lm_head` (left unquantised by load_in_8bit; models_quant_updated.py:66-67 `.logits`). */
 int b2_lm_head(const void* x, const void* W, float* logits, int M, int V, int d, void* stream);
 
+/* logits [T, ld >= V] fp32 += bias [V] fp32, in place.
+ * Replaces: the bias of Phi's lm_head (`nn.Linear(hidden, vocab, bias=True)`, transformers models/phi/modeling_phi.py),
+ * the first answerer the reference loads (Code/Quantised Models/combiner_quant_updated.py:177). */
+int b2_bias_add_f32(float* logits, const float* bias, long long ld, int T, int V, void* stream);
+
 /* Row-wise argmax of fp32 logits [T,V] -> int64 [T]; ties to the lowest index.
  * Replaces: the greedy (do_sample=False) token selection of `generate`. */
 int b2_argmax(const float* logits, long long* out, int T, int V, void* stream);

@@ -34,6 +34,16 @@ class ModelConfig:
     # HF `rope_scaling` of type "llama3" (Llama-3.1/3.2): ("llama3", factor, low_freq_factor,
     # high_freq_factor, original_max_position_embeddings); () = plain RoPE
     rope_scaling: tuple = ()
+    # --- the reference's own model families (Phi-2, Pythia / GPT-NeoX; Code/others/config.yaml:13-16) -----------
+    # parallel residual: attention and MLP both read the layer input, h + attn(ln1 h) + mlp(ln2 h)
+    parallel: bool = False
+    shared_ln: bool = False    # Phi: ONE LayerNorm feeds both branches (stored twice, as ln1 and ln2)
+    rotary_dim: int = 0        # partial rotary: only the first rotary_dim dims of a head are rotated (0 = all)
+    # head_dim is the width the KERNELS see.  A model whose heads are not a multiple of 32 wide (Phi-2: 80) is
+    # padded with zero rows / columns at load time (weights.to_kernel_layout); head_dim_model keeps the real width,
+    # which the softmax scale uses (0 = head_dim).
+    head_dim_model: int = 0
+    head_bias: bool = False    # lm_head carries a bias (Phi)
 
     @property
     def qkv_out(self) -> int:
@@ -51,7 +61,16 @@ class ModelConfig:
         """The plain-dict view the oracle consumes."""
         return dict(n_heads=self.n_heads, n_kv_heads=self.n_kv_heads, head_dim=self.head_dim, eps=self.eps,
                     rope_theta=self.rope_theta, window=self.window, act=self.act, gated=self.gated, rope=self.rope,
-                    rope_scaling=self.rope_scaling)
+                    rope_scaling=self.rope_scaling, parallel=self.parallel, rotary_dim=self.rotary_dim,
+                    head_dim_model=self.head_dim_model)
+
+    @property
+    def hd_model(self) -> int:
+        return self.head_dim_model or self.head_dim
+
+    @property
+    def attn_scale(self) -> float:
+        return 1.0 / float(self.hd_model) ** 0.5
 
     def to_dict(self) -> dict:
         return asdict(self)
@@ -66,6 +85,10 @@ PRESETS = {
     # the refiner of the reference's three-model pipeline (combiner_quant_updated.py:177-203; try.py:303)
     "llama-3.2-1b": ModelConfig("llama-3.2-1b", 16, 2048, 32, 8, 64, 8192, 128256, rope_theta=500000.0, max_pos=8192,
                                 rope_scaling=("llama3", 32.0, 1.0, 4.0, 8192)),
+    # the two answerers of the reference's pipeline (combiner_quant_updated.py:177-178; config.yaml:13-14)
+    "phi-2": ModelConfig("phi-2", 32, 2560, 32, 32, 96, 10240, 51200, eps=1e-5, max_pos=2048, act="gelu_new", gated=False,
+                         norm="layernorm", bias=True, tie_embeddings=False, parallel=True, shared_ln=True, rotary_dim=32,
+                         head_dim_model=80, head_bias=True),
     "mistral-7b": ModelConfig("mistral-7b", 32, 4096, 32, 8, 128, 14336, 32000, window=4096, max_pos=32768),
     # small shapes for tests (same structure, seconds on the CPU oracle)
     "tiny-llama-test": ModelConfig("tiny-llama-test", 4, 256, 4, 4, 64, 512, 512, max_pos=512),
@@ -74,6 +97,9 @@ PRESETS = {
     "tiny-llama3-test": ModelConfig("tiny-llama3-test", 3, 256, 4, 2, 64, 512, 640, rope_theta=500000.0, max_pos=512,
                                     rope_scaling=("llama3", 8.0, 1.0, 4.0, 64)),
     "tiny-hd128-test": ModelConfig("tiny-hd128-test", 2, 512, 4, 4, 128, 1024, 512, max_pos=512),
+    "tiny-phi-test": ModelConfig("tiny-phi-test", 3, 320, 4, 4, 96, 640, 512, eps=1e-5, max_pos=256, act="gelu_new", gated=False,
+                                 norm="layernorm", bias=True, tie_embeddings=False, parallel=True, shared_ln=True,
+                                 rotary_dim=32, head_dim_model=80, head_bias=True),
     "tiny-gpt2-test": ModelConfig("tiny-gpt2-test", 3, 256, 4, 4, 64, 1024, 512, eps=1e-5, max_pos=256, act="gelu_new",
                                   gated=False, norm="layernorm", rope=False, bias=True),
 }
@@ -103,6 +129,20 @@ def from_hf_dict(c: dict) -> ModelConfig:
         return ModelConfig(c.get("_name_or_path", "gpt2"), c["n_layer"], d, h, h, d // h, c.get("n_inner") or 4 * d,
                            c["vocab_size"], eps=c.get("layer_norm_epsilon", 1e-5), max_pos=c.get("n_positions", 1024),
                            act="gelu_new", gated=False, norm="layernorm", rope=False, bias=True)
+    if c.get("model_type") == "phi":
+        d, h = c["hidden_size"], c["num_attention_heads"]
+        hd = c.get("head_dim") or d // h
+        rp = c.get("rope_parameters") or {}
+        # transformers >= 5 keeps the factor the model uses in rope_parameters (a top-level copy defaults to 0.5)
+        prf = rp.get("partial_rotary_factor", c.get("partial_rotary_factor", 0.5))
+        if c.get("qk_layernorm"):
+            raise ValueError("phi with qk_layernorm is not supported")
+        return ModelConfig(c.get("_name_or_path", "phi"), c["num_hidden_layers"], d, h, c.get("num_key_value_heads") or h,
+                           (hd + 31) // 32 * 32, c["intermediate_size"], c["vocab_size"], eps=c.get("layer_norm_eps", 1e-5),
+                           rope_theta=rp.get("rope_theta", c.get("rope_theta", 10000.0)),
+                           max_pos=c.get("max_position_embeddings", 2048), act=c.get("hidden_act", "gelu_new"), gated=False,
+                           norm="layernorm", bias=True, tie_embeddings=False, parallel=True, shared_ln=True,
+                           rotary_dim=int(hd * prf), head_dim_model=hd, head_bias=True)
     d, h = c["hidden_size"], c["num_attention_heads"]
     rs = c.get("rope_scaling") or {}
     kind = rs.get("rope_type", rs.get("type"))

@@ -61,6 +61,7 @@ int fused_linear(const void*, long long, int, const void*, const void*, const fl
 int embed(const long long*, const int*, const void*, const void*, void*, int, int, int, cudaStream_t);
 int argmax_rows(const float*, long long*, int, int, cudaStream_t);
 int confidence(const float*, long long, float*, float*, int, int, cudaStream_t);
+int bias_add_f32(float*, const float*, long long, int, int, cudaStream_t);
 int argmax_shard(const float*, long long, long long*, float*, long long, const float*, const long long*, int, int, cudaStream_t);
 }  // namespace b2
 
@@ -137,6 +138,9 @@ int b2_p2p_wait(const unsigned int* flag, unsigned int seq, const void* src, voi
 int b2_argmax_shard(const float* logits, long long ld, long long* out_idx, float* out_val, long long idx_offset,
                     const float* other_val, const long long* other_idx, int T, int V, void* stream) {
   return b2::argmax_shard(logits, ld, out_idx, out_val, idx_offset, other_val, other_idx, T, V, ST(stream));
+}
+int b2_bias_add_f32(float* logits, const float* bias, long long ld, int T, int V, void* stream) {
+  return b2::bias_add_f32(logits, bias, ld, T, V, ST(stream));
 }
 int b2_confidence(const float* logits, long long ld, float* row_pmax, float* out, int T, int V, void* stream) {
   return b2::confidence(logits, ld, row_pmax, out, T, V, ST(stream));

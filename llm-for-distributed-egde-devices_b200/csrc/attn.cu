@@ -488,7 +488,7 @@ int decode_attn(const void* q, long long q_ld, const void* kcache, const void* v
   if (B == 0) return OK;
   if (!q || !kcache || !vcache || !seqlens || !out) return ERR_NULL_PTR;
   if (B < 0 || H <= 0 || KV <= 0 || H % KV || H / KV > 8 || (q_ld & 1) || max_seqlen <= 0) return ERR_BAD_SHAPE;
-  if (hd != 64 && hd != 128) return ERR_UNSUPPORTED;
+  if (hd != 64 && hd != 96 && hd != 128) return ERR_UNSUPPORTED;
   const int eff = (window > 0 && max_seqlen > window) ? window : max_seqlen;
   int splits = decode_attn_splits(B, KV, eff, sm_count_attn());
   // 2..8 splits: merged inside the kernel by a thread-block cluster over DSMEM (workspace unused).
@@ -507,7 +507,8 @@ int decode_attn(const void* q, long long q_ld, const void* kcache, const void* v
   p.H = H; p.KV = KV; p.Smax = Smax; p.splits = splits; p.window = window;
   p.scale_log2 = scale * 1.4426950408889634f;
   p.pf0 = (const uint8_t*)pf0; p.pf0_bytes = pf0_bytes; p.pf1 = (const uint8_t*)pf1; p.pf1_bytes = pf1_bytes;
-  return hd == 128 ? launch_decode<128>(p, B, st, use_cluster) : launch_decode<64>(p, B, st, use_cluster);
+  return hd == 128 ? launch_decode<128>(p, B, st, use_cluster)
+       : hd == 96 ? launch_decode<96>(p, B, st, use_cluster) : launch_decode<64>(p, B, st, use_cluster);
 }
 
 // =============================================================================================
@@ -553,7 +554,7 @@ int decode_attn_static(const void* q, long long q_ld, const void* kcache, const 
   if (B == 0) return OK;
   if (!q || !kcache || !vcache || !seqlens || !out) return ERR_NULL_PTR;
   if (B < 0 || H <= 0 || KV <= 0 || H % KV || H / KV > 8 || (q_ld & 1) || max_seqlen <= 0) return ERR_BAD_SHAPE;
-  if (hd != 64 && hd != 128) return ERR_UNSUPPORTED;
+  if (hd != 64 && hd != 96 && hd != 128) return ERR_UNSUPPORTED;
   const int eff = (window > 0 && max_seqlen > window) ? window : max_seqlen;
   const int splits = decode_attn_splits(B, KV, eff, sm_count_attn());
   const size_t need = decode_attn_workspace_bytes(B, H, hd, splits);
@@ -571,7 +572,7 @@ int decode_attn_static(const void* q, long long q_ld, const void* kcache, const 
   p.H = H; p.KV = KV; p.Smax = Smax; p.splits = splits; p.window = window;
   p.scale_log2 = scale * 1.4426950408889634f;
   p.pf0 = nullptr; p.pf0_bytes = 0; p.pf1 = nullptr; p.pf1_bytes = 0;
-  return hd == 128 ? launch_decode<128>(p, B, st) : launch_decode<64>(p, B, st);
+  return hd == 128 ? launch_decode<128>(p, B, st) : hd == 96 ? launch_decode<96>(p, B, st) : launch_decode<64>(p, B, st);
 }
 
 // =============================================================================================
@@ -797,12 +798,17 @@ int init_attn() {
     bool ok = cudaFuncGetAttributes(&fa, rope_kv_append_kernel) == cudaSuccess;
     ok &= cudaFuncGetAttributes(&fa, decode_merge_kernel<128>) == cudaSuccess;
     ok &= cudaFuncGetAttributes(&fa, decode_merge_kernel<64>) == cudaSuccess;
+    ok &= cudaFuncGetAttributes(&fa, decode_merge_kernel<96>) == cudaSuccess;
     if (!ok) return ERR_ARCH;
   }
   if (cudaFuncSetAttribute(decode_attn_kernel<128, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_NST * 2 * DEC_TK * (128 + 8) * 2) != cudaSuccess) return ERR_ARCH;
   if (cudaFuncSetAttribute(decode_attn_kernel<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_NST * 2 * DEC_TK * (128 + 8) * 2 + 8 * 8 * (128 + 2) * 4) != cudaSuccess) return ERR_ARCH;
   if (cudaFuncSetAttribute(decode_attn_kernel<64, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_NST * 2 * DEC_TK * (64 + 8) * 2) != cudaSuccess) return ERR_ARCH;
   if (cudaFuncSetAttribute(decode_attn_kernel<64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_NST * 2 * DEC_TK * (64 + 8) * 2 + 8 * 8 * (64 + 2) * 4) != cudaSuccess) return ERR_ARCH;
+  // head_dim 96: Phi-2's 80-wide heads padded to a multiple of 32 (weights.head_slots)
+  if (cudaFuncSetAttribute(decode_attn_kernel<96, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_NST * 2 * DEC_TK * (96 + 8) * 2) != cudaSuccess) return ERR_ARCH;
+  if (cudaFuncSetAttribute(decode_attn_kernel<96, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_NST * 2 * DEC_TK * (96 + 8) * 2 + 8 * 8 * (96 + 2) * 4) != cudaSuccess) return ERR_ARCH;
+  if (cudaFuncSetAttribute(prefill_attn_kernel<96>, cudaFuncAttributeMaxDynamicSharedMemorySize, pf_smem_bytes<96>()) != cudaSuccess) return ERR_ARCH;
   if (cudaFuncSetAttribute(prefill_attn_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, pf_smem_bytes<128>()) != cudaSuccess) return ERR_ARCH;
   if (cudaFuncSetAttribute(prefill_attn_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, pf_smem_bytes<64>()) != cudaSuccess) return ERR_ARCH;
   return OK;
@@ -822,7 +828,7 @@ int prefill_attn(const void* q, long long q_ld, const void* kcache, const void* 
   if (T == 0) return OK;
   if (!q || !kcache || !vcache || !out) return ERR_NULL_PTR;
   if (T < 0 || (!positions && (pos0 < 0 || pos0 + T > Smax)) || H <= 0 || KV <= 0 || H % KV || (q_ld & 1) || (o_ld & 1)) return ERR_BAD_SHAPE;
-  if (hd != 64 && hd != 128) return ERR_UNSUPPORTED;
+  if (hd != 64 && hd != 96 && hd != 128) return ERR_UNSUPPORTED;
   const bool tc_ok = prefill_attn_tc_supported(T, hd, window, q_ld, q, kcache, vcache) && !(o_ld & 7) &&
                      !(reinterpret_cast<uintptr_t>(out) & 15);
   if (g_prefill_impl == 2 && !tc_ok) return ERR_UNSUPPORTED;
@@ -832,7 +838,7 @@ int prefill_attn(const void* q, long long q_ld, const void* kcache, const void* 
   p.q = (const __half*)q; p.q_ld = q_ld; p.k = (const __half*)kcache; p.v = (const __half*)vcache;
   p.out = (__half*)out; p.o_ld = o_ld; p.pos_ptr = positions; p.T = T; p.pos0 = pos0; p.row = row; p.H = H; p.KV = KV; p.Smax = Smax;
   p.window = window; p.scale_log2 = scale * 1.4426950408889634f;
-  return hd == 128 ? launch_prefill<128>(p, st) : launch_prefill<64>(p, st);
+  return hd == 128 ? launch_prefill<128>(p, st) : hd == 96 ? launch_prefill<96>(p, st) : launch_prefill<64>(p, st);
 }
 
 }  // namespace b2

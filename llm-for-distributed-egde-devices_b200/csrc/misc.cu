@@ -178,11 +178,25 @@ int confidence(const float* logits, long long ld, float* row_pmax, float* out, i
   return launch_status();
 }
 
+// logits[t, v] += bias[v] (fp32): Phi's lm_head carries a bias (modeling_phi.py: lm_head = nn.Linear(..., bias=True))
+__global__ void __launch_bounds__(256) bias_add_f32_kernel(float* __restrict__ x, const float* __restrict__ b, long long ld, int V) {
+  float* row = x + (long long)blockIdx.y * ld;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < V; i += gridDim.x * blockDim.x) row[i] = add_rn(row[i], b[i]);
+}
+int bias_add_f32(float* x, const float* bias, long long ld, int T, int V, cudaStream_t st) {
+  if (T == 0) return OK;
+  if (!x || !bias) return ERR_NULL_PTR;
+  if (T < 0 || V <= 0 || ld < V) return ERR_BAD_SHAPE;
+  bias_add_f32_kernel<<<dim3((V + 2047) / 2048, T), 256, 0, st>>>(x, bias, ld, V);
+  return launch_status();
+}
+
 int init_misc() {
   cudaFuncAttributes fa;
   bool ok = cudaFuncGetAttributes(&fa, embed_kernel) == cudaSuccess;
   ok &= cudaFuncGetAttributes(&fa, argmax_kernel) == cudaSuccess;
   ok &= cudaFuncGetAttributes(&fa, row_pmax_kernel) == cudaSuccess;
+  ok &= cudaFuncGetAttributes(&fa, bias_add_f32_kernel) == cudaSuccess;
   ok &= cudaFuncGetAttributes(&fa, mean_rows_kernel) == cudaSuccess;
   return ok ? OK : ERR_ARCH;
 }

@@ -97,7 +97,9 @@ def _family(model_dir: str) -> str:
         return "gpt2"
     if mt in ("llama", "mistral"):
         return "llama"
-    raise ValueError(f"model_type {mt!r}: no tensor-name map for this family (llama, mistral and gpt2 are supported)")
+    if mt == "phi":
+        return "phi"
+    raise ValueError(f"model_type {mt!r}: no tensor-name map for this family (llama, mistral, phi and gpt2 are supported)")
 
 
 # --------------------------------------------------------------------------------------------------
@@ -113,6 +115,16 @@ def load_layer_fp32(src: TensorSource, cfg: ModelConfig, layer: int, family: str
                  wgu=torch.cat([g("mlp.gate_proj.weight"), g("mlp.up_proj.weight")], 0), wd=g("mlp.down_proj.weight"))
         if src.has(p + "self_attn.q_proj.bias"):
             raise ValueError("attention biases are not supported for the llama family here")
+    elif family == "phi":        # Phi-2: biases everywhere, ONE LayerNorm per layer, heads in the model's 80-wide layout
+        p = f"model.layers.{layer}."
+        g = lambda n: src.get(p + n, p.replace("model.", "", 1) + n)
+        w = dict(ln1_g=g("input_layernorm.weight"), ln1_b=g("input_layernorm.bias"),
+                 wqkv=torch.cat([g("self_attn.q_proj.weight"), g("self_attn.k_proj.weight"), g("self_attn.v_proj.weight")], 0),
+                 b_qkv=torch.cat([g("self_attn.q_proj.bias"), g("self_attn.k_proj.bias"), g("self_attn.v_proj.bias")], 0),
+                 wo=g("self_attn.dense.weight"), b_o=g("self_attn.dense.bias"),
+                 wgu=g("mlp.fc1.weight"), b_gu=g("mlp.fc1.bias"), wd=g("mlp.fc2.weight"), b_d=g("mlp.fc2.bias"))
+        w["ln2_g"], w["ln2_b"] = w["ln1_g"].clone(), w["ln1_b"].clone()
+        w = weights.to_kernel_layout(cfg, w)
     else:   # GPT-2: Conv1D weights are [in, out]
         p = f"transformer.h.{layer}."
         g = lambda n: src.get(p + n, p.replace("transformer.", "", 1) + n)
@@ -138,6 +150,14 @@ def load_embed_fp32(src: TensorSource, cfg: ModelConfig, family: str, first: boo
         if last:
             out["lnf_g"] = src.get("model.norm.weight", "norm.weight")
             out["lm_head"] = src.get("lm_head.weight") if src.has("lm_head.weight") else src.get(*emb)
+    elif family == "phi":
+        if first:
+            out["embed"] = src.get("model.embed_tokens.weight", "embed_tokens.weight")
+        if last:
+            out["lnf_g"] = src.get("model.final_layernorm.weight", "final_layernorm.weight")
+            out["lnf_b"] = src.get("model.final_layernorm.bias", "final_layernorm.bias")
+            out["lm_head"] = src.get("lm_head.weight")
+            out["lm_head_b"] = src.get("lm_head.bias")
     else:
         emb = ("transformer.wte.weight", "wte.weight")
         if first:
@@ -168,7 +188,7 @@ def build_stage_weights_from_checkpoint(model_dir: str, layer_begin: int, layer_
     if first or last:
         e = load_embed_fp32(src, cfg, fam, first, last)
         for k, v in e.items():
-            sw[k] = v.to(torch.float16).to(device)
+            sw[k] = v.to(torch.float32 if k == "lm_head_b" else torch.float16).to(device)
         if first and last and cfg.tie_embeddings:
             sw["lm_head"] = sw["embed"]
     return sw

@@ -423,6 +423,14 @@ def argmax_shard(logits, idx_offset=0, out_idx=None, out_val=None, other=None):
     return o
 
 
+def bias_add_f32(logits, bias):
+    """logits [T,V] fp32 += bias [V] fp32 (in place).  b2_bias_add_f32."""
+    _cuda(logits, bias)
+    T, V = logits.shape
+    check(_abi.lib().b2_bias_add_f32(ptr(logits), ptr(bias), logits.stride(0), T, V, stream_handle()), "b2_bias_add_f32")
+    return logits
+
+
 def confidence(logits):
     """logits [T,V] fp32 -> (mean over rows of the largest softmax probability [1] fp32, per-row values [T]).
     b2_confidence."""

@@ -241,6 +241,8 @@ class DistPipeline:
         self.p2p = None
         if self.world < 2 or self.device.type != "cuda" or os.environ.get("B2_HANDOFF", "p2p") == "nccl":
             return
+        if torch.cuda.device_count() < self.world:
+            return          # ranks sharing a GPU: their flag-polling kernels are not guaranteed to run at the same time
         dist, dev, R = self.dist, self.device, int(max_rows)
         slot = (2 * self.d + 16 + 255) & ~255
         off_head, off_flags = R * slot, 2 * R * slot

@@ -130,9 +130,9 @@ class Stage:
         self.first, self.last = bool(sw["first"]), bool(sw["last"])
         self.layer_begin, self.layer_end = layer_begin, layer_end
         self.device = torch.device(device)
-        cos, sin = weights.rope_table(cfg.head_dim, cfg.max_pos, cfg.rope_theta, cfg.rope_scaling)
+        cos, sin = weights.rope_table(cfg.head_dim, cfg.max_pos, cfg.rope_theta, cfg.rope_scaling, cfg.rotary_dim)
         self.cos, self.sin = cos.to(self.device), sin.to(self.device)
-        self.scale = 1.0 / float(np.sqrt(cfg.head_dim))
+        self.scale = cfg.attn_scale        # 1/sqrt of the MODEL's head width (heads padded for the kernels keep it)
         self._scratch = None
         self._ws = None
         self._runners = {}
@@ -229,6 +229,9 @@ class Stage:
             if x.data_ptr() != h.data_ptr():
                 h.copy_(x.view(T, d))
         h_alt = buf.h[1][:T]
+        # parallel residual (Phi, GPT-NeoX): the MLP branch reads the layer input h, not h + attention; the down
+        # projection still adds h_alt = h + attention, so the layer returns h + attention + mlp
+        par = cfg.parallel
         qkv, attn, gu = buf.qkv[:T], buf.attn[:T], buf.gu[:T]
         sc = buf.scale[:T]
         act = (ops.ACT_SILU_MUL if cfg.act == "silu" else ops.ACT_GELU_MUL) if cfg.gated else \
@@ -260,7 +263,7 @@ class Stage:
                 nl = layers[li + 1] if li + 1 < len(layers) else None
                 d_o = ops.fused_desc(attn, lw["wo"], lw["s_o"], x_kind=ops.X_PLAIN, smooth=lw["sm_o"], bias=lw.get("b_o"),
                                      residual=h, out=h_alt, zero_amax=buf.amax)
-                d_g = ops.fused_desc(h_alt, lw["wgu"], lw["s_gu"], x_kind=xk_norm, gamma=lw["ln2_g"], beta=lw.get("ln2_b"),
+                d_g = ops.fused_desc(h if par else h_alt, lw["wgu"], lw["s_gu"], x_kind=xk_norm, gamma=lw["ln2_g"], beta=lw.get("ln2_b"),
                                      smooth=lw["sm_gu"], eps=cfg.eps, bias=lw.get("b_gu"), out=buf.y32[:T],
                                      out_kind=ops.O_GATED, act=0 if cfg.act == "silu" else 1, out_smooth=lw["sm_d"],
                                      out_amax=buf.amax, prefetch=(lw["wd"],) if pf else None)
@@ -288,7 +291,7 @@ class Stage:
                                  residual=h, out=h_alt, zero_amax=buf.amax, prefetch=self._hints("o", lw, li))
                 n += 3 if ws is None else 4
                 if cfg.gated:
-                    ops.fused_linear(h_alt, lw["wgu"], lw["s_gu"], x_kind=xk_norm, gamma=lw["ln2_g"],
+                    ops.fused_linear(h if par else h_alt, lw["wgu"], lw["s_gu"], x_kind=xk_norm, gamma=lw["ln2_g"],
                                      beta=lw.get("ln2_b"), smooth=lw["sm_gu"], eps=cfg.eps, bias=lw.get("b_gu"),
                                      out=buf.y32[:T], out_kind=ops.O_GATED, act=0 if cfg.act == "silu" else 1,
                                      out_smooth=lw["sm_d"], out_amax=buf.amax,
@@ -300,7 +303,7 @@ class Stage:
                                      prefetch=self._hints("down", lw, li))
                     n += 2
                 else:
-                    ops.fused_linear(h_alt, lw["wgu"], lw["s_gu"], x_kind=xk_norm, gamma=lw["ln2_g"],
+                    ops.fused_linear(h if par else h_alt, lw["wgu"], lw["s_gu"], x_kind=xk_norm, gamma=lw["ln2_g"],
                                      beta=lw.get("ln2_b"), smooth=lw["sm_gu"], eps=cfg.eps, bias=lw.get("b_gu"), out=gu)
                     q8 = buf.q8view(T, F)
                     ops.act_mul_quant(gu, lw["sm_d"], act, out_q=q8, out_scale=sc)
@@ -333,7 +336,7 @@ class Stage:
             ops.smooth_quant(attn, lw["sm_o"], out_q=q8, out_scale=sc)
             ops.gemm_w8a8(q8, lw["wo"], sc, lw["s_o"], lw.get("b_o"), h, out=h_alt)
             q8 = buf.q8view(T, d)
-            ops.norm_quant(h_alt, lw["ln2_g"], lw.get("ln2_b"), lw["sm_gu"], cfg.eps, out_q=q8, out_scale=sc)
+            ops.norm_quant(h if par else h_alt, lw["ln2_g"], lw.get("ln2_b"), lw["sm_gu"], cfg.eps, out_q=q8, out_scale=sc)
             if pair and cfg.gated and F % 32 == 0:
                 y32 = gu.view(torch.float32)                     # [T,F] fp32 in the storage of the fp16 [T,2F] buffer
                 am = buf.amax_p[:T]
@@ -361,6 +364,9 @@ class Stage:
             lg = ops.lm_head(hn, self.w["lm_head"][self.head_split():], out=out)
         else:
             lg = ops.lm_head(hn, self.w["lm_head"], out=out)
+            if "lm_head_b" in self.w:           # Phi: lm_head carries a bias
+                ops.bias_add_f32(lg, self.w["lm_head_b"])
+                n += 1
         return lg, n + 2
 
     def head_split(self) -> int:
@@ -402,7 +408,7 @@ class Stage:
             ops.prefill_attn(qkv, kc, vc, 0, row0, H, KV, hd, self.scale, cfg.window, out=attn, positions=dpos)
         ops.llm_int8_linear(attn, lw["wo"], lw["s_o"], x["scr_o"], bias=lw.get("b_o"), residual=h, out=h_alt,
                             q_buf=buf.q8view(T, H * hd), scale_buf=sc, dense=dense, fused_decode=fd)
-        ops.norm(h_alt, lw["ln2_g"], lw.get("ln2_b"), cfg.eps, out=y)
+        ops.norm(h if cfg.parallel else h_alt, lw["ln2_g"], lw.get("ln2_b"), cfg.eps, out=y)
         ops.llm_int8_linear(y, lw["wgu"], lw["s_gu"], x["scr_d"], bias=lw.get("b_gu"), out=gu,
                             q_buf=buf.q8view(T, d), scale_buf=sc, dense=dense, fused_decode=fd)
         ops.act_mul(gu, F, act, out=hm)

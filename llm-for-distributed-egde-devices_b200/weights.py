@@ -31,27 +31,82 @@ def _gen(seed: int, *tags: int) -> torch.Generator:
     return g
 
 
-def init_layer_fp32(cfg: ModelConfig, layer: int, seed: int = 0) -> dict:
-    """fp32 weights of one decoder layer (HF naming collapsed: wqkv = [q;k;v], wgu = [gate;up])."""
+def head_slots(cfg: ModelConfig) -> np.ndarray:
+    """Kernel layout of one attention head: slot j of the head_dim-wide head holds model dim head_slots[j], -1 = zero.
+
+    The kernels rotate the pairs (j, j + head_dim/2) of a head and know nothing of partial rotary or odd head
+    widths.  A model that rotates only its first rotary_dim dims (pairs (j, j + rotary_dim/2): Phi, GPT-NeoX) or
+    whose heads are not a multiple of 32 wide (Phi-2: 80) is brought into that form when its weights are loaded:
+    the rotary pairs go to slots (j, j + head_dim/2), j < rotary_dim/2, the other dims fill the remaining slots
+    (their rope-table entries are cos = 1, sin = 0: an exact no-op), the rest is zero padding.  q and k are permuted
+    alike, so every q.k product is unchanged; v and the o_proj columns take the same permutation."""
+    hd, hm = cfg.head_dim, cfg.hd_model
+    rd = cfg.rotary_dim or hm
+    half, r2 = hd // 2, rd // 2
+    if rd > hm or rd % 2 or hm > hd or r2 > half:
+        raise ValueError("bad rotary_dim / head_dim_model")
+    src = np.full((hd,), -1, dtype=np.int64)
+    src[:r2] = np.arange(r2)
+    src[half:half + r2] = np.arange(r2, rd)
+    free = [j for j in range(hd) if not (j < r2 or half <= j < half + r2)]
+    rest = np.arange(rd, hm)
+    src[free[: len(rest)]] = rest
+    return src
+
+
+def to_kernel_layout(cfg: ModelConfig, w: dict) -> dict:
+    """Layer weights in the MODEL's head layout (wqkv [(H+2KV)*hd_model, d], wo [d, H*hd_model], b_qkv) -> the
+    kernels' layout (head_dim wide heads, see head_slots).  The identity for the Llama / GPT-2 families."""
+    src = head_slots(cfg)
+    hm, hd = cfg.hd_model, cfg.head_dim
+    if hm == hd and np.array_equal(src, np.arange(hd)):
+        return w
+    H, KV = cfg.n_heads, cfg.n_kv_heads
+    idx = torch.from_numpy(np.where(src >= 0, src, 0))
+    keep = torch.from_numpy((src >= 0).astype(np.float32))
+
+    def rows(t, nh):           # [nh*hm, ...] -> [nh*hd, ...]
+        t = t.reshape(nh, hm, *t.shape[1:])[:, idx]
+        return (t * keep.reshape(1, hd, *([1] * (t.dim() - 2)))).reshape(nh * hd, *t.shape[2:])
+    out = dict(w)
+    q, k, v = w["wqkv"][: H * hm], w["wqkv"][H * hm:(H + KV) * hm], w["wqkv"][(H + KV) * hm:]
+    out["wqkv"] = torch.cat([rows(q, H), rows(k, KV), rows(v, KV)], 0).contiguous()
+    if "b_qkv" in w:
+        b = w["b_qkv"]
+        out["b_qkv"] = torch.cat([rows(b[: H * hm], H), rows(b[H * hm:(H + KV) * hm], KV), rows(b[(H + KV) * hm:], KV)], 0).contiguous()
+    out["wo"] = rows(w["wo"].t().contiguous(), H).t().contiguous()
+    return out
+
+
+def init_layer_fp32(cfg: ModelConfig, layer: int, seed: int = 0, layout: str = "kernel") -> dict:
+    """fp32 weights of one decoder layer (HF naming collapsed: wqkv = [q;k;v], wgu = [gate;up]).
+    Drawn in the model's own head layout; layout="kernel" (default) applies to_kernel_layout (the identity for
+    Llama / GPT-2 shapes), layout="model" returns them as a HF module of that family would hold them."""
     g = _gen(seed, layer)
     d, F = cfg.d_model, cfg.ffn
+    hm = cfg.hd_model
     std = 0.02
 
     def rn(*shape):
         return torch.randn(*shape, generator=g, dtype=torch.float32) * std
 
+    qkv_rows = (cfg.n_heads + 2 * cfg.n_kv_heads) * hm
     w = dict(
         ln1_g=1.0 + 0.1 * torch.randn(d, generator=g), ln2_g=1.0 + 0.1 * torch.randn(d, generator=g),
-        wqkv=rn(cfg.qkv_out, d), wo=rn(d, cfg.n_heads * cfg.head_dim), wgu=rn(cfg.up_out, d), wd=rn(d, F))
+        wqkv=rn(qkv_rows, d), wo=rn(d, cfg.n_heads * hm), wgu=rn(cfg.up_out, d), wd=rn(d, F))
     if cfg.norm == "layernorm":
         w["ln1_b"] = 0.02 * torch.randn(d, generator=g)
         w["ln2_b"] = 0.02 * torch.randn(d, generator=g)
     if cfg.bias:
-        w["b_qkv"] = rn(cfg.qkv_out)
+        w["b_qkv"] = rn(qkv_rows)
         w["b_o"] = rn(d)
         w["b_gu"] = rn(cfg.up_out)
         w["b_d"] = rn(d)
-    return w
+    if cfg.shared_ln:          # one LayerNorm feeds attention and MLP: kept twice so that every code path stays uniform
+        w["ln2_g"] = w["ln1_g"].clone()
+        if "ln1_b" in w:
+            w["ln2_b"] = w["ln1_b"].clone()
+    return to_kernel_layout(cfg, w) if layout == "kernel" else w
 
 
 def init_embed_fp32(cfg: ModelConfig, seed: int = 0) -> dict:
@@ -62,7 +117,11 @@ def init_embed_fp32(cfg: ModelConfig, seed: int = 0) -> dict:
         out["lnf_b"] = 0.02 * torch.randn(cfg.d_model, generator=g)
     if not cfg.rope:
         out["pos_embed"] = torch.randn(cfg.max_pos, cfg.d_model, generator=g, dtype=torch.float32) * 0.02
-    out["lm_head"] = e if cfg.tie_embeddings else torch.randn(cfg.vocab, cfg.d_model, generator=g) * 0.02
+    # untied heads (Phi): a separate matrix, but close to the embedding table, so that greedy margins stay as wide as
+    # in the tied models (a purely random head leaves top-1 margins at the size of the W8A8 noise)
+    out["lm_head"] = e if cfg.tie_embeddings else e + torch.randn(cfg.vocab, cfg.d_model, generator=g) * 0.02
+    if cfg.head_bias:
+        out["lm_head_b"] = torch.randn(cfg.vocab, generator=g) * 0.02
     return out
 
 
@@ -152,6 +211,8 @@ def build_stage_weights(cfg: ModelConfig, layer_begin: int, layer_end: int, firs
             if "lnf_b" in e:
                 sw["lnf_b"] = e["lnf_b"].to(torch.float16).to(device)
             sw["lm_head"] = sw["embed"] if (first and cfg.tie_embeddings) else e["lm_head"].to(torch.float16).to(device)
+            if "lm_head_b" in e:
+                sw["lm_head_b"] = e["lm_head_b"].to(torch.float32).to(device)
     return sw
 
 
@@ -220,14 +281,15 @@ def to_numpy(sw: dict) -> dict:
     return out
 
 
-def rope_table(head_dim: int, max_pos: int, theta: float = 10000.0, scaling: tuple = ()):
+def rope_table(head_dim: int, max_pos: int, theta: float = 10000.0, scaling: tuple = (), rotary_dim: int = 0):
     """cos/sin fp32 [max_pos, head_dim/2]: angle formed in fp32 as HF does
     (modeling_llama.py:100-126), cos/sin evaluated in fp64 and rounded once.  Host-side table; the
     kernels only read it, so device and oracle use bit-identical values.
     scaling = ("llama3", factor, low_freq_factor, high_freq_factor, original_max_pos): the frequency
     remap of Llama-3.1/3.2 (transformers modeling_rope_utils.py `_compute_llama3_parameters`), in fp32 like HF."""
-    i = np.arange(0, head_dim, 2, dtype=np.float64)
-    inv_freq = (1.0 / (theta ** (i / head_dim))).astype(np.float32)
+    rd = rotary_dim or head_dim          # partial rotary (kernel layout, head_slots): the first rd/2 pairs rotate
+    i = np.arange(0, rd, 2, dtype=np.float64)
+    inv_freq = (1.0 / (theta ** (i / rd))).astype(np.float32)
     if scaling:
         kind, factor, low_f, high_f, old_ctx = scaling
         if kind != "llama3":
@@ -241,4 +303,6 @@ def rope_table(head_dim: int, max_pos: int, theta: float = 10000.0, scaling: tup
         inv_freq = np.where((wavelen >= high_wl) & (wavelen <= low_wl), mid, scaled).astype(f32)
     inv_freq = inv_freq.astype(np.float64)
     ang = (np.arange(max_pos, dtype=np.float64)[:, None] * inv_freq[None, :]).astype(np.float32).astype(np.float64)
-    return torch.from_numpy(np.cos(ang).astype(np.float32)), torch.from_numpy(np.sin(ang).astype(np.float32))
+    cos, sin = np.ones((max_pos, head_dim // 2), np.float32), np.zeros((max_pos, head_dim // 2), np.float32)
+    cos[:, : rd // 2], sin[:, : rd // 2] = np.cos(ang).astype(np.float32), np.sin(ang).astype(np.float32)
+    return torch.from_numpy(cos), torch.from_numpy(sin)

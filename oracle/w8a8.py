@@ -289,20 +289,25 @@ def llm_int8_linear(y16, w_q, w_scale, bias16=None, residual16=None, threshold=L
     return out, acc, cols
 
 
-def rope_table(head_dim: int, max_pos: int, theta: float = 10000.0, scaling=()):
+def rope_table(head_dim: int, max_pos: int, theta: float = 10000.0, scaling=(), rotary_dim: int = 0):
     """cos/sin tables fp32 [max_pos, head_dim/2] (modeling_llama.py:100-153: inv_freq =
     theta^(-2i/hd), angle = pos*inv_freq; optional ("llama3", factor, low, high, old_ctx) remap).
     Computed in fp64, rounded once; the GPU reads this exact table, so no device-side sincos is
     involved."""
-    i = np.arange(0, head_dim, 2, dtype=np.float64)
-    inv_freq = (1.0 / (theta ** (i / head_dim))).astype(f32)
+    rd = rotary_dim or head_dim
+    i = np.arange(0, rd, 2, dtype=np.float64)
+    inv_freq = (1.0 / (theta ** (i / rd))).astype(f32)
     if scaling:
         assert scaling[0] == "llama3", scaling
         inv_freq = llama3_inv_freq(inv_freq, *scaling[1:])
     inv_freq = inv_freq.astype(np.float64)
     ang = np.arange(max_pos, dtype=np.float64)[:, None] * inv_freq[None, :]
     ang = ang.astype(f32).astype(np.float64)   # HF forms the angle in fp32
-    return np.cos(ang).astype(f32), np.sin(ang).astype(f32)
+    # partial rotary (Phi, GPT-NeoX: modeling_phi.py:216-231): in the kernel layout the rotary pairs are the first
+    # rd/2 pairs (j, j + head_dim/2); every other pair gets cos = 1, sin = 0, which apply_rope passes through exactly
+    cos, sin = np.ones((max_pos, head_dim // 2), f32), np.zeros((max_pos, head_dim // 2), f32)
+    cos[:, : rd // 2], sin[:, : rd // 2] = np.cos(ang).astype(f32), np.sin(ang).astype(f32)
+    return cos, sin
 
 
 def apply_rope(x16: np.ndarray, positions: np.ndarray, cos: np.ndarray, sin: np.ndarray) -> np.ndarray:
@@ -384,7 +389,7 @@ def block_forward(h16, lw, cfg, cache: KVCacheOracle, li, seq_ids, positions, co
         cache.k[li, seq_ids[t], :, positions[t], :] = kh[t]
         cache.v[li, seq_ids[t], :, positions[t], :] = vh[t]
     attn = np.zeros((T, H, hd), dtype=f16)
-    scale = 1.0 / np.sqrt(hd)
+    scale = 1.0 / np.sqrt(cfg.get("head_dim_model") or hd)      # heads padded to the kernel width keep the model's scale
     for b in np.unique(seq_ids):
         idx = np.nonzero(seq_ids == b)[0]
         S = int(positions[idx].max()) + 1
@@ -394,7 +399,10 @@ def block_forward(h16, lw, cfg, cache: KVCacheOracle, li, seq_ids, positions, co
     q2, s2 = smooth_quant(attn.reshape(T, H * hd), lw.get("sm_o"))
     h1, acc_o = gemm_w8a8(q2, lw["wo"], s2, lw["s_o"], lw.get("b_o"), h16)
     # --- MLP half -------------------------------------------------------------------
-    q3, s3 = norm_quant(h1, lw["ln2_g"], lw.get("ln2_b"), lw.get("sm_gu"), eps)
+    # parallel residual (Phi: modeling_phi.py:289-307; GPT-NeoX use_parallel_residual): the MLP reads the layer
+    # INPUT, and the block returns h + attn + mlp = (h + attn) + mlp
+    mlp_in = h16 if cfg.get("parallel", False) else h1
+    q3, s3 = norm_quant(mlp_in, lw["ln2_g"], lw.get("ln2_b"), lw.get("sm_gu"), eps)
     gu, acc_gu = gemm_w8a8(q3, lw["wgu"], s3, lw["s_gu"], lw.get("b_gu"), None)
     if cfg.get("gated", True):
         q4, s4 = act_mul_quant(gu, lw.get("sm_d"), cfg.get("act", "silu"))
@@ -421,7 +429,7 @@ def _attend(qkv, cfg, cache, li, seq_ids, positions, cos, sin):
         cache.k[li, seq_ids[t], :, positions[t], :] = kh[t]
         cache.v[li, seq_ids[t], :, positions[t], :] = vh[t]
     attn = np.zeros((T, H, hd), dtype=f16)
-    scale = 1.0 / np.sqrt(hd)
+    scale = 1.0 / np.sqrt(cfg.get("head_dim_model") or hd)
     for b in np.unique(seq_ids):
         idx = np.nonzero(seq_ids == b)[0]
         S = int(positions[idx].max()) + 1
@@ -501,14 +509,17 @@ def stage_forward(x, sw, cfg, cache, seq_ids, positions, cos, sin, trace=None, l
     if logits_rows is not None:
         h = h[logits_rows]
     hn = final_norm(h, sw["lnf_g"], sw.get("lnf_b"), cfg["eps"])
-    return lm_head(hn, sw["lm_head"])
+    lg = lm_head(hn, sw["lm_head"])
+    if "lm_head_b" in sw:                    # Phi's lm_head carries a bias: one fp32 add per logit
+        lg = (lg + np.asarray(sw["lm_head_b"], f32)[None, :]).astype(f32)
+    return lg
 
 
 def greedy_generate(stages, cfg, ids, max_new_tokens, max_seq, chunk=None):
     """Greedy decode through a list of stage-weight dicts (prefill, then one token a step).
     Returns (tokens [len(ids)+max_new_tokens], top-1 margins per generated token)."""
     hd = cfg["head_dim"]
-    cos, sin = rope_table(hd, max_seq, cfg.get("rope_theta", 10000.0), cfg.get("rope_scaling", ()))
+    cos, sin = rope_table(hd, max_seq, cfg.get("rope_theta", 10000.0), cfg.get("rope_scaling", ()), cfg.get("rotary_dim", 0))
     caches = [KVCacheOracle(len(s["layers"]), 1, cfg["n_kv_heads"], max_seq, hd) for s in stages]
     toks = list(int(t) for t in ids)
     margins = []

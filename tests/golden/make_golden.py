@@ -105,16 +105,58 @@ def hf_gpt2(cfg, seed):
     return m
 
 
+def hf_phi(cfg, seed):
+    """HF PhiForCausalLM -- the class `AutoModelForCausalLM.from_pretrained("microsoft/phi-2")` instantiates, the first
+    answerer of the reference's pipeline (combiner_quant_updated.py:177; config.yaml:13) -- with the synthetic weights
+    in the MODEL's head layout (80-wide heads, first 32 dims rotary); the stage path loads the same weights through
+    weights.to_kernel_layout."""
+    from transformers import PhiConfig, PhiForCausalLM
+    hm = cfg.hd_model
+    hc = PhiConfig(vocab_size=cfg.vocab, hidden_size=cfg.d_model, intermediate_size=cfg.ffn, num_hidden_layers=cfg.n_layers,
+                   num_attention_heads=cfg.n_heads, num_key_value_heads=cfg.n_kv_heads, hidden_act=cfg.act,
+                   max_position_embeddings=cfg.max_pos, layer_norm_eps=cfg.eps, tie_word_embeddings=False,
+                   resid_pdrop=0.0, embd_pdrop=0.0, attention_dropout=0.0,
+                   rope_parameters=dict(rope_type="default", rope_theta=cfg.rope_theta, partial_rotary_factor=cfg.rotary_dim / hm))
+    assert hc.hidden_size // hc.num_attention_heads == hm
+    m = PhiForCausalLM(hc).eval().float()
+    h16 = lambda t: t.to(torch.float16).to(torch.float32)
+    H, KV = cfg.n_heads, cfg.n_kv_heads
+    sd = {}
+    for li in range(cfg.n_layers):
+        w = weights.init_layer_fp32(cfg, li, seed, layout="model")
+        p = f"model.layers.{li}."
+        for name, lo, hi in (("q_proj", 0, H * hm), ("k_proj", H * hm, (H + KV) * hm), ("v_proj", (H + KV) * hm, (H + 2 * KV) * hm)):
+            sd[p + f"self_attn.{name}.weight"] = w["wqkv"][lo:hi]
+            sd[p + f"self_attn.{name}.bias"] = h16(w["b_qkv"][lo:hi])
+        sd[p + "self_attn.dense.weight"], sd[p + "self_attn.dense.bias"] = w["wo"], h16(w["b_o"])
+        sd[p + "mlp.fc1.weight"], sd[p + "mlp.fc1.bias"] = w["wgu"], h16(w["b_gu"])
+        sd[p + "mlp.fc2.weight"], sd[p + "mlp.fc2.bias"] = w["wd"], h16(w["b_d"])
+        sd[p + "input_layernorm.weight"], sd[p + "input_layernorm.bias"] = h16(w["ln1_g"]), h16(w["ln1_b"])
+    e = weights.init_embed_fp32(cfg, seed)
+    sd["model.embed_tokens.weight"] = h16(e["embed"])
+    sd["model.final_layernorm.weight"], sd["model.final_layernorm.bias"] = h16(e["lnf_g"]), h16(e["lnf_b"])
+    sd["lm_head.weight"], sd["lm_head.bias"] = h16(e["lm_head"]), e["lm_head_b"]
+    missing, unexpected = m.load_state_dict(sd, strict=False)
+    assert not unexpected and all("rotary" in k or "inv_freq" in k for k in missing), (missing, unexpected)
+    return m
+
+
+def hf_for(cfg, seed):
+    if cfg.parallel and cfg.shared_ln:
+        return hf_phi(cfg, seed)
+    return hf_model(cfg, seed) if cfg.rope else hf_gpt2(cfg, seed)
+
+
 def main():
     warnings.filterwarnings("ignore")
     torch.set_num_threads(4)
     only = sys.argv[1:]                       # optional: regenerate just the named cases
-    for name, seed, T, new in CASES + [("tiny-gpt2-test", 9, 20, 8)]:
+    for name, seed, T, new in CASES + [("tiny-gpt2-test", 9, 20, 8), ("tiny-phi-test", 13, 40, 8)]:
         if only and name not in only:
             continue
         cfg = b200stage.get_config(name)
         ids = np.random.default_rng(seed + 100).integers(0, cfg.vocab, T)
-        m = hf_gpt2(cfg, seed) if not cfg.rope else hf_model(cfg, seed)
+        m = hf_for(cfg, seed)
         tid = torch.from_numpy(ids)[None]
         with torch.no_grad():
             hf_logits = m(tid).logits[0].numpy()
@@ -123,7 +165,7 @@ def main():
             mq = torch.quantization.quantize_dynamic(m, {torch.nn.Linear}, dtype=torch.qint8)
             hf_dyn_logits = mq(tid).logits[0].numpy()
         sw = weights.to_numpy(weights.build_stage_weights(cfg, 0, cfg.n_layers, True, True, seed, "cpu"))
-        cos, sin = O.rope_table(cfg.head_dim, cfg.max_pos, cfg.rope_theta, cfg.rope_scaling)
+        cos, sin = O.rope_table(cfg.head_dim, cfg.max_pos, cfg.rope_theta, cfg.rope_scaling, cfg.rotary_dim)
         cache = O.KVCacheOracle(cfg.n_layers, 1, cfg.n_kv_heads, T + new, cfg.head_dim)
         s_logits = O.stage_forward(ids, sw, cfg.kernel_cfg(), cache, np.zeros(T, np.int64), np.arange(T), cos, sin)
         s_greedy, margins = O.greedy_generate([sw], cfg.kernel_cfg(), ids, new, T + new)

@@ -26,22 +26,25 @@ def _same(a: dict, b: dict):
         assert a[k].dtype == b[k].dtype and torch.equal(a[k], b[k]), k
 
 
-@pytest.mark.parametrize("model,safe", [("tiny-gqa-test", True), ("tiny-llama-test", False), ("tiny-gpt2-test", True)])
+@pytest.mark.parametrize("model,safe", [("tiny-gqa-test", True), ("tiny-llama-test", False), ("tiny-gpt2-test", True),
+                                        ("tiny-phi-test", True)])
 def test_layer_range_from_checkpoint_equals_direct_quantisation(tmp_path, model, safe):
     cfg0 = b200stage.get_config(model)
     seed = 3
-    m = make_golden.hf_model(cfg0, seed) if cfg0.rope else make_golden.hf_gpt2(cfg0, seed)
+    m = make_golden.hf_for(cfg0, seed)
     m.save_pretrained(tmp_path, safe_serialization=safe)
     cfg = b200stage.get_config(str(tmp_path))
     assert (cfg.n_layers, cfg.d_model, cfg.n_heads, cfg.n_kv_heads, cfg.head_dim, cfg.ffn, cfg.vocab) == \
            (cfg0.n_layers, cfg0.d_model, cfg0.n_heads, cfg0.n_kv_heads, cfg0.head_dim, cfg0.ffn, cfg0.vocab)
+    assert (cfg.parallel, cfg.shared_ln, cfg.rotary_dim, cfg.hd_model, cfg.head_bias, cfg.act, cfg.gated) == \
+           (cfg0.parallel, cfg0.shared_ln, cfg0.rotary_dim, cfg0.hd_model, cfg0.head_bias, cfg0.act, cfg0.gated)
     b, e = 1, cfg.n_layers
     got = loader.build_stage_weights_from_checkpoint(str(tmp_path), b, e, False, True, device="cpu")
     want = weights.build_stage_weights(cfg0, b, e, False, True, seed, "cpu")
     assert len(got["layers"]) == e - b
     for lg, lw in zip(got["layers"], want["layers"]):
         _same(lg, lw)
-    for k in ("lnf_g", "lnf_b", "lm_head"):
+    for k in ("lnf_g", "lnf_b", "lm_head", "lm_head_b"):
         if k in want:
             assert torch.equal(got[k], want[k]), k
     first = loader.build_stage_weights_from_checkpoint(str(tmp_path), 0, 1, True, False, device="cpu")

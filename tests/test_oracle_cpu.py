@@ -169,6 +169,64 @@ def test_oracle_against_golden(name):
     assert np.array_equal(toks, g["s_greedy"]) and np.array_equal(toks, g["hf_greedy"])
 
 
+def test_oracle_against_golden_phi():
+    """Phi (the reference's first answerer, combiner_quant_updated.py:177): HF PhiForCausalLM holds the weights in the
+    model's layout -- 80-wide heads, the first 32 dims rotary, one LayerNorm feeding attention and MLP in parallel,
+    biases everywhere, lm_head bias -- the oracle sees them after weights.to_kernel_layout (96-wide heads, rotary pairs
+    moved to (j, j + 48), identity rope entries elsewhere).  Agreement with HF therefore pins the layout transform, the
+    partial rope table, the 1/sqrt(80) scale and the parallel residual at once.  The model's lm_head is untied, so
+    logit margins are small: argmax is compared where HF's own top-1 margin exceeds the 2 % error budget."""
+    name = "tiny-phi-test"
+    g = np.load(os.path.join(GOLD, f"{name}.npz"))
+    cfg = b200stage.get_config(name)
+    seed, new, ids = int(g["seed"]), int(g["new"]), g["ids"]
+    T = len(ids)
+    sw = weights.to_numpy(weights.build_stage_weights(cfg, 0, cfg.n_layers, True, True, seed, "cpu"))
+    assert sw["layers"][0]["wqkv"].shape == (cfg.qkv_out, cfg.d_model) and cfg.head_dim == 96 and cfg.hd_model == 80
+    cos, sin = O.rope_table(cfg.head_dim, cfg.max_pos, cfg.rope_theta, cfg.rope_scaling, cfg.rotary_dim)
+    assert (cos[:, 16:] == 1).all() and (sin[:, 16:] == 0).all() and not (cos[5, :16] == 1).all()
+    cache = O.KVCacheOracle(cfg.n_layers, 1, cfg.n_kv_heads, T + new, cfg.head_dim)
+    logits = O.stage_forward(ids, sw, cfg.kernel_cfg(), cache, np.zeros(T, np.int64), np.arange(T), cos, sin)
+    assert np.abs(logits - g["s_logits"]).max() < 1e-3
+    hf = g["hf_logits"].astype(np.float64)
+    a, b = logits.ravel().astype(np.float64), hf.ravel()
+    assert a @ b / (np.linalg.norm(a) * np.linalg.norm(b)) >= 0.999
+    budget = 0.02 * np.abs(b).max()
+    assert np.abs(a - b).max() <= budget
+    top2 = np.sort(hf, axis=-1)[:, -2:]
+    clear = (top2[:, 1] - top2[:, 0]) > 2 * budget
+    assert clear.sum() >= 3 and np.array_equal(logits.argmax(-1)[clear], hf.argmax(-1)[clear])
+    c = g["hf_dyn_logits"].ravel().astype(np.float64)
+    assert np.linalg.norm(a - b) <= np.linalg.norm(c - b) * 1.05
+    toks, _ = O.greedy_generate([sw], cfg.kernel_cfg(), ids, new, T + new)
+    assert np.array_equal(toks, g["s_greedy"]) and np.array_equal(toks, g["hf_greedy"])
+
+
+def test_head_layout_transform_is_exact_on_qk_products():
+    """to_kernel_layout permutes q and k alike and pads with zeros: every head's q.k product and v are unchanged."""
+    import torch
+    cfg = b200stage.get_config("tiny-phi-test")
+    src = weights.head_slots(cfg)
+    assert sorted(src[src >= 0].tolist()) == list(range(80)) and (src < 0).sum() == 16
+    assert list(src[:16]) == list(range(16)) and list(src[48:64]) == list(range(16, 32))      # rotary pairs (j, j + 48)
+    wm = weights.init_layer_fp32(cfg, 0, 1, layout="model")
+    wk = weights.to_kernel_layout(cfg, wm)
+    x = torch.randn(5, cfg.d_model)
+    H = cfg.n_heads
+    qm = (x @ wm["wqkv"][: H * 80].t() + wm["b_qkv"][: H * 80]).view(5, H, 80)
+    km = (x @ wm["wqkv"][H * 80: 2 * H * 80].t() + wm["b_qkv"][H * 80: 2 * H * 80]).view(5, H, 80)
+    qk = (x @ wk["wqkv"][: H * 96].t() + wk["b_qkv"][: H * 96]).view(5, H, 96)
+    kk = (x @ wk["wqkv"][H * 96: 2 * H * 96].t() + wk["b_qkv"][H * 96: 2 * H * 96]).view(5, H, 96)
+    assert torch.allclose(torch.einsum("thd,shd->hts", qm, km), torch.einsum("thd,shd->hts", qk, kk), atol=1e-5)
+    a = torch.randn(5, H * 80)
+    ak = torch.zeros(5, H, 96)
+    ak[:, :, torch.from_numpy(np.nonzero(src >= 0)[0])] = a.view(5, H, 80)[:, :, torch.from_numpy(src[src >= 0])]
+    assert torch.allclose(a @ wm["wo"].t(), ak.reshape(5, -1) @ wk["wo"].t(), atol=1e-5)
+    llama = b200stage.get_config("tiny-gqa-test")
+    wl = weights.init_layer_fp32(llama, 0, 1, layout="model")
+    assert weights.to_kernel_layout(llama, wl) is wl                                          # identity for full-rotary heads
+
+
 def test_two_stage_split_equals_one_stage():
     from b200stage.pipeline import split_layers
     cfg = b200stage.get_config("tiny-llama-test")

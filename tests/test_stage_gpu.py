@@ -39,14 +39,14 @@ def _close(got, ref, name):
 
 
 @pytest.mark.parametrize("model", ["tiny-llama-test", "tiny-gqa-test", "tiny-window-test", "tiny-hd128-test", "tiny-gpt2-test",
-                                   "tiny-llama3-test"])
+                                   "tiny-llama3-test", "tiny-phi-test"])
 def test_stage_prefill_then_decode_matches_oracle(model):
     cfg = b200stage.get_config(model)
     seed, T, S = 3, 70, 96
     stage = Stage.load(cfg, 0, cfg.n_layers, first=True, last=True, device=DEV, seed=seed)
     osw = _oracle_stages(cfg, 1, seed)[0]
     ids = np.random.default_rng(5).integers(0, cfg.vocab, T)
-    cos, sin = O.rope_table(cfg.head_dim, cfg.max_pos, cfg.rope_theta, cfg.rope_scaling)
+    cos, sin = O.rope_table(cfg.head_dim, cfg.max_pos, cfg.rope_theta, cfg.rope_scaling, cfg.rotary_dim)
     ocache = O.KVCacheOracle(cfg.n_layers, 1, cfg.n_kv_heads, S, cfg.head_dim)
     otrace = []
     ref = O.stage_forward(ids, osw, cfg.kernel_cfg(), ocache, np.zeros(T, np.int64), np.arange(T), cos, sin, otrace)
@@ -102,7 +102,8 @@ def test_chunked_prefill_equals_one_shot():
     assert int(a.argmax()) == int(b.argmax())
 
 
-@pytest.mark.parametrize("model,n_stages", [("tiny-llama-test", 1), ("tiny-gqa-test", 2), ("tiny-window-test", 2), ("tiny-gpt2-test", 2)])
+@pytest.mark.parametrize("model,n_stages", [("tiny-llama-test", 1), ("tiny-gqa-test", 2), ("tiny-window-test", 2), ("tiny-gpt2-test", 2),
+                                            ("tiny-phi-test", 2)])
 def test_greedy_tokens_identical(model, n_stages):
     cfg = b200stage.get_config(model)
     seed, T, NEW = 7, 40, 32

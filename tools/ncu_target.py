@@ -1,5 +1,5 @@
 """Small fixed workload for `ncu`: a few launches of the dominant kernels at Llama-2-7B shapes.
-usage: python tools/ncu_target.py [gemm|gemv|gemv8|attn|pattn|all]"""
+usage: python tools/ncu_target.py [gemm|gemm2|gemv|gemv8|attn|pattn|all]"""
 import os
 import sys
 
@@ -40,6 +40,29 @@ if what in ("gemm", "all"):
     for sched in (10, 14):
         for lw in L:
             ops.gemm_w8a8(x8, lw["wgu"], st, lw["s_gu"], out=out, schedule=sched)
+if what == "gemm2":       # round 2: the CTA-pair (cta_group::2) kernel at T = 2048 -- gate_up plain, gate_up with the
+    T = 2048              # act*up epilogue (+ the fp32 quantise pass), qkv with the RoPE + KV-append epilogue, down
+    x8 = torch.randint(-127, 128, (T, max(d, F)), dtype=torch.int8, device=dev)
+    xd, xf = x8[:, :d].contiguous(), x8[:, :F].contiguous()
+    st = torch.full((T,), 0.01, device=dev)
+    out = torch.empty((T, 2 * F), dtype=torch.float16, device=dev)
+    y32 = torch.empty((T, F), dtype=torch.float32, device=dev)
+    am = torch.empty((T,), dtype=torch.float32, device=dev)
+    q8 = torch.empty((T, F), dtype=torch.int8, device=dev)
+    sc = torch.empty((T,), dtype=torch.float32, device=dev)
+    qkv = torch.empty((T, cfg.qkv_out), dtype=torch.float16, device=dev)
+    hres = torch.randn((T, d), dtype=torch.float16, device=dev)
+    hout = torch.empty((T, d), dtype=torch.float16, device=dev)
+    cos, sin = (x.to(dev) for x in weights.rope_table(hd, cfg.max_pos))
+    pos = torch.arange(T, dtype=torch.int32, device=dev)
+    kc = torch.zeros((2, 1, KV, T + 8, hd), dtype=torch.float16, device=dev)
+    vc = torch.zeros_like(kc)
+    for i, lw in enumerate(L[:2]):
+        ops.gemm_w8a8(xd, lw["wgu"], st, lw["s_gu"], out=out, schedule=20)
+        ops.gemm_gated_act(xd, lw["wgu"], st, lw["s_gu"], y32=y32, amax=am, out_smooth=lw["sm_d"])
+        ops.quant_f32(y32, am, out_q=q8, out_scale=sc)
+        ops.gemm_qkv_rope(xd, lw["wqkv"], st, lw["s_qkv"], qkv, cos, sin, pos, kc[i], vc[i], H, KV, hd)
+        ops.gemm_w8a8(xf, lw["wd"], st, lw["s_d"], None, hres, out=hout, schedule=20)
 if what in ("attn", "all"):
     S = 2100
     kc = torch.randn((NL, 1, KV, S + 8, hd), dtype=torch.float16, device=dev)
