@@ -62,7 +62,7 @@ int b2_norm(const void* x, const void* gamma, const void* beta, void* y, int T, 
 int b2_smooth_quant(const void* x, const float* smooth, int8_t* q, float* row_scale, int T, int K, void* stream);
 
 /* act(gate)*up -> smoothing -> per-token int8 (input of down_proj).  gate_up [T,2F] fp16, gate in
- * columns [0,F), up in [F,2F).  act: 0 silu*up, 1 gelu_new*up, 2 gelu_new (ungated, input [T,F]),
+ * columns [0,F), up in [F,2F).  act: 0 silu*up, 1 gelu_new*up, 2 gelu_new (ungated, input [T,F]), 4 exact-erf gelu (ungated; GPT-NeoX),
  * 3 silu (ungated).
  * Replaces: `act_fn(gate_proj(x)) * up_proj(x)` (modeling_llama.py:182-184) plus the activation
  * quantisation of `down_proj`. */
@@ -266,7 +266,7 @@ int b2_prefill_attn(const void* q, long long q_ld, const void* kcache, const voi
  *   b2_outlier_side(out, y, W, ...)       out += fp16(y[:,cols] . fp16(W[:,cols]*w_scale)^T); out += residual
  * Arithmetic pinned by oracle/w8a8.py llm_int8_linear. */
 
-/* act(gate)*up (act 0/1) or act(x) (act 2/3) as fp16 [T,F], not quantised (same act codes as b2_act_mul_quant). */
+/* act(gate)*up (act 0/1) or act(x) (act 2/3/4) as fp16 [T,F], not quantised (same act codes as b2_act_mul_quant). */
 int b2_act_mul(const void* gate_up, void* y, int T, int F, int act, void* stream);
 /* y [T,K] fp16 (row pitch ld): mask [K] fp32 = 0 for columns with any |y| >= threshold else 1; cols [K] int32 =
  * the outlier columns in ascending order; count [1] int32; flags = K/8 words of scratch.  All device memory. */

@@ -20,7 +20,7 @@ def __getattr__(name):   # lazy: stage/pipeline import torch
     if name == "Pipeline":
         from .pipeline import Pipeline
         return Pipeline
-    if name in ("weights", "ops", "stage", "pipeline", "rpc", "config", "loader"):     # b200stage.<submodule> without a prior import
+    if name in ("weights", "ops", "stage", "pipeline", "rpc", "config", "loader", "ensemble"):     # b200stage.<submodule> without a prior import
         import importlib
         return importlib.import_module(f"{__name__}.{name}")
     raise AttributeError(name)

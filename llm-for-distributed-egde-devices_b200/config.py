@@ -89,6 +89,8 @@ PRESETS = {
     "phi-2": ModelConfig("phi-2", 32, 2560, 32, 32, 96, 10240, 51200, eps=1e-5, max_pos=2048, act="gelu_new", gated=False,
                          norm="layernorm", bias=True, tie_embeddings=False, parallel=True, shared_ln=True, rotary_dim=32,
                          head_dim_model=80, head_bias=True),
+    "pythia-1b": ModelConfig("pythia-1b", 16, 2048, 8, 8, 256, 8192, 50304, eps=1e-5, max_pos=2048, act="gelu", gated=False,
+                             norm="layernorm", bias=True, tie_embeddings=False, parallel=True, rotary_dim=64),
     "mistral-7b": ModelConfig("mistral-7b", 32, 4096, 32, 8, 128, 14336, 32000, window=4096, max_pos=32768),
     # small shapes for tests (same structure, seconds on the CPU oracle)
     "tiny-llama-test": ModelConfig("tiny-llama-test", 4, 256, 4, 4, 64, 512, 512, max_pos=512),
@@ -100,6 +102,8 @@ PRESETS = {
     "tiny-phi-test": ModelConfig("tiny-phi-test", 3, 320, 4, 4, 96, 640, 512, eps=1e-5, max_pos=256, act="gelu_new", gated=False,
                                  norm="layernorm", bias=True, tie_embeddings=False, parallel=True, shared_ln=True,
                                  rotary_dim=32, head_dim_model=80, head_bias=True),
+    "tiny-neox-test": ModelConfig("tiny-neox-test", 3, 512, 2, 2, 256, 1024, 512, eps=1e-5, max_pos=256, act="gelu", gated=False,
+                                  norm="layernorm", bias=True, tie_embeddings=False, parallel=True, rotary_dim=64),
     "tiny-gpt2-test": ModelConfig("tiny-gpt2-test", 3, 256, 4, 4, 64, 1024, 512, eps=1e-5, max_pos=256, act="gelu_new",
                                   gated=False, norm="layernorm", rope=False, bias=True),
 }
@@ -129,6 +133,19 @@ def from_hf_dict(c: dict) -> ModelConfig:
         return ModelConfig(c.get("_name_or_path", "gpt2"), c["n_layer"], d, h, h, d // h, c.get("n_inner") or 4 * d,
                            c["vocab_size"], eps=c.get("layer_norm_epsilon", 1e-5), max_pos=c.get("n_positions", 1024),
                            act="gelu_new", gated=False, norm="layernorm", rope=False, bias=True)
+    if c.get("model_type") == "gpt_neox":
+        d, h = c["hidden_size"], c["num_attention_heads"]
+        hd = d // h
+        rp = c.get("rope_parameters") or {}
+        pct = rp.get("partial_rotary_factor", c.get("rotary_pct", 0.25))
+        if hd % 32 or not c.get("use_parallel_residual", True):
+            raise ValueError("gpt_neox: head_dim must be a multiple of 32 and use_parallel_residual true")
+        return ModelConfig(c.get("_name_or_path", "gpt_neox"), c["num_hidden_layers"], d, h, h, hd, c["intermediate_size"],
+                           c["vocab_size"], eps=c.get("layer_norm_eps", 1e-5),
+                           rope_theta=rp.get("rope_theta", c.get("rotary_emb_base", 10000.0)),
+                           max_pos=c.get("max_position_embeddings", 2048), act=c.get("hidden_act", "gelu"), gated=False,
+                           norm="layernorm", bias=bool(c.get("attention_bias", True)), tie_embeddings=bool(c.get("tie_word_embeddings", False)),
+                           parallel=True, rotary_dim=int(hd * pct))
     if c.get("model_type") == "phi":
         d, h = c["hidden_size"], c["num_attention_heads"]
         hd = c.get("head_dim") or d // h

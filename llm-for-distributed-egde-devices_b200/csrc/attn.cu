@@ -119,7 +119,14 @@ int rope_kv_append(void* qkv, long long ld, const float* cosT, const float* sinT
 // decode attention
 // =============================================================================================
 constexpr int DEC_TK = 64;        // keys per stage (16 per warp)
-constexpr int DEC_NST = 3;        // cp.async stages: 192 keys (K and V) in flight per CTA, two CTAs per SM
+// cp.async stages: 3 = 192 keys (K and V) in flight per CTA, two CTAs per SM; 2 for head_dim 256 (GPT-NeoX), whose
+// stages are twice as large and must leave room for the cluster landing zone
+template <int HD>
+constexpr int dec_nst() { return HD > 128 ? 2 : 3; }
+template <int HD>
+constexpr int dec_smem() { return dec_nst<HD>() * 2 * DEC_TK * (HD + 8) * 2; }
+template <int HD>
+constexpr int dec_smem_cl() { return dec_smem<HD>() + 8 * 8 * (HD + 2) * 4; }
 constexpr int DEC_THREADS = 128;
 
 struct DecParams {
@@ -168,6 +175,7 @@ B2_DEVINL void st_dsmem_f32(float* local_ptr, uint32_t rank, float v) {
 template <int HD, bool CL>
 __global__ void __launch_bounds__(DEC_THREADS, 2) decode_attn_kernel(const DecParams p) {
   constexpr int LDS = HD + 8;                       // padded row (halves): ldmatrix conflict-free
+  constexpr int DEC_NST = dec_nst<HD>();
   constexpr int TILE_HALVES = DEC_TK * LDS;
   extern __shared__ __align__(16) uint8_t smem_dec[];
   __half* sK = reinterpret_cast<__half*>(smem_dec);   // [NST][TK][LDS]
@@ -438,8 +446,8 @@ static int sm_count_attn() { return device_sm_count(); }
 
 template <int HD>
 static int launch_decode(const DecParams& p, int B, cudaStream_t st, bool cluster = false) {
-  constexpr int SMEM = DEC_NST * 2 * DEC_TK * (HD + 8) * 2;
-  constexpr int SMEM_CL_MAX = SMEM + 8 * 8 * (HD + 2) * 4;      // + landing zone: 8 splits x 8 heads of a group
+  constexpr int SMEM = dec_smem<HD>();
+  constexpr int SMEM_CL_MAX = dec_smem_cl<HD>();               // + landing zone: 8 splits x 8 heads of a group
   static DeviceOnce attr_once;
   if (!attr_once.get()) {
     if (cudaFuncSetAttribute(decode_attn_kernel<HD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM) != cudaSuccess ||
@@ -488,7 +496,7 @@ int decode_attn(const void* q, long long q_ld, const void* kcache, const void* v
   if (B == 0) return OK;
   if (!q || !kcache || !vcache || !seqlens || !out) return ERR_NULL_PTR;
   if (B < 0 || H <= 0 || KV <= 0 || H % KV || H / KV > 8 || (q_ld & 1) || max_seqlen <= 0) return ERR_BAD_SHAPE;
-  if (hd != 64 && hd != 96 && hd != 128) return ERR_UNSUPPORTED;
+  if (hd != 64 && hd != 96 && hd != 128 && hd != 256) return ERR_UNSUPPORTED;
   const int eff = (window > 0 && max_seqlen > window) ? window : max_seqlen;
   int splits = decode_attn_splits(B, KV, eff, sm_count_attn());
   // 2..8 splits: merged inside the kernel by a thread-block cluster over DSMEM (workspace unused).
@@ -507,7 +515,7 @@ int decode_attn(const void* q, long long q_ld, const void* kcache, const void* v
   p.H = H; p.KV = KV; p.Smax = Smax; p.splits = splits; p.window = window;
   p.scale_log2 = scale * 1.4426950408889634f;
   p.pf0 = (const uint8_t*)pf0; p.pf0_bytes = pf0_bytes; p.pf1 = (const uint8_t*)pf1; p.pf1_bytes = pf1_bytes;
-  return hd == 128 ? launch_decode<128>(p, B, st, use_cluster)
+  return hd == 128 ? launch_decode<128>(p, B, st, use_cluster) : hd == 256 ? launch_decode<256>(p, B, st, use_cluster)
        : hd == 96 ? launch_decode<96>(p, B, st, use_cluster) : launch_decode<64>(p, B, st, use_cluster);
 }
 
@@ -554,7 +562,7 @@ int decode_attn_static(const void* q, long long q_ld, const void* kcache, const 
   if (B == 0) return OK;
   if (!q || !kcache || !vcache || !seqlens || !out) return ERR_NULL_PTR;
   if (B < 0 || H <= 0 || KV <= 0 || H % KV || H / KV > 8 || (q_ld & 1) || max_seqlen <= 0) return ERR_BAD_SHAPE;
-  if (hd != 64 && hd != 96 && hd != 128) return ERR_UNSUPPORTED;
+  if (hd != 64 && hd != 96 && hd != 128 && hd != 256) return ERR_UNSUPPORTED;
   const int eff = (window > 0 && max_seqlen > window) ? window : max_seqlen;
   const int splits = decode_attn_splits(B, KV, eff, sm_count_attn());
   const size_t need = decode_attn_workspace_bytes(B, H, hd, splits);
@@ -572,13 +580,13 @@ int decode_attn_static(const void* q, long long q_ld, const void* kcache, const 
   p.H = H; p.KV = KV; p.Smax = Smax; p.splits = splits; p.window = window;
   p.scale_log2 = scale * 1.4426950408889634f;
   p.pf0 = nullptr; p.pf0_bytes = 0; p.pf1 = nullptr; p.pf1_bytes = 0;
-  return hd == 128 ? launch_decode<128>(p, B, st) : hd == 96 ? launch_decode<96>(p, B, st) : launch_decode<64>(p, B, st);
+  return hd == 128 ? launch_decode<128>(p, B, st) : hd == 256 ? launch_decode<256>(p, B, st)
+       : hd == 96 ? launch_decode<96>(p, B, st) : launch_decode<64>(p, B, st);
 }
 
 // =============================================================================================
 // prefill attention (one contiguous chunk of one sequence; causal, optional sliding window)
 // =============================================================================================
-constexpr int PF_BM = 128;    // query rows per CTA: 4 warps x 32 rows (two 16-row MMA blocks per warp)
 constexpr int PF_TK = 64;     // keys per stage
 constexpr int PF_THREADS = 128;
 
@@ -591,8 +599,12 @@ struct PfParams {
   float scale_log2;
 };
 
+// MB = 16-row MMA blocks per warp: 2 (128 query rows per CTA) for head_dim <= 128; 1 (64 rows) for head_dim 256
+// (GPT-NeoX / Pythia-1B), where two output accumulators of 256 columns would not fit the register file.
 template <int HD>
-constexpr int pf_smem_bytes() { return (PF_BM + 2 * 2 * PF_TK) * (HD + 8) * 2; }
+constexpr int pf_mb() { return HD > 128 ? 1 : 2; }
+template <int HD>
+constexpr int pf_smem_bytes() { return (64 * pf_mb<HD>() + 2 * 2 * PF_TK) * (HD + 8) * 2; }
 
 // FA2-style: every K (and V) fragment fetched with ldmatrix is used by both 16-row blocks of the
 // warp, the Q tile lives in shared memory and its fragments are re-read per key tile (keeping them
@@ -601,19 +613,21 @@ template <int HD>
 __global__ void __launch_bounds__(PF_THREADS) prefill_attn_kernel(const PfParams pin) {
   PfParams p = pin;
   if (p.pos_ptr) p.pos0 = p.pos_ptr[0];
+  constexpr int MB = pf_mb<HD>();
+  constexpr int BM = 64 * MB;          // query rows per CTA: 4 warps x MB blocks of 16
   constexpr int LDS = HD + 8;
   constexpr int TILE_HALVES = PF_TK * LDS;
   extern __shared__ __align__(16) uint8_t smem_pf[];
-  __half* sQ = reinterpret_cast<__half*>(smem_pf);     // [PF_BM][LDS]
-  __half* sK = sQ + PF_BM * LDS;                       // [2][TK][LDS]
+  __half* sQ = reinterpret_cast<__half*>(smem_pf);     // [BM][LDS]
+  __half* sK = sQ + BM * LDS;                       // [2][TK][LDS]
   __half* sV = sK + 2 * TILE_HALVES;                   // [2][TK][LDS]
   const int qt = gridDim.x - 1 - blockIdx.x;           // heavy (late) query tiles first
   const int h = blockIdx.y;
   const int kvh = h / (p.H / p.KV);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = lane >> 2, t4 = lane & 3;
-  const int q0 = qt * PF_BM;
-  const int last_q = min(q0 + PF_BM, p.T) - 1;
+  const int q0 = qt * BM;
+  const int last_q = min(q0 + BM, p.T) - 1;
   const int kend = p.pos0 + last_q + 1;                // exclusive
   int kfirst = 0;
   if (p.window > 0) { kfirst = p.pos0 + q0 - p.window + 1; kfirst = kfirst > 0 ? (kfirst / PF_TK) * PF_TK : 0; }
@@ -634,7 +648,7 @@ __global__ void __launch_bounds__(PF_THREADS) prefill_attn_kernel(const PfParams
     }
   };
   // Q tile (rows beyond T zero-filled) travels with the first K/V tile
-  for (int i = threadIdx.x; i < PF_BM * CPR; i += PF_THREADS) {
+  for (int i = threadIdx.x; i < BM * CPR; i += PF_THREADS) {
     const int r = i / CPR, c = i - r * CPR;
     const bool ok = (q0 + r) < p.T;
     cp_async16(smem_u32(sQ + r * LDS + c * 8), p.q + (long long)(ok ? q0 + r : q0) * p.q_ld + h * HD + c * 8, ok);
@@ -642,22 +656,22 @@ __global__ void __launch_bounds__(PF_THREADS) prefill_attn_kernel(const PfParams
   load_tile(0, 0);
   cp_async_commit();
 
-  float o[2][HD / 8][4];
+  float o[MB][HD / 8][4];
 #pragma unroll
-  for (int mb = 0; mb < 2; ++mb)
+  for (int mb = 0; mb < MB; ++mb)
 #pragma unroll
     for (int i = 0; i < HD / 8; ++i) { o[mb][i][0] = o[mb][i][1] = o[mb][i][2] = o[mb][i][3] = 0.f; }
-  float m_run[2][2], l_run[2][2];
+  float m_run[MB][2], l_run[MB][2];
 #pragma unroll
-  for (int mb = 0; mb < 2; ++mb) { m_run[mb][0] = m_run[mb][1] = -INFINITY; l_run[mb][0] = l_run[mb][1] = 0.f; }
+  for (int mb = 0; mb < MB; ++mb) { m_run[mb][0] = m_run[mb][1] = -INFINITY; l_run[mb][0] = l_run[mb][1] = 0.f; }
   // absolute positions of this thread's four query rows: [mb][0] = row g, [mb][1] = row g + 8
-  int qpos[2][2];
+  int qpos[MB][2];
 #pragma unroll
-  for (int mb = 0; mb < 2; ++mb) {
-    qpos[mb][0] = p.pos0 + q0 + warp * 32 + mb * 16 + g;
+  for (int mb = 0; mb < MB; ++mb) {
+    qpos[mb][0] = p.pos0 + q0 + warp * (16 * MB) + mb * 16 + g;
     qpos[mb][1] = qpos[mb][0] + 8;
   }
-  const __half* wQ = sQ + (warp * 32) * LDS;
+  const __half* wQ = sQ + (warp * 16 * MB) * LDS;
 
   for (int tile = 0; tile < ntiles; ++tile) {
     const int stage = tile & 1;
@@ -669,18 +683,18 @@ __global__ void __launch_bounds__(PF_THREADS) prefill_attn_kernel(const PfParams
     const __half* tV = sV + stage * TILE_HALVES;
     const int key0 = kfirst + tile * PF_TK;
     // warp-uniform skip: a key tile entirely above this warp's last query row contributes nothing
-    const bool live = key0 <= p.pos0 + q0 + warp * 32 + 31;
+    const bool live = key0 <= p.pos0 + q0 + warp * (16 * MB) + 16 * MB - 1;
     if (live) {
-      float s[2][PF_TK / 8][4];
+      float s[MB][PF_TK / 8][4];
 #pragma unroll
-      for (int mb = 0; mb < 2; ++mb)
+      for (int mb = 0; mb < MB; ++mb)
 #pragma unroll
         for (int nb = 0; nb < PF_TK / 8; ++nb) { s[mb][nb][0] = s[mb][nb][1] = s[mb][nb][2] = s[mb][nb][3] = 0.f; }
 #pragma unroll
       for (int kp = 0; kp < HD / 32; ++kp) {
-        uint32_t qa[2][2][4];            // [mb][k-block within the pair][regs]
+        uint32_t qa[MB][2][4];            // [mb][k-block within the pair][regs]
 #pragma unroll
-        for (int mb = 0; mb < 2; ++mb)
+        for (int mb = 0; mb < MB; ++mb)
 #pragma unroll
           for (int kb = 0; kb < 2; ++kb) {
             const int mat = lane >> 3;
@@ -695,15 +709,15 @@ __global__ void __launch_bounds__(PF_THREADS) prefill_attn_kernel(const PfParams
           const int c = kp * 32 + (lane >> 3) * 8;
           ldsm_x4(bf, smem_u32(tK + r * LDS + c));
 #pragma unroll
-          for (int mb = 0; mb < 2; ++mb) {
+          for (int mb = 0; mb < MB; ++mb) {
             mma16816(s[mb][nb], qa[mb][0], bf[0], bf[1]);
             mma16816(s[mb][nb], qa[mb][1], bf[2], bf[3]);
           }
         }
       }
-      uint32_t pf[2][PF_TK / 16][4];
+      uint32_t pf[MB][PF_TK / 16][4];
 #pragma unroll
-      for (int mb = 0; mb < 2; ++mb) {
+      for (int mb = 0; mb < MB; ++mb) {
         float mx0 = -INFINITY, mx1 = -INFINITY;
 #pragma unroll
         for (int nb = 0; nb < PF_TK / 8; ++nb) {
@@ -751,7 +765,7 @@ __global__ void __launch_bounds__(PF_THREADS) prefill_attn_kernel(const PfParams
           const int c = np * 16 + (mat >> 1) * 8;
           ldsm_x4_t(bf, smem_u32(tV + r * LDS + c));
 #pragma unroll
-          for (int mb = 0; mb < 2; ++mb) {
+          for (int mb = 0; mb < MB; ++mb) {
             mma16816(o[mb][2 * np], pf[mb][kk2], bf[0], bf[1]);
             mma16816(o[mb][2 * np + 1], pf[mb][kk2], bf[2], bf[3]);
           }
@@ -762,10 +776,10 @@ __global__ void __launch_bounds__(PF_THREADS) prefill_attn_kernel(const PfParams
   }
   cp_async_wait<0>();
 #pragma unroll
-  for (int mb = 0; mb < 2; ++mb) {
+  for (int mb = 0; mb < MB; ++mb) {
 #pragma unroll
     for (int hf = 0; hf < 2; ++hf) {
-      const int r = q0 + warp * 32 + mb * 16 + g + hf * 8;
+      const int r = q0 + warp * (16 * MB) + mb * 16 + g + hf * 8;
       if (r < p.T) {
         const float l = l_run[mb][hf];
         const float inv = l > 0.f ? 1.f / l : 0.f;
@@ -787,8 +801,17 @@ static int launch_prefill(const PfParams& p, cudaStream_t st) {
       return ERR_ARCH;
     attr_once.set();
   }
-  prefill_attn_kernel<HD><<<dim3((p.T + PF_BM - 1) / PF_BM, p.H), PF_THREADS, SMEM, st>>>(p);
+  constexpr int BM = 64 * pf_mb<HD>();
+  prefill_attn_kernel<HD><<<dim3((p.T + BM - 1) / BM, p.H), PF_THREADS, SMEM, st>>>(p);
   return launch_status();
+}
+
+template <int HD>
+static bool init_dec() {
+  cudaFuncAttributes fa;
+  return cudaFuncGetAttributes(&fa, decode_merge_kernel<HD>) == cudaSuccess &&
+         cudaFuncSetAttribute(decode_attn_kernel<HD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, dec_smem<HD>()) == cudaSuccess &&
+         cudaFuncSetAttribute(decode_attn_kernel<HD, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, dec_smem_cl<HD>()) == cudaSuccess;
 }
 
 int init_attn() {
@@ -801,14 +824,10 @@ int init_attn() {
     ok &= cudaFuncGetAttributes(&fa, decode_merge_kernel<96>) == cudaSuccess;
     if (!ok) return ERR_ARCH;
   }
-  if (cudaFuncSetAttribute(decode_attn_kernel<128, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_NST * 2 * DEC_TK * (128 + 8) * 2) != cudaSuccess) return ERR_ARCH;
-  if (cudaFuncSetAttribute(decode_attn_kernel<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_NST * 2 * DEC_TK * (128 + 8) * 2 + 8 * 8 * (128 + 2) * 4) != cudaSuccess) return ERR_ARCH;
-  if (cudaFuncSetAttribute(decode_attn_kernel<64, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_NST * 2 * DEC_TK * (64 + 8) * 2) != cudaSuccess) return ERR_ARCH;
-  if (cudaFuncSetAttribute(decode_attn_kernel<64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_NST * 2 * DEC_TK * (64 + 8) * 2 + 8 * 8 * (64 + 2) * 4) != cudaSuccess) return ERR_ARCH;
-  // head_dim 96: Phi-2's 80-wide heads padded to a multiple of 32 (weights.head_slots)
-  if (cudaFuncSetAttribute(decode_attn_kernel<96, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_NST * 2 * DEC_TK * (96 + 8) * 2) != cudaSuccess) return ERR_ARCH;
-  if (cudaFuncSetAttribute(decode_attn_kernel<96, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_NST * 2 * DEC_TK * (96 + 8) * 2 + 8 * 8 * (96 + 2) * 4) != cudaSuccess) return ERR_ARCH;
+  if (!init_dec<64>() || !init_dec<96>() || !init_dec<128>() || !init_dec<256>()) return ERR_ARCH;
+  // head_dim 96: Phi-2's 80-wide heads padded to a multiple of 32 (weights.head_slots); 256: GPT-NeoX / Pythia-1B
   if (cudaFuncSetAttribute(prefill_attn_kernel<96>, cudaFuncAttributeMaxDynamicSharedMemorySize, pf_smem_bytes<96>()) != cudaSuccess) return ERR_ARCH;
+  if (cudaFuncSetAttribute(prefill_attn_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, pf_smem_bytes<256>()) != cudaSuccess) return ERR_ARCH;
   if (cudaFuncSetAttribute(prefill_attn_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, pf_smem_bytes<128>()) != cudaSuccess) return ERR_ARCH;
   if (cudaFuncSetAttribute(prefill_attn_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, pf_smem_bytes<64>()) != cudaSuccess) return ERR_ARCH;
   return OK;
@@ -828,7 +847,7 @@ int prefill_attn(const void* q, long long q_ld, const void* kcache, const void* 
   if (T == 0) return OK;
   if (!q || !kcache || !vcache || !out) return ERR_NULL_PTR;
   if (T < 0 || (!positions && (pos0 < 0 || pos0 + T > Smax)) || H <= 0 || KV <= 0 || H % KV || (q_ld & 1) || (o_ld & 1)) return ERR_BAD_SHAPE;
-  if (hd != 64 && hd != 96 && hd != 128) return ERR_UNSUPPORTED;
+  if (hd != 64 && hd != 96 && hd != 128 && hd != 256) return ERR_UNSUPPORTED;
   const bool tc_ok = prefill_attn_tc_supported(T, hd, window, q_ld, q, kcache, vcache) && !(o_ld & 7) &&
                      !(reinterpret_cast<uintptr_t>(out) & 15);
   if (g_prefill_impl == 2 && !tc_ok) return ERR_UNSUPPORTED;
@@ -838,7 +857,8 @@ int prefill_attn(const void* q, long long q_ld, const void* kcache, const void* 
   p.q = (const __half*)q; p.q_ld = q_ld; p.k = (const __half*)kcache; p.v = (const __half*)vcache;
   p.out = (__half*)out; p.o_ld = o_ld; p.pos_ptr = positions; p.T = T; p.pos0 = pos0; p.row = row; p.H = H; p.KV = KV; p.Smax = Smax;
   p.window = window; p.scale_log2 = scale * 1.4426950408889634f;
-  return hd == 128 ? launch_prefill<128>(p, st) : hd == 96 ? launch_prefill<96>(p, st) : launch_prefill<64>(p, st);
+  return hd == 128 ? launch_prefill<128>(p, st) : hd == 256 ? launch_prefill<256>(p, st)
+       : hd == 96 ? launch_prefill<96>(p, st) : launch_prefill<64>(p, st);
 }
 
 }  // namespace b2

@@ -170,6 +170,23 @@ B2_DEVINL float gelu_new_det(float u) {
   return mul_rn(mul_rn(0.5f, u), add_rn(1.0f, th));
 }
 
+// exact-erf GELU (HF "gelu": GPT-NeoX / Pythia): erf by Abramowitz-Stegun 7.1.26 on exp_det (oracle: gelu_erf_det)
+B2_DEVINL float gelu_erf_det(float u) {
+  const float z = mul_rn(u, 0.7071067811865476f);
+  const float a = fabsf(z);
+  const float t = div_rn(1.0f, add_rn(1.0f, mul_rn(0.3275911f, a)));
+  float p = 1.061405429f;
+  p = add_rn(mul_rn(p, t), -1.453152027f);
+  p = add_rn(mul_rn(p, t), 1.421413741f);
+  p = add_rn(mul_rn(p, t), -0.284496736f);
+  p = add_rn(mul_rn(p, t), 0.254829592f);
+  p = mul_rn(p, t);
+  const float e = exp_det(-mul_rn(a, a));
+  float er = sub_rn(1.0f, mul_rn(p, e));
+  er = z < 0.0f ? -er : er;
+  return mul_rn(mul_rn(0.5f, u), add_rn(1.0f, er));
+}
+
 // q = clamp(rint(y*inv), -127, 127)
 B2_DEVINL int quant1(float y, float inv) {
   int q = __float2int_rn(mul_rn(y, inv));

@@ -12,7 +12,8 @@
 
 namespace b2 {
 
-enum RowMode : int { ROW_PLAIN = 0, ROW_RMS = 1, ROW_LN = 2, ROW_SILU_MUL = 3, ROW_GELU_MUL = 4, ROW_GELU = 5, ROW_SILU = 6 };
+enum RowMode : int { ROW_PLAIN = 0, ROW_RMS = 1, ROW_LN = 2, ROW_SILU_MUL = 3, ROW_GELU_MUL = 4, ROW_GELU = 5, ROW_SILU = 6,
+                     ROW_GELU_ERF = 7 };
 
 template <int NWARPS>
 B2_DEVINL double block_sum_d(double v, double* sh) {
@@ -79,6 +80,9 @@ __global__ void __launch_bounds__(NTHREADS) rowquant_kernel(
       } else if (MODE == ROW_SILU) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) v[c][j] = silu_det(v[c][j]);
+      } else if (MODE == ROW_GELU_ERF) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[c][j] = gelu_erf_det(v[c][j]);
       } else if (MODE == ROW_RMS || MODE == ROW_LN) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
@@ -232,7 +236,7 @@ int smooth_quant(const void* x, const float* smooth, int8_t* q, float* row_scale
                                            0.f, st);
 }
 
-// act: 0 = silu(gate)*up, 1 = gelu_new(gate)*up, 2 = gelu_new(x) (ungated), 3 = silu(x) (ungated)
+// act: 0 = silu(gate)*up, 1 = gelu_new(gate)*up, 2 = gelu_new(x) (ungated), 3 = silu(x) (ungated), 4 = exact-erf gelu(x) (ungated)
 int act_mul_quant(const void* gate_up, const float* smooth, int8_t* q, float* row_scale, int T, int F, int act,
                   cudaStream_t st) {
   if (T == 0) return OK;
@@ -244,6 +248,7 @@ int act_mul_quant(const void* gate_up, const float* smooth, int8_t* q, float* ro
     case 1: return launch_rowquant<ROW_GELU_MUL, false>(x, 2LL * F, nullptr, nullptr, smooth, q, row_scale, nullptr, T, F, 0.f, st);
     case 2: return launch_rowquant<ROW_GELU, false>(x, F, nullptr, nullptr, smooth, q, row_scale, nullptr, T, F, 0.f, st);
     case 3: return launch_rowquant<ROW_SILU, false>(x, F, nullptr, nullptr, smooth, q, row_scale, nullptr, T, F, 0.f, st);
+    case 4: return launch_rowquant<ROW_GELU_ERF, false>(x, F, nullptr, nullptr, smooth, q, row_scale, nullptr, T, F, 0.f, st);
     default: return ERR_UNSUPPORTED;
   }
 }
@@ -260,6 +265,7 @@ int act_mul_f16(const void* gate_up, void* y, int T, int F, int act, cudaStream_
     case 1: return launch_rowquant<ROW_GELU_MUL, true>(x, 2LL * F, nullptr, nullptr, nullptr, nullptr, nullptr, (__half*)y, T, F, 0.f, st);
     case 2: return launch_rowquant<ROW_GELU, true>(x, F, nullptr, nullptr, nullptr, nullptr, nullptr, (__half*)y, T, F, 0.f, st);
     case 3: return launch_rowquant<ROW_SILU, true>(x, F, nullptr, nullptr, nullptr, nullptr, nullptr, (__half*)y, T, F, 0.f, st);
+    case 4: return launch_rowquant<ROW_GELU_ERF, true>(x, F, nullptr, nullptr, nullptr, nullptr, nullptr, (__half*)y, T, F, 0.f, st);
     default: return ERR_UNSUPPORTED;
   }
 }
@@ -280,7 +286,7 @@ int init_rowquant() {
             touch_mode<ROW_SILU_MUL, false>() && touch_mode<ROW_GELU_MUL, false>() && touch_mode<ROW_GELU, false>() &&
             touch_mode<ROW_SILU, false>() && touch_mode<ROW_RMS, true>() && touch_mode<ROW_LN, true>() &&
             touch_mode<ROW_SILU_MUL, true>() && touch_mode<ROW_GELU_MUL, true>() && touch_mode<ROW_GELU, true>() &&
-            touch_mode<ROW_SILU, true>();
+            touch_mode<ROW_SILU, true>() && touch_mode<ROW_GELU_ERF, false>() && touch_mode<ROW_GELU_ERF, true>();
   return ok ? OK : ERR_ARCH;
 }
 

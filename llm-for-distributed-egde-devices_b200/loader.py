@@ -99,7 +99,9 @@ def _family(model_dir: str) -> str:
         return "llama"
     if mt == "phi":
         return "phi"
-    raise ValueError(f"model_type {mt!r}: no tensor-name map for this family (llama, mistral, phi and gpt2 are supported)")
+    if mt == "gpt_neox":
+        return "neox"
+    raise ValueError(f"model_type {mt!r}: no tensor-name map for this family (llama, mistral, phi, gpt_neox and gpt2 are supported)")
 
 
 # --------------------------------------------------------------------------------------------------
@@ -124,6 +126,20 @@ def load_layer_fp32(src: TensorSource, cfg: ModelConfig, layer: int, family: str
                  wo=g("self_attn.dense.weight"), b_o=g("self_attn.dense.bias"),
                  wgu=g("mlp.fc1.weight"), b_gu=g("mlp.fc1.bias"), wd=g("mlp.fc2.weight"), b_d=g("mlp.fc2.bias"))
         w["ln2_g"], w["ln2_b"] = w["ln1_g"].clone(), w["ln1_b"].clone()
+        w = weights.to_kernel_layout(cfg, w)
+    elif family == "neox":       # GPT-NeoX / Pythia: query_key_value is stored head by head as [q_h | k_h | v_h]
+        p = f"gpt_neox.layers.{layer}."
+        g = lambda n: src.get(p + n, p.replace("gpt_neox.", "", 1) + n)
+        H, hm = cfg.n_heads, cfg.hd_model
+        qkv = g("attention.query_key_value.weight").view(H, 3, hm, cfg.d_model)
+        bqkv = g("attention.query_key_value.bias").view(H, 3, hm)
+        w = dict(ln1_g=g("input_layernorm.weight"), ln1_b=g("input_layernorm.bias"),
+                 ln2_g=g("post_attention_layernorm.weight"), ln2_b=g("post_attention_layernorm.bias"),
+                 wqkv=torch.cat([qkv[:, i].reshape(H * hm, cfg.d_model) for i in range(3)], 0).contiguous(),
+                 b_qkv=torch.cat([bqkv[:, i].reshape(H * hm) for i in range(3)], 0).contiguous(),
+                 wo=g("attention.dense.weight"), b_o=g("attention.dense.bias"),
+                 wgu=g("mlp.dense_h_to_4h.weight"), b_gu=g("mlp.dense_h_to_4h.bias"),
+                 wd=g("mlp.dense_4h_to_h.weight"), b_d=g("mlp.dense_4h_to_h.bias"))
         w = weights.to_kernel_layout(cfg, w)
     else:   # GPT-2: Conv1D weights are [in, out]
         p = f"transformer.h.{layer}."
@@ -150,6 +166,14 @@ def load_embed_fp32(src: TensorSource, cfg: ModelConfig, family: str, first: boo
         if last:
             out["lnf_g"] = src.get("model.norm.weight", "norm.weight")
             out["lm_head"] = src.get("lm_head.weight") if src.has("lm_head.weight") else src.get(*emb)
+    elif family == "neox":
+        emb = ("gpt_neox.embed_in.weight", "embed_in.weight")
+        if first:
+            out["embed"] = src.get(*emb)
+        if last:
+            out["lnf_g"] = src.get("gpt_neox.final_layer_norm.weight", "final_layer_norm.weight")
+            out["lnf_b"] = src.get("gpt_neox.final_layer_norm.bias", "final_layer_norm.bias")
+            out["lm_head"] = src.get("embed_out.weight") if src.has("embed_out.weight") else src.get(*emb)
     elif family == "phi":
         if first:
             out["embed"] = src.get("model.embed_tokens.weight", "embed_tokens.weight")
@@ -245,7 +269,8 @@ def _layer_fp32(cfg: ModelConfig, w: dict, h, cos, sin, stats: dict):
     gu = x @ w["wgu"].t()
     if "b_gu" in w:
         gu = gu + w["b_gu"]
-    act = torch.nn.functional.silu if cfg.act == "silu" else (lambda t: torch.nn.functional.gelu(t, approximate="tanh"))
+    act = {"silu": torch.nn.functional.silu, "gelu": torch.nn.functional.gelu,
+           "gelu_new": lambda t: torch.nn.functional.gelu(t, approximate="tanh")}[cfg.act]
     y = act(gu[:, :F]) * gu[:, F:] if cfg.gated else act(gu)
     seen("d", y)
     return h1 + y @ w["wd"].t() + (w["b_d"] if "b_d" in w else 0)

@@ -12,7 +12,7 @@ import torch
 from . import _abi
 from ._abi import check, ptr, stream_handle
 
-ACT_SILU_MUL, ACT_GELU_MUL, ACT_GELU, ACT_SILU = 0, 1, 2, 3
+ACT_SILU_MUL, ACT_GELU_MUL, ACT_GELU, ACT_SILU, ACT_GELU_ERF = 0, 1, 2, 3, 4
 
 
 def _cuda(*ts):

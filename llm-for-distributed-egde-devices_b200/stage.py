@@ -235,7 +235,7 @@ class Stage:
         qkv, attn, gu = buf.qkv[:T], buf.attn[:T], buf.gu[:T]
         sc = buf.scale[:T]
         act = (ops.ACT_SILU_MUL if cfg.act == "silu" else ops.ACT_GELU_MUL) if cfg.gated else \
-              (ops.ACT_GELU if cfg.act == "gelu_new" else ops.ACT_SILU)
+              {"gelu_new": ops.ACT_GELU, "silu": ops.ACT_SILU, "gelu": ops.ACT_GELU_ERF}[cfg.act]
         fused = self.fuse_decode and decode and T <= 8 and trace is None
         xk_norm = ops.X_LN if cfg.norm == "layernorm" else ops.X_RMS
         layers = self.w["layers"]
@@ -620,7 +620,8 @@ class GraphRunner:
         gc_was_on = gc.isenabled()
         gc.disable()
         try:
-            with torch.cuda.device(dev), torch.cuda.graph(g):
+            # thread_local: another host thread may be driving another pipeline (ensemble.py) and allocate meanwhile
+            with torch.cuda.device(dev), torch.cuda.graph(g, capture_error_mode="thread_local"):
                 self.n_launch = self._run_core()
         finally:
             if gc_was_on:

@@ -93,6 +93,28 @@ def gelu_new_det(u: np.ndarray) -> np.ndarray:
     return ((f32(0.5) * u).astype(f32) * (f32(1.0) + th).astype(f32)).astype(f32)
 
 
+def gelu_erf_det(u: np.ndarray) -> np.ndarray:
+    """Exact GELU 0.5*u*(1+erf(u/sqrt 2)) (HF "gelu": GPT-NeoX / Pythia, modeling_gpt_neox.py:43) with erf from
+    Abramowitz-Stegun 7.1.26 -- erf(a) = 1 - (a1 t + ... + a5 t^5) exp(-a^2), t = 1/(1 + p a), |error| <= 1.5e-7,
+    i.e. at the resolution of fp32 -- on exp_det, every step individually rounded (kernel: gelu_erf_det)."""
+    u = np.asarray(u, dtype=f32)
+    z = (u * f32(0.7071067811865476)).astype(f32)
+    a = np.abs(z).astype(f32)
+    t = (f32(1.0) / (f32(1.0) + (f32(0.3275911) * a).astype(f32)).astype(f32)).astype(f32)
+    p = f32(1.061405429)
+    for c in (-1.453152027, 1.421413741, -0.284496736, 0.254829592):
+        p = ((p * t).astype(f32) + f32(c)).astype(f32)
+    p = (p * t).astype(f32)
+    e = exp_det((-(a * a).astype(f32)).astype(f32))
+    er = (f32(1.0) - (p * e).astype(f32)).astype(f32)
+    er = np.where(z < 0, -er, er).astype(f32)
+    return ((f32(0.5) * u).astype(f32) * (f32(1.0) + er).astype(f32)).astype(f32)
+
+
+def act_fn(name: str):
+    return {"silu": silu_det, "gelu_new": gelu_new_det, "gelu": gelu_erf_det}[name]
+
+
 # ----------------------------------------------------------------------------------------
 # quantisation
 # ----------------------------------------------------------------------------------------
@@ -160,7 +182,7 @@ def act_mul_y(gate_up16, smooth, act="silu"):
     gu = np.asarray(gate_up16, dtype=f16).astype(f32)
     F = gu.shape[1] // 2
     g, u = gu[:, :F], gu[:, F:]
-    a = silu_det(g) if act == "silu" else gelu_new_det(g)
+    a = act_fn(act)(g)
     y = (a * u).astype(f32)
     if smooth is not None:
         y = (y * np.asarray(smooth, dtype=f32)[None, :]).astype(f32)
@@ -179,7 +201,7 @@ def act_mul_quant(gate_up16, smooth, act="silu"):
 def act_quant(h16, smooth, act="gelu_new"):
     """act(h) -> smoothing -> per-token int8, for non-gated MLPs (GPT-2)."""
     h = np.asarray(h16, dtype=f16).astype(f32)
-    y = gelu_new_det(h) if act == "gelu_new" else silu_det(h)
+    y = act_fn(act)(h)
     if smooth is not None:
         y = (y * np.asarray(smooth, dtype=f32)[None, :]).astype(f32)
     return quant_rows(y)
@@ -460,7 +482,7 @@ def block_forward_llm_int8(h16, lw, cfg, cache: KVCacheOracle, li, seq_ids, posi
         hm = act_mul_y(gu, None, cfg.get("act", "silu"))[0].astype(f16)
     else:
         g = np.asarray(gu, f16).astype(f32)
-        hm = (gelu_new_det(g) if cfg.get("act", "gelu_new") == "gelu_new" else silu_det(g)).astype(f16)
+        hm = act_fn(cfg.get("act", "gelu_new"))(g).astype(f16)
     h2, _, c4 = llm_int8_linear(hm, lw["wd"], lw["s_d"], lw.get("b_d"), h1)
     if trace is not None:
         trace.append(dict(y1=y1, qkv=qkv, attn=attn.reshape(h16.shape[0], cfg["n_heads"], cfg["head_dim"]), h1=h1, y2=y2,

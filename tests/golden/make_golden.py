@@ -141,9 +141,47 @@ def hf_phi(cfg, seed):
     return m
 
 
+def hf_neox(cfg, seed):
+    """HF GPTNeoXForCausalLM -- what `from_pretrained("EleutherAI/pythia-1b")` instantiates, the second answerer of the
+    reference's pipeline (combiner_quant_updated.py:178; config.yaml:14): parallel residual with two LayerNorms, 25 %
+    rotary, exact GELU, one fused query_key_value matrix stored head by head as [q_h | k_h | v_h]."""
+    from transformers import GPTNeoXConfig, GPTNeoXForCausalLM
+    hm, H = cfg.hd_model, cfg.n_heads
+    hc = GPTNeoXConfig(vocab_size=cfg.vocab, hidden_size=cfg.d_model, intermediate_size=cfg.ffn, num_hidden_layers=cfg.n_layers,
+                       num_attention_heads=H, hidden_act=cfg.act, max_position_embeddings=cfg.max_pos, layer_norm_eps=cfg.eps,
+                       tie_word_embeddings=False, use_parallel_residual=True, attention_bias=True, hidden_dropout=0.0,
+                       attention_dropout=0.0,
+                       rope_parameters=dict(rope_type="default", rope_theta=cfg.rope_theta, partial_rotary_factor=cfg.rotary_dim / hm))
+    m = GPTNeoXForCausalLM(hc).eval().float()
+    h16 = lambda t: t.to(torch.float16).to(torch.float32)
+    sd = {}
+    for li in range(cfg.n_layers):
+        w = weights.init_layer_fp32(cfg, li, seed, layout="model")
+        p = f"gpt_neox.layers.{li}."
+        q, k, v = (w["wqkv"][i * H * hm:(i + 1) * H * hm].view(H, hm, -1) for i in range(3))
+        bq, bk, bv = (w["b_qkv"][i * H * hm:(i + 1) * H * hm].view(H, hm) for i in range(3))
+        sd[p + "attention.query_key_value.weight"] = torch.cat([q, k, v], 1).reshape(3 * H * hm, -1).contiguous()
+        sd[p + "attention.query_key_value.bias"] = h16(torch.cat([bq, bk, bv], 1).reshape(-1))
+        sd[p + "attention.dense.weight"], sd[p + "attention.dense.bias"] = w["wo"], h16(w["b_o"])
+        sd[p + "mlp.dense_h_to_4h.weight"], sd[p + "mlp.dense_h_to_4h.bias"] = w["wgu"], h16(w["b_gu"])
+        sd[p + "mlp.dense_4h_to_h.weight"], sd[p + "mlp.dense_4h_to_h.bias"] = w["wd"], h16(w["b_d"])
+        sd[p + "input_layernorm.weight"], sd[p + "input_layernorm.bias"] = h16(w["ln1_g"]), h16(w["ln1_b"])
+        sd[p + "post_attention_layernorm.weight"], sd[p + "post_attention_layernorm.bias"] = h16(w["ln2_g"]), h16(w["ln2_b"])
+    e = weights.init_embed_fp32(cfg, seed)
+    sd["gpt_neox.embed_in.weight"] = h16(e["embed"])
+    sd["gpt_neox.final_layer_norm.weight"], sd["gpt_neox.final_layer_norm.bias"] = h16(e["lnf_g"]), h16(e["lnf_b"])
+    sd["embed_out.weight"] = h16(e["lm_head"])
+    missing, unexpected = m.load_state_dict(sd, strict=False)
+    assert not unexpected and all("rotary" in k or "inv_freq" in k or "bias" in k.split(".")[-1] and "attention.bias" in k
+                                  or "masked_bias" in k for k in missing), (missing, unexpected)
+    return m
+
+
 def hf_for(cfg, seed):
     if cfg.parallel and cfg.shared_ln:
         return hf_phi(cfg, seed)
+    if cfg.parallel:
+        return hf_neox(cfg, seed)
     return hf_model(cfg, seed) if cfg.rope else hf_gpt2(cfg, seed)
 
 
@@ -151,7 +189,7 @@ def main():
     warnings.filterwarnings("ignore")
     torch.set_num_threads(4)
     only = sys.argv[1:]                       # optional: regenerate just the named cases
-    for name, seed, T, new in CASES + [("tiny-gpt2-test", 9, 20, 8), ("tiny-phi-test", 13, 40, 8)]:
+    for name, seed, T, new in CASES + [("tiny-gpt2-test", 9, 20, 8), ("tiny-phi-test", 13, 40, 8), ("tiny-neox-test", 17, 40, 8)]:
         if only and name not in only:
             continue
         cfg = b200stage.get_config(name)

@@ -119,7 +119,7 @@ def test_fused_rejects_large_m():
         ops.fused_linear(x, w, torch.ones(16, device=DEV), x_kind=ops.X_PLAIN, out=torch.empty((9, 16), dtype=torch.float16, device=DEV))
 
 
-@pytest.mark.parametrize("model", ["tiny-llama-test", "tiny-gqa-test", "tiny-gpt2-test", "tiny-phi-test"])
+@pytest.mark.parametrize("model", ["tiny-llama-test", "tiny-gqa-test", "tiny-gpt2-test", "tiny-phi-test", "tiny-neox-test"])
 def test_fused_decode_equals_unfused_decode(model):
     """Whole-stage check: greedy decode with the fused kernels == with the unfused chain, bit for
     bit (logits of every step), with and without CUDA graphs, single and batched decode."""

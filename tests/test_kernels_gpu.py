@@ -87,6 +87,17 @@ def test_act_mul_quant_exact(T, F):
     assert np.array_equal(n(s), s_ref) and np.array_equal(n(q), q_ref)
 
 
+def test_act_gelu_erf_quant_exact():
+    """exact-erf GELU (GPT-NeoX / Pythia `hidden_act = "gelu"`), ungated, with smoothing."""
+    r = rng(6)
+    h = (r.standard_normal((9, 8192)) * 3).astype(np.float16)
+    h[0, :6] = [0, -0.0, 9, -9, 0.5, -0.5]
+    sm = r.uniform(0.2, 5.0, 8192).astype(np.float32)
+    q, s = ops.act_mul_quant(t(h), t(sm), ops.ACT_GELU_ERF)
+    q_ref, s_ref = O.act_quant(h, sm, "gelu")
+    assert np.array_equal(n(s), s_ref) and np.array_equal(n(q), q_ref)
+
+
 def test_act_gelu_quant_exact():
     r = rng(5)
     h = (r.standard_normal((9, 3072)) * 3).astype(np.float16)
@@ -216,7 +227,7 @@ def _attn_tol(got, ref):
 @pytest.mark.parametrize("H,KV,hd,B,S,window", [
     (4, 4, 64, 2, 70, 0), (8, 2, 64, 3, 300, 0), (32, 32, 128, 1, 1500, 0), (32, 8, 128, 2, 2100, 0),
     (32, 4, 64, 1, 513, 0), (8, 2, 128, 2, 700, 256), (4, 4, 64, 1, 1, 0), (40, 40, 128, 4, 33, 0),
-    (32, 8, 128, 1, 161, 96), (32, 8, 128, 1, 8000, 4096), (32, 32, 96, 2, 1300, 0), (4, 4, 96, 1, 70, 0)])
+    (32, 8, 128, 1, 161, 96), (32, 8, 128, 1, 8000, 4096), (32, 32, 96, 2, 1300, 0), (4, 4, 96, 1, 70, 0), (8, 8, 256, 2, 1100, 0), (2, 2, 256, 1, 40, 0)])
 def test_decode_attn(H, KV, hd, B, S, window):
     r = rng(H * 3 + S)
     Smax = S + 8
@@ -241,7 +252,7 @@ def test_decode_attn(H, KV, hd, B, S, window):
 @pytest.mark.parametrize("H,KV,hd,T,pos0,window", [
     (4, 4, 64, 64, 0, 0), (4, 2, 64, 100, 0, 0), (8, 8, 128, 130, 0, 0), (4, 4, 64, 50, 77, 0),
     (8, 2, 128, 200, 56, 0), (4, 2, 64, 150, 30, 48), (2, 2, 64, 1, 0, 0), (2, 1, 128, 9, 300, 100), (4, 4, 96, 200, 17, 0),
-    (32, 32, 96, 300, 0, 0)])
+    (32, 32, 96, 300, 0, 0), (8, 8, 256, 200, 33, 0), (2, 2, 256, 70, 0, 0)])
 def test_prefill_attn(H, KV, hd, T, pos0, window):
     r = rng(H + T + pos0)
     S = pos0 + T

@@ -27,7 +27,7 @@ def _same(a: dict, b: dict):
 
 
 @pytest.mark.parametrize("model,safe", [("tiny-gqa-test", True), ("tiny-llama-test", False), ("tiny-gpt2-test", True),
-                                        ("tiny-phi-test", True)])
+                                        ("tiny-phi-test", True), ("tiny-neox-test", True)])
 def test_layer_range_from_checkpoint_equals_direct_quantisation(tmp_path, model, safe):
     cfg0 = b200stage.get_config(model)
     seed = 3

@@ -57,3 +57,38 @@ def test_single_process_pipeline_on_two_devices():
         two.use_graphs = graphs
         got = two.generate(ids, max_new_tokens=16, chunk=32).cpu().numpy()
         assert np.array_equal(got, one), (graphs, got[-16:], one[-16:])
+
+
+class _Tok:
+    """Stand-in tokenizer for the ensemble test: text <-> ids as space-separated numbers (no tokenizer files offline)."""
+    eos_token_id = None
+
+    def __init__(self, vocab):
+        self.vocab = vocab
+
+    def encode(self, text):
+        return [(sum(w.encode()) * 31 + i) % self.vocab for i, w in enumerate(text.split())][:48] or [1]
+
+    def decode(self, ids):
+        return " ".join(str(int(i)) for i in ids)
+
+
+@needs2
+def test_ensemble_answerers_run_concurrently_on_two_gpus():
+    """The reference's three-model pipeline (combiner_quant_updated.py:177-203) on the stage path: the Phi-shaped and the
+    NeoX-shaped answerer on two GPUs from two host threads, then the Llama-shaped refiner.  Concurrent == sequential,
+    token for token (sampling draws are counter-based, so the result does not depend on timing)."""
+    import b200stage
+    from b200stage.pipeline import Pipeline
+    from b200stage.ensemble import Ensemble
+    a = Pipeline.load("tiny-phi-test", 1, devices=["cuda:0"], seed=1)
+    b = Pipeline.load("tiny-neox-test", 1, devices=["cuda:1"], seed=2)
+    r = Pipeline.load("tiny-llama3-test", 1, devices=["cuda:0"], seed=3)
+    ens = Ensemble([(a, _Tok(a.cfg.vocab)), (b, _Tok(b.cfg.vocab))], (r, _Tok(r.cfg.vocab)))
+    q = "who wrote the declaration of independence and when was it signed"
+    one = ens(q, reference="thomas jefferson 1776", max_new_tokens=24, temperature=0.7, top_k=50, top_p=0.9,
+              repetition_penalty=1.1, seed=5, concurrent=False)
+    two = ens(q, reference="thomas jefferson 1776", max_new_tokens=24, temperature=0.7, top_k=50, top_p=0.9,
+              repetition_penalty=1.1, seed=5, concurrent=True)
+    assert one["answers"] == two["answers"] and one["refined"] == two["refined"]
+    assert len(two["answers"]) == 2 and two["tps"] > 0 and len(two["refined"].split()) > 24

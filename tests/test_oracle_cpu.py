@@ -169,22 +169,25 @@ def test_oracle_against_golden(name):
     assert np.array_equal(toks, g["s_greedy"]) and np.array_equal(toks, g["hf_greedy"])
 
 
-def test_oracle_against_golden_phi():
+@pytest.mark.parametrize("name", ["tiny-phi-test", "tiny-neox-test"])
+def test_oracle_against_golden_parallel_families(name):
     """Phi (the reference's first answerer, combiner_quant_updated.py:177): HF PhiForCausalLM holds the weights in the
     model's layout -- 80-wide heads, the first 32 dims rotary, one LayerNorm feeding attention and MLP in parallel,
     biases everywhere, lm_head bias -- the oracle sees them after weights.to_kernel_layout (96-wide heads, rotary pairs
     moved to (j, j + 48), identity rope entries elsewhere).  Agreement with HF therefore pins the layout transform, the
-    partial rope table, the 1/sqrt(80) scale and the parallel residual at once.  The model's lm_head is untied, so
-    logit margins are small: argmax is compared where HF's own top-1 margin exceeds the 2 % error budget."""
-    name = "tiny-phi-test"
+    partial rope table, the 1/sqrt(80) scale and the parallel residual at once.
+    GPT-NeoX / Pythia (the second answerer, :178): 256-wide heads with 64 rotary dims (permuted, not padded), two
+    LayerNorms feeding the parallel branches, exact-erf GELU, HF's head-interleaved query_key_value layout."""
     g = np.load(os.path.join(GOLD, f"{name}.npz"))
     cfg = b200stage.get_config(name)
     seed, new, ids = int(g["seed"]), int(g["new"]), g["ids"]
     T = len(ids)
     sw = weights.to_numpy(weights.build_stage_weights(cfg, 0, cfg.n_layers, True, True, seed, "cpu"))
-    assert sw["layers"][0]["wqkv"].shape == (cfg.qkv_out, cfg.d_model) and cfg.head_dim == 96 and cfg.hd_model == 80
+    assert sw["layers"][0]["wqkv"].shape == (cfg.qkv_out, cfg.d_model)
+    assert (cfg.head_dim, cfg.hd_model) == ((96, 80) if name == "tiny-phi-test" else (256, 256))
     cos, sin = O.rope_table(cfg.head_dim, cfg.max_pos, cfg.rope_theta, cfg.rope_scaling, cfg.rotary_dim)
-    assert (cos[:, 16:] == 1).all() and (sin[:, 16:] == 0).all() and not (cos[5, :16] == 1).all()
+    r2 = cfg.rotary_dim // 2
+    assert (cos[:, r2:] == 1).all() and (sin[:, r2:] == 0).all() and not (cos[5, :r2] == 1).all()
     cache = O.KVCacheOracle(cfg.n_layers, 1, cfg.n_kv_heads, T + new, cfg.head_dim)
     logits = O.stage_forward(ids, sw, cfg.kernel_cfg(), cache, np.zeros(T, np.int64), np.arange(T), cos, sin)
     assert np.abs(logits - g["s_logits"]).max() < 1e-3

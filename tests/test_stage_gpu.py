@@ -39,7 +39,7 @@ def _close(got, ref, name):
 
 
 @pytest.mark.parametrize("model", ["tiny-llama-test", "tiny-gqa-test", "tiny-window-test", "tiny-hd128-test", "tiny-gpt2-test",
-                                   "tiny-llama3-test", "tiny-phi-test"])
+                                   "tiny-llama3-test", "tiny-phi-test", "tiny-neox-test"])
 def test_stage_prefill_then_decode_matches_oracle(model):
     cfg = b200stage.get_config(model)
     seed, T, S = 3, 70, 96
@@ -103,7 +103,7 @@ def test_chunked_prefill_equals_one_shot():
 
 
 @pytest.mark.parametrize("model,n_stages", [("tiny-llama-test", 1), ("tiny-gqa-test", 2), ("tiny-window-test", 2), ("tiny-gpt2-test", 2),
-                                            ("tiny-phi-test", 2)])
+                                            ("tiny-phi-test", 2), ("tiny-neox-test", 1)])
 def test_greedy_tokens_identical(model, n_stages):
     cfg = b200stage.get_config(model)
     seed, T, NEW = 7, 40, 32
@@ -190,3 +190,27 @@ def test_pipeline_from_a_checkpoint_directory(tmp_path):
     make_golden.hf_model(cfg, seed).config.save_pretrained(empty)
     with pytest.raises(FileNotFoundError):
         Stage.load(str(empty), 0, 1, first=True, last=False, device=DEV)
+
+
+def test_ensemble_on_one_gpu():
+    """answerer, answerer -> refiner (combiner_quant_updated.py:177-203) with the three pipelines on one GPU: the
+    answerers then run one after the other, as in the reference; the result is reproducible under a seed."""
+    from b200stage.ensemble import Ensemble
+
+    class Tok:
+        eos_token_id = None
+
+        def __init__(self, vocab):
+            self.vocab = vocab
+
+        def encode(self, text):
+            return [(sum(w.encode()) * 31 + i) % self.vocab for i, w in enumerate(text.split())][:48] or [1]
+
+        def decode(self, ids):
+            return " ".join(str(int(i)) for i in ids)
+    pipes = [Pipeline.load(m, 1, seed=i + 1) for i, m in enumerate(("tiny-phi-test", "tiny-neox-test", "tiny-llama3-test"))]
+    ens = Ensemble([(pipes[0], Tok(pipes[0].cfg.vocab)), (pipes[1], Tok(pipes[1].cfg.vocab))], (pipes[2], Tok(pipes[2].cfg.vocab)))
+    r1 = ens("what is the capital of france", max_new_tokens=12, seed=3)
+    r2 = ens("what is the capital of france", max_new_tokens=12, seed=3)
+    assert r1["answers"] == r2["answers"] and r1["refined"] == r2["refined"] and r1["tps"] > 0
+    assert r1["answers"] != ens("what is the capital of france", max_new_tokens=12, seed=4)["answers"]
