@@ -353,12 +353,15 @@ def run_ours(a):
     CH = a.chunk or (min(P, 2048) if world == 1 else min(P, 1024))
     max_seq = P + NEW
     n_prompts = world                       # weak scaling: one prompt stream per stage
-    pipe = DistPipeline.load(cfg, rank, world, dev, seed=0, fast_init=True, max_rows=n_prompts, max_seq=max_seq,
-                             quant=a.quant)
-    stage = pipe.stage
-    pipe.graph_chunk = CH
     g = torch.Generator(device="cpu").manual_seed(1234)
     prompts_host = [torch.randint(0, cfg.vocab, (P,), generator=g, dtype=torch.int64).pin_memory() for _ in range(n_prompts)]
+    # SmoothQuant (alpha = 0.5) calibrated on the synthetic prompts: the first 512 tokens of prompt 0, the
+    # same at every N, run through the fp32 layers while the stage's weights are drawn
+    calib = [prompts_host[0][:512].clone()] if (a.quant == "w8a8" and cfg.gated and not cfg.bias and cfg.norm == "rms") else None
+    pipe = DistPipeline.load(cfg, rank, world, dev, seed=0, fast_init=True, max_rows=n_prompts, max_seq=max_seq,
+                             quant=a.quant, calibrate_with=calib)
+    stage = pipe.stage
+    pipe.graph_chunk = CH
     prompts_dev = [p.to(dev) for p in prompts_host]
 
     def one_step(prompts, record=None):
@@ -468,6 +471,7 @@ def run_ours(a):
             "decode_handoff": (pipe.p2p["how"] + ": peer-memory store + flag kernels (b2_p2p_send / b2_p2p_wait)") if getattr(pipe, "p2p", None)
             else ("NCCL send/recv" if world > 1 else "none (one stage)"),
             "shared_lm_head": bool(getattr(pipe, "split_head", False)),
+            "smoothquant": "alpha 0.5, activation maxima calibrated on the first 512 tokens of prompt 0" if calib else "weight-only statistics",
         }
         line.update(token_check(host_out, cfg.name, a.quant, P, NEW, bool(a.layers)))
         if not a.no_cpu_baseline and world == 1:
@@ -509,7 +513,7 @@ def token_check(host_out, model: str, quant: str, P: int, NEW: int, truncated: b
     import zlib
     sums = [zlib.crc32(row.numpy().tobytes()) for row in host_out]
     out = {"token_checksums": sums, "tokens_match_n1": None}
-    key = f"{model}|{quant}|prompt{P}|new{NEW}|seed1234"
+    key = f"{model}|{quant}|prompt{P}|new{NEW}|seed1234|calib512"
     if not truncated and os.path.exists(GOLDEN_TOKENS):
         with open(GOLDEN_TOKENS) as f:
             gold = json.load(f)

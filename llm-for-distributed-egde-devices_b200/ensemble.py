@@ -6,9 +6,10 @@ Llama-3.2-1B-Instruct in 8 bit, asks both answerers the question ONE AFTER THE O
 sequence, tokens/s = new tokens / wall time), and lets the third model merge the two answers (`refine_summary`,
 :116-138: temperature 0.5, top_k 30, top_p 0.9, repetition_penalty 1.1).  Only strings cross from model to
 model.  The two answers do not depend on each other, so here each answerer is a `Pipeline` on its own GPU(s)
-and the two `generate` calls run at the same time from two host threads (every `Stage` entry point runs on its
-own device whatever device the calling thread has current); the refiner follows on a third GPU or on one of
-the two.
+and the two generations run at the same time: one host thread advances both `Pipeline.generate_steps`
+generators in turn, each step only enqueues work on that pipeline's GPU, so both GPUs stay busy (every `Stage`
+entry point runs on its own device whatever device is current); the refiner follows on a third GPU or on one
+of the two.
 
 Tokenizers are the caller's (Hugging Face `AutoTokenizer` in the reference; any object with `encode(str) ->
 ids` and `decode(ids) -> str`).  The prompt wording is a constructor argument: pass the reference's own
@@ -16,7 +17,6 @@ templates (:90-94, :117-125) to reproduce its prompts exactly.
 """
 from __future__ import annotations
 
-import threading
 import time
 
 import torch
@@ -40,43 +40,45 @@ class Ensemble:
     @staticmethod
     def _generate(pipe, tok, prompt: str, max_new_tokens: int, **sampling):
         """One `get_response` (combiner_quant_updated.py:89-113): (decoded text, new tokens per second)."""
-        ids = torch.as_tensor(tok.encode(prompt), dtype=torch.int64)
-        dev = pipe.stages[0].device
-        eos = getattr(tok, "eos_token_id", None)
-        torch.cuda.synchronize(dev)
+        return Ensemble._generate_many([(pipe, tok)], prompt, max_new_tokens, [sampling])[0]
+
+    @staticmethod
+    def _generate_many(pairs, prompt: str, max_new_tokens: int, samplings):
+        """`get_response` for several (pipeline, tokenizer) pairs AT THE SAME TIME from one host thread: every
+        pipeline's `generate_steps` only enqueues work on its own GPU(s), so advancing the generators in turn keeps all
+        of them busy; a pipeline's tokens/s is its new tokens over the time from the common start to ITS last token."""
+        its, ids_len, out = [], [], [None] * len(pairs)
+        for pipe, tok in pairs:
+            torch.cuda.synchronize(pipe.stages[0].device)
         t0 = time.perf_counter()
-        out = pipe.generate(ids, max_new_tokens=max_new_tokens, do_sample=True, eos_token_id=eos, **sampling).cpu()
-        dt = time.perf_counter() - t0
-        n_new = int(out.shape[0]) - int(ids.shape[0])
-        return tok.decode(out.tolist()).strip(), (n_new / dt if dt > 0 else 0.0)
+        for (pipe, tok), smp in zip(pairs, samplings):
+            ids = torch.as_tensor(tok.encode(prompt), dtype=torch.int64)
+            ids_len.append(int(ids.shape[0]))
+            its.append(pipe.generate_steps(ids, max_new_tokens=max_new_tokens, do_sample=True,
+                                           eos_token_id=getattr(tok, "eos_token_id", None), **smp))
+        live = list(range(len(pairs)))
+        while live:
+            for k in list(live):
+                try:
+                    next(its[k])
+                except StopIteration as done:
+                    seq = done.value.cpu()                      # waits for this pipeline's GPU only
+                    dt = time.perf_counter() - t0
+                    n_new = int(seq.shape[0]) - ids_len[k]
+                    out[k] = (pairs[k][1].decode(seq.tolist()).strip(), n_new / dt if dt > 0 else 0.0)
+                    live.remove(k)
+        return out
 
     def answers(self, question: str, max_new_tokens: int = 200, temperature: float = 0.7, top_k: int = 50, top_p: float = 0.9,
                 repetition_penalty: float = 1.1, seed: int = 0, concurrent: bool = True):
-        """All answerers on the same question; returns [(answer, tokens_per_second)] in answerer order."""
+        """All answerers on the same question; returns [(answer, tokens_per_second)] in answerer order.
+        concurrent=False runs them one after the other, as the reference does (:197, :200)."""
         prompt = self.answer_prompt.format(question=question.strip())
-        out = [None] * len(self.answerers)
-        errs = []
-
-        def work(i):
-            try:
-                pipe, tok = self.answerers[i]
-                out[i] = self._generate(pipe, tok, prompt, max_new_tokens, temperature=temperature, top_k=top_k, top_p=top_p,
-                                        repetition_penalty=repetition_penalty, seed=seed + i)
-            except Exception as e:      # noqa: BLE001 -- re-raised in the calling thread
-                errs.append(e)
-        devs = [str(p_.stages[0].device) for p_, _ in self.answerers]
-        if concurrent and len(set(devs)) == len(devs):     # same GPU: nothing to gain, and one stream would interleave them
-            ts = [threading.Thread(target=work, args=(i,)) for i in range(len(self.answerers))]
-            for t in ts:
-                t.start()
-            for t in ts:
-                t.join()
-        else:
-            for i in range(len(self.answerers)):
-                work(i)
-        if errs:
-            raise errs[0]
-        return out
+        smp = [dict(temperature=temperature, top_k=top_k, top_p=top_p, repetition_penalty=repetition_penalty, seed=seed + i)
+               for i in range(len(self.answerers))]
+        if concurrent:
+            return self._generate_many(self.answerers, prompt, max_new_tokens, smp)
+        return [self._generate_many([pr], prompt, max_new_tokens, [sm])[0] for pr, sm in zip(self.answerers, smp)]
 
     def refine(self, ans1: str, ans2: str, reference: str | None, max_new_tokens: int = 200, seed: int = 0) -> str:
         """`refine_summary` (combiner_quant_updated.py:116-138) with its fixed sampling parameters."""

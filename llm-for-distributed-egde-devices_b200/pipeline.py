@@ -111,7 +111,6 @@ class Pipeline:
         rows = np.arange(B) if rows is None else np.asarray(rows)
         return self._run(tokens, caches, np.asarray(positions), rows if B > 1 else np.asarray(rows[:1]), "last")
 
-    @torch.no_grad()
     def generate(self, input_ids, max_new_tokens: int = 32, do_sample: bool = False, chunk: int = 512,
                  max_seq: int | None = None, caches=None, eos_token_id=None, pad_token_id=None, **sample_kwargs):
         """Continuation of one prompt; returns prompt + new tokens (int64, on the device), like
@@ -121,6 +120,19 @@ class Pipeline:
         EOS token produced.  The decode loop stays asynchronous; the host looks for an EOS every 8 steps.
         pad_token_id is accepted for call compatibility (one sequence is never padded).
         Sampling note: top_k <= 0 ("off" in HF) or > 1024 is capped at 1024 candidates (b2_sample)."""
+        it = self.generate_steps(input_ids, max_new_tokens, do_sample, chunk, max_seq, caches, eos_token_id, **sample_kwargs)
+        while True:
+            try:
+                next(it)
+            except StopIteration as done:
+                return done.value
+
+    def generate_steps(self, input_ids, max_new_tokens: int = 32, do_sample: bool = False, chunk: int = 512,
+                       max_seq: int | None = None, caches=None, eos_token_id=None, **sample_kwargs):
+        """`generate` as a generator: yields after the prefill has been enqueued and after every decode step has been
+        enqueued (nothing waits for the GPU in between unless an EOS check is due); the generator's return value is
+        generate's result.  Lets ONE host thread keep several pipelines on several GPUs busy at the same time by
+        advancing them in turn (ensemble.py)."""
         temperature = float(sample_kwargs.pop("temperature", 1.0))
         top_k = int(sample_kwargs.pop("top_k", 50))
         top_p = float(sample_kwargs.pop("top_p", 1.0))
@@ -128,43 +140,47 @@ class Pipeline:
         seed = int(sample_kwargs.pop("seed", 0))
         if sample_kwargs:
             raise TypeError(f"unsupported generate() arguments: {sorted(sample_kwargs)}")
-        dev = self.stages[0].device
-        ids = torch.as_tensor(input_ids, dtype=torch.int64).view(-1).to(dev)
-        T = int(ids.shape[0])
-        max_seq = max_seq or min(self.cfg.max_pos, T + max_new_tokens)
-        if T + max_new_tokens > max_seq:
-            raise ValueError("prompt + max_new_tokens exceeds max_seq")
-        eos = None
-        if eos_token_id is not None:
-            eos = torch.as_tensor([eos_token_id] if isinstance(eos_token_id, int) else list(eos_token_id),
-                                  dtype=torch.int64, device=dev)
-        caches = caches or self.pooled_caches(1, max_seq)
-        out = torch.empty((T + max_new_tokens,), dtype=torch.int64, device=dev)
-        out[:T] = ids
-        lg = self.prefill(ids, caches, 0, 0, chunk)
+        with torch.no_grad():
+            dev = self.stages[0].device
+            ids = torch.as_tensor(input_ids, dtype=torch.int64).view(-1).to(dev)
+            T = int(ids.shape[0])
+            max_seq = max_seq or min(self.cfg.max_pos, T + max_new_tokens)
+            if T + max_new_tokens > max_seq:
+                raise ValueError("prompt + max_new_tokens exceeds max_seq")
+            eos = None
+            if eos_token_id is not None:
+                eos = torch.as_tensor([eos_token_id] if isinstance(eos_token_id, int) else list(eos_token_id),
+                                      dtype=torch.int64, device=dev)
+            caches = caches or self.pooled_caches(1, max_seq)
+            out = torch.empty((T + max_new_tokens,), dtype=torch.int64, device=dev)
+            out[:T] = ids
+            lg = self.prefill(ids, caches, 0, 0, chunk)
+        yield 0
         hist2d = out.view(1, -1)
         hlen = torch.empty((1,), dtype=torch.int32, device=dev) if do_sample else None
         n_done = max_new_tokens
         for i in range(max_new_tokens):
-            tok = out[T + i: T + i + 1]
-            with torch.cuda.device(dev):
-                lgd = lg.view(1, -1).to(dev) if lg.device != dev else lg.view(1, -1)
-                if do_sample:
-                    # the reference's call: do_sample=True, temperature, top_k, top_p, repetition_penalty
-                    # (models_quant_updated.py:84-93); the penalty sees prompt + everything generated so far
-                    hlen.fill_(T + i)
-                    ops.sample(lgd, temperature=temperature, top_k=top_k, top_p=top_p, repetition_penalty=rep, seed=seed,
-                               step=i, history=hist2d, hist_len=hlen, out=tok)
-                else:
-                    ops.argmax(lgd, out=tok)
-            self.stages[-1].launches += 1
-            if eos is not None and (i % 8 == 7 or i + 1 == max_new_tokens):
-                hit = torch.isin(out[T: T + i + 1], eos).nonzero()
-                if hit.numel():
-                    n_done = int(hit[0]) + 1
-                    break
-            if i + 1 < max_new_tokens:
-                lg = self.decode_step(tok, caches, [T + i])
+            with torch.no_grad():
+                tok = out[T + i: T + i + 1]
+                with torch.cuda.device(dev):
+                    lgd = lg.view(1, -1).to(dev) if lg.device != dev else lg.view(1, -1)
+                    if do_sample:
+                        # the reference's call: do_sample=True, temperature, top_k, top_p, repetition_penalty
+                        # (models_quant_updated.py:84-93); the penalty sees prompt + everything generated so far
+                        hlen.fill_(T + i)
+                        ops.sample(lgd, temperature=temperature, top_k=top_k, top_p=top_p, repetition_penalty=rep, seed=seed,
+                                   step=i, history=hist2d, hist_len=hlen, out=tok)
+                    else:
+                        ops.argmax(lgd, out=tok)
+                self.stages[-1].launches += 1
+                if eos is not None and (i % 8 == 7 or i + 1 == max_new_tokens):
+                    hit = torch.isin(out[T: T + i + 1], eos).nonzero()
+                    if hit.numel():
+                        n_done = int(hit[0]) + 1
+                        break
+                if i + 1 < max_new_tokens:
+                    lg = self.decode_step(tok, caches, [T + i])
+            yield i + 1
         return out[: T + n_done]
 
     @torch.no_grad()
@@ -206,13 +222,13 @@ class DistPipeline:
 
     @classmethod
     def load(cls, model, rank: int, world: int, device, seed: int = 0, fast_init: bool = True, max_rows: int = 1,
-             max_seq: int = 4096, quant: str = "w8a8"):
+             max_seq: int = 4096, quant: str = "w8a8", calibrate_with=None):
         from . import loader
         cfg = get_config(model)
         b, e = split_layers(cfg.n_layers, world)[rank]
         from_dir = loader.is_checkpoint_dir(model)
         stage = Stage.load(model if from_dir else cfg, b, e, first=(rank == 0), last=(rank == world - 1), device=device,
-                           seed=seed, fast_init=fast_init and not from_dir, quant=quant)
+                           seed=seed, fast_init=fast_init and not from_dir, quant=quant, calibrate_with=calibrate_with)
         cache = stage.new_kv_cache(max_rows, max_seq)
         self = cls(rank, world, cfg.d_model, torch.device(device), None, cfg.vocab)
         self.stage, self.cache, self.cfg = stage, cache, cfg

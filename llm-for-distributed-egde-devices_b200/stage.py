@@ -177,15 +177,18 @@ class Stage:
         if torch.device(device).type != "cuda":
             raise RuntimeError("Stage runs only on a CUDA device: the hot path has no CPU fallback")
         from_dir = loader.is_checkpoint_dir(model_dir_or_config)
+        calib_ids = None
         if calibrate_with is not None and act_stats is None:
             if fast_init and not from_dir:
-                raise ValueError("calibration needs the fp32 weights: not available with fast_init")
-            act_stats = loader.calibrate(model_dir_or_config, calibrate_with, seed, device, layers=layer_end)
+                calib_ids = calibrate_with[0]        # the fast builder calibrates while it draws the layers
+            else:
+                act_stats = loader.calibrate(model_dir_or_config, calibrate_with, seed, device, layers=layer_end)
         if from_dir:
             sw = loader.build_stage_weights_from_checkpoint(str(model_dir_or_config), layer_begin, layer_end, first, last,
                                                             device, act_stats, quant)
         elif fast_init:
-            sw = weights.build_stage_weights_fast(cfg, layer_begin, layer_end, first, last, seed, device, quant=quant)
+            sw = weights.build_stage_weights_fast(cfg, layer_begin, layer_end, first, last, seed, device, quant=quant,
+                                                  calib_ids=calib_ids)
         else:
             sw = weights.build_stage_weights(cfg, layer_begin, layer_end, first, last, seed, device, act_stats, quant=quant)
         return cls(cfg, sw, layer_begin, layer_end, device)

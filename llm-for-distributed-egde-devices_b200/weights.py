@@ -217,15 +217,32 @@ def build_stage_weights(cfg: ModelConfig, layer_begin: int, layer_end: int, firs
 
 
 def build_stage_weights_fast(cfg: ModelConfig, layer_begin: int, layer_end: int, first: bool, last: bool,
-                             seed: int = 0, device="cuda", quant: str = "w8a8") -> dict:
+                             seed: int = 0, device="cuda", quant: str = "w8a8", calib_ids=None) -> dict:
     """Same structure generated directly on `device` with torch's device RNG (benchmarks: the
     7B/13B shapes would take minutes through the CPU generator).  Statistically identical,
-    not bit-identical to build_stage_weights."""
+    not bit-identical to build_stage_weights.
+
+    calib_ids (1-D token ids): SmoothQuant calibration on the way -- the fp32 layers are run over that prompt as
+    they are drawn (loader._layer_fp32; layers below layer_begin are drawn too, forwarded and dropped), and every
+    linear of this stage is smoothed with its input's per-channel activation maxima (alpha = 0.5) instead of
+    weight-only statistics.  Every rank of a pipeline derives the same statistics for the layers it owns."""
     dev = torch.device(device)
     g = torch.Generator(device=dev)
     sw = dict(first=first, last=last, layers=[], quant=quant)
     d, F = cfg.d_model, cfg.ffn
-    for li in range(layer_begin, layer_end):
+    calib = calib_ids is not None and quant == "w8a8"
+    hcal = None
+    if calib and (cfg.bias or cfg.norm != "rms" or not cfg.gated):
+        raise ValueError("calibration inside the fast builder covers the bias-free RMSNorm families (use loader.calibrate)")
+    if calib:
+        from . import loader
+        g.manual_seed(seed * 1000003 + 100003)
+        e0 = (torch.randn(cfg.vocab, cfg.d_model, generator=g, dtype=torch.float32, device=dev) * 0.16).to(torch.float16)
+        hcal = e0[torch.as_tensor(np.asarray(calib_ids), dtype=torch.int64, device=dev)].to(torch.float32)
+        del e0
+        cos_c, sin_c = rope_table(cfg.head_dim, cfg.max_pos, cfg.rope_theta, cfg.rope_scaling, cfg.rotary_dim)
+        cos_c, sin_c = cos_c.to(dev), sin_c.to(dev)
+    for li in range(0 if calib else layer_begin, layer_end):
         g.manual_seed(seed * 1000003 + li)
 
         def rn(*shape, std=0.02):
@@ -233,8 +250,25 @@ def build_stage_weights_fast(cfg: ModelConfig, layer_begin: int, layer_end: int,
 
         w = dict(ln1_g=1.0 + rn(d, std=0.1), ln2_g=1.0 + rn(d, std=0.1))
         lw = {}
-        for wk, shape in (("wqkv", (cfg.qkv_out, d)), ("wo", (d, cfg.n_heads * cfg.head_dim)),
-                          ("wgu", (cfg.up_out, d)), ("wd", (d, F))):
+        if calib:
+            # draw the four matrices in the usual order, run the fp32 layer over the calibration prompt, then quantise
+            # with the statistics just gathered (gains rounded to fp16 first, as the kernels will read them)
+            for wk, shape in (("wqkv", (cfg.qkv_out, d)), ("wo", (d, cfg.n_heads * cfg.head_dim)),
+                              ("wgu", (cfg.up_out, d)), ("wd", (d, F))):
+                w[wk] = rn(*shape)
+            wf = dict(w, ln1_g=w["ln1_g"].to(torch.float16).float(), ln2_g=w["ln2_g"].to(torch.float16).float())
+            st = {}
+            hcal = loader._layer_fp32(cfg, wf, hcal, cos_c, sin_c, st)
+            if li < layer_begin:
+                continue
+            for wk, name in (("wqkv", "qkv"), ("wo", "o"), ("wgu", "gu"), ("wd", "d")):
+                sfx = wk[1:]
+                s_ = _smooth_vec(w[wk], st[name], ALPHA)
+                lw[wk], lw["s_" + sfx] = quantize_weight(w[wk], s_)
+                lw["sm_" + sfx] = (1.0 / s_).contiguous()
+                del w[wk]
+        for wk, shape in (() if calib else (("wqkv", (cfg.qkv_out, d)), ("wo", (d, cfg.n_heads * cfg.head_dim)),
+                                            ("wgu", (cfg.up_out, d)), ("wd", (d, F)))):
             W = rn(*shape)
             sfx = wk[1:]
             if quant == "llm_int8":

@@ -105,3 +105,22 @@ def test_calibrated_smoothing_reduces_the_w8a8_error_on_an_outlier_channel_model
     back = loader.load_stats(str(tmp_path))
     assert os.path.basename(path) == loader.STATS_FILE and len(back) == len(stats)
     assert all(torch.equal(back[li][k], stats[li][k]) for li in range(len(stats)) for k in stats[li])
+
+
+def test_fast_builder_calibration_is_the_same_on_every_rank():
+    """bench.py calibrates while the device-side builder draws the layers.  A stage that starts at layer b re-draws and
+    forwards layers 0..b-1 to get its input activations: its layers must come out identical to the same layers of a
+    single-stage build (otherwise an N-stage pipeline would not decode the tokens of one GPU), and they must differ
+    from the uncalibrated build (the statistics are used)."""
+    cfg = b200stage.get_config("tiny-gqa-test")
+    ids = np.random.default_rng(1).integers(0, cfg.vocab, 40)
+    full = weights.build_stage_weights_fast(cfg, 0, cfg.n_layers, True, True, 5, "cpu", calib_ids=ids)
+    part = weights.build_stage_weights_fast(cfg, 2, cfg.n_layers, False, True, 5, "cpu", calib_ids=ids)
+    plain = weights.build_stage_weights_fast(cfg, 0, cfg.n_layers, True, True, 5, "cpu")
+    assert len(part["layers"]) == cfg.n_layers - 2
+    for a, b in zip(part["layers"], full["layers"][2:]):
+        _same(a, b)
+    assert set(full["layers"][0]) == set(plain["layers"][0])
+    assert torch.equal(full["layers"][0]["ln1_g"], plain["layers"][0]["ln1_g"])
+    assert not torch.equal(full["layers"][1]["sm_gu"], plain["layers"][1]["sm_gu"])
+    assert torch.equal(full["lm_head"], plain["lm_head"])

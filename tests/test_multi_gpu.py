@@ -76,8 +76,8 @@ class _Tok:
 @needs2
 def test_ensemble_answerers_run_concurrently_on_two_gpus():
     """The reference's three-model pipeline (combiner_quant_updated.py:177-203) on the stage path: the Phi-shaped and the
-    NeoX-shaped answerer on two GPUs from two host threads, then the Llama-shaped refiner.  Concurrent == sequential,
-    token for token (sampling draws are counter-based, so the result does not depend on timing)."""
+    NeoX-shaped answerer on two GPUs at the same time (one host thread advancing both generators), then the Llama-shaped
+    refiner.  Concurrent == sequential, token for token."""
     import b200stage
     from b200stage.pipeline import Pipeline
     from b200stage.ensemble import Ensemble
