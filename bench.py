@@ -140,13 +140,18 @@ def _cpu_llama_int8(cfg, n_layers: int):
         m.model.embed_tokens.weight.normal_(0.0, 0.02, generator=g)
         m.lm_head.weight.normal_(0.0, 0.02, generator=g)
         m.model.norm.weight.fill_(1.0)
-        # buffers (rotary inv_freq) were created on the meta device: rebuild them
+        # buffers (rotary inv_freq) were created on the meta device and are garbage after to_empty: rebuild them
+        hd = cfg.head_dim
+        inv = 1.0 / (float(cfg.rope_theta) ** (torch.arange(0, hd, 2, dtype=torch.float32) / hd))
         for mod in m.modules():
-            if hasattr(mod, "inv_freq") and hasattr(mod, "rope_init_fn"):
-                inv, _ = mod.rope_init_fn(mod.config, "cpu")
-                mod.inv_freq = inv
+            if "inv_freq" in dict(mod.named_buffers(recurse=False)):
+                mod.inv_freq = inv.clone()
                 if hasattr(mod, "original_inv_freq"):
-                    mod.original_inv_freq = inv
+                    mod.original_inv_freq = inv.clone()
+                if not isinstance(getattr(mod, "attention_scaling", 1.0), float):
+                    mod.attention_scaling = 1.0
+        left = [n for n, b in m.named_buffers() if not torch.isfinite(b.float()).all()]
+        assert not left, f"uninitialised buffers: {left}"
     m.eval()
     return torch.quantization.quantize_dynamic(m, {torch.nn.Linear}, dtype=torch.qint8, inplace=True)     # try.py:205
 
