@@ -623,8 +623,12 @@ class GraphRunner:
         gc_was_on = gc.isenabled()
         gc.disable()
         try:
-            # thread_local: another host thread may be driving another pipeline (ensemble.py) and allocate meanwhile
-            with torch.cuda.device(dev), torch.cuda.graph(g, capture_error_mode="thread_local"):
+            # The capture stream must belong to THIS stage's device: torch's default capture stream is one process-wide
+            # stream on whichever device captured first, and entering it switches the current device -- a stage on
+            # another GPU would then record its kernels on the wrong device (they ran there through peer access when
+            # that happened to be enabled, and faulted when it was not).
+            # thread_local: another host thread may be driving another pipeline and allocate meanwhile.
+            with torch.cuda.device(dev), torch.cuda.graph(g, stream=torch.cuda.Stream(dev), capture_error_mode="thread_local"):
                 self.n_launch = self._run_core()
         finally:
             if gc_was_on:
