@@ -13,9 +13,10 @@
 // rows of A and HALF of the weight tile (64 + 64 B/clk), the tensor cores read the other half from the peer's
 // shared memory, and the ring is 6 stages of 32 KB instead of 4 of 48 KB.
 //
-// One cluster = 2 CTAs (ranks 0 = leader, 1 = peer), 384 threads each:
-//   warps 0..7  epilogue: TMEM lane quadrant = warp % 4, column half = warp / 4; arrive on the leader's
-//            `tempty` when a buffer is drained (remote mbarrier arrive from the peer)
+// One cluster = 2 CTAs (ranks 0 = leader, 1 = peer), EW + 4 warps each (EW = 8 epilogue warps, 16 for the act*up
+// epilogue; the roles below are given for EW = 8):
+//   warps 0..7  epilogue: TMEM lane quadrant = warp % 4, column half (quarter with 16 warps) = warp / 4; arrive on
+//            the leader's `tempty` when a buffer is drained (remote mbarrier arrive from the peer)
 //   warp 8   TMA producer (each CTA loads its own A rows and its own half of the weight tile; both signal the
 //            LEADER's `full` barrier -- cp.async.bulk.tensor ... .cta_group::2)
 //   warp 9   MMA issuer (leader only): waits `full`, issues 4 x tcgen05.mma per 128-byte k-block, commits to the
@@ -40,12 +41,18 @@ namespace b2 {
 constexpr int G2_BM = 256;       // rows per CTA pair (128 per CTA)
 constexpr int G2_BN = 256;       // columns per tile
 constexpr int G2_BK = 128;       // int8 per k-block = one 128-byte swizzle atom
-constexpr int G2_THREADS = 384;
+// epilogue warps per CTA: 8 (lane quadrant x column half); 16 for the act*up epilogue (lane quadrant x column
+// quarter), whose exp / division chains are latency-bound on two warps per scheduler: with 8 warps the epilogue of a
+// tile (~16 us) outlasted its MMAs (13.9 us) and the tensor pipe fell from 72 % to 61 % active (ncu, round 2)
+template <int EPI>
+constexpr int g2_epi_warps() { return EPI == 1 ? 16 : 8; }
+template <int EPI>
+constexpr int g2_threads() { return (g2_epi_warps<EPI>() + 4) * 32; }
 // Warp roles.  The epilogue warps take the LOW warp ids: when several warps of a scheduler are ready the SM issues
 // the highest warp id first, and an ALU-heavy epilogue (SiLU, rotary) is ready nearly every cycle -- with the
 // producer and the MMA issuer below it they waited for issue slots and the tensor pipe ran dry (measured: the gated
 // epilogue cost 14 % of the GEMM with the control warps at ids 0..2).
-constexpr int G2_WARP_TMA = 8, G2_WARP_MMA = 9, G2_WARP_ALLOC = 10;     // warps 0..7 = epilogue, 11 idle
+// warps 0..EW-1 = epilogue, EW = TMA producer, EW+1 = MMA issuer, EW+2 = TMEM allocator, EW+3 idle
 constexpr int G2_TMEM_COLS = 512;
 constexpr int G2_STAGE_BYTES = 128 * G2_BK * 2;   // per CTA: A 128 x 128 B + W 128 x 128 B
 
@@ -162,7 +169,7 @@ B2_DEVINL void dequant32(const uint32_t (&r)[32], float as, const float* __restr
 B2_DEVINL float round_h(float x) { return __half2float(__float2half_rn(x)); }
 
 template <int EPI, int HD, int STAGES>
-__global__ void __launch_bounds__(G2_THREADS, 1)
+__global__ void __launch_bounds__(g2_threads<EPI>(), 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const G2Params p) {
   using S = G2Smem<STAGES>;
   extern __shared__ uint8_t smem_raw[];
@@ -173,6 +180,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   uint64_t* tempty_bar = tfull_bar + 2;                                  // [2] leader's copy is the live one
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
 
+  constexpr int EW = g2_epi_warps<EPI>();
+  constexpr int G2_WARP_TMA = EW, G2_WARP_MMA = EW + 1, G2_WARP_ALLOC = EW + 2;
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
@@ -188,7 +197,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   }
   if (warp == G2_WARP_MMA && lane == 0) {
     for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 16); }   // 8 epilogue warps x 2 CTAs
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 2 * EW); }   // every epilogue warp of both CTAs
     mbar_fence_init();
   }
   if (warp == G2_WARP_ALLOC) tmem_alloc_pair(tmem_slot);
@@ -247,10 +256,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         umma_commit_pair(&tfull_bar[buf], 3);
       }
     }
-  } else if (warp < 8) {
+  } else if (warp < EW) {
     // ===================== epilogue (both CTAs) =====================
     const int quad = warp & 3;
-    const int half = warp >> 2;
+    const int half = warp >> 2;          // column half (PLAIN, QKV) or column quarter (GATED: 16 warps)
     int it = 0;
     for (int t = t_first; t < num_tiles; t += t_step, ++it) {
       const int mt = t % m_tiles, nt = t / m_tiles;
@@ -298,32 +307,46 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
           }
         }
       } else if (EPI == EPI_GATED) {
+        // warp (quad, half): 32 rows x the 32 MLP columns [half*32, half*32 + 32) of the tile, 16 at a time (the register
+        // budget of a 640-thread CTA is 96 per thread)
         float amax = 0.0f;
 #pragma unroll 1
-        for (int c = half * 2; c < half * 2 + 2; ++c) {
-          uint32_t rg[32], ru[32];
+        for (int c16 = 0; c16 < 2; ++c16) {
+          const int cc = half * 32 + c16 * 16;            // column inside the 128-wide gate (and up) block
+          uint32_t rg[16], ru[16];
           __syncwarp();
-          tmem_ld_32x32(taddr + c * 32, rg);            // gate: the leader's weight rows
-          tmem_ld_32x32(taddr + 128 + c * 32, ru);      // up: the peer's
+          tmem_ld_32x16(taddr + cc, rg);                  // gate: the leader's weight rows
+          tmem_ld_32x16(taddr + 128 + cc, ru);            // up: the peer's
           tmem_ld_wait();
-          const int f0 = nt * 128 + c * 32;
+          const int f0 = nt * 128 + cc;
           if (row_ok && f0 < p.F) {                           // F % 32 == 0 (checked on the host)
-            float g[32], u[32];
-            dequant32(rg, as, p.w_scale, p.bias, f0, g);
-            dequant32(ru, as, p.w_scale, p.bias, p.F + f0, u);
             float* yp = p.y32 + (long long)row * p.F + f0;
 #pragma unroll
-            for (int j = 0; j < 32; j += 4) {
+            for (int j = 0; j < 16; j += 4) {
+              const float4 wg = *reinterpret_cast<const float4*>(p.w_scale + f0 + j);
+              const float4 wu = *reinterpret_cast<const float4*>(p.w_scale + p.F + f0 + j);
+              const float wgs[4] = {wg.x, wg.y, wg.z, wg.w}, wus[4] = {wu.x, wu.y, wu.z, wu.w};
+              float bg[4] = {0.f, 0.f, 0.f, 0.f}, bu[4] = {0.f, 0.f, 0.f, 0.f};
+              if (p.bias) {
+                const uint2 b0 = *reinterpret_cast<const uint2*>(p.bias + f0 + j);
+                const uint2 b1 = *reinterpret_cast<const uint2*>(p.bias + p.F + f0 + j);
+                const float2 g0 = h2_to_f2(b0.x), g1 = h2_to_f2(b0.y), u0 = h2_to_f2(b1.x), u1 = h2_to_f2(b1.y);
+                bg[0] = g0.x; bg[1] = g0.y; bg[2] = g1.x; bg[3] = g1.y;
+                bu[0] = u0.x; bu[1] = u0.y; bu[2] = u1.x; bu[3] = u1.y;
+              }
               float y[4];
 #pragma unroll
               for (int e = 0; e < 4; ++e) {
-                const float gh = round_h(g[j + e]), uh = round_h(u[j + e]);
+                float vg = mul_rn(mul_rn((float)(int)rg[j + e], as), wgs[e]);
+                float vu = mul_rn(mul_rn((float)(int)ru[j + e], as), wus[e]);
+                if (p.bias) { vg = add_rn(vg, bg[e]); vu = add_rn(vu, bu[e]); }
+                const float gh = round_h(vg), uh = round_h(vu);
                 const float a = (p.act == 0) ? silu_det(gh) : gelu_new_det(gh);
                 y[e] = mul_rn(a, uh);
               }
               if (p.out_smooth) {
-                const float4 s = *reinterpret_cast<const float4*>(p.out_smooth + f0 + j);
-                y[0] = mul_rn(y[0], s.x); y[1] = mul_rn(y[1], s.y); y[2] = mul_rn(y[2], s.z); y[3] = mul_rn(y[3], s.w);
+                const float4 sm = *reinterpret_cast<const float4*>(p.out_smooth + f0 + j);
+                y[0] = mul_rn(y[0], sm.x); y[1] = mul_rn(y[1], sm.y); y[2] = mul_rn(y[2], sm.z); y[3] = mul_rn(y[3], sm.w);
               }
               amax = fmaxf(amax, fmaxf(fmaxf(fabsf(y[0]), fabsf(y[1])), fmaxf(fabsf(y[2]), fabsf(y[3]))));
               *reinterpret_cast<float4*>(yp + j) = make_float4(y[0], y[1], y[2], y[3]);
@@ -496,7 +519,7 @@ static int g2_launch(const int8_t* A, const int8_t* W, long long w_rows, const G
   const int pairs = tiles < max_pairs ? tiles : max_pairs;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(pairs * 2);
-  cfg.blockDim = dim3(G2_THREADS);
+  cfg.blockDim = dim3(g2_threads<EPI>());
   cfg.dynamicSmemBytes = S::TOTAL;
   cfg.stream = st;
   cudaLaunchAttribute at[1];
