@@ -332,6 +332,22 @@ int b2_p2p_wait(const unsigned int* flag, unsigned int seq, const void* src, voi
 int b2_argmax_shard(const float* logits, long long ld, long long* out_idx, float* out_val, long long idx_offset,
                     const float* other_val, const long long* other_idx, int T, int V, void* stream);
 
+/* lm_head and greedy selection in ONE launch, for decode steps of M <= 4 rows (more: B2_ERR_UNSUPPORTED, use
+ * b2_lm_head + b2_argmax_shard): the dot products of b2_lm_head (same values) feed a running winner instead of a
+ * logits round trip through HBM and a second launch.  x [M,d] fp16 (the normed hidden state), W [V,d] fp16 = rows
+ * [idx_offset, idx_offset + V) of the head; out_idx [M] = the winner's global index under b2_argmax_shard's rule
+ * (largest value, lowest index among equals), merged with another shard's winner other_val / other_idx ([M] each,
+ * both or neither); out_idx2 (or NULL) receives a second copy (the token history beside the next step's input);
+ * out_val [M] (or NULL) the winning value; logits [M,V] fp32 (or NULL) the logits themselves.
+ * scratch: b2_lm_head_argmax_scratch_bytes() of device memory, zeroed ONCE by the caller; every launch leaves it
+ * zeroed.  One scratch per stream of launches (launches sharing it must be stream-ordered).
+ * Replaces: the logits + greedy token selection at the end of every `generate` step
+ * (Code/Quantised Models/models_quant_updated.py:84-93). */
+long long b2_lm_head_argmax_scratch_bytes(void);
+int b2_lm_head_argmax(const void* x, const void* W, float* logits, int M, int V, int d, long long idx_offset,
+                      const float* other_val, const long long* other_idx, long long* out_idx, long long* out_idx2,
+                      float* out_val, void* scratch, void* stream);
+
 /* Confidence score of a forward pass: out[0] = mean over the T rows of the largest softmax probability,
  * i.e. mean_t 1 / sum_v exp(logits[t,v] - max_v logits[t,v]).  logits [T, ld >= V] fp32; row_pmax [T] fp32 scratch
  * (receives the per-row value); out [1] fp32.  Exponentials in the pinned fp32 sequence, sums in fp64 in a fixed

@@ -63,6 +63,9 @@ int argmax_rows(const float*, long long*, int, int, cudaStream_t);
 int confidence(const float*, long long, float*, float*, int, int, cudaStream_t);
 int bias_add_f32(float*, const float*, long long, int, int, cudaStream_t);
 int argmax_shard(const float*, long long, long long*, float*, long long, const float*, const long long*, int, int, cudaStream_t);
+size_t head_argmax_scratch_bytes();
+int lm_head_argmax(const void*, const void*, float*, int, int, int, long long, const float*, const long long*, long long*, long long*,
+                   float*, void*, cudaStream_t);
 }  // namespace b2
 
 #define ST(s) reinterpret_cast<cudaStream_t>(s)
@@ -138,6 +141,12 @@ int b2_p2p_wait(const unsigned int* flag, unsigned int seq, const void* src, voi
 int b2_argmax_shard(const float* logits, long long ld, long long* out_idx, float* out_val, long long idx_offset,
                     const float* other_val, const long long* other_idx, int T, int V, void* stream) {
   return b2::argmax_shard(logits, ld, out_idx, out_val, idx_offset, other_val, other_idx, T, V, ST(stream));
+}
+long long b2_lm_head_argmax_scratch_bytes(void) { return (long long)b2::head_argmax_scratch_bytes(); }
+int b2_lm_head_argmax(const void* x, const void* W, float* logits, int M, int V, int d, long long idx_offset,
+                      const float* other_val, const long long* other_idx, long long* out_idx, long long* out_idx2,
+                      float* out_val, void* scratch, void* stream) {
+  return b2::lm_head_argmax(x, W, logits, M, V, d, idx_offset, other_val, other_idx, out_idx, out_idx2, out_val, scratch, ST(stream));
 }
 int b2_bias_add_f32(float* logits, const float* bias, long long ld, int T, int V, void* stream) {
   return b2::bias_add_f32(logits, bias, ld, T, V, ST(stream));

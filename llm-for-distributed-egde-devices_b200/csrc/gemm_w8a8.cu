@@ -16,6 +16,8 @@
 // Both produce the exact int32 accumulator, so results are bit-identical between schedules and
 // against oracle/w8a8.py:gemm_w8a8.
 #include <cuda.h>
+#include <algorithm>
+#include <cstdlib>
 #include "common.cuh"
 
 namespace b2 {
@@ -515,11 +517,37 @@ int gemm_w8a8(const int8_t* A, const int8_t* W, const float* a_scale, const floa
 // =============================================================================================
 // fp16 lm_head:  logits[M,V] (fp32) = x[M,d] (fp16) . W[V,d]^T (fp16), fp32 accumulation
 // =============================================================================================
-template <int MT>
+// Greedy decode does not need the logits, only their argmax: with ARGMAX the same dot products (same code, same
+// fp32 order, hence the same values as the logits the plain kernel writes) feed a running (value, index) winner
+// instead of -- or besides -- being stored, and the last CTA to finish publishes the token.  This removes the
+// logits round trip and the separate argmax launch from every decode step (and, with the lm_head shared between
+// the first and the last pipeline stage, from the two stages that set the pipeline's tick).
+// Winner rule = argmax_kernel's: largest value, lowest index among equals, NaN never wins; -0 counts as +0.
+struct HeadArgmax {
+  unsigned long long* slots;        // [8][HEAD_SLOTS] packed winners + 1 ticket word; all zero before and after a launch
+  long long idx_offset;             // global index of row 0 of this vocabulary shard
+  const float* other_val;           // winner of another shard to merge with (or nullptr)
+  const long long* other_idx;
+  long long* out_idx;               // [M] winner's global index
+  long long* out_idx2;              // optional second copy (the token history), or nullptr
+  float* out_val;                   // optional [M] winning value, or nullptr
+};
+constexpr int HEAD_SLOTS = 32;
+B2_DEVINL unsigned long long head_key(float v, int idx) {
+  if (v != v) return 0ull;                                   // NaN: below everything, -inf included
+  v = add_rn(v, 0.0f);                                       // -0 -> +0
+  const unsigned u = __float_as_uint(v);
+  const unsigned k = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+  return ((unsigned long long)k << 32) | (unsigned long long)(0xFFFFFFFFu - (unsigned)idx);
+}
+
+template <int MT, bool ARGMAX = false>
 __global__ void __launch_bounds__(GEMV_WARPS * 32)
-gemv_f16_kernel(const __half* __restrict__ X, const __half* __restrict__ W, float* __restrict__ out, int M, int N, int K) {
+gemv_f16_kernel(const __half* __restrict__ X, const __half* __restrict__ W, float* __restrict__ out, int M, int N, int K,
+                HeadArgmax ha = HeadArgmax{}) {
   extern __shared__ uint8_t xs[];   // [MT][K] fp16
   const int kvec = K >> 3;          // 8 halves per 16 bytes
+  if (ARGMAX) asm volatile("griddepcontrol.wait;" ::: "memory");   // launched with programmatic stream serialisation
   for (int i = threadIdx.x; i < MT * kvec; i += blockDim.x) {
     const int m = i / kvec, c = i - m * kvec;
     uint4 v = make_uint4(0, 0, 0, 0);
@@ -528,8 +556,15 @@ gemv_f16_kernel(const __half* __restrict__ X, const __half* __restrict__ W, floa
   }
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n0 = (blockIdx.x * GEMV_WARPS + warp) * GEMV_ROWS;
-  if (n0 >= N) return;
+  // ARGMAX: a fixed grid of a few CTAs per SM strides over the row blocks (x is staged once per CTA, and only that
+  // many CTAs publish a winner); the plain kernel is launched with one CTA per row block, so its loop runs once.
+  const int nblk = (N + GEMV_WARPS * GEMV_ROWS - 1) / (GEMV_WARPS * GEMV_ROWS);
+  unsigned long long wkey[MT];
+#pragma unroll
+  for (int m = 0; m < MT; ++m) wkey[m] = 0ull;
+  for (int blk = blockIdx.x; blk < nblk; blk += gridDim.x) {
+  const int n0 = (blk * GEMV_WARPS + warp) * GEMV_ROWS;
+  if (n0 >= N) break;
   float acc[GEMV_ROWS][MT];
 #pragma unroll
   for (int r = 0; r < GEMV_ROWS; ++r)
@@ -570,8 +605,57 @@ gemv_f16_kernel(const __half* __restrict__ X, const __half* __restrict__ W, floa
 #pragma unroll
     for (int m = 0; m < MT; ++m) {
       const float v = warp_sum(acc[r][m]);
-      if (lane == r * MT + m && n0 + r < N && m < M) out[(long long)m * N + n0 + r] = v;
+      if (lane == r * MT + m && n0 + r < N && m < M && out != nullptr) out[(long long)m * N + n0 + r] = v;
+      if (ARGMAX && n0 + r < N) {
+        const unsigned long long k = head_key(v, n0 + r);
+        wkey[m] = k > wkey[m] ? k : wkey[m];
+      }
     }
+  }   // row blocks
+  if (ARGMAX) {
+    __shared__ unsigned long long sk[MT][GEMV_WARPS];
+    __shared__ unsigned ticket;
+    if (lane == 0) {
+#pragma unroll
+      for (int m = 0; m < MT; ++m) sk[m][warp] = wkey[m];
+    }
+    __syncthreads();
+    if (threadIdx.x < MT && threadIdx.x < M) {
+      unsigned long long k = sk[threadIdx.x][0];
+#pragma unroll
+      for (int w = 1; w < GEMV_WARPS; ++w) k = sk[threadIdx.x][w] > k ? sk[threadIdx.x][w] : k;
+      atomicMax(ha.slots + threadIdx.x * HEAD_SLOTS + (blockIdx.x % HEAD_SLOTS), k);
+      __threadfence();
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) ticket = atomicAdd(reinterpret_cast<unsigned*>(ha.slots + 8 * HEAD_SLOTS), 1u);
+    __syncthreads();
+    if (ticket != gridDim.x - 1 || warp != 0) return;
+    // the last CTA: every other CTA's winners are in the slots (fence + ticket order); fetch-and-clear them
+    __threadfence();
+    for (int m = 0; m < M; ++m) {
+      unsigned long long k = atomicExch(ha.slots + m * HEAD_SLOTS + lane, 0ull);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const unsigned long long ok = __shfl_xor_sync(0xffffffffu, k, o);
+        k = ok > k ? ok : k;
+      }
+      if (lane == 0) {
+        const unsigned kh = (unsigned)(k >> 32);
+        float best = k == 0ull ? -INFINITY : __uint_as_float((kh & 0x80000000u) ? (kh ^ 0x80000000u) : ~kh);
+        long long idx = (k == 0ull ? 0 : (long long)(0xFFFFFFFFu - (unsigned)(k & 0xFFFFFFFFull))) + ha.idx_offset;
+        if (ha.other_val != nullptr) {       // same merge as argmax_kernel
+          const float ov = ha.other_val[m];
+          const long long oi = ha.other_idx[m];
+          if (ov > best || (ov == best && oi < idx)) { best = ov; idx = oi; }
+        }
+        ha.out_idx[m] = idx;
+        if (ha.out_idx2 != nullptr) ha.out_idx2[m] = idx;
+        if (ha.out_val != nullptr) ha.out_val[m] = best;
+      }
+    }
+    if (lane == 0) *reinterpret_cast<unsigned*>(ha.slots + 8 * HEAD_SLOTS) = 0u;
+  }
 }
 
 template <int MT>
@@ -610,6 +694,50 @@ int lm_head(const void* x, const void* W, float* logits, int M, int V, int d, cu
   return launch_tc<64, 8, KIND_F16, 1>(x, W, p, st);
 }
 
+template <int MT>
+static int launch_head_argmax(const __half* X, const __half* W, float* logits, int M, int N, int K, const HeadArgmax& ha,
+                              cudaStream_t st) {
+  const size_t smem = (size_t)MT * K * 2;
+  if (smem > 200 * 1024) return ERR_TOO_LARGE;
+  const int rows_per_cta = GEMV_WARPS * GEMV_ROWS;
+  cudaLaunchConfig_t cfg = {};
+  const int nblk = (N + rows_per_cta - 1) / rows_per_cta;
+  static const int want_per_sm = [] { const char* e = getenv("B2_HEAD_CTAS_PER_SM"); const int v = e ? atoi(e) : 0; return v > 0 && v <= 16 ? v : 8; }();
+  const int per_sm = (int)std::min<size_t>(want_per_sm, (200 * 1024) / std::max<size_t>(smem, 1024));   // CTAs of 4 warps per SM
+  cfg.gridDim = dim3(std::min(nblk, device_sm_count() * std::max(per_sm, 1)));
+  cfg.blockDim = dim3(GEMV_WARPS * 32);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;   // the launch overlaps the predecessor's tail; the
+  at[0].val.programmaticStreamSerializationAllowed = 1;            // kernel waits before it touches anything
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  if (cudaLaunchKernelEx(&cfg, gemv_f16_kernel<MT, true>, X, W, logits, M, N, K, ha) != cudaSuccess) {
+    cudaGetLastError();
+    return ERR_LAUNCH;
+  }
+  return launch_status();
+}
+
+// lm_head + greedy argmax in one launch (M <= 4 rows: the GEMV path).  `scratch` = head_argmax_scratch_bytes() of
+// device memory, zeroed once by the caller; every launch leaves it zeroed again.  logits may be nullptr.
+size_t head_argmax_scratch_bytes() { return (8 * HEAD_SLOTS + 1) * sizeof(unsigned long long); }
+int lm_head_argmax(const void* x, const void* W, float* logits, int M, int V, int d, long long idx_offset, const float* other_val,
+                   const long long* other_idx, long long* out_idx, long long* out_idx2, float* out_val, void* scratch,
+                   cudaStream_t st) {
+  if (M == 0) return OK;
+  if (!x || !W || !out_idx || !scratch || ((other_val == nullptr) != (other_idx == nullptr))) return ERR_NULL_PTR;
+  if (M < 0 || V <= 0 || d <= 0 || (d & 7)) return ERR_BAD_SHAPE;
+  if (M > 4) return ERR_UNSUPPORTED;                 // token batches of 5+ rows take the tensor-core tile: b2_lm_head + b2_argmax_shard
+  auto mis = [](const void* q) { return q && (reinterpret_cast<uintptr_t>(q) & 15); };
+  if (mis(x) || mis(W) || mis(logits) || (reinterpret_cast<uintptr_t>(scratch) & 7)) return ERR_BAD_ALIGN;
+  HeadArgmax ha{reinterpret_cast<unsigned long long*>(scratch), idx_offset, other_val, other_idx, out_idx, out_idx2, out_val};
+  if (M == 1) return launch_head_argmax<1>((const __half*)x, (const __half*)W, logits, M, V, d, ha, st);
+  if (M == 2) return launch_head_argmax<2>((const __half*)x, (const __half*)W, logits, M, V, d, ha, st);
+  return launch_head_argmax<4>((const __half*)x, (const __half*)W, logits, M, V, d, ha, st);
+}
+
 // One-time set-up of every instantiation (dynamic shared-memory opt-in, driver entry point), so
 // that no launch path has first-call side effects -- required before capturing CUDA graphs.
 template <int BN, int STAGES, int KIND, int CM = 1, int ABOX = BM>
@@ -644,6 +772,9 @@ int init_gemm() {
   ok &= cudaFuncSetAttribute(gemv_f16_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, big) == cudaSuccess;
   ok &= cudaFuncSetAttribute(gemv_f16_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, big) == cudaSuccess;
   ok &= cudaFuncSetAttribute(gemv_f16_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, big) == cudaSuccess;
+  ok &= cudaFuncSetAttribute(gemv_f16_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, big) == cudaSuccess;
+  ok &= cudaFuncSetAttribute(gemv_f16_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, big) == cudaSuccess;
+  ok &= cudaFuncSetAttribute(gemv_f16_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, big) == cudaSuccess;
   return ok ? OK : ERR_ARCH;
 }
 

@@ -386,6 +386,24 @@ def lm_head(x, w, out=None):
     return o
 
 
+def head_argmax_scratch(device):
+    """The zeroed scratch b2_lm_head_argmax works in (it leaves it zeroed after every launch)."""
+    return torch.zeros((int(_abi.lib().b2_lm_head_argmax_scratch_bytes()),), dtype=torch.uint8, device=device)
+
+
+def lm_head_argmax(x, w, scratch, idx_offset=0, other=None, out_idx=None, out_idx2=None, out_val=None, logits=None):
+    """Greedy token of x [M<=4,d] fp16 over the head rows w [V,d] fp16 (global indices idx_offset + row) in one launch;
+    `other` = (values [M] fp32, global indices [M] int64) of another vocabulary shard to merge with.  b2_lm_head_argmax."""
+    _cuda(x, w, scratch, out_idx, out_idx2, out_val, logits)
+    M, d = x.shape
+    V = w.shape[0]
+    oi = out_idx if out_idx is not None else torch.empty((M,), dtype=torch.int64, device=x.device)
+    ov, ox = (other if other is not None else (None, None))
+    check(_abi.lib().b2_lm_head_argmax(ptr(x), ptr(w), ptr(logits), M, V, d, int(idx_offset), ptr(ov), ptr(ox), ptr(oi), ptr(out_idx2),
+                                       ptr(out_val), ptr(scratch), stream_handle()), "b2_lm_head_argmax")
+    return oi
+
+
 def argmax(logits, out=None):
     """logits [T,V] fp32 -> int64 [T].  b2_argmax."""
     _cuda(logits)

@@ -466,6 +466,10 @@ class DistPipeline:
         multi = self.world > 1
         split = multi and getattr(self, "split_head", False)
         want = ("split" if split else "last") if self.last else "none"
+        # greedy token straight from the head's dot products (b2_lm_head_argmax) wherever the step is <= 4 rows
+        tokmode = want == "last" and all(self.stage.can_fuse_head(len(r_)) for r_ in rows_per_group)
+        if tokmode:
+            want = "token"
         runners = []
         for g in range(G):
             r = self.stage.runner(self.cache, len(rows_per_group[g]), decode=True, rows=list(rows_per_group[g]), logits=want)
@@ -517,23 +521,23 @@ class DistPipeline:
                 e.record(side)
             cur.wait_event(e)
 
-        def token_from_head(g, step):
-            """first stage, shared head: receive (hidden, upper-shard winner) of `step`, finish the argmax here."""
+        def token_from_head(g, step, also_into=None):
+            """first stage, shared head: receive (hidden, upper-shard winner) of `step`, finish the argmax here
+            (`also_into`: the graph input of the next step)."""
             msg, hn, val, idx = inbox[g]
             if P is not None:
                 ops.p2p_wait(mine[g][3], bt[g] + step + 1, err=P["err"])
                 self.stage.launches += 1
             else:
                 recv_into(msg, self.world - 1, self.tok_group, self._rs_tok, g)
-            self.stage.head_lower(hn, val, idx, gen[g][step], lg_lo[g])
+            self.stage.head_lower(hn, val, idx, gen[g][step], lg_lo[g], out_tok2=also_into)
 
         for i in range(steps):
             for g in range(G):
                 r = runners[g]
                 if multi and self.first and i > 0:
                     if split:
-                        token_from_head(g, i - 1)
-                        r.x.copy_(gen[g][i - 1].view(r.x.shape))
+                        token_from_head(g, i - 1, also_into=r.x)
                     else:
                         recv_into(gen[g][i - 1], self.world - 1, self.tok_group, self._rs_tok, g, then_copy_to=r.x)
                 elif multi and not self.first:
@@ -545,7 +549,9 @@ class DistPipeline:
                 if ev_sent[g] is not None:
                     cur.wait_event(ev_sent[g])
                 r.replay()
-                if self.last and not split:
+                if self.last and tokmode:
+                    gen[g][i].copy_(r.tok)            # (a one-stage pipeline's graph has already written the next input)
+                elif self.last and not split:
                     ops.argmax(r.out, out=gen[g][i])
                     self.stage.launches += 1
                     if self.first:

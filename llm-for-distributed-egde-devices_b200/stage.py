@@ -136,6 +136,7 @@ class Stage:
         self._scratch = None
         self._ws = None
         self._runners = {}
+        self._head_scr = None
         self.launches = 0          # kernels of ours launched (bench.py's gpu_launches claim)
         self.fuse_decode = True    # decode steps with <= 8 tokens use b2_fused_linear
         self.l2_prefetch = True    # fused decode kernels pull the head of the next weights into L2
@@ -219,7 +220,7 @@ class Stage:
     # except launch geometry that depends on T alone -> capturable in a CUDA graph.
     # ------------------------------------------------------------------------------------------
     def _core(self, buf: _Scratch, x, T: int, kv_cache: KVCache, decode: bool, dpos, dseq, dlens, row0: int,
-              max_len: int, ws, logits: str, out, trace=None, hn_out=None):
+              max_len: int, ws, logits: str, out, trace=None, hn_out=None, head_out=None):
         cfg = self.cfg
         d, H, KV, hd, F = cfg.d_model, cfg.n_heads, cfg.n_kv_heads, cfg.head_dim, cfg.ffn
         n = 0
@@ -362,6 +363,14 @@ class Stage:
         hsel = h if (logits in ("all", "split") or decode) else h[T - 1:T]
         hn = ops.norm(hsel, self.w["lnf_g"], self.w.get("lnf_b"), cfg.eps,
                       out=hn_out if hn_out is not None else buf.hn[: hsel.shape[0]])
+        if head_out is not None:
+            # greedy decode: the token (or this vocabulary shard's winner) straight from the head's dot products, no
+            # logits round trip and no second launch.  head_out = (values or None, indices, second copy or None)
+            val, idx, idx2 = head_out
+            lo = self.head_split() if logits == "split" else 0
+            ops.lm_head_argmax(hn, self.w["lm_head"][lo:], self.head_scratch(), idx_offset=lo, out_idx=idx, out_idx2=idx2,
+                               out_val=val)
+            return None, n + 2
         if logits == "split":
             # the upper vocabulary shard only: the first stage computes the lower one from the normed hidden state
             lg = ops.lm_head(hn, self.w["lm_head"][self.head_split():], out=out)
@@ -377,14 +386,32 @@ class Stage:
         pipeline stage (DistPipeline.split_head): rows [0, split) on the first stage, [split, V) on the last."""
         return (self.cfg.vocab // 2 + 7) & ~7
 
-    def head_lower(self, hn, other_val, other_idx, out_tok, lg_buf):
+    def head_scratch(self):
+        """Work area of b2_lm_head_argmax for this stage's stream of launches (zeroed once; every launch re-zeroes it)."""
+        if self._head_scr is None:
+            self._head_scr = ops.head_argmax_scratch(self.device)
+        return self._head_scr
+
+    def can_fuse_head(self, rows: int) -> bool:
+        """lm_head + greedy argmax as one launch: decode steps of up to 4 rows, heads without a bias."""
+        return rows <= 4 and "lm_head_b" not in self.w
+
+    def head_lower(self, hn, other_val, other_idx, out_tok, lg_buf, out_tok2=None):
         """First stage: logits of the lower vocabulary shard from the last stage's normed hidden state hn [B,d] (the
         embedding table doubles as lm_head when the model ties them), then the greedy token over the whole
-        vocabulary by merging with the upper shard's winner (other_val, other_idx) -> out_tok [B] int64."""
+        vocabulary by merging with the upper shard's winner (other_val, other_idx) -> out_tok [B] int64 (and a
+        second copy in out_tok2, e.g. the next step's input)."""
         if "embed" not in self.w or not self.cfg.tie_embeddings:
             raise RuntimeError("head_lower needs the first stage of a model with tied embeddings")
+        if self.can_fuse_head(hn.shape[0]):
+            ops.lm_head_argmax(hn, self.w["embed"][: self.head_split()], self.head_scratch(), other=(other_val, other_idx),
+                               out_idx=out_tok, out_idx2=out_tok2)
+            self.launches += 1
+            return out_tok
         lg = ops.lm_head(hn, self.w["embed"][: self.head_split()], out=lg_buf)
         ops.argmax_shard(lg, 0, out_idx=out_tok, other=(other_val, other_idx))
+        if out_tok2 is not None:
+            out_tok2.copy_(out_tok.view(out_tok2.shape))
         self.launches += 2
         return out_tok
 
@@ -582,8 +609,16 @@ class GraphRunner:
             nb = ops.decode_attn_workspace_bytes(T, cfg.n_heads, cfg.n_kv_heads, cfg.head_dim, self.max_len, cfg.window)
             self.ws = torch.empty((nb,), dtype=torch.uint8, device=dev) if nb else None
         n_out = T if (decode or logits in ("all", "split")) else 1
-        self.msg = self.hn_msg = self.val_msg = self.idx_msg = None
-        if stage.last and logits == "split":
+        self.msg = self.hn_msg = self.val_msg = self.idx_msg = self.tok = None
+        self.fused_head = stage.last and decode and logits in ("split", "token") and stage.can_fuse_head(T)
+        if logits == "token":
+            # greedy decode on the last stage: the graph ends in b2_lm_head_argmax -> self.tok [T] int64 (and, on a
+            # one-stage pipeline, straight into the next step's input ids); no logits are produced
+            if not self.fused_head:
+                raise ValueError("logits='token' needs a decode runner of <= 4 rows on the last stage (no lm_head bias)")
+            self.tok = torch.empty((T,), dtype=torch.int64, device=dev)
+            self.out = None
+        elif stage.last and logits == "split":
             # one message to the first stage per step: normed hidden [T,d] fp16 | shard maxima [T] fp32 | indices [T] int64
             self.out = torch.empty((n_out, cfg.vocab - stage.head_split()), dtype=torch.float32, device=dev)
             self.msg, self.hn_msg, self.val_msg, self.idx_msg = head_message(T, cfg.d_model, dev)
@@ -599,9 +634,14 @@ class GraphRunner:
         self._capture()
 
     def _run_core(self):
+        head_out = None
+        if self.fused_head:
+            head_out = (self.val_msg, self.idx_msg, None) if self.msg is not None else \
+                       (None, self.tok, self.x if self.stage.first else None)
         _, n = self.stage._core(self.buf, self.x, self.T, self.cache, self.decode, self.dpos, self.dseq, self.dlens,
-                                self.rows[0], self.max_len, self.ws, self.logits, self.out, hn_out=self.hn_msg)
-        if self.msg is not None:
+                                self.rows[0], self.max_len, self.ws, "last" if self.logits == "token" else self.logits,
+                                self.out, hn_out=self.hn_msg, head_out=head_out)
+        if self.msg is not None and not self.fused_head:
             ops.argmax_shard(self.out, self.stage.head_split(), out_idx=self.idx_msg, out_val=self.val_msg)
             n += 1
         self.dpos.add_(self.stride)

@@ -285,6 +285,59 @@ def test_embed_lm_head_argmax():
         assert np.array_equal(n(am), n(logits).argmax(-1))
 
 
+@pytest.mark.parametrize("M,V,d", [(1, 32000, 4096), (1, 16000, 4096), (2, 50257, 768), (3, 1000, 256), (4, 32001, 2048), (1, 7, 64)])
+@pytest.mark.parametrize("merge", [False, True])
+def test_lm_head_argmax_one_launch(M, V, d, merge):
+    """b2_lm_head_argmax = b2_lm_head + b2_argmax_shard, exactly: same logits, same winner (ties to the lowest
+    index), same merge with another shard's winner; the scratch comes back zeroed, so launches can follow each
+    other on one stream."""
+    r = rng(M * 7 + V + d + merge)
+    x = t((r.standard_normal((M, d)) * 0.5).astype(np.float16))
+    Wn = (r.standard_normal((V, d)) * 0.05).astype(np.float16)
+    if V > 100:                                     # exact ties: the same row at several indices, two of them the maximum
+        Wn[V - 3] = Wn[5]
+        Wn[40] = Wn[5]
+        big = (n(x)[0].astype(np.float32) * 0.1).astype(np.float16)
+        Wn[V // 2] = big
+        Wn[V // 2 - 9] = big
+    W = t(Wn)
+    off = 3000 if merge else 0
+    scratch = ops.head_argmax_scratch(DEV)
+    logits_ref = ops.lm_head(x, W)
+    other = None
+    if merge:
+        ov = n(logits_ref).max(-1).astype(np.float32).copy()
+        oi = np.arange(M, dtype=np.int64) + 17
+        if M > 1:
+            ov[1] = np.float32(-1e9)                # this row's other shard loses
+        if M > 2:
+            oi[2] = off + V + 100                   # equal value, higher index: ours wins the tie
+        other = (t(ov), t(oi))                      # (row 0: equal value, lower index -> the other shard wins)
+    idx_ref = torch.empty((M,), dtype=torch.int64, device=DEV)
+    val_ref = torch.empty((M,), dtype=torch.float32, device=DEV)
+    ops.argmax_shard(logits_ref, off, out_idx=idx_ref, out_val=val_ref, other=other)
+    for rep in range(3):
+        logits = torch.full((M, V), -7.0, dtype=torch.float32, device=DEV) if rep == 0 else None
+        idx2 = torch.full((M,), -1, dtype=torch.int64, device=DEV)
+        val = torch.empty((M,), dtype=torch.float32, device=DEV)
+        idx = ops.lm_head_argmax(x, W, scratch, idx_offset=off, other=other, out_idx2=idx2, out_val=val, logits=logits)
+        assert np.array_equal(n(idx), n(idx_ref)), (rep, n(idx), n(idx_ref))
+        assert np.array_equal(n(idx2), n(idx_ref))
+        assert np.array_equal(n(val), n(val_ref))
+        if logits is not None:
+            assert np.array_equal(n(logits), n(logits_ref))
+        assert int(scratch.count_nonzero()) == 0
+    if V > 100 and not merge:
+        assert int(n(idx_ref)[0]) == V // 2 - 9     # the tie resolved to the lower of the two maximal rows
+
+
+def test_lm_head_argmax_refuses_wide_batches():
+    x = torch.zeros((5, 64), dtype=torch.float16, device=DEV)
+    W = torch.zeros((32, 64), dtype=torch.float16, device=DEV)
+    with pytest.raises(RuntimeError):
+        ops.lm_head_argmax(x, W, ops.head_argmax_scratch(DEV))
+
+
 @pytest.mark.parametrize("V", [1001, 50257])
 def test_lm_head_argmax_sample_any_vocabulary_size(V):
     """GPT-2's vocabulary (50257) is odd: the logits row pitch is then not a multiple of 16 bytes."""
