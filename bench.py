@@ -473,9 +473,9 @@ def run_ours(a):
             "e2e": {"value": tokens_step / e2e_s, "unit": UNIT, "h2d_bytes_per_step": n_prompts * P * 8,
                     "d2h_bytes_per_step": n_prompts * NEW * 8},
             "roofline": roof, "roofline_prefill": roof_pre, "clocks": clk, "peaks": pk["which"],
-            "decode_handoff": (pipe.p2p["how"] + ": peer-memory store + flag kernels (b2_p2p_send / b2_p2p_wait)") if getattr(pipe, "p2p", None)
+            "decode_handoff": (pipe.p2p["how"] + ": peer-memory store + flag kernels (b2_p2p_send / b2_p2p_send_multi / b2_p2p_wait)") if getattr(pipe, "p2p", None)
             else ("NCCL send/recv" if world > 1 else "none (one stage)"),
-            "shared_lm_head": bool(getattr(pipe, "split_head", False)),
+            "shared_lm_head": (getattr(pipe, "head_path", "last stage") if world > 1 else False),
             "smoothquant": "alpha 0.5, activation maxima calibrated on the first 512 tokens of prompt 0" if calib else "weight-only statistics",
         }
         line.update(token_check(host_out, cfg.name, a.quant, P, NEW, bool(a.layers)))

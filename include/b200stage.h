@@ -341,12 +341,32 @@ int b2_argmax_shard(const float* logits, long long ld, long long* out_idx, float
  * out_val [M] (or NULL) the winning value; logits [M,V] fp32 (or NULL) the logits themselves.
  * scratch: b2_lm_head_argmax_scratch_bytes() of device memory, zeroed ONCE by the caller; every launch leaves it
  * zeroed.  One scratch per stream of launches (launches sharing it must be stream-ordered).
+ * Pipeline hand-off inside the launch (each optional, NULL = off): with wait_flag the kernel first waits (bounded,
+ * about 30 s, then *err = 1) until this GPU's word *wait_flag has reached wait_seq -- x is a message another stage
+ * stores into this GPU's memory with b2_p2p_send / b2_p2p_send_multi; out_idx / out_val may point into another
+ * GPU's memory, and with notify_flag the kernel publishes notify_seq there after storing them (the receiver:
+ * b2_merge_winners).  Plain loads and stores only.
  * Replaces: the logits + greedy token selection at the end of every `generate` step
  * (Code/Quantised Models/models_quant_updated.py:84-93). */
 long long b2_lm_head_argmax_scratch_bytes(void);
 int b2_lm_head_argmax(const void* x, const void* W, float* logits, int M, int V, int d, long long idx_offset,
                       const float* other_val, const long long* other_idx, long long* out_idx, long long* out_idx2,
-                      float* out_val, void* scratch, void* stream);
+                      float* out_val, void* scratch, const unsigned int* wait_flag, unsigned int wait_seq,
+                      unsigned int* err, unsigned int* notify_flag, unsigned int notify_seq, void* stream);
+
+/* The lm_head shared by ALL stages of a pipeline (each holds V / stages rows): the last stage sends its normed hidden
+ * state to every stage at once -- b2_p2p_send_multi: CTA i stores `bytes` (multiple of 16) of src to dsts[i] and
+ * publishes seq at flags[i]; dsts / flags are HOST arrays of n <= 16 device pointers (peer-mapped or local) -- every
+ * stage runs b2_lm_head_argmax on its slice with the first stage's inbox as output, and the first stage picks the
+ * token -- b2_merge_winners: flags [W] and records [W] x 64 bytes (indices [4] int64 at +0, values [4] fp32 at +32)
+ * live in this GPU's memory; waits (bounded, then *err = 1) until every flag has reached seq, then out_idx [B <= 4]
+ * (and out_idx2, or NULL) = the global index of the largest value per row, lowest index among equals: exactly
+ * b2_argmax over the whole row.
+ * Replaces: as b2_p2p_send (Code/gRPC/server.py:13-19) and the greedy selection of `generate`. */
+int b2_p2p_send_multi(const void* src, long long bytes, void* const* dsts, unsigned int* const* flags, int n,
+                      unsigned int seq, void* stream);
+int b2_merge_winners(const unsigned int* flags, unsigned int seq, const void* records, int W, int B, long long* out_idx,
+                     long long* out_idx2, unsigned int* err, void* stream);
 
 /* Confidence score of a forward pass: out[0] = mean over the T rows of the largest softmax probability,
  * i.e. mean_t 1 / sum_v exp(logits[t,v] - max_v logits[t,v]).  logits [T, ld >= V] fp32; row_pmax [T] fp32 scratch

@@ -58,7 +58,9 @@ SIGNATURES = {
     "b2_p2p_wait": (_i, [_vp, C.c_uint, _vp, _vp, _ll, _vp, _vp]),
     "b2_argmax_shard": (_i, [_vp, _ll, _vp, _vp, _ll, _vp, _vp, _i, _i, _vp]),
     "b2_lm_head_argmax_scratch_bytes": (_ll, []),
-    "b2_lm_head_argmax": (_i, [_vp, _vp, _vp, _i, _i, _i, _ll, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "b2_lm_head_argmax": (_i, [_vp, _vp, _vp, _i, _i, _i, _ll, _vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_uint, _vp, _vp, C.c_uint, _vp]),
+    "b2_p2p_send_multi": (_i, [_vp, _ll, _vp, _vp, _i, C.c_uint, _vp]),
+    "b2_merge_winners": (_i, [_vp, C.c_uint, _vp, _i, _i, _vp, _vp, _vp, _vp]),
     "b2_bias_add_f32": (_i, [_vp, _vp, _ll, _i, _i, _vp]),
     "b2_confidence": (_i, [_vp, _ll, _vp, _vp, _i, _i, _vp]),
 }

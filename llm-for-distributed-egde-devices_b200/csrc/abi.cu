@@ -65,7 +65,9 @@ int bias_add_f32(float*, const float*, long long, int, int, cudaStream_t);
 int argmax_shard(const float*, long long, long long*, float*, long long, const float*, const long long*, int, int, cudaStream_t);
 size_t head_argmax_scratch_bytes();
 int lm_head_argmax(const void*, const void*, float*, int, int, int, long long, const float*, const long long*, long long*, long long*,
-                   float*, void*, cudaStream_t);
+                   float*, void*, const unsigned*, unsigned, unsigned*, unsigned*, unsigned, cudaStream_t);
+int p2p_send_multi(const void*, long long, void* const*, unsigned* const*, int, unsigned, cudaStream_t);
+int merge_winners(const unsigned*, unsigned, const void*, int, int, long long*, long long*, unsigned*, cudaStream_t);
 }  // namespace b2
 
 #define ST(s) reinterpret_cast<cudaStream_t>(s)
@@ -145,8 +147,18 @@ int b2_argmax_shard(const float* logits, long long ld, long long* out_idx, float
 long long b2_lm_head_argmax_scratch_bytes(void) { return (long long)b2::head_argmax_scratch_bytes(); }
 int b2_lm_head_argmax(const void* x, const void* W, float* logits, int M, int V, int d, long long idx_offset,
                       const float* other_val, const long long* other_idx, long long* out_idx, long long* out_idx2,
-                      float* out_val, void* scratch, void* stream) {
-  return b2::lm_head_argmax(x, W, logits, M, V, d, idx_offset, other_val, other_idx, out_idx, out_idx2, out_val, scratch, ST(stream));
+                      float* out_val, void* scratch, const unsigned int* wait_flag, unsigned int wait_seq, unsigned int* err,
+                      unsigned int* notify_flag, unsigned int notify_seq, void* stream) {
+  return b2::lm_head_argmax(x, W, logits, M, V, d, idx_offset, other_val, other_idx, out_idx, out_idx2, out_val, scratch, wait_flag,
+                            wait_seq, err, notify_flag, notify_seq, ST(stream));
+}
+int b2_p2p_send_multi(const void* src, long long bytes, void* const* dsts, unsigned int* const* flags, int n, unsigned int seq,
+                      void* stream) {
+  return b2::p2p_send_multi(src, bytes, dsts, flags, n, seq, ST(stream));
+}
+int b2_merge_winners(const unsigned int* flags, unsigned int seq, const void* records, int W, int B, long long* out_idx,
+                     long long* out_idx2, unsigned int* err, void* stream) {
+  return b2::merge_winners(flags, seq, records, W, B, out_idx, out_idx2, err, ST(stream));
 }
 int b2_bias_add_f32(float* logits, const float* bias, long long ld, int T, int V, void* stream) {
   return b2::bias_add_f32(logits, bias, ld, T, V, ST(stream));

@@ -531,6 +531,11 @@ struct HeadArgmax {
   long long* out_idx;               // [M] winner's global index
   long long* out_idx2;              // optional second copy (the token history), or nullptr
   float* out_val;                   // optional [M] winning value, or nullptr
+  // pipeline hand-off folded into the launch (all optional): x arrives in this GPU's inbox from another stage, which
+  // then publishes wait_seq at wait_flag; the outputs may point into another GPU's memory, and notify_seq is
+  // published at notify_flag once they are stored
+  const unsigned* wait_flag; unsigned wait_seq; unsigned* err;
+  unsigned* notify_flag; unsigned notify_seq;
 };
 constexpr int HEAD_SLOTS = 32;
 B2_DEVINL unsigned long long head_key(float v, int idx) {
@@ -547,11 +552,27 @@ gemv_f16_kernel(const __half* __restrict__ X, const __half* __restrict__ W, floa
                 HeadArgmax ha = HeadArgmax{}) {
   extern __shared__ uint8_t xs[];   // [MT][K] fp16
   const int kvec = K >> 3;          // 8 halves per 16 bytes
-  if (ARGMAX) asm volatile("griddepcontrol.wait;" ::: "memory");   // launched with programmatic stream serialisation
+  if (ARGMAX) {
+    asm volatile("griddepcontrol.wait;" ::: "memory");   // launched with programmatic stream serialisation
+    if (ha.wait_flag != nullptr) {
+      // x is on its way from another GPU: wait (bounded, about 30 s) for its sequence number in this GPU's memory
+      if (threadIdx.x == 0) {
+        unsigned v = 0;
+        bool good = false;
+        for (unsigned spins = 0; spins < (1u << 28); ++spins) {
+          asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(ha.wait_flag) : "memory");
+          if ((int)(v - ha.wait_seq) >= 0) { good = true; break; }
+          if (spins > 64) __nanosleep(100);
+        }
+        if (!good && ha.err != nullptr) atomicExch(ha.err, 1u);
+      }
+      __syncthreads();
+    }
+  }
   for (int i = threadIdx.x; i < MT * kvec; i += blockDim.x) {
     const int m = i / kvec, c = i - m * kvec;
     uint4 v = make_uint4(0, 0, 0, 0);
-    if (m < M) v = ld_v4(X + (long long)m * K + c * 8);
+    if (m < M) v = ARGMAX ? ld_cg_v4(X + (long long)m * K + c * 8) : ld_v4(X + (long long)m * K + c * 8);
     reinterpret_cast<uint4*>(xs)[i] = v;
   }
   __syncthreads();
@@ -654,7 +675,13 @@ gemv_f16_kernel(const __half* __restrict__ X, const __half* __restrict__ W, floa
         if (ha.out_val != nullptr) ha.out_val[m] = best;
       }
     }
-    if (lane == 0) *reinterpret_cast<unsigned*>(ha.slots + 8 * HEAD_SLOTS) = 0u;
+    if (lane == 0) {
+      *reinterpret_cast<unsigned*>(ha.slots + 8 * HEAD_SLOTS) = 0u;
+      if (ha.notify_flag != nullptr) {
+        __threadfence_system();
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(ha.notify_flag), "r"(ha.notify_seq) : "memory");
+      }
+    }
   }
 }
 
@@ -725,6 +752,7 @@ static int launch_head_argmax(const __half* X, const __half* W, float* logits, i
 size_t head_argmax_scratch_bytes() { return (8 * HEAD_SLOTS + 1) * sizeof(unsigned long long); }
 int lm_head_argmax(const void* x, const void* W, float* logits, int M, int V, int d, long long idx_offset, const float* other_val,
                    const long long* other_idx, long long* out_idx, long long* out_idx2, float* out_val, void* scratch,
+                   const unsigned* wait_flag, unsigned wait_seq, unsigned* err, unsigned* notify_flag, unsigned notify_seq,
                    cudaStream_t st) {
   if (M == 0) return OK;
   if (!x || !W || !out_idx || !scratch || ((other_val == nullptr) != (other_idx == nullptr))) return ERR_NULL_PTR;
@@ -732,7 +760,8 @@ int lm_head_argmax(const void* x, const void* W, float* logits, int M, int V, in
   if (M > 4) return ERR_UNSUPPORTED;                 // token batches of 5+ rows take the tensor-core tile: b2_lm_head + b2_argmax_shard
   auto mis = [](const void* q) { return q && (reinterpret_cast<uintptr_t>(q) & 15); };
   if (mis(x) || mis(W) || mis(logits) || (reinterpret_cast<uintptr_t>(scratch) & 7)) return ERR_BAD_ALIGN;
-  HeadArgmax ha{reinterpret_cast<unsigned long long*>(scratch), idx_offset, other_val, other_idx, out_idx, out_idx2, out_val};
+  HeadArgmax ha{reinterpret_cast<unsigned long long*>(scratch), idx_offset, other_val, other_idx, out_idx, out_idx2, out_val,
+                wait_flag, wait_seq, err, notify_flag, notify_seq};
   if (M == 1) return launch_head_argmax<1>((const __half*)x, (const __half*)W, logits, M, V, d, ha, st);
   if (M == 2) return launch_head_argmax<2>((const __half*)x, (const __half*)W, logits, M, V, d, ha, st);
   return launch_head_argmax<4>((const __half*)x, (const __half*)W, logits, M, V, d, ha, st);

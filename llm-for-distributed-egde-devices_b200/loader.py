@@ -218,6 +218,13 @@ def build_stage_weights_from_checkpoint(model_dir: str, layer_begin: int, layer_
     return sw
 
 
+def load_head_rows(model_dir: str, lo: int, hi: int, device="cuda") -> torch.Tensor:
+    """Rows [lo, hi) of the checkpoint's lm_head (the embedding table where the model ties them), fp16 on `device`."""
+    cfg = get_config(model_dir)
+    e = load_embed_fp32(TensorSource(model_dir), cfg, _family(model_dir), False, True)
+    return e["lm_head"][lo:hi].to(torch.float16).to(device)
+
+
 # --------------------------------------------------------------------------------------------------
 # calibration: per-input-channel activation maxima of the four linears of every layer
 # --------------------------------------------------------------------------------------------------

@@ -391,17 +391,48 @@ def head_argmax_scratch(device):
     return torch.zeros((int(_abi.lib().b2_lm_head_argmax_scratch_bytes()),), dtype=torch.uint8, device=device)
 
 
-def lm_head_argmax(x, w, scratch, idx_offset=0, other=None, out_idx=None, out_idx2=None, out_val=None, logits=None):
+def lm_head_argmax(x, w, scratch, idx_offset=0, other=None, out_idx=None, out_idx2=None, out_val=None, logits=None,
+                   wait=None, notify=None, err=None):
     """Greedy token of x [M<=4,d] fp16 over the head rows w [V,d] fp16 (global indices idx_offset + row) in one launch;
-    `other` = (values [M] fp32, global indices [M] int64) of another vocabulary shard to merge with.  b2_lm_head_argmax."""
+    `other` = (values [M] fp32, global indices [M] int64) of another vocabulary shard to merge with.
+    wait = (flag, seq): x is a message in this GPU's inbox, wait for its sequence number first; notify = (flag, seq):
+    publish seq there after storing the outputs (which may live in a peer's memory).  b2_lm_head_argmax."""
     _cuda(x, w, scratch, out_idx, out_idx2, out_val, logits)
     M, d = x.shape
     V = w.shape[0]
     oi = out_idx if out_idx is not None else torch.empty((M,), dtype=torch.int64, device=x.device)
     ov, ox = (other if other is not None else (None, None))
+    wf, ws = wait if wait is not None else (None, 0)
+    nf, ns = notify if notify is not None else (None, 0)
     check(_abi.lib().b2_lm_head_argmax(ptr(x), ptr(w), ptr(logits), M, V, d, int(idx_offset), ptr(ov), ptr(ox), ptr(oi), ptr(out_idx2),
-                                       ptr(out_val), ptr(scratch), stream_handle()), "b2_lm_head_argmax")
+                                       ptr(out_val), ptr(scratch), ptr(wf), int(ws) & 0xFFFFFFFF, ptr(err), ptr(nf),
+                                       int(ns) & 0xFFFFFFFF, stream_handle()), "b2_lm_head_argmax")
     return oi
+
+
+class MultiDst:
+    """The destinations of a b2_p2p_send_multi, prepared once: (tensor, flag) pairs -> two host pointer arrays."""
+
+    def __init__(self, pairs):
+        n = len(pairs)
+        self.n = n
+        self.keep = list(pairs)
+        self.dsts = (_abi.C.c_void_p * n)(*[t.data_ptr() for t, _ in pairs])
+        self.flags = (_abi.C.c_void_p * n)(*[f.data_ptr() for _, f in pairs])
+
+
+def p2p_send_multi(src, multi: MultiDst, seq: int):
+    """Store the bytes of local `src` to every destination of `multi` and publish `seq` at each flag.  b2_p2p_send_multi."""
+    nb = src.numel() * src.element_size()
+    check(_abi.lib().b2_p2p_send_multi(ptr(src), nb, multi.dsts, multi.flags, multi.n, int(seq) & 0xFFFFFFFF, stream_handle()),
+          "b2_p2p_send_multi")
+
+
+def merge_winners(flags, seq: int, records, W: int, B: int, out_idx, out_idx2=None, err=None):
+    """Greedy token from the winners of W vocabulary slices in this GPU's inbox (b2_merge_winners)."""
+    check(_abi.lib().b2_merge_winners(ptr(flags), int(seq) & 0xFFFFFFFF, ptr(records), int(W), int(B), ptr(out_idx), ptr(out_idx2),
+                                      ptr(err), stream_handle()), "b2_merge_winners")
+    return out_idx
 
 
 def argmax(logits, out=None):

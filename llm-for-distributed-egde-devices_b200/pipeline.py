@@ -14,6 +14,7 @@ Two forms:
 from __future__ import annotations
 
 import os
+import sys
 
 import numpy as np
 import torch
@@ -239,6 +240,15 @@ class DistPipeline:
         # half, and instead of the token the last stage returns its normed hidden state plus its shard's winner.
         # Exact: a row's argmax is the better of the two shard winners under the lowest-index tie rule.
         self.split_head = world > 1 and cfg.tie_embeddings and os.environ.get("B2_SPLIT_HEAD", "1") != "0"
+        # Deep pipelines: even a half of the head on each end stage keeps those two ~28 us per tick behind the
+        # others, and with N sequences on N stages the ring ticks at the pace of its slowest stage
+        # (tools/tick_probe.py).  ring_head: EVERY stage holds vocab / stages rows of the head; the last stage sends
+        # its normed hidden state to all of them at once, each finds its slice's winner, and the first stage merges
+        # the winners (_decode_stream_ring).  Measured on Llama-2-7B: 8 stages 57.4k vs 56.7k tok/s, 4 stages 31.71k
+        # vs 31.74k (the three extra small launches per tick cost what the balance gains), so it is the default
+        # from five stages up.  B2_RING_HEAD=0 turns it off, =2 uses it from two stages up (the tests do).
+        rh = os.environ.get("B2_RING_HEAD", "1")
+        self.ring_head = rh != "0" and world > (1 if rh == "2" else 4) and not cfg.head_bias
         self.fwd = lambda x, pos, seq, lg: stage.forward_auto(x, cache, pos, seq, logits=lg,
                                                               graph_chunk=self.graph_chunk)
         if world > 1:
@@ -263,12 +273,21 @@ class DistPipeline:
         slot = (2 * self.d + 16 + 255) & ~255
         off_head, off_flags = R * slot, 2 * R * slot
         nbytes = off_flags + 2 * R * 4 + 256
+        # the lm_head shared by all stages (ring_head): per row a slot for the last stage's normed hidden state; per
+        # group and stage a 64-byte winner record (read on the first stage only) and a flag; per group a flag for hn
+        W = self.world
+        off_hn = (nbytes + 255) & ~255
+        off_win = off_hn + R * slot
+        off_wflag = off_win + R * W * 64
+        off_nflag = off_wflag + ((R * W * 4 + 255) & ~255)
+        nbytes = off_nflag + R * 4 + 256
 
         def agree(ok: bool) -> bool:       # every rank takes the same branch
             t = torch.tensor([1 if ok else 0], dtype=torch.int32, device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MIN)
             return bool(t.item())
-        need = sorted({0 if self.last else self.rank + 1})          # the one peer this rank stores into
+        ring = bool(getattr(self, "ring_head", False))
+        need = sorted(set(range(self.world)) - {self.rank}) if ring else sorted({0 if self.last else self.rank + 1})   # peers this rank stores into
         buf, peers, how = None, {}, None
         try:
             import torch.distributed._symmetric_memory as symm
@@ -298,8 +317,10 @@ class DistPipeline:
         torch.cuda.synchronize(dev)
         dist.barrier()
         err = torch.zeros((1,), dtype=torch.int32, device=dev)
-        self.p2p = dict(buf=buf, peer=peers[need[0]], slot=slot, off_head=off_head, off_flags=off_flags, rows=R, how=how,
-                        err=err, base_h={}, base_t={})
+        nxt = 0 if self.last else self.rank + 1
+        self.p2p = dict(buf=buf, peer=peers[nxt], slot=slot, off_head=off_head, off_flags=off_flags, rows=R, how=how,
+                        err=err, base_h={}, base_t={}, base_n={}, peers={**peers, self.rank: buf} if ring else None,
+                        off_hn=off_hn, off_win=off_win, off_wflag=off_wflag, off_nflag=off_nflag)
 
     def _p2p_views(self, buf, g: int, row0: int, B: int):
         """(hidden slot, head slot, hidden flag, head flag) of group g in `buf` (this rank's inbox or a peer's)."""
@@ -464,7 +485,12 @@ class DistPipeline:
         cur = torch.cuda.current_stream(dev)
         G = len(rows_per_group)
         multi = self.world > 1
+        P0 = getattr(self, "p2p", None) if multi else None
+        if (P0 is not None and getattr(self, "ring_head", False) and P0.get("peers") and self.world <= G <= P0["rows"]
+                and sum(len(r_) for r_ in rows_per_group) <= P0["rows"] and all(len(r_) <= 4 for r_ in rows_per_group)):
+            return self._decode_stream_ring(first_tokens, start_positions, rows_per_group, steps)
         split = multi and getattr(self, "split_head", False)
+        self.head_path = "first + last stage" if split else "last stage"
         want = ("split" if split else "last") if self.last else "none"
         # greedy token straight from the head's dot products (b2_lm_head_argmax) wherever the step is <= 4 rows
         tokmode = want == "last" and all(self.stage.can_fuse_head(len(r_)) for r_ in rows_per_group)
@@ -599,6 +625,129 @@ class DistPipeline:
             cur.wait_stream(self._ss)
             cur.wait_stream(self._ss_tok)
         return [list(gen[g].unbind(0)) for g in range(G)] if keep else None
+
+    def head_bounds(self, rank: int):
+        """Vocabulary rows [lo, hi) of the lm_head that stage `rank` holds when all stages share it."""
+        V, W = self.vocab, self.world
+        cut = lambda r: V if r >= W else ((V * r // W) & ~7)       # noqa: E731
+        return cut(rank), cut(rank + 1)
+
+    def _decode_stream_ring(self, first_tokens, start_positions, rows_per_group, steps: int):
+        """decode_stream with the lm_head shared by ALL stages (ring_head; groups >= stages, <= 4 rows per group).
+        Per tick a stage enqueues: [wait for the hidden state | on the first stage: merge the winners of the
+        previous step into the token] -> its layer graph -> [store the result into the next stage's inbox | on the
+        last stage: store the normed hidden state into EVERY stage's inbox] -> its slice of the head for the group
+        that is leaving the last stage at that moment (stage r runs W-1-r ticks ahead of the last one), as one
+        launch that waits for the hidden state, finds the slice's winner and stores it into the first stage's
+        inbox.  Every message is a peer-memory store + sequence flag; nothing here touches the host or NCCL."""
+        dev, P, W, G, rank = self.device, self.p2p, self.world, len(rows_per_group), self.rank
+        st = self.stage
+        self.head_path = "all stages"
+        runners = []
+        for g in range(G):
+            r = st.runner(self.cache, len(rows_per_group[g]), decode=True, rows=list(rows_per_group[g]),
+                          logits="norm" if self.last else "none")
+            pos = np.asarray(start_positions[g], dtype=np.int64).reshape(-1)
+            if int(pos.max()) + steps > self.cache.max_seq:
+                raise ValueError("decode would run past the KV cache capacity")
+            if not np.array_equal(pos, r.host_pos):
+                r.set_positions(pos)
+            if self.first:
+                r.x.copy_(first_tokens[g].view(r.x.shape))
+            runners.append(r)
+        Bs = [len(r_) for r_ in rows_per_group]
+        row0 = np.concatenate([[0], np.cumsum(Bs)]).astype(int)
+        gen = [torch.empty((steps, Bs[g]), dtype=torch.int64, device=dev) for g in range(G)] if self.first else None
+        slot, d, R = P["slot"], self.d, P["rows"]
+
+        def views(buf, g):
+            """group g in the inbox `buf` of some stage: hidden slot + flag, normed-hidden slot + flag"""
+            hs = buf[int(row0[g]) * slot: int(row0[g]) * slot + Bs[g] * d * 2]
+            hf = buf[P["off_flags"]: P["off_flags"] + R * 4].view(torch.int32)[g: g + 1]
+            ns = buf[P["off_hn"] + int(row0[g]) * slot: P["off_hn"] + int(row0[g]) * slot + Bs[g] * d * 2]
+            nf = buf[P["off_nflag"]: P["off_nflag"] + R * 4].view(torch.int32)[g: g + 1]
+            return hs, hf, ns, nf
+
+        def record(buf, g, r_):
+            """stage r_'s winner record of group g in the first stage's inbox `buf`: indices [4], values [4], flag"""
+            o = P["off_win"] + (g * W + r_) * 64
+            return (buf[o: o + 32].view(torch.int64), buf[o + 32: o + 48].view(torch.float32),
+                    buf[P["off_wflag"]: P["off_wflag"] + R * W * 4].view(torch.int32)[g * W + r_: g * W + r_ + 1])
+
+        mine = [views(P["buf"], g) for g in range(G)]
+        nxt = [views(P["peer"], g) for g in range(G)] if not self.last else None
+        hn_all = [ops.MultiDst([views(P["peers"][r_], g)[2:4] for r_ in range(W)]) for g in range(G)] if self.last else None
+        rec = [record(P["peers"][0], g, rank) for g in range(G)]
+        hn_in = [mine[g][2].view(torch.float16).view(Bs[g], d) for g in range(G)]
+        if self.first:
+            my_rec = [P["buf"][P["off_win"] + g * W * 64: P["off_win"] + (g + 1) * W * 64] for g in range(G)]
+            my_wf = [P["buf"][P["off_wflag"]: P["off_wflag"] + R * W * 4].view(torch.int32)[g * W: (g + 1) * W] for g in range(G)]
+        lo, hi = self.head_bounds(rank)
+        Wslice, scratch, err = st.head_slice(lo, hi), st.head_scratch(), P["err"]
+        bh = [P["base_h"].get(g, 0) for g in range(G)]
+        bn = [P["base_n"].get(g, 0) for g in range(G)]
+        lag = W - 1 - rank
+
+        def head_slice_for(t):
+            """this stage's slice of the head for pipeline tick t = step * G + group (waits for the hidden state)"""
+            g, step = t % G, t // G
+            seq = bn[g] + step + 1
+            ops.lm_head_argmax(hn_in[g], Wslice, scratch, idx_offset=lo, out_idx=rec[g][0][: Bs[g]], out_val=rec[g][1][: Bs[g]],
+                               wait=(mine[g][3], seq), notify=(rec[g][2], seq), err=err)
+            st.launches += 1
+
+        def token(g, step, also_into):
+            ops.merge_winners(my_wf[g], bn[g] + step + 1, my_rec[g], W, Bs[g], gen[g][step], also_into, err)
+            st.launches += 1
+
+        trace = [] if os.environ.get("B2_TICK_TRACE") else None      # developer aid: where a tick's device time goes
+
+        def mark():
+            if trace is not None:
+                e = torch.cuda.Event(enable_timing=True)
+                e.record()
+                trace.append(e)
+
+        for i in range(steps):
+            for g in range(G):
+                r = runners[g]
+                mark()
+                if self.first:
+                    if i > 0:
+                        token(g, i - 1, r.x)
+                else:
+                    ops.p2p_wait(mine[g][1], bh[g] + i + 1, src=mine[g][0], dst=r.x, err=err)
+                    st.launches += 1
+                mark()
+                r.replay()
+                mark()
+                if self.last:
+                    ops.p2p_send_multi(r.hn_msg, hn_all[g], bn[g] + i + 1)
+                else:
+                    ops.p2p_send(r.out, nxt[g][0], nxt[g][1], bh[g] + i + 1)
+                st.launches += 1
+                mark()
+                if i * G + g - lag >= 0:
+                    head_slice_for(i * G + g - lag)
+        if trace is not None:
+            mark()
+            torch.cuda.synchronize(dev)
+            n_t = steps * G
+            dt = np.array([[trace[4 * k + j].elapsed_time(trace[4 * k + j + 1]) * 1e3 for j in range(4)] for k in range(n_t)])
+            dt = dt[n_t // 4:]              # steady state
+            names = ("wait/merge", "layers", "send", "head slice")
+            print(f"[rank {rank}] tick {dt.sum(1).mean():.1f} us: " + "; ".join(
+                f"{nm} mean {dt[:, j].mean():.1f} p50 {np.median(dt[:, j]):.1f} p90 {np.percentile(dt[:, j], 90):.1f}"
+                for j, nm in enumerate(names)), file=sys.stderr, flush=True)
+        for t in range(max(0, steps * G - lag), steps * G):
+            head_slice_for(t)
+        if self.first:
+            for g in range(G):
+                token(g, steps - 1, None)
+        for g in range(G):
+            P["base_h"][g] = bh[g] + steps
+            P["base_n"][g] = bn[g] + steps
+        return [list(gen[g].unbind(0)) for g in range(G)] if self.first else None
 
     def decode_round(self, tokens_per_group, positions_per_group, rows_per_group):
         """One decode step for each group (a decode_stream of a single step)."""

@@ -137,6 +137,8 @@ class Stage:
         self._ws = None
         self._runners = {}
         self._head_scr = None
+        self._head_slices = {}
+        self._origin = None
         self.launches = 0          # kernels of ours launched (bench.py's gpu_launches claim)
         self.fuse_decode = True    # decode steps with <= 8 tokens use b2_fused_linear
         self.l2_prefetch = True    # fused decode kernels pull the head of the next weights into L2
@@ -192,7 +194,9 @@ class Stage:
                                                   calib_ids=calib_ids)
         else:
             sw = weights.build_stage_weights(cfg, layer_begin, layer_end, first, last, seed, device, act_stats, quant=quant)
-        return cls(cfg, sw, layer_begin, layer_end, device)
+        st = cls(cfg, sw, layer_begin, layer_end, device)
+        st._origin = dict(model=model_dir_or_config, seed=seed, fast=bool(fast_init and not from_dir), from_dir=from_dir)
+        return st
 
     def new_kv_cache(self, rows: int, max_seq: int) -> KVCache:
         return KVCache(self.cfg, self.layer_end - self.layer_begin, rows, max_seq, self.device)
@@ -363,6 +367,8 @@ class Stage:
         hsel = h if (logits in ("all", "split") or decode) else h[T - 1:T]
         hn = ops.norm(hsel, self.w["lnf_g"], self.w.get("lnf_b"), cfg.eps,
                       out=hn_out if hn_out is not None else buf.hn[: hsel.shape[0]])
+        if logits == "norm":            # the head itself runs elsewhere (shared by all stages of the pipeline)
+            return hn, n + 1
         if head_out is not None:
             # greedy decode: the token (or this vocabulary shard's winner) straight from the head's dot products, no
             # logits round trip and no second launch.  head_out = (values or None, indices, second copy or None)
@@ -392,9 +398,31 @@ class Stage:
             self._head_scr = ops.head_argmax_scratch(self.device)
         return self._head_scr
 
+    def head_slice(self, lo: int, hi: int):
+        """Rows [lo, hi) of the model's lm_head on this stage's GPU -- every stage of a pipeline can hold one (the
+        head shared by all stages, DistPipeline.ring_head).  The last stage (and the first one of a model with tied
+        embeddings) already holds the matrix; the others read / draw their rows once."""
+        key = (int(lo), int(hi))
+        if key not in self._head_slices:
+            if self.last:
+                t = self.w["lm_head"][lo:hi]
+            elif self.first and self.cfg.tie_embeddings:
+                t = self.w["embed"][lo:hi]
+            else:
+                o = self._origin
+                if o is None:
+                    raise RuntimeError("this stage was not built by Stage.load: it cannot fetch a slice of the lm_head")
+                if o["from_dir"]:
+                    from . import loader
+                    t = loader.load_head_rows(str(o["model"]), lo, hi, self.device)
+                else:
+                    t = weights.head_rows_fp16(self.cfg, o["seed"], lo, hi, self.device, o["fast"])
+            self._head_slices[key] = t.contiguous()
+        return self._head_slices[key]
+
     def can_fuse_head(self, rows: int) -> bool:
         """lm_head + greedy argmax as one launch: decode steps of up to 4 rows, heads without a bias."""
-        return rows <= 4 and "lm_head_b" not in self.w
+        return rows <= 4 and not self.cfg.head_bias
 
     def head_lower(self, hn, other_val, other_idx, out_tok, lg_buf, out_tok2=None):
         """First stage: logits of the lower vocabulary shard from the last stage's normed hidden state hn [B,d] (the
@@ -611,7 +639,13 @@ class GraphRunner:
         n_out = T if (decode or logits in ("all", "split")) else 1
         self.msg = self.hn_msg = self.val_msg = self.idx_msg = self.tok = None
         self.fused_head = stage.last and decode and logits in ("split", "token") and stage.can_fuse_head(T)
-        if logits == "token":
+        if logits == "norm":
+            # the graph ends at the final norm: self.hn_msg [T,d] fp16 is what the last stage sends to every stage
+            if not (stage.last and decode):
+                raise ValueError("logits='norm' is a decode runner of the last stage")
+            self.hn_msg = torch.empty((T, cfg.d_model), dtype=torch.float16, device=dev)
+            self.out = None
+        elif logits == "token":
             # greedy decode on the last stage: the graph ends in b2_lm_head_argmax -> self.tok [T] int64 (and, on a
             # one-stage pipeline, straight into the next step's input ids); no logits are produced
             if not self.fused_head:

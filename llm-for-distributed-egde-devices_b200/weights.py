@@ -306,6 +306,19 @@ def build_stage_weights_fast(cfg: ModelConfig, layer_begin: int, layer_end: int,
     return sw
 
 
+def head_rows_fp16(cfg: ModelConfig, seed: int, lo: int, hi: int, device, fast: bool) -> torch.Tensor:
+    """Rows [lo, hi) of the seeded model's lm_head, fp16 on `device`, exactly as build_stage_weights (fast = False)
+    or build_stage_weights_fast gives them to the last stage: any stage of a pipeline can hold a slice of the head
+    (DistPipeline's lm_head shared by all stages)."""
+    if fast:
+        dev = torch.device(device)
+        g = torch.Generator(device=dev)
+        g.manual_seed(seed * 1000003 + 100003)
+        e = (torch.randn(cfg.vocab, cfg.d_model, generator=g, dtype=torch.float32, device=dev) * 0.16).to(torch.float16)
+        return e[lo:hi].clone()
+    return init_embed_fp32(cfg, seed)["lm_head"][lo:hi].to(torch.float16).to(device)
+
+
 def to_numpy(sw: dict) -> dict:
     """Stage weights as plain numpy arrays (the form oracle/w8a8.py consumes)."""
     def cv(v):

@@ -331,6 +331,45 @@ def test_lm_head_argmax_one_launch(M, V, d, merge):
         assert int(n(idx_ref)[0]) == V // 2 - 9     # the tie resolved to the lower of the two maximal rows
 
 
+def test_shared_head_protocol_on_one_gpu():
+    """The three launches of the head shared by all pipeline stages, with every "peer" on this GPU: the hidden state
+    goes to W inboxes at once (b2_p2p_send_multi), each slice's b2_lm_head_argmax waits for its copy (the flag is
+    already there: nothing spins), stores its winner record and publishes it, b2_merge_winners picks the token.
+    Result = b2_argmax over the whole row."""
+    r = rng(77)
+    W, B, V, d = 5, 3, 4096 + 40, 512
+    x = t((r.standard_normal((B, d)) * 0.5).astype(np.float16))
+    Wn = (r.standard_normal((V, d)) * 0.05).astype(np.float16)
+    Wn[3000] = Wn[10]                                   # equal logits in two different slices: the lower index wins
+    big = (n(x)[1].astype(np.float32) * 0.1).astype(np.float16)
+    Wn[10], Wn[3000] = big, big
+    head = t(Wn)
+    want = n(ops.argmax(ops.lm_head(x, head)))
+    assert want[1] == 10
+    cuts = [((V * k // W) & ~7) for k in range(W)] + [V]
+    inbox = torch.zeros((W, B, d), dtype=torch.float16, device=DEV)
+    nflag = torch.zeros((W,), dtype=torch.int32, device=DEV)
+    records = torch.zeros((W * 64,), dtype=torch.uint8, device=DEV)
+    wflag = torch.zeros((W,), dtype=torch.int32, device=DEV)
+    err = torch.zeros((1,), dtype=torch.int32, device=DEV)
+    scratch = ops.head_argmax_scratch(DEV)
+    md = ops.MultiDst([(inbox[k], nflag[k: k + 1]) for k in range(W)])
+    for seq in (1, 2):
+        ops.p2p_send_multi(x, md, seq)
+        for k in range(W):
+            idx = records[k * 64: k * 64 + 32].view(torch.int64)[:B]
+            val = records[k * 64 + 32: k * 64 + 48].view(torch.float32)[:B]
+            ops.lm_head_argmax(inbox[k], head[cuts[k]: cuts[k + 1]].contiguous(), scratch, idx_offset=cuts[k], out_idx=idx, out_val=val,
+                               wait=(nflag[k: k + 1], seq), notify=(wflag[k: k + 1], seq), err=err)
+        tok = torch.full((B,), -1, dtype=torch.int64, device=DEV)
+        tok2 = torch.full((B,), -1, dtype=torch.int64, device=DEV)
+        ops.merge_winners(wflag, seq, records, W, B, tok, tok2, err)
+        assert np.array_equal(n(tok), want) and np.array_equal(n(tok2), want), (seq, n(tok), want)
+        assert np.array_equal(n(nflag), np.full(W, seq)) and np.array_equal(n(wflag), np.full(W, seq))
+        assert np.array_equal(n(inbox), np.broadcast_to(n(x), (W, B, d)))
+    assert int(err.item()) == 0 and int(scratch.count_nonzero()) == 0
+
+
 def test_lm_head_argmax_refuses_wide_batches():
     x = torch.zeros((5, 64), dtype=torch.float16, device=DEV)
     W = torch.zeros((32, 64), dtype=torch.float16, device=DEV)

@@ -29,18 +29,22 @@ def _free_port():
 
 @needs2
 @pytest.mark.parametrize("model", ["tiny-llama-test", "tiny-gqa-test"])
-@pytest.mark.parametrize("split_head,handoff", [("1", "p2p"), ("1", "nccl"), ("0", "nccl")])
-def test_nccl_pipeline_tokens_identical_to_single_stage(model, split_head, handoff):
+@pytest.mark.parametrize("split_head,handoff,ring", [("1", "p2p", "2"), ("1", "p2p", "0"), ("1", "nccl", "0"), ("0", "nccl", "0")])
+def test_nccl_pipeline_tokens_identical_to_single_stage(model, split_head, handoff, ring):
     """handoff p2p: decode steps cross stages as peer-memory stores + flags (b2_p2p_send / b2_p2p_wait) when the box
-    lets the processes map each other's memory (the tool prints which hand-off ran); nccl: send/recv throughout."""
+    lets the processes map each other's memory (the tool prints which hand-off ran); nccl: send/recv throughout.
+    ring 2: the lm_head shared by ALL stages (every stage finds the winner of its vocabulary slice, the first stage
+    merges them: b2_p2p_send_multi / b2_lm_head_argmax with wait + notify / b2_merge_winners), also on two GPUs."""
     n = min(torch.cuda.device_count(), 4 if model == "tiny-gqa-test" else 2)
-    env = dict(os.environ, B2_SPLIT_HEAD=split_head, B2_HANDOFF=handoff)
+    env = dict(os.environ, B2_SPLIT_HEAD=split_head, B2_HANDOFF=handoff, B2_RING_HEAD=ring)
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
                         "--master-addr", "127.0.0.1", "--master-port", str(_free_port()),
                         os.path.join(ROOT, "tools", "check_pp_tokens.py"), model],
                        capture_output=True, text=True, timeout=600, env=env)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "pass 1:" in r.stdout and "handoff:" in r.stdout, r.stdout[-2000:]
+    if ring == "2" and "handoff: NCCL" not in r.stdout:
+        assert "lm_head: all stages" in r.stdout, r.stdout[-2000:]
     print([ln for ln in r.stdout.splitlines() if ln.startswith("handoff:")])
 
 

@@ -43,7 +43,7 @@ for rep in range(2):                           # second pass re-uses the capture
         ref = Pipeline.load(cfg, 1, devices=[dev], seed=3, fast_init=True)
         want = np.stack([ref.generate(prompts[p], max_new_tokens=NEW, chunk=16).cpu().numpy()[P:] for p in range(NP)])
         assert np.array_equal(got, want), (got, want)
-        print(f"pass {rep}: {NP} prompts x {NEW} tokens identical across {world} stages", flush=True)
+        print(f"pass {rep}: {NP} prompts x {NEW} tokens identical across {world} stages (lm_head: {getattr(pipe, 'head_path', '?')})", flush=True)
 pipe.drain()
 dist.barrier()
 dist.destroy_process_group()
