@@ -6,7 +6,7 @@ Importable as ``importlib.import_module("llm-for-distributed-egde-devices_b200")
 from .config import ModelConfig, PRESETS, get_config  # noqa: F401
 from . import _abi  # noqa: F401
 
-__all__ = ["ModelConfig", "PRESETS", "get_config", "Stage", "KVCache", "Pipeline", "build"]
+__all__ = ["ModelConfig", "PRESETS", "get_config", "Stage", "KVCache", "Pipeline", "DistPipeline", "Ensemble", "build"]
 
 
 def build(verbose: bool = False):
@@ -17,9 +17,12 @@ def __getattr__(name):   # lazy: stage/pipeline import torch
     if name in ("Stage", "KVCache"):
         from . import stage
         return getattr(stage, name)
-    if name == "Pipeline":
-        from .pipeline import Pipeline
-        return Pipeline
+    if name in ("Pipeline", "DistPipeline"):
+        from . import pipeline
+        return getattr(pipeline, name)
+    if name == "Ensemble":
+        from .ensemble import Ensemble
+        return Ensemble
     if name in ("weights", "ops", "stage", "pipeline", "rpc", "config", "loader", "ensemble"):     # b200stage.<submodule> without a prior import
         import importlib
         return importlib.import_module(f"{__name__}.{name}")

@@ -206,6 +206,39 @@ def confidence_score(pipe: Pipeline, input_ids) -> float:
 # ==============================================================================================
 # one process per GPU
 # ==============================================================================================
+def ring_head_schedule(rank: int, world: int, groups: int, steps: int):
+    """What stage `rank` of a `world`-stage pipeline enqueues, in order, for `steps` decode steps of `groups`
+    sequence groups when the lm_head is shared by all stages (DistPipeline._decode_stream_ring).  Yields
+    (op, group, step):
+      "merge"   first stage: wait for every stage's winner of (group, step), write the token (the next input)
+      "wait_h"  wait for the previous stage's hidden state of (group, step)
+      "layers"  this stage's layer graph for (group, step)
+      "send_h"  store the result into the next stage's inbox     "send_hn"  last stage: normed hidden state to ALL
+      "slice"   this stage's slice of the head for (group, step): waits for "send_hn", stores its winner on stage 0
+    Stage r runs world-1-r ticks ahead of the last stage, so its slice for the group that is leaving the last stage
+    follows its own tick that much later.  Every wait is for something an EARLIER entry of another stage's list
+    produces as long as groups >= world (tests/test_host_cpu.py runs the lists against each other)."""
+    first, last = rank == 0, rank == world - 1
+    lag = world - 1 - rank
+    for i in range(steps):
+        for g in range(groups):
+            if first:
+                if i > 0:
+                    yield ("merge", g, i - 1)
+            else:
+                yield ("wait_h", g, i)
+            yield ("layers", g, i)
+            yield ("send_hn" if last else "send_h", g, i)
+            t = i * groups + g - lag
+            if t >= 0:
+                yield ("slice", t % groups, t // groups)
+    for t in range(max(0, steps * groups - lag), steps * groups):
+        yield ("slice", t % groups, t // groups)
+    if first:
+        for g in range(groups):
+            yield ("merge", g, steps - 1)
+
+
 class DistPipeline:
     """Rank r owns stage r of `world` stages.  Hidden tiles [T,d] fp16 move r -> r+1 with
     torch.distributed send/recv (NCCL on GPUs; gloo in the CPU schedule tests); the greedy token
@@ -702,48 +735,40 @@ class DistPipeline:
 
         trace = [] if os.environ.get("B2_TICK_TRACE") else None      # developer aid: where a tick's device time goes
 
-        def mark():
+        def mark(op):
             if trace is not None:
                 e = torch.cuda.Event(enable_timing=True)
                 e.record()
-                trace.append(e)
+                trace.append((op, e))
 
-        for i in range(steps):
-            for g in range(G):
-                r = runners[g]
-                mark()
-                if self.first:
-                    if i > 0:
-                        token(g, i - 1, r.x)
-                else:
-                    ops.p2p_wait(mine[g][1], bh[g] + i + 1, src=mine[g][0], dst=r.x, err=err)
-                    st.launches += 1
-                mark()
+        for op, g, i in ring_head_schedule(rank, W, G, steps):
+            r = runners[g]
+            mark(op)
+            if op == "layers":
                 r.replay()
-                mark()
-                if self.last:
-                    ops.p2p_send_multi(r.hn_msg, hn_all[g], bn[g] + i + 1)
-                else:
-                    ops.p2p_send(r.out, nxt[g][0], nxt[g][1], bh[g] + i + 1)
+            elif op == "merge":
+                token(g, i, r.x if i + 1 < steps else None)
+            elif op == "wait_h":
+                ops.p2p_wait(mine[g][1], bh[g] + i + 1, src=mine[g][0], dst=r.x, err=err)
                 st.launches += 1
-                mark()
-                if i * G + g - lag >= 0:
-                    head_slice_for(i * G + g - lag)
+            elif op == "send_h":
+                ops.p2p_send(r.out, nxt[g][0], nxt[g][1], bh[g] + i + 1)
+                st.launches += 1
+            elif op == "send_hn":
+                ops.p2p_send_multi(r.hn_msg, hn_all[g], bn[g] + i + 1)
+                st.launches += 1
+            else:
+                head_slice_for(i * G + g)
         if trace is not None:
-            mark()
+            mark("end")
             torch.cuda.synchronize(dev)
-            n_t = steps * G
-            dt = np.array([[trace[4 * k + j].elapsed_time(trace[4 * k + j + 1]) * 1e3 for j in range(4)] for k in range(n_t)])
-            dt = dt[n_t // 4:]              # steady state
-            names = ("wait/merge", "layers", "send", "head slice")
-            print(f"[rank {rank}] tick {dt.sum(1).mean():.1f} us: " + "; ".join(
-                f"{nm} mean {dt[:, j].mean():.1f} p50 {np.median(dt[:, j]):.1f} p90 {np.percentile(dt[:, j], 90):.1f}"
-                for j, nm in enumerate(names)), file=sys.stderr, flush=True)
-        for t in range(max(0, steps * G - lag), steps * G):
-            head_slice_for(t)
-        if self.first:
-            for g in range(G):
-                token(g, steps - 1, None)
+            k0 = len(trace) // 4                      # steady state only
+            per = {}
+            for (op, e), (_, e_next) in zip(trace[k0:-1], trace[k0 + 1:]):
+                per.setdefault(op, []).append(e.elapsed_time(e_next) * 1e3)
+            n_ticks = max(1, len(per.get("layers", [])))
+            print(f"[rank {rank}] tick {sum(sum(v) for v in per.values()) / n_ticks:.1f} us: " + "; ".join(
+                f"{op} mean {np.mean(v):.1f} p90 {np.percentile(v, 90):.1f}" for op, v in per.items()), file=sys.stderr, flush=True)
         for g in range(G):
             P["base_h"][g] = bh[g] + steps
             P["base_n"][g] = bn[g] + steps

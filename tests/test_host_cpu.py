@@ -198,3 +198,80 @@ def test_two_rank_pipeline_schedule_gloo():
         assert p.exitcode == 0
     assert got[0] == want, "tokens returned to rank 0 differ from the single-process chain"
     assert got[1] == want, "tokens on the last rank differ from the single-process chain"
+
+
+# ----------------------------------------------------------------------------------------------
+# lm_head shared by all pipeline stages: the per-stage launch lists, run against each other
+# ----------------------------------------------------------------------------------------------
+def _run_ring_schedules(W, G, steps):
+    """Execute the W stages' launch lists as W in-order streams whose waits block: returns the number of launches
+    retired, or raises on a deadlock / a message overwritten before every reader has consumed it."""
+    from b200stage.pipeline import ring_head_schedule
+    lists = [list(ring_head_schedule(r, W, G, steps)) for r in range(W)]
+    pc = [0] * W
+    done = set()                                  # (rank, op, g, i)
+    readers_left = {}                             # message -> readers that still have to consume it
+
+    def ready(r, op, g, i):
+        if op == "wait_h":
+            return (r - 1, "send_h", g, i) in done
+        if op == "slice":
+            return (W - 1, "send_hn", g, i) in done
+        if op == "merge":
+            return all((q, "slice", g, i) in done for q in range(W))
+        return True
+
+    def retire(r, op, g, i):
+        # one slot per group and edge: writing step i needs step i-1 of the same group fully consumed
+        if op in ("send_h", "send_hn") and i > 0:
+            prev = ("h", r, g, i - 1) if op == "send_h" else ("hn", g, i - 1)
+            assert readers_left.get(prev, 0) == 0, (f"stage {r} overwrites {prev} before it was read", W, G)
+        if op == "slice" and i > 0:
+            assert readers_left.get(("win", g, i - 1), 0) == 0, (f"stage {r} overwrites the winners of {(g, i - 1)}", W, G)
+        if op == "send_h":
+            readers_left[("h", r, g, i)] = 1
+        elif op == "send_hn":
+            readers_left[("hn", g, i)] = W
+        elif op == "wait_h":
+            readers_left[("h", r - 1, g, i)] -= 1
+        elif op == "slice":
+            readers_left[("hn", g, i)] -= 1
+            readers_left.setdefault(("win", g, i), 1)
+        elif op == "merge":
+            readers_left[("win", g, i)] = 0
+        done.add((r, op, g, i))
+
+    total = sum(len(x) for x in lists)
+    n = 0
+    while n < total:
+        moved = False
+        for r in range(W):
+            while pc[r] < len(lists[r]) and ready(r, *lists[r][pc[r]]):
+                retire(r, *lists[r][pc[r]])
+                pc[r] += 1
+                n += 1
+                moved = True
+        assert moved, ("deadlock", W, G, steps, [lists[r][pc[r]] if pc[r] < len(lists[r]) else None for r in range(W)])
+    return n, lists
+
+
+@pytest.mark.parametrize("W,G,steps", [(2, 2, 3), (2, 3, 4), (3, 3, 1), (4, 4, 5), (4, 7, 3), (8, 8, 4), (8, 9, 2), (8, 32, 2)])
+def test_ring_head_schedule_runs_to_completion(W, G, steps):
+    n, lists = _run_ring_schedules(W, G, steps)
+    for r in range(W):
+        ops_r = lists[r]
+        assert sum(1 for o in ops_r if o[0] == "layers") == G * steps
+        assert sorted(o[1:] for o in ops_r if o[0] == "slice") == sorted((g, i) for i in range(steps) for g in range(G))
+        if r == 0:
+            assert sorted(o[1:] for o in ops_r if o[0] == "merge") == sorted((g, i) for i in range(steps) for g in range(G))
+            # a token is merged before the layers that consume it
+            for g in range(G):
+                for i in range(1, steps):
+                    assert ops_r.index(("merge", g, i - 1)) < ops_r.index(("layers", g, i))
+
+
+def test_ring_head_schedule_needs_as_many_groups_as_stages():
+    """Fewer groups than stages: a stage would wait for a hidden state that depends on a token it has not helped to
+    pick yet.  DistPipeline falls back to the two-way split there; the schedule itself must show the deadlock."""
+    with pytest.raises(AssertionError, match="deadlock"):
+        _run_ring_schedules(4, 2, 3)
