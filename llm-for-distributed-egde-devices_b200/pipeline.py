@@ -206,6 +206,13 @@ def confidence_score(pipe: Pipeline, input_ids) -> float:
 # ==============================================================================================
 # one process per GPU
 # ==============================================================================================
+def ring_head_ranks(world: int):
+    """The stages that hold a slice of the shared lm_head: from four stages up only the MIDDLE ones -- the first
+    stage (embedding, merge) and the last (final norm, the send to all) are the busy ones of a tick as it is, and a
+    slice's launch costs more than its bytes (profiles/r02_tick_trace_n8.txt) -- else all of them."""
+    return list(range(1, world - 1)) if world >= 4 else list(range(world))
+
+
 def ring_head_schedule(rank: int, world: int, groups: int, steps: int):
     """What stage `rank` of a `world`-stage pipeline enqueues, in order, for `steps` decode steps of `groups`
     sequence groups when the lm_head is shared by all stages (DistPipeline._decode_stream_ring).  Yields
@@ -215,11 +222,13 @@ def ring_head_schedule(rank: int, world: int, groups: int, steps: int):
       "layers"  this stage's layer graph for (group, step)
       "send_h"  store the result into the next stage's inbox     "send_hn"  last stage: normed hidden state to ALL
       "slice"   this stage's slice of the head for (group, step): waits for "send_hn", stores its winner on stage 0
+                (only on the stages of ring_head_ranks)
     Stage r runs world-1-r ticks ahead of the last stage, so its slice for the group that is leaving the last stage
     follows its own tick that much later.  Every wait is for something an EARLIER entry of another stage's list
     produces as long as groups >= world (tests/test_host_cpu.py runs the lists against each other)."""
     first, last = rank == 0, rank == world - 1
     lag = world - 1 - rank
+    has_slice = rank in ring_head_ranks(world)
     for i in range(steps):
         for g in range(groups):
             if first:
@@ -230,9 +239,9 @@ def ring_head_schedule(rank: int, world: int, groups: int, steps: int):
             yield ("layers", g, i)
             yield ("send_hn" if last else "send_h", g, i)
             t = i * groups + g - lag
-            if t >= 0:
+            if t >= 0 and has_slice:
                 yield ("slice", t % groups, t // groups)
-    for t in range(max(0, steps * groups - lag), steps * groups):
+    for t in range(max(0, steps * groups - lag), steps * groups if has_slice else 0):
         yield ("slice", t % groups, t // groups)
     if first:
         for g in range(groups):
@@ -275,11 +284,12 @@ class DistPipeline:
         self.split_head = world > 1 and cfg.tie_embeddings and os.environ.get("B2_SPLIT_HEAD", "1") != "0"
         # Deep pipelines: even a half of the head on each end stage keeps those two ~28 us per tick behind the
         # others, and with N sequences on N stages the ring ticks at the pace of its slowest stage
-        # (tools/tick_probe.py).  ring_head: EVERY stage holds vocab / stages rows of the head; the last stage sends
-        # its normed hidden state to all of them at once, each finds its slice's winner, and the first stage merges
-        # the winners (_decode_stream_ring).  Measured on Llama-2-7B: 8 stages 57.4k vs 56.7k tok/s, 4 stages 31.71k
-        # vs 31.74k (the three extra small launches per tick cost what the balance gains), so it is the default
-        # from five stages up.  B2_RING_HEAD=0 turns it off, =2 uses it from two stages up (the tests do).
+        # (tools/tick_probe.py).  ring_head: the MIDDLE stages (all of them below four stages) hold
+        # vocab / n rows of the head each; the last stage sends its normed hidden state to them at once, each finds
+        # its slice's winner, and the first stage merges the winners (_decode_stream_ring).  Measured on
+        # Llama-2-7B, 8 stages: 59.0k tok/s (57.4k with a slice on all eight stages) vs 56.7k with the two-way
+        # split; 4 stages, a slice on all four: 31.71k vs 31.74k, so it is the default from five stages up.
+        # B2_RING_HEAD=0 turns it off, =2 uses it from two stages up (the tests do).
         rh = os.environ.get("B2_RING_HEAD", "1")
         self.ring_head = rh != "0" and world > (1 if rh == "2" else 4) and not cfg.head_bias
         self.fwd = lambda x, pos, seq, lg: stage.forward_auto(x, cache, pos, seq, logits=lg,
@@ -660,10 +670,12 @@ class DistPipeline:
         return [list(gen[g].unbind(0)) for g in range(G)] if keep else None
 
     def head_bounds(self, rank: int):
-        """Vocabulary rows [lo, hi) of the lm_head that stage `rank` holds when all stages share it."""
-        V, W = self.vocab, self.world
-        cut = lambda r: V if r >= W else ((V * r // W) & ~7)       # noqa: E731
-        return cut(rank), cut(rank + 1)
+        """Vocabulary rows [lo, hi) of the lm_head that stage `rank` (one of ring_head_ranks) holds when the stages
+        share it."""
+        hr = ring_head_ranks(self.world)
+        V, n, k = self.vocab, len(hr), hr.index(rank)
+        cut = lambda j: V if j >= n else ((V * j // n) & ~7)       # noqa: E731
+        return cut(k), cut(k + 1)
 
     def _decode_stream_ring(self, first_tokens, start_positions, rows_per_group, steps: int):
         """decode_stream with the lm_head shared by ALL stages (ring_head; groups >= stages, <= 4 rows per group).
@@ -675,7 +687,8 @@ class DistPipeline:
         inbox.  Every message is a peer-memory store + sequence flag; nothing here touches the host or NCCL."""
         dev, P, W, G, rank = self.device, self.p2p, self.world, len(rows_per_group), self.rank
         st = self.stage
-        self.head_path = "all stages"
+        nh = len(ring_head_ranks(W))
+        self.head_path = "all stages" if nh == W else f"the middle stages ({nh} of {W})"
         runners = []
         for g in range(G):
             r = st.runner(self.cache, len(rows_per_group[g]), decode=True, rows=list(rows_per_group[g]),
@@ -701,22 +714,27 @@ class DistPipeline:
             nf = buf[P["off_nflag"]: P["off_nflag"] + R * 4].view(torch.int32)[g: g + 1]
             return hs, hf, ns, nf
 
-        def record(buf, g, r_):
-            """stage r_'s winner record of group g in the first stage's inbox `buf`: indices [4], values [4], flag"""
-            o = P["off_win"] + (g * W + r_) * 64
+        hr = ring_head_ranks(W)                       # the stages holding a slice; record k belongs to stage hr[k]
+        NH, mine_k = len(hr), (hr.index(rank) if rank in hr else None)
+
+        def record(buf, g, k):
+            """winner record k of group g in the first stage's inbox `buf`: indices [4], values [4], flag"""
+            o = P["off_win"] + (g * W + k) * 64
             return (buf[o: o + 32].view(torch.int64), buf[o + 32: o + 48].view(torch.float32),
-                    buf[P["off_wflag"]: P["off_wflag"] + R * W * 4].view(torch.int32)[g * W + r_: g * W + r_ + 1])
+                    buf[P["off_wflag"]: P["off_wflag"] + R * W * 4].view(torch.int32)[g * W + k: g * W + k + 1])
 
         mine = [views(P["buf"], g) for g in range(G)]
         nxt = [views(P["peer"], g) for g in range(G)] if not self.last else None
-        hn_all = [ops.MultiDst([views(P["peers"][r_], g)[2:4] for r_ in range(W)]) for g in range(G)] if self.last else None
-        rec = [record(P["peers"][0], g, rank) for g in range(G)]
+        hn_all = [ops.MultiDst([views(P["peers"][r_], g)[2:4] for r_ in hr]) for g in range(G)] if self.last else None
         hn_in = [mine[g][2].view(torch.float16).view(Bs[g], d) for g in range(G)]
         if self.first:
-            my_rec = [P["buf"][P["off_win"] + g * W * 64: P["off_win"] + (g + 1) * W * 64] for g in range(G)]
-            my_wf = [P["buf"][P["off_wflag"]: P["off_wflag"] + R * W * 4].view(torch.int32)[g * W: (g + 1) * W] for g in range(G)]
-        lo, hi = self.head_bounds(rank)
-        Wslice, scratch, err = st.head_slice(lo, hi), st.head_scratch(), P["err"]
+            my_rec = [P["buf"][P["off_win"] + g * W * 64: P["off_win"] + (g * W + NH) * 64] for g in range(G)]
+            my_wf = [P["buf"][P["off_wflag"]: P["off_wflag"] + R * W * 4].view(torch.int32)[g * W: g * W + NH] for g in range(G)]
+        err = P["err"]
+        if mine_k is not None:
+            rec = [record(P["peers"][0], g, mine_k) for g in range(G)]
+            lo, hi = self.head_bounds(rank)
+            Wslice, scratch = st.head_slice(lo, hi), st.head_scratch()
         bh = [P["base_h"].get(g, 0) for g in range(G)]
         bn = [P["base_n"].get(g, 0) for g in range(G)]
         lag = W - 1 - rank
@@ -730,7 +748,7 @@ class DistPipeline:
             st.launches += 1
 
         def token(g, step, also_into):
-            ops.merge_winners(my_wf[g], bn[g] + step + 1, my_rec[g], W, Bs[g], gen[g][step], also_into, err)
+            ops.merge_winners(my_wf[g], bn[g] + step + 1, my_rec[g], NH, Bs[g], gen[g][step], also_into, err)
             st.launches += 1
 
         trace = [] if os.environ.get("B2_TICK_TRACE") else None      # developer aid: where a tick's device time goes

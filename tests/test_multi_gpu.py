@@ -44,7 +44,7 @@ def test_nccl_pipeline_tokens_identical_to_single_stage(model, split_head, hando
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "pass 1:" in r.stdout and "handoff:" in r.stdout, r.stdout[-2000:]
     if ring == "2" and "handoff: NCCL" not in r.stdout:
-        assert "lm_head: all stages" in r.stdout, r.stdout[-2000:]
+        assert "lm_head: all stages" in r.stdout or "lm_head: the middle stages" in r.stdout, r.stdout[-2000:]
     print([ln for ln in r.stdout.splitlines() if ln.startswith("handoff:")])
 
 
