@@ -530,7 +530,8 @@ class DistPipeline:
         multi = self.world > 1
         P0 = getattr(self, "p2p", None) if multi else None
         if (P0 is not None and getattr(self, "ring_head", False) and P0.get("peers") and self.world <= G <= P0["rows"]
-                and sum(len(r_) for r_ in rows_per_group) <= P0["rows"] and all(len(r_) <= 4 for r_ in rows_per_group)):
+                and sum(len(r_) for r_ in rows_per_group) <= P0["rows"] and all(len(r_) == 1 for r_ in rows_per_group)):
+            # (one sequence per group: the case measured and tested on 2-8 GPUs; micro-batches keep the two-way split)
             return self._decode_stream_ring(first_tokens, start_positions, rows_per_group, steps)
         split = multi and getattr(self, "split_head", False)
         self.head_path = "first + last stage" if split else "last stage"
@@ -678,7 +679,8 @@ class DistPipeline:
         return cut(k), cut(k + 1)
 
     def _decode_stream_ring(self, first_tokens, start_positions, rows_per_group, steps: int):
-        """decode_stream with the lm_head shared by ALL stages (ring_head; groups >= stages, <= 4 rows per group).
+        """decode_stream with the lm_head shared by the stages (ring_head; groups >= stages, one sequence per group --
+        the code handles up to 4 rows per group, the dispatch in _decode_stream_graphs admits what has been measured).
         Per tick a stage enqueues: [wait for the hidden state | on the first stage: merge the winners of the
         previous step into the token] -> its layer graph -> [store the result into the next stage's inbox | on the
         last stage: store the normed hidden state into EVERY stage's inbox] -> its slice of the head for the group
