@@ -6,7 +6,8 @@
 // Why: with N prompts on N stages the decode ring is latency-bound -- a token visits every stage before the next
 // step of its sequence can start -- and a torch.distributed send/recv pair cost ~58 us per hop at 8 stages
 // (host-posted receive kernel, side streams, events) against ~230 us of compute per stage.  A peer store + flag
-// is one ~2 us kernel at each end, enqueued back to back with the stage's graph.
+// is one small kernel at each end, enqueued back to back with the stage's graph (a whole hop, store + flag ->
+// wait + fetch, measures <= 9 us on the device: tools/hop_probe.py).
 //
 // Replaces: the gRPC hop between two devices that the reference sketches (Code/gRPC/server.py:13-19,
 // client.py:7-11) for the hidden-state hand-off north_star moves onto NVLink.
