@@ -279,3 +279,17 @@ def test_ring_head_schedule_needs_as_many_groups_as_stages():
     pick yet.  DistPipeline falls back to the two-way split there; the schedule itself must show the deadlock."""
     with pytest.raises(AssertionError, match="deadlock"):
         _run_ring_schedules(4, 2, 3)
+
+
+@pytest.mark.parametrize("W", [2, 3, 4, 5, 8])
+@pytest.mark.parametrize("V", [32000, 50257, 512, 50304])
+def test_shared_head_slices_cover_the_vocabulary(W, V):
+    """head_bounds: the slices of the stages in ring_head_ranks tile [0, V) in order, every cut on a multiple of 8
+    rows (16-byte aligned fp16 rows for any d % 8 == 0), none empty."""
+    from b200stage.pipeline import DistPipeline, ring_head_ranks
+    hr = ring_head_ranks(W)
+    pipes = [DistPipeline(r, W, 64, torch.device("cpu"), None, V) for r in hr]
+    cuts = [p.head_bounds(p.rank) for p in pipes]
+    assert cuts[0][0] == 0 and cuts[-1][1] == V
+    for (lo, hi), (lo2, _) in zip(cuts, cuts[1:] + [(V, V)]):
+        assert lo < hi and hi == lo2 and lo % 8 == 0

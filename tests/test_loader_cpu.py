@@ -124,3 +124,23 @@ def test_fast_builder_calibration_is_the_same_on_every_rank():
     assert torch.equal(full["layers"][0]["ln1_g"], plain["layers"][0]["ln1_g"])
     assert not torch.equal(full["layers"][1]["sm_gu"], plain["layers"][1]["sm_gu"])
     assert torch.equal(full["lm_head"], plain["lm_head"])
+
+
+@pytest.mark.parametrize("model", ["tiny-gqa-test", "tiny-neox-test"])
+def test_head_rows_for_a_middle_stage(tmp_path, model):
+    """A stage that is neither first nor last can hold a slice of the lm_head (the head shared by the stages of a
+    deep pipeline): the rows it draws / reads are exactly the last stage's."""
+    cfg = b200stage.get_config(model)
+    seed, lo, hi = 3, 8, cfg.vocab - 16
+    last = weights.build_stage_weights(cfg, cfg.n_layers - 1, cfg.n_layers, False, True, seed, "cpu")
+    assert torch.equal(weights.head_rows_fp16(cfg, seed, lo, hi, "cpu", fast=False), last["lm_head"][lo:hi])
+    make_golden.hf_for(cfg, seed).save_pretrained(tmp_path, safe_serialization=True)
+    assert torch.equal(loader.load_head_rows(str(tmp_path), lo, hi, device="cpu"), last["lm_head"][lo:hi])
+
+
+def test_fast_builder_head_rows_match_its_last_stage():
+    cfg = b200stage.get_config("tiny-llama-test")
+    last = weights.build_stage_weights_fast(cfg, cfg.n_layers - 1, cfg.n_layers, False, True, 5, "cpu")
+    first = weights.build_stage_weights_fast(cfg, 0, 1, True, False, 5, "cpu")
+    rows = weights.head_rows_fp16(cfg, 5, 40, 200, "cpu", fast=True)
+    assert torch.equal(rows, last["lm_head"][40:200]) and torch.equal(rows, first["embed"][40:200])
