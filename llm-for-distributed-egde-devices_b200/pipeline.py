@@ -9,7 +9,9 @@ Two forms:
 * ``DistPipeline(stage)``   -- one process per GPU (torchrun); the hidden-state hand-off that the
   reference sketches as a gRPC hop between Jetsons (Code/gRPC/server.py:13-19, client.py:7-11;
   "Deploy models across Jetson ..." in Presentations/review 1.pptx) is an NCCL send/recv over
-  NVLink.  The KV cache is stage-local and never moves.
+  NVLink for prefill chunks and a peer-memory store + flag (csrc/p2p.cu) for decode steps, with the
+  lm_head shared between stages (two-way split, or one slice per middle stage on deep pipelines:
+  ``ring_head_schedule``).  The KV cache is stage-local and never moves.
 """
 from __future__ import annotations
 

@@ -577,7 +577,10 @@ class Stage:
 
     def runner(self, kv_cache: KVCache, T: int, *, decode: bool, rows=None, logits: str = "last") -> "GraphRunner":
         """CUDA-graph runner for a fixed token count: a decode step over `rows` (one token per row)
-        or a prefill chunk of T consecutive positions of cache row rows[0]."""
+        or a prefill chunk of T consecutive positions of cache row rows[0].
+        logits: "none" (hidden state out), "last" / "all" (logits), and for decode steps of the last stage "split"
+        (upper vocabulary shard's winner + normed hidden state as one message), "token" (greedy token from
+        b2_lm_head_argmax, no logits) and "norm" (stop at the final norm: the head runs on other stages)."""
         rows_t = tuple(int(r) for r in (rows if rows is not None else ([0] * (1 if decode else T))))
         if decode and len(rows_t) != T:
             raise ValueError("decode runner needs one row per token")
